@@ -1,0 +1,358 @@
+"""ctypes front end of the CPU oracle (oracle/tci_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline
+legs.  The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_ref", "libtci_oracle.so")
+
+F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE = range(7)
+INT64_MAX = np.iinfo(np.int64).max
+
+CALLBACK = C.CFUNCTYPE(C.c_double, C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "tci_oracle.cpp")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        _lib = C.CDLL(_SO)
+        _lib.orc_last_error.restype = C.c_char_p
+        _lib.orc_func_create.restype = C.c_void_p
+        _lib.orc_func_eval.restype = C.c_double
+        _lib.orc_tci_create.restype = C.c_void_p
+        _lib.orc_tci_setsize.restype = C.c_int64
+        _lib.orc_tci_maxsamplevalue.restype = C.c_double
+        _lib.orc_tci_npivoterrors.restype = C.c_int64
+    return _lib
+
+
+class OracleError(RuntimeError):
+    pass
+
+
+_MSG = {-1: "lu.L contains NaNs", -2: "lu.U contains NaNs", -3: "Error: NaN in tensor",
+        -4: "Pivot matrix is not square!"}
+
+
+def _check(st):
+    if st == 0:
+        return
+    if st in _MSG:
+        raise OracleError(_MSG[st])
+    raise OracleError(lib().orc_last_error().decode())
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def _f64(a):
+    return np.asfortranarray(np.asarray(a, dtype=np.float64))
+
+
+def submatrixargmax(A, rows, cols, mode=0):
+    """rows/cols: 1-based index lists; returns 1-based (row, col).  matrixlu.jl:46-87"""
+    A = _f64(A)
+    r = np.asarray(rows, dtype=np.int64) - 1
+    c = np.asarray(cols, dtype=np.int64) - 1
+    outr, outc = C.c_int64(), C.c_int64()
+    _check(lib().orc_submatrixargmax(_p(A, C.c_double), C.c_int64(A.shape[0]), mode, _p(r, C.c_int64), C.c_int64(len(r)),
+                                     _p(c, C.c_int64), C.c_int64(len(c)), C.byref(outr), C.byref(outc)))
+    return outr.value + 1, outc.value + 1
+
+
+class RRLU:
+    """Mirror of rrLU{Float64} (matrixlu.jl:200-207) with the accessors :716-811."""
+
+    def __init__(self, rowperm, colperm, L, U, leftorthogonal, npivot, error, pivoterrors):
+        self.rowpermutation, self.colpermutation = rowperm, colperm
+        self.L, self.U = L, U
+        self.leftorthogonal, self.npivot, self.error = leftorthogonal, npivot, error
+        self._pivoterrors = pivoterrors
+
+    def left(self, permute=True):
+        if not permute:
+            return self.L
+        out = np.empty_like(self.L)
+        out[self.rowpermutation - 1, :] = self.L
+        return out
+
+    def right(self, permute=True):
+        if not permute:
+            return self.U
+        out = np.empty_like(self.U)
+        out[:, self.colpermutation - 1] = self.U
+        return out
+
+    def rowindices(self):
+        return self.rowpermutation[: self.npivot]
+
+    def colindices(self):
+        return self.colpermutation[: self.npivot]
+
+    def pivoterrors(self):
+        return self._pivoterrors
+
+    def luci_factors(self):
+        m, n, r = self.L.shape[0], self.U.shape[1], self.npivot
+        left = np.zeros((m, r), order="F")
+        right = np.zeros((r, n), order="F")
+        L, U = _f64(self.L), _f64(self.U)
+        _check(lib().orc_luci_factors(C.c_int64(m), C.c_int64(n), C.c_int64(r), int(self.leftorthogonal),
+                                      _p(self.rowpermutation, C.c_int64), _p(self.colpermutation, C.c_int64),
+                                      _p(L, C.c_double), C.c_int64(max(m, 1)), _p(U, C.c_double), C.c_int64(max(r, 1)),
+                                      _p(left, C.c_double), _p(right, C.c_double)))
+        return left, right
+
+
+def rrlu(A, maxrank=INT64_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True):
+    A = _f64(A)
+    m, n = A.shape
+    rmax = int(min(maxrank, m, n))
+    rowperm = np.zeros(m, dtype=np.int64)
+    colperm = np.zeros(n, dtype=np.int64)
+    L = np.zeros((m, max(rmax, 1)), order="F")
+    U = np.zeros((max(rmax, 1), n), order="F")
+    pe = np.zeros(rmax + 1)
+    npivot, err = C.c_int64(), C.c_double()
+    _check(lib().orc_rrlu(_p(A, C.c_double), C.c_int64(m), C.c_int64(n), C.c_int64(m), C.c_int64(int(min(maxrank, INT64_MAX))),
+                          C.c_double(reltol), C.c_double(abstol), int(leftorthogonal), _p(rowperm, C.c_int64),
+                          _p(colperm, C.c_int64), C.byref(npivot), C.byref(err), _p(L, C.c_double), C.c_int64(m),
+                          _p(U, C.c_double), C.c_int64(max(rmax, 1)), _p(pe, C.c_double)))
+    r = npivot.value
+    return RRLU(rowperm, colperm, np.asfortranarray(L[:, :r]), np.asfortranarray(U[:r, :]), leftorthogonal, r,
+                err.value, pe[: r + 1].copy())
+
+
+def solve_right(P, B):
+    P, B = _f64(P), _f64(B)
+    X = np.zeros(B.shape, order="F")
+    _check(lib().orc_solve_right(_p(P, C.c_double), C.c_int64(P.shape[0]), _p(B, C.c_double), C.c_int64(B.shape[0]),
+                                 _p(X, C.c_double)))
+    return X
+
+
+class Func:
+    """Target function handle: a built-in kind, a dense table, or a Python callback (1-based indices)."""
+
+    def __init__(self, kind, params=(), table=None, callback=None):
+        self.kind = kind
+        p = np.asarray(params, dtype=np.float64)
+        dims = np.zeros(0, dtype=np.int32)
+        tab = np.zeros(0)
+        if kind == F_DENSE:
+            t = np.asarray(table, dtype=np.float64)
+            dims = np.asarray(t.shape, dtype=np.int32)
+            tab = np.ascontiguousarray(t.reshape(-1, order="F"))
+        self._cb = None
+        cb = C.cast(None, CALLBACK)
+        if kind == F_CALLBACK:
+            def _tramp(idx, n, _user):
+                return float(callback([idx[i] for i in range(n)]))
+            self._cb = CALLBACK(_tramp)
+            cb = self._cb
+        self.h = C.c_void_p(lib().orc_func_create(kind, _p(p, C.c_double), len(p), _p(dims, C.c_int32), len(dims),
+                                                  _p(tab, C.c_double), cb, None))
+        if not self.h:
+            raise OracleError(lib().orc_last_error().decode())
+
+    def __call__(self, idx):
+        v = np.asarray(idx, dtype=np.int32)
+        return lib().orc_func_eval(self.h, _p(v, C.c_int32), len(v))
+
+    def __del__(self):
+        try:
+            lib().orc_func_destroy(self.h)
+        except Exception:
+            pass
+
+
+def _table(sets, length):
+    a = np.asarray(sets, dtype=np.int32).reshape(len(sets), length)
+    return np.ascontiguousarray(a)
+
+
+def batchevaluate(f, localdims, left, right, M):
+    """_batchevaluate_dispatch (batcheval.jl:131-175): returns array of shape (|left|, d..., |right|)."""
+    ld = np.asarray(localdims, dtype=np.int32)
+    if len(left) == 0 or len(right) == 0:
+        return np.zeros((0,) * (M + 2))
+    nl, nr = len(left[0]), len(right[0])
+    lt, rt = _table(left, nl), _table(right, nr)
+    shape = (len(left),) + tuple(int(d) for d in ld[nl:nl + M]) + (len(right),)
+    out = np.zeros(int(np.prod(shape)))
+    _check(lib().orc_batcheval(f.h, _p(ld, C.c_int32), len(ld), _p(lt, C.c_int32), C.c_int64(len(left)), nl,
+                               _p(rt, C.c_int32), C.c_int64(len(right)), nr, M, _p(out, C.c_double)))
+    return out.reshape(shape, order="F")
+
+
+class TCI2:
+    """Handle on the oracle's TensorCI2 (tensorci2.jl:50-93).  Bond/site numbers are 1-based."""
+
+    def __init__(self, f, localdims, initialpivots=None):
+        self.f = f
+        self.localdims = np.asarray(localdims, dtype=np.int32)
+        n = len(self.localdims)
+        if initialpivots is None:
+            initialpivots = [[1] * n]
+        piv = _table(initialpivots, n) if len(initialpivots) else np.zeros((0, n), dtype=np.int32)
+        self.h = C.c_void_p(lib().orc_tci_create(f.h, _p(self.localdims, C.c_int32), n, _p(piv, C.c_int32),
+                                                 C.c_int64(len(initialpivots))))
+        if not self.h:
+            raise OracleError(lib().orc_last_error().decode())
+
+    def __del__(self):
+        try:
+            lib().orc_tci_destroy(self.h)
+        except Exception:
+            pass
+
+    def __len__(self):
+        return len(self.localdims)
+
+    def optimize(self, tolerance=1e-8, maxbonddim=INT64_MAX, maxiter=20, sweepstrategy="backandforth",
+                 normalizeerror=True, ncheckhistory=3, strictlynested=False, checkconvglobalpivot=True):
+        ranks = np.zeros(maxiter, dtype=np.int64)
+        errors = np.zeros(maxiter)
+        niter = C.c_int()
+        _check(lib().orc_tci_optimize(self.h, C.c_double(tolerance), C.c_int64(int(maxbonddim)), maxiter,
+                                      0 if sweepstrategy == "forward" else 1, int(normalizeerror), ncheckhistory,
+                                      int(strictlynested), int(checkconvglobalpivot), _p(ranks, C.c_int64),
+                                      _p(errors, C.c_double), C.byref(niter)))
+        return ranks[: niter.value].copy(), errors[: niter.value].copy()
+
+    def updatepivots(self, b, leftorthogonal, reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX):
+        _check(lib().orc_tci_updatepivots(self.h, b, int(leftorthogonal), C.c_double(reltol), C.c_double(abstol),
+                                          C.c_int64(int(maxbonddim))))
+
+    def sweep2site(self, niter, iter1=1, abstol=1e-8, maxbonddim=INT64_MAX, sweepstrategy="backandforth",
+                   strictlynested=False, fillsitetensors=True):
+        _check(lib().orc_tci_sweep2site(self.h, niter, iter1, C.c_double(abstol), C.c_int64(int(maxbonddim)),
+                                        0 if sweepstrategy == "forward" else 1, int(strictlynested), int(fillsitetensors)))
+
+    def sweep1site(self, direction="forward", reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX, updatetensors=True):
+        _check(lib().orc_tci_sweep1site(self.h, int(direction == "forward"), C.c_double(reltol), C.c_double(abstol),
+                                        C.c_int64(int(maxbonddim)), int(updatetensors)))
+
+    def makecanonical(self, reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX):
+        _check(lib().orc_tci_makecanonical(self.h, C.c_double(reltol), C.c_double(abstol), C.c_int64(int(maxbonddim))))
+
+    def addglobalpivots(self, pivots):
+        piv = _table(pivots, len(self))
+        _check(lib().orc_tci_addglobalpivots(self.h, _p(piv, C.c_int32), C.c_int64(len(pivots))))
+
+    def addglobalpivots1sitesweep(self, pivots, reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX):
+        self.addglobalpivots(pivots)                      # tensorci2.jl:367-377
+        self.makecanonical(reltol, abstol, maxbonddim)
+
+    def fillsitetensors(self):
+        _check(lib().orc_tci_fillsitetensors(self.h))
+
+    def _set(self, which, b):
+        ln = C.c_int()
+        cnt = lib().orc_tci_setsize(self.h, which, b, C.byref(ln))
+        out = np.zeros((cnt, ln.value), dtype=np.int32)
+        if out.size:
+            lib().orc_tci_getset(self.h, which, b, _p(out, C.c_int32))
+        return out
+
+    def Iset(self, b):
+        return self._set(0, b)
+
+    def Jset(self, b):
+        return self._set(1, b)
+
+    def linkdims(self):
+        return [len(self.Iset(b + 1)) for b in range(1, len(self))]
+
+    def rank(self):
+        return max(self.linkdims())
+
+    def sitetensor(self, b):
+        shp = np.zeros(3, dtype=np.int64)
+        lib().orc_tci_sitetensor_shape(self.h, b, _p(shp, C.c_int64))
+        out = np.zeros(int(np.prod(shp)))
+        if out.size:
+            lib().orc_tci_sitetensor(self.h, b, _p(out, C.c_double))
+        return out.reshape(tuple(int(s) for s in shp), order="F")
+
+    def sitetensors(self):
+        return [self.sitetensor(b) for b in range(1, len(self) + 1)]
+
+    @property
+    def maxsamplevalue(self):
+        return lib().orc_tci_maxsamplevalue(self.h)
+
+    @property
+    def pivoterrors(self):
+        out = np.zeros(lib().orc_tci_npivoterrors(self.h))
+        if out.size:
+            lib().orc_tci_pivoterrors(self.h, _p(out, C.c_double))
+        return out
+
+    @property
+    def bonderrors(self):
+        out = np.zeros(len(self) - 1)
+        lib().orc_tci_bonderrors(self.h, _p(out, C.c_double))
+        return out
+
+    def pivoterror(self):
+        return float(np.max(self.bonderrors))
+
+    def evaluate(self, idx):
+        v = np.asarray(idx, dtype=np.int32)
+        out = C.c_double()
+        _check(lib().orc_tci_evaluate(self.h, _p(v, C.c_int32), C.byref(out)))
+        return out.value
+
+    def stats(self):
+        ne, te, tl = C.c_int64(), C.c_double(), C.c_double()
+        lib().orc_tci_stats(self.h, C.byref(ne), C.byref(te), C.byref(tl))
+        return {"nevals": ne.value, "t_eval": te.value, "t_lu": tl.value}
+
+
+def crossinterpolate2(f, localdims, initialpivots=None, **kw):
+    """crossinterpolate2 (tensorci2.jl:1313-1323) with nsearchglobalpivot=0."""
+    tci = TCI2(f, localdims, initialpivots)
+    ranks, errors = tci.optimize(**kw)
+    return tci, ranks, errors
+
+
+def _flatten_tt(cores):
+    shapes = np.asarray([[c.shape[0], int(np.prod(c.shape[1:-1])), c.shape[-1]] for c in cores], dtype=np.int64)
+    flat = np.concatenate([np.asarray(c, dtype=np.float64).reshape(-1, order="F") for c in cores])
+    return flat, shapes
+
+
+def tt_sum(cores):
+    flat, shapes = _flatten_tt(cores)
+    out = C.c_double()
+    _check(lib().orc_tt_sum(_p(flat, C.c_double), _p(shapes, C.c_int64), len(cores), C.byref(out)))
+    return out.value
+
+
+def tt_evaluate(cores, points):
+    flat, shapes = _flatten_tt(cores)
+    pts = np.ascontiguousarray(np.asarray(points, dtype=np.int32).reshape(-1, len(cores)))
+    out = np.zeros(len(pts))
+    _check(lib().orc_tt_evaluate(_p(flat, C.c_double), _p(shapes, C.c_int64), len(cores), _p(pts, C.c_int32),
+                                 C.c_int64(len(pts)), _p(out, C.c_double)))
+    return out

@@ -1,0 +1,142 @@
+"""Pins the oracle's batch evaluation and TensorCI2 sweeps against the reference's tests
+(test/test_batcheval.jl, test/test_tensorci2.jl, test/test_tensortrain.jl)."""
+import itertools
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+
+def test_batcheval_M1_M2():                             # test/test_batcheval.jl:13-38
+    f = O.Func(O.F_SUM, [1.0])
+    ld = [2] * 5
+    left, right = [[1, 1]] * 100, [[1, 1]] * 100
+    res = O.batchevaluate(f, ld, left, right, 1)
+    ref = np.array([[[sum(l) + c + sum(r) for r in right] for c in (1, 2)] for l in left], dtype=float)
+    np.testing.assert_array_equal(res, ref)
+    left = [[1]] * 100
+    res = O.batchevaluate(f, ld, left, right, 2)
+    assert res.shape == (100, 2, 2, 100)
+    for c, cp in itertools.product((1, 2), (1, 2)):
+        assert res[3, c - 1, cp - 1, 7] == 1 + c + cp + 2
+
+
+def test_batcheval_shape_and_order():                   # test/test_batcheval.jl:40-69, batcheval.jl:157-171
+    rng = np.random.default_rng(5)
+    ld = [3, 2, 4, 3, 2, 3]
+    T = rng.random(ld)
+    f = O.Func(O.F_DENSE, table=T)
+    left = [[1, 2], [3, 1], [2, 2]]
+    right = [[1, 3], [2, 1]]
+    res = O.batchevaluate(f, ld, left, right, 2)
+    assert res.shape == (3, 4, 3, 2)
+    for i, l in enumerate(left):
+        for c in range(4):
+            for cp in range(3):
+                for j, r in enumerate(right):
+                    assert res[i, c, cp, j] == T[l[0] - 1, l[1] - 1, c, cp, r[0] - 1, r[1] - 1]
+    assert O.batchevaluate(f, ld, [], right, 2).shape == (0, 0, 0, 0)
+
+
+def test_pivoterrors_diagonal():                        # test/test_tensorci2.jl:27-39 (exact equality)
+    diags = [1.0, 1e-5, 0.0]
+    f = O.Func(O.F_DENSE, table=np.diag(diags))
+    tci, ranks, errors = O.crossinterpolate2(f, [3, 3], [[1, 1]], tolerance=1e-8)
+    assert list(tci.pivoterrors) == diags
+
+
+def test_callback_matches_dense():
+    diags = [1.0, 1e-5, 0.0]
+    f = O.Func(O.F_CALLBACK, callback=lambda x: diags[x[0] - 1] if x[0] == x[1] else 0.0)
+    tci, _, _ = O.crossinterpolate2(f, [3, 3], [[1, 1]], tolerance=1e-8)
+    assert list(tci.pivoterrors) == diags
+
+
+def test_trivial_mps():                                 # test/test_tensorci2.jl "trivial MPS"
+    f = O.Func(O.F_SUM, [0.5])
+    tci = O.TCI2(f, [2] * 5, [])
+    assert tci.linkdims() == [0] * 4
+    tci = O.TCI2(f, [2] * 5, [[1] * 5])
+    assert tci.linkdims() == [1] * 4 and tci.rank() == 1
+
+
+def test_lorentz_5site_linkdims():                      # test/test_tensorci2.jl:247-273
+    n = 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci = O.TCI2(f, [10] * n)
+    assert tci.linkdims() == [1] * (n - 1)
+    assert len(tci.Iset(1)) == 1 and len(tci.Jset(n)) == 1
+    for p in range(1, n):
+        tci.updatepivots(p, True, reltol=1e-8, maxbonddim=2)
+    assert tci.linkdims() == [2] * (n - 1) and tci.rank() == 2
+    tci.addglobalpivots1sitesweep([[2, 9, 10, 5, 7]], reltol=1e-12)
+    assert tci.linkdims() == [3] * (n - 1) and tci.rank() == 3
+    assert len(tci.Iset(1)) == 1 and len(tci.Jset(n)) == 1
+
+
+def test_lorentz_5site_tolerance():                     # test/test_tensorci2.jl:297-339
+    n = 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci3, ranks, errors = O.crossinterpolate2(f, [10] * n, [[1] * n], tolerance=1e-12, maxiter=200)
+    assert tci3.pivoterror() <= 2e-12
+    assert tci3.rank() <= 200
+    cores = tci3.sitetensors()
+    for v in itertools.product(range(1, 4), repeat=n):
+        val = tci3.evaluate(v)
+        assert val == pytest.approx(f(v), rel=1e-8)
+        assert val == pytest.approx(O.tt_evaluate(cores, [v])[0], rel=1e-12)
+    piv = [[1, 1, 1, 1, 1], [10, 8, 10, 4, 4], [5, 4, 8, 9, 3], [7, 7, 10, 5, 9], [7, 7, 10, 5, 9]]
+    tci4, _, _ = O.crossinterpolate2(f, [10] * n, piv, tolerance=1e-12, maxiter=200)
+    assert tci4.pivoterror() <= 2e-12 and tci4.rank() <= 200
+
+
+def test_forward_vs_backandforth_rank():                # test/test_tensorci2.jl:275-296
+    n = 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci = O.TCI2(f, [10] * n)
+    for _ in range(20):
+        for p in range(1, n):
+            tci.updatepivots(p, True, reltol=1e-8)
+    tci2, _, _ = O.crossinterpolate2(f, [10] * n, [[1] * n], tolerance=1e-8, maxiter=8, sweepstrategy="forward")
+    assert tci.rank() == tci2.rank()
+
+
+def test_quantics_exp_bond1():                          # test/test_tensorci2.jl:55-102 (nsearchglobalpivot=0 cases)
+    R, abstol = 8, 1e-4
+    f = O.Func(O.F_QEXP2, [1.0, 0.0, 0.0])
+    for strictlynested in (False, True):
+        tci, _, _ = O.crossinterpolate2(f, [2] * R, [[1] * R, [1] + [2] * (R - 1)], tolerance=abstol, maxbonddim=1,
+                                        maxiter=2, normalizeerror=False, strictlynested=strictlynested)
+        assert tci.linkdims() == [1] * (R - 1)
+        for x in (0.1, 0.3, 0.6, 0.9):
+            i = int(np.floor(x * 2 ** R))               # grid index of x = i / 2^R
+            bits = [((i >> (R - 1 - k)) & 1) + 1 for k in range(R)]
+            assert abs(tci.evaluate(bits) - f(bits)) < abstol
+            assert abs(f(bits) - np.exp(-i / 2 ** R)) < 1e-15
+
+
+def test_reconstruct_from_sets():                       # test/test_tensorci2.jl:461-475 (maxbonddim run)
+    rng = np.random.default_rng(1234)
+    M = rng.random((10, 10))
+    f = O.Func(O.F_DENSE, table=M)
+    tci, ranks, _ = O.crossinterpolate2(f, [10, 10], maxbonddim=5)
+    assert tci.rank() == 5
+    mx = max(abs(M[i[0] - 1, j[0] - 1]) for i in tci.Iset(2) for j in tci.Jset(1))
+    assert tci.maxsamplevalue >= mx
+
+
+def test_tt_sum_bruteforce():                           # test/test_tensortrain.jl:10-32
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci, _, _ = O.crossinterpolate2(f, [6] * 4, tolerance=1e-12)
+    ref = sum(f(v) for v in itertools.product(range(1, 7), repeat=4))
+    assert O.tt_sum(tci.sitetensors()) == pytest.approx(ref, rel=1e-9)
+
+
+def test_convergence_and_errors_c1():                   # BASELINE config C1 invariants
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci, ranks, errors = O.crossinterpolate2(f, [10] * 8, tolerance=1e-8)
+    assert errors[-1] < 1e-8
+    rng = np.random.default_rng(0)
+    pts = rng.integers(1, 11, size=(500, 8))
+    assert max(abs(tci.evaluate(p) - f(p)) for p in pts) < 1e-7 * tci.maxsamplevalue
