@@ -1,0 +1,9 @@
+"""B200-native TensorCI2 hot path behind the reference's own API names.
+
+Host logic (sweep strategy, index-set bookkeeping, convergence control) is Python mirroring the Julia
+package; every arithmetic step calls the C ABI of libtci_b200.so (hand-written sm_100a CUDA).  The
+package is importable without a GPU (so CPU-only tests can check symbols), but any computation
+raises if the library or a CUDA device is missing — there is no CPU fallback.
+"""
+from ._lib import Handle, TCIError, default_handle, lib, SO_PATH          # noqa: F401
+from .matrixlu import rrLU, rrlu, rrlu_inplace, submatrixargmax, rrlu_last_timing   # noqa: F401

@@ -1,0 +1,573 @@
+// rrlu.cu — K2 + K3: full-pivot rank-revealing LU on the device.
+//
+// Restates (does not translate) src/matrixlu.jl:346-396 (_optimizerrlu!), :46-87 (submatrixargmax),
+// :295-322 (addpivot!) of the reference for one B200:
+//
+//   per pivot step k                      reference                          here
+//   ------------------------------------  ---------------------------------  ---------------------------------
+//   find argmax |A[i,j]|^2, i,j >= k      separate full scan (:359)          fused into the previous step's
+//                                                                            update pass (no extra HBM read)
+//   swap rows k<->pr, cols k<->pc,        two strided whole-row/col loops    rrlu_swap_kernel: one thread per
+//   scale the pivot column (or row)       (:254-275, :303-309)               swapped pair, corners by one thread
+//   A[i,j] -= x[i]*y[j]                   scalar double loop (:316-320)      rrlu_update_kernel<...>: 128-bit
+//                                                                            coalesced column accesses, pivot row
+//                                                                            read from a packed copy (ybuf)
+//   stop test                             host (:363)                        last-finishing block of the update
+//                                                                            kernel (device-side state, no host
+//                                                                            round trip per step)
+//
+// The matrix keeps the reference's physically swapped layout, so the argmax tie rule (smallest
+// column, then smallest row, in swapped coordinates) and the final tril/triu extraction are
+// bit-identical to the reference, ties included.  Arithmetic is __dmul_rn/__dsub_rn (no FMA
+// contraction; Julia does not contract) and IEEE division.
+//
+// HBM roofline: 16 B per updated element (one FP64 read + one write); the fused
+// search adds no bytes.  DESIGN.md has the per-kernel figures.
+#include "context.h"
+#include <cmath>
+#include <cstdlib>
+
+namespace {
+
+constexpr int kThreads = 256;
+
+struct Cand {            // argmax candidate: signed value and 0-based position; i < 0 means "none yet"
+    double x;
+    int i, j;
+};
+
+struct RrluState {
+    int npivot;          // pivots placed so far
+    int stop;            // 1 once the loop of matrixlu.jl:356-369 has ended
+    int pr, pc;          // pending pivot (0-based, swapped coordinates) for step `npivot`
+    double pivval;       // A[pr, pc]
+    double maxerror;
+    double error;        // lu.error
+    unsigned int ticket; // blocks of the running update kernel that have finished
+    int flags;           // bit 0: NaN in L, bit 1: NaN in U
+};
+
+__device__ __forceinline__ bool cand_better(const Cand& a, const Cand& b) {
+    // true iff a precedes b in the reference's scan: larger abs2, then smaller column, then smaller row
+    if (a.i < 0) return false;
+    if (b.i < 0) return true;
+    const double va = __dmul_rn(a.x, a.x), vb = __dmul_rn(b.x, b.x);
+    if (va > vb) return true;
+    if (va == vb) return (a.j < b.j) || (a.j == b.j && a.i < b.i);
+    return false;
+}
+
+__device__ __forceinline__ Cand cand_shfl_down(const Cand& c, int delta) {
+    Cand o;
+    o.x = __shfl_down_sync(0xffffffffu, c.x, delta);
+    o.i = __shfl_down_sync(0xffffffffu, c.i, delta);
+    o.j = __shfl_down_sync(0xffffffffu, c.j, delta);
+    return o;
+}
+
+__device__ __forceinline__ Cand block_reduce(Cand c, Cand* smem /* kThreads/32 entries */) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        Cand o = cand_shfl_down(c, d);
+        if (cand_better(o, c)) c = o;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) smem[warp] = c;
+    __syncthreads();
+    if (warp == 0) {
+        c = (lane < kThreads / 32) ? smem[lane] : Cand{0.0, -1, -1};
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            Cand o = cand_shfl_down(c, d);
+            if (cand_better(o, c)) c = o;
+        }
+    }
+    return c;   // valid in thread 0
+}
+
+__device__ __forceinline__ double jl_max(double a, double b) {   // Julia's max propagates NaN
+    if (isnan(a) || isnan(b)) return nan("");
+    return a > b ? a : b;
+}
+
+__global__ void rrlu_init_kernel(RrluState* st, int* rowperm, int* colperm, int m, int n) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < m) rowperm[t] = t;
+    if (t < n) colperm[t] = t;
+    if (t == 0) {
+        st->npivot = 0; st->stop = 0; st->pr = 0; st->pc = 0; st->pivval = 0.0;
+        st->maxerror = 0.0; st->error = nan(""); st->ticket = 0u; st->flags = 0;
+    }
+}
+
+// One pass over the trailing block.  UPDATE: apply the rank-1 Schur update of the pivot that the swap
+// kernel just placed at position k = st->npivot, and find the next pivot in the same pass.
+// !UPDATE: only the search over the whole matrix (first pivot).  The last block to finish reduces the
+// per-block candidates and evaluates the stop rule (matrixlu.jl:360-367).
+// Tiles (TR rows x COLS columns) are dealt round-robin to a grid sized to exactly one resident wave; odd
+// steps walk the tiles backwards so that the ~L2-sized tail written by step k is the first thing
+// step k+1 reads (serpentine order: those reads, and the re-writes of the still-dirty lines, never
+// reach HBM).
+#define TCI_CONSIDER(q, val, ii, jj)                                                             \
+    if ((q) > bv || ((q) == bv && ((jj) < bj || ((jj) == bj && (ii) < bi)))) { bv = (q); bx = (val); bi = (ii); bj = (jj); }
+
+template <bool UPDATE, bool VEC, int COLS>
+__global__ void __launch_bounds__(kThreads, (COLS <= 4 ? 5 : (COLS == 8 ? 3 : 2)))
+rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const double* __restrict__ ybuf,
+                   RrluState* st, Cand* parts, int maxrank, double reltol, double abstol, int start0, int serpentine) {
+    __shared__ Cand s_c[kThreads / 32];
+    __shared__ int s_last;
+    if (st->stop) return;
+    const int k = st->npivot;
+    const int np = UPDATE ? k + 1 : start0;             // pivots in place once this pass is done
+    const int r0 = np, c0 = np;                         // trailing block starts here
+    double bv = -INFINITY, bx = 0.0;
+    int bi = -1, bj = -1;
+
+    if (np < maxrank) {                                 // otherwise the loop ends; nothing reads the block
+        constexpr int RPT = VEC ? 2 : 1;                // rows per thread
+        constexpr int TR = kThreads * RPT;
+        const int rbase = VEC ? (r0 & ~1) : r0;
+        const int nrt = (m - rbase + TR - 1) / TR;
+        const int nct = (n - c0 + COLS - 1) / COLS;
+        const long long ntiles = (long long)nrt * nct;
+        const double* xcol = A + (long long)k * lda;    // scaled pivot column (UPDATE only)
+        const bool rev = serpentine && (np & 1);
+        for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+            const long long t = rev ? ntiles - 1 - t0 : t0;
+            const int rt = (int)(t % nrt), ct = (int)(t / nrt);
+            const int i0 = rbase + rt * TR + threadIdx.x * RPT;
+            const int j0 = c0 + ct * COLS;
+            if (i0 >= m) continue;
+            if (VEC) {
+                const bool v0 = i0 >= r0, v1 = i0 + 1 < m;
+                if (v0 && v1) {
+                    double2 x = make_double2(0.0, 0.0);
+                    if (UPDATE) x = *reinterpret_cast<const double2*>(xcol + i0);
+                    double2 a[COLS];
+#pragma unroll
+                    for (int c = 0; c < COLS; ++c)
+                        if (j0 + c < n) a[c] = *reinterpret_cast<const double2*>(A + (long long)(j0 + c) * lda + i0);
+#pragma unroll
+                    for (int c = 0; c < COLS; ++c) {
+                        const int j = j0 + c;
+                        if (j < n) {
+                            double2 v = a[c];
+                            if (UPDATE) {
+                                const double y = ybuf[j];
+                                v.x = __dsub_rn(v.x, __dmul_rn(x.x, y));
+                                v.y = __dsub_rn(v.y, __dmul_rn(x.y, y));
+                                *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
+                            }
+                            const double q0 = __dmul_rn(v.x, v.x), q1 = __dmul_rn(v.y, v.y);
+                            TCI_CONSIDER(q0, v.x, i0, j)
+                            TCI_CONSIDER(q1, v.y, i0 + 1, j)
+                        }
+                    }
+                    continue;
+                }
+                // edge rows of the aligned tiling: at most one valid row, scalar path below
+                const int i = v0 ? i0 : i0 + 1;
+                if (i < r0 || i >= m) continue;
+                const double x = UPDATE ? xcol[i] : 0.0;
+#pragma unroll
+                for (int c = 0; c < COLS; ++c) {
+                    const int j = j0 + c;
+                    if (j < n) {
+                        double v = A[(long long)j * lda + i];
+                        if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
+                        const double q = __dmul_rn(v, v);
+                        TCI_CONSIDER(q, v, i, j)
+                    }
+                }
+            } else {
+                const int i = i0;
+                const double x = UPDATE ? xcol[i] : 0.0;
+                double a[COLS];
+#pragma unroll
+                for (int c = 0; c < COLS; ++c)
+                    if (j0 + c < n) a[c] = A[(long long)(j0 + c) * lda + i];
+#pragma unroll
+                for (int c = 0; c < COLS; ++c) {
+                    const int j = j0 + c;
+                    if (j < n) {
+                        double v = a[c];
+                        if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
+                        const double q = __dmul_rn(v, v);
+                        TCI_CONSIDER(q, v, i, j)
+                    }
+                }
+            }
+        }
+    }
+
+    Cand c = block_reduce(Cand{bx, bi, bj}, s_c);
+    if (threadIdx.x == 0) {
+        parts[blockIdx.x] = c;
+        __threadfence();
+        const unsigned int done = atomicAdd(&st->ticket, 1u);
+        s_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    Cand best{0.0, -1, -1};
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += kThreads) {
+        Cand o = parts[b];
+        if (cand_better(o, best)) best = o;
+    }
+    __syncthreads();
+    best = block_reduce(best, s_c);
+    if (threadIdx.x == 0) {
+        st->npivot = np;
+        st->ticket = 0u;
+        if (np >= maxrank) {
+            st->stop = 1;                                           // while lu.npivot < maxrank   (:356)
+        } else {
+            if (best.i < 0) { best.i = np; best.j = np; best.x = nan(""); }   // every entry NaN: first(rows), first(cols)
+            const double err = fabs(best.x);                        // :360
+            st->error = err;
+            if ((err < reltol * st->maxerror || err < abstol) && np > 0) {    // :363
+                st->stop = 1;
+            } else {
+                st->maxerror = jl_max(st->maxerror, err);           // :367
+                st->pr = best.i; st->pc = best.j; st->pivval = best.x;
+            }
+        }
+    }
+}
+
+// swaprow!/swapcol! (:254-275) + the scaling of addpivot! (:303-309) for the pending pivot, plus the
+// packed copy of the new pivot row that the update kernel reads.  Thread t < n handles column t of the
+// two swapped rows, n <= t < n+m handles row t-n of the two swapped columns, t == n+m the four corners
+// and the permutation bookkeeping.
+__global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf,
+                                 RrluState* st, int* rowperm, int* colperm, double* pivvals, int leftorth) {
+    if (st->stop) return;
+    const int k = st->npivot, pr = st->pr, pc = st->pc;
+    const double piv = st->pivval;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) {
+        const int j = t;
+        if (j == k || j == pc) return;
+        double* pk = A + (long long)j * lda + k;
+        double* pp = A + (long long)j * lda + pr;
+        const double a = *pk;
+        double newk = (pr != k) ? *pp : a;
+        if (!leftorth && j > k) newk = newk / piv;
+        *pk = newk;
+        if (pr != k) *pp = a;
+        if (j > k) ybuf[j] = newk;
+    } else if (t < n + m) {
+        const int i = t - n;
+        if (i == k || i == pr) return;
+        double* pk = A + (long long)k * lda + i;
+        double* pp = A + (long long)pc * lda + i;
+        const double a = *pk;
+        double newk = (pc != k) ? *pp : a;
+        if (leftorth && i > k) newk = newk / piv;
+        *pk = newk;
+        if (pc != k) *pp = a;
+    } else if (t == n + m) {
+        const double o_kk = A[(long long)k * lda + k], o_kpc = A[(long long)pc * lda + k];
+        const double o_prk = A[(long long)k * lda + pr], o_prpc = A[(long long)pc * lda + pr];
+        double n_kk = o_prpc, n_kpc = o_prk, n_prk = o_kpc, n_prpc = o_kk;
+        if (leftorth) { if (pr > k) n_prk = n_prk / piv; }
+        else          { if (pc > k) n_kpc = n_kpc / piv; }
+        // When pr == k or pc == k two of the four corners are the same address; this store order makes
+        // the (possibly scaled) canonical value the one that lands last.
+        A[(long long)pc * lda + pr] = n_prpc;
+        A[(long long)pc * lda + k] = n_kpc;
+        A[(long long)k * lda + pr] = n_prk;
+        A[(long long)k * lda + k] = n_kk;
+        if (pc > k) ybuf[pc] = n_kpc;
+        int tmp = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = tmp;
+        tmp = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = tmp;
+        pivvals[k] = piv;
+    }
+}
+
+// L = tril(A[:, 1:r]), U = triu(A[1:r, :]), NaN flags, unit diagonal (:372-388).
+__global__ void rrlu_extract_kernel(const double* __restrict__ A, int m, int n, long long lda, int r, int leftorth,
+                                    double* __restrict__ L, long long ldl, double* __restrict__ U, long long ldu,
+                                    RrluState* st) {
+    const long long nL = (long long)m * r, nU = (long long)r * n;
+    int flags = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nL + nU; t += (long long)gridDim.x * blockDim.x) {
+        if (t < nL) {
+            const int i = (int)(t % m), j = (int)(t / m);
+            double v = (i >= j) ? A[(long long)j * lda + i] : 0.0;
+            if (isnan(v)) flags |= 1;
+            if (i == j && leftorth) v = 1.0;
+            if (L) L[(long long)j * ldl + i] = v;
+        } else {
+            const long long u = t - nL;
+            const int i = (int)(u % r), j = (int)(u / r);
+            double v = (j >= i) ? A[(long long)j * lda + i] : 0.0;
+            if (isnan(v)) flags |= 2;
+            if (i == j && !leftorth) v = 1.0;
+            if (U) U[(long long)j * ldu + i] = v;
+        }
+    }
+    if (flags) atomicOr(&st->flags, flags);
+}
+
+struct SmallWs {                 // carve-up of tci_context::ws_small
+    RrluState* st; int* rowperm; int* colperm; double* ybuf; double* pivvals; Cand* parts;
+};
+
+int carve(tci_handle h, int m, int n, int grid, SmallWs* w) {
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_st = 0, o_rp = al(sizeof(RrluState)), o_cp = o_rp + al(sizeof(int) * m),
+                 o_y = o_cp + al(sizeof(int) * n), o_pv = o_y + al(sizeof(double) * n),
+                 o_parts = o_pv + al(sizeof(double) * (size_t)(m < n ? m : n)), total = o_parts + al(sizeof(Cand) * grid);
+    int rc = tci_ws_reserve(h, h->ws_small, total);
+    if (rc) return rc;
+    char* b = (char*)h->ws_small.ptr;
+    w->st = (RrluState*)(b + o_st); w->rowperm = (int*)(b + o_rp); w->colperm = (int*)(b + o_cp);
+    w->ybuf = (double*)(b + o_y); w->pivvals = (double*)(b + o_pv); w->parts = (Cand*)(b + o_parts);
+    return TCI_OK;
+}
+
+struct UpdateCfg { int cols; int grid; int serpentine; };
+
+template <bool UPDATE, bool VEC, int COLS>
+int occupancy_grid(tci_handle h) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rrlu_update_kernel<UPDATE, VEC, COLS>, kThreads, 0) != cudaSuccess || nb < 1) nb = 1;
+    return nb * h->num_sms;
+}
+
+// Tunables can be overridden from the environment for experiments (TCI_RRLU_COLS = 4|8|16,
+// TCI_RRLU_BLOCKS_PER_SM, TCI_RRLU_SERPENTINE = 0|1).
+UpdateCfg update_cfg(tci_handle h, bool vec) {
+    UpdateCfg c; c.cols = 8; c.serpentine = 1;
+    if (const char* e = getenv("TCI_RRLU_COLS")) { int v = atoi(e); if (v == 4 || v == 8 || v == 16) c.cols = v; }
+    if (const char* e = getenv("TCI_RRLU_SERPENTINE")) c.serpentine = atoi(e) ? 1 : 0;
+    if (vec) c.grid = c.cols == 4 ? occupancy_grid<true, true, 4>(h) : c.cols == 8 ? occupancy_grid<true, true, 8>(h) : occupancy_grid<true, true, 16>(h);
+    else     c.grid = occupancy_grid<true, false, 8>(h);
+    if (const char* e = getenv("TCI_RRLU_BLOCKS_PER_SM")) { int v = atoi(e); if (v > 0 && v * h->num_sms < c.grid) c.grid = v * h->num_sms; }
+    return c;
+}
+
+template <bool UPDATE>
+void launch_update(tci_handle h, bool vec, const UpdateCfg& c, double* A, int m, int n, long long lda, const SmallWs& w,
+                   int maxrank, double reltol, double abstol, int start0 = 0) {
+#define TCI_LAUNCH_UPD(V, CC) rrlu_update_kernel<UPDATE, V, CC><<<c.grid, kThreads, 0, h->stream>>>(A, m, n, lda, w.ybuf, w.st, w.parts, maxrank, reltol, abstol, start0, c.serpentine)
+    if (!vec) TCI_LAUNCH_UPD(false, 8);
+    else if (c.cols == 4) TCI_LAUNCH_UPD(true, 4);
+    else if (c.cols == 16) TCI_LAUNCH_UPD(true, 16);
+    else TCI_LAUNCH_UPD(true, 8);
+#undef TCI_LAUNCH_UPD
+}
+
+} // namespace
+
+// Shared driver: factorises d_A in place, leaves perms/pivot values in ws_small, reads the final state.
+static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int mr, double reltol, double abstol,
+                    int leftorth, SmallWs* w, RrluState* final_state) {
+    const bool vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15u) == 0);
+    const UpdateCfg cfg = update_cfg(h, vec);
+    const int grid = cfg.grid;
+    int rc = carve(h, m, n, grid, w);
+    if (rc) return rc;
+    rc = tci_pinned_reserve(h, sizeof(RrluState) + sizeof(int) * ((size_t)m + n) + sizeof(double) * (size_t)(mr + 1));
+    if (rc) return rc;
+    const int mx = m > n ? m : n;
+    rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n);
+    TCI_LAUNCH_CHECK(h);
+    TCI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    launch_update<false>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
+    TCI_LAUNCH_CHECK(h);
+    RrluState* hst = (RrluState*)h->pinned;
+    const int swap_blocks = (m + n + 1 + 255) / 256;
+    int launched = 0, chunk = 8;
+    h->rrlu_steps = 0;
+    if (h->rrlu_profile)
+        while ((int)h->ev_pool.size() < 2 * mr) { cudaEvent_t e; TCI_CUDA(h, cudaEventCreate(&e)); h->ev_pool.push_back(e); }
+    while (launched < mr) {
+        const int nb = (mr - launched < chunk) ? mr - launched : chunk;
+        for (int s = 0; s < nb; ++s) {
+            rrlu_swap_kernel<<<swap_blocks, 256, 0, h->stream>>>(d_A, m, n, lda, w->ybuf, w->st, w->rowperm, w->colperm, w->pivvals, leftorth);
+            TCI_LAUNCH_CHECK(h);
+            if (h->rrlu_profile) TCI_CUDA(h, cudaEventRecord(h->ev_pool[2 * (launched + s)], h->stream));
+            launch_update<true>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
+            TCI_LAUNCH_CHECK(h);
+            if (h->rrlu_profile) TCI_CUDA(h, cudaEventRecord(h->ev_pool[2 * (launched + s) + 1], h->stream));
+        }
+        launched += nb;
+        if (chunk < 64) chunk *= 2;
+        TCI_CUDA(h, cudaMemcpyAsync(hst, w->st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (hst->stop) break;
+    }
+    if (launched >= mr && !hst->stop) {        // cannot happen: the last update's tail always stops at maxrank
+        return tci_fail(h, TCI_ERR_CUDA, "rrlu: device loop did not terminate (npivot=%d, maxrank=%d)", hst->npivot, mr);
+    }
+    TCI_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    *final_state = *hst;
+    h->rrlu_steps = hst->npivot;
+    h->rrlu_ms[1] = 0.0;
+    if (h->rrlu_profile) {
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+        double tot = 0.0;
+        for (int s = 0; s < launched; ++s) { float ms = 0.f; cudaEventElapsedTime(&ms, h->ev_pool[2 * s], h->ev_pool[2 * s + 1]); tot += ms; }
+        h->rrlu_ms[1] = tot;
+    }
+    return TCI_OK;
+}
+
+static int rrlu_finish(tci_handle h, const double* d_A, int m, int n, long long lda, int leftorth, const SmallWs& w,
+                       RrluState* fs, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot, double* h_error,
+                       double* d_L, long long ldl, double* d_U, long long ldu, double* h_pivoterrors) {
+    const int r = fs->npivot;
+    if (r > 0) {
+        const long long work = (long long)m * r + (long long)r * n;
+        long long blocks = (work + 255) / 256;
+        if (blocks > h->num_sms * 8) blocks = h->num_sms * 8;
+        rrlu_extract_kernel<<<(int)blocks, 256, 0, h->stream>>>(d_A, m, n, lda, r, leftorth, d_L, ldl, d_U, ldu, w.st);
+        TCI_LAUNCH_CHECK(h);
+    }
+    TCI_CUDA(h, cudaEventRecord(h->ev[2], h->stream));
+    char* pin = (char*)h->pinned;
+    RrluState* hst = (RrluState*)pin;
+    int* hrp = (int*)(pin + sizeof(RrluState));
+    int* hcp = hrp + m;
+    double* hpv = (double*)(hcp + n + ((m + n) & 1));      // keep 8-byte alignment
+    TCI_CUDA(h, cudaMemcpyAsync(hst, w.st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaMemcpyAsync(hrp, w.rowperm, sizeof(int) * m, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaMemcpyAsync(hcp, w.colperm, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
+    if (r > 0) TCI_CUDA(h, cudaMemcpyAsync(hpv, w.pivvals, sizeof(double) * r, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]); h->rrlu_ms[0] = ms;
+    cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->rrlu_ms[2] = ms;
+    double err = hst->error;
+    if (r >= (m < n ? m : n)) err = 0.0;                    // matrixlu.jl:391-393
+    if (h_rowperm) for (int i = 0; i < m; ++i) h_rowperm[i] = (int64_t)hrp[i] + 1;
+    if (h_colperm) for (int j = 0; j < n; ++j) h_colperm[j] = (int64_t)hcp[j] + 1;
+    if (h_npivot) *h_npivot = r;
+    if (h_error) *h_error = err;
+    if (h_pivoterrors) { for (int i = 0; i < r; ++i) h_pivoterrors[i] = fabs(hpv[i]); h_pivoterrors[r] = err; }
+    fs->flags = hst->flags;
+    if (hst->flags & 1) return tci_fail(h, TCI_ERR_NAN_L, "lu.L contains NaNs");
+    if (hst->flags & 2) return tci_fail(h, TCI_ERR_NAN_U, "lu.U contains NaNs");
+    return TCI_OK;
+}
+
+static int check_dims(tci_handle h, int64_t m, int64_t n, int64_t lda, const char* who) {
+    if (!h) return TCI_ERR_INVALID;
+    if (m < 0 || n < 0 || m > INT32_MAX - 1024 || n > INT32_MAX - 1024) return tci_fail(h, TCI_ERR_INVALID, "%s: bad matrix size %lld x %lld", who, (long long)m, (long long)n);
+    if (lda < (m > 1 ? m : 1)) return tci_fail(h, TCI_ERR_INVALID, "%s: lda (%lld) < m (%lld)", who, (long long)lda, (long long)m);
+    return TCI_OK;
+}
+
+extern "C" {
+
+int tci_rrlu_inplace_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol,
+                         double abstol, int leftorthogonal, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot,
+                         double* h_error, double* d_L, int64_t ldl, double* d_U, int64_t ldu, double* h_pivoterrors) {
+    int rc = check_dims(h, m, n, lda, "tci_rrlu_inplace_f64");
+    if (rc) return rc;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    int64_t mn = m < n ? m : n;
+    int64_t mr = (maxrank <= 0 || maxrank > mn) ? mn : maxrank;
+    if (mn == 0) {                                          // empty matrix: zero pivots, error 0 (:353, :391)
+        if (h_rowperm) for (int64_t i = 0; i < m; ++i) h_rowperm[i] = i + 1;
+        if (h_colperm) for (int64_t j = 0; j < n; ++j) h_colperm[j] = j + 1;
+        if (h_npivot) *h_npivot = 0;
+        if (h_error) *h_error = 0.0;
+        if (h_pivoterrors) h_pivoterrors[0] = 0.0;
+        return TCI_OK;
+    }
+    if (!d_A) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_inplace_f64: d_A is NULL");
+    if (d_L && ldl < m) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_inplace_f64: ldl < m");
+    if (d_U && ldu < mr) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_inplace_f64: ldu < min(maxrank, m, n)");
+    SmallWs w; RrluState fs;
+    rc = rrlu_run(h, d_A, (int)m, (int)n, lda, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
+    if (rc) return rc;
+    return rrlu_finish(h, d_A, (int)m, (int)n, lda, leftorthogonal ? 1 : 0, w, &fs, h_rowperm, h_colperm, h_npivot, h_error,
+                       d_L, ldl, d_U, ldu, h_pivoterrors);
+}
+
+int tci_rrlu_host_f64(tci_handle h, const double* h_A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol,
+                      double abstol, int leftorthogonal, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot,
+                      double* h_error, double* h_L, int64_t ldl, double* h_U, int64_t ldu, double* h_pivoterrors) {
+    int rc = check_dims(h, m, n, lda, "tci_rrlu_host_f64");
+    if (rc) return rc;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    int64_t mn = m < n ? m : n;
+    int64_t mr = (maxrank <= 0 || maxrank > mn) ? mn : maxrank;
+    if (mn == 0) return tci_rrlu_inplace_f64(h, nullptr, m, n, lda, maxrank, reltol, abstol, leftorthogonal, h_rowperm,
+                                             h_colperm, h_npivot, h_error, nullptr, 0, nullptr, 0, h_pivoterrors);
+    if (!h_A) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_host_f64: h_A is NULL");
+    if (h_L && ldl < m) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_host_f64: ldl < m");
+    if (h_U && ldu < 1) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_host_f64: ldu < 1");
+    const int64_t ldw = (m + 15) & ~(int64_t)15;           // 128-byte aligned columns for the working copy (rrlu copies A, :462)
+    rc = tci_ws_reserve(h, h->ws_matrix, sizeof(double) * (size_t)ldw * n);
+    if (rc) return rc;
+    double* dA = (double*)h->ws_matrix.ptr;
+    TCI_CUDA(h, cudaMemcpy2DAsync(dA, sizeof(double) * ldw, h_A, sizeof(double) * lda, sizeof(double) * m, n,
+                                  cudaMemcpyHostToDevice, h->stream));
+    double *dL = nullptr, *dU = nullptr;
+    if (h_L || h_U) {
+        rc = tci_ws_reserve(h, h->ws_lu, sizeof(double) * ((size_t)m * mr + (size_t)mr * n));
+        if (rc) return rc;
+        dL = (double*)h->ws_lu.ptr; dU = dL + (size_t)m * mr;
+    }
+    SmallWs w; RrluState fs;
+    rc = rrlu_run(h, dA, (int)m, (int)n, ldw, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
+    if (rc) return rc;
+    rc = rrlu_finish(h, dA, (int)m, (int)n, ldw, leftorthogonal ? 1 : 0, w, &fs, h_rowperm, h_colperm, h_npivot, h_error,
+                     h_L ? dL : nullptr, m, h_U ? dU : nullptr, mr, h_pivoterrors);
+    if (rc) return rc;
+    const int64_t r = fs.npivot;
+    if (r > 0 && h_L)
+        TCI_CUDA(h, cudaMemcpy2DAsync(h_L, sizeof(double) * ldl, dL, sizeof(double) * m, sizeof(double) * m, r, cudaMemcpyDeviceToHost, h->stream));
+    if (r > 0 && h_U) {
+        if (ldu < r) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_host_f64: ldu (%lld) < npivot (%lld)", (long long)ldu, (long long)r);
+        TCI_CUDA(h, cudaMemcpy2DAsync(h_U, sizeof(double) * ldu, dU, sizeof(double) * mr, sizeof(double) * r, n, cudaMemcpyDeviceToHost, h->stream));
+    }
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    return TCI_OK;
+}
+
+int tci_submatrixargmax_abs2_f64(tci_handle h, const double* d_A, int64_t m, int64_t n, int64_t lda, int64_t k,
+                                 int64_t* h_row, int64_t* h_col) {
+    int rc = check_dims(h, m, n, lda, "tci_submatrixargmax_abs2_f64");
+    if (rc) return rc;
+    if (k < 1 || k > m) return tci_fail(h, TCI_ERR_INVALID, "rows must not be empty");      // matrixlu.jl:58
+    if (k > n) return tci_fail(h, TCI_ERR_INVALID, "cols must not be empty");               // matrixlu.jl:59
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    const bool vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15u) == 0);
+    const UpdateCfg cfg = update_cfg(h, vec);
+    SmallWs w;
+    rc = carve(h, (int)m, (int)n, cfg.grid, &w);
+    if (rc) return rc;
+    rc = tci_pinned_reserve(h, sizeof(RrluState));
+    if (rc) return rc;
+    rrlu_init_kernel<<<1, 32, 0, h->stream>>>(w.st, w.rowperm, w.colperm, 0, 0);
+    TCI_LAUNCH_CHECK(h);
+    launch_update<false>(h, vec, cfg, const_cast<double*>(d_A), (int)m, (int)n, lda, w, INT32_MAX, 0.0, 0.0, (int)(k - 1));
+    TCI_LAUNCH_CHECK(h);
+    RrluState* hst = (RrluState*)h->pinned;
+    TCI_CUDA(h, cudaMemcpyAsync(hst, w.st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    *h_row = hst->pr + 1; *h_col = hst->pc + 1;
+    return TCI_OK;
+}
+
+int tci_rrlu_set_profiling(tci_handle h, int on) {
+    if (!h) return TCI_ERR_INVALID;
+    h->rrlu_profile = on ? 1 : 0;
+    return TCI_OK;
+}
+
+int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps) {
+    if (!h) return TCI_ERR_INVALID;
+    if (h_ms3) for (int i = 0; i < 3; ++i) h_ms3[i] = h->rrlu_ms[i];
+    if (h_steps) *h_steps = h->rrlu_steps;
+    return TCI_OK;
+}
+
+} // extern "C"

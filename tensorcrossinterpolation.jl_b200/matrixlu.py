@@ -1,0 +1,163 @@
+"""Host-side mirror of src/matrixlu.jl and src/matrixluci.jl: `rrlu`, `rrlu_inplace` (rrlu!), the
+`rrLU` result type with its accessors, and `submatrixargmax`.  All arithmetic runs in the CUDA
+library (csrc/rrlu.cu); this file only marshals arguments and mirrors names/defaults/errors."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import TCIError, lib, p_f64, p_i64
+
+INT_MAX = np.iinfo(np.int64).max
+
+
+class rrLU:
+    """rrLU{Float64} (matrixlu.jl:200-207).  rowpermutation/colpermutation are 1-based like Julia.
+    L and U are numpy (host) or torch.cuda (device) matrices depending on the entry point used."""
+
+    def __init__(self, rowpermutation, colpermutation, L, U, leftorthogonal, npivot, error, pivoterrors):
+        self.rowpermutation = rowpermutation
+        self.colpermutation = colpermutation
+        self.L, self.U = L, U
+        self.leftorthogonal = bool(leftorthogonal)
+        self.npivot = int(npivot)
+        self.error = float(error)
+        self._pivoterrors = pivoterrors
+
+    def size(self):                                       # matrixlu.jl:685-687
+        return (self.L.shape[0], self.U.shape[1])
+
+    def left(self, permute=True):                         # matrixlu.jl:716-724
+        if not permute:
+            return self.L
+        out = _empty_like(self.L)
+        out[_index(self.rowpermutation - 1, self.L), :] = self.L
+        return out
+
+    def right(self, permute=True):                        # matrixlu.jl:738-746
+        if not permute:
+            return self.U
+        out = _empty_like(self.U)
+        out[:, _index(self.colpermutation - 1, self.U)] = self.U
+        return out
+
+    def diag(self):                                       # matrixlu.jl:756-762
+        M = self.U if self.leftorthogonal else self.L
+        return np.array([float(M[i, i]) for i in range(self.npivot)])
+
+    def rowindices(self):                                 # matrixlu.jl:769-771
+        return self.rowpermutation[: self.npivot].copy()
+
+    def colindices(self):                                 # matrixlu.jl:778-780
+        return self.colpermutation[: self.npivot].copy()
+
+    def npivots(self):                                    # matrixlu.jl:787-789
+        return self.npivot
+
+    def pivoterrors(self):                                # matrixlu.jl:799-801
+        return self._pivoterrors.copy()
+
+    def lastpivoterror(self):                             # matrixlu.jl:811-813
+        return self.error
+
+
+def _empty_like(M):
+    if isinstance(M, np.ndarray):
+        return np.empty_like(M)
+    import torch
+    return torch.empty_like(M)
+
+
+def _index(idx, M):
+    if isinstance(M, np.ndarray):
+        return idx
+    import torch
+    return torch.as_tensor(idx, device=M.device)
+
+
+def _maxrank(maxrank, m, n):
+    return int(min(maxrank, m, n)) if maxrank is not None else int(min(m, n))
+
+
+def rrlu(A, maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None):
+    """rrlu(A; maxrank, reltol, abstol, leftorthogonal) — matrixlu.jl:455-463.  A: host matrix (numpy);
+    it is not modified.  Returns an rrLU with host L/U."""
+    h = handle or _lib.default_handle()
+    A = np.asarray(A, dtype=np.float64)
+    if A.ndim != 2:
+        raise TCIError(_lib.TCI_ERR_INVALID, "rrlu: A must be a matrix")
+    if not A.flags.f_contiguous:
+        A = np.asfortranarray(A)
+    m, n = A.shape
+    mr = _maxrank(maxrank, m, n)
+    rowperm = np.zeros(m, dtype=np.int64)
+    colperm = np.zeros(n, dtype=np.int64)
+    L = np.zeros((m, max(mr, 1)), order="F")
+    U = np.zeros((max(mr, 1), n), order="F")
+    pe = np.zeros(mr + 1)
+    npivot, err = C.c_int64(), C.c_double()
+    h.check(lib().tci_rrlu_host_f64(h.h, p_f64(A), C.c_int64(m), C.c_int64(n), C.c_int64(max(m, 1)), C.c_int64(mr),
+                                    C.c_double(reltol), C.c_double(abstol), int(bool(leftorthogonal)), p_i64(rowperm),
+                                    p_i64(colperm), C.byref(npivot), C.byref(err), p_f64(L), C.c_int64(max(m, 1)),
+                                    p_f64(U), C.c_int64(max(mr, 1)), p_f64(pe)))
+    r = npivot.value
+    return rrLU(rowperm, colperm, np.asfortranarray(L[:, :r]), np.asfortranarray(U[:r, :]), leftorthogonal, r, err.value,
+                pe[: r + 1].copy())
+
+
+def rrlu_inplace(A, maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None, extract=True):
+    """rrlu!(A; ...) — matrixlu.jl:420-430 on a DEVICE matrix: `A` is a column-major view held in a torch
+    CUDA tensor of shape (n, lda) (i.e. A.T of the logical m x n matrix, lda >= m), overwritten like the
+    reference overwrites A.  Returns an rrLU whose L/U are torch CUDA tensors (logical m x r and r x n,
+    stored transposed so that they are column-major)."""
+    import torch
+    h = handle or _lib.default_handle()
+    n, lda = A.shape
+    m = getattr(A, "_tci_rows", lda)
+    return _rrlu_device(h, A, m, n, lda, maxrank, reltol, abstol, leftorthogonal, extract)
+
+
+def _rrlu_device(h, At, m, n, lda, maxrank, reltol, abstol, leftorthogonal, extract=True):
+    import torch
+    assert At.is_cuda and At.dtype == torch.float64 and At.is_contiguous()
+    mr = _maxrank(maxrank, m, n)
+    rowperm = np.zeros(m, dtype=np.int64)
+    colperm = np.zeros(n, dtype=np.int64)
+    pe = np.zeros(mr + 1)
+    npivot, err = C.c_int64(), C.c_double()
+    Lt = torch.empty((max(mr, 1), max(m, 1)), dtype=torch.float64, device=At.device) if extract else None
+    Ut = torch.empty((max(n, 1), max(mr, 1)), dtype=torch.float64, device=At.device) if extract else None
+    h.check(lib().tci_rrlu_inplace_f64(h.h, C.c_void_p(At.data_ptr()), C.c_int64(m), C.c_int64(n), C.c_int64(lda),
+                                       C.c_int64(mr), C.c_double(reltol), C.c_double(abstol), int(bool(leftorthogonal)),
+                                       p_i64(rowperm), p_i64(colperm), C.byref(npivot), C.byref(err),
+                                       C.c_void_p(Lt.data_ptr() if extract else 0), C.c_int64(max(m, 1)),
+                                       C.c_void_p(Ut.data_ptr() if extract else 0), C.c_int64(max(mr, 1)), p_f64(pe)))
+    r = npivot.value
+    L = Lt[:r, :m].T if extract else None                 # logical m x r view, column-major storage
+    U = Ut[:n, :r].T if extract else None                 # logical r x n view, column-major storage
+    return rrLU(rowperm, colperm, L, U, leftorthogonal, r, err.value, pe[: r + 1].copy())
+
+
+def submatrixargmax(A, startindex, handle=None):
+    """submatrixargmax(abs2, A, startindex) — matrixlu.jl:133-135; A host matrix; 1-based result."""
+    import torch
+    h = handle or _lib.default_handle()
+    A = np.asfortranarray(np.asarray(A, dtype=np.float64))
+    m, n = A.shape
+    if startindex > m or startindex < 1:
+        raise TCIError(_lib.TCI_ERR_INVALID, "rows must not be empty")
+    if startindex > n:
+        raise TCIError(_lib.TCI_ERR_INVALID, "cols must not be empty")
+    dA = torch.from_numpy(np.ascontiguousarray(A.T)).to(f"cuda:{h.device}")
+    r, c = C.c_int64(), C.c_int64()
+    h.check(lib().tci_submatrixargmax_abs2_f64(h.h, C.c_void_p(dA.data_ptr()), C.c_int64(m), C.c_int64(n), C.c_int64(m),
+                                               C.c_int64(startindex), C.byref(r), C.byref(c)))
+    return r.value, c.value
+
+
+def rrlu_last_timing(handle=None):
+    h = handle or _lib.default_handle()
+    ms = np.zeros(3)
+    steps = C.c_int64()
+    h.check(lib().tci_rrlu_last_timing(h.h, p_f64(ms), C.byref(steps)))
+    return {"loop_ms": float(ms[0]), "extract_ms": float(ms[2]), "steps": steps.value}
