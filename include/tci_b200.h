@@ -96,6 +96,81 @@ int tci_submatrixargmax_abs2_f64(tci_handle h, const double* d_A, int64_t m, int
 int tci_rrlu_set_profiling(tci_handle h, int on);
 int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps);
 
+/* ---- K1: batched function evaluation + Pi assembly ------------------------------------------------
+ * The target function is a DEVICE functor (the reference's `f(indexset)::Float64`, evaluated on the GPU).
+ * Built-in kinds (parameters in h_params):
+ *   1 LORENTZ      p0 / (1 + sum_i v_i^2)                         README.md:21-29, test/test_tensorci2.jl:249
+ *   2 QEXPSIN      exp(-p0 x) sin(2 pi p1 x^p2), x = sum_i (v_i - 1) 2^-i     test/test_tensorci2.jl:437
+ *   3 QEXPPLUSSIN  exp(-p0 x) + p1 sin(p2 x)                      test/test_globalsearch.jl:14
+ *   4 SUM          p0 * sum_i v_i                                 test/test_batcheval.jl:18
+ *   5 QEXP2        exp(-p0 x) + p1 exp(-p2 x)                     test/test_tensorci2.jl:63,:146
+ * tci_functor_dense: lookup in a column-major table T[v_1, ..., v_N] (copied to the device).
+ * tci_functor_from_source: the plugin path — CUDA C++ source that defines
+ *     __device__ double tci_user_f(const int* idx, int n, const double* params, int nparams);
+ *   (idx = the full 1-based multi-index, as the reference passes to f) is compiled with NVRTC for sm_100a.
+ */
+enum { TCI_F_LORENTZ_ID = 1, TCI_F_QEXPSIN_ID = 2, TCI_F_QEXPPLUSSIN_ID = 3, TCI_F_SUM_ID = 4, TCI_F_QEXP2_ID = 5 };
+int tci_functor_builtin(tci_handle h, int kind, const double* h_params, int nparams, tci_functor* out);
+int tci_functor_dense(tci_handle h, const double* h_table, const int32_t* h_dims, int ndims, tci_functor* out);
+int tci_functor_from_source(tci_handle h, const char* cuda_src, const double* h_params, int nparams, tci_functor* out);
+int tci_functor_destroy(tci_handle h, tci_functor f);
+
+/* Replaces  _batchevaluate_dispatch / (f::BatchEvaluator)(leftindexset, rightindexset, Val(M))
+ *           src/batcheval.jl:131-175, :196-214 as called by filltensor src/tensorci2.jl:475-497,
+ *           and  updatemaxsample!  src/tensorci2.jl:636-638.
+ * h_left: nleft x nl int32 (row = one 1-based multi-index), h_right: nright x nr; M = nsites - nl - nr free
+ * centre sites (<= 8), enumerated first-index-fastest (batcheval.jl:160).  Element (i, c, j) is written to
+ * d_out[i + c*stride_c + j*stride_j]; stride_c <= 0 means nleft and stride_j <= 0 means stride_c*prod(centre
+ * dims), i.e. the dense column-major Array{Float64,M+2} of the reference.  Empty index sets write nothing
+ * (batcheval.jl:140-142).  h_maxabs (may be NULL) is in/out: max(|*h_maxabs|, max |value|), NaN-propagating.
+ */
+int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                      const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                      double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs);
+
+/* ---- K4a: FP64 dense algebra for site tensors (FP64 tensor pipe, DMMA) ------------------------------
+ * tci_gemm_f64: C = alpha * A * B + beta * C, batched.  Element strides make transposes/reshaped views free:
+ *   A(m,k) = d_A[m*sam + k*sak + z*bsa], B(k,n) = d_B[k*sbk + n*sbn + z*bsb], C(m,n) = d_C[m*scm + n*scn + z*bsc].
+ * Replaces the `amat * bmat` of _contract (src/contraction.jl:214) and every `*` on the path
+ * (src/matrixluci.jl:164,:176, src/abstracttensortrain.jl:341,:436).
+ */
+int tci_gemm_f64(tci_handle h, int64_t M, int64_t N, int64_t K, double alpha,
+                 const double* d_A, int64_t sam, int64_t sak, const double* d_B, int64_t sbk, int64_t sbn,
+                 double beta, double* d_C, int64_t scm, int64_t scn,
+                 int64_t batch, int64_t bsa, int64_t bsb, int64_t bsc);
+
+/* X * T = B in place on B (q x r); T (r x r) lower (lower != 0) or upper triangular, optionally with an implicit
+ * unit diagonal; element strides as above.  Replaces `L2 / LowerTriangular(L1)` and `UpperTriangular(U1) \ U2`
+ * (src/matrixluci.jl:207, :235; the left solve is the right solve on transposed strides). */
+int tci_trsm_right_f64(tci_handle h, const double* d_T, int64_t st_row, int64_t st_col, int64_t r, int lower, int unit,
+                       double* d_B, int64_t sb_row, int64_t sb_col, int64_t q);
+
+/* Replaces  left(luci::MatrixLUCI) / right(luci)  src/matrixluci.jl:256-283 (colstimespivotinv :194-213,
+ * rowmatrix :175-177, colmatrix :161-165, pivotinvtimesrows :227-241) from the outputs of tci_rrlu_*:
+ * d_left (m x r, ld ldleft) and d_right (r x n, ld ldright); either may be NULL. */
+int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int leftorthogonal,
+                         const int64_t* h_rowperm, const int64_t* h_colperm,
+                         const double* d_L, int64_t ldl, const double* d_U, int64_t ldu,
+                         double* d_left, int64_t ldleft, double* d_right, int64_t ldright);
+
+/* Replaces  Tmat = transpose(transpose(P) \ transpose(Pi1))  src/tensorci2.jl:626:  X = B * inv(P) with
+ * B (q x r, ld ldb), P (r x r, ld ldp), X (q x r, ld ldx).  P is factorised by the full-pivot rrLU above
+ * (at least as stable as the LAPACK partial-pivot LU the reference calls), then two triangular solves. */
+int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb, const double* d_P, int64_t r, int64_t ldp,
+                        double* d_X, int64_t ldx);
+
+/* ---- K4b: TensorTrain sum / evaluate on device-resident cores ---------------------------------------
+ * A core is the column-major (chi_l, d, chi_r) array of the reference (d = product of the site legs), i.e. a
+ * (chi_l*d) x chi_r matrix; h_core_ptrs[b] is its DEVICE pointer, h_shapes[3b..3b+2] = (chi_l, d, chi_r),
+ * h_lds[b] its leading dimension (NULL: dense).
+ * tci_tt_sum_f64       replaces sum(tt)                 src/abstracttensortrain.jl:428-441
+ * tci_tt_evaluate_f64  replaces evaluate(tt, indexset)  src/abstracttensortrain.jl:328-342 for a batch of
+ *                      npoints multi-indices (h_indices: npoints x nsites, 1-based); values to h_out. */
+int tci_tt_sum_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds,
+                   int nsites, double* h_out);
+int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds,
+                        int nsites, const int32_t* h_indices, int64_t npoints, double* h_out);
+
 #ifdef __cplusplus
 }
 #endif

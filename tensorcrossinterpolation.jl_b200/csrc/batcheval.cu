@@ -1,0 +1,367 @@
+// batcheval.cu — K1: batched evaluation of the target function over Iset x (centre sites) x Jset and
+// assembly of the result (the Pi matrix of src/tensorci2.jl:848-852) straight into HBM.
+//
+// Replaces the scalar triple loop of src/batcheval.jl:157-171 (one closure call per element on a
+// reused Vector{Int}) and the extra pass of updatemaxsample! (src/tensorci2.jl:636-638, util.jl:34-43).
+//
+// Layout decisions (B200-first, not a translation):
+//   * the function is a DEVICE functor.  Built-ins are monoid functors: a small State is folded over
+//     the sites (push), states of disjoint site ranges combine (merge), and `finish` maps the state to
+//     the value.  That makes the evaluation separable: one tiny kernel folds every left multi-index and
+//     every right multi-index once (|I| + |J| threads), the assembly kernel then does
+//     merge(L[i], centre digits, R[j]) + finish per element — O(1) integer work per element instead of
+//     O(number of sites), and no per-thread index array.
+//   * user functors arrive as CUDA source through the C ABI and are compiled with NVRTC for sm_100a
+//     (tci_functor_from_source); they see the full multi-index like the reference's f(indexset).
+//   * output element (i, c, j) goes to out[i + c*stride_c + j*stride_j]: consecutive threads write
+//     consecutive i (coalesced 256 B per warp); the strides let the caller pad the leading dimension
+//     so the rrLU kernels can use 128-bit accesses on the same buffer.
+//   * max|value| (and a NaN flag, Julia's max propagates NaN) is reduced in the same pass.
+#include "context.h"
+#include <cuda.h>
+#include <nvrtc.h>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+enum { TCI_F_LORENTZ = 1, TCI_F_QEXPSIN = 2, TCI_F_QEXPPLUSSIN = 3, TCI_F_SUM = 4, TCI_F_QEXP2 = 5, TCI_F_DENSE = 6, TCI_F_USER = 100 };
+
+struct tci_functor_s {
+    int kind = 0;
+    double p[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int nparams = 0;
+    double* d_table = nullptr;           // F_DENSE
+    long long* d_strides = nullptr;
+    int ndims = 0;
+    double* d_params = nullptr;          // F_USER
+    CUmodule mod = nullptr;
+    CUfunction fn = nullptr;
+};
+
+namespace {
+
+constexpr int kMaxSites = 128;
+
+struct EvalShape {
+    int nl, nr, ncent_sites;             // multi-index lengths
+    int cdims[8];                        // centre local dims (ncent_sites <= 8)
+    long long nleft, nright, ncent;      // counts
+    long long stride_c, stride_j;        // output strides (stride of i is 1)
+};
+
+// ---- built-in monoid functors ---------------------------------------------------------------------
+struct LorentzF {                        // p0 / (1 + sum v^2): README.md:21-29
+    double coeff;
+    typedef long long State;
+    __device__ State zero() const { return 0; }
+    __device__ void push(State& s, int, int v) const { s += (long long)v * v; }
+    __device__ State merge(State a, State b) const { return a + b; }
+    __device__ double finish(State s) const { return coeff / (double)(1 + s); }
+};
+struct SumF {                            // p0 * sum v: test/test_batcheval.jl:18
+    double scale;
+    typedef long long State;
+    __device__ State zero() const { return 0; }
+    __device__ void push(State& s, int, int v) const { s += v; }
+    __device__ State merge(State a, State b) const { return a + b; }
+    __device__ double finish(State s) const { return scale * (double)s; }
+};
+// quantics coordinate x = sum_i (b_i - 1) 2^-(i)  (1-based site i; exact in FP64 for <= 52 bits, so the
+// order of the partial sums does not matter)
+template <int KIND>
+struct QuanticsF {
+    double p0, p1, p2;
+    typedef double State;
+    __device__ State zero() const { return 0.0; }
+    __device__ void push(State& s, int site, int v) const { s += ldexp((double)(v - 1), -(site + 1)); }
+    __device__ State merge(State a, State b) const { return a + b; }
+    __device__ double finish(State x) const {
+        if (KIND == TCI_F_QEXPSIN) return exp(-p0 * x) * sin(2.0 * 3.14159265358979323846 * p1 * pow(x, p2));   // test_tensorci2.jl:437
+        if (KIND == TCI_F_QEXPPLUSSIN) return exp(-p0 * x) + p1 * sin(p2 * x);                                  // test_globalsearch.jl:14
+        return exp(-p0 * x) + p1 * exp(-p2 * x);                                                               // test_tensorci2.jl:63,:146
+    }
+};
+struct DenseF {                          // column-major table lookup
+    const double* table; const long long* strides;
+    typedef long long State;
+    __device__ State zero() const { return 0; }
+    __device__ void push(State& s, int site, int v) const { s += (long long)(v - 1) * strides[site]; }
+    __device__ State merge(State a, State b) const { return a + b; }
+    __device__ double finish(State s) const { return table[s]; }
+};
+
+// fold the left multi-indices (sites 0..nl-1) and the right ones (sites N-nr..N-1)
+template <class F>
+__global__ void fold_kernel(F f, const int* __restrict__ left, const int* __restrict__ right, EvalShape sh, int nsites,
+                            typename F::State* Ls, typename F::State* Rs) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < sh.nleft) {
+        typename F::State s = f.zero();
+        for (int p = 0; p < sh.nl; ++p) f.push(s, p, left[t * sh.nl + p]);
+        Ls[t] = s;
+    } else if (t < sh.nleft + sh.nright) {
+        const long long j = t - sh.nleft;
+        typename F::State s = f.zero();
+        for (int p = 0; p < sh.nr; ++p) f.push(s, nsites - sh.nr + p, right[j * sh.nr + p]);
+        Rs[j] = s;
+    }
+}
+
+__device__ __forceinline__ void maxabs_commit(double v, bool isn, unsigned long long* maxbits, int* nanflag) {
+    // block-level: warp shuffle max, then one atomic per warp (non-negative doubles order like their bit patterns)
+    unsigned long long b = (unsigned long long)__double_as_longlong(v);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        unsigned long long o = __shfl_down_sync(0xffffffffu, b, d);
+        b = o > b ? o : b;
+    }
+    const unsigned anyn = __ballot_sync(0xffffffffu, isn);
+    if ((threadIdx.x & 31) == 0) {
+        if (b) atomicMax(maxbits, b);
+        if (anyn) atomicOr(nanflag, 1);
+    }
+}
+
+template <class F>
+__global__ void __launch_bounds__(256)
+assemble_kernel(F f, EvalShape sh, int nsites, const typename F::State* __restrict__ Ls,
+                const typename F::State* __restrict__ Rs, double* __restrict__ out,
+                unsigned long long* maxbits, int* nanflag) {
+    // grid: x over i (fastest), y over (c, j) pairs in chunks
+    const long long ncj = sh.ncent * sh.nright;
+    double mx = 0.0; bool isn = false;
+    for (long long cj = blockIdx.y; cj < ncj; cj += gridDim.y) {
+        const long long c = cj % sh.ncent, j = cj / sh.ncent;
+        typename F::State cs = Rs[j];
+        long long rem = c;
+        for (int x = 0; x < sh.ncent_sites; ++x) { f.push(cs, sh.nl + x, (int)(rem % sh.cdims[x]) + 1); rem /= sh.cdims[x]; }
+        double* col = out + c * sh.stride_c + j * sh.stride_j;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < sh.nleft; i += (long long)gridDim.x * blockDim.x) {
+            const double v = f.finish(f.merge(Ls[i], cs));
+            col[i] = v;
+            const double a = fabs(v);
+            if (a != a) isn = true; else mx = a > mx ? a : mx;
+        }
+    }
+    maxabs_commit(mx, isn, maxbits, nanflag);
+}
+
+// generic kernel source for NVRTC user functors; the user supplies
+//   __device__ double tci_user_f(const int* idx, int n, const double* params, int nparams);
+const char* kUserKernelSrc = R"SRC(
+extern "C" __global__ void __launch_bounds__(256)
+tci_user_assemble(const int* __restrict__ left, const int* __restrict__ right, int nl, int nr, int ncs,
+                  int cd0, int cd1, int cd2, int cd3, int cd4, int cd5, int cd6, int cd7,
+                  long long nleft, long long nright, long long ncent, long long stride_c, long long stride_j,
+                  const double* __restrict__ params, int nparams, double* __restrict__ out,
+                  unsigned long long* maxbits, int* nanflag) {
+    int cdims[8] = {cd0, cd1, cd2, cd3, cd4, cd5, cd6, cd7};
+    int idx[TCI_MAX_SITES];
+    const int n = nl + ncs + nr;
+    const long long total = nleft * ncent * nright;
+    double mx = 0.0; bool isn = false;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const long long i = t % nleft, cj = t / nleft, c = cj % ncent, j = cj / ncent;
+        for (int p = 0; p < nl; ++p) idx[p] = left[i * nl + p];
+        long long rem = c;
+        for (int x = 0; x < ncs; ++x) { idx[nl + x] = (int)(rem % cdims[x]) + 1; rem /= cdims[x]; }
+        for (int p = 0; p < nr; ++p) idx[nl + ncs + p] = right[j * nr + p];
+        const double v = tci_user_f(idx, n, params, nparams);
+        out[i + c * stride_c + j * stride_j] = v;
+        const double a = fabs(v);
+        if (a != a) isn = true; else mx = a > mx ? a : mx;
+    }
+    unsigned long long b = (unsigned long long)__double_as_longlong(mx);
+    for (int d = 16; d > 0; d >>= 1) { unsigned long long o = __shfl_down_sync(0xffffffffu, b, d); b = o > b ? o : b; }
+    const unsigned anyn = __ballot_sync(0xffffffffu, isn);
+    if ((threadIdx.x & 31) == 0) { if (b) atomicMax(maxbits, b); if (anyn) atomicOr(nanflag, 1); }
+}
+)SRC";
+
+} // namespace
+
+namespace {
+
+struct EvalBuffers { int* d_left; int* d_right; void* Ls; void* Rs; unsigned long long* maxbits; int* nanflag; };
+
+int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, const EvalShape& sh, EvalBuffers* b) {
+    const size_t nli = (size_t)sh.nleft * sh.nl, nri = (size_t)sh.nright * sh.nr;
+    const size_t ints = ((nli + nri) * sizeof(int) + 255) & ~(size_t)255;
+    int rc = tci_ws_reserve(h, h->ws_a, ints + 256);
+    if (rc) return rc;
+    rc = tci_ws_reserve(h, h->ws_b, sizeof(long long) * (size_t)(sh.nleft + sh.nright) + 256);
+    if (rc) return rc;
+    rc = tci_pinned_reserve(h, ints + 64);
+    if (rc) return rc;
+    int* pin = (int*)h->pinned;
+    if (nli) memcpy(pin, h_left, nli * sizeof(int));
+    if (nri) memcpy(pin + nli, h_right, nri * sizeof(int));
+    b->d_left = (int*)h->ws_a.ptr; b->d_right = b->d_left + nli;
+    b->maxbits = (unsigned long long*)((char*)h->ws_a.ptr + ints);
+    b->nanflag = (int*)(b->maxbits + 1);
+    b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + sizeof(long long) * (size_t)sh.nleft;
+    TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
+    if (nli + nri) {
+        TCI_CUDA(h, cudaMemcpyAsync(b->d_left, pin, (nli + nri) * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));     // the pinned staging area is reused by the next call
+    }
+    return TCI_OK;
+}
+
+template <class F>
+int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const EvalBuffers& b, double* d_out) {
+    typedef typename F::State S;
+    const long long nfold = sh.nleft + sh.nright;
+    fold_kernel<F><<<(unsigned)((nfold + 255) / 256), 256, 0, h->stream>>>(f, b.d_left, b.d_right, sh, nsites, (S*)b.Ls, (S*)b.Rs);
+    TCI_LAUNCH_CHECK(h);
+    long long gx = (sh.nleft + 255) / 256;
+    if (gx > 32) gx = 32;
+    long long gy = sh.ncent * sh.nright;
+    const long long want = (long long)h->num_sms * 16 / gx + 1;
+    if (gy > want) gy = want;
+    if (gy > 65535) gy = 65535;
+    assemble_kernel<F><<<dim3((unsigned)gx, (unsigned)gy), 256, 0, h->stream>>>(f, sh, nsites, (const S*)b.Ls, (const S*)b.Rs, d_out, b.maxbits, b.nanflag);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+int run_user(tci_handle h, tci_functor f, const EvalShape& sh, const EvalBuffers& b, double* d_out) {
+    int nl = sh.nl, nr = sh.nr, ncs = sh.ncent_sites, np = f->nparams;
+    int cd[8]; for (int i = 0; i < 8; ++i) cd[i] = sh.cdims[i];
+    long long nleft = sh.nleft, nright = sh.nright, ncent = sh.ncent, sc = sh.stride_c, sj = sh.stride_j;
+    const int* dl = b.d_left; const int* dr = b.d_right; const double* dp = f->d_params;
+    unsigned long long* mb = b.maxbits; int* nf = b.nanflag;
+    void* args[] = {&dl, &dr, &nl, &nr, &ncs, &cd[0], &cd[1], &cd[2], &cd[3], &cd[4], &cd[5], &cd[6], &cd[7],
+                    &nleft, &nright, &ncent, &sc, &sj, &dp, &np, &d_out, &mb, &nf};
+    long long total = nleft * ncent * nright;
+    long long blocks = (total + 255) / 256;
+    if (blocks > (long long)h->num_sms * 8) blocks = (long long)h->num_sms * 8;
+    CUresult r = cuLaunchKernel(f->fn, (unsigned)blocks, 1, 1, 256, 1, 1, 0, (CUstream)h->stream, args, nullptr);
+    h->launches++;
+    if (r != CUDA_SUCCESS) { const char* s = nullptr; cuGetErrorString(r, &s); return tci_fail(h, TCI_ERR_CUDA, "cuLaunchKernel(user functor): %s", s ? s : "?"); }
+    return TCI_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int tci_functor_builtin(tci_handle h, int kind, const double* h_params, int nparams, tci_functor* out) {
+    if (!h || !out) return TCI_ERR_INVALID;
+    if (kind < TCI_F_LORENTZ || kind > TCI_F_QEXP2) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_builtin: unknown kind %d", kind);
+    const int need = (kind == TCI_F_LORENTZ || kind == TCI_F_SUM) ? 1 : 3;
+    if (nparams < need || nparams > 8) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_builtin: kind %d needs %d parameters", kind, need);
+    tci_functor f = new tci_functor_s();
+    f->kind = kind; f->nparams = nparams;
+    for (int i = 0; i < nparams; ++i) f->p[i] = h_params[i];
+    *out = f;
+    return TCI_OK;
+}
+
+int tci_functor_dense(tci_handle h, const double* h_table, const int32_t* h_dims, int ndims, tci_functor* out) {
+    if (!h || !out || !h_table || !h_dims || ndims < 1 || ndims > kMaxSites) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_dense: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    std::vector<long long> strides(ndims);
+    long long tot = 1;
+    for (int i = 0; i < ndims; ++i) { strides[i] = tot; tot *= h_dims[i]; }
+    tci_functor f = new tci_functor_s();
+    f->kind = TCI_F_DENSE; f->ndims = ndims;
+    if (cudaMalloc(&f->d_table, sizeof(double) * tot) != cudaSuccess || cudaMalloc(&f->d_strides, sizeof(long long) * ndims) != cudaSuccess) {
+        delete f; return tci_fail(h, TCI_ERR_NOMEM, "tci_functor_dense: cudaMalloc failed");
+    }
+    TCI_CUDA(h, cudaMemcpy(f->d_table, h_table, sizeof(double) * tot, cudaMemcpyHostToDevice));
+    TCI_CUDA(h, cudaMemcpy(f->d_strides, strides.data(), sizeof(long long) * ndims, cudaMemcpyHostToDevice));
+    *out = f;
+    return TCI_OK;
+}
+
+int tci_functor_from_source(tci_handle h, const char* cuda_src, const double* h_params, int nparams, tci_functor* out) {
+    if (!h || !out || !cuda_src || nparams < 0) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_from_source: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    TCI_CUDA(h, cudaFree(0));
+    std::string src = std::string(cuda_src) + "\n" + kUserKernelSrc;
+    nvrtcProgram prog;
+    if (nvrtcCreateProgram(&prog, src.c_str(), "tci_user_functor.cu", 0, nullptr, nullptr) != NVRTC_SUCCESS)
+        return tci_fail(h, TCI_ERR_NVRTC, "nvrtcCreateProgram failed");
+    const char* opts[] = {"--gpu-architecture=sm_100a", "-DTCI_MAX_SITES=128", "--fmad=false", "-std=c++17", "-lineinfo"};
+    nvrtcResult cr = nvrtcCompileProgram(prog, 5, opts);
+    if (cr != NVRTC_SUCCESS) {
+        size_t ls = 0; nvrtcGetProgramLogSize(prog, &ls);
+        std::string log(ls, '\0'); nvrtcGetProgramLog(prog, &log[0]);
+        nvrtcDestroyProgram(&prog);
+        return tci_fail(h, TCI_ERR_NVRTC, "user functor failed to compile: %s", log.c_str());
+    }
+    size_t cs = 0; nvrtcGetCUBINSize(prog, &cs);
+    std::vector<char> cubin(cs); nvrtcGetCUBIN(prog, cubin.data());
+    nvrtcDestroyProgram(&prog);
+    tci_functor f = new tci_functor_s();
+    f->kind = TCI_F_USER; f->nparams = nparams;
+    CUresult r = cuModuleLoadData(&f->mod, cubin.data());
+    if (r == CUDA_SUCCESS) r = cuModuleGetFunction(&f->fn, f->mod, "tci_user_assemble");
+    if (r != CUDA_SUCCESS) { const char* s = nullptr; cuGetErrorString(r, &s); delete f; return tci_fail(h, TCI_ERR_CUDA, "loading user functor: %s", s ? s : "?"); }
+    if (cudaMalloc(&f->d_params, sizeof(double) * (nparams > 0 ? nparams : 1)) != cudaSuccess) { cuModuleUnload(f->mod); delete f; return tci_fail(h, TCI_ERR_NOMEM, "cudaMalloc failed"); }
+    if (nparams > 0) TCI_CUDA(h, cudaMemcpy(f->d_params, h_params, sizeof(double) * nparams, cudaMemcpyHostToDevice));
+    *out = f;
+    return TCI_OK;
+}
+
+int tci_functor_destroy(tci_handle h, tci_functor f) {
+    if (!f) return TCI_OK;
+    if (h) { cudaSetDevice(h->device); cudaStreamSynchronize(h->stream); }
+    if (f->d_table) cudaFree(f->d_table);
+    if (f->d_strides) cudaFree(f->d_strides);
+    if (f->d_params) cudaFree(f->d_params);
+    if (f->mod) cuModuleUnload(f->mod);
+    delete f;
+    return TCI_OK;
+}
+
+int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                      const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                      double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+    if (!h) return TCI_ERR_INVALID;
+    if (!f || !h_localdims) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: NULL functor or localdims");
+    if (nsites < 1 || nsites > kMaxSites) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: nsites must be in 1..%d", kMaxSites);
+    const int ncs = nsites - nl - nr;
+    if (nl < 0 || nr < 0 || ncs < 0) return tci_fail(h, TCI_ERR_INVALID, "Invalid number of central indices");    // tensorci2.jl:492
+    if (ncs > 8) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: at most 8 free centre sites");
+    if (nleft < 0 || nright < 0) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: negative set size");
+    if (nleft == 0 || nright == 0) return TCI_OK;                               // batcheval.jl:140-142: empty result
+    if (f->kind == TCI_F_DENSE && f->ndims != nsites) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, nsites);
+    if ((nl > 0 && !h_left) || (nr > 0 && !h_right) || !d_out) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: NULL buffer");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    EvalShape sh;
+    sh.nl = nl; sh.nr = nr; sh.ncent_sites = ncs; sh.nleft = nleft; sh.nright = nright; sh.ncent = 1;
+    for (int x = 0; x < 8; ++x) sh.cdims[x] = 1;
+    for (int x = 0; x < ncs; ++x) { sh.cdims[x] = h_localdims[nl + x]; sh.ncent *= h_localdims[nl + x]; }
+    sh.stride_c = stride_c > 0 ? stride_c : nleft;
+    sh.stride_j = stride_j > 0 ? stride_j : sh.stride_c * sh.ncent;
+    EvalBuffers b;
+    int rc = stage_tables(h, h_left, h_right, sh, &b);
+    if (rc) return rc;
+    switch (f->kind) {
+    case TCI_F_LORENTZ: rc = run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b, d_out); break;
+    case TCI_F_SUM: rc = run_builtin(h, SumF{f->p[0]}, sh, nsites, b, d_out); break;
+    case TCI_F_QEXPSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
+    case TCI_F_QEXPPLUSSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
+    case TCI_F_QEXP2: rc = run_builtin(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
+    case TCI_F_DENSE: rc = run_builtin(h, DenseF{f->d_table, f->d_strides}, sh, nsites, b, d_out); break;
+    case TCI_F_USER: rc = run_user(h, f, sh, b, d_out); break;
+    default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
+    }
+    if (rc) return rc;
+    if (h_maxabs) {
+        rc = tci_pinned_reserve(h, 64);
+        if (rc) return rc;
+        unsigned long long* pin = (unsigned long long*)h->pinned;
+        TCI_CUDA(h, cudaMemcpyAsync(pin, b.maxbits, 16, cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+        double mx; memcpy(&mx, &pin[0], 8);
+        int nf; memcpy(&nf, &pin[1], 4);
+        const double prev = fabs(*h_maxabs);                                    // util.jl:34-43: max(abs(x), abs(y)), NaN propagates
+        if (nf || prev != prev) *h_maxabs = NAN; else *h_maxabs = prev > mx ? prev : mx;
+    }
+    return TCI_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,360 @@
+// dense.cu — K4a: FP64 dense algebra for site-tensor formation.
+//
+//   tci_gemm_f64          strided/batched DGEMM on the FP64 tensor pipe (DMMA.8x8x4 via mma.sync m8n8k4.f64 —
+//                         tcgen05 has no FP64 kind, this is the FP64 tensor path sm_100a exposes)
+//   tci_trsm_right_f64    X * T = B for triangular T (blocked: 32x32 diagonal-block inverses + GEMMs)
+//   tci_luci_factors_f64  left(luci) / right(luci)   src/matrixluci.jl:161-283
+//   tci_solve_right_f64   Pi1 * inv(P)               src/tensorci2.jl:626
+//
+// Operands are addressed with explicit element strides (row stride, column stride), so transposes and
+// the reference's `permutedims`+`reshape` views (src/contraction.jl:211-212) cost nothing.
+#include "context.h"
+#include <cmath>
+#include <vector>
+
+namespace {
+
+constexpr int BM = 64, BN = 64, BK = 16, LDS = 68;      // LDS = 4 mod 16: conflict-free 64-bit fragment loads
+constexpr int GEMM_THREADS = 256;
+
+struct GemmArgs {
+    int M, N, K;
+    double alpha, beta;
+    const double* A; long long sam, sak, bsa;           // A(m,k) = A[m*sam + k*sak + z*bsa]
+    const double* B; long long sbk, sbn, bsb;           // B(k,n)
+    double* C; long long scm, scn, bsc;                 // C(m,n)
+};
+
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(GEMM_THREADS)
+gemm_dmma_kernel(GemmArgs g) {
+    __shared__ double As[2][BK][LDS];
+    __shared__ double Bs[2][BK][LDS];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int wm = warp & 1, wn = warp >> 1;            // warp tile: 32 rows x 16 cols
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const double* A = g.A + (long long)blockIdx.z * g.bsa;
+    const double* B = g.B + (long long)blockIdx.z * g.bsb;
+    double* C = g.C + (long long)blockIdx.z * g.bsc;
+    const bool a_mfast = (g.sam == 1) || (g.sak != 1);  // which index runs along consecutive threads
+    const bool b_kfast = (g.sbk == 1);
+
+    double acc[4][2][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    double ra[4], rb[4];
+    auto gload = [&](int k0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int m, k;
+            if (a_mfast) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
+            const int gm = m0 + m, gk = k0 + k;
+            ra[i] = (gm < g.M && gk < g.K) ? A[(long long)gm * g.sam + (long long)gk * g.sak] : 0.0;
+            int n, kb;
+            if (b_kfast) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
+            const int gn = n0 + n, gkb = k0 + kb;
+            rb[i] = (gn < g.N && gkb < g.K) ? B[(long long)gkb * g.sbk + (long long)gn * g.sbn] : 0.0;
+        }
+    };
+    auto sstore = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int m, k;
+            if (a_mfast) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
+            As[buf][k][m] = ra[i];
+            int n, kb;
+            if (b_kfast) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
+            Bs[buf][kb][n] = rb[i];
+        }
+    };
+
+    const int nk = (g.K + BK - 1) / BK;
+    gload(0);
+    sstore(0);
+    __syncthreads();
+    for (int kt = 0; kt < nk; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < nk) gload((kt + 1) * BK);
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 4) {
+            double a[4], b[2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = As[buf][kk + (lane & 3)][wm * 32 + i * 8 + (lane >> 2)];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) b[j] = Bs[buf][kk + (lane & 3)][wn * 16 + j * 8 + (lane >> 2)];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        if (kt + 1 < nk) sstore(buf ^ 1);
+        __syncthreads();
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int gm = m0 + wm * 32 + i * 8 + (lane >> 2);
+                const int gn = n0 + wn * 16 + j * 8 + (lane & 3) * 2 + e;
+                if (gm < g.M && gn < g.N) {
+                    double* p = C + (long long)gm * g.scm + (long long)gn * g.scn;
+                    double v = g.alpha * acc[i][j][e];
+                    if (g.beta != 0.0) v += g.beta * *p;
+                    *p = v;
+                }
+            }
+}
+
+__global__ void copy_strided_kernel(const double* __restrict__ src, long long ssr, long long ssc, double* __restrict__ dst,
+                                        long long dsr, long long dsc, int rows, int cols) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i < rows && j < cols) dst[(long long)i * dsr + (long long)j * dsc] = src[(long long)i * ssr + (long long)j * ssc];
+}
+
+int launch_gemm(tci_handle h, const GemmArgs& g, int batch) {
+    if (g.M <= 0 || g.N <= 0 || batch <= 0) return TCI_OK;
+    dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, batch);
+    gemm_dmma_kernel<<<grid, GEMM_THREADS, 0, h->stream>>>(g);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+// Inverse of each NB x NB diagonal block of a triangular matrix T (element (i,j) at T[i*sr + j*sc]), one
+// CUDA block per diagonal block.  inv is stored dense column-major NB x NB per block (zero outside the
+// triangle / beyond r).  lower != 0: lower triangular; unit != 0: implicit unit diagonal.
+constexpr int NB = 32;
+__global__ void diag_inverse_kernel(const double* __restrict__ T, long long sr, long long sc, int r, int lower, int unit,
+                                    double* __restrict__ inv) {
+    __shared__ double S[NB][NB + 1];
+    __shared__ double X[NB][NB + 1];
+    const int b = blockIdx.x, o = b * NB, nb = min(NB, r - o);
+    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x) {
+        const int i = e % NB, j = e / NB;
+        double v = 0.0;
+        if (i < nb && j < nb) {
+            const bool tri = lower ? (i >= j) : (i <= j);
+            if (tri) v = (i == j && unit) ? 1.0 : T[(long long)(o + i) * sr + (long long)(o + j) * sc];
+        } else if (i == j) v = 1.0;
+        S[i][j] = v; X[i][j] = 0.0;
+    }
+    __syncthreads();
+    const int j = threadIdx.x;                           // column j of the inverse: S * x = e_j
+    if (j < NB) {
+        if (lower) {
+            for (int i = j; i < NB; ++i) {
+                double s = (i == j) ? 1.0 : 0.0;
+                for (int k = j; k < i; ++k) s -= S[i][k] * X[k][j];
+                X[i][j] = s / S[i][i];
+            }
+        } else {
+            for (int i = j; i >= 0; --i) {
+                double s = (i == j) ? 1.0 : 0.0;
+                for (int k = i + 1; k <= j; ++k) s -= S[i][k] * X[k][j];
+                X[i][j] = s / S[i][i];
+            }
+        }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < NB * NB; e += blockDim.x) {
+        const int i = e % NB, jj = e / NB;
+        inv[(long long)b * NB * NB + (long long)jj * NB + i] = (i < nb && jj < nb) ? X[i][jj] : 0.0;
+    }
+}
+
+// X * T = B in place on B (q x r, element (i,j) at B[i*sbr + j*sbc]); T r x r triangular with strides (sr, sc).
+int trsm_right(tci_handle h, const double* T, long long sr, long long sc, int r, int lower, int unit,
+               double* Bm, long long sbr, long long sbc, int q) {
+    if (r <= 0 || q <= 0) return TCI_OK;
+    const int nblk = (r + NB - 1) / NB;
+    int rc = tci_ws_reserve(h, h->ws_c, sizeof(double) * ((size_t)nblk * NB * NB + (size_t)q * NB));
+    if (rc) return rc;
+    double* inv = (double*)h->ws_c.ptr;
+    double* tmp = inv + (size_t)nblk * NB * NB;           // q x NB scratch (column-major, ld q)
+    diag_inverse_kernel<<<nblk, 64, 0, h->stream>>>(T, sr, sc, r, lower, unit, inv);
+    TCI_LAUNCH_CHECK(h);
+    for (int s = 0; s < nblk; ++s) {
+        const int b = lower ? nblk - 1 - s : s;          // lower: last block column first; upper: first block first
+        const int o = b * NB, nb = (r - o < NB) ? r - o : NB;
+        // B_b -= X_done * T[done, b]
+        const int d0 = lower ? o + nb : 0, dn = lower ? r - d0 : o;
+        if (dn > 0) {
+            GemmArgs g{q, nb, dn, -1.0, 1.0, Bm + (long long)d0 * sbc, sbr, sbc, 0,
+                       T + (long long)d0 * sr + (long long)o * sc, sr, sc, 0, Bm + (long long)o * sbc, sbr, sbc, 0};
+            rc = launch_gemm(h, g, 1);
+            if (rc) return rc;
+        }
+        // X_b = B_b * inv(T_bb): GEMM into scratch (the product reads B_b), then copy back
+        GemmArgs g1{q, nb, nb, 1.0, 0.0, Bm + (long long)o * sbc, sbr, sbc, 0, inv + (size_t)b * NB * NB, 1, NB, 0, tmp, 1, q, 0};
+        rc = launch_gemm(h, g1, 1);
+        if (rc) return rc;
+        copy_strided_kernel<<<dim3((q + 255) / 256, nb), 256, 0, h->stream>>>(tmp, 1, q, Bm + (long long)o * sbc, sbr, sbc, q, nb);
+        TCI_LAUNCH_CHECK(h);
+    }
+    return TCI_OK;
+}
+
+} // namespace
+
+namespace {
+
+// out[perm[i], :] = (i < nident) ? e_i : W[i - woff, :]   (rows scattered through a 0-based permutation)
+__global__ void scatter_rows_kernel(double* __restrict__ out, long long ldo, const double* __restrict__ W, long long ldw,
+                                    const int* __restrict__ perm, int m, int r, int nident) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i >= m || j >= r) return;
+    const double v = (i < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)j * ldw + (i - nident)];
+    out[(long long)j * ldo + perm[i]] = v;
+}
+// out[:, perm[j]] = (j < nident) ? e_j : W[:, j - nident]
+__global__ void scatter_cols_kernel(double* __restrict__ out, long long ldo, const double* __restrict__ W, long long ldw,
+                                    const int* __restrict__ perm, int r, int n, int nident) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i >= r || j >= n) return;
+    const double v = (j < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)(j - nident) * ldw + i];
+    out[(long long)perm[j] * ldo + i] = v;
+}
+// W[:, j] = src[:, perm[j]]
+__global__ void gather_cols_kernel(double* __restrict__ W, long long ldw, const double* __restrict__ src, long long lds,
+                                   const int* __restrict__ perm, int q, int r) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+    if (i < q && j < r) W[(long long)j * ldw + i] = src[(long long)perm[j] * lds + i];
+}
+
+int upload_perm(tci_handle h, const int64_t* h_perm, int len, int* d_dst, size_t pinned_off) {
+    int* pin = (int*)((char*)h->pinned + pinned_off);
+    for (int i = 0; i < len; ++i) pin[i] = (int)(h_perm[i] - 1);
+    TCI_CUDA(h, cudaMemcpyAsync(d_dst, pin, sizeof(int) * len, cudaMemcpyHostToDevice, h->stream));
+    return TCI_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int tci_gemm_f64(tci_handle h, int64_t M, int64_t N, int64_t K, double alpha,
+                 const double* d_A, int64_t sam, int64_t sak, const double* d_B, int64_t sbk, int64_t sbn,
+                 double beta, double* d_C, int64_t scm, int64_t scn,
+                 int64_t batch, int64_t bsa, int64_t bsb, int64_t bsc) {
+    if (!h) return TCI_ERR_INVALID;
+    if (M < 0 || N < 0 || K < 0 || batch < 0 || M > INT32_MAX || N > INT32_MAX || K > INT32_MAX || batch > 65535)
+        return tci_fail(h, TCI_ERR_INVALID, "tci_gemm_f64: bad sizes");
+    if (M == 0 || N == 0 || batch == 0) return TCI_OK;
+    if (!d_C || (K > 0 && (!d_A || !d_B))) return tci_fail(h, TCI_ERR_INVALID, "tci_gemm_f64: NULL operand");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    GemmArgs g{(int)M, (int)N, (int)K, alpha, beta, d_A, sam, sak, bsa, d_B, sbk, sbn, bsb, d_C, scm, scn, bsc};
+    return launch_gemm(h, g, (int)batch);
+}
+
+int tci_trsm_right_f64(tci_handle h, const double* d_T, int64_t st_row, int64_t st_col, int64_t r, int lower, int unit,
+                       double* d_B, int64_t sb_row, int64_t sb_col, int64_t q) {
+    if (!h) return TCI_ERR_INVALID;
+    if (r < 0 || q < 0 || r > INT32_MAX || q > INT32_MAX) return tci_fail(h, TCI_ERR_INVALID, "tci_trsm_right_f64: bad sizes");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    return trsm_right(h, d_T, st_row, st_col, (int)r, lower, unit, d_B, sb_row, sb_col, (int)q);
+}
+
+int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int leftorthogonal,
+                         const int64_t* h_rowperm, const int64_t* h_colperm,
+                         const double* d_L, int64_t ldl, const double* d_U, int64_t ldu,
+                         double* d_left, int64_t ldleft, double* d_right, int64_t ldright) {
+    if (!h) return TCI_ERR_INVALID;
+    if (m < 0 || n < 0 || r < 0 || r > m || r > n) return tci_fail(h, TCI_ERR_INVALID, "tci_luci_factors_f64: bad sizes");
+    if (r == 0 || (!d_left && !d_right)) return TCI_OK;
+    if (!h_rowperm || !h_colperm || !d_L || !d_U) return tci_fail(h, TCI_ERR_INVALID, "tci_luci_factors_f64: NULL input");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    const int M = (int)m, N = (int)n, R = (int)r;
+    const size_t permbytes = ((sizeof(int) * (size_t)(M + N)) + 255) & ~(size_t)255;
+    const size_t wl = (size_t)M * R, wr = (size_t)R * N;
+    int rc = tci_ws_reserve(h, h->ws_a, permbytes + sizeof(double) * (wl > wr ? wl : wr) + 256);
+    if (rc) return rc;
+    rc = tci_pinned_reserve(h, permbytes + 64);
+    if (rc) return rc;
+    int* d_rp = (int*)h->ws_a.ptr; int* d_cp = d_rp + M;
+    double* W = (double*)((char*)h->ws_a.ptr + permbytes);
+    rc = upload_perm(h, h_rowperm, M, d_rp, 0); if (rc) return rc;
+    rc = upload_perm(h, h_colperm, N, d_cp, sizeof(int) * (size_t)M); if (rc) return rc;
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));       // pinned staging is reused by later calls
+    if (d_left) {
+        if (leftorthogonal) {                             // colstimespivotinv  matrixluci.jl:194-213
+            const int q = M - R;
+            if (q > 0) {
+                copy_strided_kernel<<<dim3((q + 255) / 256, R), 256, 0, h->stream>>>(d_L + R, 1, ldl, W, 1, q, q, R);
+                TCI_LAUNCH_CHECK(h);
+                rc = trsm_right(h, d_L, 1, ldl, R, 1, 1, W, 1, q, q);
+                if (rc) return rc;
+            }
+            scatter_rows_kernel<<<dim3((M + 255) / 256, R), 256, 0, h->stream>>>(d_left, ldleft, W, q > 0 ? q : 1, d_rp, M, R, R);
+            TCI_LAUNCH_CHECK(h);
+        } else {                                          // colmatrix  matrixluci.jl:161-165
+            GemmArgs g{M, R, R, 1.0, 0.0, d_L, 1, ldl, 0, d_U, 1, ldu, 0, W, 1, M, 0};
+            rc = launch_gemm(h, g, 1); if (rc) return rc;
+            scatter_rows_kernel<<<dim3((M + 255) / 256, R), 256, 0, h->stream>>>(d_left, ldleft, W, M, d_rp, M, R, 0);
+            TCI_LAUNCH_CHECK(h);
+        }
+    }
+    if (d_right) {
+        if (leftorthogonal) {                             // rowmatrix  matrixluci.jl:175-177
+            GemmArgs g{R, N, R, 1.0, 0.0, d_L, 1, ldl, 0, d_U, 1, ldu, 0, W, 1, R, 0};
+            rc = launch_gemm(h, g, 1); if (rc) return rc;
+            scatter_cols_kernel<<<dim3((R + 255) / 256, N), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, 0);
+            TCI_LAUNCH_CHECK(h);
+        } else {                                          // pivotinvtimesrows  matrixluci.jl:227-241
+            const int q = N - R;
+            if (q > 0) {
+                copy_strided_kernel<<<dim3((R + 255) / 256, q), 256, 0, h->stream>>>(d_U + (long long)R * ldu, 1, ldu, W, 1, R, R, q);
+                TCI_LAUNCH_CHECK(h);
+                // U1 X = U2  <=>  X^T U1^T = U2^T : right solve with the lower-triangular view U1^T
+                rc = trsm_right(h, d_U, ldu, 1, R, 1, 1, W, R, 1, q);
+                if (rc) return rc;
+            }
+            scatter_cols_kernel<<<dim3((R + 255) / 256, N), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, R);
+            TCI_LAUNCH_CHECK(h);
+        }
+    }
+    return TCI_OK;
+}
+
+int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb, const double* d_P, int64_t r, int64_t ldp,
+                        double* d_X, int64_t ldx) {
+    if (!h) return TCI_ERR_INVALID;
+    if (q < 0 || r < 0) return tci_fail(h, TCI_ERR_INVALID, "tci_solve_right_f64: bad sizes");
+    if (q == 0 || r == 0) return TCI_OK;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    const int Q = (int)q, R = (int)r;
+    const long long ldw = (R + 1) & ~1;
+    const size_t permbytes = ((sizeof(int) * (size_t)(2 * R)) + 255) & ~(size_t)255;
+    int rc = tci_ws_reserve(h, h->ws_b, permbytes + sizeof(double) * ((size_t)3 * ldw * R + (size_t)Q * R) + 256);
+    if (rc) return rc;
+    int* d_rp = (int*)h->ws_b.ptr; int* d_cp = d_rp + R;
+    double* Pw = (double*)((char*)h->ws_b.ptr + permbytes);
+    double* Lw = Pw + (size_t)ldw * R; double* Uw = Lw + (size_t)ldw * R; double* W = Uw + (size_t)ldw * R;
+    copy_strided_kernel<<<dim3((R + 255) / 256, R), 256, 0, h->stream>>>(d_P, 1, ldp, Pw, 1, ldw, R, R);
+    TCI_LAUNCH_CHECK(h);
+    std::vector<int64_t> rp(R), cp(R);
+    int64_t npiv = 0; double err = 0.0;
+    rc = tci_rrlu_inplace_f64(h, Pw, R, R, ldw, R, 0.0, 0.0, 1, rp.data(), cp.data(), &npiv, &err, Lw, ldw, Uw, ldw, nullptr);
+    if (rc) return rc;
+    if (npiv != R) return tci_fail(h, TCI_ERR_INVALID, "tci_solve_right_f64: pivot matrix is singular (rank %lld of %d)", (long long)npiv, R);
+    rc = tci_pinned_reserve(h, permbytes + 64); if (rc) return rc;
+    rc = upload_perm(h, rp.data(), R, d_rp, 0); if (rc) return rc;
+    rc = upload_perm(h, cp.data(), R, d_cp, sizeof(int) * (size_t)R); if (rc) return rc;
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    gather_cols_kernel<<<dim3((Q + 255) / 256, R), 256, 0, h->stream>>>(W, Q, d_B, ldb, d_cp, Q, R);
+    TCI_LAUNCH_CHECK(h);
+    rc = trsm_right(h, Uw, 1, ldw, R, 0, 0, W, 1, Q, Q); if (rc) return rc;      // W <- W U^-1
+    rc = trsm_right(h, Lw, 1, ldw, R, 1, 1, W, 1, Q, Q); if (rc) return rc;      // W <- W L^-1
+    scatter_cols_kernel<<<dim3((Q + 255) / 256, R), 256, 0, h->stream>>>(d_X, ldx, W, Q, d_rp, Q, R, 0);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+} // extern "C"

@@ -105,37 +105,38 @@ def rrlu(A, maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, hand
                 pe[: r + 1].copy())
 
 
-def rrlu_inplace(A, maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None, extract=True):
-    """rrlu!(A; ...) — matrixlu.jl:420-430 on a DEVICE matrix: `A` is a column-major view held in a torch
-    CUDA tensor of shape (n, lda) (i.e. A.T of the logical m x n matrix, lda >= m), overwritten like the
-    reference overwrites A.  Returns an rrLU whose L/U are torch CUDA tensors (logical m x r and r x n,
-    stored transposed so that they are column-major)."""
-    import torch
-    h = handle or _lib.default_handle()
-    n, lda = A.shape
-    m = getattr(A, "_tci_rows", lda)
-    return _rrlu_device(h, A, m, n, lda, maxrank, reltol, abstol, leftorthogonal, extract)
-
-
 def _rrlu_device(h, At, m, n, lda, maxrank, reltol, abstol, leftorthogonal, extract=True):
+    """rrlu! on a device matrix stored in torch tensor `At` of shape (n, lda) (column-major m x n, ld lda)."""
     import torch
+    from .dense import Mat
     assert At.is_cuda and At.dtype == torch.float64 and At.is_contiguous()
     mr = _maxrank(maxrank, m, n)
     rowperm = np.zeros(m, dtype=np.int64)
     colperm = np.zeros(n, dtype=np.int64)
     pe = np.zeros(mr + 1)
     npivot, err = C.c_int64(), C.c_double()
-    Lt = torch.empty((max(mr, 1), max(m, 1)), dtype=torch.float64, device=At.device) if extract else None
-    Ut = torch.empty((max(n, 1), max(mr, 1)), dtype=torch.float64, device=At.device) if extract else None
+    Lm = Mat.empty(m, max(mr, 1), At.device) if extract else None
+    Um = Mat.empty(max(mr, 1), n, At.device) if extract else None
     h.check(lib().tci_rrlu_inplace_f64(h.h, C.c_void_p(At.data_ptr()), C.c_int64(m), C.c_int64(n), C.c_int64(lda),
                                        C.c_int64(mr), C.c_double(reltol), C.c_double(abstol), int(bool(leftorthogonal)),
                                        p_i64(rowperm), p_i64(colperm), C.byref(npivot), C.byref(err),
-                                       C.c_void_p(Lt.data_ptr() if extract else 0), C.c_int64(max(m, 1)),
-                                       C.c_void_p(Ut.data_ptr() if extract else 0), C.c_int64(max(mr, 1)), p_f64(pe)))
+                                       Lm.ptr if extract else None, C.c_int64(Lm.ld if extract else 1),
+                                       Um.ptr if extract else None, C.c_int64(Um.ld if extract else 1), p_f64(pe)))
     r = npivot.value
-    L = Lt[:r, :m].T if extract else None                 # logical m x r view, column-major storage
-    U = Ut[:n, :r].T if extract else None                 # logical r x n view, column-major storage
-    return rrLU(rowperm, colperm, L, U, leftorthogonal, r, err.value, pe[: r + 1].copy())
+    L = U = None
+    if extract:
+        Lm.cols = r
+        Um.rows = r
+        L, U = Lm.view(), Um.view()                       # logical m x r and r x n views (column-major storage)
+    lu = rrLU(rowperm, colperm, L, U, leftorthogonal, r, err.value, pe[: r + 1].copy())
+    lu.Lmat, lu.Umat = Lm, Um
+    return lu
+
+
+def rrlu_device(A, maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None, extract=True):
+    """rrlu!(A; ...) on a `dense.Mat` (device, overwritten)."""
+    h = handle or _lib.default_handle()
+    return _rrlu_device(h, A.buf, A.rows, A.cols, A.ld, maxrank, reltol, abstol, leftorthogonal, extract)
 
 
 def submatrixargmax(A, startindex, handle=None):

@@ -1,0 +1,524 @@
+"""Host-side mirror of src/tensorci2.jl: TensorCI2 state, 1-/2-site sweeps, `optimize!`, `crossinterpolate2`.
+
+This file is bookkeeping only (index sets, sweep order, convergence control) — what the north star keeps in
+the host language.  Every number is produced by the CUDA library: K1 batch evaluation (batcheval.py), K2/K3
+rrLU (matrixlu.py), K4a factors/solves (dense.py), K4b evaluate/sum (tensortrain.py).  Index sets are int32
+tables (count x length), 1-based values like Julia.  Bond/site arguments of public methods are 1-based.
+"""
+import time
+
+import numpy as np
+
+from . import _lib
+from ._lib import TCIError
+from .batcheval import BatchEvaluator, as_table
+from .dense import Mat, solve_right
+from .matrixlu import INT_MAX
+from .matrixluci import MatrixLUCI
+from .tensortrain import AbstractTensorTrain, DeviceCore
+
+
+# ---- index-set helpers (tensorci2.jl:512-529, util.jl:94-98, Base.union) --------------------------------
+def kronecker_left(Iset, d):
+    """[is..., j] for is in Iset (fastest), j in 1:d — tensorci2.jl:512-517."""
+    n = Iset.shape[0]
+    return np.concatenate([np.tile(Iset, (d, 1)), np.repeat(np.arange(1, d + 1, dtype=np.int32), n)[:, None]], axis=1)
+
+
+def kronecker_right(d, Jset):
+    """[i, js...] for i in 1:d (fastest), js in Jset — tensorci2.jl:524-529."""
+    n = Jset.shape[0]
+    return np.concatenate([np.tile(np.arange(1, d + 1, dtype=np.int32), n)[:, None], np.repeat(Jset, d, axis=0)], axis=1)
+
+
+def _keys(tab):
+    return [r.tobytes() for r in np.ascontiguousarray(tab, dtype=np.int32)]
+
+
+def union_rows(a, b):
+    """Base.union on vectors of multi-indices: first-seen order, duplicates dropped."""
+    if b is None or b.shape[0] == 0:
+        seen, keep = set(), []
+        for i, k in enumerate(_keys(a)):
+            if k not in seen:
+                seen.add(k); keep.append(i)
+        return a if len(keep) == a.shape[0] else a[keep]
+    both = np.concatenate([a, b.reshape(-1, a.shape[1])], axis=0)
+    seen, keep = set(), []
+    for i, k in enumerate(_keys(both)):
+        if k not in seen:
+            seen.add(k); keep.append(i)
+    return both[keep]
+
+
+def pushunique(tab, row):
+    row = np.asarray(row, dtype=np.int32).reshape(1, -1)
+    if tab.shape[0] and any(k == row.tobytes() for k in _keys(tab)):
+        return tab
+    return np.concatenate([tab, row], axis=0)
+
+
+def _jl_max(a, b):
+    if np.isnan(a) or np.isnan(b):
+        return float("nan")
+    return a if a > b else b
+
+
+def forwardsweep(sweepstrategy, iteration):                # sweepstrategies.jl:41-50
+    return sweepstrategy == "forward" or (sweepstrategy == "backandforth" and iteration % 2 == 1)
+
+
+class HostFunctionAdapter(BatchEvaluator):
+    """BatchEvaluatorAdapter (batcheval.jl:32-107) for an arbitrary Python callable f(indexset): the USER's function
+    runs where the user wrote it (the host); the values are uploaded and everything downstream runs on the GPU."""
+
+    def __init__(self, f, localdims, handle=None):
+        super().__init__(localdims, handle)
+        self.f = f
+
+    def evaluate_batch(self, left, right, M, out=None, stride_c=0, stride_j=0, maxabs=None):
+        import itertools
+        import torch
+        lt, rt = as_table(left), as_table(right)
+        nleft, nright = lt.shape[0], rt.shape[0]
+        dev = f"cuda:{self.handle.device}"
+        if nleft * nright == 0:
+            return torch.zeros((0,) * (M + 2), dtype=torch.float64, device=dev), maxabs
+        nl = lt.shape[1]
+        cd = [int(d) for d in self.localdims[nl:nl + M]]
+        ncent = int(np.prod(cd)) if cd else 1
+        vals = np.empty((nright, ncent, nleft))
+        cents = list(itertools.product(*[range(1, d + 1) for d in reversed(cd)]))
+        for j in range(nright):
+            for c, cidx in enumerate(cents):
+                mid = list(reversed(cidx))
+                for i in range(nleft):
+                    vals[j, c, i] = self.f(list(lt[i]) + mid + list(rt[j]))
+        sc = stride_c if stride_c > 0 else nleft
+        sj = stride_j if stride_j > 0 else sc * ncent
+        if out is None:
+            out = torch.empty((nright,) + tuple(reversed(cd)) + (nleft,), dtype=torch.float64, device=dev)
+        flat = out.reshape(-1)
+        host = torch.from_numpy(vals)
+        view = torch.as_strided(flat, (nright, ncent, nleft), (sj, sc, 1))
+        view.copy_(host)
+        if maxabs is not None:
+            m = float(np.max(np.abs(vals))) if not np.isnan(vals).any() else float("nan")
+            maxabs = _jl_max(abs(maxabs), m)
+        return out, maxabs
+
+    def __call__(self, *args):
+        if len(args) == 1:
+            return float(self.f([int(v) for v in args[0]]))
+        return super().__call__(*args)
+
+
+def makebatchevaluatable(f, localdims, handle=None):       # batcheval.jl:57
+    return f if isinstance(f, BatchEvaluator) else HostFunctionAdapter(f, localdims, handle)
+
+
+class TensorCI2(AbstractTensorTrain):
+    """mutable struct TensorCI2{Float64} (tensorci2.jl:50-93)."""
+
+    def __init__(self, localdims, f=None, initialpivots=None, Iset=None, Jset=None, handle=None):
+        localdims = [int(d) for d in localdims]
+        if len(localdims) <= 1:
+            raise TCIError(_lib.TCI_ERR_INVALID, "localdims should have at least 2 elements!")
+        self.handle = handle or getattr(f, "handle", None) or _lib.default_handle()
+        self.device = f"cuda:{self.handle.device}"
+        n = len(localdims)
+        self.localdims = localdims
+        self.Iset = [np.zeros((0, b), dtype=np.int32) for b in range(n)]
+        self.Jset = [np.zeros((0, n - b - 1), dtype=np.int32) for b in range(n)]
+        self._T = [None] * n                                # device cores; None = invalidated
+        self.pivoterrors = np.zeros(0)
+        self.bonderrors = np.zeros(n - 1)
+        self.maxsamplevalue = 0.0
+        self.Iset_history, self.Jset_history = [], []
+        self.stats = {"nevals": 0, "t_eval": 0.0, "t_lu": 0.0, "t_factors": 0.0, "t_host": 0.0}
+        if f is not None and Iset is not None:              # tensorci2.jl:123-137
+            self.Iset = [as_table(s, b) for b, s in enumerate(Iset)]
+            self.Jset = [as_table(s, n - b - 1) for b, s in enumerate(Jset)]
+            piv = reconstractglobalpivotsfromijset(localdims, self.Iset, self.Jset)
+            self._init_maxsample(f, piv)
+        elif f is not None:                                 # tensorci2.jl:105-116
+            if initialpivots is None:
+                initialpivots = [[1] * n]
+            self.addglobalpivots(initialpivots)
+            self._init_maxsample(f, initialpivots)
+
+    def _init_maxsample(self, f, pivots):
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        m = -np.inf
+        for p in pivots:
+            m = _jl_max(m, abs(f([int(v) for v in p])))
+        self.maxsamplevalue = m
+        if not abs(self.maxsamplevalue) > 0.0:
+            raise TCIError(_lib.TCI_ERR_INVALID, "maxsamplevalue is zero!")
+        self.invalidatesitetensors()
+
+    # ---- AbstractTensorTrain plumbing
+    def _dev_cores(self):
+        if not self.issitetensorsavailable():
+            raise TCIError(_lib.TCI_ERR_INVALID, "site tensors are not available (call fillsitetensors! or a sweep first)")
+        return self._T
+
+    def __len__(self):
+        return len(self.localdims)
+
+    @property
+    def sitetensors(self):
+        n = len(self)
+        return [self._T[b].numpy() if self._T[b] is not None else np.zeros((0, self.localdims[b], 0)) for b in range(n)]
+
+    def linkdims(self):                                     # tensorci2.jl:189-191
+        return [self.Iset[b + 1].shape[0] for b in range(len(self) - 1)]
+
+    def rank(self):
+        return max(self.linkdims())
+
+    def invalidatesitetensors(self):                        # tensorci2.jl:206-211
+        self._T = [None] * len(self)
+
+    def issitetensorsavailable(self):                       # tensorci2.jl:218-220
+        return all(t is not None and t.chil * t.chir != 0 for t in self._T)
+
+    # ---- errors (tensorci2.jl:231-289)
+    def updateerrors(self, b0, errors):
+        self.bonderrors[b0] = errors[-1]
+        k = max(len(self.pivoterrors), len(errors))
+        a = np.zeros(k); a[: len(self.pivoterrors)] = self.pivoterrors
+        e = np.zeros(k); e[: len(errors)] = errors
+        self.pivoterrors = np.array([_jl_max(x, y) for x, y in zip(a, e)])
+
+    def flushpivoterror(self):
+        self.pivoterrors = np.zeros(0)
+
+    def pivoterror(self):                                   # tensorci2.jl:277-279, :243-245
+        m = -np.inf
+        for x in self.bonderrors:
+            m = _jl_max(m, x)
+        return m
+
+    # ---- pivots
+    def addglobalpivots(self, pivots):                      # tensorci2.jl:335-357
+        n = len(self)
+        pivots = [[int(v) for v in p] for p in pivots]
+        if any(len(p) != n for p in pivots):
+            raise TCIError(_lib.TCI_ERR_INVALID, "Please specify a pivot as one index per leg of the MPS.")
+        for p in pivots:
+            for b in range(n):
+                self.Iset[b] = pushunique(self.Iset[b], p[:b])
+                self.Jset[b] = pushunique(self.Jset[b], p[b + 1:])
+        if pivots:
+            self.invalidatesitetensors()
+
+    # ---- K1 call sites -----------------------------------------------------------------------------------
+    def _fill(self, f, I, J, M, rows, cols):
+        """filltensor (tensorci2.jl:475-497) + updatemaxsample! (:636-638) into a device matrix rows x cols
+        (column-major reshape of the (|I|, d..., |J|) array, exactly the reference's `reshape`)."""
+        t0 = time.perf_counter()
+        P = Mat.empty(rows, cols, self.device, pad=16)
+        nI, nJ = I.shape[0], J.shape[0]
+        if nI * nJ:
+            if M == 0:
+                sc, sj = nI, P.ld
+            elif rows == nI:                                # rows = I, cols = (c, J)
+                sc, sj = P.ld, P.ld * (cols // nJ)
+            else:                                           # rows = (I, c), cols = J
+                sc, sj = nI, P.ld
+            _, self.maxsamplevalue = f.evaluate_batch(I, J, M, out=P.buf, stride_c=sc, stride_j=sj,
+                                                      maxabs=self.maxsamplevalue)
+            self.stats["nevals"] += rows * cols
+        self.stats["t_eval"] += time.perf_counter() - t0
+        return P
+
+    def _set_core(self, b0, mat):
+        """setsitetensor!(tci, b, T) (tensorci2.jl:536-545): reshape to (|Iset[b]|, d_b, |Jset[b]|)."""
+        chil, d, chir = self.Iset[b0].shape[0], self.localdims[b0], self.Jset[b0].shape[0]
+        if mat.rows * mat.cols != chil * d * chir:
+            raise TCIError(_lib.TCI_ERR_INVALID, "setsitetensor!: size mismatch")
+        if mat.rows != chil * d:                            # r x (d*chi) matrix: same memory, other 2-D view
+            if mat.ld != mat.rows:
+                mat = Mat.from_numpy(mat.numpy().reshape(chil * d, chir, order="F"), self.device)
+            else:
+                mat = Mat(mat.buf.reshape(-1)[: chil * d * chir].reshape(chir, chil * d), chil * d, chir)
+        self._T[b0] = DeviceCore(mat, chil, (d,), chir)
+
+    def updatepivots(self, b, f, leftorthogonal, reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX, sweepdirection="forward",
+                     pivotsearch="full", verbosity=0, extraIset=None, extraJset=None):
+        """updatepivots! (tensorci2.jl:825-930), pivotsearch=:full."""
+        if pivotsearch != "full":
+            if pivotsearch == "rook":
+                raise TCIError(_lib.TCI_ERR_INVALID, "pivotsearch=:rook is not implemented in this build (SURVEY.md 8f)")
+            raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown pivot search strategy {pivotsearch}. Choose from :rook, :full.")
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        b0 = b - 1
+        self.invalidatesitetensors()
+        th = time.perf_counter()
+        noextra = (extraIset is None or len(extraIset) == 0) and (extraJset is None or len(extraJset) == 0)
+        Ic = union_rows(kronecker_left(self.Iset[b0], self.localdims[b0]), None if extraIset is None else as_table(extraIset, b0 + 1))
+        Jc = union_rows(kronecker_right(self.localdims[b0 + 1], self.Jset[b0 + 1]),
+                        None if extraJset is None else as_table(extraJset, len(self) - b0 - 1))
+        self.stats["t_host"] += time.perf_counter() - th
+        Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0])
+        t0 = time.perf_counter()
+        luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=leftorthogonal,
+                          handle=self.handle)
+        self.stats["t_lu"] += time.perf_counter() - t0
+        if verbosity > 2:
+            print(f"    Computing Pi ({Ic.shape[0]} x {Jc.shape[0]}) at bond {b}: LU: {time.perf_counter() - t0} sec")
+        self.Iset[b0 + 1] = Ic[luci.rowindices() - 1]
+        self.Jset[b0] = Jc[luci.colindices() - 1]
+        if noextra:
+            t0 = time.perf_counter()
+            self._set_core(b0, luci.left_mat())
+            self._set_core(b0 + 1, luci.right_mat())
+            self.stats["t_factors"] += time.perf_counter() - t0
+        self.updateerrors(b0, luci.pivoterrors())
+        self.last_luci = luci
+
+    def setsitetensor(self, f, b, leftorthogonal=True):
+        """setsitetensor!(tci, f, b) (tensorci2.jl:599-629)."""
+        if not leftorthogonal:
+            raise TCIError(_lib.TCI_ERR_INVALID, "leftorthogonal==false is not supported!")
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        b0 = b - 1
+        nI, nJ, d = self.Iset[b0].shape[0], self.Jset[b0].shape[0], self.localdims[b0]
+        Pi1 = self._fill(f, self.Iset[b0], self.Jset[b0], 1, nI * d, nJ)
+        if b0 == len(self) - 1:
+            self._set_core(b0, Pi1)
+            return
+        nI1 = self.Iset[b0 + 1].shape[0]
+        P = self._fill(f, self.Iset[b0 + 1], self.Jset[b0], 0, nI1, nJ)
+        if nI1 != nJ:
+            raise TCIError(_lib.TCI_ERR_NOT_SQUARE, f"Pivot matrix at bond {b} is not square!")
+        t0 = time.perf_counter()
+        T = solve_right(self.handle, Pi1, P)
+        self.stats["t_factors"] += time.perf_counter() - t0
+        self._T[b0] = DeviceCore(T, nI, (d,), nI1)
+
+    def fillsitetensors(self, f):                           # globalsearch.jl:202-208
+        for b in range(1, len(self) + 1):
+            self.setsitetensor(f, b)
+
+    def sweep1site(self, f, sweepdirection="forward", reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX, updatetensors=True):
+        """sweep1site! (tensorci2.jl:659-725)."""
+        import torch
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        self.flushpivoterror()
+        self.invalidatesitetensors()
+        if sweepdirection not in ("forward", "backward"):
+            raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown sweep direction {sweepdirection}: choose between :forward, :backward.")
+        fwd = sweepdirection == "forward"
+        n = len(self)
+        for b0 in (range(0, n - 1) if fwd else range(n - 1, 0, -1)):
+            d = self.localdims[b0]
+            Is = kronecker_left(self.Iset[b0], d) if fwd else self.Iset[b0]
+            Js = self.Jset[b0] if fwd else kronecker_right(d, self.Jset[b0])
+            Pi = self._fill(f, self.Iset[b0], self.Jset[b0], 1, Is.shape[0], Js.shape[0])
+            t0 = time.perf_counter()
+            luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=fwd, handle=self.handle)
+            self.stats["t_lu"] += time.perf_counter() - t0
+            if fwd:
+                self.Iset[b0 + 1] = Is[luci.rowindices() - 1]
+                self.Jset[b0] = Js[luci.colindices() - 1]
+            else:
+                self.Iset[b0] = Is[luci.rowindices() - 1]
+                self.Jset[b0 - 1] = Js[luci.colindices() - 1]
+            if updatetensors:
+                t0 = time.perf_counter()
+                self._set_core(b0, luci.left_mat() if fwd else luci.right_mat())
+                if bool(torch.isnan(self._T[b0].mat.view()).any()):
+                    raise TCIError(_lib.TCI_ERR_NAN_TENSOR, f"Error: NaN in tensor T[{b0 + 1}]")
+                self.stats["t_factors"] += time.perf_counter() - t0
+            self.updateerrors(b0 if fwd else b0 - 1, luci.pivoterrors())
+        if updatetensors:
+            last = n - 1 if fwd else 0
+            rows = self.Iset[last].shape[0] if fwd else self.localdims[0]
+            cols = self.localdims[last] if fwd else self.Jset[0].shape[0]
+            self._set_core(last, self._fill(f, self.Iset[last], self.Jset[last], 1, rows, cols))
+
+    def makecanonical(self, f, reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX):      # tensorci2.jl:738-749
+        self.sweep1site(f, "forward", reltol=0.0, abstol=0.0, maxbonddim=INT_MAX, updatetensors=False)
+        self.sweep1site(f, "backward", reltol=reltol, abstol=abstol, maxbonddim=maxbonddim, updatetensors=False)
+        self.sweep1site(f, "forward", reltol=reltol, abstol=abstol, maxbonddim=maxbonddim, updatetensors=True)
+
+    def addglobalpivots1sitesweep(self, f, pivots, reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX):   # :367-377
+        self.addglobalpivots(pivots)
+        self.makecanonical(f, reltol=reltol, abstol=abstol, maxbonddim=maxbonddim)
+
+    def sweep2site(self, f, niter, iter1=1, abstol=1e-8, maxbonddim=INT_MAX, sweepstrategy="backandforth",
+                   pivotsearch="full", verbosity=0, strictlynested=False, fillsitetensors=True):
+        """sweep2site! (tensorci2.jl:1195-1258)."""
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        self.invalidatesitetensors()
+        n = len(self)
+        for it in range(iter1, iter1 + niter):
+            extraI = [None] * n
+            extraJ = [None] * n
+            if not strictlynested and self.Iset_history:
+                extraI, extraJ = self.Iset_history[-1], self.Jset_history[-1]
+            self.Iset_history.append([s.copy() for s in self.Iset])
+            self.Jset_history.append([s.copy() for s in self.Jset])
+            self.flushpivoterror()
+            fwd = forwardsweep(sweepstrategy, it)
+            for b in (range(1, n) if fwd else range(n - 1, 0, -1)):
+                self.updatepivots(b, f, fwd, abstol=abstol, maxbonddim=maxbonddim,
+                                  sweepdirection="forward" if fwd else "backward", pivotsearch=pivotsearch,
+                                  verbosity=verbosity, extraIset=extraI[b], extraJset=extraJ[b - 1])
+        if fillsitetensors:
+            self.fillsitetensors(f)
+
+
+def reconstractglobalpivotsfromijset(localdims, Isets, Jsets):     # tensorci2.jl:303-320
+    piv, seen = [], set()
+    for i in range(len(Isets)):
+        for I in Isets[i]:
+            for J in Jsets[i]:
+                for j in range(1, localdims[i] + 1):
+                    p = tuple(int(v) for v in I) + (j,) + tuple(int(v) for v in J)
+                    if p not in seen:
+                        seen.add(p); piv.append(list(p))
+    return piv
+
+
+def convergencecriterion(ranks, errors, nglobalpivots, tolerance, maxbonddim, ncheckhistory, checkconvglobalpivot=True):
+    """tensorci2.jl:947-966."""
+    if len(errors) < ncheckhistory:
+        return False
+    lastranks = list(ranks)[-ncheckhistory:]
+    lastng = list(nglobalpivots)[-ncheckhistory:]
+    return ((all(e < tolerance for e in list(errors)[-ncheckhistory:])
+             and (all(g == 0 for g in lastng) if checkconvglobalpivot else True)
+             and min(lastranks) == lastranks[-1])
+            or all(r >= maxbonddim for r in lastranks))
+
+
+class GlobalPivotSearchInput:
+    """globalpivotfinder.jl:33-68."""
+
+    def __init__(self, tci):
+        from .tensortrain import TensorTrain
+        self.localdims = list(tci.localdims)
+        self.current_tt = TensorTrain(tci)
+        self.maxsamplevalue = tci.maxsamplevalue
+        self.Iset, self.Jset = tci.Iset, tci.Jset
+
+
+class DefaultGlobalPivotFinder:
+    """DefaultGlobalPivotFinder (globalpivotfinder.jl:145-265): random starts, one greedy line search per site on
+    |f - tt|.  The host keeps the RNG and the greedy control flow; all the |f - tt| values of one start
+    (sum_p d_p points) are evaluated in ONE K1 batch and ONE K4b batch instead of point by point.
+    (numpy's RNG replaces Julia's Xoshiro: global pivots are not comparable with a Julia run — SURVEY.md 7.)"""
+
+    def __init__(self, nsearch=5, maxnglobalpivot=5, tolmarginglobalsearch=10.0):
+        self.nsearch, self.maxnglobalpivot, self.tolmarginglobalsearch = nsearch, maxnglobalpivot, tolmarginglobalsearch
+
+    def __call__(self, input, f, abstol, verbosity=0, rng=None):
+        rng = rng or np.random.default_rng()
+        L = len(input.localdims)
+        found = []
+        if self.nsearch <= 0:
+            return found
+        starts = [[int(rng.integers(1, input.localdims[p] + 1)) for p in range(L)] for _ in range(self.nsearch)]
+        pts = []
+        for point in starts:                                # globalpivotfinder.jl:223-246: vary one site at a time
+            for p in range(L):
+                for v in range(1, input.localdims[p] + 1):
+                    q = list(point); q[p] = v
+                    pts.append(q)
+        pts = np.asarray(pts, dtype=np.int32)
+        fv = np.array([f(list(q)) for q in pts]) if not isinstance(f, BatchEvaluator) else _point_values(f, pts)
+        tv = input.current_tt.evaluate_batch(pts)
+        err = np.abs(fv - tv)
+        per = sum(input.localdims)
+        for s, point in enumerate(starts):
+            e = err[s * per:(s + 1) * per]
+            best_error, best_point = 0.0, list(point)
+            for k in range(per):                            # strict '>' keeps the first maximum, as the reference loop does
+                if e[k] > best_error:
+                    best_error, best_point = float(e[k]), [int(v) for v in pts[s * per + k]]
+            if best_error > abstol * self.tolmarginglobalsearch:
+                found.append(best_point)
+        if len(found) > self.maxnglobalpivot:
+            found = found[: self.maxnglobalpivot]
+        if verbosity > 0:
+            print(f"Found {len(found)} global pivots")
+        return found
+
+
+def _point_values(f, pts):
+    """f at arbitrary points in ONE K1 call: the points are the left set (length N), the right set is the single
+    empty multi-index."""
+    t, _ = f.evaluate_batch(np.ascontiguousarray(pts, dtype=np.int32), np.zeros((1, 0), dtype=np.int32), 0)
+    return t.reshape(-1).cpu().numpy()
+
+
+def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, maxiter=20, sweepstrategy="backandforth",
+             pivotsearch="full", verbosity=0, loginterval=10, normalizeerror=True, ncheckhistory=3, globalpivotfinder=None,
+             maxnglobalpivot=5, nsearchglobalpivot=5, tolmarginglobalsearch=10.0, strictlynested=False,
+             checkbatchevaluatable=False, checkconvglobalpivot=True, rng=None):
+    """optimize! (tensorci2.jl:1018-1172).  Returns (ranks, errors ./ errornormalization)."""
+    import warnings
+    errors, ranks, nglobalpivots = [], [], []
+    if checkbatchevaluatable and not isinstance(f, BatchEvaluator):
+        raise TCIError(_lib.TCI_ERR_INVALID, "Function `f` is not batch evaluatable")
+    if 0 < nsearchglobalpivot < maxnglobalpivot:
+        raise TCIError(_lib.TCI_ERR_INVALID, "nsearchglobalpivot < maxnglobalpivot!")
+    if pivottolerance is not None:
+        if tolerance is not None and tolerance != pivottolerance:
+            raise TCIError(_lib.TCI_ERR_INVALID, "Got different values for pivottolerance and tolerance in optimize!(TCI2). "
+                           "For TCI2, both of these options have the same meaning. Please assign only `tolerance`.")
+        warnings.warn("The option `pivottolerance` of `optimize!(tci::TensorCI2, f)` is deprecated. Please update your code "
+                      "to use `tolerance`, as `pivottolerance` will be removed in the future.", DeprecationWarning)
+        tol = pivottolerance
+    elif tolerance is not None:
+        tol = tolerance
+    else:
+        tol = 1e-8
+    if maxbonddim >= INT_MAX and tol <= 0:
+        raise TCIError(_lib.TCI_ERR_INVALID, "Specify either tolerance > 0 or some maxbonddim; otherwise, the convergence "
+                       "criterion is not reachable!")
+    f = makebatchevaluatable(f, tci.localdims, tci.handle)
+    finder = globalpivotfinder or DefaultGlobalPivotFinder(nsearch=nsearchglobalpivot, maxnglobalpivot=maxnglobalpivot,
+                                                           tolmarginglobalsearch=tolmarginglobalsearch)
+    tstart = time.perf_counter()
+    for it in range(1, maxiter + 1):
+        errornormalization = tci.maxsamplevalue if normalizeerror else 1.0
+        abstol = tol * errornormalization
+        if verbosity > 1:
+            print(f"  Walltime {time.perf_counter() - tstart} sec: starting 2site sweep")
+        tci.sweep2site(f, 2, iter1=1, abstol=abstol, maxbonddim=maxbonddim, pivotsearch=pivotsearch,
+                       strictlynested=strictlynested, verbosity=verbosity, sweepstrategy=sweepstrategy, fillsitetensors=True)
+        errors.append(tci.pivoterror())
+        globalpivots = finder(GlobalPivotSearchInput(tci), f, abstol, verbosity=verbosity, rng=rng) \
+            if getattr(finder, "nsearch", 1) != 0 else []
+        tci.addglobalpivots(globalpivots)
+        nglobalpivots.append(len(globalpivots))
+        ranks.append(tci.rank())
+        if verbosity > 0 and it % loginterval == 0:
+            print(f"iteration = {it}, rank = {ranks[-1]}, error= {errors[-1]}, maxsamplevalue= {tci.maxsamplevalue}, "
+                  f"nglobalpivot={len(globalpivots)}")
+        if convergencecriterion(ranks, errors, nglobalpivots, abstol, maxbonddim, ncheckhistory,
+                                checkconvglobalpivot=checkconvglobalpivot):
+            break
+    errornormalization = tci.maxsamplevalue if normalizeerror else 1.0
+    abstol = tol * errornormalization
+    tci.sweep1site(f, abstol=abstol, maxbonddim=maxbonddim)
+    _sanitycheck(tci)
+    return np.asarray(ranks, dtype=np.int64), np.asarray(errors) / errornormalization
+
+
+def _sanitycheck(tci):                                      # globalsearch.jl:226-233
+    for b in range(len(tci) - 1):
+        if tci.Iset[b + 1].shape[0] != tci.Jset[b].shape[0]:
+            raise TCIError(_lib.TCI_ERR_NOT_SQUARE, f"Pivot matrix at bond {b + 1} is not square!")
+    return True
+
+
+def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
+    """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323."""
+    tci = TensorCI2(localdims, f, initialpivots, handle=kwargs.pop("handle", None))
+    ranks, errors = optimize(tci, f, **kwargs)
+    return tci, ranks, errors
