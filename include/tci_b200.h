@@ -43,8 +43,11 @@ int tci_create(tci_handle* out, int device);
 int tci_destroy(tci_handle h);
 const char* tci_last_error(tci_handle h);               /* h may be NULL: last tci_create failure */
 const char* tci_version(void);
-/* Run on a caller-owned cudaStream_t (e.g. torch's current stream); NULL = the handle's own stream. */
+/* Run on a caller-owned cudaStream_t (e.g. torch's current stream; NULL = CUDA's legacy default stream), so the
+ * caller's own copies/kernels on that stream are ordered with this library's.  tci_reset_stream returns to the
+ * handle's private non-blocking stream (the default after tci_create). */
 int tci_set_stream(tci_handle h, void* cuda_stream);
+int tci_reset_stream(tci_handle h);
 int tci_synchronize(tci_handle h);
 /* Number of kernels this library has launched on the handle since creation (bench.py's gpu_launches). */
 int64_t tci_launch_count(tci_handle h);

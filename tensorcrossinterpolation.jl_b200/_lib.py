@@ -65,6 +65,8 @@ class Handle:
         if rc != TCI_OK:
             raise TCIError(rc, lib().tci_last_error(None).decode())
         self.device = int(device)
+        # torch owns the device buffers, so run on torch's current stream: its copies and our kernels stay ordered
+        self.use_torch_stream()
 
     @property
     def h(self):

@@ -18,7 +18,6 @@
 //     so the rrLU kernels can use 128-bit accesses on the same buffer.
 //   * max|value| (and a NaN flag, Julia's max propagates NaN) is reduced in the same pass.
 #include "context.h"
-#include <cuda.h>
 #include <nvrtc.h>
 #include <cmath>
 #include <cstring>
@@ -34,8 +33,8 @@ struct tci_functor_s {
     long long* d_strides = nullptr;
     int ndims = 0;
     double* d_params = nullptr;          // F_USER
-    CUmodule mod = nullptr;
-    CUfunction fn = nullptr;
+    cudaLibrary_t mod = nullptr;         // NVRTC cubin loaded through the runtime API (no libcuda link dependency)
+    cudaKernel_t fn = nullptr;
 };
 
 namespace {
@@ -236,9 +235,9 @@ int run_user(tci_handle h, tci_functor f, const EvalShape& sh, const EvalBuffers
     long long total = nleft * ncent * nright;
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)h->num_sms * 8) blocks = (long long)h->num_sms * 8;
-    CUresult r = cuLaunchKernel(f->fn, (unsigned)blocks, 1, 1, 256, 1, 1, 0, (CUstream)h->stream, args, nullptr);
+    cudaError_t r = cudaLaunchKernel((const void*)f->fn, dim3((unsigned)blocks), dim3(256), args, 0, h->stream);
     h->launches++;
-    if (r != CUDA_SUCCESS) { const char* s = nullptr; cuGetErrorString(r, &s); return tci_fail(h, TCI_ERR_CUDA, "cuLaunchKernel(user functor): %s", s ? s : "?"); }
+    if (r != cudaSuccess) return tci_fail(h, TCI_ERR_CUDA, "cudaLaunchKernel(user functor): %s", cudaGetErrorString(r));
     return TCI_OK;
 }
 
@@ -296,10 +295,10 @@ int tci_functor_from_source(tci_handle h, const char* cuda_src, const double* h_
     nvrtcDestroyProgram(&prog);
     tci_functor f = new tci_functor_s();
     f->kind = TCI_F_USER; f->nparams = nparams;
-    CUresult r = cuModuleLoadData(&f->mod, cubin.data());
-    if (r == CUDA_SUCCESS) r = cuModuleGetFunction(&f->fn, f->mod, "tci_user_assemble");
-    if (r != CUDA_SUCCESS) { const char* s = nullptr; cuGetErrorString(r, &s); delete f; return tci_fail(h, TCI_ERR_CUDA, "loading user functor: %s", s ? s : "?"); }
-    if (cudaMalloc(&f->d_params, sizeof(double) * (nparams > 0 ? nparams : 1)) != cudaSuccess) { cuModuleUnload(f->mod); delete f; return tci_fail(h, TCI_ERR_NOMEM, "cudaMalloc failed"); }
+    cudaError_t r = cudaLibraryLoadData(&f->mod, cubin.data(), nullptr, nullptr, 0, nullptr, nullptr, 0);
+    if (r == cudaSuccess) r = cudaLibraryGetKernel(&f->fn, f->mod, "tci_user_assemble");
+    if (r != cudaSuccess) { delete f; return tci_fail(h, TCI_ERR_CUDA, "loading user functor: %s", cudaGetErrorString(r)); }
+    if (cudaMalloc(&f->d_params, sizeof(double) * (nparams > 0 ? nparams : 1)) != cudaSuccess) { cudaLibraryUnload(f->mod); delete f; return tci_fail(h, TCI_ERR_NOMEM, "cudaMalloc failed"); }
     if (nparams > 0) TCI_CUDA(h, cudaMemcpy(f->d_params, h_params, sizeof(double) * nparams, cudaMemcpyHostToDevice));
     *out = f;
     return TCI_OK;
@@ -311,7 +310,7 @@ int tci_functor_destroy(tci_handle h, tci_functor f) {
     if (f->d_table) cudaFree(f->d_table);
     if (f->d_strides) cudaFree(f->d_strides);
     if (f->d_params) cudaFree(f->d_params);
-    if (f->mod) cuModuleUnload(f->mod);
+    if (f->mod) cudaLibraryUnload(f->mod);
     delete f;
     return TCI_OK;
 }

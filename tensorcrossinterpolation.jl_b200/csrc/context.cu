@@ -78,7 +78,12 @@ const char* tci_last_error(tci_handle h) { return h ? h->err.c_str() : g_create_
 
 int tci_set_stream(tci_handle h, void* s) {
     if (!h) return TCI_ERR_INVALID;
-    h->stream = s ? (cudaStream_t)s : h->own_stream;
+    h->stream = (cudaStream_t)s;                          // NULL is CUDA's legacy default stream
+    return TCI_OK;
+}
+int tci_reset_stream(tci_handle h) {
+    if (!h) return TCI_ERR_INVALID;
+    h->stream = h->own_stream;
     return TCI_OK;
 }
 int tci_synchronize(tci_handle h) {

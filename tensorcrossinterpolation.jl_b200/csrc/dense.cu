@@ -289,7 +289,7 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
             if (q > 0) {
                 copy_strided_kernel<<<dim3((q + 255) / 256, R), 256, 0, h->stream>>>(d_L + R, 1, ldl, W, 1, q, q, R);
                 TCI_LAUNCH_CHECK(h);
-                rc = trsm_right(h, d_L, 1, ldl, R, 1, 1, W, 1, q, q);
+                rc = trsm_right(h, d_L, 1, ldl, R, 1, 0, W, 1, q, q);   // diagonal read from L (1.0 where the LU is left-orthogonal)
                 if (rc) return rc;
             }
             scatter_rows_kernel<<<dim3((M + 255) / 256, R), 256, 0, h->stream>>>(d_left, ldleft, W, q > 0 ? q : 1, d_rp, M, R, R);
@@ -313,7 +313,7 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
                 copy_strided_kernel<<<dim3((R + 255) / 256, q), 256, 0, h->stream>>>(d_U + (long long)R * ldu, 1, ldu, W, 1, R, R, q);
                 TCI_LAUNCH_CHECK(h);
                 // U1 X = U2  <=>  X^T U1^T = U2^T : right solve with the lower-triangular view U1^T
-                rc = trsm_right(h, d_U, ldu, 1, R, 1, 1, W, R, 1, q);
+                rc = trsm_right(h, d_U, ldu, 1, R, 1, 0, W, R, 1, q);
                 if (rc) return rc;
             }
             scatter_cols_kernel<<<dim3((R + 255) / 256, N), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, R);

@@ -33,11 +33,11 @@ def test_reference_batcheval_cases(tci):                # test/test_batcheval.jl
     res = f(left, right, 2)
     assert res.shape == (100, 2, 2, 100)
     np.testing.assert_array_equal(res, O.batchevaluate(g, ld, left, right, 2))
-    f3 = tci.SumFunction([3, 3, 3, 3])
+    f3 = tci.SumFunction([3, 3, 3])
     assert f3([[1], [2]], [[1], [2]], 1).shape == (2, 3, 2)
     assert f3([], [[1]], 2).shape == (0, 0, 0, 0)       # batcheval.jl:140-142
-    with pytest.raises(tci.TCIError, match="Invalid number of central indices"):
-        f3([[1]], [[1]], 1)
+    with pytest.raises(tci.TCIError, match="Invalid number of central indices"):   # tensorci2.jl:492
+        f3([[1]], [[1]], 2)
 
 
 @pytest.mark.parametrize("M", [0, 1, 2])
