@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "_ref", "libtci_oracle.so")
+_SO = os.path.join(_HERE, "_build", "libtci_oracle.so")
 
 F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE = range(7)
 INT64_MAX = np.iinfo(np.int64).max
