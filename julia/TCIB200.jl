@@ -1,0 +1,237 @@
+# TCIB200.jl — reference-side binding of libtci_b200.so (include/tci_b200.h).
+#
+# This is the shim a maintainer of TensorCrossInterpolation.jl adds to route the TensorCI2 two-site-sweep hot path
+# through the B200 library.  It overloads the reference's own extension points and nothing else:
+#   B1  (f::BatchEvaluator{Float64})(leftindexset, rightindexset, Val(M))   src/batcheval.jl:196-214, docs/src/index.md:181-237
+#   B2  rrlu / rrlu! / MatrixLUCI on a device-resident Pi matrix            src/matrixlu.jl:420-463, src/matrixluci.jl:55
+#   B3  left/right(::MatrixLUCI), the solve of setsitetensor!, sum, evaluate src/matrixluci.jl:256-283, src/tensorci2.jl:626,
+#                                                                           src/abstracttensortrain.jl:328-441
+# Sweep strategy, index-set bookkeeping and convergence control stay in the unmodified Julia package.
+#
+# NOT TESTED in this repository: the build image and the GPU box have no Julia (see DESIGN.md §1).  The same C ABI is
+# exercised from Python (tensorcrossinterpolation.jl_b200/_lib.py), which mirrors this file call for call.
+module TCIB200
+
+import TensorCrossInterpolation as TCI
+import TensorCrossInterpolation: MultiIndex, BatchEvaluator, rrLU
+
+const LIB = get(ENV, "TCI_B200_LIB", "libtci_b200.so")
+
+# ---- status codes -> the reference's exceptions (include/tci_b200.h: tci_status) ---------------------------------------
+const TCI_OK = Cint(0)
+function check(h::Ptr{Cvoid}, rc::Cint)
+    rc == TCI_OK && return nothing
+    msg = unsafe_string(ccall((:tci_last_error, LIB), Cstring, (Ptr{Cvoid},), h))
+    rc == -1 && throw(ArgumentError(msg))          # TCI_ERR_INVALID
+    error(msg)                                     # "lu.L contains NaNs", "Pivot matrix at bond b is not square!", CUDA errors ...
+end
+
+# ---- handle: one CUDA device + stream + workspaces (one per Julia task / per GPU) ---------------------------------------
+mutable struct Handle
+    ptr::Ptr{Cvoid}
+    function Handle(device::Integer=0)
+        r = Ref{Ptr{Cvoid}}(C_NULL)
+        rc = ccall((:tci_create, LIB), Cint, (Ref{Ptr{Cvoid}}, Cint), r, device)
+        rc == TCI_OK || error(unsafe_string(ccall((:tci_last_error, LIB), Cstring, (Ptr{Cvoid},), C_NULL)))
+        h = new(r[])
+        finalizer(x -> ccall((:tci_destroy, LIB), Cint, (Ptr{Cvoid},), x.ptr), h)
+        return h
+    end
+end
+const DEFAULT = Ref{Union{Nothing,Handle}}(nothing)
+handle() = (DEFAULT[] === nothing && (DEFAULT[] = Handle(0)); DEFAULT[]::Handle)
+
+# ---- device matrix (column-major FP64, leading dimension padded to 128 B) ------------------------------------------------
+mutable struct DeviceMatrix <: AbstractMatrix{Float64}
+    h::Handle
+    ptr::Ptr{Float64}
+    m::Int
+    n::Int
+    ld::Int
+    function DeviceMatrix(h::Handle, m::Int, n::Int)
+        ld = max(cld(m, 16) * 16, 1)
+        p = Ref{Ptr{Cvoid}}(C_NULL)
+        check(h.ptr, ccall((:tci_malloc, LIB), Cint, (Ptr{Cvoid}, Ref{Ptr{Cvoid}}, Csize_t), h.ptr, p, 8 * ld * max(n, 1)))
+        A = new(h, Ptr{Float64}(p[]), m, n, ld)
+        finalizer(x -> ccall((:tci_free, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}), x.h.ptr, x.ptr), A)
+        return A
+    end
+end
+Base.size(A::DeviceMatrix) = (A.m, A.n)
+function Base.Array(A::DeviceMatrix)
+    out = Matrix{Float64}(undef, A.ld, A.n)
+    check(A.h.ptr, ccall((:tci_memcpy_d2h, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Csize_t), A.h.ptr, out, A.ptr, 8 * A.ld * A.n))
+    return out[1:A.m, :]
+end
+Base.getindex(A::DeviceMatrix, i::Int, j::Int) = Array(A)[i, j]      # debugging only; the sweep never indexes Pi element-wise
+
+# ---- B1: device functor as a BatchEvaluator ------------------------------------------------------------------------------
+"""
+    B200Function(localdims; kind=:lorentz, params=[1.0])        built-in functor (include/tci_b200.h: TCI_F_*_ID)
+    B200Function(localdims, cuda_source; params=Float64[])      plugin: CUDA source defining
+        __device__ double tci_user_f(const int* idx, int n, const double* params, int nparams);
+"""
+mutable struct B200Function <: BatchEvaluator{Float64}
+    h::Handle
+    f::Ptr{Cvoid}
+    localdims::Vector{Int32}
+end
+const KINDS = Dict(:lorentz => 1, :qexpsin => 2, :qexpplussin => 3, :sum => 4, :qexp2 => 5)
+function B200Function(localdims::Vector{Int}; kind::Symbol=:lorentz, params::Vector{Float64}=[1.0], h::Handle=handle())
+    r = Ref{Ptr{Cvoid}}(C_NULL)
+    check(h.ptr, ccall((:tci_functor_builtin, LIB), Cint, (Ptr{Cvoid}, Cint, Ptr{Float64}, Cint, Ref{Ptr{Cvoid}}),
+                       h.ptr, KINDS[kind], params, length(params), r))
+    return _finalize(B200Function(h, r[], Int32.(localdims)))
+end
+function B200Function(localdims::Vector{Int}, cuda_source::String; params::Vector{Float64}=Float64[], h::Handle=handle())
+    r = Ref{Ptr{Cvoid}}(C_NULL)
+    check(h.ptr, ccall((:tci_functor_from_source, LIB), Cint, (Ptr{Cvoid}, Cstring, Ptr{Float64}, Cint, Ref{Ptr{Cvoid}}),
+                       h.ptr, cuda_source, params, length(params), r))
+    return _finalize(B200Function(h, r[], Int32.(localdims)))
+end
+_finalize(f::B200Function) = (finalizer(x -> ccall((:tci_functor_destroy, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}), x.h.ptr, x.f), f); f)
+
+_table(set::Vector{MultiIndex}) = isempty(set) ? Matrix{Int32}(undef, 0, 0) : Int32[set[i][p] for p in 1:length(first(set)), i in 1:length(set)]  # (len, count) column-major == count rows of len ints
+
+# batch evaluation into a device matrix (what updatepivots! wants: Pi never visits the host)
+function evaluate_device!(f::B200Function, out::DeviceMatrix, left::Vector{MultiIndex}, right::Vector{MultiIndex},
+                          stride_c::Int, stride_j::Int, maxabs::Ref{Float64})
+    L, R = _table(left), _table(right)
+    check(f.h.ptr, ccall((:tci_batcheval_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Cint, Ptr{Int32}, Int64, Cint, Ptr{Int32}, Int64, Cint, Ptr{Float64}, Int64, Int64, Ref{Float64}),
+        f.h.ptr, f.f, f.localdims, length(f.localdims), L, length(left), size(L, 1), R, length(right), size(R, 1),
+        out.ptr, stride_c, stride_j, maxabs))
+    return out
+end
+
+# the reference's protocol: returns a fresh host Array{Float64,M+2} (src/batcheval.jl:196-214)
+function (f::B200Function)(left::Vector{MultiIndex}, right::Vector{MultiIndex}, ::Val{M})::Array{Float64,M + 2} where {M}
+    if length(left) * length(right) == 0
+        return Array{Float64,M + 2}(undef, ntuple(i -> 0, M + 2)...)
+    end
+    nl = length(first(left))
+    cdims = Int.(f.localdims[nl+1:nl+M])
+    rows = length(left) * prod(cdims; init=1)
+    tmp = DeviceMatrix(f.h, rows, length(right))
+    evaluate_device!(f, tmp, left, right, length(left), tmp.ld, Ref(0.0))
+    return reshape(Array(tmp), length(left), cdims..., length(right))
+end
+(f::B200Function)(indexset::MultiIndex)::Float64 = f([indexset[1:1]], [indexset[2:end]], Val(0))[1, 1]
+
+# ---- B2: rrlu on host matrices (drop-in for TCI.rrlu) and on device matrices (used by the sweep) ---------------------------
+function rrlu_b200(A::Matrix{Float64}; maxrank::Int=typemax(Int), reltol::Number=1e-14, abstol::Number=0.0,
+                   leftorthogonal::Bool=true, h::Handle=handle())::rrLU{Float64}
+    m, n = size(A)
+    mr = min(maxrank, m, n)
+    rowperm, colperm = Vector{Int}(undef, m), Vector{Int}(undef, n)
+    L, U = Matrix{Float64}(undef, m, max(mr, 1)), Matrix{Float64}(undef, max(mr, 1), n)
+    npivot, err = Ref{Int64}(0), Ref{Float64}(0.0)
+    check(h.ptr, ccall((:tci_rrlu_host_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int64, Int64, Int64, Int64, Float64, Float64, Cint, Ptr{Int64}, Ptr{Int64}, Ref{Int64}, Ref{Float64},
+         Ptr{Float64}, Int64, Ptr{Float64}, Int64, Ptr{Float64}),
+        h.ptr, A, m, n, max(m, 1), mr, reltol, abstol, leftorthogonal, rowperm, colperm, npivot, err, L, max(m, 1), U, max(mr, 1), C_NULL))
+    r = npivot[]
+    return rrLU{Float64}(rowperm, colperm, L[:, 1:r], U[1:r, :], leftorthogonal, r, err[])
+end
+
+"""Device-side MatrixLUCI: rrlu! in place on Pi, factors formed on the device (tci_luci_factors_f64)."""
+struct DeviceLUCI
+    Pi::DeviceMatrix
+    rowperm::Vector{Int}
+    colperm::Vector{Int}
+    L::DeviceMatrix
+    U::DeviceMatrix
+    leftorthogonal::Bool
+    npivot::Int
+    error::Float64
+    pivoterrors::Vector{Float64}
+end
+function DeviceLUCI(Pi::DeviceMatrix; maxrank::Int=typemax(Int), reltol::Number=1e-14, abstol::Number=0.0, leftorthogonal::Bool=true)
+    h, m, n = Pi.h, Pi.m, Pi.n
+    mr = min(maxrank, m, n)
+    rowperm, colperm = Vector{Int}(undef, m), Vector{Int}(undef, n)
+    L, U = DeviceMatrix(h, m, max(mr, 1)), DeviceMatrix(h, max(mr, 1), n)
+    npivot, err, pe = Ref{Int64}(0), Ref{Float64}(0.0), Vector{Float64}(undef, mr + 1)
+    check(h.ptr, ccall((:tci_rrlu_inplace_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int64, Int64, Int64, Int64, Float64, Float64, Cint, Ptr{Int64}, Ptr{Int64}, Ref{Int64}, Ref{Float64},
+         Ptr{Float64}, Int64, Ptr{Float64}, Int64, Ptr{Float64}),
+        h.ptr, Pi.ptr, m, n, Pi.ld, mr, reltol, abstol, leftorthogonal, rowperm, colperm, npivot, err, L.ptr, L.ld, U.ptr, U.ld, pe))
+    return DeviceLUCI(Pi, rowperm, colperm, L, U, leftorthogonal, npivot[], err[], pe[1:npivot[]+1])
+end
+TCI.rowindices(l::DeviceLUCI) = l.rowperm[1:l.npivot]
+TCI.colindices(l::DeviceLUCI) = l.colperm[1:l.npivot]
+TCI.npivots(l::DeviceLUCI) = l.npivot
+TCI.pivoterrors(l::DeviceLUCI) = l.pivoterrors
+function factors(l::DeviceLUCI)      # left(luci), right(luci)  src/matrixluci.jl:256-283
+    h, m, n, r = l.Pi.h, l.Pi.m, l.Pi.n, l.npivot
+    left, right = DeviceMatrix(h, m, r), DeviceMatrix(h, r, n)
+    check(h.ptr, ccall((:tci_luci_factors_f64, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Int64, Int64, Cint, Ptr{Int64}, Ptr{Int64}, Ptr{Float64}, Int64, Ptr{Float64}, Int64, Ptr{Float64}, Int64, Ptr{Float64}, Int64),
+        h.ptr, m, n, r, l.leftorthogonal, l.rowperm, l.colperm, l.L.ptr, l.L.ld, l.U.ptr, l.U.ld, left.ptr, left.ld, right.ptr, right.ld))
+    return left, right
+end
+TCI.left(l::DeviceLUCI) = Array(factors(l)[1])
+TCI.right(l::DeviceLUCI) = Array(factors(l)[2])
+
+# ---- the one method of the sweep that is re-routed: the :full branch of updatepivots! (src/tensorci2.jl:845-868) ----------
+# Identical to the reference except that Pi is filled and factorised on the device.
+function TCI.updatepivots!(tci::TCI.TensorCI2{Float64}, b::Int, f::B200Function, leftorthogonal::Bool;
+                           reltol::Float64=1e-14, abstol::Float64=0.0, maxbonddim::Int=typemax(Int),
+                           sweepdirection::Symbol=:forward, pivotsearch::Symbol=:full, verbosity::Int=0,
+                           extraIset::Vector{MultiIndex}=MultiIndex[], extraJset::Vector{MultiIndex}=MultiIndex[])
+    pivotsearch === :full || error("B200 path implements pivotsearch=:full")
+    TCI.invalidatesitetensors!(tci)
+    Icombined = union(TCI.kronecker(tci.Iset[b], tci.localdims[b]), extraIset)
+    Jcombined = union(TCI.kronecker(tci.localdims[b+1], tci.Jset[b+1]), extraJset)
+    Pi = DeviceMatrix(f.h, length(Icombined), length(Jcombined))
+    mx = Ref(tci.maxsamplevalue)
+    evaluate_device!(f, Pi, Icombined, Jcombined, length(Icombined), Pi.ld, mx)     # filltensor + updatemaxsample!
+    tci.maxsamplevalue = mx[]
+    luci = DeviceLUCI(Pi; reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=leftorthogonal)
+    tci.Iset[b+1] = Icombined[TCI.rowindices(luci)]
+    tci.Jset[b] = Jcombined[TCI.colindices(luci)]
+    if length(extraIset) == 0 && length(extraJset) == 0
+        TCI.setsitetensor!(tci, b, TCI.left(luci))
+        TCI.setsitetensor!(tci, b + 1, TCI.right(luci))
+    end
+    TCI.updateerrors!(tci, b, TCI.pivoterrors(luci))
+    nothing
+end
+
+# ---- B3: TensorTrain sum / evaluate on device-resident cores ---------------------------------------------------------------
+struct DeviceTT
+    h::Handle
+    cores::Vector{DeviceMatrix}          # (chi_l*d) x chi_r each
+    shapes::Vector{Int64}                # 3 per core
+end
+function DeviceTT(tt::TCI.AbstractTensorTrain{Float64}; h::Handle=handle())
+    cores, shapes = DeviceMatrix[], Int64[]
+    for T in TCI.sitetensors(tt)
+        chil, chir = size(T, 1), size(T)[end]
+        d = div(length(T), chil * chir)
+        M = DeviceMatrix(h, chil * d, chir)
+        host = zeros(M.ld, chir); host[1:chil*d, :] = reshape(T, chil * d, chir)
+        check(h.ptr, ccall((:tci_memcpy_h2d, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Csize_t), h.ptr, M.ptr, host, 8 * length(host)))
+        push!(cores, M); append!(shapes, (chil, d, chir))
+    end
+    return DeviceTT(h, cores, shapes)
+end
+function Base.sum(tt::DeviceTT)
+    out = Ref{Float64}(0.0)
+    ptrs, lds = [c.ptr for c in tt.cores], Int64[c.ld for c in tt.cores]
+    check(tt.h.ptr, ccall((:tci_tt_sum_f64, LIB), Cint, (Ptr{Cvoid}, Ptr{Ptr{Float64}}, Ptr{Int64}, Ptr{Int64}, Cint, Ref{Float64}),
+                          tt.h.ptr, ptrs, tt.shapes, lds, length(tt.cores), out))
+    return out[]
+end
+function evaluate(tt::DeviceTT, points::Vector{MultiIndex})
+    n = length(tt.cores)
+    idx = Int32[p[b] for b in 1:n, p in points]
+    out = Vector{Float64}(undef, length(points))
+    ptrs, lds = [c.ptr for c in tt.cores], Int64[c.ld for c in tt.cores]
+    check(tt.h.ptr, ccall((:tci_tt_evaluate_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Ptr{Float64}}, Ptr{Int64}, Ptr{Int64}, Cint, Ptr{Int32}, Int64, Ptr{Float64}),
+        tt.h.ptr, ptrs, tt.shapes, lds, n, idx, length(points), out))
+    return out
+end
+
+end # module
