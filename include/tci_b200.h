@@ -98,6 +98,8 @@ int tci_submatrixargmax_abs2_f64(tci_handle h, const double* d_A, int64_t m, int
  * launch overhead, so bench.py uses it on a separate pass). */
 int tci_rrlu_set_profiling(tci_handle h, int on);
 int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps);
+/* Per-launch update-kernel times (ms) of the last profiled rrlu; returns how many there are, copies at most cap. */
+int64_t tci_rrlu_last_launch_ms(tci_handle h, float* h_ms, int64_t cap);
 
 /* ---- K1: batched function evaluation + Pi assembly ------------------------------------------------
  * The target function is a DEVICE functor (the reference's `f(indexset)::Float64`, evaluated on the GPU).

@@ -31,6 +31,7 @@ struct tci_context {
     int64_t rrlu_steps = 0;
     int rrlu_profile = 0;                   // 1: bracket every update-kernel launch with events
     std::vector<cudaEvent_t> ev_pool;
+    std::vector<float> rrlu_launch_ms;      // per-launch update-kernel times of the last profiled rrlu
     // generic scratch for the other kernels
     tci_workspace ws_a, ws_b, ws_c;
 };

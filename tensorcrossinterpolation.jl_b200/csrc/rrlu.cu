@@ -125,63 +125,78 @@ rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const do
     int bi = -1, bj = -1;
 
     if (np < maxrank) {                                 // otherwise the loop ends; nothing reads the block
-        constexpr int RPT = VEC ? 2 : 1;                // rows per thread
-        constexpr int TR = kThreads * RPT;
-        const int rbase = VEC ? (r0 & ~1) : r0;
-        const int nrt = (m - rbase + TR - 1) / TR;
-        const int nct = (n - c0 + COLS - 1) / COLS;
-        const long long ntiles = (long long)nrt * nct;
         const double* xcol = A + (long long)k * lda;    // scaled pivot column (UPDATE only)
-        const bool rev = serpentine && (np & 1);
-        for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
-            const long long t = rev ? ntiles - 1 - t0 : t0;
-            const int rt = (int)(t % nrt), ct = (int)(t / nrt);
-            const int i0 = rbase + rt * TR + threadIdx.x * RPT;
-            const int j0 = c0 + ct * COLS;
-            if (i0 >= m) continue;
-            if (VEC) {
-                const bool v0 = i0 >= r0, v1 = i0 + 1 < m;
-                if (v0 && v1) {
-                    double2 x = make_double2(0.0, 0.0);
-                    if (UPDATE) x = *reinterpret_cast<const double2*>(xcol + i0);
-                    double2 a[COLS];
+        const bool rev = serpentine == 2 ? true : (serpentine == 3 ? !(np & 1) : (serpentine && (np & 1)));
+        const int nct = (n - c0 + COLS - 1) / COLS;
+        if (VEC) {
+            // Row tiling: start at the 128-byte line that holds row r0 (rows below r0 are masked), and split the
+            // height into nrt EQUAL tiles (a ragged last tile would leave the blocks that own it short of work:
+            // tiles are dealt round-robin and gridDim.x and nrt share factors).
+            constexpr int TR = kThreads * 2;
+            const int rbase = r0 & ~15;
+            const int h = m - rbase;
+            const int nrt = (h + TR - 1) / TR;
+            const int rpt = (((h + nrt - 1) / nrt) + 15) & ~15;          // rows per tile, multiple of 16, <= TR
+            const long long ntiles = (long long)nrt * nct;
+            const int il = threadIdx.x * 2;
+            if (il < rpt) {
+                for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+                    const long long t = rev ? ntiles - 1 - t0 : t0;
+                    const int rt = (int)(t % nrt), ct = (int)(t / nrt);
+                    const int i0 = rbase + rt * rpt + il;
+                    const int j0 = c0 + ct * COLS;
+                    if (i0 + 1 < r0 || i0 >= m) continue;               // both rows masked, or past the end
+                    if (i0 + 1 < m) {
+                        const bool v0 = i0 >= r0;                       // false only for the pair that straddles r0
+                        double2 x = make_double2(0.0, 0.0);
+                        if (UPDATE) x = *reinterpret_cast<const double2*>(xcol + i0);
+                        double2 a[COLS];
 #pragma unroll
-                    for (int c = 0; c < COLS; ++c)
-                        if (j0 + c < n) a[c] = *reinterpret_cast<const double2*>(A + (long long)(j0 + c) * lda + i0);
+                        for (int c = 0; c < COLS; ++c)
+                            if (j0 + c < n) a[c] = *reinterpret_cast<const double2*>(A + (long long)(j0 + c) * lda + i0);
 #pragma unroll
-                    for (int c = 0; c < COLS; ++c) {
-                        const int j = j0 + c;
-                        if (j < n) {
-                            double2 v = a[c];
-                            if (UPDATE) {
-                                const double y = ybuf[j];
-                                v.x = __dsub_rn(v.x, __dmul_rn(x.x, y));
-                                v.y = __dsub_rn(v.y, __dmul_rn(x.y, y));
-                                *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
+                        for (int c = 0; c < COLS; ++c) {
+                            const int j = j0 + c;
+                            if (j < n) {
+                                double2 v = a[c];
+                                if (UPDATE) {
+                                    const double y = ybuf[j];
+                                    if (v0) v.x = __dsub_rn(v.x, __dmul_rn(x.x, y));    // row r0-1 is the pivot row: rewritten unchanged
+                                    v.y = __dsub_rn(v.y, __dmul_rn(x.y, y));
+                                    *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
+                                }
+                                const double q0 = v0 ? __dmul_rn(v.x, v.x) : -INFINITY, q1 = __dmul_rn(v.y, v.y);
+                                TCI_CONSIDER(q0, v.x, i0, j)
+                                TCI_CONSIDER(q1, v.y, i0 + 1, j)
                             }
-                            const double q0 = __dmul_rn(v.x, v.x), q1 = __dmul_rn(v.y, v.y);
-                            TCI_CONSIDER(q0, v.x, i0, j)
-                            TCI_CONSIDER(q1, v.y, i0 + 1, j)
+                        }
+                    } else {                                            // i0 == m - 1: odd tail row, scalar
+                        const int i = i0;
+                        if (i < r0) continue;
+                        const double x = UPDATE ? xcol[i] : 0.0;
+#pragma unroll
+                        for (int c = 0; c < COLS; ++c) {
+                            const int j = j0 + c;
+                            if (j < n) {
+                                double v = A[(long long)j * lda + i];
+                                if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
+                                const double q = __dmul_rn(v, v);
+                                TCI_CONSIDER(q, v, i, j)
+                            }
                         }
                     }
-                    continue;
                 }
-                // edge rows of the aligned tiling: at most one valid row, scalar path below
-                const int i = v0 ? i0 : i0 + 1;
-                if (i < r0 || i >= m) continue;
-                const double x = UPDATE ? xcol[i] : 0.0;
-#pragma unroll
-                for (int c = 0; c < COLS; ++c) {
-                    const int j = j0 + c;
-                    if (j < n) {
-                        double v = A[(long long)j * lda + i];
-                        if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
-                        const double q = __dmul_rn(v, v);
-                        TCI_CONSIDER(q, v, i, j)
-                    }
-                }
-            } else {
-                const int i = i0;
+            }
+        } else {
+            constexpr int TR = kThreads;
+            const int nrt = (m - r0 + TR - 1) / TR;
+            const long long ntiles = (long long)nrt * nct;
+            for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+                const long long t = rev ? ntiles - 1 - t0 : t0;
+                const int rt = (int)(t % nrt), ct = (int)(t / nrt);
+                const int i = r0 + rt * TR + threadIdx.x;
+                const int j0 = c0 + ct * COLS;
+                if (i >= m) continue;
                 const double x = UPDATE ? xcol[i] : 0.0;
                 double a[COLS];
 #pragma unroll
@@ -343,7 +358,7 @@ int occupancy_grid(tci_handle h) {
 UpdateCfg update_cfg(tci_handle h, bool vec) {
     UpdateCfg c; c.cols = 8; c.serpentine = 1;
     if (const char* e = getenv("TCI_RRLU_COLS")) { int v = atoi(e); if (v == 4 || v == 8 || v == 16) c.cols = v; }
-    if (const char* e = getenv("TCI_RRLU_SERPENTINE")) c.serpentine = atoi(e) ? 1 : 0;
+    if (const char* e = getenv("TCI_RRLU_SERPENTINE")) c.serpentine = atoi(e);
     if (vec) c.grid = c.cols == 4 ? occupancy_grid<true, true, 4>(h) : c.cols == 8 ? occupancy_grid<true, true, 8>(h) : occupancy_grid<true, true, 16>(h);
     else     c.grid = occupancy_grid<true, false, 8>(h);
     if (const char* e = getenv("TCI_RRLU_BLOCKS_PER_SM")) { int v = atoi(e); if (v > 0 && v * h->num_sms < c.grid) c.grid = v * h->num_sms; }
@@ -411,7 +426,8 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     if (h->rrlu_profile) {
         TCI_CUDA(h, cudaStreamSynchronize(h->stream));
         double tot = 0.0;
-        for (int s = 0; s < launched; ++s) { float ms = 0.f; cudaEventElapsedTime(&ms, h->ev_pool[2 * s], h->ev_pool[2 * s + 1]); tot += ms; }
+        h->rrlu_launch_ms.assign(launched, 0.f);
+        for (int s = 0; s < launched; ++s) { float ms = 0.f; cudaEventElapsedTime(&ms, h->ev_pool[2 * s], h->ev_pool[2 * s + 1]); tot += ms; h->rrlu_launch_ms[s] = ms; }
         h->rrlu_ms[1] = tot;
     }
     return TCI_OK;
@@ -561,6 +577,13 @@ int tci_rrlu_set_profiling(tci_handle h, int on) {
     if (!h) return TCI_ERR_INVALID;
     h->rrlu_profile = on ? 1 : 0;
     return TCI_OK;
+}
+
+int64_t tci_rrlu_last_launch_ms(tci_handle h, float* h_ms, int64_t cap) {
+    if (!h) return 0;
+    const int64_t n = (int64_t)h->rrlu_launch_ms.size();
+    if (h_ms) for (int64_t i = 0; i < n && i < cap; ++i) h_ms[i] = h->rrlu_launch_ms[i];
+    return n;
 }
 
 int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps) {
