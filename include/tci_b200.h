@@ -109,12 +109,14 @@ int64_t tci_rrlu_last_launch_ms(tci_handle h, float* h_ms, int64_t cap);
  *   3 QEXPPLUSSIN  exp(-p0 x) + p1 sin(p2 x)                      test/test_globalsearch.jl:14
  *   4 SUM          p0 * sum_i v_i                                 test/test_batcheval.jl:18
  *   5 QEXP2        exp(-p0 x) + p1 exp(-p2 x)                     test/test_tensorci2.jl:63,:146
+ *   7 HASH         p0 u(v) + p1 / (1 + sum_i v_i^2), u = integer hash of v in [-1, 1): synthetic full-rank function (not in
+ *                  the reference) that saturates any maxbonddim; benchmarks only
  * tci_functor_dense: lookup in a column-major table T[v_1, ..., v_N] (copied to the device).
  * tci_functor_from_source: the plugin path — CUDA C++ source that defines
  *     __device__ double tci_user_f(const int* idx, int n, const double* params, int nparams);
  *   (idx = the full 1-based multi-index, as the reference passes to f) is compiled with NVRTC for sm_100a.
  */
-enum { TCI_F_LORENTZ_ID = 1, TCI_F_QEXPSIN_ID = 2, TCI_F_QEXPPLUSSIN_ID = 3, TCI_F_SUM_ID = 4, TCI_F_QEXP2_ID = 5 };
+enum { TCI_F_LORENTZ_ID = 1, TCI_F_QEXPSIN_ID = 2, TCI_F_QEXPPLUSSIN_ID = 3, TCI_F_SUM_ID = 4, TCI_F_QEXP2_ID = 5, TCI_F_HASH_ID = 7 };
 int tci_functor_builtin(tci_handle h, int kind, const double* h_params, int nparams, tci_functor* out);
 int tci_functor_dense(tci_handle h, const double* h_table, const int32_t* h_dims, int ndims, tci_functor* out);
 int tci_functor_from_source(tci_handle h, const char* cuda_src, const double* h_params, int nparams, tci_functor* out);

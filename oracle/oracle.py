@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_build", "libtci_oracle.so")
 
-F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE = range(7)
+F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE, F_HASH = range(8)
 INT64_MAX = np.iinfo(np.int64).max
 
 CALLBACK = C.CFUNCTYPE(C.c_double, C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
@@ -334,6 +334,27 @@ def crossinterpolate2(f, localdims, initialpivots=None, **kw):
     tci = TCI2(f, localdims, initialpivots)
     ranks, errors = tci.optimize(**kw)
     return tci, ranks, errors
+
+
+def optfirstpivot(f, localdims, firstpivot=None, maxsweep=1000):
+    """util.jl:260-291, literally (sequential strict-> scan)."""
+    n = len(localdims)
+    pivot = [1] * n if firstpivot is None else [int(v) for v in firstpivot]
+    valf = abs(f(pivot))
+    for _ in range(maxsweep):
+        valf_prev = valf
+        for i in range(n):
+            for d in range(1, int(localdims[i]) + 1):
+                bak = pivot[i]
+                pivot[i] = d
+                newval = abs(f(pivot))
+                if newval > valf:
+                    valf = newval
+                else:
+                    pivot[i] = bak
+        if valf_prev == valf:
+            break
+    return pivot
 
 
 def _flatten_tt(cores):

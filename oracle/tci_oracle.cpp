@@ -278,8 +278,14 @@ enum FuncKind {
     F_QEXPPLUSSIN = 3,    // exp(-p0 x) + p1 sin(p2 x)            test_globalsearch.jl:14
     F_SUM = 4,            // p0 * sum v_i                         test_batcheval.jl:18
     F_QEXP2 = 5,          // exp(-p0 x) + p1 exp(-p2 x)           test_tensorci2.jl:63,:146
-    F_DENSE = 6           // column-major table lookup T[v...]    test_tensorci2.jl:29,:464
+    F_DENSE = 6,          // column-major table lookup T[v...]    test_tensorci2.jl:29,:464
+    F_HASH = 7            // p0 * u(v) + p1 / (1 + sum v_i^2), u = integer hash of v in [-1, 1): a full-rank synthetic
+                          // function (not in the reference) that drives every bond to maxbonddim (bench only)
 };
+static inline uint64_t splitmix64(uint64_t z) {
+    z += 0x9e3779b97f4a7c15ULL; z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+    return z ^ (z >> 31);
+}
 typedef double (*orc_callback)(const int32_t* idx, int32_t n, void* user);
 
 struct Func {
@@ -306,6 +312,10 @@ struct Func {
         case F_QEXPPLUSSIN: { double x = qx(v, n); return std::exp(-p[0] * x) + p[1] * std::sin(p[2] * x); }
         case F_SUM: { int64_t s = 0; for (int i = 0; i < n; ++i) s += v[i]; return p[0] * (double)s; }
         case F_QEXP2: { double x = qx(v, n); return std::exp(-p[0] * x) + p[1] * std::exp(-p[2] * x); }
+        case F_HASH: { uint64_t hsum = 0; int64_t s2 = 0;
+                       for (int i = 0; i < n; ++i) { hsum += (uint64_t)v[i] * (splitmix64((uint64_t)i + 1) | 1ULL); s2 += (int64_t)v[i] * v[i]; }
+                       const double u = (double)(splitmix64(hsum) >> 11) * 0x1.0p-52 - 1.0;
+                       return p[0] * u + p[1] / (double)(1 + s2); }
         case F_DENSE: { int64_t off = 0, st = 1;
                         for (int i = 0; i < n; ++i) { off += (int64_t)(v[i] - 1) * st; st *= dims[i]; }
                         return table[(size_t)off]; }

@@ -10,9 +10,9 @@ from .matrixlu import rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing
 from .dense import Mat, gemm, luci_factors, solve_right                              # noqa: F401
 from .matrixluci import MatrixLUCI                                                  # noqa: F401
 from .batcheval import (BatchEvaluator, BuiltinFunction, LorentzFunction, SumFunction, QuanticsExpSin,          # noqa: F401
-                        QuanticsExpPlusSin, QuanticsExp2, DenseFunction, UserFunction, filltensor,
+                        QuanticsExpPlusSin, QuanticsExp2, DenseFunction, HashFunction, UserFunction, filltensor,
                         _batchevaluate_dispatch, to_numpy)
 from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain                       # noqa: F401
 from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecriterion, kronecker_left,      # noqa: F401
                         kronecker_right, DefaultGlobalPivotFinder, GlobalPivotSearchInput, forwardsweep,
-                        HostFunctionAdapter, makebatchevaluatable)
+                        HostFunctionAdapter, makebatchevaluatable, optfirstpivot)

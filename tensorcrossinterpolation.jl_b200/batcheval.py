@@ -9,7 +9,7 @@ import numpy as np
 from . import _lib
 from ._lib import TCIError, lib, p_f64, p_i32
 
-KIND_LORENTZ, KIND_QEXPSIN, KIND_QEXPPLUSSIN, KIND_SUM, KIND_QEXP2 = 1, 2, 3, 4, 5
+KIND_LORENTZ, KIND_QEXPSIN, KIND_QEXPPLUSSIN, KIND_SUM, KIND_QEXP2, KIND_HASH = 1, 2, 3, 4, 5, 7
 
 
 def as_table(indexset, length=None):
@@ -128,6 +128,13 @@ class QuanticsExp2(BuiltinFunction):
 
     def __init__(self, localdims, a=1.0, c=0.0, b=0.0, handle=None):
         super().__init__(KIND_QEXP2, [a, c, b], localdims, handle)
+
+
+class HashFunction(BuiltinFunction):
+    """amp * u(v) + lor / (1 + sum v_i^2) with u an integer hash of v in [-1, 1): synthetic full-rank benchmark function."""
+
+    def __init__(self, localdims, amp=1.0, lor=0.0, handle=None):
+        super().__init__(KIND_HASH, [amp, lor], localdims, handle)
 
 
 class DenseFunction(BatchEvaluator):

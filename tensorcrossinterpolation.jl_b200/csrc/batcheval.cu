@@ -23,7 +23,7 @@
 #include <cstring>
 #include <vector>
 
-enum { TCI_F_LORENTZ = 1, TCI_F_QEXPSIN = 2, TCI_F_QEXPPLUSSIN = 3, TCI_F_SUM = 4, TCI_F_QEXP2 = 5, TCI_F_DENSE = 6, TCI_F_USER = 100 };
+enum { TCI_F_LORENTZ = 1, TCI_F_QEXPSIN = 2, TCI_F_QEXPPLUSSIN = 3, TCI_F_SUM = 4, TCI_F_QEXP2 = 5, TCI_F_DENSE = 6, TCI_F_HASH = 7, TCI_F_USER = 100 };
 
 struct tci_functor_s {
     int kind = 0;
@@ -78,6 +78,23 @@ struct QuanticsF {
         if (KIND == TCI_F_QEXPSIN) return exp(-p0 * x) * sin(2.0 * 3.14159265358979323846 * p1 * pow(x, p2));   // test_tensorci2.jl:437
         if (KIND == TCI_F_QEXPPLUSSIN) return exp(-p0 * x) + p1 * sin(p2 * x);                                  // test_globalsearch.jl:14
         return exp(-p0 * x) + p1 * exp(-p2 * x);                                                               // test_tensorci2.jl:63,:146
+    }
+};
+// p0 * u(v) + p1 / (1 + sum v^2), u = integer hash of the multi-index in [-1, 1): a synthetic FULL-RANK function (not in the
+// reference) whose TT rank saturates any maxbonddim; used to benchmark sweeps in the HBM-bound regime.
+struct HashF {
+    double amp, lor;
+    struct State { unsigned long long h; long long s2; };
+    __device__ static unsigned long long mix(unsigned long long z) {
+        z += 0x9e3779b97f4a7c15ULL; z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+        return z ^ (z >> 31);
+    }
+    __device__ State zero() const { return State{0ULL, 0LL}; }
+    __device__ void push(State& s, int site, int v) const { s.h += (unsigned long long)v * (mix((unsigned long long)site + 1) | 1ULL); s.s2 += (long long)v * v; }
+    __device__ State merge(State a, State b) const { return State{a.h + b.h, a.s2 + b.s2}; }
+    __device__ double finish(State s) const {
+        const double u = (double)(mix(s.h) >> 11) * 0x1.0p-52 - 1.0;
+        return amp * u + lor / (double)(1 + s.s2);
     }
 };
 struct DenseF {                          // column-major table lookup
@@ -188,7 +205,7 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
     const size_t ints = ((nli + nri) * sizeof(int) + 255) & ~(size_t)255;
     int rc = tci_ws_reserve(h, h->ws_a, ints + 256);
     if (rc) return rc;
-    rc = tci_ws_reserve(h, h->ws_b, sizeof(long long) * (size_t)(sh.nleft + sh.nright) + 256);
+    rc = tci_ws_reserve(h, h->ws_b, 16 * (size_t)(sh.nleft + sh.nright) + 256);        // a State is at most 16 bytes
     if (rc) return rc;
     rc = tci_pinned_reserve(h, ints + 64);
     if (rc) return rc;
@@ -198,7 +215,7 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
     b->d_left = (int*)h->ws_a.ptr; b->d_right = b->d_left + nli;
     b->maxbits = (unsigned long long*)((char*)h->ws_a.ptr + ints);
     b->nanflag = (int*)(b->maxbits + 1);
-    b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + sizeof(long long) * (size_t)sh.nleft;
+    b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + 16 * (size_t)sh.nleft;
     TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
     if (nli + nri) {
         TCI_CUDA(h, cudaMemcpyAsync(b->d_left, pin, (nli + nri) * sizeof(int), cudaMemcpyHostToDevice, h->stream));
@@ -247,8 +264,8 @@ extern "C" {
 
 int tci_functor_builtin(tci_handle h, int kind, const double* h_params, int nparams, tci_functor* out) {
     if (!h || !out) return TCI_ERR_INVALID;
-    if (kind < TCI_F_LORENTZ || kind > TCI_F_QEXP2) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_builtin: unknown kind %d", kind);
-    const int need = (kind == TCI_F_LORENTZ || kind == TCI_F_SUM) ? 1 : 3;
+    if ((kind < TCI_F_LORENTZ || kind > TCI_F_QEXP2) && kind != TCI_F_HASH) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_builtin: unknown kind %d", kind);
+    const int need = (kind == TCI_F_LORENTZ || kind == TCI_F_SUM) ? 1 : (kind == TCI_F_HASH ? 2 : 3);
     if (nparams < need || nparams > 8) return tci_fail(h, TCI_ERR_INVALID, "tci_functor_builtin: kind %d needs %d parameters", kind, need);
     tci_functor f = new tci_functor_s();
     f->kind = kind; f->nparams = nparams;
@@ -344,6 +361,7 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
     case TCI_F_QEXPSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
     case TCI_F_QEXPPLUSSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
     case TCI_F_QEXP2: rc = run_builtin(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
+    case TCI_F_HASH: rc = run_builtin(h, HashF{f->p[0], f->p[1]}, sh, nsites, b, d_out); break;
     case TCI_F_DENSE: rc = run_builtin(h, DenseF{f->d_table, f->d_strides}, sh, nsites, b, d_out); break;
     case TCI_F_USER: rc = run_user(h, f, sh, b, d_out); break;
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);

@@ -26,6 +26,7 @@
 #include "context.h"
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 namespace {
 
@@ -44,7 +45,8 @@ struct RrluState {
     double maxerror;
     double error;        // lu.error
     unsigned int ticket; // blocks of the running update kernel that have finished
-    int flags;           // bit 0: NaN in L, bit 1: NaN in U
+    int flags;           // bit 0: NaN in L, bit 1: NaN in U, bit 2: grid barrier timed out
+    long long tphase[8]; // persistent kernel: clock64 cycles block 0 spent per phase (diagnostics)
 };
 
 __device__ __forceinline__ bool cand_better(const Cand& a, const Cand& b) {
@@ -90,13 +92,14 @@ __device__ __forceinline__ double jl_max(double a, double b) {   // Julia's max 
     return a > b ? a : b;
 }
 
-__global__ void rrlu_init_kernel(RrluState* st, int* rowperm, int* colperm, int m, int n) {
+__global__ void rrlu_init_kernel(RrluState* st, int* rowperm, int* colperm, int m, int n, unsigned int* bar) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t < m) rowperm[t] = t;
     if (t < n) colperm[t] = t;
     if (t == 0) {
         st->npivot = 0; st->stop = 0; st->pr = 0; st->pc = 0; st->pivval = 0.0;
         st->maxerror = 0.0; st->error = nan(""); st->ticket = 0u; st->flags = 0;
+        if (bar) *bar = 0u;
     }
 }
 
@@ -111,6 +114,110 @@ __global__ void rrlu_init_kernel(RrluState* st, int* rowperm, int* colperm, int 
 #define TCI_CONSIDER(q, val, ii, jj)                                                             \
     if ((q) > bv || ((q) == bv && ((jj) < bj || ((jj) == bj && (ii) < bi)))) { bv = (q); bx = (val); bi = (ii); bj = (jj); }
 
+// Loads that must see data written by OTHER blocks earlier in the same (persistent) kernel go around L1.
+template <bool NOL1> __device__ __forceinline__ double2 ld2(const double* p) {
+    return NOL1 ? __ldcg(reinterpret_cast<const double2*>(p)) : *reinterpret_cast<const double2*>(p);
+}
+template <bool NOL1> __device__ __forceinline__ double ld1(const double* p) { return NOL1 ? __ldcg(p) : *p; }
+
+// One pass of this block over its tiles of the trailing block [r0, m) x [c0, n), r0 = c0 = np.  UPDATE: apply the
+// rank-1 update of pivot k = np - 1 (scaled pivot column in A[:, k], packed pivot row in ybuf) and track the
+// abs2-argmax of the updated values; !UPDATE: search only.
+template <bool UPDATE, bool VEC, int COLS, bool NOL1>
+__device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n, long long lda, const double* __restrict__ ybuf,
+                                           int k, int np, int serpentine, double& bv, double& bx, int& bi, int& bj) {
+    const int r0 = np, c0 = np;
+    const double* xcol = A + (long long)k * lda;    // scaled pivot column (UPDATE only)
+    const bool rev = serpentine == 2 ? true : (serpentine == 3 ? !(np & 1) : (serpentine && (np & 1)));
+    const int nct = (n - c0 + COLS - 1) / COLS;
+    if (VEC) {
+        // Row tiling: start at the 128-byte line that holds row r0 (rows below r0 are masked), and split the
+        // height into nrt EQUAL tiles (a ragged last tile would leave the blocks that own it short of work:
+        // tiles are dealt round-robin and gridDim.x and nrt share factors).
+        constexpr int TR = kThreads * 2;
+        const int rbase = r0 & ~15;
+        const int h = m - rbase;
+        const int nrt = (h + TR - 1) / TR;
+        const int rpt = (((h + nrt - 1) / nrt) + 15) & ~15;          // rows per tile, multiple of 16, <= TR
+        const int ntiles = nrt * nct;                                // < 2^31: m, n < 2^31 - 1024 and TR * COLS >= 2048
+        const int il = threadIdx.x * 2;
+        if (il < rpt) {
+            for (int t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+                const int t = rev ? ntiles - 1 - t0 : t0;
+                const int rt = t % nrt, ct = t / nrt;
+                const int i0 = rbase + rt * rpt + il;
+                const int j0 = c0 + ct * COLS;
+                if (i0 + 1 < r0 || i0 >= m) continue;               // both rows masked, or past the end
+                if (i0 + 1 < m) {
+                    const bool v0 = i0 >= r0;                       // false only for the pair that straddles r0
+                    double2 x = make_double2(0.0, 0.0);
+                    if (UPDATE) x = ld2<NOL1>(xcol + i0);
+                    double2 a[COLS];
+#pragma unroll
+                    for (int c = 0; c < COLS; ++c)
+                        if (j0 + c < n) a[c] = ld2<NOL1>(A + (long long)(j0 + c) * lda + i0);
+#pragma unroll
+                    for (int c = 0; c < COLS; ++c) {
+                        const int j = j0 + c;
+                        if (j < n) {
+                            double2 v = a[c];
+                            if (UPDATE) {
+                                const double y = ld1<NOL1>(ybuf + j);
+                                if (v0) v.x = __dsub_rn(v.x, __dmul_rn(x.x, y));    // row r0-1 is the pivot row: rewritten unchanged
+                                v.y = __dsub_rn(v.y, __dmul_rn(x.y, y));
+                                *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
+                            }
+                            const double q0 = v0 ? __dmul_rn(v.x, v.x) : -INFINITY, q1 = __dmul_rn(v.y, v.y);
+                            TCI_CONSIDER(q0, v.x, i0, j)
+                            TCI_CONSIDER(q1, v.y, i0 + 1, j)
+                        }
+                    }
+                } else {                                            // i0 == m - 1: odd tail row, scalar
+                    const int i = i0;
+                    if (i < r0) continue;
+                    const double x = UPDATE ? ld1<NOL1>(xcol + i) : 0.0;
+#pragma unroll
+                    for (int c = 0; c < COLS; ++c) {
+                        const int j = j0 + c;
+                        if (j < n) {
+                            double v = ld1<NOL1>(A + (long long)j * lda + i);
+                            if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ld1<NOL1>(ybuf + j))); A[(long long)j * lda + i] = v; }
+                            const double q = __dmul_rn(v, v);
+                            TCI_CONSIDER(q, v, i, j)
+                        }
+                    }
+                }
+            }
+        }
+    } else {
+        constexpr int TR = kThreads;
+        const int nrt = (m - r0 + TR - 1) / TR;
+        const long long ntiles = (long long)nrt * nct;
+        for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+            const long long t = rev ? ntiles - 1 - t0 : t0;
+            const int rt = (int)(t % nrt), ct = (int)(t / nrt);
+            const int i = r0 + rt * TR + threadIdx.x;
+            const int j0 = c0 + ct * COLS;
+            if (i >= m) continue;
+            const double x = UPDATE ? ld1<NOL1>(xcol + i) : 0.0;
+            double a[COLS];
+#pragma unroll
+            for (int c = 0; c < COLS; ++c)
+                if (j0 + c < n) a[c] = ld1<NOL1>(A + (long long)(j0 + c) * lda + i);
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) {
+                const int j = j0 + c;
+                if (j < n) {
+                    double v = a[c];
+                    if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ld1<NOL1>(ybuf + j))); A[(long long)j * lda + i] = v; }
+                    const double q = __dmul_rn(v, v);
+                    TCI_CONSIDER(q, v, i, j)
+                }
+            }
+        }
+    }
+}
+
 template <bool UPDATE, bool VEC, int COLS>
 __global__ void __launch_bounds__(kThreads, (COLS <= 4 ? 5 : (COLS == 8 ? 3 : 2)))
 rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const double* __restrict__ ybuf,
@@ -120,101 +227,10 @@ rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const do
     if (st->stop) return;
     const int k = st->npivot;
     const int np = UPDATE ? k + 1 : start0;             // pivots in place once this pass is done
-    const int r0 = np, c0 = np;                         // trailing block starts here
     double bv = -INFINITY, bx = 0.0;
     int bi = -1, bj = -1;
-
-    if (np < maxrank) {                                 // otherwise the loop ends; nothing reads the block
-        const double* xcol = A + (long long)k * lda;    // scaled pivot column (UPDATE only)
-        const bool rev = serpentine == 2 ? true : (serpentine == 3 ? !(np & 1) : (serpentine && (np & 1)));
-        const int nct = (n - c0 + COLS - 1) / COLS;
-        if (VEC) {
-            // Row tiling: start at the 128-byte line that holds row r0 (rows below r0 are masked), and split the
-            // height into nrt EQUAL tiles (a ragged last tile would leave the blocks that own it short of work:
-            // tiles are dealt round-robin and gridDim.x and nrt share factors).
-            constexpr int TR = kThreads * 2;
-            const int rbase = r0 & ~15;
-            const int h = m - rbase;
-            const int nrt = (h + TR - 1) / TR;
-            const int rpt = (((h + nrt - 1) / nrt) + 15) & ~15;          // rows per tile, multiple of 16, <= TR
-            const long long ntiles = (long long)nrt * nct;
-            const int il = threadIdx.x * 2;
-            if (il < rpt) {
-                for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
-                    const long long t = rev ? ntiles - 1 - t0 : t0;
-                    const int rt = (int)(t % nrt), ct = (int)(t / nrt);
-                    const int i0 = rbase + rt * rpt + il;
-                    const int j0 = c0 + ct * COLS;
-                    if (i0 + 1 < r0 || i0 >= m) continue;               // both rows masked, or past the end
-                    if (i0 + 1 < m) {
-                        const bool v0 = i0 >= r0;                       // false only for the pair that straddles r0
-                        double2 x = make_double2(0.0, 0.0);
-                        if (UPDATE) x = *reinterpret_cast<const double2*>(xcol + i0);
-                        double2 a[COLS];
-#pragma unroll
-                        for (int c = 0; c < COLS; ++c)
-                            if (j0 + c < n) a[c] = *reinterpret_cast<const double2*>(A + (long long)(j0 + c) * lda + i0);
-#pragma unroll
-                        for (int c = 0; c < COLS; ++c) {
-                            const int j = j0 + c;
-                            if (j < n) {
-                                double2 v = a[c];
-                                if (UPDATE) {
-                                    const double y = ybuf[j];
-                                    if (v0) v.x = __dsub_rn(v.x, __dmul_rn(x.x, y));    // row r0-1 is the pivot row: rewritten unchanged
-                                    v.y = __dsub_rn(v.y, __dmul_rn(x.y, y));
-                                    *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
-                                }
-                                const double q0 = v0 ? __dmul_rn(v.x, v.x) : -INFINITY, q1 = __dmul_rn(v.y, v.y);
-                                TCI_CONSIDER(q0, v.x, i0, j)
-                                TCI_CONSIDER(q1, v.y, i0 + 1, j)
-                            }
-                        }
-                    } else {                                            // i0 == m - 1: odd tail row, scalar
-                        const int i = i0;
-                        if (i < r0) continue;
-                        const double x = UPDATE ? xcol[i] : 0.0;
-#pragma unroll
-                        for (int c = 0; c < COLS; ++c) {
-                            const int j = j0 + c;
-                            if (j < n) {
-                                double v = A[(long long)j * lda + i];
-                                if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
-                                const double q = __dmul_rn(v, v);
-                                TCI_CONSIDER(q, v, i, j)
-                            }
-                        }
-                    }
-                }
-            }
-        } else {
-            constexpr int TR = kThreads;
-            const int nrt = (m - r0 + TR - 1) / TR;
-            const long long ntiles = (long long)nrt * nct;
-            for (long long t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
-                const long long t = rev ? ntiles - 1 - t0 : t0;
-                const int rt = (int)(t % nrt), ct = (int)(t / nrt);
-                const int i = r0 + rt * TR + threadIdx.x;
-                const int j0 = c0 + ct * COLS;
-                if (i >= m) continue;
-                const double x = UPDATE ? xcol[i] : 0.0;
-                double a[COLS];
-#pragma unroll
-                for (int c = 0; c < COLS; ++c)
-                    if (j0 + c < n) a[c] = A[(long long)(j0 + c) * lda + i];
-#pragma unroll
-                for (int c = 0; c < COLS; ++c) {
-                    const int j = j0 + c;
-                    if (j < n) {
-                        double v = a[c];
-                        if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ybuf[j])); A[(long long)j * lda + i] = v; }
-                        const double q = __dmul_rn(v, v);
-                        TCI_CONSIDER(q, v, i, j)
-                    }
-                }
-            }
-        }
-    }
+    if (np < maxrank)                                   // otherwise the loop ends; nothing reads the block
+        scan_tiles<UPDATE, VEC, COLS, false>(A, m, n, lda, ybuf, k, np, serpentine, bv, bx, bi, bj);
 
     Cand c = block_reduce(Cand{bx, bi, bj}, s_c);
     if (threadIdx.x == 0) {
@@ -256,19 +272,16 @@ rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const do
 // packed copy of the new pivot row that the update kernel reads.  Thread t < n handles column t of the
 // two swapped rows, n <= t < n+m handles row t-n of the two swapped columns, t == n+m the four corners
 // and the permutation bookkeeping.
-__global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf,
-                                 RrluState* st, int* rowperm, int* colperm, double* pivvals, int leftorth) {
-    if (st->stop) return;
-    const int k = st->npivot, pr = st->pr, pc = st->pc;
-    const double piv = st->pivval;
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+template <bool NOL1>
+__device__ __forceinline__ void swap_item(int t, double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf,
+                                          int k, int pr, int pc, double piv, int* rowperm, int* colperm, double* pivvals, int leftorth) {
     if (t < n) {
         const int j = t;
         if (j == k || j == pc) return;
         double* pk = A + (long long)j * lda + k;
         double* pp = A + (long long)j * lda + pr;
-        const double a = *pk;
-        double newk = (pr != k) ? *pp : a;
+        const double a = ld1<NOL1>(pk);
+        double newk = (pr != k) ? ld1<NOL1>(pp) : a;
         if (!leftorth && j > k) newk = newk / piv;
         *pk = newk;
         if (pr != k) *pp = a;
@@ -278,14 +291,14 @@ __global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long
         if (i == k || i == pr) return;
         double* pk = A + (long long)k * lda + i;
         double* pp = A + (long long)pc * lda + i;
-        const double a = *pk;
-        double newk = (pc != k) ? *pp : a;
+        const double a = ld1<NOL1>(pk);
+        double newk = (pc != k) ? ld1<NOL1>(pp) : a;
         if (leftorth && i > k) newk = newk / piv;
         *pk = newk;
         if (pc != k) *pp = a;
     } else if (t == n + m) {
-        const double o_kk = A[(long long)k * lda + k], o_kpc = A[(long long)pc * lda + k];
-        const double o_prk = A[(long long)k * lda + pr], o_prpc = A[(long long)pc * lda + pr];
+        const double o_kk = ld1<NOL1>(A + (long long)k * lda + k), o_kpc = ld1<NOL1>(A + (long long)pc * lda + k);
+        const double o_prk = ld1<NOL1>(A + (long long)k * lda + pr), o_prpc = ld1<NOL1>(A + (long long)pc * lda + pr);
         double n_kk = o_prpc, n_kpc = o_prk, n_prk = o_kpc, n_prpc = o_kk;
         if (leftorth) { if (pr > k) n_prk = n_prk / piv; }
         else          { if (pc > k) n_kpc = n_kpc / piv; }
@@ -299,6 +312,94 @@ __global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long
         int tmp = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = tmp;
         tmp = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = tmp;
         pivvals[k] = piv;
+    }
+}
+
+__global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf,
+                                 RrluState* st, int* rowperm, int* colperm, double* pivvals, int leftorth) {
+    if (st->stop) return;
+    swap_item<false>(blockIdx.x * blockDim.x + threadIdx.x, A, m, n, lda, ybuf, st->npivot, st->pr, st->pc, st->pivval,
+                     rowperm, colperm, pivvals, leftorth);
+}
+
+// ---- persistent variant: the whole loop of _optimizerrlu! (:346-369) in ONE cooperative launch ---------------------
+// Per pivot step: [every block reduces the per-block candidates and evaluates the stop rule redundantly] ->
+// swap/scale phase spread over the grid -> grid barrier -> update + next search -> grid barrier.  No launch gaps,
+// no host round trip; the same scan_tiles/swap_item code as the step kernels, with L1-bypassing loads because
+// blocks read what other blocks wrote earlier in the same launch.
+__device__ __forceinline__ bool grid_barrier(unsigned int* bar, unsigned int target, int* s_abort) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // release-add without a return value (no round trip), then poll with acquire loads
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(bar) : "memory");
+        unsigned int v;
+        int ab = 0, spins = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+            if (++spins > (1 << 23)) { ab = 1; break; }              // a lost block must not hang the GPU
+        } while (v < target);
+        *s_abort = ab;
+    }
+    __syncthreads();
+    return *s_abort == 0;
+}
+
+template <bool VEC, int COLS>
+__global__ void __launch_bounds__(kThreads, (COLS <= 4 ? 5 : (COLS == 8 ? 3 : 2)))
+rrlu_persistent_kernel(double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf, RrluState* st,
+                       Cand* parts, int* rowperm, int* colperm, double* pivvals, int maxrank, double reltol, double abstol,
+                       int leftorth, int serpentine, unsigned int* bar) {
+    __shared__ Cand s_c[kThreads / 32];
+    __shared__ Cand s_best;
+    __shared__ int s_abort;
+    unsigned int phase = 0;
+    int np = 0;
+    double maxerror = 0.0, error = nan("");
+    double bv = -INFINITY, bx = 0.0;
+    int bi = -1, bj = -1;
+    scan_tiles<false, VEC, COLS, true>(A, m, n, lda, ybuf, 0, 0, serpentine, bv, bx, bi, bj);
+    long long tp[6] = {0, 0, 0, 0, 0, 0}, t0 = clock64(), t1;
+#define TCI_TICK(slot) { t1 = clock64(); tp[slot] += t1 - t0; t0 = t1; }
+    for (;;) {
+        Cand c = block_reduce(Cand{bx, bi, bj}, s_c);
+        if (threadIdx.x == 0) parts[blockIdx.x] = c;
+        TCI_TICK(0)
+        phase += gridDim.x;
+        if (!grid_barrier(bar, phase, &s_abort)) { if (threadIdx.x == 0) atomicOr(&st->flags, 4); return; }
+        TCI_TICK(1)
+        Cand best{0.0, -1, -1};
+        for (int b = threadIdx.x; b < (int)gridDim.x; b += kThreads) {
+            const double2 raw = __ldcg(reinterpret_cast<const double2*>(parts + b));
+            Cand o; o.x = raw.x; o.i = (int)(__double_as_longlong(raw.y) & 0xffffffffLL); o.j = (int)(__double_as_longlong(raw.y) >> 32);
+            if (cand_better(o, best)) best = o;
+        }
+        best = block_reduce(best, s_c);
+        if (threadIdx.x == 0) s_best = best;
+        __syncthreads();
+        best = s_best;
+        if (best.i < 0) { best.i = np; best.j = np; best.x = nan(""); }       // every entry NaN: first(rows), first(cols)
+        const double err = fabs(best.x);                                        // :360
+        error = err;
+        if ((err < reltol * maxerror || err < abstol) && np > 0) break;         // :363
+        maxerror = jl_max(maxerror, err);                                       // :367
+        TCI_TICK(2)
+        const int k = np;
+        for (int t = blockIdx.x * kThreads + threadIdx.x; t <= n + m; t += gridDim.x * kThreads)
+            swap_item<true>(t, A, m, n, lda, ybuf, k, best.i, best.j, best.x, rowperm, colperm, pivvals, leftorth);
+        TCI_TICK(3)
+        phase += gridDim.x;
+        if (!grid_barrier(bar, phase, &s_abort)) { if (threadIdx.x == 0) atomicOr(&st->flags, 4); return; }
+        TCI_TICK(4)
+        np = k + 1;
+        if (np >= maxrank) break;                                               // while lu.npivot < maxrank   (:356)
+        bv = -INFINITY; bx = 0.0; bi = -1; bj = -1;
+        scan_tiles<true, VEC, COLS, true>(A, m, n, lda, ybuf, k, np, serpentine, bv, bx, bi, bj);
+        TCI_TICK(5)
+    }
+#undef TCI_TICK
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        st->npivot = np; st->stop = 1; st->error = error; st->maxerror = maxerror;
+        for (int i = 0; i < 6; ++i) st->tphase[i] = tp[i];
     }
 }
 
@@ -328,18 +429,18 @@ __global__ void rrlu_extract_kernel(const double* __restrict__ A, int m, int n, 
 }
 
 struct SmallWs {                 // carve-up of tci_context::ws_small
-    RrluState* st; int* rowperm; int* colperm; double* ybuf; double* pivvals; Cand* parts;
+    RrluState* st; int* rowperm; int* colperm; double* ybuf; double* pivvals; Cand* parts; unsigned int* bar;
 };
 
 int carve(tci_handle h, int m, int n, int grid, SmallWs* w) {
     auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
-    const size_t o_st = 0, o_rp = al(sizeof(RrluState)), o_cp = o_rp + al(sizeof(int) * m),
+    const size_t o_st = 0, o_bar = al(sizeof(RrluState)), o_rp = o_bar + 256, o_cp = o_rp + al(sizeof(int) * m),
                  o_y = o_cp + al(sizeof(int) * n), o_pv = o_y + al(sizeof(double) * n),
                  o_parts = o_pv + al(sizeof(double) * (size_t)(m < n ? m : n)), total = o_parts + al(sizeof(Cand) * grid);
     int rc = tci_ws_reserve(h, h->ws_small, total);
     if (rc) return rc;
     char* b = (char*)h->ws_small.ptr;
-    w->st = (RrluState*)(b + o_st); w->rowperm = (int*)(b + o_rp); w->colperm = (int*)(b + o_cp);
+    w->st = (RrluState*)(b + o_st); w->bar = (unsigned int*)(b + o_bar); w->rowperm = (int*)(b + o_rp); w->colperm = (int*)(b + o_cp);
     w->ybuf = (double*)(b + o_y); w->pivvals = (double*)(b + o_pv); w->parts = (Cand*)(b + o_parts);
     return TCI_OK;
 }
@@ -376,6 +477,37 @@ void launch_update(tci_handle h, bool vec, const UpdateCfg& c, double* A, int m,
 #undef TCI_LAUNCH_UPD
 }
 
+template <bool VEC, int COLS>
+int launch_persistent_t(tci_handle h, double* A, int m, int n, long long lda, const SmallWs& w, int maxrank, double reltol,
+                        double abstol, int leftorth, int serpentine) {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rrlu_persistent_kernel<VEC, COLS>, kThreads, 0) != cudaSuccess || nb < 1)
+        return tci_fail(h, TCI_ERR_CUDA, "rrlu: occupancy query failed for the persistent kernel");
+    long long grid = (long long)nb * h->num_sms;
+    // small matrices: no more blocks than there are tiles / swap items at the first step (cheaper grid barrier)
+    const long long rows_per_tile = VEC ? 2 * kThreads : kThreads;
+    long long want = ((m + rows_per_tile - 1) / rows_per_tile) * (((long long)n + COLS - 1) / COLS);
+    const long long swapb = ((long long)m + n + 1 + kThreads - 1) / kThreads;
+    if (want < swapb) want = swapb;
+    if (grid > want) grid = want;
+    if (const char* e = getenv("TCI_RRLU_PGRID")) { long long v = atoll(e); if (v > 0 && v < grid) grid = v; }
+    double* ybuf = w.ybuf; RrluState* st = w.st; Cand* parts = w.parts; int* rp = w.rowperm; int* cp = w.colperm;
+    double* pv = w.pivvals; unsigned int* bar = w.bar;
+    void* args[] = {&A, &m, &n, &lda, &ybuf, &st, &parts, &rp, &cp, &pv, &maxrank, &reltol, &abstol, &leftorth, &serpentine, &bar};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)rrlu_persistent_kernel<VEC, COLS>, dim3((unsigned)grid), dim3(kThreads), args, 0, h->stream);
+    h->launches++;
+    if (e != cudaSuccess) return tci_fail(h, TCI_ERR_CUDA, "cudaLaunchCooperativeKernel(rrlu): %s", cudaGetErrorString(e));
+    return TCI_OK;
+}
+
+int launch_persistent(tci_handle h, bool vec, const UpdateCfg& c, double* A, int m, int n, long long lda, const SmallWs& w,
+                      int maxrank, double reltol, double abstol, int leftorth) {
+    if (!vec) return launch_persistent_t<false, 8>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
+    if (c.cols == 4) return launch_persistent_t<true, 4>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
+    if (c.cols == 16) return launch_persistent_t<true, 16>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
+    return launch_persistent_t<true, 8>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
+}
+
 } // namespace
 
 // Shared driver: factorises d_A in place, leaves perms/pivot values in ws_small, reads the final state.
@@ -384,17 +516,39 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     const bool vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15u) == 0);
     const UpdateCfg cfg = update_cfg(h, vec);
     const int grid = cfg.grid;
-    int rc = carve(h, m, n, grid, w);
+    int rc = carve(h, m, n, grid > h->num_sms * 8 ? grid : h->num_sms * 8, w);
     if (rc) return rc;
     rc = tci_pinned_reserve(h, sizeof(RrluState) + sizeof(int) * ((size_t)m + n) + sizeof(double) * (size_t)(mr + 1));
     if (rc) return rc;
     const int mx = m > n ? m : n;
-    rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n);
+    rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n, w->bar);
     TCI_LAUNCH_CHECK(h);
     TCI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
+    RrluState* hst = (RrluState*)h->pinned;
+    // One cooperative launch for the whole loop when the matrix is L2-resident (launch/latency-bound regime);
+    // step kernels when it streams from HBM (their launch gaps overlap, a grid barrier's do not).
+    bool persistent = (double)m * n * sizeof(double) <= 48e6;
+    if (const char* e = getenv("TCI_RRLU_MODE")) persistent = strcmp(e, "persistent") == 0 ? true : (strcmp(e, "steps") == 0 ? false : persistent);
+    if (h->rrlu_profile) persistent = false;                // per-launch profiling needs the step kernels
+    if (persistent) {
+        rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);
+        if (rc) return rc;
+        TCI_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+        TCI_CUDA(h, cudaMemcpyAsync(hst, w->st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+        if (hst->flags & 4) return tci_fail(h, TCI_ERR_CUDA, "rrlu: grid barrier timed out in the persistent kernel");
+        *final_state = *hst;
+        h->rrlu_steps = hst->npivot;
+        h->rrlu_ms[1] = 0.0;
+        if (getenv("TCI_RRLU_TPHASE")) {
+            fprintf(stderr, "rrlu persistent %dx%d steps=%d cycles/step:", m, n, hst->npivot);
+            for (int i = 0; i < 6; ++i) fprintf(stderr, " %s=%.0f", (const char*[]){"publish", "barrierA", "reduce", "swap", "barrierB", "scan"}[i], (double)hst->tphase[i] / (hst->npivot ? hst->npivot : 1));
+            fprintf(stderr, "\n");
+        }
+        return TCI_OK;
+    }
     launch_update<false>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
     TCI_LAUNCH_CHECK(h);
-    RrluState* hst = (RrluState*)h->pinned;
     const int swap_blocks = (m + n + 1 + 255) / 256;
     int launched = 0, chunk = 8;
     h->rrlu_steps = 0;
@@ -562,7 +716,7 @@ int tci_submatrixargmax_abs2_f64(tci_handle h, const double* d_A, int64_t m, int
     if (rc) return rc;
     rc = tci_pinned_reserve(h, sizeof(RrluState));
     if (rc) return rc;
-    rrlu_init_kernel<<<1, 32, 0, h->stream>>>(w.st, w.rowperm, w.colperm, 0, 0);
+    rrlu_init_kernel<<<1, 32, 0, h->stream>>>(w.st, w.rowperm, w.colperm, 0, 0, w.bar);
     TCI_LAUNCH_CHECK(h);
     launch_update<false>(h, vec, cfg, const_cast<double*>(d_A), (int)m, (int)n, lda, w, INT32_MAX, 0.0, 0.0, (int)(k - 1));
     TCI_LAUNCH_CHECK(h);

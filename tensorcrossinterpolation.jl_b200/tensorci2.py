@@ -510,6 +510,30 @@ def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, ma
     return np.asarray(ranks, dtype=np.int64), np.asarray(errors) / errornormalization
 
 
+def optfirstpivot(f, localdims, firstpivot=None, maxsweep=1000):
+    """optfirstpivot (util.jl:260-291): greedy one-site-at-a-time search for a large |f|.  All d_i candidates of a site go
+    through ONE K1 call; taking the first maximum that beats the current value is exactly the reference's sequential
+    strict-`>` scan (the other coordinates are fixed while site i is scanned)."""
+    localdims = [int(d) for d in localdims]
+    n = len(localdims)
+    f = makebatchevaluatable(f, localdims)
+    pivot = [1] * n if firstpivot is None else [int(v) for v in firstpivot]
+    valf = abs(f(pivot))
+    for _ in range(maxsweep):
+        valf_prev = valf
+        for i in range(n):
+            pts = np.tile(np.asarray(pivot, dtype=np.int32), (localdims[i], 1))
+            pts[:, i] = np.arange(1, localdims[i] + 1)
+            vals = np.abs(_point_values(f, pts)) if isinstance(f, BatchEvaluator) and not isinstance(f, HostFunctionAdapter) \
+                else np.array([abs(f(list(q))) for q in pts])
+            for d in range(localdims[i]):
+                if vals[d] > valf:
+                    valf = float(vals[d]); pivot[i] = d + 1
+        if valf_prev == valf:
+            break
+    return pivot
+
+
 def _sanitycheck(tci):                                      # globalsearch.jl:226-233
     for b in range(len(tci) - 1):
         if tci.Iset[b + 1].shape[0] != tci.Jset[b].shape[0]:

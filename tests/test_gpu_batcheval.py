@@ -130,3 +130,17 @@ def test_full_size_pi_c3(tci):
         i, j = int(rng.integers(5120)), int(rng.integers(5120))
         assert A[i, j] == g(list(Ic[i]) + list(Jc[j]))
     assert mx == A.max()
+
+
+@pytest.mark.gpu
+def test_hash_function_bit_exact(tci):
+    """The synthetic full-rank benchmark functor: integer hash, so GPU and oracle agree bit for bit."""
+    ld = [5, 4, 3, 6, 2]
+    f, g = tci.HashFunction(ld, 0.75, 1.5), O.Func(O.F_HASH, [0.75, 1.5])
+    rng = np.random.default_rng(3)
+    left = [[int(rng.integers(1, ld[0] + 1)), int(rng.integers(1, ld[1] + 1))] for _ in range(7)]
+    right = [[int(rng.integers(1, ld[3] + 1)), int(rng.integers(1, ld[4] + 1))] for _ in range(5)]
+    got = f(left, right, 1)
+    ref = O.batchevaluate(g, ld, left, right, 1)
+    assert got.shape == ref.shape == (7, 3, 5) and np.array_equal(got, ref)
+    assert np.abs(ref).max() <= 0.75 + 1.5 and len(np.unique(ref)) > 50
