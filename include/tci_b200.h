@@ -166,6 +166,24 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
 int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb, const double* d_P, int64_t r, int64_t ldp,
                         double* d_X, int64_t ldx);
 
+/* ---- K4c support: strided tensor copies, element-wise maps, permutation scatters ---------------------------
+ * tci_strided_copy_f64: out (dense column-major, extents h_shape[0..ndim), first index fastest) <- the view of d_in
+ *   that starts at element in_offset and has element stride h_in_strides[k] along output dimension k (ndim <= 8).
+ *   Replaces `permutedims` and slicing around the GEMMs of the contraction code (src/contraction.jl:211-212, :256-258,
+ *   :541-556, :595, :770).
+ * tci_elementwise_f64: x <- g(x) in place; kind 1: p0*x + p1, 2: x^2 (abs2), 3: |x|, 4: exp(p0*x).  Replaces the
+ *   `res .= obj.f.(res)` of Contraction.batchevaluate (src/contraction.jl:569-571) for the maps the tests use.
+ * tci_unpermute_f64: out[perm[i], :] = in[i, :] (by_rows != 0) or out[:, perm[j]] = in[:, j]; h_perm 1-based.
+ *   Replaces left(lu; permute=true) / right(lu; permute=true) (src/matrixlu.jl:716-746). */
+int tci_strided_copy_f64(tci_handle h, const double* d_in, int64_t in_offset, const int64_t* h_shape, const int64_t* h_in_strides,
+                         int ndim, double* d_out);
+int tci_elementwise_f64(tci_handle h, int kind, double p0, double p1, double* d_x, int64_t n);
+int tci_unpermute_f64(tci_handle h, const double* d_in, int64_t ldi, double* d_out, int64_t ldo, const int64_t* h_perm,
+                      int64_t rows, int64_t cols, int by_rows);
+/* updatemaxsample! (src/tensorci2.jl:636-638, util.jl:34-43) for a Pi matrix that was not produced by tci_batcheval_f64:
+ * *h_maxabs = max(|*h_maxabs|, max |x|), NaN-propagating; x is rows x cols with leading dimension ld. */
+int tci_maxabs_f64(tci_handle h, const double* d_x, int64_t rows, int64_t cols, int64_t ld, double* h_maxabs);
+
 /* ---- K4b: TensorTrain sum / evaluate on device-resident cores ---------------------------------------
  * A core is the column-major (chi_l, d, chi_r) array of the reference (d = product of the site legs), i.e. a
  * (chi_l*d) x chi_r matrix; h_core_ptrs[b] is its DEVICE pointer, h_shapes[3b..3b+2] = (chi_l, d, chi_r),

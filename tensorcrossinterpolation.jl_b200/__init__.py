@@ -12,7 +12,9 @@ from .matrixluci import MatrixLUCI                                              
 from .batcheval import (BatchEvaluator, BuiltinFunction, LorentzFunction, SumFunction, QuanticsExpSin,          # noqa: F401
                         QuanticsExpPlusSin, QuanticsExp2, DenseFunction, HashFunction, UserFunction, filltensor,
                         _batchevaluate_dispatch, to_numpy)
-from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain                       # noqa: F401
+from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain, compress, _factorize                       # noqa: F401
 from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecriterion, kronecker_left,      # noqa: F401
                         kronecker_right, DefaultGlobalPivotFinder, GlobalPivotSearchInput, forwardsweep,
                         HostFunctionAdapter, makebatchevaluatable, optfirstpivot)
+from .tensor import DTensor, _contract                                                                  # noqa: F401
+from .contraction import (Contraction, ElementwiseMap, contract, contract_naive, contract_zipup, contract_TCI)   # noqa: F401

@@ -69,6 +69,12 @@ class BatchEvaluator:
                                         C.c_int64(stride_c), C.c_int64(stride_j), C.byref(mx) if maxabs is not None else None))
         return out, (mx.value if maxabs is not None else None)
 
+    def evaluate_points(self, pts):
+        """f at arbitrary full-length multi-indices (npoints x N) in ONE K1 call: the points are the left set, the right
+        set is the single empty multi-index.  Returns a numpy vector."""
+        t, _ = self.evaluate_batch(np.ascontiguousarray(pts, dtype=np.int32), np.zeros((1, 0), dtype=np.int32), 0)
+        return t.reshape(-1).cpu().numpy()
+
     def __call__(self, *args):
         if len(args) == 1:                                                          # point form f(indexset)
             idx = [int(v) for v in args[0]]

@@ -449,10 +449,7 @@ class DefaultGlobalPivotFinder:
 
 
 def _point_values(f, pts):
-    """f at arbitrary points in ONE K1 call: the points are the left set (length N), the right set is the single
-    empty multi-index."""
-    t, _ = f.evaluate_batch(np.ascontiguousarray(pts, dtype=np.int32), np.zeros((1, 0), dtype=np.int32), 0)
-    return t.reshape(-1).cpu().numpy()
+    return f.evaluate_points(pts)
 
 
 def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, maxiter=20, sweepstrategy="backandforth",

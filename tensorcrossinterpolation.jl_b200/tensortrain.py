@@ -134,6 +134,9 @@ class TensorTrain(AbstractTensorTrain):
     def _dev_cores(self):
         return self._cores
 
+    def compress(self, method="LU", tolerance=1e-12, maxbonddim=None, normalizeerror=True):   # compress! tensortrain.jl:302
+        return compress(self, method, tolerance, maxbonddim, normalizeerror)
+
     def fulltensor(self):                                  # tensortrain.jl:580-600 (small trains only; host reshape)
         from .dense import gemm
         h = self.handle
@@ -153,3 +156,78 @@ class TensorTrain(AbstractTensorTrain):
 
 def tensortrain(tci):                                      # tensortrain.jl:187-189
     return TensorTrain(tci)
+
+
+# ---- factorisation / compression (tensortrain.jl:219-348) -------------------------------------------------------------
+def _unpermute(h, M, perm, by_rows):
+    """left(lu; permute=true) / right(lu; permute=true) (matrixlu.jl:716-746) on the device."""
+    out = Mat.empty(M.rows, M.cols, M.buf.device)
+    pm = np.ascontiguousarray(perm, dtype=np.int64)
+    h.check(lib().tci_unpermute_f64(h.h, M.ptr, C.c_int64(M.ld), out.ptr, C.c_int64(out.ld), p_i64(pm), C.c_int64(M.rows),
+                                    C.c_int64(M.cols), 1 if by_rows else 0))
+    return out
+
+
+def _factorize(A, method, tolerance, maxbonddim, leftorthogonal=False, normalizeerror=True, handle=None):
+    """_factorize(A, method; tolerance, maxbonddim, leftorthogonal, normalizeerror) — tensortrain.jl:219-272.
+    A: device `Mat` (consumed).  Returns (left Mat m x r, right Mat r x n, r).  method 'LU' or 'CI'; 'SVD' (LAPACK gesdd in
+    the reference) is outside this build's scope."""
+    from .matrixlu import INT_MAX, rrlu_device
+    from .matrixluci import MatrixLUCI
+    h = handle or _lib.default_handle()
+    reltol, abstol = 1e-14, 0.0
+    if normalizeerror:
+        reltol = tolerance
+    else:
+        abstol = tolerance
+    maxrank = INT_MAX if maxbonddim is None else maxbonddim
+    if method == "LU":
+        lu = rrlu_device(A, maxrank=maxrank, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal, handle=h)
+        r = lu.npivot
+        return _unpermute(h, lu.Lmat, lu.rowpermutation, True), _unpermute(h, lu.Umat, lu.colpermutation, False), r
+    if method == "CI":
+        luci = MatrixLUCI(A, maxrank=maxrank, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal, handle=h)
+        return luci.left_mat(), luci.right_mat(), luci.npivots()
+    if method == "SVD":
+        raise TCIError(_lib.TCI_ERR_INVALID, "method=:SVD is not implemented in this build (no GPU SVD on the TCI2 hot path); use :LU or :CI")
+    raise TCIError(_lib.TCI_ERR_INVALID, "Not implemented yet.")
+
+
+def _dense_copy(h, M):
+    """Mat with ld == rows (a fresh copy if the source is padded) so that it can be re-viewed with another 2-D shape."""
+    if M.ld == M.rows or M.cols <= 1:
+        return M
+    out = Mat.empty(M.rows, M.cols, M.buf.device)
+    out.buf.copy_(M.buf[: M.cols, : M.rows])
+    return out
+
+
+def compress(tt, method="LU", tolerance=1e-12, maxbonddim=None, normalizeerror=True):
+    """compress!(tt, method; tolerance, maxbonddim, normalizeerror) — tensortrain.jl:302-348 (in place)."""
+    from .dense import gemm
+    h = tt.handle
+    cores = tt._cores
+    n = len(cores)
+    for ell in range(n - 1):                               # left-to-right, no truncation
+        c = cores[ell]
+        A = _dense_copy(h, c.mat)
+        A = Mat(A.buf.clone(), A.rows, A.cols) if A is c.mat else A
+        left, right, r = _factorize(A, method, 0.0, None, leftorthogonal=True, handle=h)
+        cores[ell] = DeviceCore(left, c.chil, c.sitedims, r)
+        nx = cores[ell + 1]
+        nm = _dense_copy(h, nx.mat)
+        nxt = Mat(nm.buf.reshape(-1)[: nx.chil * nx.d * nx.chir].reshape(nx.d * nx.chir, nx.chil), nx.chil, nx.d * nx.chir)
+        prod = gemm(h, right, nxt)                         # (r x chil) * (chil x d*chir)
+        cores[ell + 1] = DeviceCore(Mat(prod.buf.reshape(-1)[: r * nx.d * nx.chir].reshape(nx.chir, r * nx.d), r * nx.d, nx.chir),
+                                    r, nx.sitedims, nx.chir)
+    for ell in range(n - 1, 0, -1):                        # right-to-left, truncating
+        c = cores[ell]
+        cm = _dense_copy(h, c.mat)
+        A = Mat(cm.buf.reshape(-1)[: c.chil * c.d * c.chir].clone().reshape(c.d * c.chir, c.chil), c.chil, c.d * c.chir)
+        left, right, r = _factorize(A, method, tolerance, maxbonddim, leftorthogonal=False, normalizeerror=normalizeerror, handle=h)
+        rd = _dense_copy(h, right)
+        cores[ell] = DeviceCore(Mat(rd.buf.reshape(-1)[: r * c.d * c.chir].reshape(c.chir, r * c.d), r * c.d, c.chir), r, c.sitedims, c.chir)
+        pv = cores[ell - 1]
+        prod = gemm(h, _dense_copy(h, pv.mat), left)       # (chil*d x chir) * (chir x r)
+        cores[ell - 1] = DeviceCore(prod, pv.chil, pv.sitedims, r)
+    return None
