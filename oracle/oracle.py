@@ -228,6 +228,12 @@ class TCI2:
     def __len__(self):
         return len(self.localdims)
 
+    def set_bondorder(self, order):
+        """'sequential' (the reference) or 'oddeven' (the product's parallel-bond schedule restated: all odd bonds, then
+        all even bonds; within one pass the bonds read and write disjoint index sets, so the order inside a pass is
+        immaterial and a concurrent execution gives the same result)."""
+        lib().orc_tci_set_bondorder(self.h, {"sequential": 0, "oddeven": 1}[order])
+
     def optimize(self, tolerance=1e-8, maxbonddim=INT64_MAX, maxiter=20, sweepstrategy="backandforth",
                  normalizeerror=True, ncheckhistory=3, strictlynested=False, checkconvglobalpivot=True):
         ranks = np.zeros(maxiter, dtype=np.int64)
@@ -329,9 +335,10 @@ class TCI2:
         return {"nevals": ne.value, "t_eval": te.value, "t_lu": tl.value}
 
 
-def crossinterpolate2(f, localdims, initialpivots=None, **kw):
+def crossinterpolate2(f, localdims, initialpivots=None, bondorder="sequential", **kw):
     """crossinterpolate2 (tensorci2.jl:1313-1323) with nsearchglobalpivot=0."""
     tci = TCI2(f, localdims, initialpivots)
+    tci.set_bondorder(bondorder)
     ranks, errors = tci.optimize(**kw)
     return tci, ranks, errors
 

@@ -399,6 +399,8 @@ struct TCI2 {
     std::vector<double> pivoterrors, bonderrors;
     double maxsamplevalue = 0.0;
     std::vector<std::vector<IndexList>> Iset_history, Jset_history;
+    int bondorder = 0;                             // 0: sequential bonds (the reference, :1226-1250); 1: odd bonds then even bonds
+                                                   // (the parallel-bond schedule of the product; NOT in the reference)
     int64_t nevals = 0;                            // bookkeeping for the bench only
     double t_eval = 0, t_lu = 0;                   // seconds spent in Pi fill and in MatrixLUCI
 
@@ -614,11 +616,13 @@ int TCI2::sweep2site(const Func& f, int niter, int iter1, double abstol, int64_t
         Iset_history.push_back(Iset); Jset_history.push_back(Jset);               // :1220-1221
         pivoterrors.clear();                                                       // :1223
         const bool fwd = (sweepstrategy == 0) || (sweepstrategy == 1 && (iter % 2 == 1));
-        for (int s = 0; s < N - 1; ++s) {
-            const int b = fwd ? s : N - 2 - s;
-            int st = updatepivots(b, f, fwd, 1e-14, abstol, maxbonddim, extraI[b + 1], extraJ[b]);   // :1227-1249
-            if (st) return st;
-        }
+        for (int pass = 0; pass < (bondorder == 1 ? 2 : 1); ++pass)
+            for (int s = 0; s < N - 1; ++s) {
+                const int b = fwd ? s : N - 2 - s;
+                if (bondorder == 1 && (b % 2) != pass) continue;          // pass 0: bonds 1, 3, 5, ... (1-based); pass 1: 2, 4, ...
+                int st = updatepivots(b, f, fwd, 1e-14, abstol, maxbonddim, extraI[b + 1], extraJ[b]);   // :1227-1249
+                if (st) return st;
+            }
     }
     if (fillsite) fillsitetensors(f);                                              // :1254-1256
     return 0;
@@ -853,6 +857,7 @@ void* orc_tci_create(void* f, const int32_t* localdims, int nsites, const int32_
     } catch (const std::exception& e) { g_err = e.what(); return nullptr; }
 }
 void orc_tci_destroy(void* h) { delete (OrcTCI*)h; }
+void orc_tci_set_bondorder(void* h, int v) { ((OrcTCI*)h)->tci.bondorder = v; }
 
 // optimize!: ranks/errors must hold maxiter entries; *niter receives the number written.
 int orc_tci_optimize(void* h_, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,

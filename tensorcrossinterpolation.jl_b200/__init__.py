@@ -18,3 +18,4 @@ from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecrite
                         HostFunctionAdapter, makebatchevaluatable, optfirstpivot)
 from .tensor import DTensor, _contract                                                                  # noqa: F401
 from .contraction import (Contraction, ElementwiseMap, contract, contract_naive, contract_zipup, contract_TCI)   # noqa: F401
+from .parallel import Comm, ShardedBatchEvaluator, partition, bond_passes                               # noqa: F401

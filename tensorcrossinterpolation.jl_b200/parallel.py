@@ -1,0 +1,219 @@
+"""Multi-GPU layer: one process per GPU, `torch.distributed` (NCCL over NVLink on the box, gloo in the
+CPU tests).  Only what shards naturally is sharded:
+
+  * the function-evaluation batch (the reference's own parallel axis, src/batcheval.jl:300): `ShardedBatchEvaluator`
+    splits the column multi-indices of a Pi matrix over the ranks; with peer-mapped buffers the assembly kernel stores
+    every value straight into all ranks' Pi buffers (compute + all-gather in one kernel, csrc/batcheval.cu); without
+    them the column blocks are exchanged with an all-gather;
+  * the bonds of a half-sweep (NOT in the reference, src/tensorci2.jl:1226-1250 is sequential): `bondorder="oddeven"`
+    updates all odd bonds, then all even bonds; inside one pass the bonds read (Iset[b], Jset[b+1]) and write
+    (Iset[b+1], Jset[b]) disjoint index sets, so they run concurrently on different GPUs and the new pivot sets are
+    exchanged afterwards.  The result is identical to running the same passes on one GPU (and to the oracle's
+    restatement of the schedule), whatever the number of ranks;
+  * `fillsitetensors!` (src/globalsearch.jl:202-208): sites are independent, dealt round-robin, tensors broadcast.
+
+rrLU, `sum`, `evaluate` and zip-up do not shard (replicas only)."""
+import numpy as np
+
+
+def partition(n, parts):
+    """Contiguous, balanced split of range(n) into `parts` blocks: list of (start, stop)."""
+    base, rem = divmod(int(n), int(parts))
+    out, s = [], 0
+    for p in range(parts):
+        e = s + base + (1 if p < rem else 0)
+        out.append((s, e))
+        s = e
+    return out
+
+
+def owner_of(items, size):
+    """Round-robin assignment: item k of the list belongs to rank k % size."""
+    return {it: k % size for k, it in enumerate(items)}
+
+
+class Comm:
+    """Thin wrapper over a torch.distributed process group for the three exchange patterns the path needs."""
+
+    def __init__(self, group=None, device=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.size = dist.get_rank(group), dist.get_world_size(group)
+        self.backend = dist.get_backend(group)
+        if device is None:
+            import torch
+            device = f"cuda:{torch.cuda.current_device()}" if self.backend == "nccl" else "cpu"
+        self.device = device
+
+    # ---- ragged all-gather of a flat numpy vector
+    def _allgather_flat(self, vec, dtype):
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(vec)).to(self.device)
+        n = torch.tensor([t.numel()], dtype=torch.int64, device=self.device)
+        sizes = [torch.zeros(1, dtype=torch.int64, device=self.device) for _ in range(self.size)]
+        self.dist.all_gather(sizes, n, group=self.group)
+        sizes = [int(s.item()) for s in sizes]
+        mx = max(max(sizes), 1)
+        pad = torch.zeros(mx, dtype=dtype, device=self.device)
+        pad[: t.numel()] = t
+        outs = [torch.zeros(mx, dtype=dtype, device=self.device) for _ in range(self.size)]
+        self.dist.all_gather(outs, pad, group=self.group)
+        return [o[:s].cpu().numpy() for o, s in zip(outs, sizes)]
+
+    def allgather_records(self, records):
+        """records: list of (key:int, tables:list of int32 2-D arrays, floats:1-D float64 array) owned by this rank.
+        Returns the union over all ranks as a dict key -> (tables, floats)."""
+        import torch
+        ints, flts = [len(records)], []
+        for key, tabs, fl in records:
+            fl = np.asarray(fl, dtype=np.float64).reshape(-1)
+            ints += [int(key), len(tabs), fl.size]
+            for t in tabs:
+                t = np.asarray(t, dtype=np.int32)
+                ints += [t.shape[0], t.shape[1]]
+                ints += t.reshape(-1).tolist()
+            flts.append(fl)
+        iv = np.asarray(ints, dtype=np.int32)
+        fv = np.concatenate(flts) if flts else np.zeros(0)
+        gi = self._allgather_flat(iv, torch.int32)
+        gf = self._allgather_flat(fv, torch.float64)
+        out = {}
+        for iv, fv in zip(gi, gf):
+            pos, fpos = 1, 0
+            for _ in range(int(iv[0])):
+                key, ntab, nfl = int(iv[pos]), int(iv[pos + 1]), int(iv[pos + 2])
+                pos += 3
+                tabs = []
+                for _ in range(ntab):
+                    r, c = int(iv[pos]), int(iv[pos + 1])
+                    pos += 2
+                    tabs.append(np.asarray(iv[pos:pos + r * c], dtype=np.int32).reshape(r, c))
+                    pos += r * c
+                out[key] = (tabs, np.asarray(fv[fpos:fpos + nfl], dtype=np.float64))
+                fpos += nfl
+        return out
+
+    def allreduce_max(self, x):
+        """NaN-propagating max of one float over the ranks (Julia's max, util.jl:34-43)."""
+        import torch
+        t = torch.tensor([np.inf if np.isnan(x) else float(x), 1.0 if np.isnan(x) else 0.0], dtype=torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return float("nan") if t[1].item() > 0 else float(t[0].item())
+
+    def broadcast(self, tensor, src):
+        self.dist.broadcast(tensor, src=src, group=self.group)
+        return tensor
+
+    def allgather_column_blocks(self, out2d, blocks):
+        """out2d: torch (ncols, ld) matrix storage (column j = row j); every rank has filled rows blocks[rank]; after the
+        call every rank has all rows.  Plain all-gather fallback of the fused peer-store kernel."""
+        import torch
+        mx = max(e - s for s, e in blocks)
+        if mx == 0:
+            return
+        ld = out2d.shape[1]
+        s, e = blocks[self.rank]
+        mine = torch.zeros((mx, ld), dtype=out2d.dtype, device=out2d.device)
+        mine[: e - s] = out2d[s:e]
+        outs = [torch.empty_like(mine) for _ in range(self.size)]
+        self.dist.all_gather(outs, mine, group=self.group)
+        for r, (s2, e2) in enumerate(blocks):
+            if r != self.rank and e2 > s2:
+                out2d[s2:e2] = outs[r][: e2 - s2]
+
+    def barrier(self):
+        self.dist.barrier(group=self.group)
+
+
+def bond_passes(nbonds, forward, bondorder):
+    """Bond visiting order of one half-sweep as a list of passes (lists of 1-based bond numbers).  'sequential' is the
+    reference's single pass (tensorci2.jl:1226-1250); 'oddeven' is two passes whose bonds are mutually independent."""
+    order = list(range(1, nbonds + 1)) if forward else list(range(nbonds, 0, -1))
+    if bondorder == "sequential":
+        return [order]
+    if bondorder == "oddeven":
+        return [[b for b in order if b % 2 == 1], [b for b in order if b % 2 == 0]]
+    raise ValueError(f"Unknown bond order {bondorder}: choose 'sequential' or 'oddeven'.")
+
+
+def run_pass(tci, bonds, update, comm):
+    """One pass of mutually independent bond updates.  `update(b)` runs updatepivots! on bond b and returns its pivot
+    errors; with a communicator the bonds are dealt round-robin over the ranks and the results exchanged."""
+    if comm is None or comm.size == 1:
+        for b in bonds:
+            update(b)
+        return
+    own = owner_of(bonds, comm.size)
+    records = []
+    for b in bonds:
+        if own[b] == comm.rank:
+            errs = update(b)
+            records.append((b, [tci.Iset[b], tci.Jset[b - 1]], np.asarray(errs, dtype=np.float64)))
+    got = comm.allgather_records(records)
+    for b in bonds:
+        if own[b] != comm.rank:
+            tabs, errs = got[b]
+            tci.Iset[b], tci.Jset[b - 1] = tabs[0], tabs[1]
+            tci.updateerrors(b - 1, errs)
+    tci.maxsamplevalue = comm.allreduce_max(tci.maxsamplevalue)
+
+
+from .batcheval import BatchEvaluator          # noqa: E402  (no CUDA needed to import)
+
+
+class ShardedBatchEvaluator(BatchEvaluator):
+    """Wraps a BatchEvaluator: the right (column) index set of every batch is split over the ranks of `comm`; each rank
+    evaluates its column block into the shared-layout output and the blocks are exchanged, so every rank ends up with the
+    whole array (what the replicated rrLU needs).  Exposes the same `evaluate_batch`/call protocol as the wrapped object."""
+
+    def __init__(self, f, comm):
+        import ctypes
+        self.f, self.comm = f, comm                        # (the parent's __init__ would create a device handle)
+        self.localdims = np.asarray(f.localdims, dtype=np.int32)
+        self.handle = getattr(f, "handle", None)
+        self._f = ctypes.c_void_p()
+
+    def __call__(self, *args):
+        if len(args) == 1:
+            return self.f(*args)
+        left, right, M = args
+        from .batcheval import to_numpy
+        t, _ = self.evaluate_batch(left, right, M)
+        return to_numpy(t)
+
+    def evaluate_points(self, pts):
+        return self.f.evaluate_points(pts)
+
+    def evaluate_batch(self, left, right, M, out=None, stride_c=0, stride_j=0, maxabs=None):
+        import torch
+        from .batcheval import as_table
+        lt, rt = as_table(left), as_table(right)
+        nI, nJ = lt.shape[0], rt.shape[0]
+        if nI * nJ == 0 or self.comm.size == 1:
+            return self.f.evaluate_batch(lt, rt, M, out=out, stride_c=stride_c, stride_j=stride_j, maxabs=maxabs)
+        nl = lt.shape[1]
+        cd = [int(d) for d in self.localdims[nl:nl + M]]
+        ncent = int(np.prod(cd)) if cd else 1
+        sc = stride_c if stride_c > 0 else nI
+        sj = stride_j if stride_j > 0 else sc * ncent
+        if out is None:
+            dev = self.comm.device if self.handle is None else f"cuda:{self.handle.device}"
+            out = torch.empty((nJ,) + tuple(reversed(cd)) + (nI,), dtype=torch.float64, device=dev)
+        flat = out.reshape(-1)
+        blocks = partition(nJ, self.comm.size)
+        s, e = blocks[self.comm.rank]
+        mx = maxabs
+        if e > s:
+            sub = flat[s * sj:]                                    # column block s..e starts at element s * stride_j
+            _, mx = self.f.evaluate_batch(lt, rt[s:e], M, out=sub, stride_c=sc, stride_j=sj, maxabs=maxabs)
+        rows = torch.as_strided(flat, (nJ, sj), (sj, 1)) if flat.numel() >= nJ * sj else None
+        if rows is None:                                           # last column shorter than stride_j: gather on a padded copy
+            pad = torch.zeros(nJ * sj, dtype=flat.dtype, device=flat.device)
+            pad[: flat.numel()] = flat
+            self.comm.allgather_column_blocks(pad.reshape(nJ, sj), blocks)
+            flat.copy_(pad[: flat.numel()])
+        else:
+            self.comm.allgather_column_blocks(rows, blocks)
+        if maxabs is not None:
+            mx = self.comm.allreduce_max(mx)
+        return out, mx

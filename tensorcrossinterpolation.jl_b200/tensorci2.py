@@ -275,8 +275,10 @@ class TensorCI2(AbstractTensorTrain):
             self._set_core(b0, luci.left_mat())
             self._set_core(b0 + 1, luci.right_mat())
             self.stats["t_factors"] += time.perf_counter() - t0
-        self.updateerrors(b0, luci.pivoterrors())
+        errs = luci.pivoterrors()
+        self.updateerrors(b0, errs)
         self.last_luci = luci
+        return errs
 
     def setsitetensor(self, f, b, leftorthogonal=True):
         """setsitetensor!(tci, f, b) (tensorci2.jl:599-629)."""
@@ -298,9 +300,29 @@ class TensorCI2(AbstractTensorTrain):
         self.stats["t_factors"] += time.perf_counter() - t0
         self._T[b0] = DeviceCore(T, nI, (d,), nI1)
 
-    def fillsitetensors(self, f):                           # globalsearch.jl:202-208
-        for b in range(1, len(self) + 1):
-            self.setsitetensor(f, b)
+    def fillsitetensors(self, f, comm=None):               # globalsearch.jl:202-208
+        n = len(self)
+        if comm is None or comm.size == 1:
+            for b in range(1, n + 1):
+                self.setsitetensor(f, b)
+            return
+        # sites are independent (each reads only the index sets): deal them over the ranks, broadcast the tensors
+        import torch
+        for b in range(1, n + 1):
+            if (b - 1) % comm.size == comm.rank:
+                self.setsitetensor(f, b)
+        for b0 in range(n):
+            chil, d, chir = self.Iset[b0].shape[0], self.localdims[b0], self.Jset[b0].shape[0]
+            src = b0 % comm.size
+            if src == comm.rank:
+                m = self._T[b0].mat
+                dense = m.buf[: m.cols, : m.rows].contiguous()
+            else:
+                dense = torch.empty((chir, chil * d), dtype=torch.float64, device=self.device)
+            comm.broadcast(dense, src)
+            if src != comm.rank:
+                self._T[b0] = DeviceCore(Mat(dense, chil * d, chir), chil, (d,), chir)
+        self.maxsamplevalue = comm.allreduce_max(self.maxsamplevalue)
 
     def sweep1site(self, f, sweepdirection="forward", reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX, updatetensors=True):
         """sweep1site! (tensorci2.jl:659-725)."""
@@ -349,9 +371,14 @@ class TensorCI2(AbstractTensorTrain):
         self.makecanonical(f, reltol=reltol, abstol=abstol, maxbonddim=maxbonddim)
 
     def sweep2site(self, f, niter, iter1=1, abstol=1e-8, maxbonddim=INT_MAX, sweepstrategy="backandforth",
-                   pivotsearch="full", verbosity=0, strictlynested=False, fillsitetensors=True):
-        """sweep2site! (tensorci2.jl:1195-1258)."""
+                   pivotsearch="full", verbosity=0, strictlynested=False, fillsitetensors=True, bondorder="sequential",
+                   comm=None):
+        """sweep2site! (tensorci2.jl:1195-1258).  bondorder='oddeven' (+ optional `comm`) is the parallel-bond variant
+        (parallel.py); the default is the reference's sequential order."""
+        from .parallel import bond_passes, run_pass
         f = makebatchevaluatable(f, self.localdims, self.handle)
+        if comm is not None and comm.size > 1 and bondorder != "oddeven":
+            raise TCIError(_lib.TCI_ERR_INVALID, "bonds can only be spread over ranks with bondorder='oddeven'")
         self.invalidatesitetensors()
         n = len(self)
         for it in range(iter1, iter1 + niter):
@@ -363,12 +390,16 @@ class TensorCI2(AbstractTensorTrain):
             self.Jset_history.append([s.copy() for s in self.Jset])
             self.flushpivoterror()
             fwd = forwardsweep(sweepstrategy, it)
-            for b in (range(1, n) if fwd else range(n - 1, 0, -1)):
-                self.updatepivots(b, f, fwd, abstol=abstol, maxbonddim=maxbonddim,
-                                  sweepdirection="forward" if fwd else "backward", pivotsearch=pivotsearch,
-                                  verbosity=verbosity, extraIset=extraI[b], extraJset=extraJ[b - 1])
+
+            def update(b):
+                return self.updatepivots(b, f, fwd, abstol=abstol, maxbonddim=maxbonddim,
+                                         sweepdirection="forward" if fwd else "backward", pivotsearch=pivotsearch,
+                                         verbosity=verbosity, extraIset=extraI[b], extraJset=extraJ[b - 1])
+
+            for bonds in bond_passes(n - 1, fwd, bondorder):
+                run_pass(self, bonds, update, comm)
         if fillsitetensors:
-            self.fillsitetensors(f)
+            self.fillsitetensors(f, comm)
 
 
 def reconstractglobalpivotsfromijset(localdims, Isets, Jsets):     # tensorci2.jl:303-320
@@ -455,7 +486,7 @@ def _point_values(f, pts):
 def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, maxiter=20, sweepstrategy="backandforth",
              pivotsearch="full", verbosity=0, loginterval=10, normalizeerror=True, ncheckhistory=3, globalpivotfinder=None,
              maxnglobalpivot=5, nsearchglobalpivot=5, tolmarginglobalsearch=10.0, strictlynested=False,
-             checkbatchevaluatable=False, checkconvglobalpivot=True, rng=None):
+             checkbatchevaluatable=False, checkconvglobalpivot=True, rng=None, bondorder="sequential", comm=None):
     """optimize! (tensorci2.jl:1018-1172).  Returns (ranks, errors ./ errornormalization)."""
     import warnings
     errors, ranks, nglobalpivots = [], [], []
@@ -487,7 +518,8 @@ def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, ma
         if verbosity > 1:
             print(f"  Walltime {time.perf_counter() - tstart} sec: starting 2site sweep")
         tci.sweep2site(f, 2, iter1=1, abstol=abstol, maxbonddim=maxbonddim, pivotsearch=pivotsearch,
-                       strictlynested=strictlynested, verbosity=verbosity, sweepstrategy=sweepstrategy, fillsitetensors=True)
+                       strictlynested=strictlynested, verbosity=verbosity, sweepstrategy=sweepstrategy, fillsitetensors=True,
+                       bondorder=bondorder, comm=comm)
         errors.append(tci.pivoterror())
         globalpivots = finder(GlobalPivotSearchInput(tci), f, abstol, verbosity=verbosity, rng=rng) \
             if getattr(finder, "nsearch", 1) != 0 else []

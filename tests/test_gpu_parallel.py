@@ -1,0 +1,91 @@
+"""Parallel-bond sweep (bondorder='oddeven') and the sharded function-evaluation batch on the GPU.
+
+Single GPU: the odd/even schedule must reproduce the oracle's restatement of the same schedule bit for bit.
+Two or more GPUs (skipped otherwise): one process per GPU over NCCL must give exactly the single-process result."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def tci():
+    import tci_b200
+    return tci_b200
+
+
+@pytest.mark.parametrize("n,d,tol", [(6, 10, 1e-8), (7, 4, 1e-10)])
+def test_oddeven_matches_oracle(tci, n, d, tol):
+    f = tci.LorentzFunction([d] * n)
+    t, ranks, errors = tci.crossinterpolate2(f, [d] * n, tolerance=tol, nsearchglobalpivot=0, bondorder="oddeven")
+    o, oranks, oerrors = O.crossinterpolate2(O.Func(O.F_LORENTZ, [1.0]), [d] * n, tolerance=tol, bondorder="oddeven")
+    assert list(ranks) == list(oranks)
+    assert np.allclose(errors, oerrors, rtol=1e-10, atol=0)
+    for b in range(n):
+        assert np.array_equal(t.Iset[b], o.Iset(b + 1)) and np.array_equal(t.Jset[b], o.Jset(b + 1))
+    seq, sranks, _ = tci.crossinterpolate2(f, [d] * n, tolerance=tol, nsearchglobalpivot=0)
+    rng = np.random.default_rng(0)
+    pts = rng.integers(1, d + 1, size=(200, n))
+    assert np.max(np.abs(t.evaluate_batch(pts) - seq.evaluate_batch(pts))) < 50 * tol     # same tolerance envelope
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{rank}"))
+    try:
+        import tci_b200 as T
+        h = T.Handle(rank)
+        comm = T.Comm()
+        n, d = 7, 6
+        f = T.LorentzFunction([d] * n, handle=h)
+        t, ranks, errors = T.crossinterpolate2(f, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, bondorder="oddeven", comm=comm, handle=h)
+        sf = T.ShardedBatchEvaluator(f, comm)
+        t2, ranks2, errors2 = T.crossinterpolate2(sf, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, handle=h)   # sharded K1, sequential bonds
+        rng = np.random.default_rng(0)
+        pts = rng.integers(1, d + 1, size=(50, n))
+        q.put((rank, {"ranks": [int(r) for r in ranks], "errors": [float(e) for e in errors],
+                      "I": [s.tolist() for s in t.Iset], "J": [s.tolist() for s in t.Jset], "vals": t.evaluate_batch(pts).tolist(),
+                      "ranks2": [int(r) for r in ranks2], "I2": [s.tolist() for s in t2.Iset], "vals2": t2.evaluate_batch(pts).tolist()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_multi_gpu_matches_single_process(tci):
+    import torch
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs at least 2 GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = dict(q.get(timeout=600) for _ in range(world))
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    n, d = 7, 6
+    o, oranks, oerrors = O.crossinterpolate2(O.Func(O.F_LORENTZ, [1.0]), [d] * n, tolerance=1e-9, bondorder="oddeven")
+    s, sranks, serrors = O.crossinterpolate2(O.Func(O.F_LORENTZ, [1.0]), [d] * n, tolerance=1e-9)
+    for r in range(world):
+        res = out[r]
+        assert res["ranks"] == list(oranks) and np.allclose(res["errors"], oerrors, rtol=1e-10)
+        for b in range(n):
+            tab = lambda rows, ln: np.asarray(rows, dtype=np.int32).reshape(len(rows), ln)
+            assert np.array_equal(tab(res["I"][b], b), o.Iset(b + 1))
+            assert np.array_equal(tab(res["J"][b], n - b - 1), o.Jset(b + 1))
+            assert np.array_equal(tab(res["I2"][b], b), s.Iset(b + 1))
+        assert res["ranks2"] == list(sranks)
+        assert res["vals"] == out[0]["vals"] and res["vals2"] == out[0]["vals2"]      # replicas agree bit for bit
