@@ -135,6 +135,19 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
                       const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
                       double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs);
 
+/* Sharded batch: the same evaluation, but every value is stored to `nouts` (1..8) destination buffers —
+ * h_d_outs[0] is this GPU's buffer, the others are the peers' buffers mapped into this process (tci_ipc_open): the
+ * assembly kernel IS the all-gather (peer stores over NVLink), there is no separate exchange pass.  The caller passes its
+ * own block of the right index set and destination pointers already offset to that block's first column. */
+int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                            const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                            double* const* h_d_outs, int nouts, int64_t stride_c, int64_t stride_j, double* h_maxabs);
+/* CUDA IPC plumbing for those buffers (memory from tci_malloc): a 64-byte handle to send to the peer processes, and the
+ * peer side's open/close. */
+int tci_ipc_export(tci_handle h, void* d_ptr, void* h_handle64);
+int tci_ipc_open(tci_handle h, const void* h_handle64, void** d_ptr);
+int tci_ipc_close(tci_handle h, void* d_ptr);
+
 /* ---- K4a: FP64 dense algebra for site tensors (FP64 tensor pipe, DMMA) ------------------------------
  * tci_gemm_f64: C = alpha * A * B + beta * C, batched.  Element strides make transposes/reshaped views free:
  *   A(m,k) = d_A[m*sam + k*sak + z*bsa], B(k,n) = d_B[k*sbk + n*sbn + z*bsb], C(m,n) = d_C[m*scm + n*scn + z*bsc].

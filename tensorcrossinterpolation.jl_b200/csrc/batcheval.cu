@@ -46,6 +46,9 @@ struct EvalShape {
     int cdims[8];                        // centre local dims (ncent_sites <= 8)
     long long nleft, nright, ncent;      // counts
     long long stride_c, stride_j;        // output strides (stride of i is 1)
+    int nouts;                           // number of destination buffers (1 = local only)
+    double* outs[8];                     // destinations: this GPU's buffer and, for a sharded batch, the peers' buffers
+                                         // (peer-mapped through NVLink): the assembly IS the all-gather
 };
 
 // ---- built-in monoid functors ---------------------------------------------------------------------
@@ -141,7 +144,7 @@ __device__ __forceinline__ void maxabs_commit(double v, bool isn, unsigned long 
 template <class F>
 __global__ void __launch_bounds__(256)
 assemble_kernel(F f, EvalShape sh, int nsites, const typename F::State* __restrict__ Ls,
-                const typename F::State* __restrict__ Rs, double* __restrict__ out,
+                const typename F::State* __restrict__ Rs,
                 unsigned long long* maxbits, int* nanflag) {
     // grid: x over i (fastest), y over (c, j) pairs in chunks
     const long long ncj = sh.ncent * sh.nright;
@@ -151,10 +154,11 @@ assemble_kernel(F f, EvalShape sh, int nsites, const typename F::State* __restri
         typename F::State cs = Rs[j];
         long long rem = c;
         for (int x = 0; x < sh.ncent_sites; ++x) { f.push(cs, sh.nl + x, (int)(rem % sh.cdims[x]) + 1); rem /= sh.cdims[x]; }
-        double* col = out + c * sh.stride_c + j * sh.stride_j;
+        const long long coff = c * sh.stride_c + j * sh.stride_j;
         for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < sh.nleft; i += (long long)gridDim.x * blockDim.x) {
             const double v = f.finish(f.merge(Ls[i], cs));
-            col[i] = v;
+            sh.outs[0][coff + i] = v;
+            for (int p = 1; p < sh.nouts; ++p) sh.outs[p][coff + i] = v;       // peer stores (coalesced 256 B per warp)
             const double a = fabs(v);
             if (a != a) isn = true; else mx = a > mx ? a : mx;
         }
@@ -170,7 +174,9 @@ tci_user_assemble(const int* __restrict__ left, const int* __restrict__ right, i
                   int cd0, int cd1, int cd2, int cd3, int cd4, int cd5, int cd6, int cd7,
                   long long nleft, long long nright, long long ncent, long long stride_c, long long stride_j,
                   const double* __restrict__ params, int nparams, double* __restrict__ out,
+                  double* o1, double* o2, double* o3, double* o4, double* o5, double* o6, double* o7, int nouts,
                   unsigned long long* maxbits, int* nanflag) {
+    double* peers[7] = {o1, o2, o3, o4, o5, o6, o7};
     int cdims[8] = {cd0, cd1, cd2, cd3, cd4, cd5, cd6, cd7};
     int idx[TCI_MAX_SITES];
     const int n = nl + ncs + nr;
@@ -183,7 +189,9 @@ tci_user_assemble(const int* __restrict__ left, const int* __restrict__ right, i
         for (int x = 0; x < ncs; ++x) { idx[nl + x] = (int)(rem % cdims[x]) + 1; rem /= cdims[x]; }
         for (int p = 0; p < nr; ++p) idx[nl + ncs + p] = right[j * nr + p];
         const double v = tci_user_f(idx, n, params, nparams);
-        out[i + c * stride_c + j * stride_j] = v;
+        const long long off = i + c * stride_c + j * stride_j;
+        out[off] = v;
+        for (int p = 1; p < nouts; ++p) peers[p - 1][off] = v;
         const double a = fabs(v);
         if (a != a) isn = true; else mx = a > mx ? a : mx;
     }
@@ -225,7 +233,7 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
 }
 
 template <class F>
-int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const EvalBuffers& b, double* d_out) {
+int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const EvalBuffers& b) {
     typedef typename F::State S;
     const long long nfold = sh.nleft + sh.nright;
     fold_kernel<F><<<(unsigned)((nfold + 255) / 256), 256, 0, h->stream>>>(f, b.d_left, b.d_right, sh, nsites, (S*)b.Ls, (S*)b.Rs);
@@ -236,19 +244,23 @@ int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const
     const long long want = (long long)h->num_sms * 16 / gx + 1;
     if (gy > want) gy = want;
     if (gy > 65535) gy = 65535;
-    assemble_kernel<F><<<dim3((unsigned)gx, (unsigned)gy), 256, 0, h->stream>>>(f, sh, nsites, (const S*)b.Ls, (const S*)b.Rs, d_out, b.maxbits, b.nanflag);
+    assemble_kernel<F><<<dim3((unsigned)gx, (unsigned)gy), 256, 0, h->stream>>>(f, sh, nsites, (const S*)b.Ls, (const S*)b.Rs, b.maxbits, b.nanflag);
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;
 }
 
-int run_user(tci_handle h, tci_functor f, const EvalShape& sh, const EvalBuffers& b, double* d_out) {
+int run_user(tci_handle h, tci_functor f, const EvalShape& sh, const EvalBuffers& b) {
+    double* d_out = sh.outs[0];
+    double* po[7]; for (int i = 0; i < 7; ++i) po[i] = (i + 1 < sh.nouts) ? sh.outs[i + 1] : nullptr;
+    int nouts = sh.nouts;
     int nl = sh.nl, nr = sh.nr, ncs = sh.ncent_sites, np = f->nparams;
     int cd[8]; for (int i = 0; i < 8; ++i) cd[i] = sh.cdims[i];
     long long nleft = sh.nleft, nright = sh.nright, ncent = sh.ncent, sc = sh.stride_c, sj = sh.stride_j;
     const int* dl = b.d_left; const int* dr = b.d_right; const double* dp = f->d_params;
     unsigned long long* mb = b.maxbits; int* nf = b.nanflag;
     void* args[] = {&dl, &dr, &nl, &nr, &ncs, &cd[0], &cd[1], &cd[2], &cd[3], &cd[4], &cd[5], &cd[6], &cd[7],
-                    &nleft, &nright, &ncent, &sc, &sj, &dp, &np, &d_out, &mb, &nf};
+                    &nleft, &nright, &ncent, &sc, &sj, &dp, &np, &d_out,
+                    &po[0], &po[1], &po[2], &po[3], &po[4], &po[5], &po[6], &nouts, &mb, &nf};
     long long total = nleft * ncent * nright;
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)h->num_sms * 8) blocks = (long long)h->num_sms * 8;
@@ -332,10 +344,13 @@ int tci_functor_destroy(tci_handle h, tci_functor f) {
     return TCI_OK;
 }
 
-int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
-                      const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
-                      double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                            const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                            double* const* h_d_outs, int nouts, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
     if (!h) return TCI_ERR_INVALID;
+    if (nouts < 1 || nouts > 8 || !h_d_outs) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_multi_f64: 1..8 destination buffers");
+    double* d_out = h_d_outs[0];
+    for (int p = 0; p < nouts; ++p) if (!h_d_outs[p] && nleft > 0 && nright > 0) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: NULL buffer");
     if (!f || !h_localdims) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: NULL functor or localdims");
     if (nsites < 1 || nsites > kMaxSites) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_f64: nsites must be in 1..%d", kMaxSites);
     const int ncs = nsites - nl - nr;
@@ -352,18 +367,20 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
     for (int x = 0; x < ncs; ++x) { sh.cdims[x] = h_localdims[nl + x]; sh.ncent *= h_localdims[nl + x]; }
     sh.stride_c = stride_c > 0 ? stride_c : nleft;
     sh.stride_j = stride_j > 0 ? stride_j : sh.stride_c * sh.ncent;
+    sh.nouts = nouts;
+    for (int p = 0; p < 8; ++p) sh.outs[p] = p < nouts ? h_d_outs[p] : nullptr;
     EvalBuffers b;
     int rc = stage_tables(h, h_left, h_right, sh, &b);
     if (rc) return rc;
     switch (f->kind) {
-    case TCI_F_LORENTZ: rc = run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b, d_out); break;
-    case TCI_F_SUM: rc = run_builtin(h, SumF{f->p[0]}, sh, nsites, b, d_out); break;
-    case TCI_F_QEXPSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
-    case TCI_F_QEXPPLUSSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
-    case TCI_F_QEXP2: rc = run_builtin(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b, d_out); break;
-    case TCI_F_HASH: rc = run_builtin(h, HashF{f->p[0], f->p[1]}, sh, nsites, b, d_out); break;
-    case TCI_F_DENSE: rc = run_builtin(h, DenseF{f->d_table, f->d_strides}, sh, nsites, b, d_out); break;
-    case TCI_F_USER: rc = run_user(h, f, sh, b, d_out); break;
+    case TCI_F_LORENTZ: rc = run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b); break;
+    case TCI_F_SUM: rc = run_builtin(h, SumF{f->p[0]}, sh, nsites, b); break;
+    case TCI_F_QEXPSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b); break;
+    case TCI_F_QEXPPLUSSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b); break;
+    case TCI_F_QEXP2: rc = run_builtin(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b); break;
+    case TCI_F_HASH: rc = run_builtin(h, HashF{f->p[0], f->p[1]}, sh, nsites, b); break;
+    case TCI_F_DENSE: rc = run_builtin(h, DenseF{f->d_table, f->d_strides}, sh, nsites, b); break;
+    case TCI_F_USER: rc = run_user(h, f, sh, b); break;
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
     }
     if (rc) return rc;
@@ -378,6 +395,40 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
         const double prev = fabs(*h_maxabs);                                    // util.jl:34-43: max(abs(x), abs(y)), NaN propagates
         if (nf || prev != prev) *h_maxabs = NAN; else *h_maxabs = prev > mx ? prev : mx;
     }
+    return TCI_OK;
+}
+
+int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                      const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                      double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+    double* outs[1] = {d_out};
+    return tci_batcheval_multi_f64(h, f, h_localdims, nsites, h_left, nleft, nl, h_right, nright, nr, outs, 1, stride_c, stride_j, h_maxabs);
+}
+
+// ---- peer-mapped buffers for the sharded batch (CUDA IPC; one process per GPU on one NVSwitch box) --------------------
+int tci_ipc_export(tci_handle h, void* d_ptr, void* h_handle64) {
+    if (!h || !d_ptr || !h_handle64) return TCI_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t mh;
+    TCI_CUDA(h, cudaIpcGetMemHandle(&mh, d_ptr));
+    memcpy(h_handle64, &mh, 64);
+    return TCI_OK;
+}
+
+int tci_ipc_open(tci_handle h, const void* h_handle64, void** d_ptr) {
+    if (!h || !d_ptr || !h_handle64) return TCI_ERR_INVALID;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, h_handle64, 64);
+    TCI_CUDA(h, cudaIpcOpenMemHandle(d_ptr, mh, cudaIpcMemLazyEnablePeerAccess));
+    return TCI_OK;
+}
+
+int tci_ipc_close(tci_handle h, void* d_ptr) {
+    if (!h || !d_ptr) return TCI_ERR_INVALID;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    TCI_CUDA(h, cudaIpcCloseMemHandle(d_ptr));
     return TCI_OK;
 }
 

@@ -161,13 +161,74 @@ def run_pass(tci, bonds, update, comm):
 from .batcheval import BatchEvaluator          # noqa: E402  (no CUDA needed to import)
 
 
+class _RawCuda:
+    """__cuda_array_interface__ carrier so torch can wrap memory that was allocated with tci_malloc."""
+
+    def __init__(self, ptr, nelem):
+        self.__cuda_array_interface__ = {"shape": (int(nelem),), "typestr": "<f8", "data": (int(ptr), False), "version": 3}
+
+
+class PeerBuffers:
+    """`nslots` equal slots of FP64 storage on every rank, allocated with tci_malloc and mapped into every peer process
+    with CUDA IPC (tci_ipc_export / tci_ipc_open): ptrs[r] is rank r's buffer as seen from this process."""
+
+    def __init__(self, handle, comm, slot_elems, nslots=3):
+        import ctypes as C
+        import torch
+        from ._lib import lib
+        self.handle, self.comm, self.slot_elems, self.nslots = handle, comm, int(slot_elems), nslots
+        nbytes = 8 * self.slot_elems * nslots
+        own = C.c_void_p()
+        handle.check(lib().tci_malloc(handle.h, C.byref(own), C.c_size_t(nbytes)))
+        self.own = own.value
+        hb = (C.c_ubyte * 64)()
+        handle.check(lib().tci_ipc_export(handle.h, own, hb))
+        mine = torch.tensor(list(hb), dtype=torch.uint8).to(comm.device)
+        alls = [torch.zeros(64, dtype=torch.uint8, device=comm.device) for _ in range(comm.size)]
+        comm.dist.all_gather(alls, mine, group=comm.group)
+        self.ptrs = []
+        for r in range(comm.size):
+            if r == comm.rank:
+                self.ptrs.append(self.own)
+                continue
+            raw = (C.c_ubyte * 64)(*alls[r].cpu().tolist())
+            p = C.c_void_p()
+            handle.check(lib().tci_ipc_open(handle.h, raw, C.byref(p)))
+            self.ptrs.append(p.value)
+        self._keep = _RawCuda(self.own, self.slot_elems * nslots)
+        self.tensor = torch.as_tensor(self._keep, device=f"cuda:{handle.device}")
+        self.next_slot = 0
+
+    def take(self, nelem):
+        """Next slot (round-robin) as a flat torch view of `nelem` doubles, plus its element offset in the buffer."""
+        k = self.next_slot
+        self.next_slot = (k + 1) % self.nslots
+        off = k * self.slot_elems
+        return self.tensor[off:off + int(nelem)], off
+
+    def close(self):
+        import ctypes as C
+        from ._lib import lib
+        self.comm.barrier()
+        for r, p in enumerate(self.ptrs):
+            if r != self.comm.rank:
+                lib().tci_ipc_close(self.handle.h, C.c_void_p(p))
+        self.tensor = None
+        lib().tci_free(self.handle.h, C.c_void_p(self.own))
+        self.ptrs = []
+
+
 class ShardedBatchEvaluator(BatchEvaluator):
     """Wraps a BatchEvaluator: the right (column) index set of every batch is split over the ranks of `comm`; each rank
     evaluates its column block into the shared-layout output and the blocks are exchanged, so every rank ends up with the
     whole array (what the replicated rrLU needs).  Exposes the same `evaluate_batch`/call protocol as the wrapped object."""
 
-    def __init__(self, f, comm):
+    def __init__(self, f, comm, fused=False):
+        """fused=True: outputs live in peer-mapped buffers (`alloc_matrix`) and the assembly kernel stores every value
+        into all ranks' buffers (tci_batcheval_multi_f64) — compute and all-gather are one kernel.  fused=False: each rank
+        fills its block and the blocks are all-gathered (NCCL / gloo)."""
         import ctypes
+        self.fused, self.peers = bool(fused), None
         self.f, self.comm = f, comm                        # (the parent's __init__ would create a device handle)
         self.localdims = np.asarray(f.localdims, dtype=np.int32)
         self.handle = getattr(f, "handle", None)
@@ -184,6 +245,42 @@ class ShardedBatchEvaluator(BatchEvaluator):
     def evaluate_points(self, pts):
         return self.f.evaluate_points(pts)
 
+    # ---- fused mode: peer-mapped output storage ------------------------------------------------------------------------
+    def alloc_matrix(self, rows, cols, pad=16):
+        """Pi storage for TensorCI2._fill: a `Mat` in the next peer-mapped slot (three slots: at most two fills are alive
+        at any time — Pi1 and P of setsitetensor! — and a rank can run at most one fill ahead of its peers)."""
+        from .dense import Mat
+        if not self.fused or self.comm.size == 1:
+            return None
+        ld = max((int(rows) + pad - 1) // pad * pad, 1)
+        need = ld * max(int(cols), 1)
+        if self.peers is None or self.peers.slot_elems < need:        # collective: every rank sees the same sizes
+            if self.peers is not None:
+                self.peers.close()
+            self.peers = PeerBuffers(self.handle, self.comm, max(need, 1 << 20))
+        flat, off = self.peers.take(need)
+        m = Mat(flat.reshape(max(int(cols), 1), ld), rows, cols)
+        m.transient, m.peer_offset = True, off
+        return m
+
+    def _fused_batch(self, lt, rt, M, out, sc, sj, maxabs):
+        import ctypes as C
+        from ._lib import lib, p_i32
+        h, comm = self.handle, self.comm
+        off = (out.data_ptr() - self.peers.own) // 8
+        blocks = partition(rt.shape[0], comm.size)
+        s, e = blocks[comm.rank]
+        mx = C.c_double(0.0 if maxabs is None else float(maxabs))
+        if e > s:
+            order = [comm.rank] + [r for r in range(comm.size) if r != comm.rank]
+            outs = (C.c_void_p * comm.size)(*[self.peers.ptrs[r] + 8 * (off + s * sj) for r in order])
+            sub = np.ascontiguousarray(rt[s:e])
+            h.check(lib().tci_batcheval_multi_f64(h.h, self.f._f, p_i32(self.f.localdims), len(self.f.localdims), p_i32(lt),
+                                                  C.c_int64(lt.shape[0]), lt.shape[1], p_i32(sub), C.c_int64(e - s), rt.shape[1],
+                                                  outs, comm.size, C.c_int64(sc), C.c_int64(sj), C.byref(mx)))
+        h.synchronize()                                            # my peer stores are complete ...
+        return comm.allreduce_max(mx.value)                        # ... and so are everyone else's (collective = barrier)
+
     def evaluate_batch(self, left, right, M, out=None, stride_c=0, stride_j=0, maxabs=None):
         import torch
         from .batcheval import as_table
@@ -199,6 +296,10 @@ class ShardedBatchEvaluator(BatchEvaluator):
         if out is None:
             dev = self.comm.device if self.handle is None else f"cuda:{self.handle.device}"
             out = torch.empty((nJ,) + tuple(reversed(cd)) + (nI,), dtype=torch.float64, device=dev)
+        if (self.fused and self.peers is not None and getattr(self.f, "_f", None)
+                and self.peers.own <= out.data_ptr() < self.peers.own + 8 * self.peers.slot_elems * self.peers.nslots):
+            mx = self._fused_batch(lt, rt, M, out, sc, sj, maxabs)
+            return out, (mx if maxabs is not None else None)
         flat = out.reshape(-1)
         blocks = partition(nJ, self.comm.size)
         s, e = blocks[self.comm.rank]

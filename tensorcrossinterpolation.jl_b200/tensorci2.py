@@ -218,7 +218,9 @@ class TensorCI2(AbstractTensorTrain):
         """filltensor (tensorci2.jl:475-497) + updatemaxsample! (:636-638) into a device matrix rows x cols
         (column-major reshape of the (|I|, d..., |J|) array, exactly the reference's `reshape`)."""
         t0 = time.perf_counter()
-        P = Mat.empty(rows, cols, self.device, pad=16)
+        P = f.alloc_matrix(rows, cols, 16) if hasattr(f, "alloc_matrix") else None     # peer-mapped storage (sharded batch)
+        if P is None:
+            P = Mat.empty(rows, cols, self.device, pad=16)
         nI, nJ = I.shape[0], J.shape[0]
         if nI * nJ:
             if M == 0:
@@ -238,6 +240,10 @@ class TensorCI2(AbstractTensorTrain):
         chil, d, chir = self.Iset[b0].shape[0], self.localdims[b0], self.Jset[b0].shape[0]
         if mat.rows * mat.cols != chil * d * chir:
             raise TCIError(_lib.TCI_ERR_INVALID, "setsitetensor!: size mismatch")
+        if getattr(mat, "transient", False):                # lives in a recycled peer-mapped slot: keep a private copy
+            keep = Mat.empty(mat.rows, mat.cols, self.device)
+            keep.buf[: mat.cols, : mat.rows].copy_(mat.buf[: mat.cols, : mat.rows])
+            mat = keep
         if mat.rows != chil * d:                            # r x (d*chi) matrix: same memory, other 2-D view
             if mat.ld != mat.rows:
                 mat = Mat.from_numpy(mat.numpy().reshape(chil * d, chir, order="F"), self.device)

@@ -51,9 +51,13 @@ def _worker(rank, world, port, q):
         t, ranks, errors = T.crossinterpolate2(f, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, bondorder="oddeven", comm=comm, handle=h)
         sf = T.ShardedBatchEvaluator(f, comm)
         t2, ranks2, errors2 = T.crossinterpolate2(sf, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, handle=h)   # sharded K1, sequential bonds
+        ff = T.ShardedBatchEvaluator(f, comm, fused=True)      # peer-store kernel: compute + all-gather in one launch
+        t3, ranks3, errors3 = T.crossinterpolate2(ff, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, handle=h)
+        fused_used = ff.peers is not None
         rng = np.random.default_rng(0)
         pts = rng.integers(1, d + 1, size=(50, n))
-        q.put((rank, {"ranks": [int(r) for r in ranks], "errors": [float(e) for e in errors],
+        q.put((rank, {"ranks3": [int(r) for r in ranks3], "I3": [s.tolist() for s in t3.Iset], "vals3": t3.evaluate_batch(pts).tolist(),
+                      "fused_used": fused_used,"ranks": [int(r) for r in ranks], "errors": [float(e) for e in errors],
                       "I": [s.tolist() for s in t.Iset], "J": [s.tolist() for s in t.Jset], "vals": t.evaluate_batch(pts).tolist(),
                       "ranks2": [int(r) for r in ranks2], "I2": [s.tolist() for s in t2.Iset], "vals2": t2.evaluate_batch(pts).tolist()}))
     finally:
@@ -87,5 +91,6 @@ def test_multi_gpu_matches_single_process(tci):
             assert np.array_equal(tab(res["I"][b], b), o.Iset(b + 1))
             assert np.array_equal(tab(res["J"][b], n - b - 1), o.Jset(b + 1))
             assert np.array_equal(tab(res["I2"][b], b), s.Iset(b + 1))
-        assert res["ranks2"] == list(sranks)
+        assert res["ranks2"] == list(sranks) and res["ranks3"] == list(sranks) and res["fused_used"]
+        assert res["I3"] == res["I2"] and res["vals3"] == res["vals2"]
         assert res["vals"] == out[0]["vals"] and res["vals2"] == out[0]["vals2"]      # replicas agree bit for bit
