@@ -224,6 +224,7 @@ rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const do
                    RrluState* st, Cand* parts, int maxrank, double reltol, double abstol, int start0, int serpentine) {
     __shared__ Cand s_c[kThreads / 32];
     __shared__ int s_last;
+    cudaGridDependencySynchronize();                    // programmatic dependent launch: block start-up overlaps the previous kernel's tail
     if (st->stop) return;
     const int k = st->npivot;
     const int np = UPDATE ? k + 1 : start0;             // pivots in place once this pass is done
@@ -317,6 +318,7 @@ __device__ __forceinline__ void swap_item(int t, double* __restrict__ A, int m, 
 
 __global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long lda, double* __restrict__ ybuf,
                                  RrluState* st, int* rowperm, int* colperm, double* pivvals, int leftorth) {
+    cudaGridDependencySynchronize();
     if (st->stop) return;
     swap_item<false>(blockIdx.x * blockDim.x + threadIdx.x, A, m, n, lda, ybuf, st->npivot, st->pr, st->pc, st->pivval,
                      rowperm, colperm, pivvals, leftorth);
@@ -466,10 +468,23 @@ UpdateCfg update_cfg(tci_handle h, bool vec) {
     return c;
 }
 
+// Launch with programmatic stream serialization (PDL): the kernel may be scheduled while its predecessor drains; both
+// kernels call cudaGridDependencySynchronize() before they read anything the predecessor wrote.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(tci_handle h, void (*kern)(KArgs...), unsigned grid, unsigned block, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = h->rrlu_pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 template <bool UPDATE>
 void launch_update(tci_handle h, bool vec, const UpdateCfg& c, double* A, int m, int n, long long lda, const SmallWs& w,
                    int maxrank, double reltol, double abstol, int start0 = 0) {
-#define TCI_LAUNCH_UPD(V, CC) rrlu_update_kernel<UPDATE, V, CC><<<c.grid, kThreads, 0, h->stream>>>(A, m, n, lda, w.ybuf, w.st, w.parts, maxrank, reltol, abstol, start0, c.serpentine)
+#define TCI_LAUNCH_UPD(V, CC) launch_pdl(h, rrlu_update_kernel<UPDATE, V, CC>, (unsigned)c.grid, (unsigned)kThreads, A, m, n, lda, (const double*)w.ybuf, w.st, w.parts, maxrank, reltol, abstol, start0, c.serpentine)
     if (!vec) TCI_LAUNCH_UPD(false, 8);
     else if (c.cols == 4) TCI_LAUNCH_UPD(true, 4);
     else if (c.cols == 16) TCI_LAUNCH_UPD(true, 16);
@@ -530,6 +545,7 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     bool persistent = (double)m * n * sizeof(double) <= 48e6;
     if (const char* e = getenv("TCI_RRLU_MODE")) persistent = strcmp(e, "persistent") == 0 ? true : (strcmp(e, "steps") == 0 ? false : persistent);
     if (h->rrlu_profile) persistent = false;                // per-launch profiling needs the step kernels
+    if (const char* e = getenv("TCI_RRLU_PDL")) h->rrlu_pdl = atoi(e) ? 1 : 0;
     if (persistent) {
         rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);
         if (rc) return rc;
@@ -557,7 +573,7 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     while (launched < mr) {
         const int nb = (mr - launched < chunk) ? mr - launched : chunk;
         for (int s = 0; s < nb; ++s) {
-            rrlu_swap_kernel<<<swap_blocks, 256, 0, h->stream>>>(d_A, m, n, lda, w->ybuf, w->st, w->rowperm, w->colperm, w->pivvals, leftorth);
+            launch_pdl(h, rrlu_swap_kernel, (unsigned)swap_blocks, 256u, d_A, m, n, lda, w->ybuf, w->st, w->rowperm, w->colperm, w->pivvals, leftorth);
             TCI_LAUNCH_CHECK(h);
             if (h->rrlu_profile) TCI_CUDA(h, cudaEventRecord(h->ev_pool[2 * (launched + s)], h->stream));
             launch_update<true>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
