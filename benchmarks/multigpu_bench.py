@@ -5,7 +5,7 @@
 (a) one Pi fill of the C3 worst-case shape (5120 x 5120, 26.2 M evaluations, 210 MB) with the full-rank hash functor and
     with an arithmetic-heavy NVRTC plugin functor: local (every rank evaluates everything), sharded + NCCL all-gather,
     sharded + fused peer-store kernel.  Device time, max over ranks.
-(b) C3H sweep (full-rank function, localdims=fill(20,10), maxbonddim=256, 1 iteration = 2 half-sweeps): sequential bonds on
+(b) C3H sweep (full-rank function, localdims=fill(20,10), maxbonddim=256, 2 iterations = 4 half-sweeps): sequential bonds on
     every rank (replicas) vs bondorder='oddeven' with the bonds spread over the ranks.  Wall time, max over ranks."""
 import json
 import os
@@ -78,7 +78,7 @@ def main():
                      "fused_nvlink_GBps_per_rank": 8 * nI * nJ * (world - 1) / world / t_fused / 1e9}
 
     f = T.HashFunction(ld, 1.0, 1.0, handle=h)
-    kw = dict(tolerance=1e-10, maxbonddim=256, maxiter=1, nsearchglobalpivot=0, handle=h)
+    kw = dict(tolerance=1e-10, maxbonddim=256, maxiter=2, nsearchglobalpivot=0, handle=h)
 
     def sweep(**extra):
         T.crossinterpolate2(f, ld, **kw, **extra)
