@@ -215,20 +215,15 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
     if (rc) return rc;
     rc = tci_ws_reserve(h, h->ws_b, 16 * (size_t)(sh.nleft + sh.nright) + 256);        // a State is at most 16 bytes
     if (rc) return rc;
-    rc = tci_pinned_reserve(h, ints + 64);
-    if (rc) return rc;
-    int* pin = (int*)h->pinned;
-    if (nli) memcpy(pin, h_left, nli * sizeof(int));
-    if (nri) memcpy(pin + nli, h_right, nri * sizeof(int));
     b->d_left = (int*)h->ws_a.ptr; b->d_right = b->d_left + nli;
     b->maxbits = (unsigned long long*)((char*)h->ws_a.ptr + ints);
     b->nanflag = (int*)(b->maxbits + 1);
     b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + 16 * (size_t)sh.nleft;
     TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
-    if (nli + nri) {
-        TCI_CUDA(h, cudaMemcpyAsync(b->d_left, pin, (nli + nri) * sizeof(int), cudaMemcpyHostToDevice, h->stream));
-        TCI_CUDA(h, cudaStreamSynchronize(h->stream));     // the pinned staging area is reused by the next call
-    }
+    // The index tables are pageable host memory: cudaMemcpyAsync stages them before it returns, so there is no host
+    // synchronisation here and the caller may reuse its arrays immediately.
+    if (nli) TCI_CUDA(h, cudaMemcpyAsync(b->d_left, h_left, nli * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    if (nri) TCI_CUDA(h, cudaMemcpyAsync(b->d_right, h_right, nri * sizeof(int), cudaMemcpyHostToDevice, h->stream));
     return TCI_OK;
 }
 

@@ -29,6 +29,7 @@ struct tci_context {
     size_t pinned_bytes = 0;
     double rrlu_ms[3] = {0, 0, 0};
     int64_t rrlu_steps = 0;
+    int rrlu_smem_optin = 0;                // the single-CTA kernel's > 48 KB dynamic shared memory has been enabled
     int rrlu_pdl = 1;                       // programmatic dependent launch between the step kernels (TCI_RRLU_PDL=0 disables)
     int rrlu_profile = 0;                   // 1: bracket every update-kernel launch with events
     std::vector<cudaEvent_t> ev_pool;

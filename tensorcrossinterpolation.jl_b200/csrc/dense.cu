@@ -229,10 +229,10 @@ __global__ void gather_cols_kernel(double* __restrict__ W, long long ldw, const 
     if (i < q && j < r) W[(long long)j * ldw + i] = src[(long long)perm[j] * lds + i];
 }
 
-int upload_perm(tci_handle h, const int64_t* h_perm, int len, int* d_dst, size_t pinned_off) {
-    int* pin = (int*)((char*)h->pinned + pinned_off);
-    for (int i = 0; i < len; ++i) pin[i] = (int)(h_perm[i] - 1);
-    TCI_CUDA(h, cudaMemcpyAsync(d_dst, pin, sizeof(int) * len, cudaMemcpyHostToDevice, h->stream));
+int upload_perm(tci_handle h, const int64_t* h_perm, int len, int* d_dst, size_t) {
+    std::vector<int> tmp(len);                             // pageable: staged by cudaMemcpyAsync before it returns, no sync needed
+    for (int i = 0; i < len; ++i) tmp[i] = (int)(h_perm[i] - 1);
+    TCI_CUDA(h, cudaMemcpyAsync(d_dst, tmp.data(), sizeof(int) * len, cudaMemcpyHostToDevice, h->stream));
     return TCI_OK;
 }
 
@@ -282,7 +282,6 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
     double* W = (double*)((char*)h->ws_a.ptr + permbytes);
     rc = upload_perm(h, h_rowperm, M, d_rp, 0); if (rc) return rc;
     rc = upload_perm(h, h_colperm, N, d_cp, sizeof(int) * (size_t)M); if (rc) return rc;
-    TCI_CUDA(h, cudaStreamSynchronize(h->stream));       // pinned staging is reused by later calls
     if (d_left) {
         if (leftorthogonal) {                             // colstimespivotinv  matrixluci.jl:194-213
             const int q = M - R;
@@ -347,7 +346,6 @@ int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb,
     rc = tci_pinned_reserve(h, permbytes + 64); if (rc) return rc;
     rc = upload_perm(h, rp.data(), R, d_rp, 0); if (rc) return rc;
     rc = upload_perm(h, cp.data(), R, d_cp, sizeof(int) * (size_t)R); if (rc) return rc;
-    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
     gather_cols_kernel<<<dim3((Q + 255) / 256, R), 256, 0, h->stream>>>(W, Q, d_B, ldb, d_cp, Q, R);
     TCI_LAUNCH_CHECK(h);
     rc = trsm_right(h, Uw, 1, ldw, R, 0, 0, W, 1, Q, Q); if (rc) return rc;      // W <- W U^-1

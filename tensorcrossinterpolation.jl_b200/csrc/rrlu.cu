@@ -324,6 +324,91 @@ __global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long
                      rowperm, colperm, pivvals, leftorth);
 }
 
+// ---- single-CTA variant: the matrix lives in shared memory for the whole factorisation -------------------------------
+// For the Pi matrices of low-rank problems (BASELINE C1/C3/C4: at most a few hundred rows and columns) every pivot step is
+// pure latency.  One CTA of 1024 threads keeps A (<= ~200 KB) in shared memory in the reference's physically swapped
+// layout and runs search -> swaps -> scale -> update with __syncthreads between the phases: ~1-2 us per pivot instead of
+// two kernel launches or two grid barriers.  Same arithmetic (mul_rn/sub_rn, IEEE division) and same tie rule.
+constexpr int kSmemThreads = 1024;
+
+__device__ __forceinline__ Cand block_reduce_1024(Cand c, Cand* smem /* 32 entries */) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        Cand o = cand_shfl_down(c, d);
+        if (cand_better(o, c)) c = o;
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) smem[warp] = c;
+    __syncthreads();
+    c = smem[lane];                                       // every warp reduces the 32 partials redundantly: no broadcast step
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        Cand o;
+        o.x = __shfl_xor_sync(0xffffffffu, c.x, d); o.i = __shfl_xor_sync(0xffffffffu, c.i, d); o.j = __shfl_xor_sync(0xffffffffu, c.j, d);
+        if (cand_better(o, c)) c = o;
+    }
+    __syncthreads();                                      // smem[] may be rewritten by the next reduction
+    return c;                                             // valid in every thread
+}
+
+__global__ void __launch_bounds__(kSmemThreads, 1)
+rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState* st, int* rowperm, int* colperm,
+                 double* pivvals, int maxrank, double reltol, double abstol, int leftorth) {
+    extern __shared__ double S[];                         // m x n, column-major, leading dimension lds (odd: conflict-free rows)
+    __shared__ Cand s_c[32];
+    const int lds = m | 1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int j = warp; j < n; j += 32)
+        for (int i = lane; i < m; i += 32) S[j * lds + i] = A[(long long)j * lda + i];
+    for (int t = tid; t < m; t += kSmemThreads) rowperm[t] = t;
+    for (int t = tid; t < n; t += kSmemThreads) colperm[t] = t;
+    __syncthreads();
+    int np = 0;
+    double maxerror = 0.0, error = nan("");
+    double bv = -INFINITY, bx = 0.0; int bi = -1, bj = -1;
+    for (int j = warp; j < n; j += 32)
+        for (int i = lane; i < m; i += 32) { const double v = S[j * lds + i]; const double q = __dmul_rn(v, v); TCI_CONSIDER(q, v, i, j) }
+    for (;;) {
+        Cand best = block_reduce_1024(Cand{bx, bi, bj}, s_c);
+        if (best.i < 0) { best.i = np; best.j = np; best.x = nan(""); }
+        const double err = fabs(best.x);                                        // :360
+        error = err;
+        if ((err < reltol * maxerror || err < abstol) && np > 0) break;         // :363
+        maxerror = jl_max(maxerror, err);                                       // :367
+        const int k = np, pr = best.i, pc = best.j;
+        const double piv = best.x;
+        // swaprow!(k, pr) over all columns, then swapcol!(k, pc) over all rows (:254-275, :297-298)
+        if (pr != k) for (int j = tid; j < n; j += kSmemThreads) { const double a = S[j * lds + k]; S[j * lds + k] = S[j * lds + pr]; S[j * lds + pr] = a; }
+        __syncthreads();
+        if (pc != k) for (int i = tid; i < m; i += kSmemThreads) { const double a = S[k * lds + i]; S[k * lds + i] = S[pc * lds + i]; S[pc * lds + i] = a; }
+        if (tid == 0) {
+            int t = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = t;
+            t = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = t;
+            pivvals[k] = piv;
+        }
+        __syncthreads();
+        if (leftorth) { for (int i = k + 1 + tid; i < m; i += kSmemThreads) S[k * lds + i] = S[k * lds + i] / piv; }      // :303-305
+        else          { for (int j = k + 1 + tid; j < n; j += kSmemThreads) S[j * lds + k] = S[j * lds + k] / piv; }      // :307-309
+        __syncthreads();
+        np = k + 1;
+        if (np >= maxrank) break;                                               // :356
+        bv = -INFINITY; bx = 0.0; bi = -1; bj = -1;
+        for (int j = np + warp; j < n; j += 32) {                               // :316-320 + the next search
+            const double y = S[j * lds + k];
+            for (int i = np + lane; i < m; i += 32) {
+                const double v = __dsub_rn(S[j * lds + i], __dmul_rn(S[k * lds + i], y));
+                S[j * lds + i] = v;
+                const double q = __dmul_rn(v, v);
+                TCI_CONSIDER(q, v, i, j)
+            }
+        }
+    }
+    __syncthreads();
+    for (int j = warp; j < n; j += 32)
+        for (int i = lane; i < m; i += 32) A[(long long)j * lda + i] = S[j * lds + i];
+    if (tid == 0) { st->npivot = np; st->stop = 1; st->error = error; st->maxerror = maxerror; }
+}
+
 // ---- persistent variant: the whole loop of _optimizerrlu! (:346-369) in ONE cooperative launch ---------------------
 // Per pivot step: [every block reduces the per-block candidates and evaluates the stop rule redundantly] ->
 // swap/scale phase spread over the grid -> grid barrier -> update + next search -> grid barrier.  No launch gaps,
@@ -546,9 +631,21 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     if (const char* e = getenv("TCI_RRLU_MODE")) persistent = strcmp(e, "persistent") == 0 ? true : (strcmp(e, "steps") == 0 ? false : persistent);
     if (h->rrlu_profile) persistent = false;                // per-launch profiling needs the step kernels
     if (const char* e = getenv("TCI_RRLU_PDL")) h->rrlu_pdl = atoi(e) ? 1 : 0;
+    const size_t smem_need = sizeof(double) * (size_t)(m | 1) * n;
+    bool in_smem = persistent && smem_need <= 200 * 1024;
+    if (const char* e = getenv("TCI_RRLU_SMEM")) in_smem = in_smem && atoi(e) != 0;
     if (persistent) {
-        rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);
-        if (rc) return rc;
+        if (in_smem) {
+            if (smem_need > 48 * 1024 && !h->rrlu_smem_optin) {
+                TCI_CUDA(h, cudaFuncSetAttribute(rrlu_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                h->rrlu_smem_optin = 1;
+            }
+            rrlu_smem_kernel<<<1, kSmemThreads, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
+            TCI_LAUNCH_CHECK(h);
+        } else {
+            rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);
+            if (rc) return rc;
+        }
         TCI_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
         TCI_CUDA(h, cudaMemcpyAsync(hst, w->st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
         TCI_CUDA(h, cudaStreamSynchronize(h->stream));

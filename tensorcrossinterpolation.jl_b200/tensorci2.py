@@ -35,20 +35,23 @@ def _keys(tab):
     return [r.tobytes() for r in np.ascontiguousarray(tab, dtype=np.int32)]
 
 
+def _first_seen_unique(tab):
+    """Rows of `tab` with duplicates dropped, first occurrence kept, original order (Base.union / unique semantics)."""
+    n, ln = tab.shape
+    if n <= 1 or ln == 0:
+        return tab[: min(n, 1)] if ln == 0 else tab
+    flat = np.ascontiguousarray(tab, dtype=np.int32).view(np.dtype((np.void, 4 * ln))).reshape(-1)
+    _, first = np.unique(flat, return_index=True)
+    if len(first) == n:
+        return tab
+    return tab[np.sort(first)]
+
+
 def union_rows(a, b):
     """Base.union on vectors of multi-indices: first-seen order, duplicates dropped."""
     if b is None or b.shape[0] == 0:
-        seen, keep = set(), []
-        for i, k in enumerate(_keys(a)):
-            if k not in seen:
-                seen.add(k); keep.append(i)
-        return a if len(keep) == a.shape[0] else a[keep]
-    both = np.concatenate([a, b.reshape(-1, a.shape[1])], axis=0)
-    seen, keep = set(), []
-    for i, k in enumerate(_keys(both)):
-        if k not in seen:
-            seen.add(k); keep.append(i)
-    return both[keep]
+        return _first_seen_unique(a)
+    return _first_seen_unique(np.concatenate([a, b.reshape(-1, a.shape[1])], axis=0))
 
 
 def pushunique(tab, row):
