@@ -146,21 +146,45 @@ __global__ void __launch_bounds__(256)
 assemble_kernel(F f, EvalShape sh, int nsites, const typename F::State* __restrict__ Ls,
                 const typename F::State* __restrict__ Rs,
                 unsigned long long* maxbits, int* nanflag) {
-    // grid: x over i (fastest), y over (c, j) pairs in chunks
+    // grid: x over i (fastest), y over (c, j) pairs in chunks.  The (c, j) decode and the centre-site pushes are done once
+    // per pair and amortised over ROWS_PER_THREAD-ish rows (the host sizes gridDim.x for that); 32-bit index arithmetic
+    // whenever the pair count allows (a 64-bit division costs ~100 instructions, more than the functor itself).
     const long long ncj = sh.ncent * sh.nright;
+    const bool small = ncj < 0x7fffffffLL && sh.nleft < 0x7fffffffLL;
+    const int nleft32 = (int)sh.nleft, ncent32 = (int)sh.ncent;
     double mx = 0.0; bool isn = false;
     for (long long cj = blockIdx.y; cj < ncj; cj += gridDim.y) {
-        const long long c = cj % sh.ncent, j = cj / sh.ncent;
+        long long c, j;
+        if (small) { const unsigned q = (unsigned)cj / (unsigned)ncent32; j = q; c = (unsigned)cj - q * (unsigned)ncent32; }
+        else { c = cj % sh.ncent; j = cj / sh.ncent; }
         typename F::State cs = Rs[j];
-        long long rem = c;
-        for (int x = 0; x < sh.ncent_sites; ++x) { f.push(cs, sh.nl + x, (int)(rem % sh.cdims[x]) + 1); rem /= sh.cdims[x]; }
+        unsigned rem = (unsigned)c;                               // ncent = prod of <= 8 local dims: fits 32 bits when `small`
+        long long rem64 = c;
+        for (int x = 0; x < sh.ncent_sites; ++x) {
+            int digit;
+            if (small) { const unsigned q = rem / (unsigned)sh.cdims[x]; digit = (int)(rem - q * (unsigned)sh.cdims[x]); rem = q; }
+            else { digit = (int)(rem64 % sh.cdims[x]); rem64 /= sh.cdims[x]; }
+            f.push(cs, sh.nl + x, digit + 1);
+        }
         const long long coff = c * sh.stride_c + j * sh.stride_j;
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < sh.nleft; i += (long long)gridDim.x * blockDim.x) {
-            const double v = f.finish(f.merge(Ls[i], cs));
-            sh.outs[0][coff + i] = v;
-            for (int p = 1; p < sh.nouts; ++p) sh.outs[p][coff + i] = v;       // peer stores (coalesced 256 B per warp)
-            const double a = fabs(v);
-            if (a != a) isn = true; else mx = a > mx ? a : mx;
+        double* __restrict__ o0 = sh.outs[0] + coff;
+        if (small) {
+            const int step = (int)(gridDim.x * blockDim.x);
+            for (int i = (int)(blockIdx.x * blockDim.x + threadIdx.x); i < nleft32; i += step) {
+                const double v = f.finish(f.merge(Ls[i], cs));
+                o0[i] = v;
+                for (int p = 1; p < sh.nouts; ++p) sh.outs[p][coff + i] = v;   // peer stores (coalesced 256 B per warp)
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+            }
+        } else {
+            for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < sh.nleft; i += (long long)gridDim.x * blockDim.x) {
+                const double v = f.finish(f.merge(Ls[i], cs));
+                o0[i] = v;
+                for (int p = 1; p < sh.nouts; ++p) sh.outs[p][coff + i] = v;
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+            }
         }
     }
     maxabs_commit(mx, isn, maxbits, nanflag);
@@ -233,7 +257,7 @@ int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const
     const long long nfold = sh.nleft + sh.nright;
     fold_kernel<F><<<(unsigned)((nfold + 255) / 256), 256, 0, h->stream>>>(f, b.d_left, b.d_right, sh, nsites, (S*)b.Ls, (S*)b.Rs);
     TCI_LAUNCH_CHECK(h);
-    long long gx = (sh.nleft + 255) / 256;
+    long long gx = (sh.nleft + 256 * 8 - 1) / (256 * 8);        // ~8 rows per thread per (c, j) pair
     if (gx > 32) gx = 32;
     long long gy = sh.ncent * sh.nright;
     const long long want = (long long)h->num_sms * 16 / gx + 1;
