@@ -58,7 +58,13 @@ struct LorentzF {                        // p0 / (1 + sum v^2): README.md:21-29
     __device__ State zero() const { return 0; }
     __device__ void push(State& s, int, int v) const { s += (long long)v * v; }
     __device__ State merge(State a, State b) const { return a + b; }
-    __device__ double finish(State s) const { return coeff / (double)(1 + s); }
+    __device__ double finish(State s) const {
+        const long long d = 1 + s;
+        // int32 -> double conversion when it fits (the 64-bit one runs on the slow XU path); 1/x through the correctly
+        // rounded reciprocal when coeff == 1 (same bits as the IEEE division 1.0 / x, fewer Newton steps)
+        const double x = (d < 0x7fffffffLL) ? (double)(int)d : (double)d;
+        return coeff == 1.0 ? __drcp_rn(x) : coeff / x;
+    }
 };
 struct SumF {                            // p0 * sum v: test/test_batcheval.jl:18
     double scale;

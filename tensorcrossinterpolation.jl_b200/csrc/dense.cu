@@ -30,18 +30,27 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
+// Shared-memory layout of an operand tile follows the operand's contiguous direction so that BOTH the coalesced global
+// load -> shared store and the DMMA fragment load are bank-conflict free:
+//   row index (m or n) contiguous in global memory: tile[k][row], leading dimension LDS = 68  (68 mod 16 = 4)
+//   k contiguous in global memory:                  tile[row][k], leading dimension LDK = 20  (20 mod 16 = 4)
+// (64-bit accesses are served per half-warp; 16 addresses are conflict-free iff distinct mod 16 in 8-byte units.)
+constexpr int LDK = 20;
+constexpr int TILE_DOUBLES = (BK * LDS > BM * LDK) ? BK * LDS : BM * LDK;
+
+template <bool KFAST> __device__ __forceinline__ int tile_off(int row, int k) { return KFAST ? row * LDK + k : k * LDS + row; }
+
+template <bool A_KFAST, bool B_KFAST>
 __global__ void __launch_bounds__(GEMM_THREADS)
 gemm_dmma_kernel(GemmArgs g) {
-    __shared__ double As[2][BK][LDS];
-    __shared__ double Bs[2][BK][LDS];
+    __shared__ double As[2][TILE_DOUBLES];
+    __shared__ double Bs[2][TILE_DOUBLES];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int wm = warp & 1, wn = warp >> 1;            // warp tile: 32 rows x 16 cols
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     const double* A = g.A + (long long)blockIdx.z * g.bsa;
     const double* B = g.B + (long long)blockIdx.z * g.bsb;
     double* C = g.C + (long long)blockIdx.z * g.bsc;
-    const bool a_mfast = (g.sam == 1) || (g.sak != 1);  // which index runs along consecutive threads
-    const bool b_kfast = (g.sbk == 1);
 
     double acc[4][2][2];
 #pragma unroll
@@ -54,11 +63,11 @@ gemm_dmma_kernel(GemmArgs g) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             int m, k;
-            if (a_mfast) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
+            if (!A_KFAST) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
             const int gm = m0 + m, gk = k0 + k;
             ra[i] = (gm < g.M && gk < g.K) ? A[(long long)gm * g.sam + (long long)gk * g.sak] : 0.0;
             int n, kb;
-            if (b_kfast) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
+            if (B_KFAST) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
             const int gn = n0 + n, gkb = k0 + kb;
             rb[i] = (gn < g.N && gkb < g.K) ? B[(long long)gkb * g.sbk + (long long)gn * g.sbn] : 0.0;
         }
@@ -67,11 +76,11 @@ gemm_dmma_kernel(GemmArgs g) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             int m, k;
-            if (a_mfast) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
-            As[buf][k][m] = ra[i];
+            if (!A_KFAST) { m = t & 63; k = (t >> 6) + 4 * i; } else { k = t & 15; m = (t >> 4) + 16 * i; }
+            As[buf][tile_off<A_KFAST>(m, k)] = ra[i];
             int n, kb;
-            if (b_kfast) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
-            Bs[buf][kb][n] = rb[i];
+            if (B_KFAST) { kb = t & 15; n = (t >> 4) + 16 * i; } else { n = t & 63; kb = (t >> 6) + 4 * i; }
+            Bs[buf][tile_off<B_KFAST>(n, kb)] = rb[i];
         }
     };
 
@@ -86,9 +95,9 @@ gemm_dmma_kernel(GemmArgs g) {
         for (int kk = 0; kk < BK; kk += 4) {
             double a[4], b[2];
 #pragma unroll
-            for (int i = 0; i < 4; ++i) a[i] = As[buf][kk + (lane & 3)][wm * 32 + i * 8 + (lane >> 2)];
+            for (int i = 0; i < 4; ++i) a[i] = As[buf][tile_off<A_KFAST>(wm * 32 + i * 8 + (lane >> 2), kk + (lane & 3))];
 #pragma unroll
-            for (int j = 0; j < 2; ++j) b[j] = Bs[buf][kk + (lane & 3)][wn * 16 + j * 8 + (lane >> 2)];
+            for (int j = 0; j < 2; ++j) b[j] = Bs[buf][tile_off<B_KFAST>(wn * 16 + j * 8 + (lane >> 2), kk + (lane & 3))];
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
@@ -123,7 +132,9 @@ __global__ void copy_strided_kernel(const double* __restrict__ src, long long ss
 int launch_gemm(tci_handle h, const GemmArgs& g, int batch) {
     if (g.M <= 0 || g.N <= 0 || batch <= 0) return TCI_OK;
     dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, batch);
-    gemm_dmma_kernel<<<grid, GEMM_THREADS, 0, h->stream>>>(g);
+    const bool a_kfast = (g.sak == 1) && (g.sam != 1), b_kfast = (g.sbk == 1);
+    if (a_kfast) { if (b_kfast) gemm_dmma_kernel<true, true><<<grid, GEMM_THREADS, 0, h->stream>>>(g); else gemm_dmma_kernel<true, false><<<grid, GEMM_THREADS, 0, h->stream>>>(g); }
+    else         { if (b_kfast) gemm_dmma_kernel<false, true><<<grid, GEMM_THREADS, 0, h->stream>>>(g); else gemm_dmma_kernel<false, false><<<grid, GEMM_THREADS, 0, h->stream>>>(g); }
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;
 }
