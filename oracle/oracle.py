@@ -142,6 +142,31 @@ def rrlu(A, maxrank=INT64_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True):
                 err.value, pe[: r + 1].copy())
 
 
+def arrlu(A, I0=(), J0=(), maxrank=INT64_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, numrookiter=5, seed=0):
+    """arrlu(Float64, (i, j) -> A[i, j], size(A), I0, J0; ...) — matrixlu.jl:500-569 (rook pivot search).  The random
+    column/row draws come from the oracle's own seeded stream (see tci_oracle.cpp `Rng`), not Julia's RNG.
+    Returns (RRLU, number of matrix elements sampled)."""
+    A = _f64(A)
+    m, n = A.shape
+    rmax = int(min(maxrank, m, n))
+    rowperm = np.zeros(m, dtype=np.int64)
+    colperm = np.zeros(n, dtype=np.int64)
+    L = np.zeros((m, max(rmax, 1)), order="F")
+    U = np.zeros((max(rmax, 1), n), order="F")
+    pe = np.zeros(rmax + 1)
+    npivot, err, nev = C.c_int64(), C.c_double(), C.c_int64()
+    i0 = np.asarray(list(I0), dtype=np.int64)
+    j0 = np.asarray(list(J0), dtype=np.int64)
+    _check(lib().orc_arrlu(_p(A, C.c_double), C.c_int64(m), C.c_int64(n), C.c_int64(m), _p(i0, C.c_int64), C.c_int64(len(i0)),
+                           _p(j0, C.c_int64), C.c_int64(len(j0)), C.c_int64(int(min(maxrank, INT64_MAX))), C.c_double(reltol),
+                           C.c_double(abstol), int(leftorthogonal), int(numrookiter), C.c_uint64(seed), _p(rowperm, C.c_int64),
+                           _p(colperm, C.c_int64), C.byref(npivot), C.byref(err), _p(L, C.c_double), C.c_int64(m),
+                           _p(U, C.c_double), C.c_int64(max(rmax, 1)), _p(pe, C.c_double), C.byref(nev)))
+    r = npivot.value
+    return RRLU(rowperm, colperm, np.asfortranarray(L[:, :r]), np.asfortranarray(U[:r, :]), leftorthogonal, r,
+                err.value, pe[: r + 1].copy()), nev.value
+
+
 def solve_right(P, B):
     P, B = _f64(P), _f64(B)
     X = np.zeros(B.shape, order="F")
@@ -233,6 +258,10 @@ class TCI2:
         all even bonds; within one pass the bonds read and write disjoint index sets, so the order inside a pass is
         immaterial and a concurrent execution gives the same result)."""
         lib().orc_tci_set_bondorder(self.h, {"sequential": 0, "oddeven": 1}[order])
+
+    def set_pivotsearch(self, pivotsearch, seed=0):
+        """'full' or 'rook' (tensorci2.jl:845-914); `seed` starts the stream behind pushrandomsubset!."""
+        lib().orc_tci_set_pivotsearch(self.h, {"full": 0, "rook": 1}[pivotsearch], C.c_uint64(seed))
 
     def optimize(self, tolerance=1e-8, maxbonddim=INT64_MAX, maxiter=20, sweepstrategy="backandforth",
                  normalizeerror=True, ncheckhistory=3, strictlynested=False, checkconvglobalpivot=True):
@@ -335,10 +364,11 @@ class TCI2:
         return {"nevals": ne.value, "t_eval": te.value, "t_lu": tl.value}
 
 
-def crossinterpolate2(f, localdims, initialpivots=None, bondorder="sequential", **kw):
+def crossinterpolate2(f, localdims, initialpivots=None, bondorder="sequential", pivotsearch="full", seed=0, **kw):
     """crossinterpolate2 (tensorci2.jl:1313-1323) with nsearchglobalpivot=0."""
     tci = TCI2(f, localdims, initialpivots)
     tci.set_bondorder(bondorder)
+    tci.set_pivotsearch(pivotsearch, seed)
     ranks, errors = tci.optimize(**kw)
     return tci, ranks, errors
 

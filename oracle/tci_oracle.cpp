@@ -186,6 +186,112 @@ static int rrlu_inplace(Mat& A, RRLU& lu, int64_t maxrank, double reltol, double
     return optimizerrlu(lu, A, maxrank, reltol, abstol);
 }
 
+// ---------------------------------------------------------------------------------------
+// arrlu (rook pivot search) — src/matrixlu.jl:500-569, helpers :627-674, util.jl:173-219.
+// The reference draws from Julia's global RNG (`rand(1:length(c))`, util.jl:186), whose stream
+// cannot be restated; oracle and product share the counter-based generator below instead, so the
+// random columns differ from a Julia run while every other step follows the reference line by line.
+// ---------------------------------------------------------------------------------------
+struct Rng {
+    uint64_t s = 0;
+    uint64_t next() {                              // splitmix64 stream
+        s += 0x9e3779b97f4a7c15ULL;
+        uint64_t z = s; z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+        return z ^ (z >> 31);
+    }
+    int64_t randint(int64_t n) { return (int64_t)(next() % (uint64_t)n); }      // 0-based stand-in for rand(1:n)
+};
+typedef std::function<Mat(const std::vector<int64_t>&, const std::vector<int64_t>&)> BatchF;   // 1-based rows, cols -> matrix
+
+static void pushrandomsubset(std::vector<int64_t>& subset, int64_t setsize, int64_t n, Rng& rng) {   // util.jl:173-219
+    std::vector<char> in(setsize + 1, 0);
+    for (int64_t v : subset) in[v] = 1;
+    std::vector<int64_t> c;                                        // setdiff(1:setsize, subset), ascending
+    for (int64_t v = 1; v <= setsize; ++v) if (!in[v]) c.push_back(v);
+    n = std::min<int64_t>(n, (int64_t)c.size());
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t idx = rng.randint((int64_t)c.size());
+        subset.push_back(c[idx]);
+        c.erase(c.begin() + idx);                                  // deleteat!
+    }
+}
+static void cols2Lmatrix(Mat& C, const Mat& P) {                   // :627-648  (C <- C * inv(triu P), column by column)
+    if (C.n != P.n) throw std::runtime_error("C and P matrices must have same number of columns in `cols2Lmatrix!`.");
+    if (P.m != P.n) throw std::runtime_error("P matrix must be square in `cols2Lmatrix!`.");
+    for (int64_t k = 0; k < P.m; ++k) {
+        for (int64_t i = 0; i < C.m; ++i) C(i, k) = C(i, k) / P(k, k);
+        for (int64_t j = k + 1; j < C.n; ++j) {
+            const double y = P(k, j);
+            for (int64_t i = 0; i < C.m; ++i) C(i, j) = C(i, j) - C(i, k) * y;
+        }
+    }
+}
+static void rows2Umatrix(Mat& R, const Mat& P) {                   // :655-674  (R <- inv(tril P) * R, row by row)
+    if (R.m != P.m) throw std::runtime_error("R and P matrices must have same number of rows in `rows2Umatrix!`.");
+    if (P.m != P.n) throw std::runtime_error("P matrix must be square in `rows2Umatrix!`.");
+    for (int64_t k = 0; k < P.m; ++k) {
+        for (int64_t j = 0; j < R.n; ++j) R(k, j) = R(k, j) / P(k, k);
+        for (int64_t j = 0; j < R.n; ++j) {
+            const double y = R(k, j);
+            for (int64_t i = k + 1; i < R.m; ++i) R(i, j) = R(i, j) - P(i, k) * y;
+        }
+    }
+}
+static Mat topleft(const Mat& A, int64_t r) { Mat B(r, r); for (int64_t j = 0; j < r; ++j) for (int64_t i = 0; i < r; ++i) B(i, j) = A(i, j); return B; }
+
+static int arrlu(const BatchF& f, int64_t m, int64_t n, std::vector<int64_t> I0, std::vector<int64_t> J0, RRLU& lu,
+                 int64_t maxrank, double reltol, double abstol, bool leftorth, int numrookiter, Rng& rng) {
+    lu = RRLU(); lu.leftorthogonal = leftorth;                     // :513
+    lu.rowperm.resize(m); lu.colperm.resize(n);
+    for (int64_t i = 0; i < m; ++i) lu.rowperm[i] = i + 1;
+    for (int64_t j = 0; j < n; ++j) lu.colperm[j] = j + 1;
+    lu.L = Mat(0, 0); lu.U = Mat(0, 0);
+    bool islowrank = false;
+    maxrank = std::min(maxrank, std::min(m, n));                   // :515
+    while (true) {
+        if (leftorth) pushrandomsubset(J0, n, std::max<int64_t>(1, (int64_t)J0.size()), rng);     // :521-525
+        else          pushrandomsubset(I0, m, std::max<int64_t>(1, (int64_t)I0.size()), rng);
+        for (int rookiter = 1; rookiter <= numrookiter; ++rookiter) {
+            const bool colmove = ((rookiter % 2 == 0) == leftorth);                                // :529
+            Mat sub = colmove ? f(I0, lu.colperm) : f(lu.rowperm, J0);                             // :532-536
+            lu.npivot = 0;                                                                         // :539
+            // _optimizerrlu! swaps lu.rowpermutation / lu.colpermutation at the POSITIONS of the submatrix (:254-275)
+            int st = optimizerrlu(lu, sub, maxrank, reltol, abstol);
+            if (st) return st;
+            islowrank = islowrank || (lu.npivot < std::min(sub.m, sub.n));                         // :541
+            std::vector<int64_t> ri(lu.rowperm.begin(), lu.rowperm.begin() + lu.npivot);
+            std::vector<int64_t> ci(lu.colperm.begin(), lu.colperm.begin() + lu.npivot);
+            if (ri == I0 && ci == J0) break;                                                       // :544-546
+            J0 = ci; I0 = ri;                                                                      // :548-549
+        }
+        if (islowrank || (int64_t)I0.size() >= maxrank) break;                                     // :552-554
+    }
+    const int64_t r = lu.npivot;
+    if (lu.L.m < m) {                                                                              // :558-564
+        std::vector<char> in(m + 1, 0); for (int64_t v : I0) in[v] = 1;
+        std::vector<int64_t> I2; for (int64_t v = 1; v <= m; ++v) if (!in[v]) I2.push_back(v);
+        lu.rowperm = I0; lu.rowperm.insert(lu.rowperm.end(), I2.begin(), I2.end());
+        Mat L2 = f(I2, J0);
+        cols2Lmatrix(L2, topleft(lu.U, r));
+        Mat L(m, r);
+        for (int64_t j = 0; j < r; ++j) { for (int64_t i = 0; i < r; ++i) L(i, j) = lu.L(i, j);
+                                          for (int64_t i = 0; i < L2.m; ++i) L(r + i, j) = L2(i, j); }
+        lu.L = L;
+    }
+    if (lu.U.n < n) {                                                                              // :567-573
+        std::vector<char> in(n + 1, 0); for (int64_t v : J0) in[v] = 1;
+        std::vector<int64_t> J2; for (int64_t v = 1; v <= n; ++v) if (!in[v]) J2.push_back(v);
+        lu.colperm = J0; lu.colperm.insert(lu.colperm.end(), J2.begin(), J2.end());
+        Mat U2 = f(I0, J2);
+        rows2Umatrix(U2, topleft(lu.L, r));
+        Mat U(r, n);
+        for (int64_t j = 0; j < r; ++j) for (int64_t i = 0; i < r; ++i) U(i, j) = lu.U(i, j);
+        for (int64_t j = 0; j < U2.n; ++j) for (int64_t i = 0; i < r; ++i) U(i, r + j) = U2(i, j);
+        lu.U = U;
+    }
+    return 0;
+}
+
 static Mat lu_left(const RRLU& lu, bool permute) {                 // :716-724
     if (!permute) return lu.L;
     Mat l(lu.L.m, lu.L.n);
@@ -401,6 +507,8 @@ struct TCI2 {
     std::vector<std::vector<IndexList>> Iset_history, Jset_history;
     int bondorder = 0;                             // 0: sequential bonds (the reference, :1226-1250); 1: odd bonds then even bonds
                                                    // (the parallel-bond schedule of the product; NOT in the reference)
+    int pivotsearch = 0;                           // 0: :full, 1: :rook (:863-905)
+    Rng rng;                                       // stream behind pushrandomsubset! in the rook search
     int64_t nevals = 0;                            // bookkeeping for the bench only
     double t_eval = 0, t_lu = 0;                   // seconds spent in Pi fill and in MatrixLUCI
 
@@ -496,12 +604,35 @@ int TCI2::updatepivots(int b, const Func& f, bool leftorth, double reltol, doubl
     invalidatesitetensors();
     IndexList Ic = set_union(kronecker_left(Iset[b], localdims[b]), extraI);      // :842
     IndexList Jc = set_union(kronecker_right(localdims[b + 1], Jset[b + 1]), extraJ);   // :843
-    Mat Pi = fillmatrix(f, Ic, Jc, 0, (int64_t)Ic.size(), (int64_t)Jc.size());    // :848-852
-    updatemaxsample(Pi.a);                                                         // :855
-    const double t0 = now_s();
     RRLU lu;
-    int st = rrlu_inplace(Pi, lu, maxbonddim, reltol, abstol, leftorth);           // :856-862 (Pi is a fresh array: no copy needed)
-    if (st) return st;
+    double t0 = now_s();
+    bool full = pivotsearch == 0;
+    if (pivotsearch == 1) {                                                        // :863-905
+        std::vector<int64_t> I0, J0;                                               // :866-867 positions of the current pivots
+        for (const auto& x : Iset[b + 1]) { auto it = std::find(Ic.begin(), Ic.end(), x); if (it != Ic.end()) I0.push_back(it - Ic.begin() + 1); }
+        for (const auto& x : Jset[b])     { auto it = std::find(Jc.begin(), Jc.end(), x); if (it != Jc.end()) J0.push_back(it - Jc.begin() + 1); }
+        double submax = 0.0;                                                       // SubMatrix.maxsamplevalue :769-790
+        BatchF pif = [&](const std::vector<int64_t>& ir, const std::vector<int64_t>& ic) {
+            IndexList rows, cols;
+            for (int64_t i : ir) rows.push_back(Ic[i - 1]);
+            for (int64_t j : ic) cols.push_back(Jc[j - 1]);
+            Mat S = fillmatrix(f, rows, cols, 0, (int64_t)rows.size(), (int64_t)cols.size());
+            for (double v : S.a) submax = jl_max(submax, std::fabs(v));
+            return S;
+        };
+        t0 = now_s();
+        int st = arrlu(pif, (int64_t)Ic.size(), (int64_t)Jc.size(), I0, J0, lu, maxbonddim, reltol, abstol, leftorth, 5, rng);
+        if (st) return st;
+        updatemaxsample({submax});                                                 // :881
+        full = lu.npivot == 0;                                                     // :886 fall back to the full search
+    }
+    if (full) {
+        Mat Pi = fillmatrix(f, Ic, Jc, 0, (int64_t)Ic.size(), (int64_t)Jc.size());    // :848-852
+        updatemaxsample(Pi.a);                                                         // :855
+        t0 = now_s();
+        int st = rrlu_inplace(Pi, lu, maxbonddim, reltol, abstol, leftorth);           // :856-862 (Pi is a fresh array: no copy needed)
+        if (st) return st;
+    }
     IndexList newI, newJ;
     for (int64_t k = 0; k < lu.npivot; ++k) newI.push_back(Ic[lu.rowperm[k] - 1]); // :919
     for (int64_t k = 0; k < lu.npivot; ++k) newJ.push_back(Jc[lu.colperm[k] - 1]); // :920
@@ -797,6 +928,35 @@ int orc_rrlu(const double* A, int64_t m, int64_t n, int64_t lda, int64_t maxrank
     ORC_CATCH(-10)
 }
 
+// arrlu on a dense matrix used as f(i, j) = A[i, j] (the form test/test_matrixlu.jl:79 calls).  I0/J0 1-based.
+// L is m x min(maxrank,m,n) (ld ldl), U has ld ldu; *nevals = matrix elements sampled.
+int orc_arrlu(const double* A, int64_t m, int64_t n, int64_t lda, const int64_t* I0, int64_t nI0, const int64_t* J0, int64_t nJ0,
+              int64_t maxrank, double reltol, double abstol, int leftorthogonal, int numrookiter, uint64_t seed,
+              int64_t* rowperm, int64_t* colperm, int64_t* npivot, double* error,
+              double* L, int64_t ldl, double* U, int64_t ldu, double* pivoterrors, int64_t* nevals) {
+    ORC_TRY
+    int64_t count = 0;
+    BatchF f = [&](const std::vector<int64_t>& ir, const std::vector<int64_t>& ic) {
+        Mat S((int64_t)ir.size(), (int64_t)ic.size());
+        for (size_t j = 0; j < ic.size(); ++j) for (size_t i = 0; i < ir.size(); ++i) S((int64_t)i, (int64_t)j) = A[(size_t)(ic[j] - 1) * lda + (ir[i] - 1)];
+        count += S.m * S.n;
+        return S;
+    };
+    RRLU lu; Rng rng; rng.s = seed;
+    int st = arrlu(f, m, n, std::vector<int64_t>(I0, I0 + nI0), std::vector<int64_t>(J0, J0 + nJ0), lu, maxrank, reltol, abstol,
+                   leftorthogonal != 0, numrookiter, rng);
+    *npivot = lu.npivot; *error = lu.error; *nevals = count;
+    std::copy(lu.rowperm.begin(), lu.rowperm.end(), rowperm);
+    std::copy(lu.colperm.begin(), lu.colperm.end(), colperm);
+    if (st) return st;
+    for (int64_t j = 0; j < lu.npivot; ++j) for (int64_t i = 0; i < m; ++i) L[(size_t)j * ldl + i] = lu.L(i, j);
+    for (int64_t j = 0; j < n; ++j) for (int64_t i = 0; i < lu.npivot; ++i) U[(size_t)j * ldu + i] = lu.U(i, j);
+    auto pe = lu_pivoterrors(lu);
+    std::copy(pe.begin(), pe.end(), pivoterrors);
+    return 0;
+    ORC_CATCH(-10)
+}
+
 // MatrixLUCI left (m x r) and right (r x n) from rrlu outputs (L m x r ld ldl, U r x n ld ldu)
 int orc_luci_factors(int64_t m, int64_t n, int64_t r, int leftorthogonal, const int64_t* rowperm, const int64_t* colperm,
                      const double* L, int64_t ldl, const double* U, int64_t ldu, double* left, double* right) {
@@ -858,6 +1018,7 @@ void* orc_tci_create(void* f, const int32_t* localdims, int nsites, const int32_
 }
 void orc_tci_destroy(void* h) { delete (OrcTCI*)h; }
 void orc_tci_set_bondorder(void* h, int v) { ((OrcTCI*)h)->tci.bondorder = v; }
+void orc_tci_set_pivotsearch(void* h, int rook, uint64_t seed) { ((OrcTCI*)h)->tci.pivotsearch = rook; ((OrcTCI*)h)->tci.rng.s = seed; }
 
 // optimize!: ranks/errors must hold maxiter entries; *niter receives the number written.
 int orc_tci_optimize(void* h_, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,

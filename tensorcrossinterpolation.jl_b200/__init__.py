@@ -6,8 +6,9 @@ package is importable without a GPU (so CPU-only tests can check symbols), but a
 raises if the library or a CUDA device is missing — there is no CPU fallback.
 """
 from ._lib import Handle, TCIError, default_handle, lib, SO_PATH          # noqa: F401
-from .matrixlu import rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing   # noqa: F401
-from .dense import Mat, gemm, luci_factors, solve_right                              # noqa: F401
+from .matrixlu import (rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing, arrlu, rrlu_function, Rng,   # noqa: F401
+                       pushrandomsubset)
+from .dense import Mat, gemm, luci_factors, solve_right, trsm_right                              # noqa: F401
 from .matrixluci import MatrixLUCI                                                  # noqa: F401
 from .batcheval import (BatchEvaluator, BuiltinFunction, LorentzFunction, SumFunction, QuanticsExpSin,          # noqa: F401
                         QuanticsExpPlusSin, QuanticsExp2, DenseFunction, HashFunction, UserFunction, filltensor,

@@ -84,3 +84,18 @@ def solve_right(h, B, P):
     h.check(lib().tci_solve_right_f64(h.h, B.ptr, C.c_int64(B.rows), C.c_int64(B.ld), P.ptr, C.c_int64(P.rows),
                                       C.c_int64(P.ld), X.ptr, C.c_int64(X.ld)))
     return X
+
+
+def trsm_right(h, T, r, lower, unit, B, left=False):
+    """In place on B: X * T = B (left=False, B is q x r) or T * X = B (left=True, B is r x q; the right solve on transposed
+    strides) with the leading r x r triangle of `T` — tci_trsm_right_f64.  Serves cols2Lmatrix!/rows2Umatrix!
+    (matrixlu.jl:627-674) of the rook search."""
+    if r == 0 or B.rows * B.cols == 0:
+        return B
+    if left:
+        h.check(lib().tci_trsm_right_f64(h.h, T.ptr, C.c_int64(T.ld), C.c_int64(1), C.c_int64(r), int(not lower), int(bool(unit)),
+                                         B.ptr, C.c_int64(B.ld), C.c_int64(1), C.c_int64(B.cols)))
+    else:
+        h.check(lib().tci_trsm_right_f64(h.h, T.ptr, C.c_int64(1), C.c_int64(T.ld), C.c_int64(r), int(bool(lower)), int(bool(unit)),
+                                         B.ptr, C.c_int64(1), C.c_int64(B.ld), C.c_int64(B.rows)))
+    return B

@@ -162,3 +162,126 @@ def rrlu_last_timing(handle=None):
     steps = C.c_int64()
     h.check(lib().tci_rrlu_last_timing(h.h, p_f64(ms), C.byref(steps)))
     return {"loop_ms": float(ms[0]), "extract_ms": float(ms[2]), "steps": steps.value}
+
+
+# ---- rook pivot search: arrlu (matrixlu.jl:500-569) -------------------------------------------------------------------
+class Rng:
+    """Counter-based splitmix64 stream behind `pushrandomsubset!` (util.jl:173-219).  The reference draws from Julia's
+    global RNG, whose stream has no portable restatement; the oracle (oracle/tci_oracle.cpp `Rng`) uses this same
+    generator, so product and oracle pick identical random rows/columns for a given seed."""
+    MASK = (1 << 64) - 1
+
+    def __init__(self, seed=0):
+        self.s = int(seed) & self.MASK
+
+    def next(self):
+        self.s = (self.s + 0x9E3779B97F4A7C15) & self.MASK
+        z = self.s
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & self.MASK
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & self.MASK
+        return z ^ (z >> 31)
+
+    def randint(self, n):                                  # 0-based stand-in for rand(1:n)
+        return self.next() % int(n)
+
+
+def pushrandomsubset(subset, setsize, n, rng):
+    """pushrandomsubset!(subset, 1:setsize, n) — util.jl:214-219 with randomsubset :173-191 (draw, then deleteat!)."""
+    taken = np.zeros(setsize + 1, dtype=bool)
+    taken[np.asarray(subset, dtype=np.int64)] = True
+    c = [int(v) for v in np.nonzero(~taken[1:])[0] + 1]
+    for _ in range(min(int(n), len(c))):
+        subset.append(c.pop(rng.randint(len(c))))
+
+
+def _as_device_mat(x, h):
+    from .dense import Mat
+    if isinstance(x, Mat):
+        return x
+    return Mat.from_numpy(np.asarray(x, dtype=np.float64), f"cuda:{h.device}", pad=16)
+
+
+def arrlu(f, matrixsize, I0=(), J0=(), maxrank=INT_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, numrookiter=5,
+          usebatcheval=False, rng=None, handle=None):
+    """arrlu(Float64, f, matrixsize, I0, J0; ...) — matrixlu.jl:500-569.  `f(i, j)` (1-based scalars; usebatcheval=False: the
+    user's function runs on the host and the sampled strips are uploaded) or `f(rows, cols)` returning the sub-matrix as a
+    `dense.Mat`/array (usebatcheval=True; the TCI path passes a device evaluator).  Every strip is factorised on the GPU
+    by the same rrLU kernels as the full search; the final L/U completion (:558-573) is two device triangular solves."""
+    import torch
+    from .dense import Mat, trsm_right
+    h = handle or _lib.default_handle()
+    rng = rng or Rng(0)
+    m, n = int(matrixsize[0]), int(matrixsize[1])
+    if usebatcheval:
+        batchf = lambda r, c: _as_device_mat(f(r, c), h)
+    else:
+        batchf = lambda r, c: _as_device_mat(np.array([[f(int(i), int(j)) for j in c] for i in r], dtype=np.float64).reshape(len(r), len(c)), h)
+    rowperm = np.arange(1, m + 1, dtype=np.int64)
+    colperm = np.arange(1, n + 1, dtype=np.int64)
+    I0, J0 = [int(v) for v in I0], [int(v) for v in J0]
+    islowrank = False
+    maxrank = int(min(maxrank, m, n))
+    lus = None
+    while True:
+        if leftorthogonal:                                 # :521-525
+            pushrandomsubset(J0, n, max(1, len(J0)), rng)
+        else:
+            pushrandomsubset(I0, m, max(1, len(I0)), rng)
+        for rookiter in range(1, numrookiter + 1):
+            colmove = ((rookiter % 2 == 0) == bool(leftorthogonal))                 # :529
+            sub = batchf(np.asarray(I0, dtype=np.int64), colperm.copy()) if colmove else batchf(rowperm.copy(), np.asarray(J0, dtype=np.int64))
+            kr, kc = sub.rows, sub.cols
+            lus = rrlu_device(sub, maxrank=maxrank, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal, handle=h)
+            # _optimizerrlu! swaps lu.rowpermutation/colpermutation at the POSITIONS of the strip (:254-275, :539-540)
+            rowperm[:kr] = rowperm[:kr][lus.rowpermutation - 1]
+            colperm[:kc] = colperm[:kc][lus.colpermutation - 1]
+            r = lus.npivot
+            islowrank = islowrank or r < min(kr, kc)                                 # :541
+            ri, ci = [int(v) for v in rowperm[:r]], [int(v) for v in colperm[:r]]
+            if ri == I0 and ci == J0:                                                # :544-546
+                break
+            I0, J0 = ri, ci
+        if islowrank or len(I0) >= maxrank:                                          # :552-554
+            break
+    r = lus.npivot
+    dev = lus.Lmat.buf.device
+    Lm, Um = lus.Lmat, lus.Umat
+    if Lm.rows < m:                                                                  # :558-564
+        i0 = np.asarray(I0, dtype=np.int64)
+        I2 = np.setdiff1d(np.arange(1, m + 1, dtype=np.int64), i0)                   # ascending, like setdiff(1:m, I0)
+        rowperm = np.concatenate([i0, I2])
+        L2 = batchf(I2, np.asarray(J0, dtype=np.int64))
+        trsm_right(h, Um, r, False, False, L2)                                       # cols2Lmatrix! :627-648
+        full = Mat.empty(m, max(r, 1), dev)
+        full.buf[:r, :r].copy_(Lm.buf[:r, :r])
+        full.buf[:r, r:m].copy_(L2.buf[:r, : m - r])
+        full.cols = r
+        Lm = full
+    if Um.cols < n:                                                                  # :567-573
+        j0 = np.asarray(J0, dtype=np.int64)
+        J2 = np.setdiff1d(np.arange(1, n + 1, dtype=np.int64), j0)
+        colperm = np.concatenate([j0, J2])
+        U2 = batchf(np.asarray(I0, dtype=np.int64), J2)
+        trsm_right(h, Lm, r, True, False, U2, left=True)                             # rows2Umatrix! :655-674
+        full = Mat.empty(max(r, 1), n, dev)
+        full.buf[:r, :r].copy_(Um.buf[:r, :r])
+        full.buf[r:n, :r].copy_(U2.buf[: n - r, :r])
+        full.rows = r
+        Um = full
+    lu = rrLU(rowperm, colperm, Lm.view(), Um.view(), leftorthogonal, r, lus.error, lus.pivoterrors())
+    lu.Lmat, lu.Umat = Lm, Um
+    return lu
+
+
+def rrlu_function(f, matrixsize, I0=(), J0=(), pivotsearch="full", usebatcheval=False, handle=None, **kw):
+    """rrlu(Float64, f, matrixsize, I0, J0; pivotsearch, kwargs...) — matrixlu.jl:599-617."""
+    h = handle or _lib.default_handle()
+    if pivotsearch == "rook":
+        return arrlu(f, matrixsize, I0, J0, usebatcheval=usebatcheval, handle=h, **kw)
+    if pivotsearch == "full":
+        m, n = int(matrixsize[0]), int(matrixsize[1])
+        kw.pop("numrookiter", None), kw.pop("rng", None)
+        rows, cols = np.arange(1, m + 1, dtype=np.int64), np.arange(1, n + 1, dtype=np.int64)
+        A = f(rows, cols) if usebatcheval else np.array([[f(int(i), int(j)) for j in cols] for i in rows], dtype=np.float64).reshape(m, n)
+        return rrlu_device(_as_device_mat(A, h), handle=h, **kw)
+    raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown pivot search strategy {pivotsearch}. Choose between :rook and :full.")

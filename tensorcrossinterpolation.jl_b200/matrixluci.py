@@ -20,6 +20,18 @@ class MatrixLUCI:
                               handle=self.handle)
         self._left = self._right = None
 
+    @classmethod
+    def from_function(cls, f, matrixsize, I0=(), J0=(), handle=None, **kw):
+        """MatrixLUCI(Float64, f, matrixsize, I0, J0; kwargs...) — matrixluci.jl:75-84: never holds the full matrix;
+        kwargs go to matrixlu.rrlu_function (pivotsearch="rook" runs the rook search arrlu)."""
+        from .matrixlu import rrlu_function
+        self = cls.__new__(cls)
+        self.handle = handle or _lib.default_handle()
+        self.m, self.n = int(matrixsize[0]), int(matrixsize[1])
+        self.lu = rrlu_function(f, matrixsize, I0, J0, handle=self.handle, **kw)
+        self._left = self._right = None
+        return self
+
     def size(self):                                        # matrixluci.jl:94-96
         return (self.m, self.n)
 

@@ -54,6 +54,13 @@ def union_rows(a, b):
     return _first_seen_unique(np.concatenate([a, b.reshape(-1, a.shape[1])], axis=0))
 
 
+def _positions(sub, tab):
+    """1-based positions in `tab` of the rows of `sub` that occur in it, in `sub` order
+    (findfirst(isequal(i), Icombined) filtered for nothing — tensorci2.jl:866-867)."""
+    where = {k: i + 1 for i, k in reversed(list(enumerate(_keys(tab))))}
+    return [where[k] for k in _keys(sub) if k in where]
+
+
 def pushunique(tab, row):
     row = np.asarray(row, dtype=np.int32).reshape(1, -1)
     if tab.shape[0] and any(k == row.tobytes() for k in _keys(tab)):
@@ -139,6 +146,8 @@ class TensorCI2(AbstractTensorTrain):
         self.maxsamplevalue = 0.0
         self.Iset_history, self.Jset_history = [], []
         self.stats = {"nevals": 0, "t_eval": 0.0, "t_lu": 0.0, "t_factors": 0.0, "t_host": 0.0}
+        from .matrixlu import Rng
+        self.rng = Rng(0)                                   # stream behind the rook search's random rows/columns (seed: `seed=` of crossinterpolate2)
         if f is not None and Iset is not None:              # tensorci2.jl:123-137
             self.Iset = [as_table(s, b) for b, s in enumerate(Iset)]
             self.Jset = [as_table(s, n - b - 1) for b, s in enumerate(Jset)]
@@ -256,10 +265,9 @@ class TensorCI2(AbstractTensorTrain):
 
     def updatepivots(self, b, f, leftorthogonal, reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX, sweepdirection="forward",
                      pivotsearch="full", verbosity=0, extraIset=None, extraJset=None):
-        """updatepivots! (tensorci2.jl:825-930), pivotsearch=:full."""
-        if pivotsearch != "full":
-            if pivotsearch == "rook":
-                raise TCIError(_lib.TCI_ERR_INVALID, "pivotsearch=:rook is not implemented in this build (SURVEY.md 8f)")
+        """updatepivots! (tensorci2.jl:825-930): pivotsearch=:full fills the whole Pi matrix; :rook samples strips of it
+        through a SubMatrix (:764-804) and never holds Pi."""
+        if pivotsearch not in ("full", "rook"):
             raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown pivot search strategy {pivotsearch}. Choose from :rook, :full.")
         f = makebatchevaluatable(f, self.localdims, self.handle)
         b0 = b - 1
@@ -270,11 +278,29 @@ class TensorCI2(AbstractTensorTrain):
         Jc = union_rows(kronecker_right(self.localdims[b0 + 1], self.Jset[b0 + 1]),
                         None if extraJset is None else as_table(extraJset, len(self) - b0 - 1))
         self.stats["t_host"] += time.perf_counter() - th
-        Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0])
-        t0 = time.perf_counter()
-        luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=leftorthogonal,
-                          handle=self.handle)
-        self.stats["t_lu"] += time.perf_counter() - t0
+        luci = None
+        if pivotsearch == "rook":                           # :863-905
+            I0 = _positions(self.Iset[b0 + 1], Ic)          # :866-867, current pivots that survive in the combined sets
+            J0 = _positions(self.Jset[b0], Jc)
+
+            def pif(irows, icols):                          # SubMatrix (:764-804): strips of Pi on demand, on the device
+                return self._fill(f, Ic[irows - 1], Jc[icols - 1], 0, len(irows), len(icols))
+
+            t0 = time.perf_counter()
+            te = self.stats["t_eval"]
+            luci = MatrixLUCI.from_function(pif, (Ic.shape[0], Jc.shape[0]), I0, J0, reltol=reltol, abstol=abstol,
+                                            maxrank=maxbonddim, leftorthogonal=leftorthogonal, pivotsearch="rook",
+                                            usebatcheval=True, rng=self.rng, handle=self.handle)
+            self.stats["t_lu"] += time.perf_counter() - t0 - (self.stats["t_eval"] - te)
+            if luci.npivots() == 0:                         # :886-899 fall back to the full search
+                luci = None
+        if luci is None:
+            Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0])
+            t0 = time.perf_counter()
+            luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=leftorthogonal,
+                              handle=self.handle)
+            self.stats["t_lu"] += time.perf_counter() - t0
+            t0 = time.perf_counter()
         if verbosity > 2:
             print(f"    Computing Pi ({Ic.shape[0]} x {Jc.shape[0]}) at bond {b}: LU: {time.perf_counter() - t0} sec")
         self.Iset[b0 + 1] = Ic[luci.rowindices() - 1]
@@ -581,6 +607,10 @@ def _sanitycheck(tci):                                      # globalsearch.jl:22
 
 def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323."""
+    seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): rook-search stream
     tci = TensorCI2(localdims, f, initialpivots, handle=kwargs.pop("handle", None))
+    if seed is not None:
+        from .matrixlu import Rng
+        tci.rng = Rng(seed)
     ranks, errors = optimize(tci, f, **kwargs)
     return tci, ranks, errors

@@ -140,3 +140,54 @@ def test_convergence_and_errors_c1():                   # BASELINE config C1 inv
     rng = np.random.default_rng(0)
     pts = rng.integers(1, 11, size=(500, 8))
     assert max(abs(tci.evaluate(p) - f(p)) for p in pts) < 1e-7 * tci.maxsamplevalue
+
+
+# ---- rook pivot search (matrixlu.jl:500-569, tensorci2.jl:863-905) ---------------------------------------------
+A4 = np.array([[0.711002, 0.724557, 0.789335, 0.382373], [0.910429, 0.726781, 0.719957, 0.486302],
+               [0.632716, 0.39967, 0.571809, 0.0803125], [0.885709, 0.531645, 0.569399, 0.481214]])
+
+
+@pytest.mark.parametrize("leftorthogonal", [True, False])
+def test_arrlu_reference_matrix(leftorthogonal):        # test/test_matrixlu.jl:71-86
+    for seed in range(4):
+        lu, _ = O.arrlu(A4, [1], [1], leftorthogonal=leftorthogonal, seed=seed)
+        assert lu.L.shape[0] == 4 and lu.U.shape[1] == 4
+        unit, other = (lu.L, lu.U) if leftorthogonal else (lu.U.T, lu.L.T)
+        assert np.all(np.tril(lu.L) == lu.L) and np.all(np.triu(lu.U) == lu.U)
+        assert np.all(np.diag(unit) == 1.0) and other.shape[0] == 4
+        assert np.allclose(lu.left() @ lu.right(), A4, rtol=1e-13, atol=0)
+
+
+def test_arrlu_lowrank_samples_few_elements():
+    rng = np.random.default_rng(3)
+    B = rng.standard_normal((300, 7)) @ rng.standard_normal((7, 400))
+    lu, nev = O.arrlu(B, [1], [1], reltol=1e-10, seed=11)
+    assert lu.npivot == 7
+    assert nev < 0.35 * B.size                           # the point of the rook search: most of the matrix is never sampled
+    assert np.allclose(lu.left() @ lu.right(), B, rtol=0, atol=1e-10 * np.abs(B).max())
+    assert sorted(lu.rowpermutation) == list(range(1, 301)) and sorted(lu.colpermutation) == list(range(1, 401))
+
+
+def test_lorentz_5site_linkdims_rook():                 # test/test_tensorci2.jl:247-273, pivotsearch=:rook
+    n = 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci = O.TCI2(f, [10] * n)
+    tci.set_pivotsearch("rook", seed=7)
+    for p in range(1, n):
+        tci.updatepivots(p, True, reltol=1e-8, maxbonddim=2)
+    assert tci.linkdims() == [2] * (n - 1) and tci.rank() == 2
+    tci.addglobalpivots1sitesweep([[2, 9, 10, 5, 7]], reltol=1e-12)
+    assert tci.linkdims() == [3] * (n - 1) and tci.rank() == 3
+    for _ in range(4, 21):
+        for p in range(1, n):
+            tci.updatepivots(p, True, reltol=1e-8)
+    assert len(tci.Iset(1)) == 1 and len(tci.Jset(n)) == 1
+
+
+def test_lorentz_5site_tolerance_rook():                # test/test_tensorci2.jl:297-339, pivotsearch=:rook
+    n = 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    tci3, ranks, errors = O.crossinterpolate2(f, [10] * n, [[1] * n], tolerance=1e-12, maxiter=200, pivotsearch="rook", seed=1)
+    assert tci3.pivoterror() <= 2e-12 and tci3.rank() <= 200
+    for v in itertools.product(range(1, 4), repeat=n):
+        assert tci3.evaluate(v) == pytest.approx(f(v), rel=1e-8)
