@@ -167,8 +167,8 @@ def rrlu_last_timing(handle=None):
 # ---- rook pivot search: arrlu (matrixlu.jl:500-569) -------------------------------------------------------------------
 class Rng:
     """Counter-based splitmix64 stream behind `pushrandomsubset!` (util.jl:173-219).  The reference draws from Julia's
-    global RNG, whose stream has no portable restatement; the oracle (oracle/tci_oracle.cpp `Rng`) uses this same
-    generator, so product and oracle pick identical random rows/columns for a given seed."""
+    global RNG, whose stream has no portable restatement; the CPU checker under tests/ restates this same generator, so
+    both pick identical random rows/columns for a given seed."""
     MASK = (1 << 64) - 1
 
     def __init__(self, seed=0):
