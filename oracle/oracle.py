@@ -414,3 +414,42 @@ def tt_evaluate(cores, points):
     _check(lib().orc_tt_evaluate(_p(flat, C.c_double), _p(shapes, C.c_int64), len(cores), _p(pts, C.c_int32),
                                  C.c_int64(len(pts)), _p(out, C.c_double)))
     return out
+
+
+# ---- integrate (src/integration.jl:68-161) -------------------------------------------------------------------------
+# QuadGK.kronrod(7, -1, +1) (integration.jl:63; QuadGK.jl is a registry dependency, not in the reference tree): the 15-point
+# Gauss–Kronrod rule.  The constants below are the published QUADPACK qk15 values (positive half, centre last).
+_QK15_X = [0.991455371120812639206854697526329, 0.949107912342758524526189684047851, 0.864864423359769072789712788640926,
+           0.741531185599394439863864773280788, 0.586087235467691130294144838258730, 0.405845151377397166906606412076961,
+           0.207784955007898467600689403773245, 0.0]
+_QK15_W = [0.022935322010529224963732008058970, 0.063092092629978553290700663189204, 0.104790010322250183839876322541518,
+           0.140653259715525918745189590510238, 0.169004726639267902826583426598550, 0.190350578064785409913256402421014,
+           0.204432940075298892414161999234649, 0.209482141084727828012999174891714]
+
+
+def kronrod15():
+    x = np.array([-v for v in _QK15_X] + _QK15_X[-2::-1])
+    w = np.array(_QK15_W + _QK15_W[-2::-1])
+    return x, w
+
+
+def integrate(f, a, b, **kw):
+    """integrate(Float64, f, a, b; GKorder=15, kwargs...) with nsearchglobalpivot=0 (the oracle has no global search)."""
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    if len(a) != len(b):
+        raise OracleError(f"Integral bounds must have the same dimensionality, but got {len(a)} lower bounds and {len(b)} upper bounds.")
+    x1, w1 = kronrod15()
+    N = len(a)
+    nodes = (b - a)[:, None] * (x1[None, :] + 1.0) / 2.0 + a[:, None]
+    weights = (b - a)[:, None] * w1[None, :] / 2.0
+    normalization = 15.0 ** N
+
+    def F(indices):
+        x = [float(nodes[n, i - 1]) for n, i in enumerate(indices)]
+        w = 1.0
+        for n, i in enumerate(indices):
+            w = w * float(weights[n, i - 1])
+        return w * f(x) * normalization
+
+    tci, ranks, errors = crossinterpolate2(Func(F_CALLBACK, callback=F), [15] * N, **kw)
+    return tt_sum(tci.sitetensors()) / normalization

@@ -191,3 +191,34 @@ def test_lorentz_5site_tolerance_rook():                # test/test_tensorci2.jl
     assert tci3.pivoterror() <= 2e-12 and tci3.rank() <= 200
     for v in itertools.product(range(1, 4), repeat=n):
         assert tci3.evaluate(v) == pytest.approx(f(v), rel=1e-8)
+
+
+# ---- integrate (src/integration.jl, test/test_integration.jl) ---------------------------------------------------------
+POLY = [0.23637074801483304, 0.20661524945577847, 0.1850826417895819, 0.8433788714289417, 0.5801482873508491,
+        0.20339438932656262, 0.21593267492457668, 0.8052490409622802, 0.7189346124875339, 0.9400806688257749,
+        0.355210845205325, 0.5251561513473092, 0.6819965273401778, 0.9221987248861162, 0.04166444723413998]
+
+
+def _poly(x):
+    return sum(c * x ** i for i, c in enumerate(POLY))
+
+
+def _polyint(x):
+    return sum(c * x ** (i + 1) / (i + 1) for i, c in enumerate(POLY))
+
+
+def test_integrate_polynomials():                       # test/test_integration.jl:5-29
+    N = 5
+    f = lambda x: float(np.prod([_poly(v) for v in x]))
+    assert O.integrate(f, [0.0] * N, [1.0] * N) == pytest.approx(_polyint(1.0) ** N, rel=1e-8)
+    rng = np.random.default_rng(1234)
+    a, b = rng.random(N), rng.random(N)
+    exact = float(np.prod([_polyint(v) - _polyint(u) for u, v in zip(a, b)]))
+    assert O.integrate(f, a, b) == pytest.approx(exact, rel=1e-8)
+
+
+def test_kronrod15_rule_is_exact_to_degree_22():
+    x, w = O.kronrod15()
+    assert np.all(np.diff(x) > 0) and abs(w.sum() - 2.0) < 1e-15
+    for k in range(0, 23, 2):
+        assert abs(np.sum(w * x ** k) - 2.0 / (k + 1)) < 1e-14
