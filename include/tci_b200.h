@@ -179,12 +179,23 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
 int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb, const double* d_P, int64_t r, int64_t ldp,
                         double* d_X, int64_t ldx);
 
+/* ---- Thin SVD ---------------------------------------------------------------------------------------
+ * Replaces  LinearAlgebra.svd(A)  in _factorize(A, :SVD)  src/tensortrain.jl:244-262 (used by compress!(tt, :SVD) :302-348,
+ * add/subtract src/abstracttensortrain.jl:524-545, contract_naive/contract_zipup src/contraction.jl:616-637, :751-788).
+ * A (m x n, ld lda, OVERWRITTEN) = U diag(S) Vt with k = min(m, n): d_U (m x k, ld ldu), h_S[k] in descending order,
+ * d_Vt (k x n, ld ldvt); d_U / d_Vt may be NULL.  One-sided Jacobi rotations (csrc/svd.cu); columns of U that belong to an
+ * exactly zero singular value are zero.  h_sweeps (may be NULL) receives the number of Jacobi sweeps. */
+int tci_svd_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_t lda, double* d_U, int64_t ldu, double* h_S,
+                double* d_Vt, int64_t ldvt, int* h_sweeps);
+/* M[i, j] *= s[i] (by_rows != 0) or s[j]: the `Diagonal(S) * Vt` / `U * Diagonal(S)` of src/tensortrain.jl:252-259. */
+int tci_diag_scale_f64(tci_handle h, double* d_M, int64_t rows, int64_t cols, int64_t ld, const double* h_s, int by_rows);
+
 /* ---- K4c support: strided tensor copies, element-wise maps, permutation scatters ---------------------------
  * tci_strided_copy_f64: out (dense column-major, extents h_shape[0..ndim), first index fastest) <- the view of d_in
  *   that starts at element in_offset and has element stride h_in_strides[k] along output dimension k (ndim <= 8).
  *   Replaces `permutedims` and slicing around the GEMMs of the contraction code (src/contraction.jl:211-212, :256-258,
  *   :541-556, :595, :770).
- * tci_elementwise_f64: x <- g(x) in place; kind 1: p0*x + p1, 2: x^2 (abs2), 3: |x|, 4: exp(p0*x).  Replaces the
+ * tci_elementwise_f64: x <- g(x) in place; kind 1: p0*x + p1, 2: x^2 (abs2), 3: |x|, 4: exp(p0*x), 5: x / p0.  Replaces the
  *   `res .= obj.f.(res)` of Contraction.batchevaluate (src/contraction.jl:569-571) for the maps the tests use.
  * tci_unpermute_f64: out[perm[i], :] = in[i, :] (by_rows != 0) or out[:, perm[j]] = in[:, j]; h_perm 1-based.
  *   Replaces left(lu; permute=true) / right(lu; permute=true) (src/matrixlu.jl:716-746). */

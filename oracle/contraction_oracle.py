@@ -138,13 +138,73 @@ def _factorize(A, method, tolerance, maxbonddim, leftorthogonal=False, normalize
     else:
         abstol = tolerance
     mr = O.INT64_MAX if maxbonddim is None else maxbonddim
-    lu = O.rrlu(np.asfortranarray(A), maxrank=mr, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal)
-    if method == "LU":
-        return lu.left(), lu.right(), lu.npivot
-    if method == "CI":
+    if method in ("LU", "CI"):
+        lu = O.rrlu(np.asfortranarray(A), maxrank=mr, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal)
+        if method == "LU":
+            return lu.left(), lu.right(), lu.npivot
         left, right = lu.luci_factors()
         return left, right, lu.npivot
+    if method == "SVD":                                                  # tensortrain.jl:244-262 (LinearAlgebra.svd = LAPACK gesdd)
+        U, S, Vt = np.linalg.svd(np.asarray(A, dtype=np.float64), full_matrices=False)
+        err = np.array([np.sum(S[n + 1:] ** 2) for n in range(len(S))])
+        with np.errstate(divide="ignore", invalid="ignore"):
+            nerr = err / np.sum(S ** 2)
+
+        def first(mask):                                                 # replacenothing(findfirst(...), length(err))
+            w = np.nonzero(mask)[0]
+            return int(w[0]) + 1 if len(w) else len(S)
+        trunci = min(first(err < abstol ** 2), first(nerr < reltol ** 2), mr)
+        if leftorthogonal:
+            return U[:, :trunci], np.diag(S[:trunci]) @ Vt[:trunci, :], trunci
+        return U[:, :trunci] @ np.diag(S[:trunci]), Vt[:trunci, :], trunci
     raise NotImplementedError(method)
+
+
+def _addtttensor(A, B, factorA=1.0, factorB=1.0, lefttensor=False, righttensor=False):   # abstracttensortrain.jl:467-485
+    if A.ndim != B.ndim:
+        raise ValueError("Elementwise addition only works if both tensors have the same indices")
+    off1 = 0 if lefttensor else A.shape[0]
+    off3 = 0 if righttensor else A.shape[-1]
+    C = np.zeros((off1 + B.shape[0],) + A.shape[1:-1] + (off3 + B.shape[-1],))
+    C[: A.shape[0], ..., : A.shape[-1]] = factorA * A
+    C[off1:, ..., off3:] = factorB * B
+    return C
+
+
+def add(lhs, rhs, factorlhs=1.0, factorrhs=1.0, tolerance=0.0, maxbonddim=None):          # abstracttensortrain.jl:524-545
+    if len(lhs) != len(rhs):
+        raise ValueError("Two tensor trains with different length cannot be added elementwise.")
+    L = len(lhs)
+    tt = [_addtttensor(lhs[e], rhs[e], factorA=factorlhs if e == L - 1 else 1.0, factorB=factorrhs if e == L - 1 else 1.0,
+                       lefttensor=e == 0, righttensor=e == L - 1) for e in range(L)]
+    return compress(tt, "SVD", tolerance=tolerance, maxbonddim=maxbonddim)
+
+
+def subtract(lhs, rhs, tolerance=0.0, maxbonddim=None):                                   # :560-565
+    return add(lhs, rhs, factorrhs=-1.0, tolerance=tolerance, maxbonddim=maxbonddim)
+
+
+def norm2(tt):                                                                            # :625-634, literally
+    def _f(t):
+        t3 = t.reshape((t.shape[0], -1, t.shape[-1]), order="F")
+        tct = np.transpose(_contract(t3, t3, (2,), (2,)), (0, 2, 1, 3))
+        return tct.reshape((tct.shape[0] * tct.shape[1], tct.shape[2] * tct.shape[3]), order="F")
+    acc = _f(tt[0])
+    for t in tt[1:]:
+        acc = acc @ _f(t)
+    assert acc.shape == (1, 1)
+    return float(acc[0, 0])
+
+
+def reverse(tt):                                                                          # tensortrain.jl:452-456
+    return [np.transpose(T, (T.ndim - 1,) + tuple(range(1, T.ndim - 1)) + (0,)) for T in reversed(tt)]
+
+
+def fulltensor(tt):
+    res = tt[0]
+    for t in tt[1:]:
+        res = np.tensordot(res, t, axes=([res.ndim - 1], [0]))
+    return res.reshape(res.shape[1:-1])
 
 
 def compress(cores, method="LU", tolerance=1e-12, maxbonddim=None, normalizeerror=True):          # tensortrain.jl:302-348
@@ -172,14 +232,14 @@ def _contractsitetensors(a, b):                                          # contr
     return abp.reshape((a.shape[0] * b.shape[0], a.shape[1], b.shape[2], a.shape[3] * b.shape[3]), order="F")
 
 
-def contract_naive(a, b, tolerance=0.0, maxbonddim=None, method="LU"):   # contraction.jl:616-637 (LU/CI compression only)
+def contract_naive(a, b, tolerance=0.0, maxbonddim=None, method="SVD"):  # contraction.jl:616-637 (the reference compresses with :SVD)
     tt = [_contractsitetensors(x, y) for x, y in zip(a, b)]
     if tolerance > 0 or maxbonddim is not None:
         tt = compress(tt, method, tolerance=tolerance, maxbonddim=maxbonddim)
     return tt
 
 
-def contract_zipup(A, B, tolerance=1e-12, method="LU", maxbonddim=None):  # contraction.jl:751-788
+def contract_zipup(A, B, tolerance=1e-12, method="SVD", maxbonddim=None):  # contraction.jl:751-788
     R = np.ones((1, 1, 1))
     out = []
     N = len(A)

@@ -8,12 +8,12 @@ raises if the library or a CUDA device is missing — there is no CPU fallback.
 from ._lib import Handle, TCIError, default_handle, lib, SO_PATH          # noqa: F401
 from .matrixlu import (rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing, arrlu, rrlu_function, Rng,   # noqa: F401
                        pushrandomsubset)
-from .dense import Mat, gemm, luci_factors, solve_right, trsm_right                              # noqa: F401
+from .dense import Mat, gemm, luci_factors, solve_right, trsm_right, svd, diag_scale                              # noqa: F401
 from .matrixluci import MatrixLUCI                                                  # noqa: F401
 from .batcheval import (BatchEvaluator, BuiltinFunction, LorentzFunction, SumFunction, QuanticsExpSin,          # noqa: F401
                         QuanticsExpPlusSin, QuanticsExp2, DenseFunction, HashFunction, UserFunction, filltensor,
                         _batchevaluate_dispatch, to_numpy)
-from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain, compress, _factorize                       # noqa: F401
+from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain, compress, _factorize, add, subtract, norm2, norm, _addtttensor                       # noqa: F401
 from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecriterion, kronecker_left,      # noqa: F401
                         kronecker_right, DefaultGlobalPivotFinder, GlobalPivotSearchInput, forwardsweep,
                         HostFunctionAdapter, makebatchevaluatable, optfirstpivot)

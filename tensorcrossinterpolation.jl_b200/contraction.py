@@ -254,10 +254,9 @@ def _contractsitetensors(a, b, h):                                      # contra
     return abp.reshape((a.shape[0] * b.shape[0], a.shape[1], b.shape[2], a.shape[3] * b.shape[3]), h)
 
 
-def contract_naive(a, b=None, tolerance=0.0, maxbonddim=None, method="LU"):
-    """contract_naive (contraction.jl:616-637).  DEVIATION: when a tolerance or maxbonddim is given the reference
-    compresses with :SVD (LAPACK); this build has no GPU SVD and compresses with the rrLU (`method` 'LU' or 'CI') instead —
-    the same tensor train up to the tolerance, in another gauge."""
+def contract_naive(a, b=None, tolerance=0.0, maxbonddim=None, method="SVD"):
+    """contract_naive (contraction.jl:616-637): site-wise product, then compress!(tt, :SVD; tolerance, maxbonddim) when a
+    tolerance or maxbonddim is given (`method` 'LU'/'CI' selects the rrLU compression instead; not a reference option)."""
     obj = a if isinstance(a, Contraction) else Contraction(a, b)
     if obj.f is not None:
         raise TCIError(_lib.TCI_ERR_INVALID, "Naive contraction implementation cannot contract matrix product with a function. "
@@ -269,9 +268,8 @@ def contract_naive(a, b=None, tolerance=0.0, maxbonddim=None, method="LU"):
     return tt
 
 
-def contract_zipup(A, B, tolerance=1e-12, method="LU", maxbonddim=None):
-    """contract_zipup (contraction.jl:751-788); method 'LU' | 'CI'.  DEVIATION: the reference's default method is :SVD,
-    which is outside this build (no GPU SVD); the default here is 'LU' (contraction.jl:778 with method=:LU)."""
+def contract_zipup(A, B, tolerance=1e-12, method="SVD", maxbonddim=None):
+    """contract_zipup (contraction.jl:751-788); method 'SVD' (default, like the reference) | 'LU' | 'CI'."""
     if len(A) != len(B):
         raise TCIError(_lib.TCI_ERR_INVALID, "Cannot contract tensor trains with different length.")
     h = A.handle

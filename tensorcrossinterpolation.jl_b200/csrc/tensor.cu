@@ -79,6 +79,7 @@ __global__ void elementwise_kernel(double* __restrict__ x, long long n, int kind
         case 2: r = v * v; break;                // abs2
         case 3: r = fabs(v); break;              // abs
         case 4: r = exp(p0 * v); break;
+        case 5: r = v / p0; break;               // true division (divide!, tensortrain.jl:412-415)
         default: r = v;
         }
         x[t] = r;
@@ -161,7 +162,7 @@ int tci_strided_copy_f64(tci_handle h, const double* d_in, int64_t in_offset, co
 
 int tci_elementwise_f64(tci_handle h, int kind, double p0, double p1, double* d_x, int64_t n) {
     if (!h) return TCI_ERR_INVALID;
-    if (kind < 1 || kind > 4) return tci_fail(h, TCI_ERR_INVALID, "tci_elementwise_f64: unknown kind %d", kind);
+    if (kind < 1 || kind > 5) return tci_fail(h, TCI_ERR_INVALID, "tci_elementwise_f64: unknown kind %d", kind);
     if (n <= 0) return TCI_OK;
     if (!d_x) return tci_fail(h, TCI_ERR_INVALID, "tci_elementwise_f64: NULL buffer");
     TCI_CUDA(h, cudaSetDevice(h->device));

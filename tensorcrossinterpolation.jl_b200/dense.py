@@ -99,3 +99,26 @@ def trsm_right(h, T, r, lower, unit, B, left=False):
         h.check(lib().tci_trsm_right_f64(h.h, T.ptr, C.c_int64(1), C.c_int64(T.ld), C.c_int64(r), int(bool(lower)), int(bool(unit)),
                                          B.ptr, C.c_int64(1), C.c_int64(B.ld), C.c_int64(B.rows)))
     return B
+
+
+def svd(h, A):
+    """Thin SVD of the device matrix A (consumed): (U Mat m x k, S numpy[k] descending, Vt Mat k x n) — tci_svd_f64,
+    replaces LinearAlgebra.svd(A) (tensortrain.jl:244)."""
+    m, n = A.rows, A.cols
+    k = min(m, n)
+    dev = A.buf.device
+    U, Vt = Mat.empty(m, max(k, 1), dev), Mat.empty(max(k, 1), n, dev)
+    S = np.zeros(max(k, 1))
+    sweeps = C.c_int()
+    h.check(lib().tci_svd_f64(h.h, A.ptr, C.c_int64(m), C.c_int64(n), C.c_int64(A.ld), U.ptr, C.c_int64(U.ld),
+                              S.ctypes.data_as(C.POINTER(C.c_double)), Vt.ptr, C.c_int64(Vt.ld), C.byref(sweeps)))
+    U.cols, Vt.rows = k, k
+    return U, S[:k], Vt
+
+
+def diag_scale(h, M, s, by_rows):
+    """M[i, j] *= s[i] (by_rows) or s[j], in place — tci_diag_scale_f64."""
+    s = np.ascontiguousarray(s, dtype=np.float64)
+    h.check(lib().tci_diag_scale_f64(h.h, M.ptr, C.c_int64(M.rows), C.c_int64(M.cols), C.c_int64(M.ld),
+                                     s.ctypes.data_as(C.POINTER(C.c_double)), 1 if by_rows else 0))
+    return M

@@ -137,6 +137,48 @@ class TensorTrain(AbstractTensorTrain):
     def compress(self, method="LU", tolerance=1e-12, maxbonddim=None, normalizeerror=True):   # compress! tensortrain.jl:302
         return compress(self, method, tolerance, maxbonddim, normalizeerror)
 
+    def copy(self):                                        # deepcopy(tt)
+        return TensorTrain([DeviceCore(Mat(c.mat.buf.clone(), c.mat.rows, c.mat.cols), c.chil, c.sitedims, c.chir) for c in self._cores],
+                           handle=self.handle)
+
+    def multiply_(self, a):                                # multiply!(tt, a) — tensortrain.jl:359-368: scales the LAST core
+        c = self._cores[-1]
+        self.handle.check(lib().tci_elementwise_f64(self.handle.h, 1, C.c_double(float(a)), C.c_double(0.0), c.mat.ptr,
+                                                    C.c_int64(c.mat.buf.numel())))
+
+    def divide_(self, a):                                  # divide!(tt, a) — tensortrain.jl:412-415
+        c = self._cores[-1]                                # true division, like `./ a`
+        self.handle.check(lib().tci_elementwise_f64(self.handle.h, 5, C.c_double(float(a)), C.c_double(0.0), c.mat.ptr,
+                                                    C.c_int64(c.mat.buf.numel())))
+
+    def multiply(self, a):                                 # :375-384
+        t = self.copy(); t.multiply_(a); return t
+
+    def divide(self, a):                                   # :422-426
+        t = self.copy(); t.divide_(a); return t
+
+    def __mul__(self, a):                                  # :399-405
+        return self.multiply(a)
+
+    __rmul__ = __mul__
+
+    def __truediv__(self, a):                              # :433-435
+        return self.divide(a)
+
+    def __add__(self, other):                              # abstracttensortrain.jl:578-580
+        return add(self, other)
+
+    def __sub__(self, other):                              # :590-592
+        return subtract(self, other)
+
+    def reverse(self):                                     # Base.reverse — tensortrain.jl:452-456
+        out = []
+        for c in reversed(self._cores):                    # permutedims(T, (N, 2:N-1..., 1)): swap the two bond legs (device copy)
+            m = _dense_copy(self.handle, c.mat)
+            t = m.buf.reshape(-1)[: c.chil * c.d * c.chir].reshape(c.chir, c.d, c.chil).permute(2, 1, 0).contiguous()
+            out.append(DeviceCore(Mat(t.reshape(c.chil, c.d * c.chir), c.chir * c.d, c.chil), c.chir, c.sitedims, c.chil))
+        return TensorTrain(out, handle=self.handle)
+
     def fulltensor(self):                                  # tensortrain.jl:580-600 (small trains only; host reshape)
         from .dense import gemm
         h = self.handle
@@ -152,6 +194,77 @@ class TensorTrain(AbstractTensorTrain):
             res = Mat.from_numpy(prod.numpy().reshape(left, c.chir, order="F"), res.buf.device)
         dims = [d for c in cores for d in c.sitedims]
         return res.numpy().reshape(dims, order="F")
+
+
+def _addtttensor(A, B, factorA=1.0, factorB=1.0, lefttensor=False, righttensor=False, handle=None):
+    """_addtttensor (abstracttensortrain.jl:467-485): block-diagonal stacking [factorA*A 0; 0 factorB*B] of two device cores
+    (first/last cores stack along one bond only).  Data movement (torch slice copies) + the affine element-wise kernel."""
+    import torch
+    h = handle or _lib.default_handle()
+    if len(A.sitedims) != len(B.sitedims):
+        raise TCIError(_lib.TCI_ERR_INVALID, "Elementwise addition only works if both tensors have the same indices, but A and B "
+                       f"have different numbers ({len(A.sitedims) + 2} and {len(B.sitedims) + 2}) of indices.")
+    if tuple(A.sitedims) != tuple(B.sitedims):
+        raise TCIError(_lib.TCI_ERR_INVALID, "Elementwise addition only works if both tensors have the same local dimensions.")
+    off1 = 0 if lefttensor else A.chil
+    off3 = 0 if righttensor else A.chir
+    cl, cr, d = off1 + B.chil, off3 + B.chir, A.d
+    out = torch.zeros((cr, d, cl), dtype=torch.float64, device=A.mat.buf.device)      # memory of the (cl, d, cr) column-major core
+
+    def block(core):
+        return _dense_copy(h, core.mat).buf.reshape(-1)[: core.chil * core.d * core.chir].reshape(core.chir, core.d, core.chil)
+
+    def scaled(core, factor):
+        t = block(core).clone()
+        if factor != 1.0:
+            h.check(lib().tci_elementwise_f64(h.h, 1, C.c_double(factor), C.c_double(0.0), C.c_void_p(t.data_ptr()), C.c_int64(t.numel())))
+        return t
+    out[: A.chir, :, : A.chil].copy_(scaled(A, factorA))             # :482
+    out[off3:, :, off1:].copy_(scaled(B, factorB))                   # :483
+    return DeviceCore(Mat(out.reshape(cr, d * cl), cl * d, cr), cl, A.sitedims, cr)
+
+
+def add(lhs, rhs, factorlhs=1.0, factorrhs=1.0, tolerance=0.0, maxbonddim=None):
+    """add(lhs, rhs; factorlhs, factorrhs, tolerance, maxbonddim) — abstracttensortrain.jl:524-545 (then compress!(:SVD))."""
+    if len(lhs) != len(rhs):
+        raise TCIError(_lib.TCI_ERR_INVALID, f"Two tensor trains with different length ({len(lhs)} and {len(rhs)}) cannot be added elementwise.")
+    L = len(lhs)
+    h = lhs.handle or _lib.default_handle()
+    a, b = lhs._dev_cores(), rhs._dev_cores()
+    tt = TensorTrain([_addtttensor(a[ell], b[ell], factorA=factorlhs if ell == L - 1 else 1.0,
+                                   factorB=factorrhs if ell == L - 1 else 1.0, lefttensor=ell == 0, righttensor=ell == L - 1,
+                                   handle=h) for ell in range(L)], handle=h)
+    compress(tt, "SVD", tolerance=tolerance, maxbonddim=maxbonddim)
+    return tt
+
+
+def subtract(lhs, rhs, tolerance=0.0, maxbonddim=None):     # abstracttensortrain.jl:560-565
+    return add(lhs, rhs, factorrhs=-1.0, tolerance=tolerance, maxbonddim=maxbonddim)
+
+
+def norm2(tt):
+    """LA.norm2(tt) — abstracttensortrain.jl:625-634: sum of |f|^2 over all indices.  The reference multiplies the
+    (chi^2 x chi^2) transfer matrices; here the same contraction runs as a left-to-right environment
+    E <- sum_s T_s^T E T_s (two GEMMs per site, chi^3 d work instead of chi^4 d)."""
+    from .dense import gemm
+    import torch
+    h = tt.handle or _lib.default_handle()
+    cores = tt._dev_cores()
+    dev = cores[0].mat.buf.device
+    E = Mat(torch.ones((1, 1), dtype=torch.float64, device=dev), 1, 1)
+    if cores[0].chil != 1 or cores[-1].chir != 1:
+        raise TCIError(_lib.TCI_ERR_INVALID, "norm2: the tensor train must have boundary bond dimensions 1")
+    for c in cores:
+        T = _dense_copy(h, c.mat)                          # (chil*d) x chir
+        Tw = Mat(T.buf.reshape(-1)[: c.chil * c.d * c.chir].reshape(c.d * c.chir, c.chil), c.chil, c.d * c.chir)   # chil x (d*chir)
+        X = gemm(h, E, Tw)                                 # E (chil x chil) * T (chil x d*chir)
+        Xm = Mat(X.buf.reshape(-1)[: c.chil * c.d * c.chir].reshape(c.chir, c.chil * c.d), c.chil * c.d, c.chir)  # (chil*d) x chir
+        E = gemm(h, T, Xm, transa=True)                    # T^T (chir x chil*d) * X
+    return float(E.numpy()[0, 0])
+
+
+def norm(tt):                                              # abstracttensortrain.jl:646-648
+    return float(np.sqrt(norm2(tt)))
 
 
 def tensortrain(tci):                                      # tensortrain.jl:187-189
@@ -170,8 +283,8 @@ def _unpermute(h, M, perm, by_rows):
 
 def _factorize(A, method, tolerance, maxbonddim, leftorthogonal=False, normalizeerror=True, handle=None):
     """_factorize(A, method; tolerance, maxbonddim, leftorthogonal, normalizeerror) — tensortrain.jl:219-272.
-    A: device `Mat` (consumed).  Returns (left Mat m x r, right Mat r x n, r).  method 'LU' or 'CI'; 'SVD' (LAPACK gesdd in
-    the reference) is outside this build's scope."""
+    A: device `Mat` (consumed).  Returns (left Mat m x r, right Mat r x n, r).  method 'LU', 'CI' or 'SVD' (one-sided Jacobi
+    on the device, csrc/svd.cu, where the reference calls LAPACK gesdd)."""
     from .matrixlu import INT_MAX, rrlu_device
     from .matrixluci import MatrixLUCI
     h = handle or _lib.default_handle()
@@ -188,8 +301,25 @@ def _factorize(A, method, tolerance, maxbonddim, leftorthogonal=False, normalize
     if method == "CI":
         luci = MatrixLUCI(A, maxrank=maxrank, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal, handle=h)
         return luci.left_mat(), luci.right_mat(), luci.npivots()
-    if method == "SVD":
-        raise TCIError(_lib.TCI_ERR_INVALID, "method=:SVD is not implemented in this build (no GPU SVD on the TCI2 hot path); use :LU or :CI")
+    if method == "SVD":                                    # tensortrain.jl:244-262
+        from .dense import diag_scale, svd
+        U, S, Vt = svd(h, A)
+        S2 = S * S
+        err = np.array([np.sum(S2[i + 1:]) for i in range(len(S))])          # err[n] = sum(S[n+1:end].^2)
+        tot = np.sum(S2)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            nerr = err / tot
+        def first(mask):                                   # replacenothing(findfirst(...), length)
+            w = np.nonzero(mask)[0]
+            return int(w[0]) + 1 if len(w) else len(S)
+        trunci = min(first(err < abstol ** 2), first(nerr < reltol ** 2), maxrank)
+        left = Mat(U.buf[:max(trunci, 1)], U.rows, trunci)
+        right = Vt if trunci == Vt.rows else Mat(Vt.buf[:, :max(trunci, 1)].contiguous(), trunci, Vt.cols)   # Vt[1:trunci, :]
+        if leftorthogonal:
+            diag_scale(h, right, S[:trunci], True)
+        else:
+            diag_scale(h, left, S[:trunci], False)
+        return left, right, trunci
     raise TCIError(_lib.TCI_ERR_INVALID, "Not implemented yet.")
 
 

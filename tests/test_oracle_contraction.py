@@ -77,3 +77,63 @@ def test_mpo_mps():                                        # test/test_contracti
     v = [rng.standard_normal((bonds[n], 3, 1, bonds[n + 1])) for n in range(4)]      # MPS as an MPO with a unit leg
     res = CO.contract_naive(a, v)
     assert np.allclose(CO.tomat(res), CO.tomat(a) @ CO.tomat(v), atol=1e-12)
+
+
+# ---- SVD factorisation and tensor-train arithmetic (tensortrain.jl:244-262, abstracttensortrain.jl:467-648) -----------
+def _tt(rng, linkdims, localdims):
+    return [rng.standard_normal((linkdims[n], localdims[n], linkdims[n + 1])) for n in range(len(localdims))]
+
+
+def test_add_multiply_subtract():                          # test/test_tensortrain.jl:166-199
+    rng = np.random.default_rng(10)
+    t1, t2 = _tt(rng, [1, 2, 3, 1], [2, 2, 2]), _tt(rng, [1, 2, 3, 1], [2, 2, 2])
+    f1, f2 = CO.fulltensor(t1), CO.fulltensor(t2)
+    assert np.allclose(CO.fulltensor(CO.add(t1, t2)), f1 + f2, rtol=1e-12, atol=1e-13)
+    half = [c.copy() for c in t1]
+    half[-1] = half[-1] * 1.6 / 3.2
+    assert np.allclose(CO.fulltensor(CO.subtract(t1, half)), f1 / 2.0, rtol=1e-12, atol=1e-13)
+    with pytest.raises(ValueError):
+        CO.add(t1, t1[:-1])
+    ml = [rng.standard_normal((l, 2, 2, r)) for l, r in [(1, 2), (2, 3), (3, 1)]]
+    assert np.allclose(CO.fulltensor(CO.add(ml, ml)), 2 * CO.fulltensor(ml), rtol=1e-12, atol=1e-13)
+
+
+def test_norm():                                           # test/test_tensortrain.jl:201-214
+    rng = np.random.default_rng(3)
+    t = _tt(rng, [1, 3, 4, 2, 1], [2, 3, 2, 3])
+    full = CO.fulltensor(t)
+    assert CO.norm2(t) == pytest.approx(float(np.sum(full ** 2)), rel=1e-13)
+    assert CO.norm2(CO.reverse(t)) == pytest.approx(CO.norm2(t), rel=1e-13)
+
+
+def test_compress_svd():                                   # test/test_tensortrain.jl:216-239
+    rng = np.random.default_rng(10)
+    N, chi, tol = 10, 10, 0.1
+    bond = [1] + [chi] * (N - 1) + [1]
+    tt = [rng.standard_normal((bond[n], 2, bond[n + 1])) for n in range(N)]
+    comp = CO.compress(tt, "SVD", tolerance=tol)
+    assert np.sqrt(CO.norm2(CO.subtract(tt, comp)) / CO.norm2(tt)) < np.sqrt(N) * tol
+    comp2 = CO.compress(tt, "SVD", tolerance=np.sqrt(CO.norm2(tt)) * tol, normalizeerror=False)
+    assert np.sqrt(CO.norm2(CO.subtract(tt, comp2)) / CO.norm2(tt)) < np.sqrt(N) * tol
+    assert max(c.shape[-1] for c in comp) < chi
+
+
+def test_factorize_svd_truncation_rule():                  # tensortrain.jl:246-251
+    rng = np.random.default_rng(2)
+    A = rng.standard_normal((30, 8)) @ np.diag([1, 1e-1, 1e-2, 1e-3, 1e-4, 1e-5, 1e-6, 1e-7]) @ rng.standard_normal((8, 20))
+    S = np.linalg.svd(A, compute_uv=False)
+    l, r, k = CO._factorize(A, "SVD", 0.0, None)
+    assert k == 20 and np.allclose(l @ r, A, atol=1e-13)
+    l, r, k = CO._factorize(A, "SVD", 1e-4, None, leftorthogonal=True)
+    tail = np.array([np.sum(S[n + 1:] ** 2) for n in range(len(S))]) / np.sum(S ** 2)
+    assert k == int(np.nonzero(tail < 1e-8)[0][0]) + 1
+    assert np.allclose(l.T @ l, np.eye(k), atol=1e-13)
+    l, r, k = CO._factorize(A, "SVD", 0.0, 3)
+    assert k == 3 and np.allclose(r @ r.T, np.eye(3), atol=1e-13)
+
+
+def test_zipup_and_naive_default_to_svd():                 # contraction.jl:616-637, :751-788
+    a, b = _testdata(4)
+    dense = CO.tomat(a) @ CO.tomat(b)
+    assert np.allclose(CO.tomat(CO.contract_zipup(a, b)), dense, rtol=1e-10, atol=1e-10)
+    assert np.allclose(CO.tomat(CO.contract_naive(a, b, tolerance=1e-12)), dense, rtol=1e-10, atol=1e-10)
