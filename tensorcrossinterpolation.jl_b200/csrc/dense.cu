@@ -10,6 +10,7 @@
 // the reference's `permutedims`+`reshape` views (src/contraction.jl:211-212) cost nothing.
 #include "context.h"
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 namespace {
@@ -123,6 +124,160 @@ gemm_dmma_kernel(GemmArgs g) {
             }
 }
 
+// ---- pipelined variant for large products: 128 x 64 x 16 CTA tile, 8 warps of 32 x 32, 3-stage cp.async ring -----------
+// Same fragment layout, same k order (so bit-identical results to the kernel above); the operand tiles are fetched by
+// 8-byte cp.async (any element strides; out-of-range elements are zero-filled with src-size 0) two k-tiles ahead of the
+// DMMAs, with one __syncthreads per k-tile.
+constexpr int PM = 128, PN = 64, PSTAGES = 3;
+constexpr int LDSA = 132;                                // 132 mod 16 = 4: conflict-free like LDS = 68
+constexpr int PA_DOUBLES = (BK * LDSA > PM * LDK) ? BK * LDSA : PM * LDK;     // 2560
+constexpr int PB_DOUBLES = (BK * LDS > PN * LDK) ? BK * LDS : PN * LDK;       // 1280
+constexpr int PIPE_SMEM_BYTES = PSTAGES * (PA_DOUBLES + PB_DOUBLES) * 8;      // 92160
+
+template <bool KFAST> __device__ __forceinline__ int tile_off_a(int row, int k) { return KFAST ? row * LDK + k : k * LDSA + row; }
+
+__device__ __forceinline__ void cp_async8(double* smem, const double* gptr, bool valid) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = valid ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gptr), "r"(sz) : "memory");
+}
+
+template <bool A_KFAST, bool B_KFAST>
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
+gemm_dmma_pipe_kernel(GemmArgs g) {
+    extern __shared__ __align__(16) double psm[];
+    double* As = psm;                                    // [PSTAGES][PA_DOUBLES]
+    double* Bs = psm + PSTAGES * PA_DOUBLES;             // [PSTAGES][PB_DOUBLES]
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int wm = warp & 3, wn = warp >> 2;             // warp tile: 32 rows x 32 cols
+    const int m0 = blockIdx.x * PM, n0 = blockIdx.y * PN;
+    const double* A = g.A + (long long)blockIdx.z * g.bsa;
+    const double* B = g.B + (long long)blockIdx.z * g.bsb;
+    double* C = g.C + (long long)blockIdx.z * g.bsc;
+
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    // Per-thread load plan, hoisted out of the k loop: element i of this thread's share of a tile sits at
+    // base + i * step (global) and off0 + i * sstep (shared); only the k offset changes from tile to tile.
+    const int am = A_KFAST ? (t >> 4) : (t & 127), ak = A_KFAST ? (t & 15) : (t >> 7);      // i = 0 element (row, k)
+    const int bn = B_KFAST ? (t >> 4) : (t & 63), bk = B_KFAST ? (t & 15) : (t >> 6);
+    const long long a_step = A_KFAST ? 16 * g.sam : 2 * g.sak;          // A_KFAST: row += 16 per i; else k += 2 per i
+    const long long b_step = B_KFAST ? 16 * g.sbn : 4 * g.sbk;
+    constexpr int a_sstep = A_KFAST ? 16 * LDK : 2 * LDSA;
+    constexpr int b_sstep = B_KFAST ? 16 * LDK : 4 * LDS;
+    const int a_soff = tile_off_a<A_KFAST>(am, ak), b_soff = tile_off<B_KFAST>(bn, bk);
+    const double* a_base = A + (long long)(m0 + am) * g.sam + (long long)ak * g.sak;
+    const double* b_base = B + (long long)(n0 + bn) * g.sbn + (long long)bk * g.sbk;
+    unsigned a_rows = 0, b_rows = 0;                     // bit i: the row of element i is inside the matrix
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a_rows |= ((m0 + am + (A_KFAST ? 16 * i : 0)) < g.M ? 1u : 0u) << i;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) b_rows |= ((n0 + bn + (B_KFAST ? 16 * i : 0)) < g.N ? 1u : 0u) << i;
+    const long long a_kstep = (long long)BK * g.sak, b_kstep = (long long)BK * g.sbk;
+
+    const unsigned a_saddr = (unsigned)__cvta_generic_to_shared(As + a_soff);
+    const unsigned b_saddr = (unsigned)__cvta_generic_to_shared(Bs + b_soff);
+    const bool interior = (m0 + PM <= g.M) && (n0 + PN <= g.N);       // CTA tile entirely inside C: no row checks
+    const double* a_next = a_base;                       // running pointers: the next k-tile to be loaded
+    const double* b_next = b_base;
+
+    auto load_stage = [&](int stage, int kt_) {
+        const int krem = g.K - kt_ * BK;                 // k indices < krem are valid in this tile
+        if (interior && krem >= BK) {                    // the common case: plain copies, two adds per element
+            const double* ap = a_next;
+            const double* bp = b_next;
+            const unsigned sa = a_saddr + stage * (PA_DOUBLES * 8), sb = b_saddr + stage * (PB_DOUBLES * 8);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa + i * (a_sstep * 8)), "l"(ap) : "memory");
+                ap += a_step;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sb + i * (b_sstep * 8)), "l"(bp) : "memory");
+                bp += b_step;
+            }
+        } else {
+            double* as = As + stage * PA_DOUBLES + a_soff;
+            double* bs = Bs + stage * PB_DOUBLES + b_soff;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {                // A tile: 128 x 16
+                const bool ok = ((a_rows >> i) & 1u) && (ak + (A_KFAST ? 0 : 2 * i)) < krem;
+                cp_async8(as + i * a_sstep, ok ? a_next + i * a_step : A, ok);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {                // B tile: 16 x 64
+                const bool ok = ((b_rows >> i) & 1u) && (bk + (B_KFAST ? 0 : 4 * i)) < krem;
+                cp_async8(bs + i * b_sstep, ok ? b_next + i * b_step : B, ok);
+            }
+        }
+        a_next += a_kstep;
+        b_next += b_kstep;
+    };
+
+    const int nk = (g.K + BK - 1) / BK;
+#pragma unroll
+    for (int s = 0; s < PSTAGES - 1; ++s) {
+        if (s < nk) load_stage(s, s);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int kt = 0; kt < nk; ++kt) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(PSTAGES - 2) : "memory");
+        __syncthreads();                                 // stage kt has landed for everyone; stage kt-1 is free again
+        const int nxt = kt + PSTAGES - 1;
+        if (nxt < nk) load_stage(nxt % PSTAGES, nxt);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const double* as = As + (kt % PSTAGES) * PA_DOUBLES;
+        const double* bs = Bs + (kt % PSTAGES) * PB_DOUBLES;
+#pragma unroll
+        for (int kk = 0; kk < BK; kk += 4) {
+            double a[4], b[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = as[tile_off_a<A_KFAST>(wm * 32 + i * 8 + (lane >> 2), kk + (lane & 3))];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bs[tile_off<B_KFAST>(wn * 32 + j * 8 + (lane >> 2), kk + (lane & 3))];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int gm = m0 + wm * 32 + i * 8 + (lane >> 2);
+                const int gn = n0 + wn * 32 + j * 8 + (lane & 3) * 2 + e;
+                if (gm < g.M && gn < g.N) {
+                    double* p = C + (long long)gm * g.scm + (long long)gn * g.scn;
+                    double v = g.alpha * acc[i][j][e];
+                    if (g.beta != 0.0) v += g.beta * *p;
+                    *p = v;
+                }
+            }
+}
+
+template <bool AK, bool BKF>
+int launch_pipe(tci_handle h, const GemmArgs& g, int batch) {
+    static bool optin[8] = {false, false, false, false, false, false, false, false};   // per device
+    const int dev = h->device & 7;
+    if (!optin[dev]) {
+        TCI_CUDA(h, cudaFuncSetAttribute(gemm_dmma_pipe_kernel<AK, BKF>, cudaFuncAttributeMaxDynamicSharedMemorySize, PIPE_SMEM_BYTES));
+        optin[dev] = true;
+    }
+    dim3 grid((g.M + PM - 1) / PM, (g.N + PN - 1) / PN, batch);
+    gemm_dmma_pipe_kernel<AK, BKF><<<grid, GEMM_THREADS, PIPE_SMEM_BYTES, h->stream>>>(g);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
 __global__ void copy_strided_kernel(const double* __restrict__ src, long long ssr, long long ssc, double* __restrict__ dst,
                                         long long dsr, long long dsc, int rows, int cols) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
@@ -133,6 +288,11 @@ int launch_gemm(tci_handle h, const GemmArgs& g, int batch) {
     if (g.M <= 0 || g.N <= 0 || batch <= 0) return TCI_OK;
     dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, batch);
     const bool a_kfast = (g.sak == 1) && (g.sam != 1), b_kfast = (g.sbk == 1);
+    static const int pipe_min = []() { const char* e = getenv("TCI_GEMM_PIPE_MIN"); return e ? atoi(e) : 128; }();
+    if (pipe_min >= 0 && g.M >= pipe_min && g.N >= 64 && g.K >= 64 && (long long)((g.M + PM - 1) / PM) * ((g.N + PN - 1) / PN) * batch >= 2LL * h->num_sms) {   // at least one full wave of 2 CTAs per SM
+        if (a_kfast) return b_kfast ? launch_pipe<true, true>(h, g, batch) : launch_pipe<true, false>(h, g, batch);
+        return b_kfast ? launch_pipe<false, true>(h, g, batch) : launch_pipe<false, false>(h, g, batch);
+    }
     if (a_kfast) { if (b_kfast) gemm_dmma_kernel<true, true><<<grid, GEMM_THREADS, 0, h->stream>>>(g); else gemm_dmma_kernel<true, false><<<grid, GEMM_THREADS, 0, h->stream>>>(g); }
     else         { if (b_kfast) gemm_dmma_kernel<false, true><<<grid, GEMM_THREADS, 0, h->stream>>>(g); else gemm_dmma_kernel<false, false><<<grid, GEMM_THREADS, 0, h->stream>>>(g); }
     TCI_LAUNCH_CHECK(h);
