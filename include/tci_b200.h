@@ -101,6 +101,30 @@ int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps);
 /* Per-launch update-kernel times (ms) of the last profiled rrlu; returns how many there are, copies at most cap. */
 int64_t tci_rrlu_last_launch_ms(tci_handle h, float* h_ms, int64_t cap);
 
+/* ---- Column-sharded rrLU over several GPUs (SURVEY 8e, row "rrLU"; an experiment next to the single-GPU default) ----------
+ * Same factorisation as tci_rrlu_inplace_f64 (src/matrixlu.jl:346-396), with the columns of A dealt to `nranks` GPUs:
+ * this rank holds the nloc columns [col0, col0 + nloc) as d_A (m x nloc, ld lda, overwritten).  One "record"
+ * (tci_rrlu_dist_record_doubles doubles: best local candidate + that candidate's column) per rank and pivot step is the only
+ * data exchanged; the caller gathers the records of all ranks (rank order) between the calls — an all-gather, or peer stores:
+ *     tci_rrlu_dist_search(..., d_record);                       first search
+ *     repeat maxrank times:  d_gathered <- all-gather(d_record); tci_rrlu_dist_step(..., d_gathered, d_record);
+ *     tci_rrlu_dist_finish(...)
+ * Every rank takes identical decisions (pivot choice with the reference's tie rule on the swapped column order, stop rule), so
+ * permutations, pivots and factors are bit-identical to the single-GPU call.  finish returns the full L (m x npivot) on every
+ * rank, this rank's columns of U (npivot x nloc, in LOCAL column order) and h_locpos[j] = 0-based position of local column j
+ * in the swapped order (U[:, locpos[j]] = Uloc[:, j]). */
+typedef struct tci_rrlu_dist_s* tci_rrlu_dist;
+int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64_t col0, int rank, int nranks, int64_t maxrank,
+                         double reltol, double abstol, int leftorthogonal, tci_rrlu_dist* out);
+int64_t tci_rrlu_dist_record_doubles(tci_rrlu_dist d);
+int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, double* d_record);
+int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record);
+int tci_rrlu_dist_status(tci_handle h, tci_rrlu_dist d, int64_t* h_npivot, int* h_stop);
+int tci_rrlu_dist_finish(tci_handle h, tci_rrlu_dist d, const double* d_A, int64_t lda, int64_t* h_rowperm, int64_t* h_colperm,
+                         int64_t* h_npivot, double* h_error, double* d_L, int64_t ldl, double* d_Uloc, int64_t ldu,
+                         int64_t* h_locpos, double* h_pivoterrors);
+int tci_rrlu_dist_destroy(tci_handle h, tci_rrlu_dist d);
+
 /* ---- K1: batched function evaluation + Pi assembly ------------------------------------------------
  * The target function is a DEVICE functor (the reference's `f(indexset)::Float64`, evaluated on the GPU).
  * Built-in kinds (parameters in h_params):

@@ -111,8 +111,19 @@ __global__ void rrlu_init_kernel(RrluState* st, int* rowperm, int* colperm, int 
 // steps walk the tiles backwards so that the ~L2-sized tail written by step k is the first thing
 // step k+1 reads (serpentine order: those reads, and the re-writes of the still-dirty lines, never
 // reach HBM).
+// DIST (column-sharded factorisation): local column j stands at position vpos[j] of the reference's swapped layout, and ties
+// are broken by that position instead of the local index.
 #define TCI_CONSIDER(q, val, ii, jj)                                                             \
     if ((q) > bv || ((q) == bv && ((jj) < bj || ((jj) == bj && (ii) < bi)))) { bv = (q); bx = (val); bi = (ii); bj = (jj); }
+#define TCI_CONSIDER_D(q, val, ii, jj)                                                           \
+    if ((q) > bv || ((q) == bv && (col_before<DIST>((jj), bj, vpos) || ((jj) == bj && (ii) < bi)))) { bv = (q); bx = (val); bi = (ii); bj = (jj); }
+
+struct ColOrder { const int* gid; const int* col2pos; };   // local column -> global column id -> position in the swapped order
+
+template <bool DIST> __device__ __forceinline__ bool col_before(int a, int b, const ColOrder& vpos) {
+    if (!DIST) return a < b;
+    return b < 0 ? true : vpos.col2pos[vpos.gid[a]] < vpos.col2pos[vpos.gid[b]];
+}
 
 // Loads that must see data written by OTHER blocks earlier in the same (persistent) kernel go around L1.
 template <bool NOL1> __device__ __forceinline__ double2 ld2(const double* p) {
@@ -123,11 +134,11 @@ template <bool NOL1> __device__ __forceinline__ double ld1(const double* p) { re
 // One pass of this block over its tiles of the trailing block [r0, m) x [c0, n), r0 = c0 = np.  UPDATE: apply the
 // rank-1 update of pivot k = np - 1 (scaled pivot column in A[:, k], packed pivot row in ybuf) and track the
 // abs2-argmax of the updated values; !UPDATE: search only.
-template <bool UPDATE, bool VEC, int COLS, bool NOL1>
+template <bool UPDATE, bool VEC, int COLS, bool NOL1, bool DIST = false>
 __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n, long long lda, const double* __restrict__ ybuf,
-                                           int k, int np, int serpentine, double& bv, double& bx, int& bi, int& bj) {
-    const int r0 = np, c0 = np;
-    const double* xcol = A + (long long)k * lda;    // scaled pivot column (UPDATE only)
+                                           const double* __restrict__ xcol /* scaled pivot column, indexed by row (UPDATE only) */,
+                                           int r0, int c0, int np, int serpentine, const ColOrder vpos,
+                                           double& bv, double& bx, int& bi, int& bj) {
     const bool rev = serpentine == 2 ? true : (serpentine == 3 ? !(np & 1) : (serpentine && (np & 1)));
     const int nct = (n - c0 + COLS - 1) / COLS;
     if (VEC) {
@@ -168,8 +179,8 @@ __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n,
                                 *reinterpret_cast<double2*>(A + (long long)j * lda + i0) = v;
                             }
                             const double q0 = v0 ? __dmul_rn(v.x, v.x) : -INFINITY, q1 = __dmul_rn(v.y, v.y);
-                            TCI_CONSIDER(q0, v.x, i0, j)
-                            TCI_CONSIDER(q1, v.y, i0 + 1, j)
+                            TCI_CONSIDER_D(q0, v.x, i0, j)
+                            TCI_CONSIDER_D(q1, v.y, i0 + 1, j)
                         }
                     }
                 } else {                                            // i0 == m - 1: odd tail row, scalar
@@ -183,7 +194,7 @@ __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n,
                             double v = ld1<NOL1>(A + (long long)j * lda + i);
                             if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ld1<NOL1>(ybuf + j))); A[(long long)j * lda + i] = v; }
                             const double q = __dmul_rn(v, v);
-                            TCI_CONSIDER(q, v, i, j)
+                            TCI_CONSIDER_D(q, v, i, j)
                         }
                     }
                 }
@@ -211,7 +222,7 @@ __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n,
                     double v = a[c];
                     if (UPDATE) { v = __dsub_rn(v, __dmul_rn(x, ld1<NOL1>(ybuf + j))); A[(long long)j * lda + i] = v; }
                     const double q = __dmul_rn(v, v);
-                    TCI_CONSIDER(q, v, i, j)
+                    TCI_CONSIDER_D(q, v, i, j)
                 }
             }
         }
@@ -231,7 +242,7 @@ rrlu_update_kernel(double* __restrict__ A, int m, int n, long long lda, const do
     double bv = -INFINITY, bx = 0.0;
     int bi = -1, bj = -1;
     if (np < maxrank)                                   // otherwise the loop ends; nothing reads the block
-        scan_tiles<UPDATE, VEC, COLS, false>(A, m, n, lda, ybuf, k, np, serpentine, bv, bx, bi, bj);
+        scan_tiles<UPDATE, VEC, COLS, false>(A, m, n, lda, ybuf, A + (long long)k * lda, np, np, np, serpentine, ColOrder{nullptr, nullptr}, bv, bx, bi, bj);
 
     Cand c = block_reduce(Cand{bx, bi, bj}, s_c);
     if (threadIdx.x == 0) {
@@ -444,7 +455,7 @@ rrlu_persistent_kernel(double* __restrict__ A, int m, int n, long long lda, doub
     double maxerror = 0.0, error = nan("");
     double bv = -INFINITY, bx = 0.0;
     int bi = -1, bj = -1;
-    scan_tiles<false, VEC, COLS, true>(A, m, n, lda, ybuf, 0, 0, serpentine, bv, bx, bi, bj);
+    scan_tiles<false, VEC, COLS, true>(A, m, n, lda, ybuf, A, 0, 0, 0, serpentine, ColOrder{nullptr, nullptr}, bv, bx, bi, bj);
     long long tp[6] = {0, 0, 0, 0, 0, 0}, t0 = clock64(), t1;
 #define TCI_TICK(slot) { t1 = clock64(); tp[slot] += t1 - t0; t0 = t1; }
     for (;;) {
@@ -480,7 +491,7 @@ rrlu_persistent_kernel(double* __restrict__ A, int m, int n, long long lda, doub
         np = k + 1;
         if (np >= maxrank) break;                                               // while lu.npivot < maxrank   (:356)
         bv = -INFINITY; bx = 0.0; bi = -1; bj = -1;
-        scan_tiles<true, VEC, COLS, true>(A, m, n, lda, ybuf, k, np, serpentine, bv, bx, bi, bj);
+        scan_tiles<true, VEC, COLS, true>(A, m, n, lda, ybuf, A + (long long)k * lda, np, np, np, serpentine, ColOrder{nullptr, nullptr}, bv, bx, bi, bj);
         TCI_TICK(5)
     }
 #undef TCI_TICK
@@ -606,6 +617,258 @@ int launch_persistent(tci_handle h, bool vec, const UpdateCfg& c, double* A, int
     if (c.cols == 4) return launch_persistent_t<true, 4>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
     if (c.cols == 16) return launch_persistent_t<true, 16>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
     return launch_persistent_t<true, 8>(h, A, m, n, lda, w, maxrank, reltol, abstol, leftorth, c.serpentine);
+}
+
+
+// ---- column-sharded factorisation over several GPUs (SURVEY.md 8e, row "rrLU") ----------------------------------------
+// Rank g owns nloc columns of the m x n matrix (all rows).  Per pivot step every rank
+//   1. reads the G candidate records of the previous step (its own + the peers', gathered by the host layer's collective or
+//      written by the peers into its mailbox), picks the global pivot by the reference's order (largest abs2, then smallest
+//      column POSITION in the swapped layout, then smallest row) and applies the stop rule — identically on every rank;
+//   2. swaps rows k <-> pr in its columns (and in the L columns gathered so far); the owner of the pivot column also moves
+//      that column to the front of its local trailing block (a LOCAL swap: columns never cross ranks — the reference's
+//      global column order lives in the pos2col/col2pos maps that every rank updates identically);
+//   3. applies the rank-1 update to its local trailing columns with the broadcast pivot column (part of the winner's
+//      record) and its own piece of the pivot row, searching the updated values in the same pass; the last block to finish
+//      writes this rank's next record: best candidate + that candidate's whole column.
+// Arithmetic per element is identical to the single-GPU kernels (same scan_tiles), so the factors are bit-identical.
+struct DistState {
+    int npivot, stop, pr, owner, pcl, posw;   // pending pivot: row, owning rank, local column there, its position
+    int kl, kl_next;                          // local columns already pivoted (the local trailing block starts here)
+    int flags;
+    unsigned int ticket;
+    double pivval, maxerror, error;
+};
+struct Cand4 { double x; int i, pos, jl; };
+
+__device__ __forceinline__ bool cand4_better(const Cand4& a, const Cand4& b) {
+    if (a.i < 0) return false;
+    if (b.i < 0) return true;
+    const double va = __dmul_rn(a.x, a.x), vb = __dmul_rn(b.x, b.x);
+    if (va > vb) return true;
+    if (va == vb) return (a.pos < b.pos) || (a.pos == b.pos && a.i < b.i);
+    return false;
+}
+__device__ __forceinline__ Cand4 cand4_shfl_down(const Cand4& c, int d) {
+    Cand4 o;
+    o.x = __shfl_down_sync(0xffffffffu, c.x, d); o.i = __shfl_down_sync(0xffffffffu, c.i, d);
+    o.pos = __shfl_down_sync(0xffffffffu, c.pos, d); o.jl = __shfl_down_sync(0xffffffffu, c.jl, d);
+    return o;
+}
+__device__ __forceinline__ Cand4 block_reduce4(Cand4 c, Cand4* smem) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { Cand4 o = cand4_shfl_down(c, d); if (cand4_better(o, c)) c = o; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) smem[warp] = c;
+    __syncthreads();
+    if (warp == 0) {
+        c = (lane < kThreads / 32) ? smem[lane] : Cand4{0.0, -1, -1, -1};
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { Cand4 o = cand4_shfl_down(c, d); if (cand4_better(o, c)) c = o; }
+    }
+    return c;   // valid in thread 0
+}
+
+struct DistArrays {
+    DistState* st; int* rowperm; int* pos2col; int* col2pos; int* gid;
+    double* ybuf; double* xcol; double* pivvals; double* Lbuf; Cand4* parts;
+    long long ldl;
+};
+
+__global__ void rrlu_dist_init_kernel(DistArrays a, int m, int n, int nloc, int col0) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < m) a.rowperm[t] = t;
+    if (t < n) { a.pos2col[t] = t; a.col2pos[t] = t; }
+    if (t < nloc) a.gid[t] = col0 + t;
+    if (t == 0) {
+        DistState* st = a.st;
+        st->npivot = 0; st->stop = 0; st->pr = 0; st->owner = 0; st->pcl = 0; st->posw = 0; st->kl = 0; st->kl_next = 0;
+        st->flags = 0; st->ticket = 0u; st->pivval = 0.0; st->maxerror = 0.0; st->error = nan("");
+    }
+}
+
+// Step part 1 (one block): global pivot choice + stop rule (matrixlu.jl:359-367), pivot column broadcast -> xcol / Lbuf.
+__global__ void __launch_bounds__(kThreads)
+rrlu_dist_select_kernel(DistArrays a, const double* __restrict__ gathered, long long reclen, int nranks, int m,
+                        int maxrank, double reltol, double abstol, int leftorth) {
+    __shared__ int s_commit;
+    DistState* st = a.st;
+    const int k = st->npivot;                               // written only by the update kernel
+    if (threadIdx.x == 0) {
+        s_commit = 0;
+        if (st->stop) {
+            // the loop has ended on an earlier step: nothing to do
+        } else if (k >= maxrank) {
+            st->stop = 1;                                           // while lu.npivot < maxrank (:356)
+        } else {
+            Cand4 best{0.0, -1, -1, -1}; int owner = -1;
+            for (int g = 0; g < nranks; ++g) {
+                const double* r = gathered + (long long)g * reclen;
+                Cand4 c{r[0], (int)r[1], (int)r[2], (int)r[3]};
+                if (cand4_better(c, best)) { best = c; owner = g; }
+            }
+            if (best.i < 0) {                                       // every remaining entry is NaN: not supported in the sharded path
+                st->flags |= 8; st->stop = 1; st->error = nan("");
+            } else {
+                const double err = fabs(best.x);                    // :360
+                st->error = err;
+                if ((err < reltol * st->maxerror || err < abstol) && k > 0) {    // :363
+                    st->stop = 1;
+                } else {
+                    st->maxerror = jl_max(st->maxerror, err);       // :367
+                    st->pr = best.i; st->owner = owner; st->pcl = best.jl; st->posw = best.pos; st->pivval = best.x;
+                    s_commit = 1;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (!s_commit) return;
+    const int pr = st->pr;
+    const double piv = st->pivval;
+    const double* col = gathered + (long long)st->owner * reclen + 4;
+    for (int i = threadIdx.x; i < m; i += kThreads) {
+        const int src = (i == k) ? pr : (i == pr ? k : i);          // the row swap k <-> pr applied to the broadcast column
+        double v = col[src];
+        if (leftorth && i > k) v = v / piv;                         // :303-305
+        a.xcol[i] = v;
+        if (i >= k) a.Lbuf[(long long)k * a.ldl + i] = v;
+    }
+    if (threadIdx.x == 0) {
+        int t = a.rowperm[k]; a.rowperm[k] = a.rowperm[pr]; a.rowperm[pr] = t;
+        const int P = st->posw, ck = a.pos2col[k], cw = a.pos2col[P];                 // swapcol!(k, P) on the position maps
+        a.pos2col[k] = cw; a.pos2col[P] = ck; a.col2pos[cw] = k; a.col2pos[ck] = P;
+        a.pivvals[k] = piv;
+    }
+}
+
+// Step part 2: the row swap in the local columns and in the L columns gathered so far; on the owner also the local column
+// swap that brings the pivot column to the front of the trailing block; packed copy of the local piece of the pivot row.
+__global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int rank, int leftorth) {
+    DistState* st = a.st;
+    if (st->stop) return;
+    const int k = st->npivot, pr = st->pr, kl = st->kl, pcl = st->pcl;
+    const bool mine = st->owner == rank;
+    const double piv = st->pivval;
+    const int klnext = kl + (mine ? 1 : 0);
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < nloc) {
+        const int j = t;
+        if (mine && (j == kl || j == pcl)) return;                  // the corner item handles these two columns
+        double* pk = A + (long long)j * lda + k;
+        double* pp = A + (long long)j * lda + pr;
+        const double old_k = *pk;
+        double newk = (pr != k) ? *pp : old_k;
+        if (j >= klnext) {                                          // trailing column: its row-k entry is part of the pivot row
+            if (!leftorth) newk = newk / piv;                       // :306-308
+            a.ybuf[j] = newk;
+        }
+        *pk = newk;
+        if (pr != k) *pp = old_k;
+    } else if (t < nloc + m) {
+        if (!mine || pcl == kl) return;
+        const int i = t - nloc;
+        if (i == k || i == pr) return;
+        double* p0 = A + (long long)kl * lda + i;
+        double* p1 = A + (long long)pcl * lda + i;
+        const double v = *p0; *p0 = *p1; *p1 = v;
+    } else if (t < nloc + m + k) {
+        if (pr == k) return;
+        const int c = t - nloc - m;
+        double* p0 = a.Lbuf + (long long)c * a.ldl + k;
+        double* p1 = a.Lbuf + (long long)c * a.ldl + pr;
+        const double v = *p0; *p0 = *p1; *p1 = v;
+    } else if (t == nloc + m + k) {
+        if (mine) {
+            const double o_kk = A[(long long)kl * lda + k], o_kp = A[(long long)pcl * lda + k];
+            const double o_rk = A[(long long)kl * lda + pr], o_rp = A[(long long)pcl * lda + pr];
+            double n_kk = o_rp, n_kp = o_rk, n_rk = o_kp, n_rp = o_kk;           // new[r][c] = old[rowswap(r)][colswap(c)]
+            if (!leftorth && pcl != kl) n_kp = n_kp / piv;                       // column pcl stays in the trailing block
+            // coinciding addresses (pr == k or pcl == kl): the canonical value lands last, as in swap_item
+            A[(long long)pcl * lda + pr] = n_rp;
+            A[(long long)pcl * lda + k] = n_kp;
+            A[(long long)kl * lda + pr] = n_rk;
+            A[(long long)kl * lda + k] = n_kk;
+            if (pcl != kl) a.ybuf[pcl] = n_kp;
+            const int g0 = a.gid[kl]; a.gid[kl] = a.gid[pcl]; a.gid[pcl] = g0;
+        }
+        st->kl_next = klnext;
+    }
+}
+
+// Step part 3: local rank-1 update + search; the last block writes this rank's record for the next step.
+template <bool UPDATE, bool VEC, int COLS>
+__global__ void __launch_bounds__(kThreads, (COLS == 8 ? 3 : 2))
+rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int maxrank, int serpentine,
+                        double* __restrict__ record) {
+    __shared__ Cand4 s_c[kThreads / 32];
+    __shared__ int s_last;
+    DistState* st = a.st;
+    if (st->stop) return;
+    const int k = st->npivot;
+    const int np = UPDATE ? k + 1 : 0;
+    const int c0 = UPDATE ? st->kl_next : 0;
+    double bv = -INFINITY, bx = 0.0;
+    int bi = -1, bj = -1;
+    const ColOrder ord{a.gid, a.col2pos};
+    if (np < maxrank && c0 < nloc)
+        scan_tiles<UPDATE, VEC, COLS, false, true>(A, m, nloc, lda, a.ybuf, a.xcol, np, c0, np, serpentine, ord, bv, bx, bi, bj);
+    Cand4 c{bx, bi, bj >= 0 ? a.col2pos[a.gid[bj]] : -1, bj};
+    c = block_reduce4(c, s_c);
+    if (threadIdx.x == 0) {
+        a.parts[blockIdx.x] = c;
+        __threadfence();
+        const unsigned int done = atomicAdd(&st->ticket, 1u);
+        s_last = (done == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    Cand4 best{0.0, -1, -1, -1};
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += kThreads) {
+        Cand4 o = a.parts[b];
+        if (cand4_better(o, best)) best = o;
+    }
+    __syncthreads();
+    best = block_reduce4(best, s_c);
+    __shared__ int s_jl;
+    if (threadIdx.x == 0) {
+        record[0] = best.x; record[1] = (double)best.i; record[2] = (double)best.pos; record[3] = (double)best.jl;
+        s_jl = best.i >= 0 ? best.jl : -1;
+        st->npivot = np; st->kl = c0; st->ticket = 0u;
+    }
+    __syncthreads();
+    const int jl = s_jl;
+    if (jl >= 0)
+        for (int i = threadIdx.x; i < m; i += kThreads) record[4 + i] = __ldcg(A + (long long)jl * lda + i);
+}
+
+// L (m x r): tril of the gathered columns with the reference's diagonal; U_loc (r x nloc): triu of the local columns in
+// terms of their POSITIONS (:372-388); locpos[j] = position of local column j.
+__global__ void rrlu_dist_extract_kernel(DistArrays a, const double* __restrict__ A, int m, int nloc, long long lda, int r, int leftorth,
+                                         double* __restrict__ L, long long ldl, double* __restrict__ U, long long ldu, int* __restrict__ locpos) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long nl = (long long)m * r, nu = (long long)r * nloc;
+    if (t < nl) {
+        if (!L) return;
+        const int i = (int)(t % m), c = (int)(t / m);
+        double v = 0.0;
+        if (i > c) v = a.Lbuf[(long long)c * a.ldl + i];
+        else if (i == c) v = leftorth ? 1.0 : a.Lbuf[(long long)c * a.ldl + c];
+        L[(long long)c * ldl + i] = v;
+    } else if (t < nl + nu) {
+        if (!U) return;
+        const long long e = t - nl;
+        const int c = (int)(e % r), j = (int)(e / r);
+        const int pos = a.col2pos[a.gid[j]];
+        double v = 0.0;
+        if (c < pos) v = A[(long long)j * lda + c];
+        else if (c == pos) v = leftorth ? A[(long long)j * lda + c] : 1.0;
+        U[(long long)j * ldu + c] = v;
+    } else if (t < nl + nu + nloc) {
+        const int j = (int)(t - nl - nu);
+        locpos[j] = a.col2pos[a.gid[j]];
+    }
 }
 
 } // namespace
@@ -857,6 +1120,138 @@ int tci_rrlu_last_timing(tci_handle h, double* h_ms3, int64_t* h_steps) {
     if (!h) return TCI_ERR_INVALID;
     if (h_ms3) for (int i = 0; i < 3; ++i) h_ms3[i] = h->rrlu_ms[i];
     if (h_steps) *h_steps = h->rrlu_steps;
+    return TCI_OK;
+}
+
+} // extern "C"
+
+// ---- column-sharded rrLU: host side ------------------------------------------------------------------------------------
+struct tci_rrlu_dist_s {
+    int m, n, nloc, col0, rank, nranks, maxrank, leftorth, vec, grid;
+    double reltol, abstol;
+    long long reclen;
+    void* block;                 // one allocation behind all the arrays
+    DistArrays a;
+};
+
+template <bool UPDATE>
+static void launch_dist_update(tci_handle h, tci_rrlu_dist_s* d, double* A, long long lda, double* record) {
+    if (d->vec) rrlu_dist_update_kernel<UPDATE, true, 8><<<d->grid, kThreads, 0, h->stream>>>(d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record);
+    else        rrlu_dist_update_kernel<UPDATE, false, 8><<<d->grid, kThreads, 0, h->stream>>>(d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record);
+}
+
+extern "C" {
+
+int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64_t col0, int rank, int nranks, int64_t maxrank,
+                         double reltol, double abstol, int leftorthogonal, tci_rrlu_dist* out) {
+    if (!h || !out) return TCI_ERR_INVALID;
+    if (m < 1 || n < 1 || nloc < 0 || col0 < 0 || col0 + nloc > n || nranks < 1 || rank < 0 || rank >= nranks || m > (1 << 30) || n > (1 << 30))
+        return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_create: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    tci_rrlu_dist_s* d = new tci_rrlu_dist_s();
+    d->m = (int)m; d->n = (int)n; d->nloc = (int)nloc; d->col0 = (int)col0; d->rank = rank; d->nranks = nranks;
+    const int64_t mn = m < n ? m : n;
+    d->maxrank = (int)((maxrank <= 0 || maxrank > mn) ? mn : maxrank);
+    d->leftorth = leftorthogonal ? 1 : 0; d->reltol = reltol; d->abstol = abstol;
+    d->reclen = 4 + ((m + 1) & ~(int64_t)1);
+    d->vec = 0;
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rrlu_dist_update_kernel<true, true, 8>, kThreads, 0) != cudaSuccess || nb < 1) nb = 1;
+    d->grid = nb * h->num_sms;
+    auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    const size_t o_st = 0, o_rp = al(sizeof(DistState)), o_p2c = o_rp + al(sizeof(int) * m), o_c2p = o_p2c + al(sizeof(int) * n),
+                 o_gid = o_c2p + al(sizeof(int) * n), o_y = o_gid + al(sizeof(int) * (nloc + 1)), o_x = o_y + al(sizeof(double) * (nloc + 1)),
+                 o_pv = o_x + al(sizeof(double) * (m + 2)), o_parts = o_pv + al(sizeof(double) * d->maxrank),
+                 o_L = o_parts + al(sizeof(Cand4) * d->grid), total = o_L + al(sizeof(double) * (size_t)m * d->maxrank);
+    if (cudaMalloc(&d->block, total) != cudaSuccess) { delete d; return tci_fail(h, TCI_ERR_NOMEM, "tci_rrlu_dist_create: cudaMalloc of %zu bytes failed", total); }
+    char* b = (char*)d->block;
+    d->a.st = (DistState*)(b + o_st); d->a.rowperm = (int*)(b + o_rp); d->a.pos2col = (int*)(b + o_p2c); d->a.col2pos = (int*)(b + o_c2p);
+    d->a.gid = (int*)(b + o_gid); d->a.ybuf = (double*)(b + o_y); d->a.xcol = (double*)(b + o_x); d->a.pivvals = (double*)(b + o_pv);
+    d->a.parts = (Cand4*)(b + o_parts); d->a.Lbuf = (double*)(b + o_L); d->a.ldl = m;
+    const int64_t mx = m > n ? m : n;
+    rrlu_dist_init_kernel<<<(unsigned)((mx + 255) / 256), 256, 0, h->stream>>>(d->a, d->m, d->n, d->nloc, d->col0);
+    TCI_LAUNCH_CHECK(h);
+    *out = d;
+    return TCI_OK;
+}
+
+int64_t tci_rrlu_dist_record_doubles(tci_rrlu_dist d) { return d ? d->reclen : 0; }
+
+int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, double* d_record) {
+    if (!h || !d || !d_record || (d->nloc > 0 && (!d_A || lda < d->m))) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_search: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    d->vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15) == 0) ? 1 : 0;
+    launch_dist_update<false>(h, d, d_A, lda, d_record);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record) {
+    if (!h || !d || !d_gathered || !d_record) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_step: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    rrlu_dist_select_kernel<<<1, kThreads, 0, h->stream>>>(d->a, d_gathered, d->reclen, d->nranks, d->m, d->maxrank, d->reltol, d->abstol, d->leftorth);
+    TCI_LAUNCH_CHECK(h);
+    const long long items = (long long)d->nloc + d->m + d->maxrank + 1;
+    rrlu_dist_swap_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(d->a, d_A, d->m, d->nloc, lda, d->rank, d->leftorth);
+    TCI_LAUNCH_CHECK(h);
+    launch_dist_update<true>(h, d, d_A, lda, d_record);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_status(tci_handle h, tci_rrlu_dist d, int64_t* h_npivot, int* h_stop) {
+    if (!h || !d) return TCI_ERR_INVALID;
+    int rc = tci_pinned_reserve(h, sizeof(DistState)); if (rc) return rc;
+    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, d->a.st, sizeof(DistState), cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    const DistState* st = (const DistState*)h->pinned;
+    if (h_npivot) *h_npivot = st->npivot;
+    if (h_stop) *h_stop = st->stop || st->npivot >= d->maxrank;
+    if (st->flags & 8) return tci_fail(h, TCI_ERR_NAN_L, "sharded rrlu: every remaining entry is NaN");
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_finish(tci_handle h, tci_rrlu_dist d, const double* d_A, int64_t lda, int64_t* h_rowperm, int64_t* h_colperm,
+                         int64_t* h_npivot, double* h_error, double* d_L, int64_t ldl, double* d_Uloc, int64_t ldu,
+                         int64_t* h_locpos, double* h_pivoterrors) {
+    if (!h || !d || !h_rowperm || !h_colperm || !h_npivot || !h_error) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_finish: bad arguments");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    const int m = d->m, n = d->n, nloc = d->nloc;
+    const size_t pin = sizeof(DistState) + sizeof(int) * ((size_t)m + n + nloc) + sizeof(double) * d->maxrank + 256;
+    int rc = tci_pinned_reserve(h, pin); if (rc) return rc;
+    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, d->a.st, sizeof(DistState), cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    DistState st = *(const DistState*)h->pinned;
+    const int r = st.npivot;
+    if (r > 0 && ((d_L && ldl < m) || (d_Uloc && ldu < r))) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_finish: leading dimensions too small");
+    rc = tci_ws_reserve(h, h->ws_c, sizeof(int) * (size_t)(nloc + 1)); if (rc) return rc;
+    int* d_locpos = (int*)h->ws_c.ptr;
+    const long long items = (long long)m * r + (long long)r * nloc + nloc;
+    if (items > 0) {
+        rrlu_dist_extract_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(d->a, d_A, m, nloc, lda, r, d->leftorth, d_L, ldl, d_Uloc, ldu, d_locpos);
+        TCI_LAUNCH_CHECK(h);
+    }
+    int* p_rp = (int*)((char*)h->pinned + 256); int* p_cp = p_rp + m; int* p_lp = p_cp + n; double* p_pv = (double*)(p_lp + nloc + ((m + n + nloc) & 1));
+    TCI_CUDA(h, cudaMemcpyAsync(p_rp, d->a.rowperm, sizeof(int) * m, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaMemcpyAsync(p_cp, d->a.pos2col, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
+    if (nloc > 0) TCI_CUDA(h, cudaMemcpyAsync(p_lp, d_locpos, sizeof(int) * nloc, cudaMemcpyDeviceToHost, h->stream));
+    if (r > 0) TCI_CUDA(h, cudaMemcpyAsync(p_pv, d->a.pivvals, sizeof(double) * r, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < m; ++i) h_rowperm[i] = p_rp[i] + 1;
+    for (int j = 0; j < n; ++j) h_colperm[j] = p_cp[j] + 1;
+    if (h_locpos) for (int j = 0; j < nloc; ++j) h_locpos[j] = p_lp[j];
+    *h_npivot = r;
+    *h_error = (r >= (m < n ? m : n)) ? 0.0 : st.error;                 // :391-393
+    if (h_pivoterrors) { for (int c = 0; c < r; ++c) h_pivoterrors[c] = fabs(p_pv[c]); h_pivoterrors[r] = *h_error; }
+    if (st.flags & 8) return tci_fail(h, TCI_ERR_NAN_L, "sharded rrlu: every remaining entry is NaN");
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_destroy(tci_handle h, tci_rrlu_dist d) {
+    if (!d) return TCI_OK;
+    if (h) cudaSetDevice(h->device);
+    cudaFree(d->block);
+    delete d;
     return TCI_OK;
 }
 

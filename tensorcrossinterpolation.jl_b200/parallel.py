@@ -318,3 +318,145 @@ class ShardedBatchEvaluator(BatchEvaluator):
         if maxabs is not None:
             mx = self.comm.allreduce_max(mx)
         return out, mx
+
+
+# ---- column-sharded full-pivot rrLU (SURVEY.md 8e row "rrLU": one exchange per pivot step) ----------------------------------
+class ShardedRRLU:
+    """One rank's part of a column-sharded rrlu (csrc/rrlu.cu, tci_rrlu_dist_*).  `A` is this rank's column block as a
+    `dense.Mat` (m x nloc, overwritten), `col0` its first global column."""
+
+    def __init__(self, A, n, col0, rank, nranks, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None):
+        import ctypes as C
+        import torch
+        from . import _lib
+        from ._lib import lib
+        self.h = handle or _lib.default_handle()
+        self.A, self.m, self.n, self.nloc, self.col0 = A, A.rows, int(n), A.cols, int(col0)
+        self.rank, self.nranks, self.leftorthogonal = rank, nranks, bool(leftorthogonal)
+        mn = min(self.m, self.n)
+        self.maxrank = mn if maxrank is None or maxrank <= 0 or maxrank > mn else int(maxrank)
+        self._d = C.c_void_p()
+        self.h.check(lib().tci_rrlu_dist_create(self.h.h, C.c_int64(self.m), C.c_int64(self.n), C.c_int64(self.nloc), C.c_int64(col0),
+                                                int(rank), int(nranks), C.c_int64(self.maxrank), C.c_double(reltol), C.c_double(abstol),
+                                                int(self.leftorthogonal), C.byref(self._d)))
+        lib().tci_rrlu_dist_record_doubles.restype = C.c_int64
+        self.reclen = int(lib().tci_rrlu_dist_record_doubles(self._d))
+        self.record = torch.zeros(self.reclen, dtype=torch.float64, device=A.buf.device)
+
+    def _aptr(self):
+        import ctypes as C
+        return C.c_void_p(self.A.buf.data_ptr())
+
+    def search(self):
+        import ctypes as C
+        from ._lib import lib
+        self.h.check(lib().tci_rrlu_dist_search(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld), C.c_void_p(self.record.data_ptr())))
+
+    def step(self, gathered):
+        import ctypes as C
+        from ._lib import lib
+        self.h.check(lib().tci_rrlu_dist_step(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld), C.c_void_p(gathered.data_ptr()),
+                                              C.c_void_p(self.record.data_ptr())))
+
+    def status(self):
+        import ctypes as C
+        from ._lib import lib
+        np_, stop = C.c_int64(), C.c_int()
+        self.h.check(lib().tci_rrlu_dist_status(self.h.h, self._d, C.byref(np_), C.byref(stop)))
+        return np_.value, bool(stop.value)
+
+    def finish(self):
+        """-> dict(rowperm, colperm (1-based, full length), npivot, error, pivoterrors, L (Mat m x r), Uloc (Mat r x nloc), locpos)."""
+        import ctypes as C
+        from ._lib import lib, p_f64, p_i64
+        from .dense import Mat
+        rowperm, colperm = np.zeros(self.m, dtype=np.int64), np.zeros(self.n, dtype=np.int64)
+        locpos = np.zeros(max(self.nloc, 1), dtype=np.int64)
+        pe = np.zeros(self.maxrank + 1)
+        npiv, err = C.c_int64(), C.c_double()
+        dev = self.A.buf.device
+        L = Mat.empty(self.m, max(self.maxrank, 1), dev)
+        U = Mat.empty(max(self.maxrank, 1), self.nloc, dev)
+        self.h.check(lib().tci_rrlu_dist_finish(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld), p_i64(rowperm), p_i64(colperm),
+                                                C.byref(npiv), C.byref(err), L.ptr, C.c_int64(L.ld), U.ptr, C.c_int64(U.ld),
+                                                p_i64(locpos), p_f64(pe)))
+        r = npiv.value
+        L.cols, U.rows = r, r
+        return {"rowperm": rowperm, "colperm": colperm, "npivot": r, "error": err.value, "pivoterrors": pe[: r + 1].copy(),
+                "L": L, "Uloc": U, "locpos": locpos[: self.nloc]}
+
+    def close(self):
+        from ._lib import lib
+        if self._d:
+            lib().tci_rrlu_dist_destroy(self.h.h, self._d)
+            self._d = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def rrlu_sharded(A_local, n, col0, comm=None, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None,
+                 check_every=32):
+    """rrlu!(A; ...) (matrixlu.jl:420-430) with the columns of A spread over the ranks of `comm` (NCCL): per pivot step one
+    all-gather of the ranks' candidate records (8 x (m + 4) bytes each).  Returns this rank's `ShardedRRLU.finish()` dict;
+    rowperm / colperm / npivot / pivoterrors / L are the same on every rank and bit-identical to the single-GPU rrlu."""
+    import torch
+    size = 1 if comm is None else comm.size
+    rank = 0 if comm is None else comm.rank
+    s = ShardedRRLU(A_local, n, col0, rank, size, maxrank, reltol, abstol, leftorthogonal, handle)
+    gathered = torch.empty(size * s.reclen, dtype=torch.float64, device=A_local.buf.device)
+    s.search()
+    for it in range(s.maxrank):
+        if size == 1:
+            gathered = s.record
+        else:
+            comm.dist.all_gather_into_tensor(gathered, s.record, group=comm.group)
+        s.step(gathered)
+        if check_every and (it + 1) % check_every == 0 and it + 1 < s.maxrank:
+            if s.status()[1]:                            # every rank takes the same decision: the loop lengths agree
+                break
+    out = s.finish()
+    s.close()
+    return out
+
+
+def rrlu_sharded_virtual(A, nranks, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None):
+    """The sharded factorisation with `nranks` VIRTUAL ranks on one GPU (lock-step, records concatenated by device copies):
+    the algorithm and kernels of `rrlu_sharded` without a process group — used by the single-GPU parity tests.
+    A: numpy matrix.  Returns (list of per-rank finish() dicts, column blocks)."""
+    import torch
+    from . import _lib
+    from .dense import Mat
+    h = handle or _lib.default_handle()
+    dev = f"cuda:{h.device}"
+    A = np.asarray(A, dtype=np.float64)
+    m, n = A.shape
+    blocks = partition(n, nranks)
+    parts = [ShardedRRLU(Mat.from_numpy(A[:, s:e], dev, pad=2), n, s, r, nranks, maxrank, reltol, abstol, leftorthogonal, h)
+             for r, (s, e) in enumerate(blocks)]
+    reclen = parts[0].reclen
+    gathered = torch.empty(nranks * reclen, dtype=torch.float64, device=dev)
+    for p in parts:
+        p.search()
+    for it in range(parts[0].maxrank):
+        for r, p in enumerate(parts):
+            gathered[r * reclen:(r + 1) * reclen].copy_(p.record)
+        for p in parts:
+            p.step(gathered)
+    outs = [p.finish() for p in parts]
+    for p in parts:
+        p.close()
+    return outs, blocks
+
+
+def assemble_sharded_U(outs, n):
+    """Full U (npivot x n, swapped column order) from the per-rank pieces of `rrlu_sharded` (host, numpy)."""
+    r = outs[0]["npivot"]
+    U = np.zeros((r, n))
+    for o in outs:
+        if o["Uloc"].cols:
+            U[:, o["locpos"]] = o["Uloc"].numpy()[:r]
+    return U
