@@ -120,6 +120,15 @@ int64_t tci_rrlu_dist_record_doubles(tci_rrlu_dist d);
 int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, double* d_record);
 int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record);
 int tci_rrlu_dist_status(tci_handle h, tci_rrlu_dist d, int64_t* h_npivot, int* h_stop);
+/* Fused exchange: instead of the caller's all-gather, the update kernel's last block stores this rank's record straight into
+ * every rank's MAILBOX (peer-mapped device memory: allocate tci_rrlu_dist_mailbox_bytes with tci_malloc, share it with
+ * tci_ipc_export/open) and the next step's kernel waits for the G sequence flags (acquire/release at system scope, 4 s
+ * timeout).  h_boxes[g] = rank g's mailbox as mapped in THIS process (h_boxes[rank] = own).  All ranks must have called
+ * set_mailboxes (which zeroes the own mailbox) before any rank calls run; run enqueues the whole factorisation (search +
+ * maxrank steps) without a host synchronisation. */
+int64_t tci_rrlu_dist_mailbox_bytes(tci_rrlu_dist d);
+int tci_rrlu_dist_set_mailboxes(tci_handle h, tci_rrlu_dist d, void* const* h_boxes);
+int tci_rrlu_dist_run(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda);
 int tci_rrlu_dist_finish(tci_handle h, tci_rrlu_dist d, const double* d_A, int64_t lda, int64_t* h_rowperm, int64_t* h_colperm,
                          int64_t* h_npivot, double* h_error, double* d_L, int64_t ldl, double* d_Uloc, int64_t ldu,
                          int64_t* h_locpos, double* h_pivoterrors);

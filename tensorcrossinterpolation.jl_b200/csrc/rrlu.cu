@@ -669,6 +669,30 @@ __device__ __forceinline__ Cand4 block_reduce4(Cand4 c, Cand4* smem) {
     return c;   // valid in thread 0
 }
 
+// Mailbox exchange over peer-mapped memory (CUDA IPC / NVLink): rank g's mailbox holds, for each parity of the step counter,
+// one record slot per rank and one sequence flag per rank.  The last block of a rank's update kernel stores its record into
+// the slot [parity][rank] of EVERY rank's mailbox and then releases the flag; the select kernel of the next step acquires
+// the G flags of its own mailbox.  A rank can be at most one step ahead of a peer, so two parities suffice.
+constexpr int kMaxPeers = 8;
+struct PeerBox { double* box[kMaxPeers]; int n; };       // n == 0: records go to `record` and are gathered by the caller
+
+__device__ __forceinline__ unsigned int* box_flags(double* box, long long reclen, int n) {
+    return reinterpret_cast<unsigned int*>(box + 2LL * n * reclen);
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 struct DistArrays {
     DistState* st; int* rowperm; int* pos2col; int* col2pos; int* gid;
     double* ybuf; double* xcol; double* pivvals; double* Lbuf; Cand4* parts;
@@ -690,21 +714,42 @@ __global__ void rrlu_dist_init_kernel(DistArrays a, int m, int n, int nloc, int 
 // Step part 1 (one block): global pivot choice + stop rule (matrixlu.jl:359-367), pivot column broadcast -> xcol / Lbuf.
 __global__ void __launch_bounds__(kThreads)
 rrlu_dist_select_kernel(DistArrays a, const double* __restrict__ gathered, long long reclen, int nranks, int m,
-                        int maxrank, double reltol, double abstol, int leftorth) {
+                        int maxrank, double reltol, double abstol, int leftorth, double* mybox) {
     __shared__ int s_commit;
+    cudaGridDependencySynchronize();
     DistState* st = a.st;
     const int k = st->npivot;                               // written only by the update kernel
+    if (mybox) {                                            // mailbox mode: wait for the G records with sequence number k + 1
+        if (!st->stop && k < maxrank && (int)threadIdx.x < nranks) {
+            const unsigned int* f = box_flags(mybox, reclen, nranks) + (k & 1) * nranks + threadIdx.x;
+            const unsigned long long t0 = globaltimer_ns();
+            while (ld_acquire_sys(f) < (unsigned int)(k + 1)) {
+                if (globaltimer_ns() - t0 > 4000000000ULL) { atomicOr(&st->flags, 4); break; }   // a peer died: give up after 4 s
+                __nanosleep(200);
+            }
+        }
+        __syncthreads();
+        gathered = mybox + (long long)(k & 1) * nranks * reclen;
+    }
+    __shared__ double s_hdr[kMaxPeers * 2][4];              // the G record headers, fetched in parallel
+    if ((int)threadIdx.x < 4 * nranks && nranks <= kMaxPeers * 2)
+        s_hdr[threadIdx.x >> 2][threadIdx.x & 3] = __ldcg(gathered + (long long)(threadIdx.x >> 2) * reclen + (threadIdx.x & 3));
+    __syncthreads();
     if (threadIdx.x == 0) {
         s_commit = 0;
         if (st->stop) {
             // the loop has ended on an earlier step: nothing to do
+        } else if (st->flags & 4) {
+            st->stop = 1;                                           // exchange timed out
         } else if (k >= maxrank) {
             st->stop = 1;                                           // while lu.npivot < maxrank (:356)
         } else {
             Cand4 best{0.0, -1, -1, -1}; int owner = -1;
             for (int g = 0; g < nranks; ++g) {
-                const double* r = gathered + (long long)g * reclen;
-                Cand4 c{r[0], (int)r[1], (int)r[2], (int)r[3]};
+                double hdr[4];
+                if (nranks <= kMaxPeers * 2) { hdr[0] = s_hdr[g][0]; hdr[1] = s_hdr[g][1]; hdr[2] = s_hdr[g][2]; hdr[3] = s_hdr[g][3]; }
+                else { const double* r = gathered + (long long)g * reclen; hdr[0] = __ldcg(r); hdr[1] = __ldcg(r + 1); hdr[2] = __ldcg(r + 2); hdr[3] = __ldcg(r + 3); }
+                Cand4 c{hdr[0], (int)hdr[1], (int)hdr[2], (int)hdr[3]};
                 if (cand4_better(c, best)) { best = c; owner = g; }
             }
             if (best.i < 0) {                                       // every remaining entry is NaN: not supported in the sharded path
@@ -724,27 +769,20 @@ rrlu_dist_select_kernel(DistArrays a, const double* __restrict__ gathered, long 
     }
     __syncthreads();
     if (!s_commit) return;
-    const int pr = st->pr;
-    const double piv = st->pivval;
-    const double* col = gathered + (long long)st->owner * reclen + 4;
-    for (int i = threadIdx.x; i < m; i += kThreads) {
-        const int src = (i == k) ? pr : (i == pr ? k : i);          // the row swap k <-> pr applied to the broadcast column
-        double v = col[src];
-        if (leftorth && i > k) v = v / piv;                         // :303-305
-        a.xcol[i] = v;
-        if (i >= k) a.Lbuf[(long long)k * a.ldl + i] = v;
-    }
     if (threadIdx.x == 0) {
+        const int pr = st->pr;
         int t = a.rowperm[k]; a.rowperm[k] = a.rowperm[pr]; a.rowperm[pr] = t;
         const int P = st->posw, ck = a.pos2col[k], cw = a.pos2col[P];                 // swapcol!(k, P) on the position maps
         a.pos2col[k] = cw; a.pos2col[P] = ck; a.col2pos[cw] = k; a.col2pos[ck] = P;
-        a.pivvals[k] = piv;
+        a.pivvals[k] = st->pivval;
     }
 }
 
 // Step part 2: the row swap in the local columns and in the L columns gathered so far; on the owner also the local column
 // swap that brings the pivot column to the front of the trailing block; packed copy of the local piece of the pivot row.
-__global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int rank, int leftorth) {
+__global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int rank, int leftorth,
+                                      const double* __restrict__ gathered, long long reclen, int nranks) {
+    cudaGridDependencySynchronize();
     DistState* st = a.st;
     if (st->stop) return;
     const int k = st->npivot, pr = st->pr, kl = st->kl, pcl = st->pcl;
@@ -793,6 +831,15 @@ __global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int 
             const int g0 = a.gid[kl]; a.gid[kl] = a.gid[pcl]; a.gid[pcl] = g0;
         }
         st->kl_next = klnext;
+    } else if (t <= nloc + m + k + m) {
+        // the broadcast pivot column (part of the winner's record) with the row swap applied -> xcol and column k of L
+        const int i = t - (nloc + m + k + 1);
+        const double* col = gathered + (long long)st->owner * reclen + 4;
+        const int src = (i == k) ? pr : (i == pr ? k : i);
+        double v = __ldcg(col + src);                               // written by a peer: around L1
+        if (leftorth && i > k) v = v / piv;                         // :303-305
+        a.xcol[i] = v;
+        if (i >= k) a.Lbuf[(long long)k * a.ldl + i] = v;
     }
 }
 
@@ -800,9 +847,10 @@ __global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int 
 template <bool UPDATE, bool VEC, int COLS>
 __global__ void __launch_bounds__(kThreads, (COLS == 8 ? 3 : 2))
 rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int maxrank, int serpentine,
-                        double* __restrict__ record) {
+                        double* __restrict__ record, PeerBox peers, int rank, long long reclen) {
     __shared__ Cand4 s_c[kThreads / 32];
     __shared__ int s_last;
+    cudaGridDependencySynchronize();
     DistState* st = a.st;
     if (st->stop) return;
     const int k = st->npivot;
@@ -832,15 +880,55 @@ rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, l
     __syncthreads();
     best = block_reduce4(best, s_c);
     __shared__ int s_jl;
+    if (peers.n == 0) {
+        if (threadIdx.x == 0) {
+            record[0] = best.x; record[1] = (double)best.i; record[2] = (double)best.pos; record[3] = (double)best.jl;
+            s_jl = best.i >= 0 ? best.jl : -1;
+            st->npivot = np; st->kl = c0; st->ticket = 0u;
+        }
+        __syncthreads();
+        const int jl = s_jl;
+        if (jl >= 0) {
+            const double* src = A + (long long)jl * lda;
+            for (int i0 = threadIdx.x; i0 < m; i0 += 8 * kThreads) {
+                double v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { const int i = i0 + u * kThreads; v[u] = i < m ? __ldcg(src + i) : 0.0; }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { const int i = i0 + u * kThreads; if (i < m) record[4 + i] = v[u]; }
+            }
+        }
+        return;
+    }
+    // compute + all-gather in one kernel: the record goes straight into every rank's mailbox (peer stores over NVLink)
+    const long long slot = ((long long)(np & 1) * peers.n + rank) * reclen;
     if (threadIdx.x == 0) {
-        record[0] = best.x; record[1] = (double)best.i; record[2] = (double)best.pos; record[3] = (double)best.jl;
+        for (int g = 0; g < peers.n; ++g) {
+            double* r = peers.box[g] + slot;
+            r[0] = best.x; r[1] = (double)best.i; r[2] = (double)best.pos; r[3] = (double)best.jl;
+        }
         s_jl = best.i >= 0 ? best.jl : -1;
         st->npivot = np; st->kl = c0; st->ticket = 0u;
     }
     __syncthreads();
     const int jl = s_jl;
-    if (jl >= 0)
-        for (int i = threadIdx.x; i < m; i += kThreads) record[4 + i] = __ldcg(A + (long long)jl * lda + i);
+    if (jl >= 0) {
+        const double* src = A + (long long)jl * lda;
+        for (int i0 = threadIdx.x; i0 < m; i0 += 8 * kThreads) {     // 8 independent loads in flight per thread
+            double v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { const int i = i0 + u * kThreads; v[u] = i < m ? __ldcg(src + i) : 0.0; }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int i = i0 + u * kThreads;
+                if (i < m) for (int g = 0; g < peers.n; ++g) peers.box[g][slot + 4 + i] = v[u];
+            }
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < peers.n)
+        st_release_sys(box_flags(peers.box[threadIdx.x], reclen, peers.n) + (np & 1) * peers.n + rank, (unsigned int)(np + 1));
 }
 
 // L (m x r): tril of the gathered columns with the reference's diagonal; U_loc (r x nloc): triu of the local columns in
@@ -1132,12 +1220,15 @@ struct tci_rrlu_dist_s {
     long long reclen;
     void* block;                 // one allocation behind all the arrays
     DistArrays a;
+    PeerBox peers;               // n == 0 until tci_rrlu_dist_set_mailboxes
 };
 
 template <bool UPDATE>
 static void launch_dist_update(tci_handle h, tci_rrlu_dist_s* d, double* A, long long lda, double* record) {
-    if (d->vec) rrlu_dist_update_kernel<UPDATE, true, 8><<<d->grid, kThreads, 0, h->stream>>>(d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record);
-    else        rrlu_dist_update_kernel<UPDATE, false, 8><<<d->grid, kThreads, 0, h->stream>>>(d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record);
+    PeerBox pb = d->peers;
+    if (record) pb.n = 0;                                // explicit record buffer: the caller gathers
+    if (d->vec) launch_pdl(h, rrlu_dist_update_kernel<UPDATE, true, 8>, (unsigned)d->grid, (unsigned)kThreads, d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record, pb, d->rank, d->reclen);
+    else        launch_pdl(h, rrlu_dist_update_kernel<UPDATE, false, 8>, (unsigned)d->grid, (unsigned)kThreads, d->a, A, d->m, d->nloc, lda, d->maxrank, 1, record, pb, d->rank, d->reclen);
 }
 
 extern "C" {
@@ -1154,7 +1245,7 @@ int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64
     d->maxrank = (int)((maxrank <= 0 || maxrank > mn) ? mn : maxrank);
     d->leftorth = leftorthogonal ? 1 : 0; d->reltol = reltol; d->abstol = abstol;
     d->reclen = 4 + ((m + 1) & ~(int64_t)1);
-    d->vec = 0;
+    d->vec = 0; d->peers.n = 0;
     int nb = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, rrlu_dist_update_kernel<true, true, 8>, kThreads, 0) != cudaSuccess || nb < 1) nb = 1;
     d->grid = nb * h->num_sms;
@@ -1189,13 +1280,55 @@ int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda
 int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record) {
     if (!h || !d || !d_gathered || !d_record) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_step: bad arguments");
     TCI_CUDA(h, cudaSetDevice(h->device));
-    rrlu_dist_select_kernel<<<1, kThreads, 0, h->stream>>>(d->a, d_gathered, d->reclen, d->nranks, d->m, d->maxrank, d->reltol, d->abstol, d->leftorth);
+    rrlu_dist_select_kernel<<<1, kThreads, 0, h->stream>>>(d->a, d_gathered, d->reclen, d->nranks, d->m, d->maxrank, d->reltol, d->abstol, d->leftorth, nullptr);
     TCI_LAUNCH_CHECK(h);
-    const long long items = (long long)d->nloc + d->m + d->maxrank + 1;
-    rrlu_dist_swap_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(d->a, d_A, d->m, d->nloc, lda, d->rank, d->leftorth);
+    const long long items = (long long)d->nloc + 2LL * d->m + d->maxrank + 1;
+    launch_pdl(h, rrlu_dist_swap_kernel, (unsigned)((items + 255) / 256), 256u, d->a, d_A, d->m, d->nloc, (long long)lda, d->rank, d->leftorth,
+               d_gathered, d->reclen, d->nranks);
     TCI_LAUNCH_CHECK(h);
     launch_dist_update<true>(h, d, d_A, lda, d_record);
     TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+int64_t tci_rrlu_dist_mailbox_bytes(tci_rrlu_dist d) {
+    if (!d) return 0;
+    return (int64_t)(2LL * d->nranks * d->reclen * sizeof(double) + 2LL * d->nranks * sizeof(unsigned int) + 256);
+}
+
+int tci_rrlu_dist_set_mailboxes(tci_handle h, tci_rrlu_dist d, void* const* h_boxes) {
+    if (!h || !d || !h_boxes) return TCI_ERR_INVALID;
+    if (d->nranks > kMaxPeers) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_set_mailboxes: at most %d ranks", kMaxPeers);
+    for (int g = 0; g < d->nranks; ++g) {
+        if (!h_boxes[g]) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_set_mailboxes: NULL mailbox");
+        d->peers.box[g] = (double*)h_boxes[g];
+    }
+    d->peers.n = d->nranks;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    TCI_CUDA(h, cudaMemsetAsync(h_boxes[d->rank], 0, (size_t)tci_rrlu_dist_mailbox_bytes(d), h->stream));   // own flags start at 0
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_run(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda) {
+    if (!h || !d || (d->nloc > 0 && (!d_A || lda < d->m))) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_run: bad arguments");
+    if (d->peers.n != d->nranks) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_run: call tci_rrlu_dist_set_mailboxes first");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    d->vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15) == 0) ? 1 : 0;
+    launch_dist_update<false>(h, d, d_A, lda, nullptr);
+    TCI_LAUNCH_CHECK(h);
+    const long long items = (long long)d->nloc + 2LL * d->m + d->maxrank + 1;
+    for (int s = 0; s < d->maxrank; ++s) {
+        const double* gathered = d->peers.box[d->rank] + (long long)(s & 1) * d->nranks * d->reclen;   // npivot == s while the loop runs
+        launch_pdl(h, rrlu_dist_select_kernel, 1u, (unsigned)kThreads, d->a, (const double*)nullptr, d->reclen, d->nranks, d->m, d->maxrank,
+                   d->reltol, d->abstol, d->leftorth, d->peers.box[d->rank]);
+        TCI_LAUNCH_CHECK(h);
+        launch_pdl(h, rrlu_dist_swap_kernel, (unsigned)((items + 255) / 256), 256u, d->a, d_A, d->m, d->nloc, (long long)lda, d->rank, d->leftorth,
+                   gathered, d->reclen, d->nranks);
+        TCI_LAUNCH_CHECK(h);
+        launch_dist_update<true>(h, d, d_A, lda, nullptr);
+        TCI_LAUNCH_CHECK(h);
+    }
     return TCI_OK;
 }
 
@@ -1244,6 +1377,7 @@ int tci_rrlu_dist_finish(tci_handle h, tci_rrlu_dist d, const double* d_A, int64
     *h_error = (r >= (m < n ? m : n)) ? 0.0 : st.error;                 // :391-393
     if (h_pivoterrors) { for (int c = 0; c < r; ++c) h_pivoterrors[c] = fabs(p_pv[c]); h_pivoterrors[r] = *h_error; }
     if (st.flags & 8) return tci_fail(h, TCI_ERR_NAN_L, "sharded rrlu: every remaining entry is NaN");
+    if (st.flags & 4) return tci_fail(h, TCI_ERR_CUDA, "sharded rrlu: a peer's record did not arrive within 4 s");
     return TCI_OK;
 }
 

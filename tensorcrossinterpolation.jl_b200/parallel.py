@@ -12,7 +12,11 @@ CPU tests).  Only what shards naturally is sharded:
     restatement of the schedule), whatever the number of ranks;
   * `fillsitetensors!` (src/globalsearch.jl:202-208): sites are independent, dealt round-robin, tensors broadcast.
 
-rrLU, `sum`, `evaluate` and zip-up do not shard (replicas only)."""
+  * the rrLU itself (an experiment next to the single-GPU default): `rrlu_sharded` deals the COLUMNS of the matrix to the
+    ranks; one candidate record per rank and pivot step is exchanged (NCCL all-gather, or peer stores into mailboxes
+    fused into the update kernel); bit-identical to the single-GPU factorisation.
+
+`sum`, `evaluate` and zip-up do not shard (replicas only)."""
 import numpy as np
 
 
@@ -358,6 +362,24 @@ class ShardedRRLU:
         self.h.check(lib().tci_rrlu_dist_step(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld), C.c_void_p(gathered.data_ptr()),
                                               C.c_void_p(self.record.data_ptr())))
 
+    def mailbox_doubles(self):
+        import ctypes as C
+        from ._lib import lib
+        lib().tci_rrlu_dist_mailbox_bytes.restype = C.c_int64
+        return (int(lib().tci_rrlu_dist_mailbox_bytes(self._d)) + 7) // 8
+
+    def set_mailboxes(self, ptrs):
+        import ctypes as C
+        from ._lib import lib
+        arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(p) for p in ptrs])
+        self.h.check(lib().tci_rrlu_dist_set_mailboxes(self.h.h, self._d, arr))
+
+    def run(self):
+        """Enqueue the whole factorisation (fused peer-store exchange); returns without synchronising."""
+        import ctypes as C
+        from ._lib import lib
+        self.h.check(lib().tci_rrlu_dist_run(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld)))
+
     def status(self):
         import ctypes as C
         from ._lib import lib
@@ -399,14 +421,31 @@ class ShardedRRLU:
 
 
 def rrlu_sharded(A_local, n, col0, comm=None, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None,
-                 check_every=32):
-    """rrlu!(A; ...) (matrixlu.jl:420-430) with the columns of A spread over the ranks of `comm` (NCCL): per pivot step one
-    all-gather of the ranks' candidate records (8 x (m + 4) bytes each).  Returns this rank's `ShardedRRLU.finish()` dict;
-    rowperm / colperm / npivot / pivoterrors / L are the same on every rank and bit-identical to the single-GPU rrlu."""
+                 check_every=32, fused=False, peers=None):
+    """rrlu!(A; ...) (matrixlu.jl:420-430) with the columns of A spread over the ranks of `comm` (NCCL).  Per pivot step the
+    ranks exchange one candidate record each (8 x (m + 4) bytes): fused=False -> an NCCL all-gather issued from the host
+    between the step kernels; fused=True -> the update kernel stores its record straight into every rank's peer-mapped
+    mailbox (`peers`: a PeerBuffers with >= mailbox_doubles() elements per slot, created once and reused) and the whole
+    factorisation is enqueued without any host round trip.  Returns this rank's `ShardedRRLU.finish()` dict; rowperm /
+    colperm / npivot / pivoterrors / L are the same on every rank and bit-identical to the single-GPU rrlu."""
     import torch
     size = 1 if comm is None else comm.size
     rank = 0 if comm is None else comm.rank
     s = ShardedRRLU(A_local, n, col0, rank, size, maxrank, reltol, abstol, leftorthogonal, handle)
+    if fused and size > 1:
+        own_peers = peers is None
+        if own_peers:
+            peers = PeerBuffers(s.h, comm, s.mailbox_doubles(), nslots=1)
+        if peers.slot_elems * peers.nslots < s.mailbox_doubles():
+            raise ValueError("rrlu_sharded: the peer buffers are smaller than one mailbox")
+        s.set_mailboxes(peers.ptrs)                      # zeroes the own mailbox
+        comm.barrier()                                   # nobody stores into a mailbox that is still being cleared
+        s.run()
+        out = s.finish()
+        s.close()
+        if own_peers:
+            peers.close()
+        return out
     gathered = torch.empty(size * s.reclen, dtype=torch.float64, device=A_local.buf.device)
     s.search()
     for it in range(s.maxrank):

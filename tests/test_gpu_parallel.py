@@ -94,3 +94,58 @@ def test_multi_gpu_matches_single_process(tci):
         assert res["ranks2"] == list(sranks) and res["ranks3"] == list(sranks) and res["fused_used"]
         assert res["I3"] == res["I2"] and res["vals3"] == res["vals2"]
         assert res["vals"] == out[0]["vals"] and res["vals2"] == out[0]["vals2"]      # replicas agree bit for bit
+
+
+def _sharded_worker(rank, world, port, q):
+    import os
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{rank}"))
+    import tci_b200 as T
+    from tci_b200.parallel import partition, rrlu_sharded
+    h = T.Handle(rank)
+    comm = T.Comm()
+    rng = np.random.default_rng(11)
+    A = rng.standard_normal((300, 12)) @ rng.standard_normal((12, 260)) + 1e-9 * rng.standard_normal((300, 260))
+    s, e = partition(260, world)[rank]
+    res = {}
+    for mode in ("nccl", "fused"):
+        blk = T.Mat.from_numpy(A[:, s:e], f"cuda:{rank}", pad=2)
+        out = rrlu_sharded(blk, 260, s, comm, maxrank=40, reltol=1e-12, handle=h, fused=(mode == "fused"), check_every=8)
+        res[mode] = (out["rowperm"], out["colperm"], out["npivot"], out["pivoterrors"], out["L"].numpy(), out["locpos"], out["Uloc"].numpy())
+    q.put((rank, res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_rrlu_two_gpus_nccl_and_fused(tci):
+    """Column-sharded rrLU over 2 processes / 2 GPUs, both exchange modes, against the oracle (bit-exact)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_sharded_worker, args=(r, 2, 29631, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+    rng = np.random.default_rng(11)
+    A = rng.standard_normal((300, 12)) @ rng.standard_normal((12, 260)) + 1e-9 * rng.standard_normal((300, 260))
+    ref = O.rrlu(A, maxrank=40, reltol=1e-12)
+    for mode in ("nccl", "fused"):
+        U = np.zeros((ref.npivot, 260))
+        for r in range(2):
+            rowperm, colperm, npiv, pe, L, locpos, Uloc = got[r][mode]
+            assert npiv == ref.npivot
+            np.testing.assert_array_equal(rowperm, ref.rowpermutation)
+            np.testing.assert_array_equal(colperm, ref.colpermutation)
+            np.testing.assert_array_equal(pe, ref.pivoterrors())
+            np.testing.assert_array_equal(L[:, :npiv], ref.L)
+            U[:, locpos] = Uloc[:npiv]
+        np.testing.assert_array_equal(U, ref.U)
