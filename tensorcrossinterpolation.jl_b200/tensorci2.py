@@ -40,8 +40,14 @@ def _first_seen_unique(tab):
     n, ln = tab.shape
     if n <= 1 or ln == 0:
         return tab[: min(n, 1)] if ln == 0 else tab
-    flat = np.ascontiguousarray(tab, dtype=np.int32).view(np.dtype((np.void, 4 * ln))).reshape(-1)
-    _, first = np.unique(flat, return_index=True)
+    t64 = np.ascontiguousarray(tab, dtype=np.int64)
+    span = t64.max(axis=0) + 1                              # per-column radix: a mixed-radix key identifies a row
+    if float(np.prod(span.astype(np.float64))) < 2.0 ** 62:
+        w = np.concatenate([[1], np.cumprod(span[:-1])])
+        _, first = np.unique(t64 @ w, return_index=True)   # integer sort: far cheaper than sorting the raw rows
+    else:
+        flat = np.ascontiguousarray(tab, dtype=np.int32).view(np.dtype((np.void, 4 * ln))).reshape(-1)
+        _, first = np.unique(flat, return_index=True)
     if len(first) == n:
         return tab
     return tab[np.sort(first)]
@@ -146,6 +152,7 @@ class TensorCI2(AbstractTensorTrain):
         self.maxsamplevalue = 0.0
         self.Iset_history, self.Jset_history = [], []
         self.stats = {"nevals": 0, "t_eval": 0.0, "t_lu": 0.0, "t_factors": 0.0, "t_host": 0.0}
+        self._pool = {}                                     # recycled Pi buffers (see _pool_mat)
         from .matrixlu import Rng
         self.rng = Rng(0)                                   # stream behind the rook search's random rows/columns (seed: `seed=` of crossinterpolate2)
         if f is not None and Iset is not None:              # tensorci2.jl:123-137
@@ -201,7 +208,7 @@ class TensorCI2(AbstractTensorTrain):
         k = max(len(self.pivoterrors), len(errors))
         a = np.zeros(k); a[: len(self.pivoterrors)] = self.pivoterrors
         e = np.zeros(k); e[: len(errors)] = errors
-        self.pivoterrors = np.array([_jl_max(x, y) for x, y in zip(a, e)])
+        self.pivoterrors = np.maximum(a, e)                 # propagates NaN like Julia's max (padzero + max., :252-260)
 
     def flushpivoterror(self):
         self.pivoterrors = np.zeros(0)
@@ -226,13 +233,26 @@ class TensorCI2(AbstractTensorTrain):
             self.invalidatesitetensors()
 
     # ---- K1 call sites -----------------------------------------------------------------------------------
-    def _fill(self, f, I, J, M, rows, cols):
+    def _pool_mat(self, slot, rows, cols, pad=16):
+        """Pi matrices are consumed (factorised in place) right after they are filled: recycle one buffer per slot instead
+        of a fresh allocation per bond."""
+        import torch
+        ld = max((int(rows) + pad - 1) // pad * pad, 1)
+        need = max(int(cols), 1) * ld
+        buf = self._pool.get(slot)
+        if buf is None or buf.numel() < need:
+            buf = torch.empty(need, dtype=torch.float64, device=self.device)
+            self._pool[slot] = buf
+        return Mat(buf[:need].view(max(int(cols), 1), ld), rows, cols)
+
+    def _fill(self, f, I, J, M, rows, cols, slot=None):
         """filltensor (tensorci2.jl:475-497) + updatemaxsample! (:636-638) into a device matrix rows x cols
-        (column-major reshape of the (|I|, d..., |J|) array, exactly the reference's `reshape`)."""
+        (column-major reshape of the (|I|, d..., |J|) array, exactly the reference's `reshape`).  `slot`: recycle the
+        buffer of that pool slot (for matrices that do not outlive the next fill of the same slot)."""
         t0 = time.perf_counter()
         P = f.alloc_matrix(rows, cols, 16) if hasattr(f, "alloc_matrix") else None     # peer-mapped storage (sharded batch)
         if P is None:
-            P = Mat.empty(rows, cols, self.device, pad=16)
+            P = self._pool_mat(slot, rows, cols) if slot is not None else Mat.empty(rows, cols, self.device, pad=16)
         nI, nJ = I.shape[0], J.shape[0]
         if nI * nJ:
             if M == 0:
@@ -284,7 +304,7 @@ class TensorCI2(AbstractTensorTrain):
             J0 = _positions(self.Jset[b0], Jc)
 
             def pif(irows, icols):                          # SubMatrix (:764-804): strips of Pi on demand, on the device
-                return self._fill(f, Ic[irows - 1], Jc[icols - 1], 0, len(irows), len(icols))
+                return self._fill(f, Ic[irows - 1], Jc[icols - 1], 0, len(irows), len(icols), slot=0)
 
             t0 = time.perf_counter()
             te = self.stats["t_eval"]
@@ -295,7 +315,7 @@ class TensorCI2(AbstractTensorTrain):
             if luci.npivots() == 0:                         # :886-899 fall back to the full search
                 luci = None
         if luci is None:
-            Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0])
+            Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0], slot=0)
             t0 = time.perf_counter()
             luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=leftorthogonal,
                               handle=self.handle)
@@ -322,12 +342,12 @@ class TensorCI2(AbstractTensorTrain):
         f = makebatchevaluatable(f, self.localdims, self.handle)
         b0 = b - 1
         nI, nJ, d = self.Iset[b0].shape[0], self.Jset[b0].shape[0], self.localdims[b0]
-        Pi1 = self._fill(f, self.Iset[b0], self.Jset[b0], 1, nI * d, nJ)
+        Pi1 = self._fill(f, self.Iset[b0], self.Jset[b0], 1, nI * d, nJ, slot=None if b0 == len(self) - 1 else 1)
         if b0 == len(self) - 1:
             self._set_core(b0, Pi1)
             return
         nI1 = self.Iset[b0 + 1].shape[0]
-        P = self._fill(f, self.Iset[b0 + 1], self.Jset[b0], 0, nI1, nJ)
+        P = self._fill(f, self.Iset[b0 + 1], self.Jset[b0], 0, nI1, nJ, slot=2)
         if nI1 != nJ:
             raise TCIError(_lib.TCI_ERR_NOT_SQUARE, f"Pivot matrix at bond {b} is not square!")
         t0 = time.perf_counter()
@@ -373,7 +393,7 @@ class TensorCI2(AbstractTensorTrain):
             d = self.localdims[b0]
             Is = kronecker_left(self.Iset[b0], d) if fwd else self.Iset[b0]
             Js = self.Jset[b0] if fwd else kronecker_right(d, self.Jset[b0])
-            Pi = self._fill(f, self.Iset[b0], self.Jset[b0], 1, Is.shape[0], Js.shape[0])
+            Pi = self._fill(f, self.Iset[b0], self.Jset[b0], 1, Is.shape[0], Js.shape[0], slot=0)
             t0 = time.perf_counter()
             luci = MatrixLUCI(Pi, reltol=reltol, abstol=abstol, maxrank=maxbonddim, leftorthogonal=fwd, handle=self.handle)
             self.stats["t_lu"] += time.perf_counter() - t0
