@@ -298,6 +298,24 @@ class TCI2:
         self.addglobalpivots(pivots)                      # tensorci2.jl:367-377
         self.makecanonical(reltol, abstol, maxbonddim)
 
+    def addglobalpivots2sitesweep(self, pivots, tolerance=1e-8, normalizeerror=True, maxbonddim=INT64_MAX, ntry=10,
+                                  strictlynested=False):
+        """addglobalpivots2sitesweep! (tensorci2.jl:407-453)."""
+        pivots = [[int(v) for v in p] for p in pivots]
+        if any(len(p) != len(self) for p in pivots):
+            raise OracleError("Please specify a pivot as one index per leg of the MPS.")
+        pivots_ = pivots
+        for _ in range(ntry):
+            errnorm = self.maxsamplevalue if normalizeerror else 1.0
+            abstol = tolerance * errnorm
+            self.addglobalpivots(pivots_)
+            self.sweep2site(2, abstol=abstol, maxbonddim=maxbonddim, strictlynested=strictlynested)
+            newpivots = [p for p in pivots if abs(self.evaluate(p) - self.f(p)) > abstol]
+            if len(newpivots) == 0 or set(map(tuple, newpivots)) == set(map(tuple, pivots_)):
+                return len(newpivots)
+            pivots_ = newpivots
+        return len(pivots_)
+
     def fillsitetensors(self):
         _check(lib().orc_tci_fillsitetensors(self.h))
 

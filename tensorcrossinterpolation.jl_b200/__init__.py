@@ -6,7 +6,7 @@ package is importable without a GPU (so CPU-only tests can check symbols), but a
 raises if the library or a CUDA device is missing — there is no CPU fallback.
 """
 from ._lib import Handle, TCIError, default_handle, lib, SO_PATH          # noqa: F401
-from .matrixlu import (rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing, arrlu, rrlu_function, Rng,   # noqa: F401
+from .matrixlu import (rrLU, rrlu, rrlu_device, submatrixargmax, rrlu_last_timing, arrlu, rrlu_function, Rng, solve,   # noqa: F401
                        pushrandomsubset)
 from .dense import Mat, gemm, luci_factors, solve_right, trsm_right, svd, diag_scale                              # noqa: F401
 from .matrixluci import MatrixLUCI                                                  # noqa: F401
@@ -22,3 +22,4 @@ from .contraction import (Contraction, ElementwiseMap, contract, contract_naive,
 from .parallel import Comm, ShardedBatchEvaluator, partition, bond_passes                               # noqa: F401
 from .cachedfunction import CachedFunction                                                              # noqa: F401
 from .integration import integrate, kronrod                                                            # noqa: F401
+from .cachedtensortrain import TTCache, estimatetrueerror, _floatingzone                                # noqa: F401

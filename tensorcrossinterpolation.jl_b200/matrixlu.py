@@ -60,6 +60,43 @@ class rrLU:
     def lastpivoterror(self):                             # matrixlu.jl:811-813
         return self.error
 
+    def transpose(self):                                  # Base.transpose(A::rrLU) — matrixlu.jl:918-922
+        tr = (lambda M: np.asfortranarray(M.T)) if isinstance(self.L, np.ndarray) else (lambda M: M.T)
+        return rrLU(self.colpermutation, self.rowpermutation, tr(self.U), tr(self.L), not self.leftorthogonal, self.npivot,
+                    self.error, self._pivoterrors)
+
+    def solve(self, b, handle=None):                      # Base.:\(A::rrLU, b) — matrixlu.jl:891-901
+        m, n = self.size()
+        if m != n:
+            raise TCIError(_lib.TCI_ERR_INVALID, "Matrix must be square.")
+        if self.npivot != m:
+            raise TCIError(_lib.TCI_ERR_INVALID, "rank-deficient matrix is not supportred!")
+        b = np.asarray(b, dtype=np.float64)
+        x_perm = solve(_host(self.L), _host(self.U), b[self.rowpermutation - 1, :], handle=handle)
+        x = np.empty_like(x_perm)
+        x[self.colpermutation - 1, :] = x_perm
+        return x
+
+
+def _host(M):
+    return M if isinstance(M, np.ndarray) else M.cpu().numpy()
+
+
+def solve(L, U, b, handle=None):
+    """solve(L, U, b) — matrixlu.jl:839-868: x with (L * U) x = b by forward and backward substitution; here two device
+    triangular solves (csrc/dense.cu) on host matrices."""
+    from .dense import Mat, trsm_right
+    h = handle or _lib.default_handle()
+    L, U, b = np.asarray(L, dtype=np.float64), np.asarray(U, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    n2 = L.shape[1]
+    if U.shape[0] != n2 or U.shape[1] != n2 or L.shape[0] < n2 or b.shape[0] < n2:
+        raise TCIError(_lib.TCI_ERR_INVALID, "solve: L and U must be square factors of the same size")
+    dev = f"cuda:{h.device}"
+    Lm, Um, Bm = Mat.from_numpy(L[:n2], dev), Mat.from_numpy(U, dev), Mat.from_numpy(b[:n2], dev)
+    trsm_right(h, Lm, n2, True, False, Bm, left=True)      # L y = b
+    trsm_right(h, Um, n2, False, False, Bm, left=True)     # U x = y
+    return Bm.numpy()
+
 
 def _empty_like(M):
     if isinstance(M, np.ndarray):

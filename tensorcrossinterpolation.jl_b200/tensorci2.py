@@ -425,6 +425,34 @@ class TensorCI2(AbstractTensorTrain):
         self.addglobalpivots(pivots)
         self.makecanonical(f, reltol=reltol, abstol=abstol, maxbonddim=maxbonddim)
 
+    def addglobalpivots2sitesweep(self, f, pivots, tolerance=1e-8, normalizeerror=True, maxbonddim=INT_MAX, pivotsearch="full",
+                                  verbosity=0, ntry=10, strictlynested=False):
+        """addglobalpivots2sitesweep! (tensorci2.jl:407-453): add the pivots, run two 2-site half-sweeps, repeat with the
+        pivots that are still not interpolated within tolerance.  Returns how many remain."""
+        pivots = [[int(v) for v in p] for p in pivots]
+        if any(len(p) != len(self) for p in pivots):
+            raise TCIError(_lib.TCI_ERR_INVALID, "Please specify a pivot as one index per leg of the MPS.")
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        pivots_ = pivots
+        for _ in range(ntry):
+            errornormalization = self.maxsamplevalue if normalizeerror else 1.0
+            abstol = tolerance * errornormalization
+            self.addglobalpivots(pivots_)
+            self.sweep2site(f, 2, abstol=abstol, maxbonddim=maxbonddim, pivotsearch=pivotsearch, strictlynested=strictlynested,
+                            verbosity=verbosity)
+            if pivots:
+                pts = np.asarray(pivots, dtype=np.int32)
+                err = np.abs(self.evaluate_batch(pts) - _point_values(f, pts))      # one K4b + one K1 call for all pivots
+                newpivots = [p for p, e in zip(pivots, err) if e > abstol]
+            else:
+                newpivots = []
+            if verbosity > 0:
+                print(f"Trying to add {len(pivots_)} global pivots, {len(newpivots)} still remain.")
+            if len(newpivots) == 0 or set(map(tuple, newpivots)) == set(map(tuple, pivots_)):
+                return len(newpivots)
+            pivots_ = newpivots
+        return len(pivots_)
+
     def sweep2site(self, f, niter, iter1=1, abstol=1e-8, maxbonddim=INT_MAX, sweepstrategy="backandforth",
                    pivotsearch="full", verbosity=0, strictlynested=False, fillsitetensors=True, bondorder="sequential",
                    comm=None):

@@ -222,3 +222,13 @@ def test_kronrod15_rule_is_exact_to_degree_22():
     assert np.all(np.diff(x) > 0) and abs(w.sum() - 2.0) < 1e-15
     for k in range(0, 23, 2):
         assert abs(np.sum(w * x ** k) - 2.0 / (k + 1)) < 1e-14
+
+
+def test_insert_global_pivots_oracle():                 # test/test_tensorci2.jl:395-431
+    R, abstol = 12, 1e-4
+    f = O.Func(O.F_CALLBACK, callback=lambda q: 1.0 if (all(v == 1 for v in q) or all(v == 2 for v in q)) else 0.0)
+    tci, _, _ = O.crossinterpolate2(f, [2] * R, [[1] * R], tolerance=abstol, maxbonddim=1000, maxiter=20, normalizeerror=False)
+    r = [2] * R
+    tci.addglobalpivots2sitesweep([r], tolerance=abstol, normalizeerror=False, maxbonddim=1000)
+    assert tci.evaluate(r) == pytest.approx(1.0, rel=1e-12)
+    assert tci.evaluate([1] * R) == pytest.approx(1.0, rel=1e-12)
