@@ -11,9 +11,11 @@
 // columns of W and of the accumulated V).  HBM-bound: a round reads and writes W and V once, 16 B per element.
 // A sweep is n-1 rounds; sweeps repeat until no pair needed a rotation (|a.b| <= tol |a||b|, tol = sqrt(m) eps, the dgesvj
 // criterion).  Singular values are the column norms, sorted on the host (k doubles), U/V^T are emitted in that order.
+// One sweep (n-1 launches of a few microseconds) is captured once into a CUDA graph and replayed per sweep.
 #include "context.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <numeric>
 #include <vector>
 
@@ -170,6 +172,17 @@ int tci_svd_f64(tci_handle h, double* d_A, int64_t m64, int64_t n64, int64_t lda
     int* dperm = (int*)(dS + wn);
     int* dflag = dperm + wn;
     double* W = d_A; long long ldw = lda;
+    // The sweep loop is launch-bound for the bond dimensions TCI produces (n - 1 rounds of a few microseconds each), so one
+    // sweep is captured into a CUDA graph and replayed.  The legacy default stream cannot be captured: all of this call's
+    // work runs on the handle's own stream, ordered after the caller's stream by an event.
+    cudaStream_t caller = h->stream;
+    cudaStream_t cs = h->own_stream ? h->own_stream : h->stream;
+    if (cs != caller) {
+        TCI_CUDA(h, cudaEventRecord(h->ev[3], caller));
+        TCI_CUDA(h, cudaStreamWaitEvent(cs, h->ev[3], 0));
+    }
+    struct StreamGuard { tci_handle h; cudaStream_t s; ~StreamGuard() { h->stream = s; } } guard{h, caller};
+    h->stream = cs;
     if (!tall) {
         rc = tci_ws_reserve(h, h->ws_b, sizeof(double) * (size_t)wm * wn);
         if (rc) return rc;
@@ -183,17 +196,38 @@ int tci_svd_f64(tci_handle h, double* d_A, int64_t m64, int64_t n64, int64_t lda
     const double tol = sqrt((double)wm) * 1.1102230246251565e-16;
     int sweeps = 0, flag = wn > 1 ? 1 : 0;
     const int kMaxSweeps = 60;
+    cudaGraphExec_t exec = nullptr;
+    static const int use_graph = []() { const char* e = getenv("TCI_SVD_GRAPH"); return e ? atoi(e) : 1; }();
+    if (flag && use_graph && npad - 1 >= 8 && cs != nullptr && cs != cudaStreamLegacy) {
+        if (cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+            cudaMemsetAsync(dflag, 0, sizeof(int), cs);
+            for (int round = 0; round < npad - 1; ++round)
+                jacobi_round_kernel<<<npad / 2, JT, 0, cs>>>(W, ldw, wm, V, wn, wn, wn, npad, round, tol, dflag);
+            cudaGraph_t g = nullptr;
+            if (cudaStreamEndCapture(cs, &g) == cudaSuccess && g) {
+                if (cudaGraphInstantiate(&exec, g, 0) != cudaSuccess) exec = nullptr;
+                cudaGraphDestroy(g);
+            }
+        }
+        (void)cudaGetLastError();                         // a failed capture falls back to plain launches
+    }
     while (flag && sweeps < kMaxSweeps) {
-        TCI_CUDA(h, cudaMemsetAsync(dflag, 0, sizeof(int), h->stream));
-        for (int round = 0; round < npad - 1; ++round) {
-            jacobi_round_kernel<<<npad / 2, JT, 0, h->stream>>>(W, ldw, wm, V, wn, wn, wn, npad, round, tol, dflag);
-            TCI_LAUNCH_CHECK(h);
+        if (exec) {
+            TCI_CUDA(h, cudaGraphLaunch(exec, cs));
+            h->launches += npad - 1;
+        } else {
+            TCI_CUDA(h, cudaMemsetAsync(dflag, 0, sizeof(int), h->stream));
+            for (int round = 0; round < npad - 1; ++round) {
+                jacobi_round_kernel<<<npad / 2, JT, 0, h->stream>>>(W, ldw, wm, V, wn, wn, wn, npad, round, tol, dflag);
+                TCI_LAUNCH_CHECK(h);
+            }
         }
         TCI_CUDA(h, cudaMemcpyAsync(h->pinned, dflag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
         TCI_CUDA(h, cudaStreamSynchronize(h->stream));
         flag = *(int*)h->pinned;
         ++sweeps;
     }
+    if (exec) cudaGraphExecDestroy(exec);
     if (h_sweeps) *h_sweeps = sweeps;
     if (flag) return tci_fail(h, TCI_ERR_INVALID, "tci_svd_f64: Jacobi iteration did not converge in %d sweeps", kMaxSweeps);
     col_norm_kernel<<<wn, JT, 0, h->stream>>>(W, ldw, wm, dS);
