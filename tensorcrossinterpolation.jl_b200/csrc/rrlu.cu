@@ -139,7 +139,8 @@ __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n,
                                            const double* __restrict__ xcol /* scaled pivot column, indexed by row (UPDATE only) */,
                                            int r0, int c0, int np, int serpentine, const ColOrder vpos,
                                            double& bv, double& bx, int& bi, int& bj) {
-    const bool rev = serpentine == 2 ? true : (serpentine == 3 ? !(np & 1) : (serpentine && (np & 1)));
+    const int smode = serpentine & 7;
+    const bool rev = smode == 2 ? true : (smode == 3 ? !(np & 1) : (smode && (np & 1)));
     const int nct = (n - c0 + COLS - 1) / COLS;
     if (VEC) {
         // Row tiling: start at the 128-byte line that holds row r0 (rows below r0 are masked), and split the
@@ -152,8 +153,14 @@ __device__ __forceinline__ void scan_tiles(double* __restrict__ A, int m, int n,
         const int rpt = (((h + nrt - 1) / nrt) + 15) & ~15;          // rows per tile, multiple of 16, <= TR
         const int ntiles = nrt * nct;                                // < 2^31: m, n < 2^31 - 1024 and TR * COLS >= 2048
         const int il = threadIdx.x * 2;
+        // serpentine & 8: contiguous tile ranges per block (each block streams down its own columns) instead of round-robin
+        const bool blocked = (serpentine & 8) != 0;
+        const int per = (ntiles + (int)gridDim.x - 1) / (int)gridDim.x;
+        const int tb = blocked ? (int)blockIdx.x * per : (int)blockIdx.x;
+        const int te = blocked ? min(ntiles, tb + per) : ntiles;
+        const int ts = blocked ? 1 : (int)gridDim.x;
         if (il < rpt) {
-            for (int t0 = blockIdx.x; t0 < ntiles; t0 += gridDim.x) {
+            for (int t0 = tb; t0 < te; t0 += ts) {
                 const int t = rev ? ntiles - 1 - t0 : t0;
                 const int rt = t % nrt, ct = t / nrt;
                 const int i0 = rbase + rt * rpt + il;
@@ -577,10 +584,34 @@ cudaError_t launch_pdl(tci_handle h, void (*kern)(KArgs...), unsigned grid, unsi
     return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 
+// Same, plus an L2 access-policy window: accesses inside [win, win + winbytes) are cached as PERSISTING, everything else as
+// streaming.  The step kernels put the window on the part of the trailing block that the current pass touches LAST and the
+// next (reversed) pass touches FIRST, so those lines are still in L2 — dirty — when they are read and rewritten again.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl_win(tci_handle h, void (*kern)(KArgs...), unsigned grid, unsigned block, void* win, size_t winbytes, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = h->stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = h->rrlu_pdl ? 1 : 0;
+    int na = 1;
+    if (win && winbytes) {
+        attr[1].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[1].val.accessPolicyWindow.base_ptr = win;
+        attr[1].val.accessPolicyWindow.num_bytes = winbytes;
+        attr[1].val.accessPolicyWindow.hitRatio = 1.0f;
+        attr[1].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[1].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        na = 2;
+    }
+    cfg.attrs = attr; cfg.numAttrs = na;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 template <bool UPDATE>
 void launch_update(tci_handle h, bool vec, const UpdateCfg& c, double* A, int m, int n, long long lda, const SmallWs& w,
-                   int maxrank, double reltol, double abstol, int start0 = 0) {
-#define TCI_LAUNCH_UPD(V, CC) launch_pdl(h, rrlu_update_kernel<UPDATE, V, CC>, (unsigned)c.grid, (unsigned)kThreads, A, m, n, lda, (const double*)w.ybuf, w.st, w.parts, maxrank, reltol, abstol, start0, c.serpentine)
+                   int maxrank, double reltol, double abstol, int start0 = 0, void* win = nullptr, size_t winbytes = 0) {
+#define TCI_LAUNCH_UPD(V, CC) launch_pdl_win(h, rrlu_update_kernel<UPDATE, V, CC>, (unsigned)c.grid, (unsigned)kThreads, win, winbytes, A, m, n, lda, (const double*)w.ybuf, w.st, w.parts, maxrank, reltol, abstol, start0, c.serpentine)
     if (!vec) TCI_LAUNCH_UPD(false, 8);
     else if (c.cols == 4) TCI_LAUNCH_UPD(true, 4);
     else if (c.cols == 16) TCI_LAUNCH_UPD(true, 16);
@@ -1011,7 +1042,40 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
         }
         return TCI_OK;
     }
-    launch_update<false>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
+    // Persisting-L2 window (see launch_pdl_win): sized to the device's persisting set-aside; TCI_RRLU_L2PERSIST = MB (0 off).
+    if (h->l2_window_bytes < 0) {
+        h->l2_window_bytes = 0;
+        long long want_mb = 16;                                // measured best on B200: +1.6 % (8192^2) / +2.9 % (5120^2); 32 MB and more lose
+        if (const char* e = getenv("TCI_RRLU_L2PERSIST")) want_mb = atoll(e);
+        int maxpersist = 0, maxwin = 0;
+        cudaDeviceGetAttribute(&maxpersist, cudaDevAttrMaxPersistingL2CacheSize, h->device);
+        cudaDeviceGetAttribute(&maxwin, cudaDevAttrMaxAccessPolicyWindowSize, h->device);
+        if (want_mb != 0 && maxpersist > 0 && maxwin > 0) {
+            long long bytes = want_mb < 0 ? (long long)maxpersist : want_mb * (1LL << 20);
+            if (bytes > maxpersist) bytes = maxpersist;
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)bytes) == cudaSuccess)
+                h->l2_window_bytes = bytes < maxwin ? bytes : maxwin;
+            if (getenv("TCI_RRLU_L2PERSIST_VERBOSE"))
+                fprintf(stderr, "rrlu: persisting L2 max %d B, max window %d B, using %lld B\n", maxpersist, maxwin, h->l2_window_bytes);
+        }
+        (void)cudaGetLastError();
+    }
+    const bool use_win = h->l2_window_bytes > 0 && (cfg.serpentine & 7) == 1 && (double)m * n * 8.0 > 2.0 * (double)h->l2_window_bytes;
+    auto window_of = [&](int np, void** base, size_t* bytes) {   // the tail of the pass that ends with np pivots in place
+        *base = nullptr; *bytes = 0;
+        if (!use_win || np >= n) return;
+        long long wcols = h->l2_window_bytes / (long long)(lda * 8);
+        if (wcols > n - np) wcols = n - np;
+        if (wcols <= 0) return;
+        const bool rev = (np & 1) != 0;                          // same rule as scan_tiles (serpentine mode 1)
+        const long long c_first = rev ? np : n - wcols;          // forward passes end on the highest columns, reversed ones on the lowest
+        *base = d_A + c_first * lda;
+        *bytes = (size_t)(wcols * lda * 8);
+    };
+    {
+        void* wb; size_t wn; window_of(0, &wb, &wn);
+        launch_update<false>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, 0, wb, wn);
+    }
     TCI_LAUNCH_CHECK(h);
     const int swap_blocks = (m + n + 1 + 255) / 256;
     int launched = 0, chunk = 8;
@@ -1024,7 +1088,10 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
             launch_pdl(h, rrlu_swap_kernel, (unsigned)swap_blocks, 256u, d_A, m, n, lda, w->ybuf, w->st, w->rowperm, w->colperm, w->pivvals, leftorth);
             TCI_LAUNCH_CHECK(h);
             if (h->rrlu_profile) TCI_CUDA(h, cudaEventRecord(h->ev_pool[2 * (launched + s)], h->stream));
-            launch_update<true>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol);
+            {
+                void* wb; size_t wn; window_of(launched + s + 1, &wb, &wn);
+                launch_update<true>(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, 0, wb, wn);
+            }
             TCI_LAUNCH_CHECK(h);
             if (h->rrlu_profile) TCI_CUDA(h, cudaEventRecord(h->ev_pool[2 * (launched + s) + 1], h->stream));
         }
@@ -1038,6 +1105,7 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
         return tci_fail(h, TCI_ERR_CUDA, "rrlu: device loop did not terminate (npivot=%d, maxrank=%d)", hst->npivot, mr);
     }
     TCI_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+    if (use_win) (void)cudaCtxResetPersistingL2Cache();    // hand the set-aside lines back
     *final_state = *hst;
     h->rrlu_steps = hst->npivot;
     h->rrlu_ms[1] = 0.0;
