@@ -85,8 +85,22 @@ def main():
     t_seq = timed(lambda: sweep(), reps=2)
     t_oe1 = timed(lambda: sweep(bondorder="oddeven"), reps=2)
     t_oe = timed(lambda: sweep(bondorder="oddeven", comm=comm), reps=2)
+    # sequential bond order (the reference's) with the columns of every large Pi spread over the ranks: K1 evaluates only
+    # the local column block, the sharded rrLU factorises it in place; must reproduce the one-GPU pivots exactly
+    ref_tci = T.crossinterpolate2(f, ld, **kw)[0]
+    sh_tci = T.crossinterpolate2(f, ld, **kw, comm=comm)[0]
+    same = all(np.array_equal(a, b) for a, b in zip(ref_tci.Iset, sh_tci.Iset)) and \
+        all(np.array_equal(a, b) for a, b in zip(ref_tci.Jset, sh_tci.Jset))
+    t_cs = timed(lambda: sweep(comm=comm), reps=2)
     out["c3h_sweep"] = {"sequential_replicated_s": t_seq, "oddeven_one_gpu_s": t_oe1, "oddeven_bonds_over_ranks_s": t_oe,
-                        "speedup_vs_sequential": t_seq / t_oe}
+                        "speedup_vs_sequential": t_seq / t_oe, "sequential_columns_over_ranks_s": t_cs,
+                        "columns_speedup_vs_sequential": t_seq / t_cs, "columns_pivots_identical": bool(same),
+                        "columns_sharded_bonds": int(sh_tci.stats.get("nsharded", 0))}
+    if os.environ.get("C3H512", "1") != "0":             # the same sweep at maxbonddim=512: Pi up to 10240 x 10240
+        kw5 = dict(kw, maxbonddim=512, maxiter=1)
+        t1 = timed(lambda: T.crossinterpolate2(f, ld, **kw5), reps=1)
+        t8 = timed(lambda: T.crossinterpolate2(f, ld, **kw5, comm=comm), reps=1)
+        out["c3h512_sweep"] = {"sequential_replicated_s": t1, "sequential_columns_over_ranks_s": t8, "speedup": t1 / t8}
     if rank == 0:
         print(json.dumps({"n_gpus": world, **out}), flush=True)
     dist.destroy_process_group()

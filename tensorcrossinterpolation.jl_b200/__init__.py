@@ -19,7 +19,7 @@ from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecrite
                         HostFunctionAdapter, makebatchevaluatable, optfirstpivot)
 from .tensor import DTensor, _contract                                                                  # noqa: F401
 from .contraction import (Contraction, ElementwiseMap, contract, contract_naive, contract_zipup, contract_TCI)   # noqa: F401
-from .parallel import Comm, ShardedBatchEvaluator, partition, bond_passes                               # noqa: F401
+from .parallel import Comm, ShardedBatchEvaluator, partition, bond_passes, MailboxPool, gather_sharded_U                               # noqa: F401
 from .cachedfunction import CachedFunction                                                              # noqa: F401
 from .integration import integrate, kronrod                                                            # noqa: F401
 from .cachedtensortrain import TTCache, estimatetrueerror, _floatingzone                                # noqa: F401

@@ -64,7 +64,7 @@ int tci_destroy(tci_handle h) {
     if (!h) return TCI_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    tci_workspace* wss[] = {&h->ws_matrix, &h->ws_lu, &h->ws_small, &h->ws_a, &h->ws_b, &h->ws_c};
+    tci_workspace* wss[] = {&h->ws_matrix, &h->ws_lu, &h->ws_small, &h->ws_a, &h->ws_b, &h->ws_c, &h->dist_parked};
     for (auto* w : wss) if (w->ptr) cudaFree(w->ptr);
     if (h->pinned) cudaFreeHost(h->pinned);
     for (int i = 0; i < 4; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);

@@ -37,6 +37,7 @@ struct tci_context {
     std::vector<float> rrlu_launch_ms;      // per-launch update-kernel times of the last profiled rrlu
     // generic scratch for the other kernels
     tci_workspace ws_a, ws_b, ws_c;
+    tci_workspace dist_parked;              // state block of the last destroyed sharded rrLU, reused by the next create
 };
 
 int tci_fail(tci_handle h, int code, const char* fmt, ...);

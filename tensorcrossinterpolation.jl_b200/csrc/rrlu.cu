@@ -1287,6 +1287,7 @@ struct tci_rrlu_dist_s {
     double reltol, abstol;
     long long reclen;
     void* block;                 // one allocation behind all the arrays
+    size_t block_bytes;
     DistArrays a;
     PeerBox peers;               // n == 0 until tci_rrlu_dist_set_mailboxes
 };
@@ -1322,7 +1323,15 @@ int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64
                  o_gid = o_c2p + al(sizeof(int) * n), o_y = o_gid + al(sizeof(int) * (nloc + 1)), o_x = o_y + al(sizeof(double) * (nloc + 1)),
                  o_pv = o_x + al(sizeof(double) * (m + 2)), o_parts = o_pv + al(sizeof(double) * d->maxrank),
                  o_L = o_parts + al(sizeof(Cand4) * d->grid), total = o_L + al(sizeof(double) * (size_t)m * d->maxrank);
-    if (cudaMalloc(&d->block, total) != cudaSuccess) { delete d; return tci_fail(h, TCI_ERR_NOMEM, "tci_rrlu_dist_create: cudaMalloc of %zu bytes failed", total); }
+    // a sweep creates one of these per bond: take the block the previous one parked in the handle when it is large enough
+    // (cudaMalloc / cudaFree cost milliseconds each once peer mappings exist)
+    if (h->dist_parked.ptr && h->dist_parked.bytes >= total) {
+        d->block = h->dist_parked.ptr; d->block_bytes = h->dist_parked.bytes;
+        h->dist_parked.ptr = nullptr; h->dist_parked.bytes = 0;
+    } else {
+        if (cudaMalloc(&d->block, total) != cudaSuccess) { delete d; return tci_fail(h, TCI_ERR_NOMEM, "tci_rrlu_dist_create: cudaMalloc of %zu bytes failed", total); }
+        d->block_bytes = total;
+    }
     char* b = (char*)d->block;
     d->a.st = (DistState*)(b + o_st); d->a.rowperm = (int*)(b + o_rp); d->a.pos2col = (int*)(b + o_p2c); d->a.col2pos = (int*)(b + o_c2p);
     d->a.gid = (int*)(b + o_gid); d->a.ybuf = (double*)(b + o_y); d->a.xcol = (double*)(b + o_x); d->a.pivvals = (double*)(b + o_pv);
@@ -1452,7 +1461,13 @@ int tci_rrlu_dist_finish(tci_handle h, tci_rrlu_dist d, const double* d_A, int64
 int tci_rrlu_dist_destroy(tci_handle h, tci_rrlu_dist d) {
     if (!d) return TCI_OK;
     if (h) cudaSetDevice(h->device);
-    cudaFree(d->block);
+    if (h && d->block_bytes > h->dist_parked.bytes) {    // park the larger block (stream order protects its reuse)
+        if (h->dist_parked.ptr) { cudaStreamSynchronize(h->stream); cudaFree(h->dist_parked.ptr); }
+        h->dist_parked.ptr = d->block; h->dist_parked.bytes = d->block_bytes;
+    } else {
+        if (h) cudaStreamSynchronize(h->stream);
+        cudaFree(d->block);
+    }
     delete d;
     return TCI_OK;
 }

@@ -32,6 +32,17 @@ class MatrixLUCI:
         self._left = self._right = None
         return self
 
+    @classmethod
+    def from_rrlu(cls, lu, m, n, handle=None):
+        """MatrixLUCI around an rrLU that was computed elsewhere (the column-sharded factorisation): `lu` carries device
+        factors `Lmat` (m x r) and `Umat` (r x n)."""
+        self = cls.__new__(cls)
+        self.handle = handle or _lib.default_handle()
+        self.m, self.n = int(m), int(n)
+        self.lu = lu
+        self._left = self._right = None
+        return self
+
     def size(self):                                        # matrixluci.jl:94-96
         return (self.m, self.n)
 

@@ -433,6 +433,8 @@ def rrlu_sharded(A_local, n, col0, comm=None, maxrank=None, reltol=1e-14, abstol
     rank = 0 if comm is None else comm.rank
     s = ShardedRRLU(A_local, n, col0, rank, size, maxrank, reltol, abstol, leftorthogonal, handle)
     if fused and size > 1:
+        if hasattr(peers, "get"):                        # a MailboxPool: grows collectively when this matrix needs more
+            peers = peers.get(s.mailbox_doubles())
         own_peers = peers is None
         if own_peers:
             peers = PeerBuffers(s.h, comm, s.mailbox_doubles(), nslots=1)
@@ -460,6 +462,52 @@ def rrlu_sharded(A_local, n, col0, comm=None, maxrank=None, reltol=1e-14, abstol
     out = s.finish()
     s.close()
     return out
+
+
+class MailboxPool:
+    """The peer-mapped mailboxes of the fused sharded rrLU, created once per run and re-created (collectively: every rank
+    sees the same matrix sizes) only when a larger matrix arrives."""
+
+    def __init__(self, handle, comm):
+        self.handle, self.comm, self.peers = handle, comm, None
+
+    def get(self, need):
+        if self.peers is None or self.peers.slot_elems < need:
+            if self.peers is not None:
+                self.peers.close()
+            self.peers = PeerBuffers(self.handle, self.comm, max(int(need), 1 << 16), nslots=1)
+        return self.peers
+
+    def close(self):
+        if self.peers is not None:
+            self.peers.close()
+            self.peers = None
+
+
+def gather_sharded_U(out, n, blocks, comm):
+    """The full U (npivot x n, swapped column order) as a device `Mat` on every rank, from the per-rank pieces of
+    `rrlu_sharded`: one all-gather of the (padded) local blocks, each column tagged with its global position, then a
+    device scatter of the columns to their positions."""
+    import torch
+    from .dense import Mat
+    r, Uloc, locpos = out["npivot"], out["Uloc"], out["locpos"]
+    dev = Uloc.buf.device
+    mx = max(e - s for s, e in blocks)
+    nloc = Uloc.cols
+    mine = torch.zeros((mx, r + 1), dtype=torch.float64, device=dev)
+    if nloc:
+        mine[:nloc, :r] = Uloc.buf[:nloc, :r]
+        mine[:nloc, r] = torch.from_numpy(np.asarray(locpos, dtype=np.float64)).to(dev)
+    allb = torch.empty((comm.size * mx, r + 1), dtype=torch.float64, device=dev)
+    comm.dist.all_gather_into_tensor(allb, mine, group=comm.group)
+    keep = np.concatenate([np.arange(q * mx, q * mx + (e - s)) for q, (s, e) in enumerate(blocks)])
+    if len(keep) != n:
+        raise ValueError("gather_sharded_U: the column blocks do not cover the matrix")
+    rows = allb[torch.from_numpy(keep).to(dev)] if len(keep) != comm.size * mx else allb
+    U = Mat.empty(max(r, 1), n, dev)
+    U.rows = r
+    U.buf[:n, :r].index_copy_(0, rows[:, r].to(torch.int64), rows[:, :r].contiguous())
+    return U
 
 
 def rrlu_sharded_virtual(A, nranks, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None):

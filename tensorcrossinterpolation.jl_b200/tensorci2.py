@@ -5,6 +5,7 @@ the host language.  Every number is produced by the CUDA library: K1 batch evalu
 rrLU (matrixlu.py), K4a factors/solves (dense.py), K4b evaluate/sum (tensortrain.py).  Index sets are int32
 tables (count x length), 1-based values like Julia.  Bond/site arguments of public methods are 1-based.
 """
+import os
 import time
 
 import numpy as np
@@ -153,6 +154,8 @@ class TensorCI2(AbstractTensorTrain):
         self.Iset_history, self.Jset_history = [], []
         self.stats = {"nevals": 0, "t_eval": 0.0, "t_lu": 0.0, "t_factors": 0.0, "t_host": 0.0}
         self._pool = {}                                     # recycled Pi buffers (see _pool_mat)
+        self._colcomm, self._mailpool = None, None          # column-sharded bonds (sweep2site with a communicator)
+        self.shard_min_elems = int(os.environ.get("TCI_SHARD_MIN_ELEMS", 1 << 20))   # smaller Pi stay replicated
         from .matrixlu import Rng
         self.rng = Rng(0)                                   # stream behind the rook search's random rows/columns (seed: `seed=` of crossinterpolate2)
         if f is not None and Iset is not None:              # tensorci2.jl:123-137
@@ -314,6 +317,11 @@ class TensorCI2(AbstractTensorTrain):
             self.stats["t_lu"] += time.perf_counter() - t0 - (self.stats["t_eval"] - te)
             if luci.npivots() == 0:                         # :886-899 fall back to the full search
                 luci = None
+        cc = self._colcomm
+        if luci is None and cc is not None and Jc.shape[0] >= 2 * cc.size \
+                and Ic.shape[0] * Jc.shape[0] >= self.shard_min_elems:
+            luci = self._luci_colsharded(f, Ic, Jc, cc, reltol, abstol, maxbonddim, leftorthogonal)
+            t0 = time.perf_counter()
         if luci is None:
             Pi = self._fill(f, Ic, Jc, 0, Ic.shape[0], Jc.shape[0], slot=0)
             t0 = time.perf_counter()
@@ -334,6 +342,37 @@ class TensorCI2(AbstractTensorTrain):
         self.updateerrors(b0, errs)
         self.last_luci = luci
         return errs
+
+    def _luci_colsharded(self, f, Ic, Jc, comm, reltol, abstol, maxbonddim, leftorthogonal):
+        """The full-search branch of updatepivots! with the COLUMNS of Pi spread over the ranks of `comm`:
+        every rank evaluates only its column block (K1, no exchange), the blocks are factorised in place by the
+        column-sharded rrLU (one candidate record per rank and pivot step through the peer mailboxes) and only the
+        r x n factor U is gathered.  Pi is never assembled on one GPU; pivots, L, U are bit-identical to the one-GPU rrLU."""
+        from .matrixlu import rrLU
+        from .parallel import MailboxPool, gather_sharded_U, partition, rrlu_sharded
+        nI, nJ = Ic.shape[0], Jc.shape[0]
+        blocks = partition(nJ, comm.size)
+        s, e = blocks[comm.rank]
+        Pl = self._fill(f, Ic, Jc[s:e], 0, nI, e - s, slot=0)
+        t0 = time.perf_counter()
+        if self._mailpool is None:
+            self._mailpool = MailboxPool(self.handle, comm)
+        out = rrlu_sharded(Pl, nJ, s, comm, maxrank=maxbonddim, reltol=reltol, abstol=abstol, leftorthogonal=leftorthogonal,
+                           handle=self.handle, fused=True, peers=self._mailpool)
+        U = gather_sharded_U(out, nJ, blocks, comm)
+        L = out["L"]
+        lu = rrLU(out["rowperm"], out["colperm"], L.view(), U.view(), leftorthogonal, out["npivot"], out["error"],
+                  out["pivoterrors"])
+        lu.Lmat, lu.Umat = L, U
+        self.stats["t_lu"] += time.perf_counter() - t0
+        self.stats["nsharded"] = self.stats.get("nsharded", 0) + 1
+        return MatrixLUCI.from_rrlu(lu, nI, nJ, self.handle)
+
+    def close_parallel(self):
+        """Release the peer-mapped mailboxes (collective: every rank calls it)."""
+        if self._mailpool is not None:
+            self._mailpool.close()
+            self._mailpool = None
 
     def setsitetensor(self, f, b, leftorthogonal=True):
         """setsitetensor!(tci, f, b) (tensorci2.jl:599-629)."""
@@ -457,11 +496,16 @@ class TensorCI2(AbstractTensorTrain):
                    pivotsearch="full", verbosity=0, strictlynested=False, fillsitetensors=True, bondorder="sequential",
                    comm=None):
         """sweep2site! (tensorci2.jl:1195-1258).  bondorder='oddeven' (+ optional `comm`) is the parallel-bond variant
-        (parallel.py); the default is the reference's sequential order."""
+        (parallel.py); the default is the reference's sequential order, and with a communicator of several ranks that order
+        is kept: every rank visits every bond and each Pi of at least `shard_min_elems` entries is evaluated and
+        factorised column-sharded (`_luci_colsharded`), the smaller ones redundantly on every rank."""
         from .parallel import bond_passes, run_pass
         f = makebatchevaluatable(f, self.localdims, self.handle)
-        if comm is not None and comm.size > 1 and bondorder != "oddeven":
-            raise TCIError(_lib.TCI_ERR_INVALID, "bonds can only be spread over ranks with bondorder='oddeven'")
+        colsharded = comm is not None and comm.size > 1 and bondorder == "sequential"
+        if colsharded and pivotsearch != "full":
+            raise TCIError(_lib.TCI_ERR_INVALID, "with several ranks the sequential bond order shards the columns of Pi, "
+                           "which needs pivotsearch=:full")
+        self._colcomm = comm if colsharded else None       # every rank visits every bond; large Pi are column-sharded
         self.invalidatesitetensors()
         n = len(self)
         for it in range(iter1, iter1 + niter):
@@ -480,7 +524,10 @@ class TensorCI2(AbstractTensorTrain):
                                          verbosity=verbosity, extraIset=extraI[b], extraJset=extraJ[b - 1])
 
             for bonds in bond_passes(n - 1, fwd, bondorder):
-                run_pass(self, bonds, update, comm)
+                run_pass(self, bonds, update, None if colsharded else comm)
+        if colsharded:
+            self._colcomm = None
+            self.maxsamplevalue = comm.allreduce_max(self.maxsamplevalue)
         if fillsitetensors:
             self.fillsitetensors(f, comm)
 
@@ -618,6 +665,8 @@ def optimize(tci, f, tolerance=None, pivottolerance=None, maxbonddim=INT_MAX, ma
     errornormalization = tci.maxsamplevalue if normalizeerror else 1.0
     abstol = tol * errornormalization
     tci.sweep1site(f, abstol=abstol, maxbonddim=maxbonddim)
+    if comm is not None:
+        tci.close_parallel()
     _sanitycheck(tci)
     return np.asarray(ranks, dtype=np.int64), np.asarray(errors) / errornormalization
 

@@ -54,9 +54,22 @@ def _worker(rank, world, port, q):
         ff = T.ShardedBatchEvaluator(f, comm, fused=True)      # peer-store kernel: compute + all-gather in one launch
         t3, ranks3, errors3 = T.crossinterpolate2(ff, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, handle=h)
         fused_used = ff.peers is not None
+        # sequential bonds, columns of every Pi with >= 64 entries spread over the ranks (sharded K1 + sharded rrLU)
+        t1, ranks1, errors1 = T.crossinterpolate2(f, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, handle=h)
+        os.environ["TCI_SHARD_MIN_ELEMS"] = "64"
+        t4, ranks4, errors4 = T.crossinterpolate2(f, [d] * n, tolerance=1e-9, nsearchglobalpivot=0, comm=comm, handle=h)
+        os.environ.pop("TCI_SHARD_MIN_ELEMS")
+        cols = {"ranks4": [int(r) for r in ranks4], "errors4": [float(e) for e in errors4], "nsharded": int(t4.stats.get("nsharded", 0)),
+                "I4": [s.tolist() for s in t4.Iset], "J4": [s.tolist() for s in t4.Jset],
+                "same_as_one_gpu": bool(all(np.array_equal(a, b) for a, b in zip(t1.Iset, t4.Iset))
+                                        and all(np.array_equal(a, b) for a, b in zip(t1.Jset, t4.Jset))
+                                        and list(errors1) == list(errors4))}
         rng = np.random.default_rng(0)
         pts = rng.integers(1, d + 1, size=(50, n))
-        q.put((rank, {"ranks3": [int(r) for r in ranks3], "I3": [s.tolist() for s in t3.Iset], "vals3": t3.evaluate_batch(pts).tolist(),
+        pts4 = np.random.default_rng(1).integers(1, d + 1, size=(50, n))
+        cols["vals4"] = t4.evaluate_batch(pts4).tolist()
+        cols["vals1"] = t1.evaluate_batch(pts4).tolist()
+        q.put((rank, {**cols, "ranks3": [int(r) for r in ranks3], "I3": [s.tolist() for s in t3.Iset], "vals3": t3.evaluate_batch(pts).tolist(),
                       "fused_used": fused_used,"ranks": [int(r) for r in ranks], "errors": [float(e) for e in errors],
                       "I": [s.tolist() for s in t.Iset], "J": [s.tolist() for s in t.Jset], "vals": t.evaluate_batch(pts).tolist(),
                       "ranks2": [int(r) for r in ranks2], "I2": [s.tolist() for s in t2.Iset], "vals2": t2.evaluate_batch(pts).tolist()}))
@@ -93,6 +106,9 @@ def test_multi_gpu_matches_single_process(tci):
             assert np.array_equal(tab(res["I2"][b], b), s.Iset(b + 1))
         assert res["ranks2"] == list(sranks) and res["ranks3"] == list(sranks) and res["fused_used"]
         assert res["I3"] == res["I2"] and res["vals3"] == res["vals2"]
+        assert res["nsharded"] > 0 and res["same_as_one_gpu"] and res["ranks4"] == list(sranks)
+        assert np.allclose(res["errors4"], serrors, rtol=1e-10) and res["I4"] == res["I2"]
+        assert np.allclose(res["vals4"], res["vals1"], rtol=1e-12, atol=0) and res["vals4"] == out[0]["vals4"]
         assert res["vals"] == out[0]["vals"] and res["vals2"] == out[0]["vals2"]      # replicas agree bit for bit
 
 
