@@ -97,7 +97,7 @@ def main():
                         "columns_speedup_vs_sequential": t_seq / t_cs, "columns_pivots_identical": bool(same),
                         "columns_sharded_bonds": int(sh_tci.stats.get("nsharded", 0))}
     if os.environ.get("C3H512", "1") != "0":             # the same sweep at maxbonddim=512: Pi up to 10240 x 10240
-        kw5 = dict(kw, maxbonddim=512, maxiter=1)
+        kw5 = dict(kw, maxbonddim=512, maxiter=2)
         t1 = timed(lambda: T.crossinterpolate2(f, ld, **kw5), reps=1)
         t8 = timed(lambda: T.crossinterpolate2(f, ld, **kw5, comm=comm), reps=1)
         out["c3h512_sweep"] = {"sequential_replicated_s": t1, "sequential_columns_over_ranks_s": t8, "speedup": t1 / t8}

@@ -69,7 +69,7 @@ def main():
         res[f"{mode}_GBps_aggregate"] = res["algorithmic_update_GB"] / float(t.item())
     res["npivot"] = int(out["npivot"])
     res["exchange"] = {"nccl": "NCCL all_gather_into_tensor issued from the host between the step kernels",
-                       "fused": "record stored into every rank's peer-mapped mailbox by the update kernel; no host round trip"}
+                       "fused": "two rounds over peer-mapped mailboxes inside the step kernels (32-byte candidate headers from the update kernel, then the winner's column from the owner's swap kernel); two launches per step, no host round trip"}
     if rank == 0:
         full = T.Mat(A.T.contiguous(), N, N)
         torch.cuda.synchronize(); t0 = time.perf_counter()

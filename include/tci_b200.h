@@ -120,12 +120,19 @@ int64_t tci_rrlu_dist_record_doubles(tci_rrlu_dist d);
 int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, double* d_record);
 int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record);
 int tci_rrlu_dist_status(tci_handle h, tci_rrlu_dist d, int64_t* h_npivot, int* h_stop);
-/* Fused exchange: instead of the caller's all-gather, the update kernel's last block stores this rank's record straight into
- * every rank's MAILBOX (peer-mapped device memory: allocate tci_rrlu_dist_mailbox_bytes with tci_malloc, share it with
- * tci_ipc_export/open) and the next step's kernel waits for the G sequence flags (acquire/release at system scope, 4 s
- * timeout).  h_boxes[g] = rank g's mailbox as mapped in THIS process (h_boxes[rank] = own).  All ranks must have called
- * set_mailboxes (which zeroes the own mailbox) before any rank calls run; run enqueues the whole factorisation (search +
- * maxrank steps) without a host synchronisation. */
+/* Debug aid: with TCI_DIST_TRACE=1 in the environment at create time the step kernels record 8 device timestamps
+ * (%globaltimer, ns) per pivot step — 0 swap kernel running, 1 headers arrived, 2 pivot column stored / arrived, 3 update
+ * kernel running, 4 block 0 done, 5 all tiles done, 6 header released; h_stamps receives 8 * nsteps values. */
+int tci_rrlu_dist_trace(tci_handle h, tci_rrlu_dist d, uint64_t* h_stamps, int64_t nsteps);
+/* Fused exchange: instead of the caller's all-gather the step kernels talk through MAILBOXES (peer-mapped device memory:
+ * allocate tci_rrlu_dist_mailbox_bytes with tci_malloc, share it with tci_ipc_export/open), two rounds per pivot step:
+ * the update kernel's last block stores a 48-byte candidate header into every rank's mailbox, every block of the next
+ * (swap) kernel picks the winner from the G headers, and the winner's owner stores the pivot column into the peers'
+ * mailboxes from that same kernel.  Packets are self-validating (16 bytes = 2 x {32 data bits | 32-bit step number}), so
+ * there are no flags and no fences; a receiver gives up after 4 s.  Two launches per step.  h_boxes[g] = rank g's mailbox
+ * as mapped in THIS process (h_boxes[rank] = own).  All ranks must have called set_mailboxes (which zeroes the own
+ * mailbox) before any rank calls run; run enqueues the whole factorisation (search + maxrank steps) without a host
+ * synchronisation. */
 int64_t tci_rrlu_dist_mailbox_bytes(tci_rrlu_dist d);
 int tci_rrlu_dist_set_mailboxes(tci_handle h, tci_rrlu_dist d, void* const* h_boxes);
 int tci_rrlu_dist_run(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda);

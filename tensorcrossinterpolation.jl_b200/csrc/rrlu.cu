@@ -667,8 +667,9 @@ struct DistState {
     int npivot, stop, pr, owner, pcl, posw;   // pending pivot: row, owning rank, local column there, its position
     int kl, kl_next;                          // local columns already pivoted (the local trailing block starts here)
     int flags;
-    unsigned int ticket;
+    unsigned int ticket, ticket2;             // last-block detection of the update kernel / of the owner's swap kernel
     double pivval, maxerror, error;
+    double maxerr2[2];                        // mailbox mode: running maximum by step parity (every block reads [k & 1], block 0 writes the other)
 };
 struct Cand4 { double x; int i, pos, jl; };
 
@@ -700,23 +701,54 @@ __device__ __forceinline__ Cand4 block_reduce4(Cand4 c, Cand4* smem) {
     return c;   // valid in thread 0
 }
 
-// Mailbox exchange over peer-mapped memory (CUDA IPC / NVLink): rank g's mailbox holds, for each parity of the step counter,
-// one record slot per rank and one sequence flag per rank.  The last block of a rank's update kernel stores its record into
-// the slot [parity][rank] of EVERY rank's mailbox and then releases the flag; the select kernel of the next step acquires
-// the G flags of its own mailbox.  A rank can be at most one step ahead of a peer, so two parities suffice.
+// Mailbox exchange over peer-mapped memory (CUDA IPC / NVLink), two rounds per pivot step, with a self-validating packet
+// format instead of flags: every 16-byte packet is two 8-byte words {32 data bits | 32-bit sequence number k + 1}, so a
+// double travels as one packet and a receiver that sees the expected sequence number in both words has the data — no
+// release/acquire fences, no flag round trip, nothing to order (8-byte stores are single transactions on NVLink, and each
+// word validates itself).  Rank g's mailbox holds, for each parity of the step counter, one 3-packet candidate HEADER per
+// rank (value | row, position | local column) and one pivot COLUMN of m packets.  Round 1: the last block of a rank's
+// update kernel stores its header into slot [parity][rank] of EVERY rank's mailbox; every block of the next swap kernel
+// polls the G headers of its own mailbox and picks the winner.  Round 2: the winner's owner stores the pivot column into
+// every peer's mailbox from the (grid-wide) swap kernel — the threads that swap that column locally hold its entries
+// anyway; the peers' builder threads poll their own entry.  Only one column per step crosses NVLink, written by a whole
+// grid.  A rank can be at most one step ahead of a peer, so two parities suffice; the mailbox starts zeroed (sequence 0
+// never matches).
+//   layout (16-byte packets): hdr[2][n][3] | col[2][mpad];  mpad = reclen - 4
 constexpr int kMaxPeers = 8;
 struct PeerBox { double* box[kMaxPeers]; int n; };       // n == 0: records go to `record` and are gathered by the caller
+struct alignas(16) Packet { unsigned long long w0, w1; };
 
-__device__ __forceinline__ unsigned int* box_flags(double* box, long long reclen, int n) {
-    return reinterpret_cast<unsigned int*>(box + 2LL * n * reclen);
+__device__ __forceinline__ Packet* box_hdr(double* box, int n, int parity, int g) {
+    return reinterpret_cast<Packet*>(box) + ((long long)parity * n + g) * 3;
 }
-__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ Packet* box_col(double* box, long long reclen, int n, int parity) {
+    return reinterpret_cast<Packet*>(box) + 6LL * n + (long long)parity * (reclen - 4);
 }
-__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void packet_store(Packet* dst, unsigned int lo, unsigned int hi, unsigned int seq) {
+    const unsigned long long w0 = (unsigned long long)lo | ((unsigned long long)seq << 32);
+    const unsigned long long w1 = (unsigned long long)hi | ((unsigned long long)seq << 32);
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(w0), "l"(w1) : "memory");
+}
+__device__ __forceinline__ void packet_store_f64(Packet* dst, double v, unsigned int seq) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    packet_store(dst, (unsigned int)(b & 0xffffffffULL), (unsigned int)(b >> 32), seq);
+}
+__device__ __forceinline__ bool packet_try_load(const Packet* src, unsigned int seq, unsigned int& lo, unsigned int& hi) {
+    unsigned long long w0, w1;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(src) : "memory");
+    lo = (unsigned int)(w0 & 0xffffffffULL); hi = (unsigned int)(w1 & 0xffffffffULL);
+    return (unsigned int)(w0 >> 32) == seq && (unsigned int)(w1 >> 32) == seq;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns();
+// spin until the packet carries `seq` (false after 4 s: the sender died)
+__device__ __forceinline__ bool packet_wait(const Packet* src, unsigned int seq, unsigned int& lo, unsigned int& hi) {
+    if (packet_try_load(src, seq, lo, hi)) return true;
+    const unsigned long long t0 = globaltimer_ns();
+    for (;;) {
+        if (packet_try_load(src, seq, lo, hi)) return true;
+        if (globaltimer_ns() - t0 > 4000000000ULL) return false;
+        __nanosleep(50);
+    }
 }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
@@ -728,7 +760,9 @@ struct DistArrays {
     DistState* st; int* rowperm; int* pos2col; int* col2pos; int* gid;
     double* ybuf; double* xcol; double* pivvals; double* Lbuf; Cand4* parts;
     long long ldl;
+    unsigned long long* trace;               // TCI_DIST_TRACE=1: 8 %globaltimer stamps per step (tci_rrlu_dist_trace), else NULL
 };
+#define TCI_TRACE(a, step, slot) do { if ((a).trace) (a).trace[(long long)(step) * 8 + (slot)] = globaltimer_ns(); } while (0)
 
 __global__ void rrlu_dist_init_kernel(DistArrays a, int m, int n, int nloc, int col0) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -738,30 +772,19 @@ __global__ void rrlu_dist_init_kernel(DistArrays a, int m, int n, int nloc, int 
     if (t == 0) {
         DistState* st = a.st;
         st->npivot = 0; st->stop = 0; st->pr = 0; st->owner = 0; st->pcl = 0; st->posw = 0; st->kl = 0; st->kl_next = 0;
-        st->flags = 0; st->ticket = 0u; st->pivval = 0.0; st->maxerror = 0.0; st->error = nan("");
+        st->flags = 0; st->ticket = 0u; st->ticket2 = 0u; st->pivval = 0.0; st->maxerror = 0.0; st->error = nan("");
+        st->maxerr2[0] = 0.0; st->maxerr2[1] = 0.0;
     }
 }
 
 // Step part 1 (one block): global pivot choice + stop rule (matrixlu.jl:359-367), pivot column broadcast -> xcol / Lbuf.
 __global__ void __launch_bounds__(kThreads)
 rrlu_dist_select_kernel(DistArrays a, const double* __restrict__ gathered, long long reclen, int nranks, int m,
-                        int maxrank, double reltol, double abstol, int leftorth, double* mybox) {
+                        int maxrank, double reltol, double abstol, int leftorth) {
     __shared__ int s_commit;
     cudaGridDependencySynchronize();
     DistState* st = a.st;
     const int k = st->npivot;                               // written only by the update kernel
-    if (mybox) {                                            // mailbox mode: wait for the G records with sequence number k + 1
-        if (!st->stop && k < maxrank && (int)threadIdx.x < nranks) {
-            const unsigned int* f = box_flags(mybox, reclen, nranks) + (k & 1) * nranks + threadIdx.x;
-            const unsigned long long t0 = globaltimer_ns();
-            while (ld_acquire_sys(f) < (unsigned int)(k + 1)) {
-                if (globaltimer_ns() - t0 > 4000000000ULL) { atomicOr(&st->flags, 4); break; }   // a peer died: give up after 4 s
-                __nanosleep(200);
-            }
-        }
-        __syncthreads();
-        gathered = mybox + (long long)(k & 1) * nranks * reclen;
-    }
     __shared__ double s_hdr[kMaxPeers * 2][4];              // the G record headers, fetched in parallel
     if ((int)threadIdx.x < 4 * nranks && nranks <= kMaxPeers * 2)
         s_hdr[threadIdx.x >> 2][threadIdx.x & 3] = __ldcg(gathered + (long long)(threadIdx.x >> 2) * reclen + (threadIdx.x & 3));
@@ -810,44 +833,117 @@ rrlu_dist_select_kernel(DistArrays a, const double* __restrict__ gathered, long 
 }
 
 // Step part 2: the row swap in the local columns and in the L columns gathered so far; on the owner also the local column
-// swap that brings the pivot column to the front of the trailing block; packed copy of the local piece of the pivot row.
+// swap that brings the pivot column to the front of the trailing block; packed copy of the local piece of the pivot row;
+// the pivot column with the row swap applied -> xcol and column k of L.  Mailbox mode (peers.n > 0): round 2 of the
+// exchange — the owner's column-swap threads also store the column into the peers' mailboxes and build xcol / L locally,
+// the peers wait for the column flag (one lane per warp) before they build theirs.
 __global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, long long lda, int rank, int leftorth,
-                                      const double* __restrict__ gathered, long long reclen, int nranks) {
+                                      const double* __restrict__ gathered, long long reclen, int nranks, PeerBox peers,
+                                      int maxrank, double reltol, double abstol) {
     cudaGridDependencySynchronize();
     DistState* st = a.st;
     if (st->stop) return;
-    const int k = st->npivot, pr = st->pr, kl = st->kl, pcl = st->pcl;
-    const bool mine = st->owner == rank;
-    const double piv = st->pivval;
-    const int klnext = kl + (mine ? 1 : 0);
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < nloc) {
-        const int j = t;
-        if (mine && (j == kl || j == pcl)) return;                  // the corner item handles these two columns
-        double* pk = A + (long long)j * lda + k;
-        double* pp = A + (long long)j * lda + pr;
-        const double old_k = *pk;
-        double newk = (pr != k) ? *pp : old_k;
-        if (j >= klnext) {                                          // trailing column: its row-k entry is part of the pivot row
-            if (!leftorth) newk = newk / piv;                       // :306-308
-            a.ybuf[j] = newk;
+    const bool mail = peers.n > 0;
+    const int k = st->npivot, kl = st->kl;
+    int pr, pcl, owner;
+    double piv;
+    if (blockIdx.x == 0 && threadIdx.x == 0) TCI_TRACE(a, k, 0);   // swap kernel running
+    if (mail) {
+        // round 1, receiving side, fused with the pivot choice: EVERY block waits for the G headers of its own mailbox and
+        // takes the decision of the select kernel redundantly (pivot, stop rule :359-367); block 0 alone writes the shared
+        // state.  The running maximum is double-buffered by step parity so that no block reads what block 0 writes.
+        __shared__ unsigned int s_hw[kMaxPeers][3][2];
+        const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+        if (k >= maxrank) { if (lead) st->stop = 1; return; }       // while lu.npivot < maxrank (:356)
+        double* mybox = peers.box[rank];
+        int to = 0;
+        if ((int)threadIdx.x < 3 * nranks) {                        // one thread per header packet
+            const int g = threadIdx.x / 3, part = threadIdx.x % 3;
+            unsigned int lo, hi;
+            if (!packet_wait(box_hdr(mybox, nranks, k & 1, g) + part, (unsigned int)(k + 1), lo, hi)) to = 1;   // a peer died
+            s_hw[g][part][0] = lo; s_hw[g][part][1] = hi;
         }
-        *pk = newk;
-        if (pr != k) *pp = old_k;
-    } else if (t < nloc + m) {
-        if (!mine || pcl == kl) return;
+        to = __syncthreads_or(to);
+        if (to) { if (threadIdx.x == 0) { atomicOr(&st->flags, 4); st->stop = 1; } return; }
+        Cand4 best{0.0, -1, -1, -1};
+        owner = -1;
+        for (int g = 0; g < nranks; ++g) {
+            const double x = __longlong_as_double((long long)((unsigned long long)s_hw[g][0][0] | ((unsigned long long)s_hw[g][0][1] << 32)));
+            const Cand4 c{x, (int)s_hw[g][1][0], (int)s_hw[g][1][1], (int)s_hw[g][2][0]};
+            if (cand4_better(c, best)) { best = c; owner = g; }
+        }
+        if (best.i < 0) {                                           // every remaining entry is NaN: not supported in the sharded path
+            if (lead) { st->flags |= 8; st->stop = 1; st->error = nan(""); }
+            return;
+        }
+        const double err = fabs(best.x);                            // :360
+        const double maxerr = st->maxerr2[k & 1];
+        if ((err < reltol * maxerr || err < abstol) && k > 0) {     // :363
+            if (lead) { st->error = err; st->stop = 1; }
+            return;
+        }
+        pr = best.i; pcl = best.jl; piv = best.x;
+        if (lead) {
+            TCI_TRACE(a, k, 1);                                     // headers arrived, pivot chosen
+            st->error = err;
+            st->maxerr2[(k + 1) & 1] = jl_max(maxerr, err);         // :367
+            st->pr = pr; st->owner = owner; st->pcl = pcl; st->posw = best.pos; st->pivval = piv;
+            int t0 = a.rowperm[k]; a.rowperm[k] = a.rowperm[pr]; a.rowperm[pr] = t0;
+            const int P = best.pos, ck = a.pos2col[k], cw = a.pos2col[P];          // swapcol!(k, P) on the position maps
+            a.pos2col[k] = cw; a.pos2col[P] = ck; a.col2pos[cw] = k; a.col2pos[ck] = P;
+            a.pivvals[k] = piv;
+        }
+    } else {
+        pr = st->pr; pcl = st->pcl; owner = st->owner; piv = st->pivval;
+    }
+    const bool mine = owner == rank;
+    const int klnext = kl + (mine ? 1 : 0);
+    const int par = k & 1;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b_cols = nloc, b_L = nloc + m, b_corner = nloc + m + k, b_build = nloc + m + k + 1;   // first item of each kind
+    const bool builder = t >= b_build && t < b_build + m && !(mail && mine);
+    const double* col = mail ? nullptr : gathered + (long long)owner * reclen + 4;
+    if (t < b_cols) {
+        const int j = t;
+        if (!(mine && (j == kl || j == pcl))) {                     // the corner item handles these two columns
+            double* pk = A + (long long)j * lda + k;
+            double* pp = A + (long long)j * lda + pr;
+            const double old_k = *pk;
+            double newk = (pr != k) ? *pp : old_k;
+            if (j >= klnext) {                                      // trailing column: its row-k entry is part of the pivot row
+                if (!leftorth) newk = newk / piv;                   // :306-308
+                a.ybuf[j] = newk;
+            }
+            *pk = newk;
+            if (pr != k) *pp = old_k;
+        }
+    } else if (t < b_L) {
         const int i = t - nloc;
-        if (i == k || i == pr) return;
-        double* p0 = A + (long long)kl * lda + i;
-        double* p1 = A + (long long)pcl * lda + i;
-        const double v = *p0; *p0 = *p1; *p1 = v;
-    } else if (t < nloc + m + k) {
-        if (pr == k) return;
-        const int c = t - nloc - m;
-        double* p0 = a.Lbuf + (long long)c * a.ldl + k;
-        double* p1 = a.Lbuf + (long long)c * a.ldl + pr;
-        const double v = *p0; *p0 = *p1; *p1 = v;
-    } else if (t == nloc + m + k) {
+        if (mine && i != k && i != pr) {
+            if (mail) {
+                double* p1 = A + (long long)pcl * lda + i;
+                const double v1 = *p1;                              // entry i of the pivot column
+                if (pcl != kl) { double* p0 = A + (long long)kl * lda + i; const double v0 = *p0; *p0 = v1; *p1 = v0; }
+                for (int g = 0; g < peers.n; ++g)
+                    if (g != rank) packet_store_f64(box_col(peers.box[g], reclen, nranks, par) + i, v1, (unsigned int)(k + 1));
+                double v = v1;
+                if (leftorth && i > k) v = v / piv;                 // :303-305
+                a.xcol[i] = v;
+                if (i >= k) a.Lbuf[(long long)k * a.ldl + i] = v;
+            } else if (pcl != kl) {
+                double* p0 = A + (long long)kl * lda + i;
+                double* p1 = A + (long long)pcl * lda + i;
+                const double v = *p0; *p0 = *p1; *p1 = v;
+            }
+        }
+    } else if (t < b_corner) {
+        if (pr != k) {
+            const int c = t - b_L;
+            double* p0 = a.Lbuf + (long long)c * a.ldl + k;
+            double* p1 = a.Lbuf + (long long)c * a.ldl + pr;
+            const double v = *p0; *p0 = *p1; *p1 = v;
+        }
+    } else if (t == b_corner) {
         if (mine) {
             const double o_kk = A[(long long)kl * lda + k], o_kp = A[(long long)pcl * lda + k];
             const double o_rk = A[(long long)kl * lda + pr], o_rp = A[(long long)pcl * lda + pr];
@@ -860,18 +956,43 @@ __global__ void rrlu_dist_swap_kernel(DistArrays a, double* __restrict__ A, int 
             A[(long long)kl * lda + k] = n_kk;
             if (pcl != kl) a.ybuf[pcl] = n_kp;
             const int g0 = a.gid[kl]; a.gid[kl] = a.gid[pcl]; a.gid[pcl] = g0;
+            if (mail) {                                             // rows k and pr of the pivot column (before the swaps)
+                for (int g = 0; g < peers.n; ++g)
+                    if (g != rank) {
+                        Packet* c = box_col(peers.box[g], reclen, nranks, par);
+                        packet_store_f64(c + k, o_kp, (unsigned int)(k + 1));
+                        packet_store_f64(c + pr, o_rp, (unsigned int)(k + 1));
+                    }
+                a.xcol[k] = o_rp;                                   // the pivot itself lands in row k
+                a.Lbuf[(long long)k * a.ldl + k] = o_rp;
+                if (pr != k) {
+                    const double v = leftorth ? o_kp / piv : o_kp;
+                    a.xcol[pr] = v;
+                    a.Lbuf[(long long)k * a.ldl + pr] = v;
+                }
+            }
         }
         st->kl_next = klnext;
-    } else if (t <= nloc + m + k + m) {
-        // the broadcast pivot column (part of the winner's record) with the row swap applied -> xcol and column k of L
-        const int i = t - (nloc + m + k + 1);
-        const double* col = gathered + (long long)st->owner * reclen + 4;
+    } else if (builder) {
+        // the broadcast pivot column with the row swap applied -> xcol and column k of L
+        const int i = t - b_build;
         const int src = (i == k) ? pr : (i == pr ? k : i);
-        double v = __ldcg(col + src);                               // written by a peer: around L1
+        double v;
+        if (mail) {                                                 // round 2, receiving side: poll the own entry
+            unsigned int lo, hi;
+            if (!packet_wait(box_col(peers.box[rank], reclen, nranks, par) + src, (unsigned int)(k + 1), lo, hi)) {
+                atomicOr(&st->flags, 4); st->stop = 1;              // the owner died
+            }
+            v = __longlong_as_double((long long)((unsigned long long)lo | ((unsigned long long)hi << 32)));
+            if (i == 0) TCI_TRACE(a, k, 2);                         // peer: pivot column arriving
+        } else {
+            v = __ldcg(col + src);                                  // written by a peer: around L1
+        }
         if (leftorth && i > k) v = v / piv;                         // :303-305
         a.xcol[i] = v;
         if (i >= k) a.Lbuf[(long long)k * a.ldl + i] = v;
     }
+    if (mail && mine && t == b_corner) TCI_TRACE(a, k, 2);         // owner: corner entries stored
 }
 
 // Step part 3: local rank-1 update + search; the last block writes this rank's record for the next step.
@@ -890,8 +1011,10 @@ rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, l
     double bv = -INFINITY, bx = 0.0;
     int bi = -1, bj = -1;
     const ColOrder ord{a.gid, a.col2pos};
+    if (UPDATE && blockIdx.x == 0 && threadIdx.x == 0) TCI_TRACE(a, k, 3);        // update kernel running
     if (np < maxrank && c0 < nloc)
         scan_tiles<UPDATE, VEC, COLS, false, true>(A, m, nloc, lda, a.ybuf, a.xcol, np, c0, np, serpentine, ord, bv, bx, bi, bj);
+    if (UPDATE && blockIdx.x == 0 && threadIdx.x == 0) TCI_TRACE(a, k, 4);        // block 0 done with its tiles
     Cand4 c{bx, bi, bj >= 0 ? a.col2pos[a.gid[bj]] : -1, bj};
     c = block_reduce4(c, s_c);
     if (threadIdx.x == 0) {
@@ -903,6 +1026,7 @@ rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, l
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    if (UPDATE && threadIdx.x == 0) TCI_TRACE(a, k, 5);             // last block: every tile done
     Cand4 best{0.0, -1, -1, -1};
     for (int b = threadIdx.x; b < (int)gridDim.x; b += kThreads) {
         Cand4 o = a.parts[b];
@@ -931,35 +1055,24 @@ rrlu_dist_update_kernel(DistArrays a, double* __restrict__ A, int m, int nloc, l
         }
         return;
     }
-    // compute + all-gather in one kernel: the record goes straight into every rank's mailbox (peer stores over NVLink)
-    const long long slot = ((long long)(np & 1) * peers.n + rank) * reclen;
+    // round 1 of the mailbox exchange: the 4-double header goes straight into every rank's mailbox (peer stores over
+    // NVLink), each followed by its own release flag; the pivot column follows in round 2 from the owner's swap kernel
+    __shared__ Cand4 s_best;
     if (threadIdx.x == 0) {
-        for (int g = 0; g < peers.n; ++g) {
-            double* r = peers.box[g] + slot;
-            r[0] = best.x; r[1] = (double)best.i; r[2] = (double)best.pos; r[3] = (double)best.jl;
-        }
-        s_jl = best.i >= 0 ? best.jl : -1;
+        s_best = best;
         st->npivot = np; st->kl = c0; st->ticket = 0u;
     }
     __syncthreads();
-    const int jl = s_jl;
-    if (jl >= 0) {
-        const double* src = A + (long long)jl * lda;
-        for (int i0 = threadIdx.x; i0 < m; i0 += 8 * kThreads) {     // 8 independent loads in flight per thread
-            double v[8];
-#pragma unroll
-            for (int u = 0; u < 8; ++u) { const int i = i0 + u * kThreads; v[u] = i < m ? __ldcg(src + i) : 0.0; }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int i = i0 + u * kThreads;
-                if (i < m) for (int g = 0; g < peers.n; ++g) peers.box[g][slot + 4 + i] = v[u];
-            }
-        }
+    if ((int)threadIdx.x < 3 * peers.n && np < maxrank) {           // one thread per (peer, packet); nobody reads a header after the last step
+        const Cand4 bb = s_best;
+        const int g = threadIdx.x / 3, part = threadIdx.x % 3;
+        Packet* r = box_hdr(peers.box[g], peers.n, np & 1, rank) + part;
+        const unsigned long long xb = (unsigned long long)__double_as_longlong(bb.x);
+        const unsigned int lo = part == 0 ? (unsigned int)(xb & 0xffffffffULL) : (part == 1 ? (unsigned int)bb.i : (unsigned int)bb.jl);
+        const unsigned int hi = part == 0 ? (unsigned int)(xb >> 32) : (part == 1 ? (unsigned int)bb.pos : 0u);
+        packet_store(r, lo, hi, (unsigned int)(np + 1));
+        if (UPDATE && threadIdx.x == 0) TCI_TRACE(a, k, 6);         // header stored
     }
-    __threadfence_system();
-    __syncthreads();
-    if ((int)threadIdx.x < peers.n)
-        st_release_sys(box_flags(peers.box[threadIdx.x], reclen, peers.n) + (np & 1) * peers.n + rank, (unsigned int)(np + 1));
 }
 
 // L (m x r): tril of the gathered columns with the reference's diagonal; U_loc (r x nloc): triu of the local columns in
@@ -1322,7 +1435,10 @@ int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64
     const size_t o_st = 0, o_rp = al(sizeof(DistState)), o_p2c = o_rp + al(sizeof(int) * m), o_c2p = o_p2c + al(sizeof(int) * n),
                  o_gid = o_c2p + al(sizeof(int) * n), o_y = o_gid + al(sizeof(int) * (nloc + 1)), o_x = o_y + al(sizeof(double) * (nloc + 1)),
                  o_pv = o_x + al(sizeof(double) * (m + 2)), o_parts = o_pv + al(sizeof(double) * d->maxrank),
-                 o_L = o_parts + al(sizeof(Cand4) * d->grid), total = o_L + al(sizeof(double) * (size_t)m * d->maxrank);
+                 o_L = o_parts + al(sizeof(Cand4) * d->grid), o_tr = o_L + al(sizeof(double) * (size_t)m * d->maxrank);
+    const char* tr_env = getenv("TCI_DIST_TRACE");
+    const bool tracing = tr_env && atoi(tr_env) > 0;
+    const size_t total = o_tr + (tracing ? al(sizeof(unsigned long long) * 8 * ((size_t)d->maxrank + 1)) : 0);
     // a sweep creates one of these per bond: take the block the previous one parked in the handle when it is large enough
     // (cudaMalloc / cudaFree cost milliseconds each once peer mappings exist)
     if (h->dist_parked.ptr && h->dist_parked.bytes >= total) {
@@ -1336,6 +1452,8 @@ int tci_rrlu_dist_create(tci_handle h, int64_t m, int64_t n, int64_t nloc, int64
     d->a.st = (DistState*)(b + o_st); d->a.rowperm = (int*)(b + o_rp); d->a.pos2col = (int*)(b + o_p2c); d->a.col2pos = (int*)(b + o_c2p);
     d->a.gid = (int*)(b + o_gid); d->a.ybuf = (double*)(b + o_y); d->a.xcol = (double*)(b + o_x); d->a.pivvals = (double*)(b + o_pv);
     d->a.parts = (Cand4*)(b + o_parts); d->a.Lbuf = (double*)(b + o_L); d->a.ldl = m;
+    d->a.trace = tracing ? (unsigned long long*)(b + o_tr) : nullptr;
+    if (tracing) cudaMemsetAsync(d->a.trace, 0, sizeof(unsigned long long) * 8 * ((size_t)d->maxrank + 1), h->stream);
     const int64_t mx = m > n ? m : n;
     rrlu_dist_init_kernel<<<(unsigned)((mx + 255) / 256), 256, 0, h->stream>>>(d->a, d->m, d->n, d->nloc, d->col0);
     TCI_LAUNCH_CHECK(h);
@@ -1357,11 +1475,12 @@ int tci_rrlu_dist_search(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda
 int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, const double* d_gathered, double* d_record) {
     if (!h || !d || !d_gathered || !d_record) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_step: bad arguments");
     TCI_CUDA(h, cudaSetDevice(h->device));
-    rrlu_dist_select_kernel<<<1, kThreads, 0, h->stream>>>(d->a, d_gathered, d->reclen, d->nranks, d->m, d->maxrank, d->reltol, d->abstol, d->leftorth, nullptr);
+    rrlu_dist_select_kernel<<<1, kThreads, 0, h->stream>>>(d->a, d_gathered, d->reclen, d->nranks, d->m, d->maxrank, d->reltol, d->abstol, d->leftorth);
     TCI_LAUNCH_CHECK(h);
     const long long items = (long long)d->nloc + 2LL * d->m + d->maxrank + 1;
+    PeerBox nobox = d->peers; nobox.n = 0;
     launch_pdl(h, rrlu_dist_swap_kernel, (unsigned)((items + 255) / 256), 256u, d->a, d_A, d->m, d->nloc, (long long)lda, d->rank, d->leftorth,
-               d_gathered, d->reclen, d->nranks);
+               d_gathered, d->reclen, d->nranks, nobox, d->maxrank, d->reltol, d->abstol);
     TCI_LAUNCH_CHECK(h);
     launch_dist_update<true>(h, d, d_A, lda, d_record);
     TCI_LAUNCH_CHECK(h);
@@ -1370,7 +1489,7 @@ int tci_rrlu_dist_step(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda, 
 
 int64_t tci_rrlu_dist_mailbox_bytes(tci_rrlu_dist d) {
     if (!d) return 0;
-    return (int64_t)(2LL * d->nranks * d->reclen * sizeof(double) + 2LL * d->nranks * sizeof(unsigned int) + 256);
+    return (int64_t)((6LL * d->nranks + 2LL * (d->reclen - 4)) * 16 + 256);    // 16-byte packets: hdr[2][n][3] | col[2][mpad]
 }
 
 int tci_rrlu_dist_set_mailboxes(tci_handle h, tci_rrlu_dist d, void* const* h_boxes) {
@@ -1396,12 +1515,8 @@ int tci_rrlu_dist_run(tci_handle h, tci_rrlu_dist d, double* d_A, int64_t lda) {
     TCI_LAUNCH_CHECK(h);
     const long long items = (long long)d->nloc + 2LL * d->m + d->maxrank + 1;
     for (int s = 0; s < d->maxrank; ++s) {
-        const double* gathered = d->peers.box[d->rank] + (long long)(s & 1) * d->nranks * d->reclen;   // npivot == s while the loop runs
-        launch_pdl(h, rrlu_dist_select_kernel, 1u, (unsigned)kThreads, d->a, (const double*)nullptr, d->reclen, d->nranks, d->m, d->maxrank,
-                   d->reltol, d->abstol, d->leftorth, d->peers.box[d->rank]);
-        TCI_LAUNCH_CHECK(h);
         launch_pdl(h, rrlu_dist_swap_kernel, (unsigned)((items + 255) / 256), 256u, d->a, d_A, d->m, d->nloc, (long long)lda, d->rank, d->leftorth,
-                   gathered, d->reclen, d->nranks);
+                   (const double*)nullptr, d->reclen, d->nranks, d->peers, d->maxrank, d->reltol, d->abstol);
         TCI_LAUNCH_CHECK(h);
         launch_dist_update<true>(h, d, d_A, lda, nullptr);
         TCI_LAUNCH_CHECK(h);
@@ -1418,6 +1533,16 @@ int tci_rrlu_dist_status(tci_handle h, tci_rrlu_dist d, int64_t* h_npivot, int* 
     if (h_npivot) *h_npivot = st->npivot;
     if (h_stop) *h_stop = st->stop || st->npivot >= d->maxrank;
     if (st->flags & 8) return tci_fail(h, TCI_ERR_NAN_L, "sharded rrlu: every remaining entry is NaN");
+    return TCI_OK;
+}
+
+int tci_rrlu_dist_trace(tci_handle h, tci_rrlu_dist d, uint64_t* h_stamps, int64_t nsteps) {
+    if (!h || !d || !h_stamps) return TCI_ERR_INVALID;
+    if (!d->a.trace) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_dist_trace: create the factorisation with TCI_DIST_TRACE=1");
+    if (nsteps > d->maxrank) nsteps = d->maxrank;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    TCI_CUDA(h, cudaMemcpy(h_stamps, d->a.trace, sizeof(uint64_t) * 8 * (size_t)nsteps, cudaMemcpyDeviceToHost));
     return TCI_OK;
 }
 

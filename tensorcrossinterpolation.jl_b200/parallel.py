@@ -380,6 +380,14 @@ class ShardedRRLU:
         from ._lib import lib
         self.h.check(lib().tci_rrlu_dist_run(self.h.h, self._d, self._aptr(), C.c_int64(self.A.ld)))
 
+    def trace(self, nsteps):
+        """Device timestamps of the step kernels (TCI_DIST_TRACE=1 at creation): (nsteps, 8) uint64 ns, see tci_b200.h."""
+        import ctypes as C
+        from ._lib import lib
+        out = np.zeros((int(nsteps), 8), dtype=np.uint64)
+        self.h.check(lib().tci_rrlu_dist_trace(self.h.h, self._d, out.ctypes.data_as(C.c_void_p), C.c_int64(int(nsteps))))
+        return out
+
     def status(self):
         import ctypes as C
         from ._lib import lib
@@ -423,10 +431,11 @@ class ShardedRRLU:
 def rrlu_sharded(A_local, n, col0, comm=None, maxrank=None, reltol=1e-14, abstol=0.0, leftorthogonal=True, handle=None,
                  check_every=32, fused=False, peers=None):
     """rrlu!(A; ...) (matrixlu.jl:420-430) with the columns of A spread over the ranks of `comm` (NCCL).  Per pivot step the
-    ranks exchange one candidate record each (8 x (m + 4) bytes): fused=False -> an NCCL all-gather issued from the host
-    between the step kernels; fused=True -> the update kernel stores its record straight into every rank's peer-mapped
-    mailbox (`peers`: a PeerBuffers with >= mailbox_doubles() elements per slot, created once and reused) and the whole
-    factorisation is enqueued without any host round trip.  Returns this rank's `ShardedRRLU.finish()` dict; rowperm /
+    ranks exchange their best candidates: fused=False -> one record per rank (header + the candidate's column,
+    8 x (m + 4) bytes) through an NCCL all-gather issued from the host between the step kernels; fused=True -> two rounds
+    over peer-mapped mailboxes inside the step kernels (32-byte headers stored by the update kernel, then only the
+    winner's column, stored by the owner's swap kernel; `peers`: a PeerBuffers with >= mailbox_doubles() elements per
+    slot or a MailboxPool, created once and reused) and the whole factorisation is enqueued without any host round trip.  Returns this rank's `ShardedRRLU.finish()` dict; rowperm /
     colperm / npivot / pivoterrors / L are the same on every rank and bit-identical to the single-GPU rrlu."""
     import torch
     size = 1 if comm is None else comm.size
