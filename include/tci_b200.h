@@ -260,6 +260,58 @@ int tci_tt_sum_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t
 int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds,
                         int nsites, const int32_t* h_indices, int64_t npoints, double* h_out);
 
+/* ---- Compiled host driver of the TensorCI2 sweeps (csrc/tci2_driver.cpp) -------------------------------------------------
+ * The reference keeps sweep strategy, index-set bookkeeping and convergence control in its host language and so does this
+ * library's boundary: a Julia host calls the entry points above once per bond.  For hosts whose per-call overhead is large
+ * next to a microsecond-sized kernel (Python), the same host logic is available compiled: a tci_tci2 object is the
+ * `TensorCI2{Float64}` state (src/tensorci2.jl:50-93) — Iset/Jset as int32 tables on the host, site tensors in device memory —
+ * and the calls below are the reference's functions of the same names, written purely on top of the entry points above
+ * (every number still comes from those kernels; pivotsearch = :full only).  Sites and bonds are 1-based, index values
+ * 1-based; maxbonddim <= 0 means unbounded (typemax(Int)).  sweepstrategy: 0 :forward, 1 :backandforth, 2 :backward
+ * (src/sweepstrategies.jl:41-50).  The message of the last failure on an object is tci_tci2_last_error(t). */
+typedef struct tci_tci2_s* tci_tci2;
+int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tci2* out);       /* TensorCI2{V}(localdims) :95-103 */
+int tci_tci2_destroy(tci_tci2 t);
+const char* tci_tci2_last_error(tci_tci2 t);
+/* Seed of the global pivot finder's random starts (the reference draws from Julia's default RNG, which has no portable
+ * restatement: global pivots are not comparable with a Julia run). */
+int tci_tci2_seed(tci_tci2 t, uint64_t seed);
+/* addglobalpivots!(tci, pivots) :335-357 — h_pivots: npivots x nsites. */
+int tci_tci2_addglobalpivots(tci_tci2 t, const int32_t* h_pivots, int64_t npivots);
+/* The constructor's maxsamplevalue = maximum(abs(f(p)) for p in pivots) and its zero check :105-116. */
+int tci_tci2_init_maxsample(tci_tci2 t, tci_functor f, const int32_t* h_pivots, int64_t npivots);
+/* State in / out: which = 0 Iset[site] (rows of length site-1), 1 Jset[site] (rows of length nsites-site).
+ * tci_tci2_indexset: h_rows may be NULL to query the count only. */
+int tci_tci2_set_indexset(tci_tci2 t, int which, int site, const int32_t* h_rows, int64_t count);
+int tci_tci2_indexset(tci_tci2 t, int which, int site, int32_t* h_rows, int64_t* h_count);
+int tci_tci2_set_maxsamplevalue(tci_tci2 t, double v);
+/* updatepivots!(tci, b, f, leftorthogonal; reltol, abstol, maxbonddim, extraIset, extraJset) :825-930 (:full branch).
+ * h_extraI: nextraI rows of length bond, h_extraJ: nextraJ rows of length nsites-bond; either may be NULL/0. */
+int tci_tci2_updatepivots(tci_tci2 t, tci_functor f, int bond, int leftorthogonal, double reltol, double abstol, int64_t maxbonddim,
+                          const int32_t* h_extraI, int64_t nextraI, const int32_t* h_extraJ, int64_t nextraJ);
+/* sweep2site!(tci, f, niter; iter1, abstol, maxbonddim, sweepstrategy, strictlynested, fillsitetensors) :1195-1258 */
+int tci_tci2_sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, int64_t maxbonddim, int sweepstrategy,
+                        int strictlynested, int fillsitetensors);
+/* sweep1site!(tci, f, sweepdirection; reltol, abstol, maxbonddim, updatetensors) :659-725; forward != 0 is :forward */
+int tci_tci2_sweep1site(tci_tci2 t, tci_functor f, int forward, double reltol, double abstol, int64_t maxbonddim, int updatetensors);
+int tci_tci2_makecanonical(tci_tci2 t, tci_functor f, double reltol, double abstol, int64_t maxbonddim);      /* :738-749 */
+int tci_tci2_fillsitetensors(tci_tci2 t, tci_functor f);                      /* src/globalsearch.jl:202-208, setsitetensor! :599-629 */
+/* optimize!(tci, f; tolerance, maxbonddim, maxiter, sweepstrategy, normalizeerror, ncheckhistory, nsearchglobalpivot,
+ * maxnglobalpivot, tolmarginglobalsearch, strictlynested, checkconvglobalpivot) :1018-1172 with the DefaultGlobalPivotFinder
+ * (src/globalpivotfinder.jl:205-264; all candidates of an iteration in one batch evaluation).  h_ranks / h_errors receive
+ * *h_niter <= maxiter entries (errors already divided by the normalisation, as the reference returns them). */
+int tci_tci2_optimize(tci_tci2 t, tci_functor f, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,
+                      int ncheckhistory, int nsearchglobalpivot, int maxnglobalpivot, double tolmarginglobalsearch, int strictlynested,
+                      int checkconvglobalpivot, int64_t* h_ranks, double* h_errors, int* h_niter);
+/* Site tensor `site` as a dense column-major (chi_l, d, chi_r) array in device memory; the pointer stays valid until the next
+ * call that changes the object.  Fails when the site tensors are invalidated (:206-220). */
+int tci_tci2_core(tci_tci2 t, int site, const double** d_core, int64_t* h_shape3);
+int tci_tci2_sitetensors_available(tci_tci2 t);
+/* bonderrors (nsites-1), pivoterrors (query the count with h_pivoterrors = NULL first), maxsamplevalue; any may be NULL. */
+int tci_tci2_errors(tci_tci2 t, double* h_bonderrors, double* h_pivoterrors, int64_t* h_npivoterrors, double* h_maxsamplevalue);
+/* h_counts2 = {function evaluations, bond updates}; h_seconds4 = host wall time in {evaluation, rrLU, factors, index sets}. */
+int tci_tci2_stats(tci_tci2 t, int64_t* h_counts2, double* h_seconds4);
+
 #ifdef __cplusplus
 }
 #endif

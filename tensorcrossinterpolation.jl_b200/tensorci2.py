@@ -702,9 +702,69 @@ def _sanitycheck(tci):                                      # globalsearch.jl:22
     return True
 
 
+_NATIVE_KW = {"tolerance", "maxbonddim", "maxiter", "sweepstrategy", "normalizeerror", "ncheckhistory", "nsearchglobalpivot",
+              "maxnglobalpivot", "tolmarginglobalsearch", "strictlynested", "checkconvglobalpivot", "pivotsearch", "verbosity",
+              "loginterval", "checkbatchevaluatable"}
+
+
+def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs):
+    """crossinterpolate2 with the whole optimize! loop run by the compiled sweep driver (csrc/tci2_driver.cpp, native.py): one
+    C call instead of an interpreted host loop over bonds.  Same kernels, same order of operations; the result is handed
+    back as an ordinary TensorCI2 (index sets on the host, site tensors in torch-owned device memory)."""
+    import torch
+    from .native import NativeTCI2
+    from .parallel import _RawCuda
+    unknown = set(kwargs) - _NATIVE_KW
+    if unknown:
+        raise TCIError(_lib.TCI_ERR_INVALID, f"engine='native' does not take {sorted(unknown)} (use engine='python')")
+    if kwargs.pop("pivotsearch", "full") != "full":
+        raise TCIError(_lib.TCI_ERR_INVALID, "engine='native' implements pivotsearch=:full only (use engine='python' for :rook)")
+    if not isinstance(f, BatchEvaluator) or not getattr(f, "_f", None):
+        raise TCIError(_lib.TCI_ERR_INVALID, "engine='native' needs a device functor (a BatchEvaluator built on tci_functor_*); "
+                       "host callables run with engine='python'")
+    for k in ("verbosity", "loginterval", "checkbatchevaluatable"):
+        kwargs.pop(k, None)
+    h = handle or f.handle
+    h.use_torch_stream()
+    localdims = [int(d) for d in localdims]
+    n = len(localdims)
+    if initialpivots is None:
+        initialpivots = [[1] * n]
+    nat = NativeTCI2(_lib.lib(), h.h, localdims)
+    if seed is not None:
+        nat.seed(seed)
+    nat.addglobalpivots(initialpivots)
+    nat.init_maxsample(f._f, initialpivots)
+    if kwargs.get("tolerance") is None:
+        kwargs["tolerance"] = 1e-8
+    ranks, errors = nat.optimize(f._f, **kwargs)
+    tci = TensorCI2(localdims, handle=h)
+    tci.Iset = [nat.Iset(b + 1) for b in range(n)]
+    tci.Jset = [nat.Jset(b + 1) for b in range(n)]
+    tci.bonderrors, tci.pivoterrors, tci.maxsamplevalue = nat.errors()
+    dev = f"cuda:{h.device}"
+    for b in range(n):
+        ptr, (chil, d, chir) = nat.core(b + 1)
+        size = chil * d * chir
+        flat = torch.as_tensor(_RawCuda(ptr, size), device=dev).clone()        # own the memory: the driver's buffers die with `nat`
+        tci._T[b] = DeviceCore(Mat(flat.view(chir, chil * d), chil * d, chir), chil, (d,), chir)
+    st = nat.stats()
+    tci.stats.update({k: st[k] for k in ("nevals", "t_eval", "t_lu", "t_factors", "t_host")})
+    tci.stats["nbondupdates"] = st["nbondupdates"]
+    nat.close()
+    return tci, ranks, errors
+
+
 def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
-    """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323."""
+    """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323.
+    `engine` (not in the reference): "python" (default) runs optimize! in this module, "native" hands the same loop to the
+    compiled sweep driver — fewer microseconds of host work per bond, identical kernels and results."""
     seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): rook-search stream
+    engine = kwargs.pop("engine", "python")
+    if engine == "native":
+        return _crossinterpolate2_native(f, localdims, initialpivots, seed, kwargs.pop("handle", None), kwargs)
+    if engine != "python":
+        raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown engine {engine}: choose 'python' or 'native'.")
     tci = TensorCI2(localdims, f, initialpivots, handle=kwargs.pop("handle", None))
     if seed is not None:
         from .matrixlu import Rng

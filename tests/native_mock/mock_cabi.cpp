@@ -1,0 +1,131 @@
+// mock_cabi.cpp — TEST INFRASTRUCTURE ONLY.  A host-memory stand-in for the handful of C-ABI entry points that
+// csrc/tci2_driver.cpp calls, backed by the CPU oracle (oracle/_build/libtci_oracle.so).  Linking the UNCHANGED driver
+// source against this file lets the driver's bookkeeping (index sets, sweep order, histories, error merging, convergence)
+// be checked bit for bit against the oracle's own TensorCI2 on a machine without a GPU (tests/test_native_driver_mock.py).
+// "Device" pointers are plain host pointers here; a tci_functor is an oracle Func*.  Nothing in the product links this.
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/tci_b200.h"
+
+extern "C" {
+const char* orc_last_error();
+int orc_rrlu(const double* A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol, double abstol, int leftorthogonal,
+             int64_t* rowperm, int64_t* colperm, int64_t* npivot, double* error, double* L, int64_t ldl, double* U, int64_t ldu,
+             double* pivoterrors);
+int orc_luci_factors(int64_t m, int64_t n, int64_t r, int leftorthogonal, const int64_t* rowperm, const int64_t* colperm,
+                     const double* L, int64_t ldl, const double* U, int64_t ldu, double* left, double* right);
+int orc_solve_right(const double* P, int64_t r, const double* B, int64_t q, double* X);
+int orc_batcheval(void* f, const int32_t* localdims, int nsites, const int32_t* left, int64_t nleft, int nl, const int32_t* right,
+                  int64_t nright, int nr, int M, double* out);
+int orc_tt_evaluate(const double* cores, const int64_t* shapes, int nsites, const int32_t* idx, int64_t npoints, double* out);
+}
+
+struct tci_context { std::string err; int64_t ncalls = 0; };
+
+static int mfail(tci_handle h, int code, const char* what) { if (h) h->err = what; return code; }
+
+extern "C" {
+
+int mock_create(tci_handle* out) { *out = new tci_context; return TCI_OK; }
+int mock_destroy(tci_handle h) { delete h; return TCI_OK; }
+int64_t mock_ncalls(tci_handle h) { return h->ncalls; }
+
+const char* tci_last_error(tci_handle h) { return h ? h->err.c_str() : ""; }
+int tci_malloc(tci_handle, void** p, size_t bytes) { *p = std::malloc(bytes ? bytes : 1); return *p ? TCI_OK : TCI_ERR_NOMEM; }
+int tci_free(tci_handle, void* p) { std::free(p); return TCI_OK; }
+int tci_memcpy_d2h(tci_handle, void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); return TCI_OK; }
+
+static void merge_maxabs(double* h_maxabs, const double* x, size_t n) {
+    if (!h_maxabs) return;
+    double m = std::fabs(*h_maxabs);
+    bool nan = m != m;
+    for (size_t i = 0; i < n; ++i) { const double a = std::fabs(x[i]); if (a != a) nan = true; else if (a > m) m = a; }
+    *h_maxabs = nan ? NAN : m;
+}
+
+int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites, const int32_t* h_left, int64_t nleft, int nl,
+                      const int32_t* h_right, int64_t nright, int nr, double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+    h->ncalls++;
+    const int M = nsites - nl - nr;
+    if (M < 0) return mfail(h, TCI_ERR_INVALID, "Invalid number of central indices");
+    if (nleft == 0 || nright == 0) return TCI_OK;
+    int64_t ncent = 1;
+    for (int x = 0; x < M; ++x) ncent *= h_localdims[nl + x];
+    std::vector<double> dense((size_t)(nleft * ncent * nright));
+    static const int32_t dummy = 0;
+    if (orc_batcheval((void*)f, h_localdims, nsites, h_left ? h_left : &dummy, nleft, nl, h_right ? h_right : &dummy, nright, nr, M, dense.data()))
+        return mfail(h, TCI_ERR_INVALID, orc_last_error());
+    const int64_t sc = stride_c > 0 ? stride_c : nleft, sj = stride_j > 0 ? stride_j : sc * ncent;
+    for (int64_t j = 0; j < nright; ++j)
+        for (int64_t c = 0; c < ncent; ++c)
+            for (int64_t i = 0; i < nleft; ++i) d_out[i + c * sc + j * sj] = dense[(size_t)(i + nleft * (c + ncent * j))];
+    merge_maxabs(h_maxabs, dense.data(), dense.size());
+    return TCI_OK;
+}
+
+int tci_rrlu_inplace_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol, double abstol,
+                         int leftorthogonal, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot, double* h_error, double* d_L,
+                         int64_t ldl, double* d_U, int64_t ldu, double* h_pivoterrors) {
+    h->ncalls++;
+    const int64_t mn = m < n ? m : n;
+    const int64_t mr = (maxrank <= 0 || maxrank > mn) ? mn : maxrank;
+    if (mn == 0) { *h_npivot = 0; *h_error = 0.0; if (h_pivoterrors) h_pivoterrors[0] = 0.0; return TCI_OK; }
+    const int st = orc_rrlu(d_A, m, n, lda, mr, reltol, abstol, leftorthogonal, h_rowperm, h_colperm, h_npivot, h_error, d_L, ldl, d_U, ldu,
+                            h_pivoterrors);
+    if (st == -1) return mfail(h, TCI_ERR_NAN_L, "lu.L contains NaNs");
+    if (st == -2) return mfail(h, TCI_ERR_NAN_U, "lu.U contains NaNs");
+    if (st) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+    return TCI_OK;
+}
+
+int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int leftorthogonal, const int64_t* h_rowperm, const int64_t* h_colperm,
+                         const double* d_L, int64_t ldl, const double* d_U, int64_t ldu, double* d_left, int64_t ldleft, double* d_right,
+                         int64_t ldright) {
+    h->ncalls++;
+    if (r == 0 || (!d_left && !d_right)) return TCI_OK;
+    std::vector<double> left((size_t)(m * r)), right((size_t)(r * n));
+    if (orc_luci_factors(m, n, r, leftorthogonal, h_rowperm, h_colperm, d_L, ldl, d_U, ldu, left.data(), right.data()))
+        return mfail(h, TCI_ERR_INVALID, orc_last_error());
+    if (d_left) for (int64_t k = 0; k < r; ++k) std::memcpy(d_left + k * ldleft, &left[(size_t)(k * m)], sizeof(double) * m);
+    if (d_right) for (int64_t j = 0; j < n; ++j) std::memcpy(d_right + j * ldright, &right[(size_t)(j * r)], sizeof(double) * r);
+    return TCI_OK;
+}
+
+int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb, const double* d_P, int64_t r, int64_t ldp, double* d_X,
+                        int64_t ldx) {
+    h->ncalls++;
+    if (q == 0 || r == 0) return TCI_OK;
+    std::vector<double> P((size_t)(r * r)), B((size_t)(q * r)), X((size_t)(q * r));
+    for (int64_t j = 0; j < r; ++j) {
+        std::memcpy(&P[(size_t)(j * r)], d_P + j * ldp, sizeof(double) * r);
+        std::memcpy(&B[(size_t)(j * q)], d_B + j * ldb, sizeof(double) * q);
+    }
+    if (orc_solve_right(P.data(), r, B.data(), q, X.data())) return mfail(h, TCI_ERR_INVALID, "tci_solve_right_f64: pivot matrix is singular");
+    for (int64_t j = 0; j < r; ++j) std::memcpy(d_X + j * ldx, &X[(size_t)(j * q)], sizeof(double) * q);
+    return TCI_OK;
+}
+
+int tci_maxabs_f64(tci_handle h, const double* d_x, int64_t rows, int64_t cols, int64_t ld, double* h_maxabs) {
+    h->ncalls++;
+    for (int64_t j = 0; j < cols; ++j) merge_maxabs(h_maxabs, d_x + j * ld, (size_t)rows);
+    return TCI_OK;
+}
+
+int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds, int nsites,
+                        const int32_t* h_indices, int64_t npoints, double* h_out) {
+    h->ncalls++;
+    std::vector<double> flat;
+    for (int b = 0; b < nsites; ++b) {
+        const int64_t rows = h_shapes[3 * b] * h_shapes[3 * b + 1], cols = h_shapes[3 * b + 2], ld = h_lds ? h_lds[b] : rows;
+        for (int64_t j = 0; j < cols; ++j) flat.insert(flat.end(), h_core_ptrs[b] + j * ld, h_core_ptrs[b] + j * ld + rows);
+    }
+    if (orc_tt_evaluate(flat.data(), h_shapes, nsites, h_indices, npoints, h_out)) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+    return TCI_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,174 @@
+"""GPU parity of the compiled sweep driver (csrc/tci2_driver.cpp behind `engine="native"` / native.NativeTCI2) on the real
+kernels: against the oracle (pivot sets, ranks, errors identical; tensors to 1e-10 like the Python-driven path) and
+against the Python-driven path itself (same kernels in the same order: everything identical).  Its bookkeeping alone is
+also checked on the CPU in tests/test_native_driver_mock.py."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tci():
+    import tci_b200
+    return tci_b200
+
+
+def _same_sets(t, o):
+    for b in range(1, len(t) + 1):
+        np.testing.assert_array_equal(t.Iset[b - 1], o.Iset(b), err_msg=f"Iset[{b}]")
+        np.testing.assert_array_equal(t.Jset[b - 1], o.Jset(b), err_msg=f"Jset[{b}]")
+
+
+def _close(a, r, tol):
+    assert a.shape == r.shape, (a.shape, r.shape)
+    if r.size:
+        assert np.max(np.abs(a - r)) <= tol * max(np.max(np.abs(r)), 1e-300), np.max(np.abs(a - r))
+
+
+@pytest.mark.parametrize("n,d,tol", [(5, 10, 1e-8), (8, 10, 1e-8), (6, 4, 1e-10)])
+def test_native_matches_oracle(tci, n, d, tol):
+    """C1 family through ONE C call (tci_tci2_optimize): the parity bar of tests/test_gpu_tci2.py."""
+    f, g = tci.LorentzFunction([d] * n), O.Func(O.F_LORENTZ, [1.0])
+    t, ranks, errors = tci.crossinterpolate2(f, [d] * n, tolerance=tol, nsearchglobalpivot=0, maxiter=200, engine="native")
+    o, oranks, oerrors = O.crossinterpolate2(g, [d] * n, tolerance=tol, maxiter=200)
+    assert list(ranks) == list(oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_sets(t, o)
+    for a, r in zip(t.sitetensors, o.sitetensors()):
+        _close(a, r, 1e-10)
+    assert t.maxsamplevalue == o.maxsamplevalue
+    np.testing.assert_array_equal(t.bonderrors, o.bonderrors)
+    np.testing.assert_array_equal(t.pivoterrors, o.pivoterrors)
+    pts = np.random.default_rng(0).integers(1, d + 1, size=(300, n))
+    ref = np.array([g(p) for p in pts])
+    assert np.max(np.abs(t.evaluate_batch(pts) - ref)) < 100 * tol * t.maxsamplevalue
+    assert t.sum() == pytest.approx(O.tt_sum(o.sitetensors()), rel=1e-10)
+    assert t.stats["nevals"] == o.stats()["nevals"]
+
+
+@pytest.mark.parametrize("kw", [dict(sweepstrategy="forward", maxiter=6), dict(maxbonddim=5), dict(strictlynested=True, maxiter=5),
+                                dict(normalizeerror=False)], ids=["forward", "maxbonddim", "nested", "unnormalized"])
+def test_native_identical_to_python_engine(tci, kw):
+    n = 6
+    f = tci.LorentzFunction([8] * n)
+    a, ra, ea = tci.crossinterpolate2(f, [8] * n, tolerance=1e-7, nsearchglobalpivot=0, engine="native", **kw)
+    b, rb, eb = tci.crossinterpolate2(f, [8] * n, tolerance=1e-7, nsearchglobalpivot=0, **kw)
+    np.testing.assert_array_equal(ra, rb)
+    np.testing.assert_array_equal(ea, eb)
+    for s in range(n):
+        np.testing.assert_array_equal(a.Iset[s], b.Iset[s])
+        np.testing.assert_array_equal(a.Jset[s], b.Jset[s])
+    for x, y in zip(a.sitetensors, b.sitetensors):
+        _close(x, y, 1e-13)
+    np.testing.assert_array_equal(a.pivoterrors, b.pivoterrors)
+    assert a.maxsamplevalue == b.maxsamplevalue
+
+
+def test_native_hash_function_hbm_regime(tci):
+    """Full-rank function up to maxbonddim 64 (Pi 1280 x 1280: the persistent-kernel regime of the rrLU), pivots vs oracle."""
+    ld = [20] * 6
+    f, g = tci.HashFunction(ld, 1.0, 1.0), O.Func(O.F_HASH, [1.0, 1.0])
+    kw = dict(tolerance=1e-10, maxbonddim=64, maxiter=1)
+    t, ranks, errors = tci.crossinterpolate2(f, ld, nsearchglobalpivot=0, engine="native", **kw)
+    o, oranks, oerrors = O.crossinterpolate2(g, ld, **kw)
+    assert list(ranks) == list(oranks)
+    _same_sets(t, o)
+
+
+def test_native_stepwise_reference_case(tci):
+    """test/test_tensorci2.jl:247-273 call by call on a NativeTCI2: updatepivots! per bond (linkdims 2), one global pivot +
+    makecanonical (linkdims 3), then sweeps; state compared with the oracle after every stage."""
+    from tci_b200.native import NativeTCI2
+    ld = [10] * 5
+    f, g = tci.LorentzFunction(ld), O.Func(O.F_LORENTZ, [1.0])
+    h = f.handle
+    nat = NativeTCI2(tci.lib(), h.h, ld)
+    nat.addglobalpivots([[1] * 5])
+    nat.init_maxsample(f._f, [[1] * 5])
+    o = O.TCI2(g, ld, [[1] * 5])
+
+    def same(cores):
+        for b in range(1, 6):
+            np.testing.assert_array_equal(nat.Iset(b), o.Iset(b))
+            np.testing.assert_array_equal(nat.Jset(b), o.Jset(b))
+        be, pe, mx = nat.errors()
+        np.testing.assert_array_equal(be, o.bonderrors)
+        np.testing.assert_array_equal(pe, o.pivoterrors)
+        assert mx == o.maxsamplevalue
+        if cores:
+            import torch
+            from tci_b200.parallel import _RawCuda
+            for b in range(1, 6):
+                ptr, shape = nat.core(b)
+                got = torch.as_tensor(_RawCuda(ptr, int(np.prod(shape))), device=f"cuda:{h.device}").cpu().numpy().reshape(shape, order="F")
+                _close(got, o.sitetensor(b), 1e-10)
+
+    for b in range(1, 5):
+        nat.updatepivots(f._f, b, True, reltol=1e-8, maxbonddim=2)
+        o.updatepivots(b, True, reltol=1e-8, maxbonddim=2)
+    assert nat.linkdims() == [2] * 4
+    same(False)
+    nat.addglobalpivots([[2, 9, 10, 5, 7]])
+    nat.makecanonical(f._f, reltol=1e-8)
+    o.addglobalpivots1sitesweep([[2, 9, 10, 5, 7]], reltol=1e-8)
+    assert nat.linkdims() == [3] * 4
+    same(True)
+    nat.sweep2site(f._f, 3, abstol=1e-9, fillsitetensors=False)
+    o.sweep2site(3, abstol=1e-9, fillsitetensors=False)
+    same(False)
+    assert not nat.sitetensors_available()
+    nat.sweep1site(f._f, "backward", abstol=1e-9)
+    o.sweep1site("backward", abstol=1e-9)
+    same(True)
+    nat.fillsitetensors(f._f)
+    o.fillsitetensors()
+    same(True)
+    assert nat.stats()["nbondupdates"] == 4 + 3 * 4
+    nat.close()
+
+
+def test_native_global_pivot_search(tci):
+    """Default finder inside the driver (one batch of f and one of the tensor train per iteration): a feature that needs
+    v2 = v5 = 4 together is invisible to two-site sweeps started at [1, 1, ...] and found by the line search."""
+    ld = [4] * 6
+    table = np.full(ld, 0.5)
+    table[:, 3, :, :, 3, :] = 5.0
+    f = tci.DenseFunction(table)
+    t0, _, _ = tci.crossinterpolate2(f, ld, tolerance=1e-10, nsearchglobalpivot=0, engine="native")
+    assert t0.rank() == 1
+    t, ranks, errors = tci.crossinterpolate2(f, ld, tolerance=1e-10, nsearchglobalpivot=40, maxnglobalpivot=5, seed=7, engine="native")
+    assert t.rank() == 2
+    pts = np.random.default_rng(2).integers(1, 5, size=(200, 6))
+    ref = np.array([table[tuple(p - 1)] for p in pts])
+    assert np.max(np.abs(t.evaluate_batch(pts) - ref)) < 1e-9
+
+
+def test_native_quantics_c4_small(tci):
+    R = 16
+    f, g = tci.QuanticsExpPlusSin([2] * R), O.Func(O.F_QEXPPLUSSIN, [1.0, 1e-3, 1000.0])
+    t, ranks, errors = tci.crossinterpolate2(f, [2] * R, tolerance=1e-10, nsearchglobalpivot=0, maxbonddim=64, engine="native")
+    o, oranks, oerrors = O.crossinterpolate2(g, [2] * R, tolerance=1e-10, maxbonddim=64)
+    assert abs(int(ranks[-1]) - int(oranks[-1])) <= 1
+    pts = np.random.default_rng(1).integers(1, 3, size=(500, R))
+    ref = np.array([g(p) for p in pts])
+    assert np.max(np.abs(t.evaluate_batch(pts) - ref)) < 1e-7
+
+
+def test_native_errors(tci):
+    f = tci.LorentzFunction([3, 3, 3])
+    with pytest.raises(tci.TCIError, match="pivotsearch=:full only"):
+        tci.crossinterpolate2(f, [3, 3, 3], engine="native", pivotsearch="rook")
+    with pytest.raises(tci.TCIError, match="device functor"):
+        tci.crossinterpolate2(lambda v: 1.0, [3, 3, 3], engine="native")
+    with pytest.raises(tci.TCIError, match="convergence criterion is not reachable"):
+        tci.crossinterpolate2(f, [3, 3, 3], engine="native", tolerance=0.0)
+    with pytest.raises(tci.TCIError, match="maxsamplevalue is zero!"):
+        tci.crossinterpolate2(tci.DenseFunction(np.zeros((3, 3))), [3, 3], engine="native")
+    with pytest.raises(tci.TCIError, match="Unknown engine"):
+        tci.crossinterpolate2(f, [3, 3, 3], engine="fortran")
+    assert C.sizeof(C.c_void_p) == 8

@@ -1,0 +1,187 @@
+"""CPU check of the compiled sweep driver's BOOKKEEPING (csrc/tci2_driver.cpp): the unchanged driver source is linked
+against tests/native_mock/mock_cabi.cpp — host-memory stand-ins of the few C-ABI entry points it calls, backed by the
+oracle's arithmetic — and driven through the product's own ctypes front end (native.py).  Index sets, ranks, errors
+and site tensors must then be IDENTICAL to the oracle's TensorCI2 (same arithmetic underneath, so any difference is
+a bookkeeping bug: union/kronecker order, history extras, error merging, sweep order, convergence).
+The GPU parity tests of the same driver on the real kernels are in tests/test_gpu_native_driver.py."""
+import ctypes as C
+import importlib.util
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "tensorcrossinterpolation.jl_b200")
+
+
+def _load(name):
+    """Load one host-side module of the package without importing the package (no CUDA library needed)."""
+    import tci_b200                                          # noqa: F401  (importable without a GPU)
+    return importlib.import_module(f"tci_b200.{name}")
+
+
+@pytest.fixture(scope="module")
+def mock():
+    O.build()
+    out = os.path.join(ROOT, "tests", "_build")
+    os.makedirs(out, exist_ok=True)
+    so = os.path.join(out, "libtci2_mock.so")
+    srcs = [os.path.join(ROOT, "tests", "native_mock", "mock_cabi.cpp"), os.path.join(PKG, "csrc", "tci2_driver.cpp")]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-fPIC", "-shared", "-o", so, *srcs,
+                               "-L" + os.path.join(ROOT, "oracle", "_build"), "-ltci_oracle",
+                               "-Wl,-rpath," + os.path.join(ROOT, "oracle", "_build")])
+    L = C.CDLL(so)
+    h = C.c_void_p()
+    assert L.mock_create(C.byref(h)) == 0
+    yield L, h
+    L.mock_destroy(h)
+
+
+def _native(mock, localdims, f, pivots):
+    L, h = mock
+    N = _load("native").NativeTCI2
+    t = N(L, h, localdims)
+    t.addglobalpivots(pivots)
+    t.init_maxsample(f.h, pivots)
+    return t
+
+
+def _same_state(t, o, cores=True):
+    n = len(t)
+    for b in range(1, n + 1):
+        np.testing.assert_array_equal(t.Iset(b), o.Iset(b))
+        np.testing.assert_array_equal(t.Jset(b), o.Jset(b))
+    be, pe, mx = t.errors()
+    np.testing.assert_array_equal(be, o.bonderrors)
+    np.testing.assert_array_equal(pe, o.pivoterrors)
+    assert mx == o.maxsamplevalue
+    if cores:
+        assert t.sitetensors_available()
+        for b in range(1, n + 1):
+            ptr, shape = t.core(b)
+            size = int(np.prod(shape))
+            got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(size,)).reshape(shape, order="F")
+            np.testing.assert_array_equal(got, o.sitetensor(b))
+
+
+CASES = [
+    ("lorentz5", O.F_LORENTZ, [1.0], [10] * 5, dict(tolerance=1e-8)),
+    ("lorentz8_c1", O.F_LORENTZ, [1.0], [10] * 8, dict(tolerance=1e-8)),
+    ("lorentz_maxbond", O.F_LORENTZ, [1.0], [6] * 6, dict(tolerance=1e-12, maxbonddim=5)),
+    ("lorentz_forward", O.F_LORENTZ, [1.0], [5] * 6, dict(tolerance=1e-9, sweepstrategy="forward")),
+    ("lorentz_nested", O.F_LORENTZ, [1.0], [5] * 6, dict(tolerance=1e-9, strictlynested=True)),
+    ("quantics_c4_small", O.F_QEXPSIN, [10.0, 100.0, 1.1], [2] * 16, dict(tolerance=1e-10, maxbonddim=64)),
+    ("hash_fullrank", O.F_HASH, [1.0, 0.0], [4] * 6, dict(tolerance=1e-10, maxbonddim=12, maxiter=4)),
+    ("mixed_dims", O.F_LORENTZ, [2.5], [3, 7, 2, 5, 4], dict(tolerance=1e-10, normalizeerror=False)),
+]
+
+
+@pytest.mark.parametrize("name,kind,params,localdims,kw", CASES, ids=[c[0] for c in CASES])
+def test_optimize_identical_to_oracle(mock, name, kind, params, localdims, kw):
+    f = O.Func(kind, params)
+    piv = [[1] * len(localdims)] if kind != O.F_QEXPSIN else [[2, 1] * (len(localdims) // 2)]   # f(x = 0) = 0 there
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, **kw)
+    t = _native(mock, localdims, f, piv)
+    ranks, errors = t.optimize(f.h, nsearchglobalpivot=0, **kw)
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+    assert t.stats()["nevals"] > 0
+
+
+def test_stepwise_calls_identical_to_oracle(mock):
+    """test/test_tensorci2.jl:247-273 driven call by call: updatepivots! per bond, addglobalpivots + makecanonical,
+    sweep2site without the final fill, sweep1site in both directions, fillsitetensors."""
+    localdims = [10] * 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    piv = [[1] * 5]
+    o = O.TCI2(f, localdims, piv)
+    t = _native(mock, localdims, f, piv)
+    for b in range(1, 5):
+        o.updatepivots(b, True, reltol=1e-8, maxbonddim=2)
+        t.updatepivots(f.h, b, True, reltol=1e-8, maxbonddim=2)
+    assert t.linkdims() == [2] * 4
+    _same_state(t, o, cores=False)
+    gp = [[2, 9, 10, 5, 7]]
+    o.addglobalpivots1sitesweep(gp, reltol=1e-8)
+    t.addglobalpivots(gp)
+    t.makecanonical(f.h, reltol=1e-8)
+    assert t.linkdims() == [3] * 4
+    _same_state(t, o)
+    o.sweep2site(3, iter1=1, abstol=1e-9, fillsitetensors=False)
+    t.sweep2site(f.h, 3, iter1=1, abstol=1e-9, fillsitetensors=False)
+    _same_state(t, o, cores=False)
+    assert not t.sitetensors_available()
+    o.sweep1site("backward", abstol=1e-9, updatetensors=True)
+    t.sweep1site(f.h, "backward", abstol=1e-9, updatetensors=True)
+    _same_state(t, o)
+    o.sweep1site("forward", abstol=1e-9, updatetensors=False)
+    t.sweep1site(f.h, "forward", abstol=1e-9, updatetensors=False)
+    _same_state(t, o, cores=False)
+    o.fillsitetensors()
+    t.fillsitetensors(f.h)
+    _same_state(t, o)
+
+
+def test_pivoterrors_diagonal_exact(mock):                 # test/test_tensorci2.jl:27-39
+    diags = [1.0, 1e-5, 0.0]
+    f = O.Func(O.F_DENSE, table=np.diag(diags))
+    t = _native(mock, [3, 3], f, [[1, 1]])
+    t.optimize(f.h, tolerance=1e-8, nsearchglobalpivot=0)
+    assert list(t.errors()[1]) == diags
+
+
+def test_global_pivot_search_finds_hidden_feature(mock):
+    """The line search of the default finder (globalpivotfinder.jl:205-264) on a function whose feature the two-site
+    sweeps started at [1, 1, ...] cannot see: with the search the interpolation is exact on the feature, without it is not."""
+    localdims = [4] * 6
+    table = np.ones(localdims) * 0.5
+    table[:, 3, :, :, 3, :] = 5.0                          # needs v2 = v5 = 4 together: no two-site Pi built from [1, 1, ...] holds it
+    f = O.Func(O.F_DENSE, table=table)
+    Nat = _load("native")
+    t0 = _native(mock, localdims, f, [[1] * 6])
+    t0.optimize(f.h, tolerance=1e-10, nsearchglobalpivot=0)
+    assert t0.rank() == 1
+    t = _native(mock, localdims, f, [[1] * 6])
+    t.seed(7)
+    ranks, errors = t.optimize(f.h, tolerance=1e-10, nsearchglobalpivot=40, maxnglobalpivot=5)
+    assert t.rank() == 2 and ranks[-1] == 2
+    cores = [np.ctypeslib.as_array(C.cast(t.core(b)[0], C.POINTER(C.c_double)),
+                                   shape=(int(np.prod(t.core(b)[1])),)).reshape(t.core(b)[1], order="F") for b in range(1, 7)]
+    v = np.ones((1, 1))
+    for c, i in zip(cores, [1, 4, 1, 1, 4, 1]):
+        v = v @ c[:, i - 1, :]
+    assert abs(v[0, 0] - 5.0) < 1e-9
+    assert Nat.STRATEGY["backandforth"] == 1
+
+
+def test_errors_mirror_the_reference(mock):
+    L, h = mock
+    Nat = _load("native")
+    TCIError = _load("_lib").TCIError
+    with pytest.raises(TCIError, match="at least 2 elements"):
+        Nat.NativeTCI2(L, h, [3])
+    f = O.Func(O.F_DENSE, table=np.zeros((3, 3)))
+    t = Nat.NativeTCI2(L, h, [3, 3])
+    t.addglobalpivots([[1, 1]])
+    with pytest.raises(TCIError, match="maxsamplevalue is zero!"):
+        t.init_maxsample(f.h, [[1, 1]])
+    with pytest.raises(TCIError, match="one index per leg"):
+        t.addglobalpivots([[1, 1, 1]])
+    g = O.Func(O.F_LORENTZ, [1.0])
+    t = _native(mock, [3, 3, 3], g, [[1, 1, 1]])
+    with pytest.raises(TCIError, match="convergence criterion is not reachable"):
+        t.optimize(g.h, tolerance=0.0)
+    with pytest.raises(TCIError, match="nsearchglobalpivot < maxnglobalpivot"):
+        t.optimize(g.h, tolerance=1e-8, nsearchglobalpivot=2, maxnglobalpivot=5)
+    with pytest.raises(TCIError, match="site tensors are not available"):
+        t.core(1)
+    t2 = _native(mock, [3, 3, 3], g, [[1, 1, 1]])
+    t2.set_indexset(0, 2, [[1], [2]])                       # |Iset[2]| = 2 but |Jset[1]| = 1: not square
+    with pytest.raises(TCIError, match="Pivot matrix at bond 1 is not square!"):
+        t2.fillsitetensors(g.h)
