@@ -509,9 +509,10 @@ rrlu_persistent_kernel(double* __restrict__ A, int m, int n, long long lda, doub
 }
 
 // L = tril(A[:, 1:r]), U = triu(A[1:r, :]), NaN flags, unit diagonal (:372-388).
-__global__ void rrlu_extract_kernel(const double* __restrict__ A, int m, int n, long long lda, int r, int leftorth,
+__global__ void rrlu_extract_kernel(const double* __restrict__ A, int m, int n, long long lda, int r_in, int leftorth,
                                     double* __restrict__ L, long long ldl, double* __restrict__ U, long long ldu,
                                     RrluState* st) {
+    const int r = r_in >= 0 ? r_in : st->npivot;          // r_in < 0: the host has not read the pivot count back yet
     const long long nL = (long long)m * r, nU = (long long)r * n;
     int flags = 0;
     for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < nL + nU; t += (long long)gridDim.x * blockDim.x) {
@@ -1126,6 +1127,7 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     if (const char* e = getenv("TCI_RRLU_MODE")) persistent = strcmp(e, "persistent") == 0 ? true : (strcmp(e, "steps") == 0 ? false : persistent);
     if (h->rrlu_profile) persistent = false;                // per-launch profiling needs the step kernels
     if (const char* e = getenv("TCI_RRLU_PDL")) h->rrlu_pdl = atoi(e) ? 1 : 0;
+    if (const char* e = getenv("TCI_RRLU_LATE_STATE")) h->rrlu_late_state = atoi(e) ? 1 : 0;
     const size_t smem_need = sizeof(double) * (size_t)(m | 1) * n;
     bool in_smem = persistent && smem_need <= 200 * 1024;
     if (const char* e = getenv("TCI_RRLU_SMEM")) in_smem = in_smem && atoi(e) != 0;
@@ -1142,6 +1144,14 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
             if (rc) return rc;
         }
         TCI_CUDA(h, cudaEventRecord(h->ev[1], h->stream));
+        if (in_smem && h->rrlu_late_state) {
+            // Single-CTA kernel: nothing to check before the extraction (no grid barrier that could time out), so the
+            // state is read back once, together with the permutations, by rrlu_finish — one host synchronisation per
+            // factorisation instead of two (the small-Pi regime is bound by exactly these round trips).
+            final_state->npivot = -1; final_state->flags = 0;
+            h->rrlu_ms[1] = 0.0;
+            return TCI_OK;
+        }
         TCI_CUDA(h, cudaMemcpyAsync(hst, w->st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
         TCI_CUDA(h, cudaStreamSynchronize(h->stream));
         if (hst->flags & 4) return tci_fail(h, TCI_ERR_CUDA, "rrlu: grid barrier timed out in the persistent kernel");
@@ -1233,14 +1243,15 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
 }
 
 static int rrlu_finish(tci_handle h, const double* d_A, int m, int n, long long lda, int leftorth, const SmallWs& w,
-                       RrluState* fs, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot, double* h_error,
+                       RrluState* fs, int mr, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot, double* h_error,
                        double* d_L, long long ldl, double* d_U, long long ldu, double* h_pivoterrors) {
-    const int r = fs->npivot;
+    const bool late = fs->npivot < 0;                       // rrlu_run left the state on the device (see there)
+    int r = late ? mr : fs->npivot;                         // late: an upper bound, the kernel reads the count itself
     if (r > 0) {
         const long long work = (long long)m * r + (long long)r * n;
         long long blocks = (work + 255) / 256;
         if (blocks > h->num_sms * 8) blocks = h->num_sms * 8;
-        rrlu_extract_kernel<<<(int)blocks, 256, 0, h->stream>>>(d_A, m, n, lda, r, leftorth, d_L, ldl, d_U, ldu, w.st);
+        rrlu_extract_kernel<<<(int)blocks, 256, 0, h->stream>>>(d_A, m, n, lda, late ? -1 : r, leftorth, d_L, ldl, d_U, ldu, w.st);
         TCI_LAUNCH_CHECK(h);
     }
     TCI_CUDA(h, cudaEventRecord(h->ev[2], h->stream));
@@ -1254,6 +1265,7 @@ static int rrlu_finish(tci_handle h, const double* d_A, int m, int n, long long 
     TCI_CUDA(h, cudaMemcpyAsync(hcp, w.colperm, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
     if (r > 0) TCI_CUDA(h, cudaMemcpyAsync(hpv, w.pivvals, sizeof(double) * r, cudaMemcpyDeviceToHost, h->stream));
     TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (late) { r = hst->npivot; *fs = *hst; h->rrlu_steps = r; }
     float ms = 0.f;
     cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]); h->rrlu_ms[0] = ms;
     cudaEventElapsedTime(&ms, h->ev[1], h->ev[2]); h->rrlu_ms[2] = ms;
@@ -1301,7 +1313,7 @@ int tci_rrlu_inplace_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_
     SmallWs w; RrluState fs;
     rc = rrlu_run(h, d_A, (int)m, (int)n, lda, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
     if (rc) return rc;
-    return rrlu_finish(h, d_A, (int)m, (int)n, lda, leftorthogonal ? 1 : 0, w, &fs, h_rowperm, h_colperm, h_npivot, h_error,
+    return rrlu_finish(h, d_A, (int)m, (int)n, lda, leftorthogonal ? 1 : 0, w, &fs, (int)mr, h_rowperm, h_colperm, h_npivot, h_error,
                        d_L, ldl, d_U, ldu, h_pivoterrors);
 }
 
@@ -1333,7 +1345,7 @@ int tci_rrlu_host_f64(tci_handle h, const double* h_A, int64_t m, int64_t n, int
     SmallWs w; RrluState fs;
     rc = rrlu_run(h, dA, (int)m, (int)n, ldw, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
     if (rc) return rc;
-    rc = rrlu_finish(h, dA, (int)m, (int)n, ldw, leftorthogonal ? 1 : 0, w, &fs, h_rowperm, h_colperm, h_npivot, h_error,
+    rc = rrlu_finish(h, dA, (int)m, (int)n, ldw, leftorthogonal ? 1 : 0, w, &fs, (int)mr, h_rowperm, h_colperm, h_npivot, h_error,
                      h_L ? dL : nullptr, m, h_U ? dU : nullptr, mr, h_pivoterrors);
     if (rc) return rc;
     const int64_t r = fs.npivot;
