@@ -175,6 +175,17 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
                       const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
                       double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs);
 
+/* The same evaluation without the host round trip for the maximum: max |value| (and a NaN flag) are merged into a 16-byte
+ * DEVICE accumulator the caller owns (tci_malloc), across as many batches as it likes; nothing is synchronised.  The
+ * accumulator is initialised with tci_maxacc_set(value) (= the running maxsamplevalue) and read with tci_maxacc_get, which
+ * synchronises and returns max(|initial|, every value since), NaN-propagating — `updatemaxsample!` (src/tensorci2.jl:636-638)
+ * deferred to where the host next needs the number (the tolerance of the next sweep, src/tensorci2.jl:1089-1090). */
+int tci_batcheval_acc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                          const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                          double* d_out, int64_t stride_c, int64_t stride_j, void* d_acc16);
+int tci_maxacc_set(tci_handle h, void* d_acc16, double value);
+int tci_maxacc_get(tci_handle h, const void* d_acc16, double* h_value);
+
 /* Sharded batch: the same evaluation, but every value is stored to `nouts` (1..8) destination buffers —
  * h_d_outs[0] is this GPU's buffer, the others are the peers' buffers mapped into this process (tci_ipc_open): the
  * assembly kernel IS the all-gather (peer stores over NVLink), there is no separate exchange pass.  The caller passes its

@@ -238,7 +238,7 @@ namespace {
 
 struct EvalBuffers { int* d_left; int* d_right; void* Ls; void* Rs; unsigned long long* maxbits; int* nanflag; };
 
-int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, const EvalShape& sh, EvalBuffers* b) {
+int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, const EvalShape& sh, EvalBuffers* b, bool zero_acc = true) {
     const size_t nli = (size_t)sh.nleft * sh.nl, nri = (size_t)sh.nright * sh.nr;
     const size_t ints = ((nli + nri) * sizeof(int) + 255) & ~(size_t)255;
     int rc = tci_ws_reserve(h, h->ws_a, ints + 256);
@@ -249,7 +249,7 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
     b->maxbits = (unsigned long long*)((char*)h->ws_a.ptr + ints);
     b->nanflag = (int*)(b->maxbits + 1);
     b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + 16 * (size_t)sh.nleft;
-    TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
+    if (zero_acc) TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
     // The index tables are pageable host memory: cudaMemcpyAsync stages them before it returns, so there is no host
     // synchronisation here and the caller may reuse its arrays immediately.
     if (nli) TCI_CUDA(h, cudaMemcpyAsync(b->d_left, h_left, nli * sizeof(int), cudaMemcpyHostToDevice, h->stream));
@@ -369,9 +369,16 @@ int tci_functor_destroy(tci_handle h, tci_functor f) {
     return TCI_OK;
 }
 
-int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
-                            const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
-                            double* const* h_d_outs, int nouts, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+} // extern "C"
+
+// Shared body of the batch-evaluation entry points: validates, stages the index tables and enqueues the kernels; no host
+// synchronisation.  The running max |value| / NaN flag go to `d_acc` (16 bytes: u64 bits of the maximum, int flag) WITHOUT
+// resetting it when the caller owns an accumulator, else to a scratch accumulator that is zeroed first; *d_acc_used tells
+// which (NULL when nothing was launched because a set is empty).
+static int batcheval_enqueue(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                             const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                             double* const* h_d_outs, int nouts, int64_t stride_c, int64_t stride_j, void* d_acc, void** d_acc_used) {
+    if (d_acc_used) *d_acc_used = nullptr;
     if (!h) return TCI_ERR_INVALID;
     if (nouts < 1 || nouts > 8 || !h_d_outs) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_multi_f64: 1..8 destination buffers");
     double* d_out = h_d_outs[0];
@@ -395,8 +402,9 @@ int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_locald
     sh.nouts = nouts;
     for (int p = 0; p < 8; ++p) sh.outs[p] = p < nouts ? h_d_outs[p] : nullptr;
     EvalBuffers b;
-    int rc = stage_tables(h, h_left, h_right, sh, &b);
+    int rc = stage_tables(h, h_left, h_right, sh, &b, d_acc == nullptr);
     if (rc) return rc;
+    if (d_acc) { b.maxbits = (unsigned long long*)d_acc; b.nanflag = (int*)(b.maxbits + 1); }
     switch (f->kind) {
     case TCI_F_LORENTZ: rc = run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b); break;
     case TCI_F_SUM: rc = run_builtin(h, SumF{f->p[0]}, sh, nsites, b); break;
@@ -409,17 +417,33 @@ int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_locald
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
     }
     if (rc) return rc;
-    if (h_maxabs) {
-        rc = tci_pinned_reserve(h, 64);
-        if (rc) return rc;
-        unsigned long long* pin = (unsigned long long*)h->pinned;
-        TCI_CUDA(h, cudaMemcpyAsync(pin, b.maxbits, 16, cudaMemcpyDeviceToHost, h->stream));
-        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
-        double mx; memcpy(&mx, &pin[0], 8);
-        int nf; memcpy(&nf, &pin[1], 4);
-        const double prev = fabs(*h_maxabs);                                    // util.jl:34-43: max(abs(x), abs(y)), NaN propagates
-        if (nf || prev != prev) *h_maxabs = NAN; else *h_maxabs = prev > mx ? prev : mx;
-    }
+    if (d_acc_used) *d_acc_used = b.maxbits;
+    return TCI_OK;
+}
+
+// 16 accumulator bytes -> max(|prev|, maximum), NaN-propagating (util.jl:34-43); synchronises the stream.
+static int read_acc(tci_handle h, const void* d_acc, double prev_in, double* out) {
+    int rc = tci_pinned_reserve(h, 64);
+    if (rc) return rc;
+    unsigned long long* pin = (unsigned long long*)h->pinned;
+    TCI_CUDA(h, cudaMemcpyAsync(pin, d_acc, 16, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    double mx; memcpy(&mx, &pin[0], 8);
+    int nf; memcpy(&nf, &pin[1], 4);
+    const double prev = fabs(prev_in);
+    if (nf || prev != prev) *out = NAN; else *out = prev > mx ? prev : mx;
+    return TCI_OK;
+}
+
+extern "C" {
+int tci_batcheval_multi_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                            const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                            double* const* h_d_outs, int nouts, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
+    void* acc = nullptr;
+    int rc = batcheval_enqueue(h, f, h_localdims, nsites, h_left, nleft, nl, h_right, nright, nr, h_d_outs, nouts, stride_c, stride_j,
+                               nullptr, &acc);
+    if (rc) return rc;
+    if (h_maxabs && acc) return read_acc(h, acc, *h_maxabs, h_maxabs);
     return TCI_OK;
 }
 
@@ -428,6 +452,33 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
                       double* d_out, int64_t stride_c, int64_t stride_j, double* h_maxabs) {
     double* outs[1] = {d_out};
     return tci_batcheval_multi_f64(h, f, h_localdims, nsites, h_left, nleft, nl, h_right, nright, nr, outs, 1, stride_c, stride_j, h_maxabs);
+}
+
+int tci_batcheval_acc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                          const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                          double* d_out, int64_t stride_c, int64_t stride_j, void* d_acc16) {
+    if (h && !d_acc16) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_acc_f64: NULL accumulator");
+    double* outs[1] = {d_out};
+    return batcheval_enqueue(h, f, h_localdims, nsites, h_left, nleft, nl, h_right, nright, nr, outs, 1, stride_c, stride_j, d_acc16, nullptr);
+}
+
+int tci_maxacc_set(tci_handle h, void* d_acc16, double value) {
+    if (!h) return TCI_ERR_INVALID;
+    if (!d_acc16) return tci_fail(h, TCI_ERR_INVALID, "tci_maxacc_set: NULL accumulator");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    unsigned long long w[2] = {0ull, 0ull};
+    const double a = fabs(value);
+    if (a != a) { const int one = 1; memcpy(&w[1], &one, 4); } else memcpy(&w[0], &a, 8);
+    // pageable source: cudaMemcpyAsync stages it before returning (same as the index tables)
+    TCI_CUDA(h, cudaMemcpyAsync(d_acc16, w, 16, cudaMemcpyHostToDevice, h->stream));
+    return TCI_OK;
+}
+
+int tci_maxacc_get(tci_handle h, const void* d_acc16, double* h_value) {
+    if (!h) return TCI_ERR_INVALID;
+    if (!d_acc16 || !h_value) return tci_fail(h, TCI_ERR_INVALID, "tci_maxacc_get: NULL argument");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    return read_acc(h, d_acc16, 0.0, h_value);
 }
 
 // ---- peer-mapped buffers for the sharded batch (CUDA IPC; one process per GPU on one NVSwitch box) --------------------

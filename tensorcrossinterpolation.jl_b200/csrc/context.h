@@ -31,7 +31,7 @@ struct tci_context {
     int64_t rrlu_steps = 0;
     int rrlu_smem_optin = 0;                // the single-CTA kernel's > 48 KB dynamic shared memory has been enabled
     int rrlu_pdl = 1;                       // programmatic dependent launch between the step kernels (TCI_RRLU_PDL=0 disables)
-    int rrlu_late_state = 0;                // single-CTA kernel: read the final state once, in rrlu_finish (TCI_RRLU_LATE_STATE=1)
+    int rrlu_late_state = 1;                // single-CTA kernel: read the final state once, in rrlu_finish (TCI_RRLU_LATE_STATE=0: twice)
     int rrlu_profile = 0;                   // 1: bracket every update-kernel launch with events
     long long l2_window_bytes = -1;         // persisting-L2 window of the step kernels (-1: not initialised, 0: off)
     std::vector<cudaEvent_t> ev_pool;

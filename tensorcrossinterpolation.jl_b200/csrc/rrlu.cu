@@ -1114,8 +1114,12 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     const int grid = cfg.grid;
     int rc = carve(h, m, n, grid > h->num_sms * 8 ? grid : h->num_sms * 8, w);
     if (rc) return rc;
-    rc = tci_pinned_reserve(h, sizeof(RrluState) + sizeof(int) * ((size_t)m + n) + sizeof(double) * (size_t)(mr + 1));
-    if (rc) return rc;
+    {   // read-back staging: either the packed layout or an image of the workspace up to the pivot values (rrlu_finish)
+        const size_t packed = sizeof(RrluState) + sizeof(int) * ((size_t)m + n) + sizeof(double) * (size_t)(mr + 1) + 32;
+        const size_t image = (size_t)((char*)w->pivvals - (char*)w->st) + sizeof(double) * (size_t)(mr + 1);
+        rc = tci_pinned_reserve(h, packed > image ? packed : image);
+        if (rc) return rc;
+    }
     const int mx = m > n ? m : n;
     rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n, w->bar);
     TCI_LAUNCH_CHECK(h);
@@ -1260,10 +1264,20 @@ static int rrlu_finish(tci_handle h, const double* d_A, int m, int n, long long 
     int* hrp = (int*)(pin + sizeof(RrluState));
     int* hcp = hrp + m;
     double* hpv = (double*)(hcp + n + ((m + n) & 1));      // keep 8-byte alignment
-    TCI_CUDA(h, cudaMemcpyAsync(hst, w.st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
-    TCI_CUDA(h, cudaMemcpyAsync(hrp, w.rowperm, sizeof(int) * m, cudaMemcpyDeviceToHost, h->stream));
-    TCI_CUDA(h, cudaMemcpyAsync(hcp, w.colperm, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
-    if (r > 0) TCI_CUDA(h, cudaMemcpyAsync(hpv, w.pivvals, sizeof(double) * r, cudaMemcpyDeviceToHost, h->stream));
+    const size_t image = (size_t)((const char*)w.pivvals - (const char*)w.st) + sizeof(double) * (size_t)(r > 0 ? r : 0);
+    if (image <= 64 * 1024) {
+        // small problem: state, permutations and pivot values are one contiguous stretch of the workspace (carve) —
+        // one copy instead of four
+        TCI_CUDA(h, cudaMemcpyAsync(pin, w.st, image, cudaMemcpyDeviceToHost, h->stream));
+        hrp = (int*)(pin + ((const char*)w.rowperm - (const char*)w.st));
+        hcp = (int*)(pin + ((const char*)w.colperm - (const char*)w.st));
+        hpv = (double*)(pin + ((const char*)w.pivvals - (const char*)w.st));
+    } else {
+        TCI_CUDA(h, cudaMemcpyAsync(hst, w.st, sizeof(RrluState), cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaMemcpyAsync(hrp, w.rowperm, sizeof(int) * m, cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaMemcpyAsync(hcp, w.colperm, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
+        if (r > 0) TCI_CUDA(h, cudaMemcpyAsync(hpv, w.pivvals, sizeof(double) * r, cudaMemcpyDeviceToHost, h->stream));
+    }
     TCI_CUDA(h, cudaStreamSynchronize(h->stream));
     if (late) { r = hst->npivot; *fs = *hst; h->rrlu_steps = r; }
     float ms = 0.f;

@@ -3,7 +3,7 @@
 // The north star keeps sweep strategy, index-set bookkeeping and convergence control in the host language and lets it
 // call the kernels through the C ABI.  This file is that host side in C++: it restates src/tensorci2.jl's control flow
 // (citations per function) and produces every number through the public entry points of include/tci_b200.h only
-// (tci_batcheval_f64, tci_rrlu_inplace_f64, tci_luci_factors_f64, tci_solve_right_f64, tci_maxabs_f64,
+// (tci_batcheval_acc_f64 / tci_maxacc_*, tci_rrlu_inplace_f64, tci_luci_factors_f64, tci_solve_right_f64, tci_maxabs_f64,
 // tci_tt_evaluate_f64, tci_malloc/free/memcpy) — no CUDA header, no internal symbol.  It exists because a half-sweep
 // over small Pi matrices is a chain of hundreds of microsecond-sized device calls: an interpreted host pays ~200 us of
 // bookkeeping per bond on top of them, a compiled one a few.  Being pure C-ABI client code it also compiles against any
@@ -167,6 +167,8 @@ struct tci_tci2_s {
     std::vector<IdxTable> histI, histJ;
     int64_t nhist = 0;
     DevBuf pi, L, U, pi1, pmat, pts;                    // scratch: Pi, rrLU factors, setsitetensor! operands, point values
+    void* acc = nullptr;                                // device-side max |f| accumulator: updatemaxsample! without a host round
+                                                        // trip per batch; read back where a sweep ends (sync_maxsample)
     std::vector<int64_t> rowperm, colperm;
     std::vector<double> pe;
     std::string err;
@@ -225,10 +227,24 @@ double pivoterror(const tci_tci2_s* t) {                                     // 
 int fill(tci_tci2 t, tci_functor f, const IdxTable& I, const IdxTable& J, double* d_out, int64_t sc, int64_t sj, int64_t ncenter_elems) {
     if (I.n == 0 || J.n == 0) return TCI_OK;
     const double t0 = now_s();
-    TCI2_CALL(t, tci_batcheval_f64(t->h, f, t->localdims.data(), t->N, I.data(), I.n, I.len, J.data(), J.n, J.len, d_out, sc, sj,
-                                   &t->maxsamplevalue));
+    TCI2_CALL(t, tci_batcheval_acc_f64(t->h, f, t->localdims.data(), t->N, I.data(), I.n, I.len, J.data(), J.n, J.len, d_out, sc, sj,
+                                       t->acc));
     t->nevals += I.n * J.n * ncenter_elems;
     t->t_eval += now_s() - t0;
+    return TCI_OK;
+}
+
+// maxsamplevalue <- the device accumulator (every fill since the last read has been merged into it on the device)
+int sync_maxsample(tci_tci2 t) {
+    double v = 0.0;
+    TCI2_CALL(t, tci_maxacc_get(t->h, t->acc, &v));
+    t->maxsamplevalue = v;
+    return TCI_OK;
+}
+
+int set_maxsample(tci_tci2 t, double v) {
+    t->maxsamplevalue = v;
+    TCI2_CALL(t, tci_maxacc_set(t->h, t->acc, v));
     return TCI_OK;
 }
 
@@ -376,7 +392,7 @@ int sweep1site(tci_tci2 t, tci_functor f, bool fwd, double reltol, double abstol
         rc = fill(t, f, t->I[last], t->J[last], c.buf.p, nI, nI * d, d); if (rc) return rc;
         c.chil = nI; c.d = d; c.chir = nJ; c.valid = true;
     }
-    return TCI_OK;
+    return sync_maxsample(t);
 }
 
 int makecanonical(tci_tci2 t, tci_functor f, double reltol, double abstol, int64_t maxbonddim) {     // tensorci2.jl:738-749
@@ -408,8 +424,8 @@ int sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, i
             if (rc) return rc;
         }
     }
-    if (dofill) return fillsitetensors(t, f);                                                // :1253-1255
-    return TCI_OK;
+    if (dofill) { int rc = fillsitetensors(t, f); if (rc) return rc; }                       // :1253-1255
+    return sync_maxsample(t);
 }
 
 bool convergencecriterion(const std::vector<int64_t>& ranks, const std::vector<double>& errors, const std::vector<int64_t>& nglobal,
@@ -507,6 +523,11 @@ int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tc
     t->I.resize(nsites); t->J.resize(nsites); t->T.resize(nsites);
     for (int b = 0; b < nsites; ++b) { t->I[b].len = b; t->J[b].len = nsites - b - 1; }
     t->bonderrors.assign((size_t)nsites - 1, 0.0);
+    if (tci_malloc(h, &t->acc, 64) != TCI_OK || tci_maxacc_set(h, t->acc, 0.0) != TCI_OK) {
+        if (t->acc) tci_free(h, t->acc);
+        delete t;
+        return TCI_ERR_NOMEM;
+    }
     *out = t;
     return TCI_OK;
 }
@@ -516,6 +537,7 @@ int tci_tci2_destroy(tci_tci2 t) {
     DevBuf* bufs[] = {&t->pi, &t->L, &t->U, &t->pi1, &t->pmat, &t->pts};
     for (DevBuf* b : bufs) if (b->p) tci_free(t->h, b->p);
     for (auto& c : t->T) if (c.buf.p) tci_free(t->h, c.buf.p);
+    if (t->acc) tci_free(t->h, t->acc);
     delete t;
     return TCI_OK;
 }
@@ -543,7 +565,7 @@ int tci_tci2_init_maxsample(tci_tci2 t, tci_functor f, const int32_t* h_pivots, 
         TCI2_CALL(t, tci_batcheval_f64(t->h, f, t->localdims.data(), t->N, h_pivots, npivots, t->N, nullptr, 1, 0, t->pts.p, 0, 0, &mx));
         m = jl_max(m, mx);
     }
-    t->maxsamplevalue = m;
+    int rc = set_maxsample(t, m); if (rc) return rc;
     if (!(std::fabs(m) > 0.0)) return fail(t, TCI_ERR_INVALID, "maxsamplevalue is zero!");     // :113
     invalidate(t);
     return TCI_OK;
@@ -567,7 +589,7 @@ int tci_tci2_indexset(tci_tci2 t, int which, int site, int32_t* h_rows, int64_t*
     return TCI_OK;
 }
 
-int tci_tci2_set_maxsamplevalue(tci_tci2 t, double v) { if (!t) return TCI_ERR_INVALID; t->maxsamplevalue = v; return TCI_OK; }
+int tci_tci2_set_maxsamplevalue(tci_tci2 t, double v) { if (!t) return TCI_ERR_INVALID; return set_maxsample(t, v); }
 
 int tci_tci2_updatepivots(tci_tci2 t, tci_functor f, int bond, int leftorthogonal, double reltol, double abstol, int64_t maxbonddim,
                           const int32_t* h_extraI, int64_t nextraI, const int32_t* h_extraJ, int64_t nextraJ) {
@@ -575,7 +597,9 @@ int tci_tci2_updatepivots(tci_tci2 t, tci_functor f, int bond, int leftorthogona
     IdxTable eI, eJ;
     eI.len = bond; eI.n = nextraI; if (nextraI > 0) eI.v.assign(h_extraI, h_extraI + (size_t)nextraI * eI.len);
     eJ.len = t->N - bond; eJ.n = nextraJ; if (nextraJ > 0) eJ.v.assign(h_extraJ, h_extraJ + (size_t)nextraJ * eJ.len);
-    return updatepivots(t, f, bond - 1, leftorthogonal != 0, reltol, abstol, maxbonddim, nextraI ? &eI : nullptr, nextraJ ? &eJ : nullptr);
+    int rc = updatepivots(t, f, bond - 1, leftorthogonal != 0, reltol, abstol, maxbonddim, nextraI ? &eI : nullptr, nextraJ ? &eJ : nullptr);
+    if (rc) return rc;
+    return sync_maxsample(t);
 }
 
 int tci_tci2_sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, int64_t maxbonddim, int sweepstrategy,
@@ -596,7 +620,8 @@ int tci_tci2_makecanonical(tci_tci2 t, tci_functor f, double reltol, double abst
 
 int tci_tci2_fillsitetensors(tci_tci2 t, tci_functor f) {
     if (!t || !f) return TCI_ERR_INVALID;
-    return fillsitetensors(t, f);
+    int rc = fillsitetensors(t, f); if (rc) return rc;
+    return sync_maxsample(t);
 }
 
 int tci_tci2_optimize(tci_tci2 t, tci_functor f, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,

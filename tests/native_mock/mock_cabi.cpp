@@ -68,6 +68,28 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
     return TCI_OK;
 }
 
+struct MockAcc { double mx; int nan; int pad; };         // same 16 bytes as the device accumulator: bits of the maximum, NaN flag
+
+int tci_maxacc_set(tci_handle, void* acc, double v) {
+    MockAcc* a = (MockAcc*)acc; a->mx = 0.0; a->nan = 0; a->pad = 0;
+    if (v != v) a->nan = 1; else a->mx = std::fabs(v);
+    return TCI_OK;
+}
+int tci_maxacc_get(tci_handle, const void* acc, double* out) {
+    const MockAcc* a = (const MockAcc*)acc;
+    *out = a->nan ? NAN : a->mx;
+    return TCI_OK;
+}
+int tci_batcheval_acc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites, const int32_t* h_left, int64_t nleft, int nl,
+                          const int32_t* h_right, int64_t nright, int nr, double* d_out, int64_t stride_c, int64_t stride_j, void* acc) {
+    MockAcc* a = (MockAcc*)acc;
+    double m = a->nan ? NAN : a->mx;
+    const int rc = tci_batcheval_f64(h, f, h_localdims, nsites, h_left, nleft, nl, h_right, nright, nr, d_out, stride_c, stride_j, &m);
+    if (rc) return rc;
+    if (m != m) a->nan = 1; else a->mx = m;
+    return TCI_OK;
+}
+
 int tci_rrlu_inplace_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol, double abstol,
                          int leftorthogonal, int64_t* h_rowperm, int64_t* h_colperm, int64_t* h_npivot, double* h_error, double* d_L,
                          int64_t ldl, double* d_U, int64_t ldu, double* h_pivoterrors) {
