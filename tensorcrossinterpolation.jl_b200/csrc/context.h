@@ -30,6 +30,7 @@ struct tci_context {
     double rrlu_ms[3] = {0, 0, 0};
     int64_t rrlu_steps = 0;
     int rrlu_smem_optin = 0;                // the single-CTA kernel's > 48 KB dynamic shared memory has been enabled
+    int solve_smem_optin = 0;               // the small-solve kernel's > 48 KB dynamic shared memory has been enabled
     int rrlu_pdl = 1;                       // programmatic dependent launch between the step kernels (TCI_RRLU_PDL=0 disables)
     int rrlu_late_state = 1;                // single-CTA kernel: read the final state once, in rrlu_finish (TCI_RRLU_LATE_STATE=0: twice)
     int rrlu_profile = 0;                   // 1: bracket every update-kernel launch with events

@@ -84,7 +84,7 @@ def test_luci_golden(tci, literals):                     # test/test_matrixluci.
     _close(luci.left() @ luci.right(), A3, 1e-11)
 
 
-@pytest.mark.parametrize("q,r", [(1, 1), (30, 7), (200, 64), (5120, 256)])
+@pytest.mark.parametrize("q,r", [(1, 1), (30, 7), (129, 33), (1000, 40), (200, 64), (300, 65), (5120, 256)])
 def test_solve_right(tci, q, r):                         # tensorci2.jl:626
     rng = np.random.default_rng(q + r)
     P = rng.standard_normal((r, r)) + 3.0 * np.eye(r)
@@ -95,6 +95,28 @@ def test_solve_right(tci, q, r):                         # tensorci2.jl:626
     ref = O.solve_right(P, B)
     _close(X, ref, 1e-12 * np.linalg.cond(P))
     _close(X @ P, B, 1e-12 * np.linalg.cond(P))
+
+
+def test_solve_right_small_kernel_cases(tci):
+    """The one-launch path for pivot matrices up to 64 x 64: padded leading dimensions, a badly scaled P (full pivoting),
+    exact singularity reported like the general path, and agreement with that path (TCI_SOLVE_SMALL is read once per process,
+    so the general path is reached through r = 65 above and through the factor identities here)."""
+    h = tci.default_handle()
+    dev = f"cuda:{h.device}"
+    rng = np.random.default_rng(11)
+    q, r = 77, 20
+    P = rng.standard_normal((r, r)) * np.logspace(0, -9, r)[None, :]          # columns scaled over nine decades
+    B = rng.standard_normal((q, r))
+    X = tci.solve_right(h, tci.Mat.from_numpy(B, dev, pad=16), tci.Mat.from_numpy(P, dev, pad=16)).numpy()
+    _close(X @ P, B, 1e-12 * r)                                               # backward error: small whatever cond(P) is
+    Ps = P.copy(); Ps[:, 3] = Ps[:, 5]                                        # two equal columns: exactly singular
+    with pytest.raises(tci.TCIError, match="singular"):
+        tci.solve_right(h, tci.Mat.from_numpy(B, dev), tci.Mat.from_numpy(Ps, dev))
+    Pn = P.copy(); Pn[2, 2] = np.nan
+    try:                                                                      # NaN input must not hang or crash; either outcome is
+        tci.solve_right(h, tci.Mat.from_numpy(B, dev), tci.Mat.from_numpy(Pn, dev))   # an error or a NaN-carrying result
+    except tci.TCIError:
+        pass
 
 
 def test_tt_sum_and_evaluate(tci):                       # test/test_tensortrain.jl:10-32
