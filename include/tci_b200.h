@@ -280,6 +280,9 @@ int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const in
  * (every number still comes from those kernels; pivotsearch = :full only).  Sites and bonds are 1-based, index values
  * 1-based; maxbonddim <= 0 means unbounded (typemax(Int)).  sweepstrategy: 0 :forward, 1 :backandforth, 2 :backward
  * (src/sweepstrategies.jl:41-50).  The message of the last failure on an object is tci_tci2_last_error(t). */
+/* optfirstpivot(f, localdims, firstpivot; maxsweep) src/util.jl:260-291: h_pivot (nsites, 1-based) is improved in place by a
+ * greedy one-site-at-a-time search for a large |f| (one batch evaluation per site). */
+int tci_optfirstpivot_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites, int32_t* h_pivot, int maxsweep);
 typedef struct tci_tci2_s* tci_tci2;
 int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tci2* out);       /* TensorCI2{V}(localdims) :95-103 */
 int tci_tci2_destroy(tci_tci2 t);

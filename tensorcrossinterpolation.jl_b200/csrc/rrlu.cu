@@ -349,7 +349,8 @@ __global__ void rrlu_swap_kernel(double* __restrict__ A, int m, int n, long long
 // two kernel launches or two grid barriers.  Same arithmetic (mul_rn/sub_rn, IEEE division) and same tie rule.
 constexpr int kSmemThreads = 1024;
 
-__device__ __forceinline__ Cand block_reduce_1024(Cand c, Cand* smem /* 32 entries */) {
+template <int NW>
+__device__ __forceinline__ Cand block_reduce_all(Cand c, Cand* smem /* 32 entries */) {
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         Cand o = cand_shfl_down(c, d);
@@ -358,7 +359,7 @@ __device__ __forceinline__ Cand block_reduce_1024(Cand c, Cand* smem /* 32 entri
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) smem[warp] = c;
     __syncthreads();
-    c = smem[lane];                                       // every warp reduces the 32 partials redundantly: no broadcast step
+    c = (lane < NW) ? smem[lane] : Cand{0.0, -1, -1};     // every warp reduces the NW partials redundantly: no broadcast step
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         Cand o;
@@ -369,25 +370,28 @@ __device__ __forceinline__ Cand block_reduce_1024(Cand c, Cand* smem /* 32 entri
     return c;                                             // valid in every thread
 }
 
-__global__ void __launch_bounds__(kSmemThreads, 1)
+// NT threads: 1024 in general; 256 for matrices of at most 64 x 64 elements' worth of work, where 8 warps cover the columns
+// and every __syncthreads is several times cheaper (the quantics configs: Pi <= 34 x 34, ~430 factorisations per run).
+template <int NT>
+__global__ void __launch_bounds__(NT, 1)
 rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState* st, int* rowperm, int* colperm,
                  double* pivvals, int maxrank, double reltol, double abstol, int leftorth) {
     extern __shared__ double S[];                         // m x n, column-major, leading dimension lds (odd: conflict-free rows)
     __shared__ Cand s_c[32];
     const int lds = m | 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int j = warp; j < n; j += 32)
+    for (int j = warp; j < n; j += NT / 32)
         for (int i = lane; i < m; i += 32) S[j * lds + i] = A[(long long)j * lda + i];
-    for (int t = tid; t < m; t += kSmemThreads) rowperm[t] = t;
-    for (int t = tid; t < n; t += kSmemThreads) colperm[t] = t;
+    for (int t = tid; t < m; t += NT) rowperm[t] = t;
+    for (int t = tid; t < n; t += NT) colperm[t] = t;
     __syncthreads();
     int np = 0;
     double maxerror = 0.0, error = nan("");
     double bv = -INFINITY, bx = 0.0; int bi = -1, bj = -1;
-    for (int j = warp; j < n; j += 32)
+    for (int j = warp; j < n; j += NT / 32)
         for (int i = lane; i < m; i += 32) { const double v = S[j * lds + i]; const double q = __dmul_rn(v, v); TCI_CONSIDER(q, v, i, j) }
     for (;;) {
-        Cand best = block_reduce_1024(Cand{bx, bi, bj}, s_c);
+        Cand best = block_reduce_all<NT / 32>(Cand{bx, bi, bj}, s_c);
         if (best.i < 0) { best.i = np; best.j = np; best.x = nan(""); }
         const double err = fabs(best.x);                                        // :360
         error = err;
@@ -396,22 +400,22 @@ rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState*
         const int k = np, pr = best.i, pc = best.j;
         const double piv = best.x;
         // swaprow!(k, pr) over all columns, then swapcol!(k, pc) over all rows (:254-275, :297-298)
-        if (pr != k) for (int j = tid; j < n; j += kSmemThreads) { const double a = S[j * lds + k]; S[j * lds + k] = S[j * lds + pr]; S[j * lds + pr] = a; }
+        if (pr != k) for (int j = tid; j < n; j += NT) { const double a = S[j * lds + k]; S[j * lds + k] = S[j * lds + pr]; S[j * lds + pr] = a; }
         __syncthreads();
-        if (pc != k) for (int i = tid; i < m; i += kSmemThreads) { const double a = S[k * lds + i]; S[k * lds + i] = S[pc * lds + i]; S[pc * lds + i] = a; }
+        if (pc != k) for (int i = tid; i < m; i += NT) { const double a = S[k * lds + i]; S[k * lds + i] = S[pc * lds + i]; S[pc * lds + i] = a; }
         if (tid == 0) {
             int t = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = t;
             t = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = t;
             pivvals[k] = piv;
         }
         __syncthreads();
-        if (leftorth) { for (int i = k + 1 + tid; i < m; i += kSmemThreads) S[k * lds + i] = S[k * lds + i] / piv; }      // :303-305
-        else          { for (int j = k + 1 + tid; j < n; j += kSmemThreads) S[j * lds + k] = S[j * lds + k] / piv; }      // :307-309
+        if (leftorth) { for (int i = k + 1 + tid; i < m; i += NT) S[k * lds + i] = S[k * lds + i] / piv; }      // :303-305
+        else          { for (int j = k + 1 + tid; j < n; j += NT) S[j * lds + k] = S[j * lds + k] / piv; }      // :307-309
         __syncthreads();
         np = k + 1;
         if (np >= maxrank) break;                                               // :356
         bv = -INFINITY; bx = 0.0; bi = -1; bj = -1;
-        for (int j = np + warp; j < n; j += 32) {                               // :316-320 + the next search
+        for (int j = np + warp; j < n; j += NT / 32) {                               // :316-320 + the next search
             const double y = S[j * lds + k];
             for (int i = np + lane; i < m; i += 32) {
                 const double v = __dsub_rn(S[j * lds + i], __dmul_rn(S[k * lds + i], y));
@@ -422,7 +426,7 @@ rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState*
         }
     }
     __syncthreads();
-    for (int j = warp; j < n; j += 32)
+    for (int j = warp; j < n; j += NT / 32)
         for (int i = lane; i < m; i += 32) A[(long long)j * lda + i] = S[j * lds + i];
     if (tid == 0) { st->npivot = np; st->stop = 1; st->error = error; st->maxerror = maxerror; }
 }
@@ -1138,10 +1142,14 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     if (persistent) {
         if (in_smem) {
             if (smem_need > 48 * 1024 && !h->rrlu_smem_optin) {
-                TCI_CUDA(h, cudaFuncSetAttribute(rrlu_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                TCI_CUDA(h, cudaFuncSetAttribute(rrlu_smem_kernel<kSmemThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
                 h->rrlu_smem_optin = 1;
             }
-            rrlu_smem_kernel<<<1, kSmemThreads, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
+            static const bool tiny_off = getenv("TCI_RRLU_TINY") && atoi(getenv("TCI_RRLU_TINY")) == 0;
+            if ((long long)m * n <= 4096 && !tiny_off)
+                rrlu_smem_kernel<256><<<1, 256, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
+            else
+                rrlu_smem_kernel<kSmemThreads><<<1, kSmemThreads, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
             TCI_LAUNCH_CHECK(h);
         } else {
             rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);

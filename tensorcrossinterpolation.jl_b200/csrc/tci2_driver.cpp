@@ -514,6 +514,48 @@ int sanitycheck(tci_tci2 t) {                                                   
 
 extern "C" {
 
+// optfirstpivot (util.jl:260-291): greedy one-site-at-a-time search for a large |f|.  The d_i candidates of a site differ
+// only in coordinate i, so they go through ONE batch evaluation; keeping the first value that beats the current maximum is
+// exactly the reference's sequential strict-`>` scan.
+int tci_optfirstpivot_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites, int32_t* h_pivot, int maxsweep) {
+    if (!h || !f || !h_localdims || !h_pivot || nsites < 1) return TCI_ERR_INVALID;
+    int dmax = 1;
+    for (int b = 0; b < nsites; ++b) {
+        if (h_localdims[b] < 1 || h_pivot[b] < 1 || h_pivot[b] > h_localdims[b]) return TCI_ERR_INVALID;
+        dmax = std::max(dmax, (int)h_localdims[b]);
+    }
+    void* d_vals = nullptr;
+    int rc = tci_malloc(h, &d_vals, sizeof(double) * (size_t)dmax);
+    if (rc) return rc;
+    std::vector<double> vals((size_t)dmax);
+    std::vector<int32_t> pts((size_t)dmax * nsites);
+    auto eval = [&](int count) -> int {                 // the points are the left set, the right set is the empty index
+        int r = tci_batcheval_f64(h, f, h_localdims, nsites, pts.data(), count, nsites, nullptr, 1, 0, (double*)d_vals, 0, 0, nullptr);
+        if (r) return r;
+        return tci_memcpy_d2h(h, vals.data(), d_vals, sizeof(double) * (size_t)count);
+    };
+    std::memcpy(pts.data(), h_pivot, sizeof(int32_t) * nsites);
+    rc = eval(1);
+    double valf = std::fabs(vals[0]);
+    for (int sweep = 0; sweep < maxsweep && rc == TCI_OK; ++sweep) {
+        const double prev = valf;
+        for (int i = 0; i < nsites && rc == TCI_OK; ++i) {
+            const int d = h_localdims[i];
+            for (int v = 0; v < d; ++v) {
+                std::memcpy(pts.data() + (size_t)v * nsites, h_pivot, sizeof(int32_t) * nsites);
+                pts[(size_t)v * nsites + i] = v + 1;
+            }
+            rc = eval(d);
+            if (rc) break;
+            for (int v = 0; v < d; ++v)
+                if (std::fabs(vals[v]) > valf) { valf = std::fabs(vals[v]); h_pivot[i] = v + 1; }
+        }
+        if (prev == valf) break;
+    }
+    tci_free(h, d_vals);
+    return rc;
+}
+
 int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tci2* out) {
     if (!h || !h_localdims || !out || nsites < 2) return TCI_ERR_INVALID;                     // "localdims should have at least 2 elements!"
     for (int b = 0; b < nsites; ++b) if (h_localdims[b] < 1) return TCI_ERR_INVALID;

@@ -679,6 +679,11 @@ def optfirstpivot(f, localdims, firstpivot=None, maxsweep=1000):
     n = len(localdims)
     f = makebatchevaluatable(f, localdims)
     pivot = [1] * n if firstpivot is None else [int(v) for v in firstpivot]
+    if isinstance(f, BatchEvaluator) and getattr(f, "_f", None):            # device functor: the same scan as one C call
+        import ctypes as C
+        ld, pv = np.asarray(localdims, dtype=np.int32), np.asarray(pivot, dtype=np.int32)
+        f.handle.check(_lib.lib().tci_optfirstpivot_f64(f.handle.h, f._f, _lib.p_i32(ld), n, _lib.p_i32(pv), C.c_int(int(maxsweep))))
+        return [int(v) for v in pv]
     valf = abs(f(pivot))
     for _ in range(maxsweep):
         valf_prev = valf

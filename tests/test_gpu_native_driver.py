@@ -217,3 +217,13 @@ def test_device_max_accumulator(tci):
                                     C.c_void_p(out.data_ptr()), C.c_int64(0), C.c_int64(0), C.c_void_p(acc.data_ptr())))
     h.check(L.tci_maxacc_get(h.h, C.c_void_p(acc.data_ptr()), C.byref(got)))
     assert np.isnan(got.value)
+
+
+def test_optfirstpivot_native(tci):                        # util.jl:260-291; device functors take the one-call path
+    rng = np.random.default_rng(8)
+    ld = [5, 3, 7, 2, 6, 4]
+    f, g = tci.HashFunction(ld, 1.0, 0.3), O.Func(O.F_HASH, [1.0, 0.3])
+    for _ in range(4):
+        first = [int(rng.integers(1, d + 1)) for d in ld]
+        assert tci.optfirstpivot(f, ld, first) == list(O.optfirstpivot(g, ld, first))
+    assert tci.optfirstpivot(tci.SumFunction([3, 4, 5, 6]), [3, 4, 5, 6], [1, 2, 1, 2]) == [3, 4, 5, 6]

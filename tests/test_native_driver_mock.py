@@ -185,3 +185,19 @@ def test_errors_mirror_the_reference(mock):
     t2.set_indexset(0, 2, [[1], [2]])                       # |Iset[2]| = 2 but |Jset[1]| = 1: not square
     with pytest.raises(TCIError, match="Pivot matrix at bond 1 is not square!"):
         t2.fillsitetensors(g.h)
+
+
+def test_optfirstpivot_identical_to_oracle(mock):          # util.jl:260-291 through tci_optfirstpivot_f64
+    from tci_b200._lib import p_i32
+    L, h = mock
+    rng = np.random.default_rng(3)
+    for kind, params, ld in [(O.F_HASH, [1.0, 0.3], [5, 3, 7, 2, 6, 4]), (O.F_QEXPSIN, [10.0, 100.0, 1.1], [2] * 20),
+                             (O.F_SUM, [1.0], [3, 4, 5, 6])]:
+        f = O.Func(kind, params)
+        for _ in range(3):
+            first = [int(rng.integers(1, d + 1)) for d in ld]
+            pv = np.asarray(first, dtype=np.int32)
+            lda = np.asarray(ld, dtype=np.int32)
+            assert L.tci_optfirstpivot_f64(h, f.h, p_i32(lda), len(ld), p_i32(pv), 1000) == 0
+            assert pv.tolist() == list(O.optfirstpivot(f, ld, first))
+    assert pv.tolist() == [3, 4, 5, 6]                     # test/test_util.jl:28-36: the maximum of sum(v) is the all-d corner
