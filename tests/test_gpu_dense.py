@@ -110,7 +110,7 @@ def test_solve_right_small_kernel_cases(tci):
     X = tci.solve_right(h, tci.Mat.from_numpy(B, dev, pad=16), tci.Mat.from_numpy(P, dev, pad=16)).numpy()
     resid = np.abs(X @ P - B)                                                 # backward error: small against |X| |P| whatever cond(P) is
     assert np.max(resid / (np.abs(X) @ np.abs(P))) < 1e-13 * r
-    Ps = P.copy(); Ps[:, 3] = Ps[:, 5]                                        # two equal columns: exactly singular
+    Ps = P.copy(); Ps[:, 3] = 0.0                                             # a zero column stays exactly zero: singular
     with pytest.raises(tci.TCIError, match="singular"):
         tci.solve_right(h, tci.Mat.from_numpy(B, dev), tci.Mat.from_numpy(Ps, dev))
     Pn = P.copy(); Pn[2, 2] = np.nan
