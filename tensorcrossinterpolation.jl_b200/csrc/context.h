@@ -31,6 +31,7 @@ struct tci_context {
     int64_t rrlu_steps = 0;
     int rrlu_smem_optin = 0;                // the single-CTA kernel's > 48 KB dynamic shared memory has been enabled
     int solve_smem_optin = 0;               // the small-solve kernel's > 48 KB dynamic shared memory has been enabled
+    int rrlu_extracted = 0;                 // the last rrlu_run already wrote L and U (single-CTA kernel): rrlu_finish skips its launch
     int rrlu_pdl = 1;                       // programmatic dependent launch between the step kernels (TCI_RRLU_PDL=0 disables)
     int rrlu_late_state = 1;                // single-CTA kernel: read the final state once, in rrlu_finish (TCI_RRLU_LATE_STATE=0: twice)
     int rrlu_profile = 0;                   // 1: bracket every update-kernel launch with events

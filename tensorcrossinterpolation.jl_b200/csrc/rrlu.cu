@@ -374,16 +374,22 @@ __device__ __forceinline__ Cand block_reduce_all(Cand c, Cand* smem /* 32 entrie
 // and every __syncthreads is several times cheaper (the quantics configs: Pi <= 34 x 34, ~430 factorisations per run).
 template <int NT>
 __global__ void __launch_bounds__(NT, 1)
-rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState* st, int* rowperm, int* colperm,
-                 double* pivvals, int maxrank, double reltol, double abstol, int leftorth) {
+rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState* st, int* g_rowperm, int* g_colperm,
+                 double* pivvals, int maxrank, double reltol, double abstol, int leftorth,
+                 double* __restrict__ L, long long ldl, double* __restrict__ U, long long ldu, int extract) {
     extern __shared__ double S[];                         // m x n, column-major, leading dimension lds (odd: conflict-free rows)
     __shared__ Cand s_c[32];
     const int lds = m | 1;
+    // the permutations live in shared memory too (after S): thread 0 swaps two entries of each per pivot, and a global
+    // round trip there would sit on the critical path of every step
+    int* rowperm = (int*)(S + (size_t)lds * n);
+    int* colperm = rowperm + m;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int j = warp; j < n; j += NT / 32)
         for (int i = lane; i < m; i += 32) S[j * lds + i] = A[(long long)j * lda + i];
     for (int t = tid; t < m; t += NT) rowperm[t] = t;
     for (int t = tid; t < n; t += NT) colperm[t] = t;
+    if (tid == 0) st->flags = 0;                          // this kernel needs no rrlu_init_kernel before it
     __syncthreads();
     int np = 0;
     double maxerror = 0.0, error = nan("");
@@ -428,7 +434,30 @@ rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState*
     __syncthreads();
     for (int j = warp; j < n; j += NT / 32)
         for (int i = lane; i < m; i += 32) A[(long long)j * lda + i] = S[j * lds + i];
+    for (int t = tid; t < m; t += NT) g_rowperm[t] = rowperm[t];
+    for (int t = tid; t < n; t += NT) g_colperm[t] = colperm[t];
     if (tid == 0) { st->npivot = np; st->stop = 1; st->error = error; st->maxerror = maxerror; }
+    if (extract) {
+        // L = tril(A[:, 1:r]), U = triu(A[1:r, :]), NaN flags, unit diagonal (:372-388): what rrlu_extract_kernel does, from
+        // shared memory, so the small-matrix path is ONE launch
+        const int r = np;
+        int flags = 0;
+        for (int j = warp; j < r; j += NT / 32)
+            for (int i = lane; i < m; i += 32) {
+                double v = (i >= j) ? S[j * lds + i] : 0.0;
+                if (isnan(v)) flags |= 1;
+                if (i == j && leftorth) v = 1.0;
+                if (L) L[(long long)j * ldl + i] = v;
+            }
+        for (int j = warp; j < n; j += NT / 32)
+            for (int i = lane; i < r; i += 32) {
+                double v = (j >= i) ? S[j * lds + i] : 0.0;
+                if (isnan(v)) flags |= 2;
+                if (i == j && !leftorth) v = 1.0;
+                if (U) U[(long long)j * ldu + i] = v;
+            }
+        if (flags) atomicOr(&st->flags, flags);
+    }
 }
 
 // ---- persistent variant: the whole loop of _optimizerrlu! (:346-369) in ONE cooperative launch ---------------------
@@ -1112,7 +1141,9 @@ __global__ void rrlu_dist_extract_kernel(DistArrays a, const double* __restrict_
 
 // Shared driver: factorises d_A in place, leaves perms/pivot values in ws_small, reads the final state.
 static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int mr, double reltol, double abstol,
-                    int leftorth, SmallWs* w, RrluState* final_state) {
+                    int leftorth, SmallWs* w, RrluState* final_state,
+                    double* d_L = nullptr, long long ldl = 0, double* d_U = nullptr, long long ldu = 0, bool may_extract = false) {
+    h->rrlu_extracted = 0;
     const bool vec = (lda % 2 == 0) && (((uintptr_t)d_A & 15u) == 0);
     const UpdateCfg cfg = update_cfg(h, vec);
     const int grid = cfg.grid;
@@ -1125,9 +1156,6 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
         if (rc) return rc;
     }
     const int mx = m > n ? m : n;
-    rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n, w->bar);
-    TCI_LAUNCH_CHECK(h);
-    TCI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
     RrluState* hst = (RrluState*)h->pinned;
     // One cooperative launch for the whole loop when the matrix is L2-resident (launch/latency-bound regime);
     // step kernels when it streams from HBM (their launch gaps overlap, a grid barrier's do not).
@@ -1136,9 +1164,14 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     if (h->rrlu_profile) persistent = false;                // per-launch profiling needs the step kernels
     if (const char* e = getenv("TCI_RRLU_PDL")) h->rrlu_pdl = atoi(e) ? 1 : 0;
     if (const char* e = getenv("TCI_RRLU_LATE_STATE")) h->rrlu_late_state = atoi(e) ? 1 : 0;
-    const size_t smem_need = sizeof(double) * (size_t)(m | 1) * n;
+    const size_t smem_need = sizeof(double) * (size_t)(m | 1) * n + sizeof(int) * (((size_t)m + n + 1) & ~(size_t)1);   // matrix + permutations
     bool in_smem = persistent && smem_need <= 200 * 1024;
     if (const char* e = getenv("TCI_RRLU_SMEM")) in_smem = in_smem && atoi(e) != 0;
+    if (!in_smem) {                                         // the single-CTA kernel initialises its own state
+        rrlu_init_kernel<<<(mx + 255) / 256, 256, 0, h->stream>>>(w->st, w->rowperm, w->colperm, m, n, w->bar);
+        TCI_LAUNCH_CHECK(h);
+    }
+    TCI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
     if (persistent) {
         if (in_smem) {
             if (smem_need > 48 * 1024 && !h->rrlu_smem_optin) {
@@ -1146,11 +1179,13 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
                 h->rrlu_smem_optin = 1;
             }
             static const bool tiny_off = getenv("TCI_RRLU_TINY") && atoi(getenv("TCI_RRLU_TINY")) == 0;
-            if ((long long)m * n <= 4096 && !tiny_off)
-                rrlu_smem_kernel<256><<<1, 256, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
+            const int extract = may_extract ? 1 : 0;       // L/U straight from shared memory: no separate extraction launch
+            if ((long long)m * n <= 4096 && smem_need <= 48 * 1024 && !tiny_off)
+                rrlu_smem_kernel<256><<<1, 256, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth, d_L, ldl, d_U, ldu, extract);
             else
-                rrlu_smem_kernel<kSmemThreads><<<1, kSmemThreads, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth);
+                rrlu_smem_kernel<kSmemThreads><<<1, kSmemThreads, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth, d_L, ldl, d_U, ldu, extract);
             TCI_LAUNCH_CHECK(h);
+            h->rrlu_extracted = extract;
         } else {
             rc = launch_persistent(h, vec, cfg, d_A, m, n, lda, *w, mr, reltol, abstol, leftorth);
             if (rc) return rc;
@@ -1259,7 +1294,7 @@ static int rrlu_finish(tci_handle h, const double* d_A, int m, int n, long long 
                        double* d_L, long long ldl, double* d_U, long long ldu, double* h_pivoterrors) {
     const bool late = fs->npivot < 0;                       // rrlu_run left the state on the device (see there)
     int r = late ? mr : fs->npivot;                         // late: an upper bound, the kernel reads the count itself
-    if (r > 0) {
+    if (r > 0 && !h->rrlu_extracted) {
         const long long work = (long long)m * r + (long long)r * n;
         long long blocks = (work + 255) / 256;
         if (blocks > h->num_sms * 8) blocks = h->num_sms * 8;
@@ -1333,7 +1368,7 @@ int tci_rrlu_inplace_f64(tci_handle h, double* d_A, int64_t m, int64_t n, int64_
     if (d_L && ldl < m) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_inplace_f64: ldl < m");
     if (d_U && ldu < mr) return tci_fail(h, TCI_ERR_INVALID, "tci_rrlu_inplace_f64: ldu < min(maxrank, m, n)");
     SmallWs w; RrluState fs;
-    rc = rrlu_run(h, d_A, (int)m, (int)n, lda, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
+    rc = rrlu_run(h, d_A, (int)m, (int)n, lda, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs, d_L, ldl, d_U, ldu, true);
     if (rc) return rc;
     return rrlu_finish(h, d_A, (int)m, (int)n, lda, leftorthogonal ? 1 : 0, w, &fs, (int)mr, h_rowperm, h_colperm, h_npivot, h_error,
                        d_L, ldl, d_U, ldu, h_pivoterrors);
@@ -1365,7 +1400,8 @@ int tci_rrlu_host_f64(tci_handle h, const double* h_A, int64_t m, int64_t n, int
         dL = (double*)h->ws_lu.ptr; dU = dL + (size_t)m * mr;
     }
     SmallWs w; RrluState fs;
-    rc = rrlu_run(h, dA, (int)m, (int)n, ldw, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs);
+    rc = rrlu_run(h, dA, (int)m, (int)n, ldw, (int)mr, reltol, abstol, leftorthogonal ? 1 : 0, &w, &fs, h_L ? dL : nullptr, m,
+                  h_U ? dU : nullptr, mr, true);
     if (rc) return rc;
     rc = rrlu_finish(h, dA, (int)m, (int)n, ldw, leftorthogonal ? 1 : 0, w, &fs, (int)mr, h_rowperm, h_colperm, h_npivot, h_error,
                      h_L ? dL : nullptr, m, h_U ? dU : nullptr, mr, h_pivoterrors);

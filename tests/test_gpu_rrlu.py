@@ -44,7 +44,8 @@ def test_golden_literals(tci, literals):
     assert tci.rrlu(A).npivot == 1
 
 
-@pytest.mark.parametrize("shape", [(1, 1), (1, 7), (9, 1), (33, 65), (257, 130), (513, 515), (700, 300), (1025, 1024)])
+@pytest.mark.parametrize("shape", [(1, 1), (1, 7), (9, 1), (33, 65), (64, 64), (34, 34), (4096, 1), (1, 4096), (3000, 8), (8, 3100),
+                                   (257, 130), (513, 515), (700, 300), (1025, 1024)])
 @pytest.mark.parametrize("lo", [True, False])
 def test_random_shapes(tci, shape, lo):
     rng = np.random.default_rng(shape[0] * 1000 + shape[1])
