@@ -460,6 +460,140 @@ rrlu_smem_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState*
     }
 }
 
+// Second generation of the single-CTA kernel: TWO block barriers per pivot instead of six.  The first generation follows the
+// reference phase by phase (search | swap rows | swap columns | scale | update), each phase waiting for the previous one
+// through __syncthreads, and at ~0.5 us per phase that chain IS the run time of a small factorisation.  Here, once the pivot
+// (pr, pc) is known, one short phase copies what the swaps would overwrite — old row k and old column k — and forms the final
+// pivot column and row (already swapped, the column or row already divided by the pivot); after ONE barrier a single pass
+// writes every element its final value: moved rows/columns come from the copies, the trailing block gets
+// final(i, j) = old(sigma(i), tau(j)) - Lk[i] * Uk[j]  (sigma, tau = the two transpositions) and is searched for the next
+// pivot on the way.  Operands and operations per element are exactly those of the first generation, so results stay bit-identical.
+template <int NT>
+__global__ void __launch_bounds__(NT, 1)
+rrlu_smem2_kernel(double* __restrict__ A, int m, int n, long long lda, RrluState* st, int* g_rowperm, int* g_colperm,
+                  double* pivvals, int maxrank, double reltol, double abstol, int leftorth,
+                  double* __restrict__ L, long long ldl, double* __restrict__ U, long long ldu, int extract) {
+    extern __shared__ double S[];                         // m x n, column-major, leading dimension lds
+    __shared__ Cand s_c[2][32];                           // double-buffered by step parity: no barrier to protect its reuse
+    const int lds = m | 1;
+    double* Lk = S + (size_t)lds * n;                     // final column k (all rows; rows > k scaled when leftorthogonal)
+    double* Uk = Lk + m;                                  // final row k (all columns; columns > k scaled otherwise)
+    double* colK = Uk + n;                                // old column k
+    double* rowK = colK + m;                              // old row k
+    int* rowperm = (int*)(rowK + n);
+    int* colperm = rowperm + m;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = NT / 32;
+    for (int j = warp; j < n; j += NW)
+        for (int i = lane; i < m; i += 32) S[j * lds + i] = A[(long long)j * lda + i];
+    for (int t = tid; t < m; t += NT) rowperm[t] = t;
+    for (int t = tid; t < n; t += NT) colperm[t] = t;
+    if (tid == 0) st->flags = 0;
+    __syncthreads();
+    int np = 0;
+    double maxerror = 0.0, error = nan("");
+    double bv = -INFINITY, bx = 0.0; int bi = -1, bj = -1;
+    for (int j = warp; j < n; j += NW)
+        for (int i = lane; i < m; i += 32) { const double v = S[j * lds + i]; const double q = __dmul_rn(v, v); TCI_CONSIDER(q, v, i, j) }
+    for (;;) {
+        // ---- reduce the per-thread candidates; every thread ends up with the winner (barrier 1)
+        Cand c{bx, bi, bj};
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) { Cand o = cand_shfl_down(c, d); if (cand_better(o, c)) c = o; }
+        Cand* sc = s_c[np & 1];
+        if (lane == 0) sc[warp] = c;
+        __syncthreads();
+        Cand best = (lane < NW) ? sc[lane] : Cand{0.0, -1, -1};
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            Cand o;
+            o.x = __shfl_xor_sync(0xffffffffu, best.x, d); o.i = __shfl_xor_sync(0xffffffffu, best.i, d); o.j = __shfl_xor_sync(0xffffffffu, best.j, d);
+            if (cand_better(o, best)) best = o;
+        }
+        if (best.i < 0) { best.i = np; best.j = np; best.x = nan(""); }
+        const double err = fabs(best.x);                                        // :360
+        error = err;
+        if ((err < reltol * maxerror || err < abstol) && np > 0) break;         // :363
+        maxerror = jl_max(maxerror, err);                                       // :367
+        const int k = np, pr = best.i, pc = best.j;
+        const double piv = best.x;
+        // ---- save what the swaps overwrite, form the final pivot column and row (barrier 2)
+        for (int t = tid; t < m + n; t += NT) {
+            if (t < m) {
+                const int i = t, si = (i == k) ? pr : ((i == pr) ? k : i);      // sigma: rows k <-> pr
+                colK[i] = S[k * lds + i];
+                const double v = S[pc * lds + si];                              // final column k = old column pc, rows swapped
+                Lk[i] = (leftorth && i > k) ? v / piv : v;                      // :303-305
+            } else {
+                const int j = t - m, tj = (j == k) ? pc : ((j == pc) ? k : j);  // tau: columns k <-> pc
+                rowK[j] = S[j * lds + k];
+                const double v = S[tj * lds + pr];                              // final row k = old row pr, columns swapped
+                Uk[j] = (!leftorth && j > k) ? v / piv : v;                     // :307-309
+            }
+        }
+        if (tid == 0) {
+            int t = rowperm[k]; rowperm[k] = rowperm[pr]; rowperm[pr] = t;
+            t = colperm[k]; colperm[k] = colperm[pc]; colperm[pc] = t;
+            pivvals[k] = piv;
+        }
+        __syncthreads();
+        np = k + 1;
+        const bool last = np >= maxrank;                                        // :356: swaps and scaling still happen, the update does not
+        // ---- one pass: every element gets its final value
+        for (int t = tid; t < m + n; t += NT) {
+            if (t < m) {
+                const int i = t;
+                S[k * lds + i] = Lk[i];                                         // column k, all rows
+                if (pc != k && i < k) S[pc * lds + i] = colK[i];                // column pc above the pivot row: old column k
+            } else {
+                const int j = t - m;
+                if (j != k) S[j * lds + k] = Uk[j];                             // row k, all other columns
+                if (pr != k && j < k) S[j * lds + pr] = rowK[j];                // row pr left of the pivot column: old row k
+            }
+        }
+        bv = -INFINITY; bx = 0.0; bi = -1; bj = -1;
+        for (int j = np + warp; j < n; j += NW) {                               // trailing block: :316-320 + the next search
+            const double y = Uk[j];
+            const int tj = (j == pc) ? k : j;
+            for (int i = np + lane; i < m; i += 32) {
+                // value at (i, j) after the swaps: old(sigma(i), tau(j)); only row pr and column pc actually moved
+                const double a = (i == pr) ? rowK[tj] : ((j == pc) ? colK[i] : S[j * lds + i]);
+                if (last) { S[j * lds + i] = a; continue; }
+                const double v = __dsub_rn(a, __dmul_rn(Lk[i], y));
+                S[j * lds + i] = v;
+                const double q = __dmul_rn(v, v);
+                TCI_CONSIDER(q, v, i, j)
+            }
+        }
+        if (last) break;
+    }
+    __syncthreads();
+    for (int j = warp; j < n; j += NW)
+        for (int i = lane; i < m; i += 32) A[(long long)j * lda + i] = S[j * lds + i];
+    for (int t = tid; t < m; t += NT) g_rowperm[t] = rowperm[t];
+    for (int t = tid; t < n; t += NT) g_colperm[t] = colperm[t];
+    if (tid == 0) { st->npivot = np; st->stop = 1; st->error = error; st->maxerror = maxerror; }
+    if (extract) {
+        const int r = np;
+        int flags = 0;
+        for (int j = warp; j < r; j += NW)
+            for (int i = lane; i < m; i += 32) {
+                double v = (i >= j) ? S[j * lds + i] : 0.0;
+                if (isnan(v)) flags |= 1;
+                if (i == j && leftorth) v = 1.0;
+                if (L) L[(long long)j * ldl + i] = v;
+            }
+        for (int j = warp; j < n; j += NW)
+            for (int i = lane; i < r; i += 32) {
+                double v = (j >= i) ? S[j * lds + i] : 0.0;
+                if (isnan(v)) flags |= 2;
+                if (i == j && !leftorth) v = 1.0;
+                if (U) U[(long long)j * ldu + i] = v;
+            }
+        if (flags) atomicOr(&st->flags, flags);
+    }
+}
+
 // ---- persistent variant: the whole loop of _optimizerrlu! (:346-369) in ONE cooperative launch ---------------------
 // Per pivot step: [every block reduces the per-block candidates and evaluates the stop rule redundantly] ->
 // swap/scale phase spread over the grid -> grid barrier -> update + next search -> grid barrier.  No launch gaps,
@@ -1174,12 +1308,26 @@ static int rrlu_run(tci_handle h, double* d_A, int m, int n, long long lda, int 
     TCI_CUDA(h, cudaEventRecord(h->ev[0], h->stream));
     if (persistent) {
         if (in_smem) {
-            if (smem_need > 48 * 1024 && !h->rrlu_smem_optin) {
+            if (smem_need > 48 * 1024 && !(h->rrlu_smem_optin & 1)) {
                 TCI_CUDA(h, cudaFuncSetAttribute(rrlu_smem_kernel<kSmemThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-                h->rrlu_smem_optin = 1;
+                h->rrlu_smem_optin |= 1;
             }
             static const bool tiny_off = getenv("TCI_RRLU_TINY") && atoi(getenv("TCI_RRLU_TINY")) == 0;
             const int extract = may_extract ? 1 : 0;       // L/U straight from shared memory: no separate extraction launch
+            // second-generation kernel (two barriers per pivot) when its four extra vectors fit as well
+            const size_t smem2 = smem_need + sizeof(double) * 2 * ((size_t)m + n);
+            static const bool gen2_off = getenv("TCI_RRLU_SMEM2") && atoi(getenv("TCI_RRLU_SMEM2")) == 0;
+            if (!gen2_off && smem2 <= 200 * 1024) {
+                const bool tiny = (long long)m * n <= 4096 && smem2 <= 48 * 1024 && !tiny_off;
+                if (!tiny && smem2 > 48 * 1024 && !(h->rrlu_smem_optin & 2)) {
+                    TCI_CUDA(h, cudaFuncSetAttribute(rrlu_smem2_kernel<kSmemThreads>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    h->rrlu_smem_optin |= 2;
+                }
+                if (tiny)
+                    rrlu_smem2_kernel<256><<<1, 256, smem2, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth, d_L, ldl, d_U, ldu, extract);
+                else
+                    rrlu_smem2_kernel<kSmemThreads><<<1, kSmemThreads, smem2, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth, d_L, ldl, d_U, ldu, extract);
+            } else
             if ((long long)m * n <= 4096 && smem_need <= 48 * 1024 && !tiny_off)
                 rrlu_smem_kernel<256><<<1, 256, smem_need, h->stream>>>(d_A, m, n, lda, w->st, w->rowperm, w->colperm, w->pivvals, mr, reltol, abstol, leftorth, d_L, ldl, d_U, ldu, extract);
             else
