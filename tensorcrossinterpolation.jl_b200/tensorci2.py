@@ -712,6 +712,18 @@ _NATIVE_KW = {"tolerance", "maxbonddim", "maxiter", "sweepstrategy", "normalizee
               "loginterval", "checkbatchevaluatable"}
 
 
+def _native_eligible(f, kwargs):
+    """engine="auto": does the compiled driver cover this call?  Device functor evaluated by the stock batch path (wrappers
+    that override evaluate_batch — sharded, cached, contraction, host adapters — stay on the Python host), only keywords the
+    driver implements, full pivot search, nothing to print."""
+    return (isinstance(f, BatchEvaluator) and bool(getattr(f, "_f", None))
+            and type(f).evaluate_batch is BatchEvaluator.evaluate_batch
+            and set(kwargs) <= (_NATIVE_KW | {"handle"})
+            and kwargs.get("pivotsearch", "full") == "full"
+            and not kwargs.get("verbosity", 0)
+            and not kwargs.get("checkbatchevaluatable", False))
+
+
 def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs):
     """crossinterpolate2 with the whole optimize! loop run by the compiled sweep driver (csrc/tci2_driver.cpp, native.py): one
     C call instead of an interpreted host loop over bonds.  Same kernels, same order of operations; the result is handed
@@ -762,10 +774,13 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs)
 
 def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323.
-    `engine` (not in the reference): "python" (default) runs optimize! in this module, "native" hands the same loop to the
-    compiled sweep driver — fewer microseconds of host work per bond, identical kernels and results."""
+    `engine` (not in the reference): "native" hands the optimize! loop to the compiled sweep driver (fewer microseconds of host
+    work per bond, identical kernels and results), "python" runs it in this module; the default "auto" takes the compiled
+    driver whenever it covers the call (device functor, pivotsearch=:full, one GPU, no Python-side finder / rng / verbosity)."""
     seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): rook-search stream
-    engine = kwargs.pop("engine", "python")
+    engine = kwargs.pop("engine", "auto")
+    if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module
+        engine = "native" if _native_eligible(f, kwargs) else "python"
     if engine == "native":
         return _crossinterpolate2_native(f, localdims, initialpivots, seed, kwargs.pop("handle", None), kwargs)
     if engine != "python":

@@ -57,7 +57,7 @@ def test_native_identical_to_python_engine(tci, kw):
     n = 6
     f = tci.LorentzFunction([8] * n)
     a, ra, ea = tci.crossinterpolate2(f, [8] * n, tolerance=1e-7, nsearchglobalpivot=0, engine="native", **kw)
-    b, rb, eb = tci.crossinterpolate2(f, [8] * n, tolerance=1e-7, nsearchglobalpivot=0, **kw)
+    b, rb, eb = tci.crossinterpolate2(f, [8] * n, tolerance=1e-7, nsearchglobalpivot=0, engine="python", **kw)
     np.testing.assert_array_equal(ra, rb)
     np.testing.assert_array_equal(ea, eb)
     for s in range(n):
@@ -227,3 +227,22 @@ def test_optfirstpivot_native(tci):                        # util.jl:260-291; de
         first = [int(rng.integers(1, d + 1)) for d in ld]
         assert tci.optfirstpivot(f, ld, first) == list(O.optfirstpivot(g, ld, first))
     assert tci.optfirstpivot(tci.SumFunction([3, 4, 5, 6]), [3, 4, 5, 6], [1, 2, 1, 2]) == [3, 4, 5, 6]
+
+
+def test_engine_auto_selection(tci):
+    """engine="auto" (the default): the compiled driver for device functors with the stock keywords, the Python host otherwise."""
+    from tci_b200.tensorci2 import _native_eligible
+    f = tci.LorentzFunction([4] * 4)
+    assert _native_eligible(f, dict(tolerance=1e-8, nsearchglobalpivot=0))
+    assert _native_eligible(f, dict(tolerance=1e-8, maxbonddim=7, handle=None))
+    assert not _native_eligible(f, dict(pivotsearch="rook"))
+    assert not _native_eligible(f, dict(rng=np.random.default_rng(0)))
+    assert not _native_eligible(f, dict(verbosity=1))
+    assert not _native_eligible(f, dict(bondorder="oddeven"))
+    assert not _native_eligible(lambda v: 1.0, {})
+    assert not _native_eligible(tci.HostFunctionAdapter(lambda v: 1.0, [4] * 4), {})
+    assert not _native_eligible(tci.CachedFunction(lambda v: 1.0, [4] * 4), {})
+    t, _, _ = tci.crossinterpolate2(f, [4] * 4, tolerance=1e-8, nsearchglobalpivot=0)
+    assert "nbondupdates" in t.stats                        # ran in the compiled driver
+    t, _, _ = tci.crossinterpolate2(f, [4] * 4, tolerance=1e-8, nsearchglobalpivot=0, engine="python")
+    assert "nbondupdates" not in t.stats
