@@ -201,3 +201,63 @@ def test_optfirstpivot_identical_to_oracle(mock):          # util.jl:260-291 thr
             assert L.tci_optfirstpivot_f64(h, f.h, p_i32(lda), len(ld), p_i32(pv), 1000) == 0
             assert pv.tolist() == list(O.optfirstpivot(f, ld, first))
     assert pv.tolist() == [3, 4, 5, 6]                     # test/test_util.jl:28-36: the maximum of sum(v) is the all-d corner
+
+
+EDGE = [
+    ("two_sites", O.F_LORENTZ, [1.0], [7, 5], dict(tolerance=1e-10)),
+    ("unit_dims", O.F_LORENTZ, [1.0], [1, 4, 1, 3, 1], dict(tolerance=1e-10)),
+    ("maxiter_1", O.F_LORENTZ, [1.0], [4] * 5, dict(tolerance=1e-12, maxiter=1)),
+    ("ncheck_1", O.F_LORENTZ, [1.0], [4] * 5, dict(tolerance=1e-6, ncheckhistory=1)),
+    ("maxbond_1", O.F_LORENTZ, [1.0], [4] * 5, dict(tolerance=1e-12, maxbonddim=1, maxiter=3)),
+    ("noglobalcheck", O.F_HASH, [1.0, 0.5], [3] * 5, dict(tolerance=1e-9, checkconvglobalpivot=False, maxiter=6)),
+]
+
+
+@pytest.mark.parametrize("name,kind,params,localdims,kw", EDGE, ids=[c[0] for c in EDGE])
+def test_edge_configurations_identical_to_oracle(mock, name, kind, params, localdims, kw):
+    f = O.Func(kind, params)
+    piv = [[1] * len(localdims)]
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, **kw)
+    t = _native(mock, localdims, f, piv)
+    ranks, errors = t.optimize(f.h, nsearchglobalpivot=0, **kw)
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+
+
+def test_several_initial_pivots_and_state_transfer(mock):
+    """Two initial pivots (test/test_tensorci2.jl:55-102 style), then the state is copied into a fresh object through
+    set_indexset / set_maxsamplevalue and one more sweep gives the same result on both."""
+    localdims = [2] * 8
+    f = O.Func(O.F_QEXP2, [1.0, 0.5, 3.0])
+    piv = [[1] * 8, [1] + [2] * 7]
+    o = O.TCI2(f, localdims, piv)
+    t = _native(mock, localdims, f, piv)
+    o.sweep2site(2, abstol=1e-9)
+    t.sweep2site(f.h, 2, abstol=1e-9)
+    _same_state(t, o)
+    L, h = mock
+    u = _load("native").NativeTCI2(L, h, localdims)
+    for b in range(1, 9):
+        u.set_indexset(0, b, t.Iset(b))
+        u.set_indexset(1, b, t.Jset(b))
+    u.set_maxsamplevalue(t.errors()[2])
+    assert not u.sitetensors_available()
+    # a fresh object has no sweep history: compare with strictly nested sweeps, where the history is not used
+    t.sweep2site(f.h, 2, iter1=3, abstol=1e-9, strictlynested=True)
+    u.sweep2site(f.h, 2, iter1=3, abstol=1e-9, strictlynested=True)
+    for b in range(1, 9):
+        np.testing.assert_array_equal(t.Iset(b), u.Iset(b))
+        np.testing.assert_array_equal(t.Jset(b), u.Jset(b))
+    np.testing.assert_array_equal(t.errors()[0], u.errors()[0])
+    assert t.errors()[2] == u.errors()[2]
+
+
+def test_nan_function_reports_like_the_reference(mock):
+    """A NaN in Pi: the rrLU's "lu.L contains NaNs" / "lu.U contains NaNs" (matrixlu.jl:376-381) comes through the driver."""
+    table = np.ones((3, 3, 3)); table[0, 1, 0] = np.nan       # in the first pivot's row of the first Pi
+    f = O.Func(O.F_DENSE, table=table)
+    TCIError = _load("_lib").TCIError
+    t = _native(mock, [3, 3, 3], f, [[1, 1, 1]])
+    with pytest.raises(TCIError, match="contains NaNs"):
+        t.optimize(f.h, tolerance=1e-8, nsearchglobalpivot=0)
