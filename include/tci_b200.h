@@ -277,7 +277,7 @@ int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const in
  * next to a microsecond-sized kernel (Python), the same host logic is available compiled: a tci_tci2 object is the
  * `TensorCI2{Float64}` state (src/tensorci2.jl:50-93) — Iset/Jset as int32 tables on the host, site tensors in device memory —
  * and the calls below are the reference's functions of the same names, written purely on top of the entry points above
- * (every number still comes from those kernels; pivotsearch = :full only).  Sites and bonds are 1-based, index values
+ * (every number still comes from those kernels).  Sites and bonds are 1-based, index values
  * 1-based; maxbonddim <= 0 means unbounded (typemax(Int)).  sweepstrategy: 0 :forward, 1 :backandforth, 2 :backward
  * (src/sweepstrategies.jl:41-50).  The message of the last failure on an object is tci_tci2_last_error(t). */
 /* optfirstpivot(f, localdims, firstpivot; maxsweep) src/util.jl:260-291: h_pivot (nsites, 1-based) is improved in place by a
@@ -290,6 +290,10 @@ const char* tci_tci2_last_error(tci_tci2 t);
 /* Seed of the global pivot finder's random starts (the reference draws from Julia's default RNG, which has no portable
  * restatement: global pivots are not comparable with a Julia run). */
 int tci_tci2_seed(tci_tci2 t, uint64_t seed);
+/* Pivot search strategy of updatepivots! (and therefore of sweep2site! / optimize!): rook = 0 is :full (the default), 1 is :rook
+ * (src/tensorci2.jl:863-905 -> arrlu src/matrixlu.jl:500-569 over SubMatrix strips :764-804: Pi is never formed).  `seed` starts
+ * the stream behind pushrandomsubset! (src/util.jl:173-219; Julia's global RNG in the reference). */
+int tci_tci2_set_pivotsearch(tci_tci2 t, int rook, uint64_t seed);
 /* addglobalpivots!(tci, pivots) :335-357 — h_pivots: npivots x nsites. */
 int tci_tci2_addglobalpivots(tci_tci2 t, const int32_t* h_pivots, int64_t npivots);
 /* The constructor's maxsamplevalue = maximum(abs(f(p)) for p in pivots) and its zero check :105-116. */

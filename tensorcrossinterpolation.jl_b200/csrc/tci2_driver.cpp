@@ -4,7 +4,7 @@
 // call the kernels through the C ABI.  This file is that host side in C++: it restates src/tensorci2.jl's control flow
 // (citations per function) and produces every number through the public entry points of include/tci_b200.h only
 // (tci_batcheval_acc_f64 / tci_maxacc_*, tci_rrlu_inplace_f64, tci_luci_factors_f64, tci_solve_right_f64, tci_maxabs_f64,
-// tci_tt_evaluate_f64, tci_malloc/free/memcpy) — no CUDA header, no internal symbol.  It exists because a half-sweep
+// tci_trsm_right_f64, tci_tt_evaluate_f64, tci_malloc/free/memcpy) — no CUDA header, no internal symbol.  It exists because a half-sweep
 // over small Pi matrices is a chain of hundreds of microsecond-sized device calls: an interpreted host pays ~200 us of
 // bookkeeping per bond on top of them, a compiled one a few.  Being pure C-ABI client code it also compiles against any
 // other implementation of those entry points, which is how its bookkeeping is tested without a GPU
@@ -145,12 +145,57 @@ void pushunique(IdxTable& t, const int32_t* r) {                                
     t.n++;
 }
 
+// 1-based positions in `tab` of the rows of `sub` that occur in it (first occurrence), in `sub` order:
+// findfirst(isequal(i), Icombined) filtered for nothing — tensorci2.jl:866-867
+std::vector<int64_t> positions_of(const IdxTable& sub, const IdxTable& tab) {
+    std::vector<int64_t> out;
+    if (sub.n == 0 || tab.n == 0) return out;
+    if (tab.len == 0) { out.assign((size_t)sub.n, 1); return out; }
+    size_t cap = 16; while (cap < (size_t)tab.n * 2) cap <<= 1;
+    std::vector<int64_t> slot(cap, -1);
+    for (int64_t i = 0; i < tab.n; ++i) {
+        const int32_t* r = tab.row(i);
+        size_t s = (size_t)hash_row(r, tab.len) & (cap - 1);
+        bool dup = false;
+        while (slot[s] >= 0) {
+            if (std::memcmp(tab.row(slot[s]), r, sizeof(int32_t) * tab.len) == 0) { dup = true; break; }
+            s = (s + 1) & (cap - 1);
+        }
+        if (!dup) slot[s] = i;
+    }
+    for (int64_t k = 0; k < sub.n; ++k) {
+        const int32_t* r = sub.row(k);
+        size_t s = (size_t)hash_row(r, tab.len) & (cap - 1);
+        while (slot[s] >= 0) {
+            if (std::memcmp(tab.row(slot[s]), r, sizeof(int32_t) * tab.len) == 0) { out.push_back(slot[s] + 1); break; }
+            s = (s + 1) & (cap - 1);
+        }
+    }
+    return out;
+}
+
 inline uint64_t splitmix64(uint64_t& s) {
     s += 0x9E3779B97F4A7C15ull;
     uint64_t z = s;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     return z ^ (z >> 31);
+}
+
+// pushrandomsubset!(subset, 1:setsize, n) — util.jl:214-219 with randomsubset :173-191 (draw, then deleteat!).  The reference
+// draws from Julia's global RNG, which has no portable restatement; the stream here is the counter-based splitmix64 the
+// Python host (matrixlu.Rng) and the CPU checker use, so all three pick the same rows/columns for a given seed.
+void pushrandomsubset(std::vector<int64_t>& subset, int64_t setsize, int64_t n, uint64_t& rng) {
+    std::vector<char> in((size_t)setsize + 1, 0);
+    for (int64_t v : subset) in[(size_t)v] = 1;
+    std::vector<int64_t> c;
+    for (int64_t v = 1; v <= setsize; ++v) if (!in[(size_t)v]) c.push_back(v);
+    n = std::min<int64_t>(n, (int64_t)c.size());
+    for (int64_t i = 0; i < n; ++i) {
+        const size_t idx = (size_t)(splitmix64(rng) % (uint64_t)c.size());
+        subset.push_back(c[idx]);
+        c.erase(c.begin() + (std::ptrdiff_t)idx);
+    }
 }
 
 } // namespace
@@ -172,7 +217,9 @@ struct tci_tci2_s {
     std::vector<int64_t> rowperm, colperm;
     std::vector<double> pe;
     std::string err;
-    uint64_t rng = 0;
+    uint64_t rng = 0;                                   // random starts of the global pivot finder
+    int pivotsearch = 0;                                // 0 :full, 1 :rook (tensorci2.jl:845-914)
+    uint64_t rookrng = 0;                               // stream behind pushrandomsubset! of the rook search
     // statistics (host wall clock around the calls; the batch-eval and rrLU entry points synchronise)
     int64_t nevals = 0, nbondupdates = 0;
     double t_eval = 0, t_lu = 0, t_factors = 0, t_host = 0;
@@ -294,7 +341,92 @@ int core_from_factor(tci_tci2 t, const Luci& lu, int b0, bool left) {
     return TCI_OK;
 }
 
-// updatepivots! (tensorci2.jl:825-930), pivotsearch = :full.  b0: 0-based bond (between sites b0 and b0+1).
+// arrlu(Float64, f, (m, n), I0, J0; maxrank, reltol, abstol, leftorthogonal, numrookiter) — matrixlu.jl:500-569 — on the Pi matrix
+// defined by the combined index sets, which is never formed: alternating row and column STRIPS of it (SubMatrix,
+// tensorci2.jl:764-804) are evaluated (K1) and factorised (rrLU) until the pivots stop moving, then the factors are completed
+// by two triangular solves (cols2Lmatrix!/rows2Umatrix!, matrixlu.jl:627-674).  Every strip's rrLU writes L and U straight
+// into the full-size factor buffers (leading dimensions m and maxrank), so the completion happens in place.
+int arrlu(tci_tci2 t, tci_functor f, const IdxTable& Ic, const IdxTable& Jc, std::vector<int64_t> I0, std::vector<int64_t> J0,
+          int64_t maxbonddim, double reltol, double abstol, bool leftorth, Luci* out) {
+    const int numrookiter = 5;
+    const int64_t m = Ic.n, n = Jc.n, mn = std::min(m, n);
+    const int64_t maxrank = (maxbonddim <= 0 || maxbonddim > mn) ? mn : maxbonddim;
+    out->m = m; out->n = n; out->leftorth = leftorth; out->r = 0;
+    out->ldl = std::max<int64_t>(m, 1); out->ldu = std::max<int64_t>(maxrank, 1);
+    if (mn == 0) { out->errs.assign(1, 0.0); return TCI_OK; }
+    int rc = reserve(t, t->L, (size_t)out->ldl * (size_t)std::max<int64_t>(maxrank, 1)); if (rc) return rc;
+    rc = reserve(t, t->U, (size_t)out->ldu * (size_t)n); if (rc) return rc;
+    std::vector<int64_t> rowperm((size_t)m), colperm((size_t)n), srow, scol, tmp;
+    for (int64_t i = 0; i < m; ++i) rowperm[(size_t)i] = i + 1;
+    for (int64_t j = 0; j < n; ++j) colperm[(size_t)j] = j + 1;
+    bool islowrank = false;
+    int64_t r = 0, lastrows = 0, lastcols = 0;
+    std::vector<double> pe;
+    for (;;) {
+        if (leftorth) pushrandomsubset(J0, n, std::max<int64_t>(1, (int64_t)J0.size()), t->rookrng);     // :521-525
+        else          pushrandomsubset(I0, m, std::max<int64_t>(1, (int64_t)I0.size()), t->rookrng);
+        for (int rookiter = 1; rookiter <= numrookiter; ++rookiter) {
+            const bool colmove = ((rookiter % 2 == 0) == leftorth);                                       // :529
+            const std::vector<int64_t>& rows = colmove ? I0 : rowperm;                                    // :532-536
+            const std::vector<int64_t>& cols = colmove ? colperm : J0;
+            const int64_t kr = (int64_t)rows.size(), kc = (int64_t)cols.size(), ld = pad16(kr);
+            IdxTable left = select_rows(Ic, rows.data(), kr), right = select_rows(Jc, cols.data(), kc);
+            rc = reserve(t, t->pi, (size_t)ld * (size_t)std::max<int64_t>(kc, 1)); if (rc) return rc;
+            rc = fill(t, f, left, right, t->pi.p, kr, ld, 1); if (rc) return rc;
+            const double t0 = now_s();
+            const int64_t kmn = std::min(kr, kc), mr = std::min(maxrank, kmn);
+            srow.assign((size_t)std::max<int64_t>(kr, 1), 0); scol.assign((size_t)std::max<int64_t>(kc, 1), 0);
+            pe.assign((size_t)mr + 1, 0.0);
+            int64_t npivot = 0; double error = 0.0;
+            TCI2_CALL(t, tci_rrlu_inplace_f64(t->h, t->pi.p, kr, kc, ld, mr, reltol, abstol, leftorth ? 1 : 0, srow.data(), scol.data(), &npivot,
+                                              &error, t->L.p, out->ldl, t->U.p, out->ldu, pe.data()));
+            t->t_lu += now_s() - t0;
+            // _optimizerrlu! swaps lu.rowpermutation / lu.colpermutation at the POSITIONS of the strip (:254-275, :539-540)
+            tmp.assign(rowperm.begin(), rowperm.begin() + kr);
+            for (int64_t i = 0; i < kr; ++i) rowperm[(size_t)i] = tmp[(size_t)(srow[(size_t)i] - 1)];
+            tmp.assign(colperm.begin(), colperm.begin() + kc);
+            for (int64_t j = 0; j < kc; ++j) colperm[(size_t)j] = tmp[(size_t)(scol[(size_t)j] - 1)];
+            r = npivot; lastrows = kr; lastcols = kc;
+            pe.resize((size_t)r + 1);
+            islowrank = islowrank || r < kmn;                                                             // :541
+            std::vector<int64_t> ri(rowperm.begin(), rowperm.begin() + r), ci(colperm.begin(), colperm.begin() + r);
+            if (ri == I0 && ci == J0) break;                                                              // :544-546
+            I0.swap(ri); J0.swap(ci);                                                                     // :548-549
+        }
+        if (islowrank || (int64_t)I0.size() >= maxrank) break;                                            // :552-554
+    }
+    out->r = r; out->errs = pe;
+    if (r > 0 && lastrows < m) {                                                                          // :558-564
+        std::vector<char> in((size_t)m + 1, 0); for (int64_t v : I0) in[(size_t)v] = 1;
+        std::vector<int64_t> I2; for (int64_t v = 1; v <= m; ++v) if (!in[(size_t)v]) I2.push_back(v);
+        rowperm = I0; rowperm.insert(rowperm.end(), I2.begin(), I2.end());
+        const int64_t q = (int64_t)I2.size();
+        IdxTable left = select_rows(Ic, I2.data(), q), right = select_rows(Jc, J0.data(), r);
+        rc = fill(t, f, left, right, t->L.p + r, q, out->ldl, 1); if (rc) return rc;                      // rows r.. of L, in place
+        const double t0 = now_s();
+        TCI2_CALL(t, tci_trsm_right_f64(t->h, t->U.p, 1, out->ldu, r, 0, 0, t->L.p + r, 1, out->ldl, q)); // cols2Lmatrix! :627-648
+        t->t_factors += now_s() - t0;
+    }
+    if (r > 0 && lastcols < n) {                                                                          // :567-573
+        std::vector<char> in((size_t)n + 1, 0); for (int64_t v : J0) in[(size_t)v] = 1;
+        std::vector<int64_t> J2; for (int64_t v = 1; v <= n; ++v) if (!in[(size_t)v]) J2.push_back(v);
+        colperm = J0; colperm.insert(colperm.end(), J2.begin(), J2.end());
+        const int64_t q = (int64_t)J2.size();
+        IdxTable left = select_rows(Ic, I0.data(), r), right = select_rows(Jc, J2.data(), q);
+        double* U2 = t->U.p + (size_t)r * (size_t)out->ldu;                                               // columns r.. of U, in place
+        rc = fill(t, f, left, right, U2, r, out->ldu, 1); if (rc) return rc;
+        const double t0 = now_s();
+        // rows2Umatrix! :655-674: L1 X = U2  <=>  X^T L1^T = U2^T — the right solve on transposed strides
+        TCI2_CALL(t, tci_trsm_right_f64(t->h, t->L.p, out->ldl, 1, r, 0, 0, U2, out->ldu, 1, q));
+        t->t_factors += now_s() - t0;
+    }
+    t->rowperm = rowperm; t->colperm = colperm;
+    if (t->rowperm.empty()) t->rowperm.assign(1, 1);
+    if (t->colperm.empty()) t->colperm.assign(1, 1);
+    return TCI_OK;
+}
+
+// updatepivots! (tensorci2.jl:825-930), pivotsearch = :full or :rook.  b0: 0-based bond (between sites b0 and b0+1).
 int updatepivots(tci_tci2 t, tci_functor f, int b0, bool leftorth, double reltol, double abstol, int64_t maxbonddim,
                  const IdxTable* extraI, const IdxTable* extraJ) {
     invalidate(t);
@@ -304,10 +436,19 @@ int updatepivots(tci_tci2 t, tci_functor f, int b0, bool leftorth, double reltol
     IdxTable Jc = union_rows(kronecker_right(t->localdims[b0 + 1], t->J[b0 + 1]), extraJ);   // :843
     t->t_host += now_s() - th;
     const int64_t m = Ic.n, n = Jc.n, ld = pad16(m);
-    int rc = reserve(t, t->pi, (size_t)ld * std::max<int64_t>(n, 1)); if (rc) return rc;
-    rc = fill(t, f, Ic, Jc, t->pi.p, m, ld, 1); if (rc) return rc;                           // :851-854
     Luci lu;
-    rc = luci_factorize(t, m, n, ld, maxbonddim, reltol, abstol, leftorth, &lu); if (rc) return rc;   // :856-862
+    int rc = TCI_OK;
+    bool full = t->pivotsearch == 0;
+    if (t->pivotsearch == 1) {                                                               // :863-905
+        rc = arrlu(t, f, Ic, Jc, positions_of(t->I[b0 + 1], Ic), positions_of(t->J[b0], Jc), maxbonddim, reltol, abstol, leftorth, &lu);
+        if (rc) return rc;
+        full = lu.r == 0;                                                                    // :886-899 fall back to the full search
+    }
+    if (full) {
+        rc = reserve(t, t->pi, (size_t)ld * std::max<int64_t>(n, 1)); if (rc) return rc;
+        rc = fill(t, f, Ic, Jc, t->pi.p, m, ld, 1); if (rc) return rc;                       // :851-854
+        rc = luci_factorize(t, m, n, ld, maxbonddim, reltol, abstol, leftorth, &lu); if (rc) return rc;   // :856-862
+    }
     t->I[b0 + 1] = select_rows(Ic, t->rowperm.data(), lu.r);                                 // :915
     t->J[b0] = select_rows(Jc, t->colperm.data(), lu.r);                                     // :916
     if (noextra) {                                                                           // :917-920
@@ -587,6 +728,12 @@ int tci_tci2_destroy(tci_tci2 t) {
 const char* tci_tci2_last_error(tci_tci2 t) { return t ? t->err.c_str() : "NULL tci_tci2"; }
 
 int tci_tci2_seed(tci_tci2 t, uint64_t seed) { if (!t) return TCI_ERR_INVALID; t->rng = seed; return TCI_OK; }
+
+int tci_tci2_set_pivotsearch(tci_tci2 t, int rook, uint64_t seed) {
+    if (!t || (rook != 0 && rook != 1)) return TCI_ERR_INVALID;
+    t->pivotsearch = rook; t->rookrng = seed;
+    return TCI_OK;
+}
 
 int tci_tci2_addglobalpivots(tci_tci2 t, const int32_t* h_pivots, int64_t npivots) {
     if (!t || npivots < 0 || (npivots > 0 && !h_pivots)) return TCI_ERR_INVALID;

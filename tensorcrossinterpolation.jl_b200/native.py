@@ -61,6 +61,12 @@ class NativeTCI2:
     def seed(self, seed):
         self._check(self.L.tci_tci2_seed(self._t, C.c_uint64(int(seed) & ((1 << 64) - 1))))
 
+    def set_pivotsearch(self, pivotsearch, seed=0):
+        """'full' or 'rook' (tensorci2.jl:845-914); `seed` starts the stream behind pushrandomsubset!."""
+        if pivotsearch not in ("full", "rook"):
+            raise TCIError(-1, f"Unknown pivot search strategy {pivotsearch}. Choose from :rook, :full.")
+        self._check(self.L.tci_tci2_set_pivotsearch(self._t, int(pivotsearch == "rook"), C.c_uint64(int(seed) & ((1 << 64) - 1))))
+
     def addglobalpivots(self, pivots):
         if any(len(p) != len(self) for p in pivots):
             raise TCIError(-1, "Please specify a pivot as one index per leg of the MPS.")

@@ -715,11 +715,11 @@ _NATIVE_KW = {"tolerance", "maxbonddim", "maxiter", "sweepstrategy", "normalizee
 def _native_eligible(f, kwargs):
     """engine="auto": does the compiled driver cover this call?  Device functor evaluated by the stock batch path (wrappers
     that override evaluate_batch — sharded, cached, contraction, host adapters — stay on the Python host), only keywords the
-    driver implements, full pivot search, nothing to print."""
+    driver implements, nothing to print."""
     return (isinstance(f, BatchEvaluator) and bool(getattr(f, "_f", None))
             and type(f).evaluate_batch is BatchEvaluator.evaluate_batch
             and set(kwargs) <= (_NATIVE_KW | {"handle"})
-            and kwargs.get("pivotsearch", "full") == "full"
+            and kwargs.get("pivotsearch", "full") in ("full", "rook")
             and not kwargs.get("verbosity", 0)
             and not kwargs.get("checkbatchevaluatable", False))
 
@@ -734,8 +734,9 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs)
     unknown = set(kwargs) - _NATIVE_KW
     if unknown:
         raise TCIError(_lib.TCI_ERR_INVALID, f"engine='native' does not take {sorted(unknown)} (use engine='python')")
-    if kwargs.pop("pivotsearch", "full") != "full":
-        raise TCIError(_lib.TCI_ERR_INVALID, "engine='native' implements pivotsearch=:full only (use engine='python' for :rook)")
+    pivotsearch = kwargs.pop("pivotsearch", "full")
+    if pivotsearch not in ("full", "rook"):
+        raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown pivot search strategy {pivotsearch}. Choose from :rook, :full.")
     if not isinstance(f, BatchEvaluator) or not getattr(f, "_f", None):
         raise TCIError(_lib.TCI_ERR_INVALID, "engine='native' needs a device functor (a BatchEvaluator built on tci_functor_*); "
                        "host callables run with engine='python'")
@@ -750,6 +751,7 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs)
     nat = NativeTCI2(_lib.lib(), h.h, localdims)
     if seed is not None:
         nat.seed(seed)
+    nat.set_pivotsearch(pivotsearch, 0 if seed is None else seed)        # same default stream as TensorCI2.rng = Rng(0)
     nat.addglobalpivots(initialpivots)
     nat.init_maxsample(f._f, initialpivots)
     if kwargs.get("tolerance") is None:
@@ -776,7 +778,7 @@ def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323.
     `engine` (not in the reference): "native" hands the optimize! loop to the compiled sweep driver (fewer microseconds of host
     work per bond, identical kernels and results), "python" runs it in this module; the default "auto" takes the compiled
-    driver whenever it covers the call (device functor, pivotsearch=:full, one GPU, no Python-side finder / rng / verbosity)."""
+    driver whenever it covers the call (device functor, one GPU, no Python-side finder / rng / verbosity)."""
     seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): rook-search stream
     engine = kwargs.pop("engine", "auto")
     if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module

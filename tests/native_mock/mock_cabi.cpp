@@ -132,6 +132,24 @@ int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb,
     return TCI_OK;
 }
 
+// X * T = B in place on B (q x r), T triangular; same operation order as the checker's cols2Lmatrix / rows2Umatrix
+// (column k scaled by the diagonal, then eliminated from the columns that follow), so the stand-in is bit-identical to it.
+int tci_trsm_right_f64(tci_handle h, const double* T, int64_t st_row, int64_t st_col, int64_t r, int lower, int unit, double* B,
+                       int64_t sb_row, int64_t sb_col, int64_t q) {
+    h->ncalls++;
+    auto t = [&](int64_t i, int64_t j) { return T[i * st_row + j * st_col]; };
+    auto b = [&](int64_t i, int64_t j) -> double& { return B[i * sb_row + j * sb_col]; };
+    for (int64_t kk = 0; kk < r; ++kk) {
+        const int64_t k = lower ? r - 1 - kk : kk;
+        if (!unit) for (int64_t i = 0; i < q; ++i) b(i, k) = b(i, k) / t(k, k);
+        for (int64_t j = lower ? 0 : k + 1; j < (lower ? k : r); ++j) {
+            const double y = t(k, j);
+            for (int64_t i = 0; i < q; ++i) b(i, j) = b(i, j) - b(i, k) * y;
+        }
+    }
+    return TCI_OK;
+}
+
 int tci_maxabs_f64(tci_handle h, const double* d_x, int64_t rows, int64_t cols, int64_t ld, double* h_maxabs) {
     h->ncalls++;
     for (int64_t j = 0; j < cols; ++j) merge_maxabs(h_maxabs, d_x + j * ld, (size_t)rows);

@@ -163,8 +163,8 @@ def test_native_quantics_c4_small(tci):
 
 def test_native_errors(tci):
     f = tci.LorentzFunction([3, 3, 3])
-    with pytest.raises(tci.TCIError, match="pivotsearch=:full only"):
-        tci.crossinterpolate2(f, [3, 3, 3], engine="native", pivotsearch="rook")
+    with pytest.raises(tci.TCIError, match="Unknown pivot search strategy"):
+        tci.crossinterpolate2(f, [3, 3, 3], engine="native", pivotsearch="castle")
     with pytest.raises(tci.TCIError, match="device functor"):
         tci.crossinterpolate2(lambda v: 1.0, [3, 3, 3], engine="native")
     with pytest.raises(tci.TCIError, match="convergence criterion is not reachable"):
@@ -235,7 +235,7 @@ def test_engine_auto_selection(tci):
     f = tci.LorentzFunction([4] * 4)
     assert _native_eligible(f, dict(tolerance=1e-8, nsearchglobalpivot=0))
     assert _native_eligible(f, dict(tolerance=1e-8, maxbonddim=7, handle=None))
-    assert not _native_eligible(f, dict(pivotsearch="rook"))
+    assert _native_eligible(f, dict(pivotsearch="rook"))
     assert not _native_eligible(f, dict(rng=np.random.default_rng(0)))
     assert not _native_eligible(f, dict(verbosity=1))
     assert not _native_eligible(f, dict(bondorder="oddeven"))
@@ -246,3 +246,24 @@ def test_engine_auto_selection(tci):
     assert "nbondupdates" in t.stats                        # ran in the compiled driver
     t, _, _ = tci.crossinterpolate2(f, [4] * 4, tolerance=1e-8, nsearchglobalpivot=0, engine="python")
     assert "nbondupdates" not in t.stats
+
+
+@pytest.mark.parametrize("n,d,kw,seed", [(6, 8, dict(tolerance=1e-8), 1), (6, 6, dict(tolerance=1e-12, maxbonddim=5), 7),
+                                         (5, 5, dict(tolerance=1e-9, strictlynested=True), 11)])
+def test_native_rook_search(tci, n, d, kw, seed):
+    """pivotsearch=:rook inside the compiled driver (arrlu over strips, matrixlu.jl:500-569): same seeded stream as the checker
+    and as the Python host, so all three sample the same strips — index sets, errors and evaluation counts identical."""
+    f, g = tci.LorentzFunction([d] * n), O.Func(O.F_LORENTZ, [1.0])
+    t, ranks, errors = tci.crossinterpolate2(f, [d] * n, nsearchglobalpivot=0, pivotsearch="rook", seed=seed, engine="native", **kw)
+    o, oranks, oerrors = O.crossinterpolate2(g, [d] * n, pivotsearch="rook", seed=seed, **kw)
+    assert list(ranks) == list(oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_sets(t, o)
+    assert t.stats["nevals"] == o.stats()["nevals"]
+    for a, r in zip(t.sitetensors, o.sitetensors()):
+        _close(a, r, 1e-10)
+    p, pranks, perrors = tci.crossinterpolate2(f, [d] * n, nsearchglobalpivot=0, pivotsearch="rook", seed=seed, engine="python", **kw)
+    np.testing.assert_array_equal(ranks, pranks)
+    for s in range(n):
+        np.testing.assert_array_equal(t.Iset[s], p.Iset[s])
+        np.testing.assert_array_equal(t.Jset[s], p.Jset[s])

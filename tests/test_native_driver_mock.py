@@ -261,3 +261,28 @@ def test_nan_function_reports_like_the_reference(mock):
     t = _native(mock, [3, 3, 3], f, [[1, 1, 1]])
     with pytest.raises(TCIError, match="contains NaNs"):
         t.optimize(f.h, tolerance=1e-8, nsearchglobalpivot=0)
+
+
+ROOK = [
+    ("lorentz6", O.F_LORENTZ, [1.0], [8] * 6, dict(tolerance=1e-8), 1),
+    ("lorentz_maxbond", O.F_LORENTZ, [1.0], [6] * 6, dict(tolerance=1e-12, maxbonddim=5), 7),
+    ("hash_fullrank", O.F_HASH, [1.0, 0.5], [4] * 6, dict(tolerance=1e-10, maxbonddim=12, maxiter=3), 3),
+    ("nested", O.F_LORENTZ, [1.0], [5] * 5, dict(tolerance=1e-9, strictlynested=True), 11),
+    ("forward", O.F_LORENTZ, [1.0], [5] * 5, dict(tolerance=1e-9, sweepstrategy="forward", maxiter=6), 5),
+]
+
+
+@pytest.mark.parametrize("name,kind,params,localdims,kw,seed", ROOK, ids=[c[0] for c in ROOK])
+def test_rook_search_identical_to_oracle(mock, name, kind, params, localdims, kw, seed):
+    """pivotsearch=:rook (arrlu over SubMatrix strips, matrixlu.jl:500-569) in the driver against the checker's restatement with
+    the same seeded stream: the same strips are sampled, so index sets, errors, evaluation counts and tensors are identical."""
+    f = O.Func(kind, params)
+    piv = [[1] * len(localdims)]
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, pivotsearch="rook", seed=seed, **kw)
+    t = _native(mock, localdims, f, piv)
+    t.set_pivotsearch("rook", seed)
+    ranks, errors = t.optimize(f.h, nsearchglobalpivot=0, **kw)
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+    assert t.stats()["nevals"] == o.stats()["nevals"]
