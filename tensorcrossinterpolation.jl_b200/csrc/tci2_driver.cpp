@@ -427,8 +427,10 @@ int arrlu(tci_tci2 t, tci_functor f, const IdxTable& Ic, const IdxTable& Jc, std
 }
 
 // updatepivots! (tensorci2.jl:825-930), pivotsearch = :full or :rook.  b0: 0-based bond (between sites b0 and b0+1).
+// want_cores = false: the caller is about to invalidate or recompute the site tensors anyway (every later updatepivots!
+// invalidates them, fillsitetensors! recomputes all of them), so left(luci)/right(luci) need not be formed.
 int updatepivots(tci_tci2 t, tci_functor f, int b0, bool leftorth, double reltol, double abstol, int64_t maxbonddim,
-                 const IdxTable* extraI, const IdxTable* extraJ) {
+                 const IdxTable* extraI, const IdxTable* extraJ, bool want_cores = true) {
     invalidate(t);
     const double th = now_s();
     const bool noextra = (!extraI || extraI->n == 0) && (!extraJ || extraJ->n == 0);
@@ -451,7 +453,7 @@ int updatepivots(tci_tci2 t, tci_functor f, int b0, bool leftorth, double reltol
     }
     t->I[b0 + 1] = select_rows(Ic, t->rowperm.data(), lu.r);                                 // :915
     t->J[b0] = select_rows(Jc, t->colperm.data(), lu.r);                                     // :916
-    if (noextra) {                                                                           // :917-920
+    if (noextra && want_cores) {                                                             // :917-920
         rc = core_from_factor(t, lu, b0, true); if (rc) return rc;
         rc = core_from_factor(t, lu, b0 + 1, false); if (rc) return rc;
     }
@@ -560,8 +562,10 @@ int sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, i
         const bool fwd = forwardsweep(strategy, it);
         for (int step = 0; step < N - 1; ++step) {                                           // :1226-1250
             const int b0 = fwd ? step : N - 2 - step;
+            // only the tensors of the very last bond update can survive this call, and only without the final fill
+            const bool keep = !dofill && it == iter1 + niter - 1 && step == N - 2;
             int rc = updatepivots(t, f, b0, fwd, 1e-14, abstol, maxbonddim, useextra ? &extraI[b0 + 1] : nullptr,
-                                  useextra ? &extraJ[b0] : nullptr);
+                                  useextra ? &extraJ[b0] : nullptr, keep);
             if (rc) return rc;
         }
     }

@@ -286,3 +286,23 @@ def test_rook_search_identical_to_oracle(mock, name, kind, params, localdims, kw
     np.testing.assert_array_equal(errors, oerrors)
     _same_state(t, o)
     assert t.stats()["nevals"] == o.stats()["nevals"]
+
+
+def test_last_bond_tensors_survive_a_sweep_without_fill(mock):
+    """sweep2site!(...; fillsitetensors=false) with strictly nested sets: every updatepivots! invalidates the tensors and sets
+    those of its own two sites (tensorci2.jl:917-920), so exactly the last bond's pair is available afterwards — the driver
+    skips forming the others, which nobody can observe."""
+    localdims = [4] * 5
+    f = O.Func(O.F_LORENTZ, [1.0])
+    t = _native(mock, localdims, f, [[1] * 5])
+    t.sweep2site(f.h, 1, abstol=1e-9, strictlynested=True, fillsitetensors=False)      # forward: last bond is 4 (sites 4, 5)
+    TCIError = _load("_lib").TCIError
+    for site in (1, 2, 3):
+        with pytest.raises(TCIError, match="not available"):
+            t.core(site)
+    o = O.TCI2(f, localdims, [[1] * 5])
+    o.sweep2site(1, abstol=1e-9, strictlynested=True, fillsitetensors=False)
+    for site in (4, 5):
+        ptr, shape = t.core(site)
+        got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(int(np.prod(shape)),)).reshape(shape, order="F")
+        np.testing.assert_array_equal(got, o.sitetensor(site))
