@@ -234,4 +234,43 @@ function evaluate(tt::DeviceTT, points::Vector{MultiIndex})
     return out
 end
 
+# ---- optional: fewer host round trips in a sweep ----------------------------------------------------------------------------
+# updatemaxsample! (src/tensorci2.jl:636-638) merged on the device: a sweep passes the accumulator to evaluate_device_acc! for
+# every Pi and reads it once at the end (the value is only consumed by the tolerance of the next sweep, :1089-1090).
+mutable struct MaxAccumulator
+    h::Handle
+    ptr::Ptr{Cvoid}
+    function MaxAccumulator(value::Float64=0.0; h::Handle=handle())
+        p = Ref{Ptr{Cvoid}}(C_NULL)
+        check(h.ptr, ccall((:tci_malloc, LIB), Cint, (Ptr{Cvoid}, Ref{Ptr{Cvoid}}, Csize_t), h.ptr, p, 64))
+        a = new(h, p[])
+        finalizer(x -> ccall((:tci_free, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}), x.h.ptr, x.ptr), a)
+        check(h.ptr, ccall((:tci_maxacc_set, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Cdouble), h.ptr, a.ptr, value))
+        return a
+    end
+end
+function Base.getindex(a::MaxAccumulator)::Float64      # synchronises; max(|initial|, every value since), NaN-propagating
+    v = Ref(0.0)
+    check(a.h.ptr, ccall((:tci_maxacc_get, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ref{Float64}), a.h.ptr, a.ptr, v))
+    return v[]
+end
+function evaluate_device_acc!(f::B200Function, out::DeviceMatrix, left::Vector{MultiIndex}, right::Vector{MultiIndex},
+                              stride_c::Int, stride_j::Int, acc::MaxAccumulator)
+    L, R = _table(left), _table(right)
+    check(f.h.ptr, ccall((:tci_batcheval_acc_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Cint, Ptr{Int32}, Int64, Cint, Ptr{Int32}, Int64, Cint, Ptr{Float64}, Int64, Int64, Ptr{Cvoid}),
+        f.h.ptr, f.f, f.localdims, length(f.localdims), L, length(left), size(L, 1), R, length(right), size(R, 1),
+        out.ptr, stride_c, stride_j, acc.ptr))
+    return out
+end
+
+# optfirstpivot(f, localdims, firstpivot; maxsweep) (src/util.jl:260-291) as one call for device functors
+function TCI.optfirstpivot(f::B200Function, localdims::Union{Vector{Int},NTuple{N,Int}},
+                           firstpivot::MultiIndex=ones(Int, length(localdims)); maxsweep::Int=1000) where {N}
+    pivot = Int32.(firstpivot)
+    check(f.h.ptr, ccall((:tci_optfirstpivot_f64, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Cint, Ptr{Int32}, Cint),
+        f.h.ptr, f.f, f.localdims, length(f.localdims), pivot, maxsweep))
+    return Int.(pivot)
+end
+
 end # module
