@@ -306,3 +306,33 @@ def test_last_bond_tensors_survive_a_sweep_without_fill(mock):
         ptr, shape = t.core(site)
         got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(int(np.prod(shape)),)).reshape(shape, order="F")
         np.testing.assert_array_equal(got, o.sitetensor(site))
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_configurations_identical_to_oracle(mock, seed):
+    """Randomised sweep over the driver's control flow: chain length, mixed local dimensions, function family, tolerance,
+    maxbonddim, sweep strategy, nesting, normalisation, history length, pivot search — everything identical to the checker."""
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(2, 8))
+    localdims = [int(rng.integers(1, 6)) for _ in range(n)]
+    if all(d == 1 for d in localdims):
+        localdims[0] = 3
+    kind, params = [(O.F_LORENTZ, [1.0]), (O.F_HASH, [1.0, 0.7]), (O.F_SUM, [0.25])][int(rng.integers(0, 3))]
+    kw = dict(tolerance=float(10.0 ** -rng.integers(3, 13)), maxiter=int(rng.integers(1, 7)),
+              sweepstrategy=["backandforth", "forward"][int(rng.integers(0, 2))], strictlynested=bool(rng.integers(0, 2)),
+              normalizeerror=bool(rng.integers(0, 2)), ncheckhistory=int(rng.integers(1, 4)))
+    if rng.integers(0, 2):
+        kw["maxbonddim"] = int(rng.integers(1, 9))
+    rook = bool(rng.integers(0, 2))
+    piv = [[int(rng.integers(1, d + 1)) for d in localdims]]
+    f = O.Func(kind, params)
+    okw = dict(pivotsearch="rook", seed=seed) if rook else {}
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, **okw, **kw)
+    t = _native(mock, localdims, f, piv)
+    if rook:
+        t.set_pivotsearch("rook", seed)
+    ranks, errors = t.optimize(f.h, nsearchglobalpivot=0, **kw)
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+    assert t.stats()["nevals"] == o.stats()["nevals"]
