@@ -325,6 +325,10 @@ int tci_tci2_optimize(tci_tci2 t, tci_functor f, double tolerance, int64_t maxbo
  * call that changes the object.  Fails when the site tensors are invalidated (:206-220). */
 int tci_tci2_core(tci_tci2 t, int site, const double** d_core, int64_t* h_shape3);
 int tci_tci2_sitetensors_available(tci_tci2 t);
+/* evaluate(tci, indexset) src/abstracttensortrain.jl:328-342 at npoints multi-indices (h_points: npoints x nsites, 1-based; values
+ * to h_out) and sum(tci) :428-441, on the object's own site tensors (tci_tt_evaluate_f64 / tci_tt_sum_f64 underneath). */
+int tci_tci2_evaluate(tci_tci2 t, const int32_t* h_points, int64_t npoints, double* h_out);
+int tci_tci2_sum(tci_tci2 t, double* h_out);
 /* bonderrors (nsites-1), pivoterrors (query the count with h_pivoterrors = NULL first), maxsamplevalue; any may be NULL. */
 int tci_tci2_errors(tci_tci2 t, double* h_bonderrors, double* h_pivoterrors, int64_t* h_npivoterrors, double* h_maxsamplevalue);
 /* h_counts2 = {function evaluations, bond updates}; h_seconds4 = host wall time in {evaluation, rrLU, factors, index sets}. */

@@ -636,6 +636,20 @@ int find_global_pivots(tci_tci2 t, tci_functor f, double abstol, int nsearch, in
     return TCI_OK;
 }
 
+// device pointers / shapes / leading dimensions of the site tensors, as tci_tt_sum_f64 / tci_tt_evaluate_f64 take them
+int core_args(tci_tci2 t, std::vector<const double*>& ptrs, std::vector<int64_t>& shapes, std::vector<int64_t>& lds) {
+    const int N = t->N;
+    ptrs.resize((size_t)N); shapes.resize(3 * (size_t)N); lds.resize((size_t)N);
+    for (int b = 0; b < N; ++b) {
+        const Core& c = t->T[b];
+        if (!c.valid || c.chil * c.chir == 0)
+            return fail(t, TCI_ERR_INVALID, "site tensors are not available (call fillsitetensors! or a sweep first)");
+        ptrs[(size_t)b] = c.buf.p; shapes[3 * (size_t)b] = c.chil; shapes[3 * (size_t)b + 1] = c.d; shapes[3 * (size_t)b + 2] = c.chir;
+        lds[(size_t)b] = std::max<int64_t>(c.chil * c.d, 1);
+    }
+    return TCI_OK;
+}
+
 int addglobalpivots(tci_tci2 t, const int32_t* pivots, int64_t np) {                          // tensorci2.jl:335-357
     const int N = t->N;
     for (int64_t k = 0; k < np; ++k) {
@@ -855,6 +869,26 @@ int tci_tci2_core(tci_tci2 t, int site, const double** d_core, int64_t* h_shape3
     if (!c.valid) return fail(t, TCI_ERR_INVALID, "site tensors are not available (call fillsitetensors! or a sweep first)");
     if (d_core) *d_core = c.buf.p;
     if (h_shape3) { h_shape3[0] = c.chil; h_shape3[1] = c.d; h_shape3[2] = c.chir; }
+    return TCI_OK;
+}
+
+/* evaluate(tci, indexset) (src/abstracttensortrain.jl:328-342) for a batch of points, and sum(tci) (:428-441), on the object's
+ * own site tensors: with these a C or Julia caller gets from a device functor to an interpolated value or an integral without
+ * any other host library. */
+int tci_tci2_evaluate(tci_tci2 t, const int32_t* h_points, int64_t npoints, double* h_out) {
+    if (!t || npoints < 0 || (npoints > 0 && (!h_points || !h_out))) return TCI_ERR_INVALID;
+    std::vector<const double*> ptrs; std::vector<int64_t> shapes, lds;
+    int rc = core_args(t, ptrs, shapes, lds); if (rc) return rc;
+    if (npoints == 0) return TCI_OK;
+    TCI2_CALL(t, tci_tt_evaluate_f64(t->h, ptrs.data(), shapes.data(), lds.data(), t->N, h_points, npoints, h_out));
+    return TCI_OK;
+}
+
+int tci_tci2_sum(tci_tci2 t, double* h_out) {
+    if (!t || !h_out) return TCI_ERR_INVALID;
+    std::vector<const double*> ptrs; std::vector<int64_t> shapes, lds;
+    int rc = core_args(t, ptrs, shapes, lds); if (rc) return rc;
+    TCI2_CALL(t, tci_tt_sum_f64(t->h, ptrs.data(), shapes.data(), lds.data(), t->N, h_out));
     return TCI_OK;
 }
 

@@ -125,6 +125,18 @@ class NativeTCI2:
         self._check(self.L.tci_tci2_core(self._t, site, C.byref(ptr), p_i64(shape)))
         return ptr.value, tuple(int(v) for v in shape)
 
+    def evaluate(self, points):
+        """evaluate(tci, indexset) at many multi-indices (npoints x nsites, 1-based): numpy vector."""
+        tab, n = _table(points, len(self))
+        out = np.zeros(n)
+        self._check(self.L.tci_tci2_evaluate(self._t, p_i32(tab), C.c_int64(n), p_f64(out)))
+        return out
+
+    def sum(self):
+        out = C.c_double()
+        self._check(self.L.tci_tci2_sum(self._t, C.byref(out)))
+        return out.value
+
     def stats(self):
         counts, secs = np.zeros(2, dtype=np.int64), np.zeros(4)
         self._check(self.L.tci_tci2_stats(self._t, p_i64(counts), p_f64(secs)))

@@ -23,6 +23,7 @@ int orc_solve_right(const double* P, int64_t r, const double* B, int64_t q, doub
 int orc_batcheval(void* f, const int32_t* localdims, int nsites, const int32_t* left, int64_t nleft, int nl, const int32_t* right,
                   int64_t nright, int nr, int M, double* out);
 int orc_tt_evaluate(const double* cores, const int64_t* shapes, int nsites, const int32_t* idx, int64_t npoints, double* out);
+int orc_tt_sum(const double* cores, const int64_t* shapes, int nsites, double* out);
 }
 
 struct tci_context { std::string err; int64_t ncalls = 0; };
@@ -165,6 +166,17 @@ int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const in
         for (int64_t j = 0; j < cols; ++j) flat.insert(flat.end(), h_core_ptrs[b] + j * ld, h_core_ptrs[b] + j * ld + rows);
     }
     if (orc_tt_evaluate(flat.data(), h_shapes, nsites, h_indices, npoints, h_out)) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+    return TCI_OK;
+}
+
+int tci_tt_sum_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds, int nsites, double* h_out) {
+    h->ncalls++;
+    std::vector<double> flat;
+    for (int b = 0; b < nsites; ++b) {
+        const int64_t rows = h_shapes[3 * b] * h_shapes[3 * b + 1], cols = h_shapes[3 * b + 2], ld = h_lds ? h_lds[b] : rows;
+        for (int64_t j = 0; j < cols; ++j) flat.insert(flat.end(), h_core_ptrs[b] + j * ld, h_core_ptrs[b] + j * ld + rows);
+    }
+    if (orc_tt_sum(flat.data(), h_shapes, nsites, h_out)) return mfail(h, TCI_ERR_INVALID, orc_last_error());
     return TCI_OK;
 }
 

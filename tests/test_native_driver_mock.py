@@ -6,6 +6,7 @@ a bookkeeping bug: union/kronecker order, history extras, error merging, sweep o
 The GPU parity tests of the same driver on the real kernels are in tests/test_gpu_native_driver.py."""
 import ctypes as C
 import importlib.util
+import itertools
 import os
 import subprocess
 
@@ -336,3 +337,21 @@ def test_random_configurations_identical_to_oracle(mock, seed):
     np.testing.assert_array_equal(errors, oerrors)
     _same_state(t, o)
     assert t.stats()["nevals"] == o.stats()["nevals"]
+
+
+def test_evaluate_and_sum_on_the_object(mock):             # abstracttensortrain.jl:328-342, :428-441; test/test_tensortrain.jl:10-32
+    localdims = [6] * 4
+    f = O.Func(O.F_LORENTZ, [2.0])
+    t = _native(mock, localdims, f, [[1] * 4])
+    TCIError = _load("_lib").TCIError
+    with pytest.raises(TCIError, match="not available"):
+        t.sum()
+    t.optimize(f.h, tolerance=1e-12, nsearchglobalpivot=0)
+    pts = np.asarray(list(itertools.product(range(1, 7), repeat=4)), dtype=np.int32)
+    ref = np.array([f(p) for p in pts])
+    vals = t.evaluate(pts)
+    assert np.max(np.abs(vals - ref)) < 1e-10
+    assert t.sum() == pytest.approx(ref.sum(), rel=1e-10)
+    o, _, _ = O.crossinterpolate2(f, localdims, [[1] * 4], tolerance=1e-12)
+    np.testing.assert_array_equal(vals, O.tt_evaluate(o.sitetensors(), pts))
+    assert t.sum() == O.tt_sum(o.sitetensors())
