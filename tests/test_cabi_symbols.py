@@ -62,3 +62,20 @@ def test_host_index_helpers():
     assert tci_b200.convergencecriterion([4, 4, 4], [1.0, 1.0, 1.0], [0, 0, 0], 1e-4, 4, 3) is True
     assert tci_b200.forwardsweep("forward", 2) and tci_b200.forwardsweep("backandforth", 1)          # sweepstrategies.jl:41-50
     assert not tci_b200.forwardsweep("backandforth", 2)
+
+
+def test_header_is_plain_c_and_example_fails_loudly_without_a_device(tmp_path):
+    """include/tci_b200.h compiles as C99 (-pedantic) — the boundary is a C ABI, not a C++ one — and examples/c1_lorentz.c (the
+    whole of crossinterpolate2 + sum + evaluate from plain C) links against the library; without a CUDA device it stops at
+    tci_create with the "no CPU fallback" message."""
+    import subprocess
+    import torch
+    import tci_b200
+    exe = str(tmp_path / "c1_lorentz")
+    libdir = os.path.dirname(tci_b200.SO_PATH)
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "c1_lorentz.c"), "-L" + libdir, "-ltci_b200", "-Wl,-rpath," + libdir, "-o", exe])
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present: the example would run the full interpolation")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CPU fallback" in r.stderr
