@@ -12,10 +12,12 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_build", "libtci_oracle.so")
 
-F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE, F_HASH = range(8)
+F_CALLBACK, F_LORENTZ, F_QEXPSIN, F_QEXPPLUSSIN, F_SUM, F_QEXP2, F_DENSE, F_HASH, F_BATCHCB = range(9)
 INT64_MAX = np.iinfo(np.int64).max
 
 CALLBACK = C.CFUNCTYPE(C.c_double, C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
+BATCH_CALLBACK = C.CFUNCTYPE(None, C.POINTER(C.c_int32), C.c_int64, C.c_int32, C.POINTER(C.c_int32), C.c_int64, C.c_int32,
+                             C.c_int32, C.POINTER(C.c_double), C.c_void_p)
 
 
 def build(force=False):
@@ -123,7 +125,21 @@ class RRLU:
         return left, right
 
 
-def rrlu(A, maxrank=INT64_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True):
+def max_threads():
+    return int(lib().orc_max_threads())
+
+
+def rrlu(A, maxrank=INT64_MAX, reltol=1e-14, abstol=0.0, leftorthogonal=True, threads=1):
+    """rrlu (matrixlu.jl:455-463).  threads > 1 runs the same loop with the column ranges of the update and of the search
+    spread over host threads; every value and every decision is unchanged (see optimizerrlu_mt)."""
+    lib().orc_rrlu_set_threads(int(threads))
+    try:
+        return _rrlu(A, maxrank, reltol, abstol, leftorthogonal)
+    finally:
+        lib().orc_rrlu_set_threads(1)
+
+
+def _rrlu(A, maxrank, reltol, abstol, leftorthogonal):
     A = _f64(A)
     m, n = A.shape
     rmax = int(min(maxrank, m, n))
@@ -176,7 +192,9 @@ def solve_right(P, B):
 
 
 class Func:
-    """Target function handle: a built-in kind, a dense table, or a Python callback (1-based indices)."""
+    """Target function handle: a built-in kind, a dense table, a Python callback (1-based indices), or (F_BATCHCB) a batch
+    evaluator `callback(left, right, M) -> array of shape (len(left), d..., len(right))` with left/right as int32 tables —
+    the BatchEvaluator protocol of the reference (batcheval.jl:196-214)."""
 
     def __init__(self, kind, params=(), table=None, callback=None):
         self.kind = kind
@@ -194,6 +212,14 @@ class Func:
                 return float(callback([idx[i] for i in range(n)]))
             self._cb = CALLBACK(_tramp)
             cb = self._cb
+        if kind == F_BATCHCB:
+            def _btramp(left, nleft, nl, right, nright, nr, M, out, _user):
+                lt = np.ctypeslib.as_array(left, shape=(nleft, nl)).copy() if nl > 0 else np.zeros((nleft, 0), dtype=np.int32)
+                rt = np.ctypeslib.as_array(right, shape=(nright, nr)).copy() if nr > 0 else np.zeros((nright, 0), dtype=np.int32)
+                vals = np.asarray(callback(lt, rt, int(M)), dtype=np.float64).reshape(-1, order="F")
+                np.ctypeslib.as_array(out, shape=(vals.size,))[:] = vals
+            self._cb = BATCH_CALLBACK(_btramp)
+            cb = C.cast(self._cb, CALLBACK)
         self.h = C.c_void_p(lib().orc_func_create(kind, _p(p, C.c_double), len(p), _p(dims, C.c_int32), len(dims),
                                                   _p(tab, C.c_double), cb, None))
         if not self.h:
@@ -264,14 +290,18 @@ class TCI2:
         lib().orc_tci_set_pivotsearch(self.h, {"full": 0, "rook": 1}[pivotsearch], C.c_uint64(seed))
 
     def optimize(self, tolerance=1e-8, maxbonddim=INT64_MAX, maxiter=20, sweepstrategy="backandforth",
-                 normalizeerror=True, ncheckhistory=3, strictlynested=False, checkconvglobalpivot=True):
+                 normalizeerror=True, ncheckhistory=3, strictlynested=False, checkconvglobalpivot=True,
+                 nsearchglobalpivot=0, maxnglobalpivot=5, tolmarginglobalsearch=10.0, globalseed=0):
+        """optimize! (tensorci2.jl:1018-1172).  nsearchglobalpivot > 0 runs the DefaultGlobalPivotFinder with its random
+        starts drawn from the splitmix64 stream seeded with `globalseed` (the stream the product's `seed=` uses)."""
         ranks = np.zeros(maxiter, dtype=np.int64)
         errors = np.zeros(maxiter)
         niter = C.c_int()
-        _check(lib().orc_tci_optimize(self.h, C.c_double(tolerance), C.c_int64(int(maxbonddim)), maxiter,
-                                      0 if sweepstrategy == "forward" else 1, int(normalizeerror), ncheckhistory,
-                                      int(strictlynested), int(checkconvglobalpivot), _p(ranks, C.c_int64),
-                                      _p(errors, C.c_double), C.byref(niter)))
+        _check(lib().orc_tci_optimize_gp(self.h, C.c_double(tolerance), C.c_int64(int(maxbonddim)), maxiter,
+                                         0 if sweepstrategy == "forward" else 1, int(normalizeerror), ncheckhistory,
+                                         int(strictlynested), int(checkconvglobalpivot), int(nsearchglobalpivot),
+                                         int(maxnglobalpivot), C.c_double(tolmarginglobalsearch), C.c_uint64(int(globalseed)),
+                                         _p(ranks, C.c_int64), _p(errors, C.c_double), C.byref(niter)))
         return ranks[: niter.value].copy(), errors[: niter.value].copy()
 
     def updatepivots(self, b, leftorthogonal, reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX):
@@ -383,10 +413,12 @@ class TCI2:
 
 
 def crossinterpolate2(f, localdims, initialpivots=None, bondorder="sequential", pivotsearch="full", seed=0, **kw):
-    """crossinterpolate2 (tensorci2.jl:1313-1323) with nsearchglobalpivot=0."""
+    """crossinterpolate2 (tensorci2.jl:1313-1323); nsearchglobalpivot defaults to 0 here (the reference's default is 5).
+    `seed` starts both random streams (rook columns and global-pivot starts), like the product's `seed=`."""
     tci = TCI2(f, localdims, initialpivots)
     tci.set_bondorder(bondorder)
     tci.set_pivotsearch(pivotsearch, seed)
+    kw.setdefault("globalseed", seed)
     ranks, errors = tci.optimize(**kw)
     return tci, ranks, errors
 

@@ -27,6 +27,7 @@
 #include <functional>
 #include <limits>
 #include <map>
+#include <omp.h>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -175,6 +176,54 @@ static int optimizerrlu(RRLU& lu, Mat& A, int64_t maxrank, double reltol, double
     else                   { for (int64_t i = 0; i < r; ++i) lu.U(i, i) = 1.0; }
     if (lu.npivot >= std::min(A.m, A.n)) lu.error = 0.0;           // :391-393
     return 0;
+}
+
+// Thread-parallel execution of the SAME loop (matrixlu.jl:346-369) for big matrices (the 8192 x 8192 C2 workload takes
+// ~70 s on one thread).  The reference's loops are scalar Julia; nothing here changes a value or a decision: every element
+// of the trailing block gets the identical `a - x*y` (one multiply, one subtract), the search keeps per-thread winners over
+// contiguous column ranges with the same strict '>' scan and merges them in column order with strict '>', which is the
+// sequential first-maximum rule.  tests/test_oracle_golden.py checks it against the single-thread loop bit for bit.
+static int optimizerrlu_mt(RRLU& lu, Mat& A, int64_t maxrank, double reltol, double abstol, int nthreads) {
+    maxrank = std::min(maxrank, std::min(A.m, A.n));
+    double maxerror = 0.0;
+    const int64_t m = A.m, n = A.n;
+    struct alignas(64) Best { double v; int64_t r, c; };
+    std::vector<Best> best((size_t)nthreads);
+    while (lu.npivot < maxrank) {
+        const int64_t k = lu.npivot;
+#pragma omp parallel num_threads(nthreads)
+        {
+            const int t = omp_get_thread_num(), T = omp_get_num_threads();
+            const int64_t c0 = k + (n - k) * t / T, c1 = k + (n - k) * (t + 1) / T;
+            Best b{-std::numeric_limits<double>::infinity(), -1, -1};
+            for (int64_t c = c0; c < c1; ++c) {
+                const double* col = &A.a[(size_t)c * m];
+                for (int64_t r = k; r < m; ++r) { const double v = col[r] * col[r]; if (v > b.v) { b.v = v; b.r = r; b.c = c; } }
+            }
+            best[(size_t)t] = b;
+            if (t == 0) for (int u = T; u < nthreads; ++u) best[(size_t)u] = Best{-std::numeric_limits<double>::infinity(), -1, -1};
+        }
+        double bv = -std::numeric_limits<double>::infinity(); int64_t pr = k, pc = k;
+        for (int t = 0; t < nthreads; ++t) if (best[(size_t)t].r >= 0 && best[(size_t)t].v > bv) { bv = best[(size_t)t].v; pr = best[(size_t)t].r; pc = best[(size_t)t].c; }
+        lu.error = std::fabs(A(pr, pc));
+        if ((std::fabs(lu.error) < reltol * maxerror || std::fabs(lu.error) < abstol) && lu.npivot > 0) break;
+        maxerror = jl_max(maxerror, lu.error);
+        lu.npivot += 1;
+        swaprow(lu, A, k, pr);
+        swapcol(lu, A, k, pc);
+        const double piv = A(k, k);
+        if (lu.leftorthogonal) { for (int64_t i = k + 1; i < m; ++i) A(i, k) = A(i, k) / piv; }
+        else                   { for (int64_t j = k + 1; j < n; ++j) A(k, j) = A(k, j) / piv; }
+        const double* x = &A.a[(size_t)k * m];
+#pragma omp parallel for schedule(static) num_threads(nthreads)
+        for (int64_t j = k + 1; j < n; ++j) {
+            const double y = A(k, j);
+            double* col = &A.a[(size_t)j * m];
+            for (int64_t i = k + 1; i < m; ++i) col[i] = col[i] - x[i] * y;
+        }
+    }
+    // the extraction below is the tail of optimizerrlu (maxrank already reached or the stop rule fired): run it with no further pivots
+    return optimizerrlu(lu, A, lu.npivot, reltol, abstol) ;
 }
 
 static int rrlu_inplace(Mat& A, RRLU& lu, int64_t maxrank, double reltol, double abstol, bool leftorth) {
@@ -385,14 +434,21 @@ enum FuncKind {
     F_SUM = 4,            // p0 * sum v_i                         test_batcheval.jl:18
     F_QEXP2 = 5,          // exp(-p0 x) + p1 exp(-p2 x)           test_tensorci2.jl:63,:146
     F_DENSE = 6,          // column-major table lookup T[v...]    test_tensorci2.jl:29,:464
-    F_HASH = 7            // p0 * u(v) + p1 / (1 + sum v_i^2), u = integer hash of v in [-1, 1): a full-rank synthetic
+    F_HASH = 7,           // p0 * u(v) + p1 / (1 + sum v_i^2), u = integer hash of v in [-1, 1): a full-rank synthetic
                           // function (not in the reference) that drives every bond to maxbonddim (bench only)
+    F_BATCHCB = 8         // a BatchEvaluator (cachedtensortrain.jl:16-31, batcheval.jl:196-214): the host supplies whole
+                          // (left, right, M) batches.  Tests use it to feed the oracle the function VALUES the device
+                          // functor produced (hard part 1: libm and libdevice differ in the last ulp), so that
+                          // index sets can be compared bit for bit and the values separately.
 };
 static inline uint64_t splitmix64(uint64_t z) {
     z += 0x9e3779b97f4a7c15ULL; z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
     return z ^ (z >> 31);
 }
 typedef double (*orc_callback)(const int32_t* idx, int32_t n, void* user);
+// out[i + c*nleft + j*nleft*ncent] = f([left_i..., c..., right_j...]); tables are row-major (count x len), 1-based values
+typedef void (*orc_batch_callback)(const int32_t* left, int64_t nleft, int32_t nl, const int32_t* right, int64_t nright, int32_t nr,
+                                   int32_t M, double* out, void* user);
 
 struct Func {
     int kind = F_LORENTZ;
@@ -400,6 +456,7 @@ struct Func {
     std::vector<int32_t> dims;                     // F_DENSE: table dims
     std::vector<double> table;
     orc_callback cb = nullptr; void* user = nullptr;
+    orc_batch_callback bcb = nullptr;
 
     // quantics coordinate x = sum_i (b_i - 1) 2^{-i}, i = 1..R  (bit 1 most significant;
     // the in-tree statement is test/test_tensorci2.jl:66, x = (i-1)/2^R)
@@ -411,6 +468,7 @@ struct Func {
     double operator()(const int32_t* v, int n) const {
         switch (kind) {
         case F_CALLBACK: return cb(v, n, user);
+        case F_BATCHCB: { double out = 0.0; bcb(v, 1, n, nullptr, 1, 0, 0, &out, user); return out; }   // point form of a BatchEvaluator
         case F_LORENTZ: { int64_t s = 0; for (int i = 0; i < n; ++i) s += (int64_t)v[i] * v[i];
                           return p[0] / (double)(1 + s); }
         case F_QEXPSIN: { double x = qx(v, n);
@@ -449,6 +507,13 @@ static std::vector<double> batchevaluate(const Func& f, const std::vector<int32_
     shape->push_back(nI);
     for (int x = 0; x < M; ++x) shape->push_back(localdims[nl + x]);
     shape->push_back(nJ);
+    if (f.kind == F_BATCHCB) {                                                       // batcheval.jl:196-214: the evaluator gets the batch
+        std::vector<int32_t> lt((size_t)nI * nl), rt((size_t)nJ * nr);
+        for (int64_t i = 0; i < nI; ++i) std::copy(left[i].begin(), left[i].end(), lt.begin() + (size_t)i * nl);
+        for (int64_t j = 0; j < nJ; ++j) std::copy(right[j].begin(), right[j].end(), rt.begin() + (size_t)j * nr);
+        f.bcb(lt.data(), nI, nl, rt.data(), nJ, nr, M, res.data(), f.user);
+        return res;
+    }
 #pragma omp parallel
     {
         std::vector<int32_t> idx(L);
@@ -509,6 +574,7 @@ struct TCI2 {
                                                    // (the parallel-bond schedule of the product; NOT in the reference)
     int pivotsearch = 0;                           // 0: :full, 1: :rook (:863-905)
     Rng rng;                                       // stream behind pushrandomsubset! in the rook search
+    Rng grng;                                      // stream behind the random starts of the global pivot finder
     int64_t nevals = 0;                            // bookkeeping for the bench only
     double t_eval = 0, t_lu = 0;                   // seconds spent in Pi fill and in MatrixLUCI
 
@@ -794,13 +860,48 @@ static bool convergencecriterion(const std::vector<int64_t>& ranks, const std::v
 
 struct OptimizeResult { std::vector<int64_t> ranks; std::vector<double> errors; int status = 0; };
 
-// optimize! — :1018-1172 with the default global pivot finder configured to nsearchglobalpivot=0
-// (globalpivotfinder.jl:205-264 then returns no pivots; the RNG it uses cannot be restated).
+// DefaultGlobalPivotFinder — globalpivotfinder.jl:205-264: nsearch random starts; from each, one line search per site over
+// |f - tt| (strict '>' keeps the first maximum, the start's own coordinate is restored after each site); a start contributes its
+// best point when that error exceeds abstol * tolmarginglobalsearch; the list is cut to maxnglobalpivot.  The reference draws
+// the starts from Julia's default RNG (`rand(rng, 1:d)`, :219), which cannot be restated; oracle and product share the seeded
+// splitmix64 stream `grng` instead (all starts are drawn before any search, start-major, site-minor, as in :219).  f is read
+// through ONE batch (left set = the candidate points, right set = the empty index): the values are those of the point calls.
+static IndexList find_global_pivots(TCI2& tci, const Func& f, double abstol, int nsearch, int maxnglobalpivot, double tolmargin) {
+    const int L = tci.n();
+    IndexList found;
+    if (nsearch <= 0) return found;
+    IndexList initial((size_t)nsearch, MultiIndex((size_t)L));
+    for (int s = 0; s < nsearch; ++s)
+        for (int p = 0; p < L; ++p) initial[(size_t)s][(size_t)p] = 1 + (int32_t)tci.grng.randint(tci.localdims[(size_t)p]);
+    IndexList pts;
+    for (const auto& point : initial)
+        for (int p = 0; p < L; ++p)
+            for (int v = 1; v <= tci.localdims[(size_t)p]; ++v) { MultiIndex c(point); c[(size_t)p] = v; pts.push_back(c); }
+    std::vector<int64_t> shape;
+    const std::vector<double> fv = batchevaluate(f, tci.localdims, pts, IndexList(1, MultiIndex()), 0, &shape);
+    size_t k = 0;
+    for (const auto& point : initial) {
+        double best_error = 0.0;
+        MultiIndex best_point(point);
+        for (int p = 0; p < L; ++p)
+            for (int v = 1; v <= tci.localdims[(size_t)p]; ++v, ++k) {
+                const double error = std::fabs(fv[k] - tci.evaluate(pts[k]));              // :236
+                if (error > best_error) { best_error = error; best_point = pts[k]; }       // :239-242
+            }
+        if (best_error > abstol * tolmargin) found.push_back(best_point);                  // :249-251
+    }
+    if ((int64_t)found.size() > maxnglobalpivot) found.resize((size_t)maxnglobalpivot);    // :255-257
+    return found;
+}
+
+// optimize! — :1018-1172 with the DefaultGlobalPivotFinder (nsearchglobalpivot = 0 turns the search off).
 static OptimizeResult optimize(TCI2& tci, const Func& f, double tol, int64_t maxbonddim, int maxiter,
                                int sweepstrategy, bool normalizeerror, int ncheckhistory, bool strictlynested,
-                               bool checkconvglobalpivot) {
+                               bool checkconvglobalpivot, int nsearchglobalpivot = 0, int maxnglobalpivot = 5,
+                               double tolmarginglobalsearch = 10.0) {
     OptimizeResult R;
     std::vector<int64_t> nglobalpivots;
+    if (nsearchglobalpivot > 0 && nsearchglobalpivot < maxnglobalpivot) throw std::invalid_argument("nsearchglobalpivot < maxnglobalpivot!");   // :1056-1058
     if (maxbonddim >= std::numeric_limits<int64_t>::max() && tol <= 0)
         throw std::invalid_argument("Specify either tolerance > 0 or some maxbonddim; otherwise, the convergence criterion is not reachable!");
     for (int iter = 1; iter <= maxiter; ++iter) {
@@ -809,7 +910,9 @@ static OptimizeResult optimize(TCI2& tci, const Func& f, double tol, int64_t max
         R.status = tci.sweep2site(f, 2, 1, abstol, maxbonddim, sweepstrategy, strictlynested, true);   // :1098-1108
         if (R.status) return R;
         R.errors.push_back(tci.pivoterror());                                      // :1118
-        nglobalpivots.push_back(0);                                                // :1126-1133, nsearch = 0
+        const IndexList found = find_global_pivots(tci, f, abstol, nsearchglobalpivot, maxnglobalpivot, tolmarginglobalsearch);   // :1126-1131
+        tci.addglobalpivots(found);                                                // :1132
+        nglobalpivots.push_back((int64_t)found.size());                            // :1133
         R.ranks.push_back(tci.rank());                                             // :1140
         if (convergencecriterion(R.ranks, R.errors, nglobalpivots, abstol, maxbonddim, ncheckhistory, checkconvglobalpivot))
             break;                                                                 // :1147-1154
@@ -888,6 +991,7 @@ static Func make_func(int kind, const double* params, int nparams, const int32_t
         f.table.assign(table, table + tot);
     }
     f.cb = cb; f.user = user;
+    if (kind == F_BATCHCB) { f.bcb = (orc_batch_callback)(void*)cb; f.cb = nullptr; }
     return f;
 }
 static IndexList to_list(const int32_t* flat, int64_t count, int len) {   // row-major table: count rows of `len` ints
@@ -906,6 +1010,11 @@ int orc_submatrixargmax(const double* A, int64_t lda, int mode, const int64_t* r
     ORC_TRY submatrixargmax(A, lda, mode, rows, nrows, cols, ncols, outr, outc); return 0; ORC_CATCH(-10)
 }
 
+// Threads the next orc_rrlu calls of this thread use (1 = the plain scalar loop, the reference's execution model).
+static thread_local int g_rrlu_threads = 1;
+void orc_rrlu_set_threads(int n) { g_rrlu_threads = n < 1 ? 1 : n; }
+int orc_max_threads() { return omp_get_max_threads(); }
+
 // rrlu (copies A).  L is m x ldl_cols (first npivot columns valid), U is maxr x n with leading dim ldu.
 // pivoterrors must hold min(maxrank,m,n)+1 doubles; returns npivot+1 entries.
 int orc_rrlu(const double* A, int64_t m, int64_t n, int64_t lda, int64_t maxrank, double reltol, double abstol,
@@ -915,7 +1024,16 @@ int orc_rrlu(const double* A, int64_t m, int64_t n, int64_t lda, int64_t maxrank
     Mat W(m, n);
     for (int64_t j = 0; j < n; ++j) std::memcpy(&W.a[(size_t)j * m], A + (size_t)j * lda, sizeof(double) * m);
     RRLU lu;
-    int st = rrlu_inplace(W, lu, maxrank, reltol, abstol, leftorthogonal != 0);
+    int st;
+    if (g_rrlu_threads > 1) {
+        lu.leftorthogonal = leftorthogonal != 0;
+        lu.rowperm.resize((size_t)m); lu.colperm.resize((size_t)n);
+        for (int64_t i = 0; i < m; ++i) lu.rowperm[(size_t)i] = i + 1;
+        for (int64_t j = 0; j < n; ++j) lu.colperm[(size_t)j] = j + 1;
+        st = optimizerrlu_mt(lu, W, maxrank, reltol, abstol, g_rrlu_threads);
+    } else {
+        st = rrlu_inplace(W, lu, maxrank, reltol, abstol, leftorthogonal != 0);
+    }
     *npivot = lu.npivot; *error = lu.error;
     std::copy(lu.rowperm.begin(), lu.rowperm.end(), rowperm);
     std::copy(lu.colperm.begin(), lu.colperm.end(), colperm);
@@ -1021,13 +1139,25 @@ void orc_tci_set_bondorder(void* h, int v) { ((OrcTCI*)h)->tci.bondorder = v; }
 void orc_tci_set_pivotsearch(void* h, int rook, uint64_t seed) { ((OrcTCI*)h)->tci.pivotsearch = rook; ((OrcTCI*)h)->tci.rng.s = seed; }
 
 // optimize!: ranks/errors must hold maxiter entries; *niter receives the number written.
+int orc_tci_optimize_gp(void* h_, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,
+                        int ncheckhistory, int strictlynested, int checkconvglobalpivot, int nsearchglobalpivot, int maxnglobalpivot,
+                        double tolmarginglobalsearch, uint64_t seed, int64_t* ranks, double* errors, int* niter);
 int orc_tci_optimize(void* h_, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,
                      int ncheckhistory, int strictlynested, int checkconvglobalpivot,
                      int64_t* ranks, double* errors, int* niter) {
+    return orc_tci_optimize_gp(h_, tolerance, maxbonddim, maxiter, sweepstrategy, normalizeerror, ncheckhistory, strictlynested,
+                               checkconvglobalpivot, 0, 5, 10.0, 0, ranks, errors, niter);
+}
+// the same with the DefaultGlobalPivotFinder: nsearchglobalpivot starts per iteration drawn from the stream seeded with `seed`
+int orc_tci_optimize_gp(void* h_, double tolerance, int64_t maxbonddim, int maxiter, int sweepstrategy, int normalizeerror,
+                        int ncheckhistory, int strictlynested, int checkconvglobalpivot, int nsearchglobalpivot, int maxnglobalpivot,
+                        double tolmarginglobalsearch, uint64_t seed, int64_t* ranks, double* errors, int* niter) {
     ORC_TRY
     OrcTCI* h = (OrcTCI*)h_;
+    h->tci.grng.s = seed;
     OptimizeResult R = optimize(h->tci, *h->f, tolerance, maxbonddim, maxiter, sweepstrategy, normalizeerror != 0,
-                                ncheckhistory, strictlynested != 0, checkconvglobalpivot != 0);
+                                ncheckhistory, strictlynested != 0, checkconvglobalpivot != 0, nsearchglobalpivot, maxnglobalpivot,
+                                tolmarginglobalsearch);
     *niter = (int)R.ranks.size();
     std::copy(R.ranks.begin(), R.ranks.end(), ranks);
     std::copy(R.errors.begin(), R.errors.end(), errors);

@@ -161,6 +161,33 @@ def test_global_pivot_search_finds_hidden_feature(mock):
     assert Nat.STRATEGY["backandforth"] == 1
 
 
+GLOBAL = [
+    ("hidden_feature", 7, [4] * 6, dict(tolerance=1e-10, nsearchglobalpivot=40, maxnglobalpivot=5)),
+    ("hidden_feature_defaults", 3, [4] * 6, dict(tolerance=1e-10, nsearchglobalpivot=5, maxnglobalpivot=5)),
+    ("hidden_feature_margin", 11, [4] * 6, dict(tolerance=1e-6, nsearchglobalpivot=20, maxnglobalpivot=3, tolmarginglobalsearch=2.0)),
+]
+
+
+@pytest.mark.parametrize("name,seed,localdims,kw", GLOBAL, ids=[c[0] for c in GLOBAL])
+def test_global_pivot_finder_identical_to_oracle(mock, name, seed, localdims, kw):
+    """DefaultGlobalPivotFinder (globalpivotfinder.jl:205-264) in the driver against the checker's restatement on the shared
+    seeded stream: the same starts, the same found pivots, hence identical index sets, ranks, errors and tensors."""
+    table = np.ones(localdims) * 0.5
+    table[:, 3, :, :, 3, :] = 5.0
+    table[2, :, 1, :, :, 0] += 0.25
+    f = O.Func(O.F_DENSE, table=table)
+    piv = [[1] * len(localdims)]
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, seed=seed, **kw)
+    t = _native(mock, localdims, f, piv)
+    t.seed(seed)
+    ranks, errors = t.optimize(f.h, **kw)
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+    o0, r0, _ = O.crossinterpolate2(f, localdims, piv, tolerance=kw["tolerance"])
+    assert o.rank() >= o0.rank()
+
+
 def test_errors_mirror_the_reference(mock):
     L, h = mock
     Nat = _load("native")

@@ -126,3 +126,47 @@ def test_solve_right():                                 # tensorci2.jl:626
     rng = np.random.default_rng(3)
     P, B = rng.random((6, 6)) + np.eye(6), rng.random((9, 6))
     np.testing.assert_allclose(O.solve_right(P, B) @ P, B, rtol=1e-12, atol=1e-13)
+
+
+def test_threaded_rrlu_is_the_same_loop():
+    """optimizerrlu_mt (the loop of matrixlu.jl:346-369 with the column ranges spread over host threads) against the scalar
+    loop: permutations, pivot errors, L, U bit for bit — full rank, low rank, ties, maxrank and abstol stops, both orientations."""
+    rng = np.random.default_rng(5)
+    mats = [rng.standard_normal((97, 113)), rng.standard_normal((150, 20)) @ rng.standard_normal((20, 90)),
+            np.ones((40, 33)), np.round(rng.standard_normal((64, 64)) * 2) / 2, np.eye(17)]
+    for A in mats:
+        for kw in (dict(), dict(maxrank=9), dict(abstol=0.5), dict(leftorthogonal=False), dict(reltol=1e-3)):
+            a = O.rrlu(A, **kw)
+            for nt in (2, 5):
+                b = O.rrlu(A, threads=nt, **kw)
+                assert a.npivot == b.npivot and (a.error == b.error or (np.isnan(a.error) and np.isnan(b.error)))
+                np.testing.assert_array_equal(a.rowpermutation, b.rowpermutation)
+                np.testing.assert_array_equal(a.colpermutation, b.colpermutation)
+                np.testing.assert_array_equal(a.L, b.L)
+                np.testing.assert_array_equal(a.U, b.U)
+                np.testing.assert_array_equal(a.pivoterrors(), b.pivoterrors())
+
+
+def test_batch_callback_functor_matches_builtin():
+    """F_BATCHCB (the BatchEvaluator protocol, batcheval.jl:196-214): an oracle run fed with externally produced batches is the
+    same run as the built-in functor's — the mechanism the GPU tests use to hand the oracle device-evaluated values."""
+    ld = [2] * 12
+    f0 = O.Func(O.F_QEXPSIN, [10.0, 100.0, 1.1])
+    calls = []
+
+    def cb(left, right, M):
+        calls.append((left.shape, right.shape, M))
+        return O.batchevaluate(f0, ld, [list(r) for r in left], [list(r) for r in right], M)
+
+    fb = O.Func(O.F_BATCHCB, callback=cb)
+    piv = [[2, 1] * 6]
+    assert fb(piv[0]) == f0(piv[0])
+    a, ra, ea = O.crossinterpolate2(f0, ld, piv, tolerance=1e-10, nsearchglobalpivot=5, seed=3)
+    b, rb, eb = O.crossinterpolate2(fb, ld, piv, tolerance=1e-10, nsearchglobalpivot=5, seed=3)
+    np.testing.assert_array_equal(ra, rb)
+    np.testing.assert_array_equal(ea, eb)
+    for s in range(1, 13):
+        np.testing.assert_array_equal(a.Iset(s), b.Iset(s))
+        np.testing.assert_array_equal(a.Jset(s), b.Jset(s))
+        np.testing.assert_array_equal(a.sitetensor(s), b.sitetensor(s))
+    assert any(M == 1 for _, _, M in calls) and any(M == 0 for _, _, M in calls)
