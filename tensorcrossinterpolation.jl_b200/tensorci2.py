@@ -544,6 +544,9 @@ def reconstractglobalpivotsfromijset(localdims, Isets, Jsets):     # tensorci2.j
     return piv
 
 
+ENGINES = ("python", "native")
+
+
 def convergencecriterion(ranks, errors, nglobalpivots, tolerance, maxbonddim, ncheckhistory, checkconvglobalpivot=True):
     """tensorci2.jl:947-966."""
     if len(errors) < ncheckhistory:
@@ -582,7 +585,10 @@ class DefaultGlobalPivotFinder:
         found = []
         if self.nsearch <= 0:
             return found
-        starts = [[int(rng.integers(1, input.localdims[p] + 1)) for p in range(L)] for _ in range(self.nsearch)]
+        if hasattr(rng, "randint") and hasattr(rng, "next"):       # matrixlu.Rng: the seeded stream the compiled driver and the CPU checker use
+            starts = [[1 + int(rng.randint(input.localdims[p])) for p in range(L)] for _ in range(self.nsearch)]
+        else:
+            starts = [[int(rng.integers(1, input.localdims[p] + 1)) for p in range(L)] for _ in range(self.nsearch)]
         pts = []
         for point in starts:                                # globalpivotfinder.jl:223-246: vary one site at a time
             for p in range(L):
@@ -779,7 +785,9 @@ def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     `engine` (not in the reference): "native" hands the optimize! loop to the compiled sweep driver (fewer microseconds of host
     work per bond, identical kernels and results), "python" runs it in this module; the default "auto" takes the compiled
     driver whenever it covers the call (device functor, one GPU, no Python-side finder / rng / verbosity)."""
-    seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): rook-search stream
+    seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): starts the two
+                                                            # splitmix64 streams (rook columns, global-pivot starts) for every engine;
+                                                            # without it the Python engine's finder draws from an unseeded numpy RNG
     engine = kwargs.pop("engine", "auto")
     if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module
         engine = "native" if _native_eligible(f, kwargs) else "python"
@@ -791,5 +799,7 @@ def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     if seed is not None:
         from .matrixlu import Rng
         tci.rng = Rng(seed)
+        if kwargs.get("rng") is None:                       # `seed` means the same for every engine: it also starts the stream of
+            kwargs["rng"] = Rng(seed)                       # the global pivot finder's random starts (tci_tci2_seed in the driver)
     ranks, errors = optimize(tci, f, **kwargs)
     return tci, ranks, errors

@@ -151,11 +151,17 @@ def test_native_global_pivot_search(tci):
 
 
 def test_native_quantics_c4_small(tci):
+    """R=16 quantics through the compiled driver; the oracle consumes the device-evaluated values (see test_gpu_baseline_configs)."""
     R = 16
     f, g = tci.QuanticsExpPlusSin([2] * R), O.Func(O.F_QEXPPLUSSIN, [1.0, 1e-3, 1000.0])
+    fed = O.Func(O.F_BATCHCB, callback=lambda left, right, M: f(left, right, M))
     t, ranks, errors = tci.crossinterpolate2(f, [2] * R, tolerance=1e-10, nsearchglobalpivot=0, maxbonddim=64, engine="native")
-    o, oranks, oerrors = O.crossinterpolate2(g, [2] * R, tolerance=1e-10, maxbonddim=64)
-    assert abs(int(ranks[-1]) - int(oranks[-1])) <= 1
+    o, oranks, oerrors = O.crossinterpolate2(fed, [2] * R, tolerance=1e-10, maxbonddim=64)
+    assert list(ranks) == list(oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    for b in range(1, R + 1):
+        np.testing.assert_array_equal(t.Iset[b - 1], o.Iset(b))
+        np.testing.assert_array_equal(t.Jset[b - 1], o.Jset(b))
     pts = np.random.default_rng(1).integers(1, 3, size=(500, R))
     ref = np.array([g(p) for p in pts])
     assert np.max(np.abs(t.evaluate_batch(pts) - ref)) < 1e-7
