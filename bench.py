@@ -137,8 +137,12 @@ def cpu_rrlu(A_host, steps, threads):
 
 
 def host_threads():
-    from oracle import oracle as O
-    return max(1, min(O.max_threads(), os.cpu_count() or 1))
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1; the oracle's loops take an explicit thread
+    count, so that setting does not apply)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 def run_reference(args):
