@@ -271,6 +271,29 @@ int tci_tt_sum_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t
 int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t* h_shapes, const int64_t* h_lds,
                         int nsites, const int32_t* h_indices, int64_t npoints, double* h_out);
 
+/* ---- Device-resident sweeps (csrc/sweep.cu): the bond loop of a half-sweep in ONE launch ----------------------------------
+ * Replaces the loop `for bondindex in 1:n-1 updatepivots!(...)` of sweep2site! (src/tensorci2.jl:1226-1250; each iteration =
+ * updatepivots! :825-930, :full branch: kronecker/union :842-843, filltensor :848-852, updatemaxsample! :855, MatrixLUCI ->
+ * rrlu src/matrixlu.jl:346-396, new Iset[b+1]/Jset[b] :915-916, pivoterrors) for Pi matrices that fit shared memory (one CTA:
+ * ~210 KB; a cluster of 8 CTAs with distributed shared memory: ~1.7 MB).  The host keeps the index sets between launches and
+ * exchanges them as int32 arenas:
+ *   h_in  (in_words):  [0] N  [1] forward (1/0)  [2] s0  [3] s1  — steps [s0, s1) of the sweep order, bond b0 = forward ? s : N-2-s
+ *                      (0-based) —  [4] maxbonddim (<= 0: none)  [5] useextra  [6..7] 0;  localdims[N];  per site b (8 words):
+ *                      nI, offI, nJ, offJ, nXI, offXI, nXJ, offXJ — counts and word offsets of Iset[b] (rows of length b),
+ *                      Jset[b] (rows of length N-b-1) and of the history entries used as extraIset / extraJset; then the tables
+ *                      (row-major, 1-based values).
+ *   h_out (capacity out_cap_words, *h_used_words written): [0] status — 0 all steps done, 1 stopped before step [1] because
+ *                      its Pi does not fit (run that bond through tci_tci2_updatepivots-style calls and continue), 2 / 3
+ *                      "lu.L / lu.U contains NaNs" at step [1];  [2] words used;  per step s-s0 (6 words at 8 + 6 (s-s0)):
+ *                      r, offA (new Iset[b0+1]: r rows of length b0+1), offB (new Jset[b0]: r rows of length N-b0-1), offE
+ *                      (pivoterrors(luci): r+1 doubles, 8-byte aligned), m, n (the size of that bond's Pi).
+ * reltol / abstol: the rrlu tolerances of every bond (sweep2site! passes reltol = 1e-14, src/tensorci2.jl:1236);
+ * leftorthogonal = forward.  max |f| of every evaluated element is merged into d_acc16 (see tci_batcheval_acc_f64).
+ * Built-in functor kinds only (tci_dsweep_supported); results are bit-identical to the per-bond entry points. */
+int tci_dsweep_supported(tci_handle h, tci_functor f);
+int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
+                             void* d_acc16, int32_t* h_out, int64_t out_cap_words, int64_t* h_used_words);
+
 /* ---- Compiled host driver of the TensorCI2 sweeps (csrc/tci2_driver.cpp) -------------------------------------------------
  * The reference keeps sweep strategy, index-set bookkeeping and convergence control in its host language and so does this
  * library's boundary: a Julia host calls the entry points above once per bond.  For hosts whose per-call overhead is large
@@ -290,6 +313,10 @@ const char* tci_tci2_last_error(tci_tci2 t);
 /* Seed of the global pivot finder's random starts (the reference draws from Julia's default RNG, which has no portable
  * restatement: global pivots are not comparable with a Julia run). */
 int tci_tci2_seed(tci_tci2 t, uint64_t seed);
+/* engine 0 (default): one C-ABI call per bond phase (batch evaluation, rrLU, factors).  engine 1: half-sweeps whose Pi matrices
+ * fit shared memory run as ONE launch each (tci_dsweep_halfsweep_f64); bonds that do not fit, the rook search and plugin
+ * functors take the per-bond calls.  Index sets, ranks and errors are identical either way. */
+int tci_tci2_set_engine(tci_tci2 t, int engine);
 /* Pivot search strategy of updatepivots! (and therefore of sweep2site! / optimize!): rook = 0 is :full (the default), 1 is :rook
  * (src/tensorci2.jl:863-905 -> arrlu src/matrixlu.jl:500-569 over SubMatrix strips :764-804: Pi is never formed).  `seed` starts
  * the stream behind pushrandomsubset! (src/util.jl:173-219; Julia's global RNG in the reference). */

@@ -1038,8 +1038,8 @@ int orc_rrlu(const double* A, int64_t m, int64_t n, int64_t lda, int64_t maxrank
     std::copy(lu.rowperm.begin(), lu.rowperm.end(), rowperm);
     std::copy(lu.colperm.begin(), lu.colperm.end(), colperm);
     if (st) return st;
-    for (int64_t j = 0; j < lu.npivot; ++j) std::memcpy(L + (size_t)j * ldl, &lu.L.a[(size_t)j * m], sizeof(double) * m);
-    for (int64_t j = 0; j < n; ++j) for (int64_t i = 0; i < lu.npivot; ++i) U[(size_t)j * ldu + i] = lu.U(i, j);
+    if (L) for (int64_t j = 0; j < lu.npivot; ++j) std::memcpy(L + (size_t)j * ldl, &lu.L.a[(size_t)j * m], sizeof(double) * m);
+    if (U) for (int64_t j = 0; j < n; ++j) for (int64_t i = 0; i < lu.npivot; ++i) U[(size_t)j * ldu + i] = lu.U(i, j);
     auto pe = lu_pivoterrors(lu);
     std::copy(pe.begin(), pe.end(), pivoterrors);
     return 0;

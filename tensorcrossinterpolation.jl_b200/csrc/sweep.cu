@@ -1,0 +1,621 @@
+// sweep.cu — device-resident TensorCI2 sweeps: a whole HALF-SWEEP (every bond in order) is ONE kernel launch.
+//
+// For the low-rank functions the reference is quoted on (README Lorentzian: rank 12; 20-d Lorentzian: rank 18; quantics
+// R = 40: rank 17) a Pi matrix has 34^2 ... 360^2 entries and a half-sweep is a chain of N - 1 dependent bond updates of a
+// few microseconds each.  Driving that chain from the host — per bond: upload two index tables, K1, rrLU, read the pivots
+// back, build the next bond's index sets — costs a launch latency and a host synchronisation per bond, more than the
+// arithmetic.  Here the bond loop of sweep2site! (src/tensorci2.jl:1226-1250) runs on the device:
+//
+//   per bond b (tensorci2.jl:825-930, :full branch)          where
+//   -------------------------------------------------------  ----------------------------------------------------------
+//   Icombined = union(kronecker(Iset[b], d_b), extraIset)    never materialised: a row of Pi is (I row, site digit) or a
+//   Jcombined = union(kronecker(d_b+1, Jset[b+1]), extraJ)   kept extra; first-seen union = "extra whose prefix is not in
+//                                                            Iset[b]" (the sets hold unique rows), order kept by a scan
+//   Pi = f(Icombined x Jcombined), updatemaxsample!          monoid functor states per row / per column (functors.h), one
+//                                                            merge + finish per element, straight into SHARED memory
+//   MatrixLUCI(Pi) -> rrlu (matrixlu.jl:346-396)             in shared memory, WITHOUT moving data: rows / columns keep
+//                                                            their physical place and two position maps simulate the
+//                                                            reference's swaps (the tie rule of submatrixargmax :46-87 is
+//                                                            evaluated on positions, i.e. in swapped coordinates); every
+//                                                            element gets the identical `a - x*y` (one multiply, one
+//                                                            subtract, IEEE division for x), so pivots, errors and index
+//                                                            sets are bit-identical to the step kernels of rrlu.cu
+//   Iset[b+1] = Icombined[rowindices], Jset[b] = ...          rows gathered from the tables into the output arena; the
+//                                                            functor states of the chosen rows are carried to the next
+//                                                            bond (no re-fold of the set that moves with the sweep)
+//
+// Per pivot: two block barriers (winner partials | scaled pivot column), a warp-level argmax in three redux.sync + one
+// ballot (64-bit key = bits(|a|^2) + 1, then the smallest (column position, row position) among equals), no swap traffic,
+// no extraction inside the loop: everything the factorisation defines stays where it was computed.
+//
+// Cluster variant (CS = 8 CTAs, distributed shared memory) for Pi of a few hundred KB to ~1.7 MB (the 20-d Lorentzian's
+// 360^2): columns are dealt round-robin to the CTAs; per pivot every CTA publishes its best candidate (32-byte record
+// into every peer's shared memory) TOGETHER with that candidate's scaled column (a global scratch slot, L2-resident), so
+// ONE cluster barrier per pivot decides the winner and makes its column visible.
+//
+// The host (csrc/tci2_driver.cpp, or a Julia caller) stays the owner of the index sets between launches: it packs them
+// into one int32 arena, gets one arena back.  tci_dsweep_* are declared in include/tci_b200.h.
+#include "context.h"
+#include "functors.h"
+#include <cooperative_groups.h>
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace cg = cooperative_groups;
+using namespace tci_functors;
+
+namespace {
+
+// ---- arena formats (int32 words) ------------------------------------------------------------------------------------
+// input:  [0] N  [1] forward  [2] s0  [3] s1 (steps [s0, s1) of the sweep order; bond b0 = forward ? s : N-2-s)
+//         [4] maxbonddim (<= 0: none)  [5] useextra  [6] reserved  [7] reserved
+//         localdims[N]
+//         per site b: nI, offI, nJ, offJ, nXI, offXI, nXJ, offXJ      (Iset[b] rows of length b, Jset[b] rows of length N-b-1,
+//                                                                      extraIset / extraJset = the history entries, same lengths)
+//         tables (row-major, 1-based values)
+// output: [0] status (0 ok, 1 stopped: step [1] does not fit, 2 lu.L contains NaNs, 3 lu.U contains NaNs at step [1])
+//         [1] next step  [2] words used  [3..7] reserved
+//         per step (s - s0), 6 words: r, offA (new Iset[b0+1], r rows of length b0+1), offB (new Jset[b0], rows of length
+//                            N-b0-1), offE (pivoterrors(luci): r+1 doubles at an even word offset), m, n (size of Pi)
+//         data
+constexpr int kHdr = 8;
+constexpr int kDesc = 8;
+constexpr int kStepRec = 6;
+constexpr int kRMax = 512;                   // carried functor states (rows of the set that moves with the sweep)
+constexpr int kMaxCS = 8;
+constexpr unsigned FULL = 0xffffffffu;
+
+struct alignas(16) Win {                     // argmax candidate: key = bits(|a|^2) + 1 (0: none), pos = colpos << 16 | rowpos
+    unsigned long long key;
+    double x;
+    unsigned pos;
+    int i, j, pad;
+};
+
+__device__ __forceinline__ void warp_argmax(Win& w) {
+    const unsigned hi = (unsigned)(w.key >> 32), lo = (unsigned)w.key;
+    const unsigned mhi = __reduce_max_sync(FULL, hi);
+    const unsigned mlo = __reduce_max_sync(FULL, hi == mhi ? lo : 0u);
+    const bool eq = hi == mhi && lo == mlo;
+    const unsigned mpos = __reduce_min_sync(FULL, eq ? w.pos : 0xffffffffu);
+    const unsigned b = __ballot_sync(FULL, eq && w.pos == mpos);
+    const int src = __ffs(b) - 1;
+    w.key = ((unsigned long long)mhi << 32) | mlo;
+    w.pos = mpos;
+    w.x = __shfl_sync(FULL, w.x, src);
+    w.i = __shfl_sync(FULL, w.i, src);
+    w.j = __shfl_sync(FULL, w.j, src);
+}
+
+__device__ __forceinline__ bool win_before(const Win& a, const Win& b) {       // a precedes b in the reference's scan
+    return a.key > b.key || (a.key == b.key && a.pos < b.pos);
+}
+
+__device__ __forceinline__ double jl_max(double a, double b) {                  // Julia's max propagates NaN
+    if (isnan(a) || isnan(b)) return nan("");
+    return a > b ? a : b;
+}
+
+template <int CS> __device__ __forceinline__ void cluster_or_block_sync() {
+    if constexpr (CS > 1) cg::this_cluster().sync(); else __syncthreads();
+}
+
+struct Carve {                               // dynamic shared memory of one bond
+    double* A; int lds;
+    double* xs;
+    double* piv;
+    void* Lst; void* Rst;
+    int* rowpos; int* rowat; int* colpos; int* colat;
+    int* xkeepI; int* xkeepJ;
+    size_t bytes;
+};
+
+template <class S>
+__host__ __device__ inline Carve carve(unsigned char* base, int m, int n, int nloc, int rcap, int nXI, int nXJ) {
+    Carve c;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { void* p = base ? (void*)(base + o) : nullptr; o += (bytes + 15) & ~(size_t)15; return p; };
+    c.lds = m | 1;
+    c.A = (double*)take(sizeof(double) * (size_t)c.lds * (size_t)(nloc > 0 ? nloc : 1));
+    c.xs = (double*)take(sizeof(double) * (size_t)m);
+    c.piv = (double*)take(sizeof(double) * (size_t)(rcap + 1));
+    c.Lst = take(sizeof(S) * (size_t)m);
+    c.Rst = take(sizeof(S) * (size_t)n);
+    c.rowpos = (int*)take(sizeof(int) * (size_t)m);
+    c.rowat = (int*)take(sizeof(int) * (size_t)m);
+    c.colpos = (int*)take(sizeof(int) * (size_t)n);
+    c.colat = (int*)take(sizeof(int) * (size_t)n);
+    c.xkeepI = (int*)take(sizeof(int) * (size_t)(nXI > 0 ? nXI : 1));
+    c.xkeepJ = (int*)take(sizeof(int) * (size_t)(nXJ > 0 ? nXJ : 1));
+    c.bytes = o;
+    return c;
+}
+
+// Does any row of `tab` (cnt rows of `len` ints) equal `row`?  One warp; returns the same value in every lane.
+__device__ __forceinline__ bool warp_contains(const int* __restrict__ tab, int cnt, int len, const int* __restrict__ row, int lane) {
+    bool found = false;
+    for (int r0 = 0; r0 < cnt && !found; r0 += 32) {
+        const int r = r0 + lane;
+        bool eq = r < cnt;
+        if (eq) { const int* t = tab + (size_t)r * len; for (int p = 0; p < len; ++p) if (t[p] != row[p]) { eq = false; break; } }
+        found = __any_sync(FULL, eq);
+    }
+    return found;
+}
+
+// Stable compaction of the extras that are not already in the kronecker part: keep[e] = original index of the e-th kept
+// extra.  Warp 0 only; returns the number kept (valid in warp 0's lanes).
+//   left side  (rows of length len = b0 + 1): extra is a duplicate iff its first b0 entries are a row of Iset[b0]
+//   right side (rows of length len = N - b0 - 1): duplicate iff its last len - 1 entries are a row of Jset[b0 + 1]
+__device__ int keep_extras(const int* __restrict__ xt, int nx, int len, const int* __restrict__ base, int nbase, bool left, int* keep, int lane) {
+    int kept = 0;
+    for (int e = 0; e < nx; ++e) {
+        const int* row = xt + (size_t)e * len;
+        const bool dup = nbase > 0 && ((len - 1 == 0) ? true : warp_contains(base, nbase, len - 1, left ? row : row + 1, lane));
+        if (!dup) { if (lane == 0) keep[kept] = e; ++kept; }
+    }
+    return kept;
+}
+
+struct SweepParams {
+    const int* in;
+    int* out;
+    long long out_cap;                       // words
+    double reltol, abstol;
+    unsigned long long* acc;                 // 16 bytes: bits of max |f|, NaN flag (same accumulator as tci_batcheval_acc_f64)
+    double* xs_g;                            // cluster variant: [2][CS][mcap] candidate columns
+    int mcap;
+    int smem_bytes;                          // dynamic shared memory available per CTA
+};
+
+// One half-sweep.  All CTAs of the cluster run the same control flow on the same inputs (index bookkeeping is replicated,
+// it is a few hundred integer operations); only the columns of Pi are divided.
+template <class F, int NT, int CS>
+__global__ void __launch_bounds__(NT, 1)
+dsweep_halfsweep_kernel(F f, SweepParams P) {
+    typedef typename F::State S;
+    extern __shared__ __align__(16) unsigned char dyn[];
+    __shared__ Win s_w[2][32];
+    __shared__ Win s_cl[2][kMaxCS];
+    __shared__ __align__(16) unsigned char s_carry_raw[kRMax * sizeof(S)];
+    __shared__ int s_keepI, s_keepJ, s_flags;
+    S* carry = reinterpret_cast<S*>(s_carry_raw);
+    constexpr int NW = NT / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int crank = 0;
+    if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
+    const bool writer = crank == 0;
+
+    const int* in = P.in;
+    const int N = in[0], fwd = in[1], s0 = in[2], s1 = in[3], maxbond = in[4], useextra = in[5];
+    const int* ld = in + kHdr;
+    const int* desc = ld + N;
+    int* out = P.out;
+    long long used = kHdr + (long long)kStepRec * (s1 - s0);
+    if (writer && tid == 0) { out[0] = 0; out[1] = s1; out[2] = (int)used; }
+
+    const int* mov = nullptr;                // the set that moves with the sweep (Iset[b0] forward, Jset[b0+1] backward) ...
+    int nmov = -1;                           // ... -1: take it from the input arena (first step of the launch)
+    double mx = 0.0; bool isn = false;       // running max |f| of this thread
+
+    for (int s = s0; s < s1; ++s) {
+        const int b0 = fwd ? s : N - 2 - s;
+        const int dL = ld[b0], dR = ld[b0 + 1];
+        const int* dI = desc + kDesc * b0;            // Iset[b0]
+        const int* dJ = desc + kDesc * (b0 + 1);      // Jset[b0 + 1]
+        const int lenI = b0, lenJ = N - b0 - 2;
+        const int* tabI = in + dI[1]; int nI = dI[0];
+        const int* tabJ = in + dJ[3]; int nJ = dJ[2];
+        const bool carried = nmov >= 0;
+        if (carried) { if (fwd) { tabI = mov; nI = nmov; } else { tabJ = mov; nJ = nmov; } }
+        // extras: extraIset = history Iset[b0 + 1] (rows of length b0 + 1), extraJset = history Jset[b0] (length N - b0 - 1)
+        const int* dXI = desc + kDesc * (b0 + 1);
+        const int* dXJ = desc + kDesc * b0;
+        const int nXI = useextra ? dXI[4] : 0, nXJ = useextra ? dXJ[6] : 0;
+        const int* tabXI = in + dXI[5];
+        const int* tabXJ = in + dXJ[7];
+        const int lenXI = b0 + 1, lenXJ = N - b0 - 1;
+
+        // ---- which extras survive the union (tensorci2.jl:842-843); needs a provisional place for the keep lists: the
+        //      start of the dynamic buffer (re-carved below, after the counts are known)
+        int* keepI0 = reinterpret_cast<int*>(dyn);
+        int* keepJ0 = keepI0 + (nXI > 0 ? nXI : 1);
+        if ((size_t)(nXI + nXJ + 2) * sizeof(int) > (size_t)P.smem_bytes) {         // cannot even hold the lists
+            if (writer && tid == 0) { out[0] = 1; out[1] = s; }
+            break;
+        }
+        if (warp == 0) {
+            const int k = keep_extras(tabXI, nXI, lenXI, tabI, nI, true, keepI0, lane);
+            if (lane == 0) s_keepI = k;
+        } else if (warp == 1) {
+            const int k = keep_extras(tabXJ, nXJ, lenXJ, tabJ, nJ, false, keepJ0, lane);
+            if (lane == 0) s_keepJ = k;
+        }
+        __syncthreads();
+        const int nKI = s_keepI, nKJ = s_keepJ;
+        const int mk = nI * dL, nk = dR * nJ;          // kronecker parts
+        const int m = mk + nKI, n = nk + nKJ;
+        const int mn = m < n ? m : n;
+        const int rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
+        const int nloc = (n + CS - 1) / CS;
+        // stash the keep lists in registers of the first threads while the buffer is re-carved
+        int myKeepI = -1, myKeepJ = -1;
+        if (tid < nKI) myKeepI = keepI0[tid];
+        if (tid < nKJ) myKeepJ = keepJ0[tid];
+        const Carve c = carve<S>(dyn, m, n, nloc, rcap, nXI, nXJ);
+        const long long need_out = used + (long long)rcap * (lenXI + lenXJ) + 2 * (rcap + 1) + 2;
+        const bool fits = m >= 1 && n >= 1 && m <= 1024 && n <= 65535 && c.bytes <= (size_t)P.smem_bytes && rcap <= kRMax
+                          && nKI <= NT && nKJ <= NT && need_out <= P.out_cap && (CS == 1 || m <= P.mcap);
+        if (!fits) {                                   // uniform over the cluster: same inputs everywhere
+            if (writer && tid == 0) { out[0] = 1; out[1] = s; }
+            break;
+        }
+        __syncthreads();
+        if (tid < nKI) c.xkeepI[tid] = myKeepI;
+        if (tid < nKJ) c.xkeepJ[tid] = myKeepJ;
+        S* Lst = reinterpret_cast<S*>(c.Lst);
+        S* Rst = reinterpret_cast<S*>(c.Rst);
+        __syncthreads();
+
+        // ---- functor states of every row and every column of Pi
+        for (int t = tid; t < m + n; t += NT) {
+            if (t < m) {
+                const int i = t;
+                S st;
+                if (i < mk) {
+                    const int ir = i % nI, dig = i / nI + 1;
+                    if (carried && fwd) st = carry[ir];
+                    else { st = f.zero(); const int* row = tabI + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, row[p]); }
+                    f.push(st, b0, dig);
+                } else {
+                    st = f.zero();
+                    const int* row = tabXI + (size_t)c.xkeepI[i - mk] * lenXI;
+                    for (int p = 0; p < lenXI; ++p) f.push(st, p, row[p]);
+                }
+                Lst[i] = st;
+                c.rowpos[i] = i; c.rowat[i] = i;
+            } else {
+                const int j = t - m;
+                S st;
+                if (j < nk) {
+                    const int dig = j % dR + 1, jr = j / dR;
+                    if (carried && !fwd) st = carry[jr];
+                    else { st = f.zero(); const int* row = tabJ + (size_t)jr * lenJ; for (int p = 0; p < lenJ; ++p) f.push(st, b0 + 2 + p, row[p]); }
+                    f.push(st, b0 + 1, dig);
+                } else {
+                    st = f.zero();
+                    const int* row = tabXJ + (size_t)c.xkeepJ[j - nk] * lenXJ;
+                    for (int p = 0; p < lenXJ; ++p) f.push(st, b0 + 1 + p, row[p]);
+                }
+                Rst[j] = st;
+                c.colpos[j] = j; c.colat[j] = j;
+            }
+        }
+        if (tid == 0) s_flags = 0;
+        __syncthreads();
+
+        // ---- Pi (own columns) + the first pivot search (positions are the identity)
+        double* A = c.A;
+        const int lds = c.lds;
+        Win best; best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1; best.pad = 0;
+#define TCI_DS_CONSIDER(v, ii, jj)                                                                          \
+        {                                                                                                   \
+            const double q__ = __dmul_rn((v), (v));                                                         \
+            if (q__ == q__) {                                                                               \
+                const unsigned long long k__ = (unsigned long long)__double_as_longlong(q__) + 1ull;        \
+                if (k__ > best.key) { best.key = k__; best.x = (v); best.i = (ii); best.j = (jj); }         \
+                else if (k__ == best.key) {                                                                 \
+                    const unsigned p1__ = ((unsigned)c.colpos[(jj)] << 16) | (unsigned)c.rowpos[(ii)];      \
+                    const unsigned p0__ = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];  \
+                    if (p1__ < p0__) { best.x = (v); best.i = (ii); best.j = (jj); }                        \
+                }                                                                                           \
+            }                                                                                               \
+        }
+        for (int j = crank + CS * warp; j < n; j += CS * NW) {
+            const S rj = Rst[j];
+            double* col = A + (size_t)(j / CS) * lds;
+            for (int i = lane; i < m; i += 32) {
+                const double v = f.finish(f.merge(Lst[i], rj));
+                col[i] = v;
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+                TCI_DS_CONSIDER(v, i, j)
+            }
+        }
+
+        // ---- the loop of _optimizerrlu! (matrixlu.jl:356-369)
+        int np = 0;
+        double maxerror = 0.0, error = nan("");
+        unsigned rmask = 0xffffffffu;                  // bit q: row lane + 32 q is still in the trailing block
+        for (;;) {
+            if (best.i >= 0) best.pos = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];
+            else { best.key = 0; best.pos = 0xffffffffu; }
+            warp_argmax(best);
+            Win* sw = s_w[np & 1];
+            if (lane == 0) sw[warp] = best;
+            __syncthreads();                                                        // barrier 1
+            Win g = (lane < NW) ? sw[lane] : Win{0ull, 0.0, 0xffffffffu, -1, -1, 0};
+            warp_argmax(g);                                                         // every warp: the CTA's winner
+            double piv_own = g.x;
+            if constexpr (CS > 1) {
+                // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
+                cg::cluster_group cl = cg::this_cluster();
+                const int par = np & 1;
+                if (tid < CS) { Win* dst = cl.map_shared_rank(&s_cl[par][crank], tid); *dst = g; }
+                if (g.key != 0) {
+                    double* slot = P.xs_g + ((size_t)par * CS + crank) * P.mcap;
+                    const double* col = A + (size_t)(g.j / CS) * lds;
+                    const bool lo = fwd != 0;
+                    for (int i = tid; i < m; i += NT) slot[i] = lo ? col[i] / piv_own : col[i];
+                }
+                cl.sync();                                                          // the one cluster barrier of the step
+                Win w = s_cl[par][0];
+                int owner = 0;
+                for (int cc = 1; cc < CS; ++cc) { const Win o = s_cl[par][cc]; if (win_before(o, w)) { w = o; owner = cc; } }
+                g = w; g.pad = owner;
+            }
+            int pi, pj; double piv;
+            if (g.key == 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }   // all-NaN block: the reference keeps (k, k)
+            else { pi = g.i; pj = g.j; piv = g.x; }
+            const double err = fabs(piv);                                           // :360
+            error = err;
+            if ((err < P.reltol * maxerror || err < P.abstol) && np > 0) break;     // :363
+            maxerror = jl_max(maxerror, err);                                       // :367
+            const int k = np;
+            // stage the pivot column: x[i] = A[i, pj] / pivot (leftorthogonal, :303-305) or A[i, pj]
+            if constexpr (CS > 1) {
+                if (g.key != 0) {
+                    const double* slot = P.xs_g + ((size_t)(np & 1) * CS + g.pad) * P.mcap;
+                    for (int i = tid; i < m; i += NT) c.xs[i] = __ldcg(slot + i);
+                } else if (pj % CS == crank) {
+                    // NaN pivot picked by position: only its owner has the column; everything it touches becomes NaN anyway
+                    const double* col = A + (size_t)(pj / CS) * lds;
+                    for (int i = tid; i < m; i += NT) c.xs[i] = nan("");
+                    (void)col;
+                } else { for (int i = tid; i < m; i += NT) c.xs[i] = nan(""); }
+            } else {
+                const double* col = A + (size_t)pj * lds;
+                if (fwd) { for (int i = tid; i < m; i += NT) c.xs[i] = col[i] / piv; }
+                else     { for (int i = tid; i < m; i += NT) c.xs[i] = col[i]; }
+            }
+            if (tid == 0) {                                                         // swaprow!/swapcol! on the position maps (:254-275)
+                const int rk = c.rowat[k], pp = c.rowpos[pi];
+                c.rowat[k] = pi; c.rowat[pp] = rk; c.rowpos[rk] = pp; c.rowpos[pi] = k;
+                const int ck = c.colat[k], qq = c.colpos[pj];
+                c.colat[k] = pj; c.colat[qq] = ck; c.colpos[ck] = qq; c.colpos[pj] = k;
+                c.piv[k] = piv;
+            }
+            if ((pi & 31) == lane) rmask &= ~(1u << (pi >> 5));
+            __syncthreads();                                                        // barrier 2
+            np = k + 1;
+            if (np >= rcap) break;                                                  // :356
+            best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1;
+            for (int j = crank + CS * warp; j < n; j += CS * NW) {                  // :316-320 + the next search
+                if (c.colpos[j] < np) continue;
+                double* col = A + (size_t)(j / CS) * lds;
+                double y = col[pi];
+                if (!fwd) y = y / piv;                                              // :307-309
+                unsigned rm = rmask;
+                for (int i = lane; i < m; i += 32, rm >>= 1) {
+                    if (!(rm & 1u)) continue;
+                    const double v = __dsub_rn(col[i], __dmul_rn(c.xs[i], y));
+                    col[i] = v;
+                    TCI_DS_CONSIDER(v, i, j)
+                }
+            }
+        }
+        const int r = np;
+        if (r >= mn) error = 0.0;                                                    // :391-393
+        __syncthreads();
+
+        // ---- lu.L / lu.U contain NaNs? (:376-381)  L(p, t) = A[rowat[p], colat[t]] (/ pivot_t below the diagonal when
+        //      leftorthogonal), p >= t;  U(t, q) = A[rowat[t], colat[q]] (/ pivot_t right of the diagonal otherwise), q >= t
+        {
+            int flags = 0;
+            for (int t = warp; t < r; t += NW) {
+                const int ct = c.colat[t], rt = c.rowat[t];
+                const double pv = c.piv[t];
+                if (ct % CS == crank) {
+                    const double* col = A + (size_t)(ct / CS) * lds;
+                    for (int i = lane; i < m; i += 32) {
+                        const int p = c.rowpos[i];
+                        if (p < t) continue;
+                        const double v = (fwd && p > t) ? col[i] / pv : col[i];
+                        if (v != v) flags |= 1;
+                    }
+                }
+                for (int j = crank + CS * lane; j < n; j += CS * 32) {
+                    const int q = c.colpos[j];
+                    if (q < t) continue;
+                    const double a = A[(size_t)(j / CS) * lds + rt];
+                    const double v = (!fwd && q > t) ? a / pv : a;
+                    if (v != v) flags |= 2;
+                }
+            }
+            if (flags) atomicOr(&s_flags, flags);
+            __syncthreads();
+            if constexpr (CS > 1) {
+                cg::cluster_group cl = cg::this_cluster();
+                if (tid == 0 && s_flags && crank != 0) atomicOr(cl.map_shared_rank(&s_flags, 0), s_flags);
+                cl.sync();
+                const int fl = *cl.map_shared_rank(&s_flags, 0);
+                cl.sync();
+                if (tid == 0) s_flags = fl;
+                __syncthreads();
+            }
+        }
+        if (s_flags) {
+            if (writer && tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = s; }
+            break;
+        }
+
+        // ---- Iset[b0+1] = Icombined[rowindices], Jset[b0] = Jcombined[colindices] (:915-916), pivoterrors(luci)
+        const long long offA = used, offB = offA + (long long)r * lenXI;
+        long long offE = offB + (long long)r * lenXJ; offE += offE & 1;
+        const long long endw = offE + 2LL * (r + 1);
+        if (writer) {
+            int* oa = out + offA; int* ob = out + offB;
+            for (int e = tid; e < r * lenXI; e += NT) {
+                const int kk = e / lenXI, p = e % lenXI, i = c.rowat[kk];
+                int v;
+                if (i < mk) v = (p < lenI) ? tabI[(size_t)(i % nI) * lenI + p] : i / nI + 1;
+                else v = tabXI[(size_t)c.xkeepI[i - mk] * lenXI + p];
+                oa[e] = v;
+            }
+            for (int e = tid; e < r * lenXJ; e += NT) {
+                const int kk = e / lenXJ, p = e % lenXJ, j = c.colat[kk];
+                int v;
+                if (j < nk) v = (p == 0) ? j % dR + 1 : tabJ[(size_t)(j / dR) * lenJ + p - 1];
+                else v = tabXJ[(size_t)c.xkeepJ[j - nk] * lenXJ + p];
+                ob[e] = v;
+            }
+            double* oe = reinterpret_cast<double*>(out + offE);
+            for (int t = tid; t <= r; t += NT) oe[t] = t < r ? fabs(c.piv[t]) : error;
+            if (tid == 0) {
+                int* rec = out + kHdr + kStepRec * (s - s0);
+                rec[0] = r; rec[1] = (int)offA; rec[2] = (int)offB; rec[3] = (int)offE; rec[4] = m; rec[5] = n;
+                out[2] = (int)endw;
+            }
+        }
+        // carry the functor states of the chosen rows (forward) / columns (backward) to the next bond
+        for (int t = tid; t < r; t += NT) carry[t] = fwd ? Lst[c.rowat[t]] : Rst[c.colat[t]];
+        used = endw;
+        mov = fwd ? out + offA : out + offB;
+        nmov = r;
+        __threadfence();
+        cluster_or_block_sync<CS>();                   // the new rows (global) and `carry` are visible to every thread / CTA
+    }
+#undef TCI_DS_CONSIDER
+
+    // ---- updatemaxsample! (tensorci2.jl:636-638): one atomic per warp
+    unsigned long long b = (unsigned long long)__double_as_longlong(mx);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_down_sync(FULL, b, d); b = o > b ? o : b; }
+    const unsigned anyn = __ballot_sync(FULL, isn);
+    if (lane == 0) { if (b) atomicMax(P.acc, b); if (anyn) atomicOr(reinterpret_cast<int*>(P.acc + 1), 1); }
+}
+
+} // namespace
+
+// ---- host side ---------------------------------------------------------------------------------------------------------
+namespace {
+
+struct SweepShape { int maxm = 0, maxn = 0; long long maxelems = 0; };
+
+SweepShape predict(const int32_t* in) {
+    // Pi sizes of the steps of this launch from the INPUT set sizes (the set that moves with the sweep may grow or shrink;
+    // the kernel re-checks every bond and stops when one does not fit)
+    SweepShape sh;
+    const int N = in[0], fwd = in[1], s0 = in[2], s1 = in[3], useextra = in[5];
+    const int32_t* ld = in + kHdr; const int32_t* desc = ld + N;
+    for (int s = s0; s < s1; ++s) {
+        const int b0 = fwd ? s : N - 2 - s;
+        const int nI = desc[kDesc * b0 + 0], nJ = desc[kDesc * (b0 + 1) + 2];
+        const int nXI = useextra ? desc[kDesc * (b0 + 1) + 4] : 0, nXJ = useextra ? desc[kDesc * b0 + 6] : 0;
+        const int m = nI * ld[b0] + nXI, n = ld[b0 + 1] * nJ + nXJ;
+        sh.maxm = std::max(sh.maxm, m); sh.maxn = std::max(sh.maxn, n);
+        sh.maxelems = std::max(sh.maxelems, (long long)m * n);
+    }
+    return sh;
+}
+
+template <class F, int NT, int CS>
+int launch_halfsweep(tci_handle h, const F& f, const SweepParams& P, int dyn_bytes) {
+    auto kern = dsweep_halfsweep_kernel<F, NT, CS>;
+    static thread_local int optin_done = 0;              // per instantiation
+    if (!optin_done) {
+        TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes));
+        optin_done = 1;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CS); cfg.blockDim = dim3(NT); cfg.dynamicSmemBytes = (size_t)dyn_bytes; cfg.stream = h->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = CS > 1 ? 1 : 0;
+    TCI_CUDA(h, cudaLaunchKernelEx(&cfg, kern, f, P));
+    h->launches++;
+    return TCI_OK;
+}
+
+constexpr int kDynBytes = 214 * 1024;                    // + ~11 KB static (carried states, candidate records) <= 227 KB
+
+template <class F>
+int run_halfsweep(tci_handle h, const F& f, SweepParams P, const SweepShape& sh, int force_cs) {
+    P.smem_bytes = kDynBytes;
+    const size_t one = sizeof(double) * (size_t)(sh.maxm | 1) * (size_t)sh.maxn + 40 * (size_t)(sh.maxm + sh.maxn) + 4096;
+    int cs = one <= (size_t)kDynBytes ? 1 : kMaxCS;
+    if (force_cs == 1 || force_cs == kMaxCS) cs = force_cs;
+    if (cs == 1) {
+        if (sh.maxelems <= 4096) return launch_halfsweep<F, 256, 1>(h, f, P, kDynBytes);
+        return launch_halfsweep<F, 1024, 1>(h, f, P, kDynBytes);
+    }
+    return launch_halfsweep<F, 1024, kMaxCS>(h, f, P, kDynBytes);
+}
+
+} // namespace
+
+extern "C" {
+
+int tci_dsweep_supported(tci_handle h, tci_functor f) {
+    (void)h;
+    if (!f) return 0;
+    switch (f->kind) {
+    case TCI_F_LORENTZ: case TCI_F_SUM: case TCI_F_QEXPSIN: case TCI_F_QEXPPLUSSIN: case TCI_F_QEXP2: case TCI_F_HASH: case TCI_F_DENSE: return 1;
+    default: return 0;
+    }
+}
+
+int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
+                             void* d_acc16, int32_t* h_out, int64_t out_cap_words, int64_t* h_used_words) {
+    if (!h) return TCI_ERR_INVALID;
+    if (!f || !h_in || !h_out || !d_acc16 || in_words < kHdr || out_cap_words < kHdr)
+        return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: bad arguments");
+    if (!tci_dsweep_supported(h, f)) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: needs a built-in device functor");
+    const int N = h_in[0], s0 = h_in[2], s1 = h_in[3];
+    if (N < 2 || N > 128 || s0 < 0 || s1 > N - 1 || s0 > s1 || in_words < kHdr + (int64_t)N * (1 + kDesc))
+        return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: malformed input arena");
+    if (f->kind == TCI_F_DENSE && f->ndims != N) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, N);
+    if (out_cap_words < kHdr + (int64_t)kStepRec * (s1 - s0)) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: output arena too small");
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    const SweepShape sh = predict(h_in);
+    const int mcap = ((std::max(sh.maxm, 1) * 2 + 63) / 64) * 64;                  // room for the moving set to grow
+    const size_t in_b = ((size_t)in_words * 4 + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
+    const size_t xs_b = sizeof(double) * 2 * kMaxCS * (size_t)mcap;
+    int rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + xs_b + 256); if (rc) return rc;
+    unsigned char* base = (unsigned char*)h->ws_c.ptr;
+    SweepParams P;
+    P.in = (const int*)base; P.out = (int*)(base + in_b); P.out_cap = out_cap_words; P.reltol = reltol; P.abstol = abstol;
+    P.acc = (unsigned long long*)d_acc16; P.xs_g = (double*)(base + in_b + out_b); P.mcap = mcap; P.smem_bytes = 0;
+    TCI_CUDA(h, cudaMemcpyAsync(base, h_in, (size_t)in_words * 4, cudaMemcpyHostToDevice, h->stream));
+    const char* fe = getenv("TCI_DSWEEP_CLUSTER");         // tests: 1 / 8 force the single-CTA / cluster variant
+    const int force_cs = fe ? atoi(fe) : 0;
+    switch (f->kind) {
+    case TCI_F_LORENTZ: rc = run_halfsweep(h, LorentzF{f->p[0]}, P, sh, force_cs); break;
+    case TCI_F_SUM: rc = run_halfsweep(h, SumF{f->p[0]}, P, sh, force_cs); break;
+    case TCI_F_QEXPSIN: rc = run_halfsweep(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, P, sh, force_cs); break;
+    case TCI_F_QEXPPLUSSIN: rc = run_halfsweep(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, P, sh, force_cs); break;
+    case TCI_F_QEXP2: rc = run_halfsweep(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, P, sh, force_cs); break;
+    case TCI_F_HASH: rc = run_halfsweep(h, HashF{f->p[0], f->p[1]}, P, sh, force_cs); break;
+    case TCI_F_DENSE: rc = run_halfsweep(h, DenseF{f->d_table, f->d_strides}, P, sh, force_cs); break;
+    default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
+    }
+    if (rc) return rc;
+    // the output is append-only: read a prefix, then the rest only when more was written
+    const int64_t first = std::min<int64_t>(out_cap_words, 16384);
+    rc = tci_pinned_reserve(h, (size_t)first * 4); if (rc) return rc;
+    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, P.out, (size_t)first * 4, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    memcpy(h_out, h->pinned, (size_t)first * 4);
+    const int64_t used = h_out[2];
+    if (used > out_cap_words) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: output arena overrun");
+    if (used > first) {
+        TCI_CUDA(h, cudaMemcpyAsync(h_out + first, P.out + first, (size_t)(used - first) * 4, cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    if (h_used_words) *h_used_words = used;
+    return TCI_OK;
+}
+
+} // extern "C"

@@ -218,6 +218,9 @@ struct tci_tci2_s {
     std::vector<double> pe;
     std::string err;
     uint64_t rng = 0;                                   // random starts of the global pivot finder
+    int engine = 0;                                     // 1: device-resident half-sweeps (tci_dsweep_*) where they apply
+    std::vector<int32_t> arena_in, arena_out;           // packed index sets for / from the device-resident sweeps
+    int64_t ndevsweeps = 0, ndevbonds = 0;
     int pivotsearch = 0;                                // 0 :full, 1 :rook (tensorci2.jl:845-914)
     uint64_t rookrng = 0;                               // stream behind pushrandomsubset! of the rook search
     // statistics (host wall clock around the calls; the batch-eval and rrLU entry points synchronise)
@@ -548,6 +551,97 @@ inline bool forwardsweep(int strategy, int iter) {      // sweepstrategies.jl:41
     return strategy == 0 || (strategy == 1 && iter % 2 == 1);
 }
 
+// ---- device-resident half-sweep (csrc/sweep.cu) ---------------------------------------------------------------------------
+// The bond loop of one half-sweep (tensorci2.jl:1226-1250) as ONE launch per stretch of bonds whose Pi fits shared memory:
+// the index sets (and the history entries used as extras) go down as one int32 arena, the new sets and pivot errors come
+// back as one arena.  A bond that does not fit is done by the per-bond path above and the sweep continues behind it.
+constexpr int kArenaHdr = 8, kArenaDesc = 8, kArenaStep = 6;
+
+bool device_bond_fits(int64_t m, int64_t n) {             // mirror of the kernel's own check (8-CTA cluster, 214 KB each)
+    if (m < 1 || n < 1 || m > 1024 || n > 65535) return false;
+    const int64_t nloc = (n + 7) / 8;
+    return 8 * (m | 1) * nloc + 48 * (m + n) + 8192 <= 214 * 1024;
+}
+
+void append_table(std::vector<int32_t>& a, const IdxTable* t, int32_t* cnt_off) {
+    cnt_off[0] = t ? (int32_t)t->n : 0;
+    cnt_off[1] = (int32_t)a.size();
+    if (t && !t->v.empty()) a.insert(a.end(), t->v.begin(), t->v.end());
+}
+
+int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t maxbonddim, const std::vector<IdxTable>* extraI,
+                     const std::vector<IdxTable>* extraJ) {
+    const int N = t->N;
+    const bool useextra = extraI != nullptr;
+    invalidate(t);
+    int s = 0;
+    while (s < N - 1) {
+        const int b0 = fwd ? s : N - 2 - s;
+        {   // does the bond at the head of the stretch fit?  (the kernel re-checks every later bond with the sizes it produces)
+            const int64_t m = t->I[b0].n * t->localdims[b0] + (useextra ? (*extraI)[b0 + 1].n : 0);
+            const int64_t n = t->localdims[b0 + 1] * t->J[b0 + 1].n + (useextra ? (*extraJ)[b0].n : 0);
+            if (!device_bond_fits(m, n)) {
+                int rc = updatepivots(t, f, b0, fwd, 1e-14, abstol, maxbonddim, useextra ? &(*extraI)[b0 + 1] : nullptr,
+                                      useextra ? &(*extraJ)[b0] : nullptr, false);
+                if (rc) return rc;
+                ++s;
+                continue;
+            }
+        }
+        const double t0 = now_s();
+        std::vector<int32_t>& a = t->arena_in;
+        a.assign((size_t)kArenaHdr + (size_t)N * (1 + kArenaDesc), 0);
+        a[0] = N; a[1] = fwd ? 1 : 0; a[2] = s; a[3] = N - 1;
+        a[4] = (maxbonddim <= 0 || maxbonddim > 0x7fffffff) ? 0 : (int32_t)maxbonddim; a[5] = useextra ? 1 : 0;
+        for (int b = 0; b < N; ++b) a[(size_t)kArenaHdr + b] = t->localdims[b];
+        int64_t rowsum = 0;
+        for (int b = 0; b < N; ++b) {
+            int32_t d[8];
+            append_table(a, &t->I[b], d + 0);
+            append_table(a, &t->J[b], d + 2);
+            append_table(a, useextra ? &(*extraI)[b] : nullptr, d + 4);
+            append_table(a, useextra ? &(*extraJ)[b] : nullptr, d + 6);
+            std::memcpy(a.data() + kArenaHdr + N + (size_t)kArenaDesc * b, d, sizeof d);
+            rowsum = std::max<int64_t>(rowsum, std::max(t->I[b].n, t->J[b].n));
+        }
+        // output capacity: every bond may return up to rcap rows of N ints twice; rcap is bounded by what fits the kernel (512)
+        int64_t rcap = 512;
+        if (maxbonddim > 0 && maxbonddim < rcap) rcap = maxbonddim;
+        const int64_t cap = kArenaHdr + (int64_t)kArenaStep * (N - 1) + (int64_t)(N - 1 - s) * (rcap * (N + 1) + 2 * (rcap + 2));
+        t->arena_out.resize((size_t)cap);
+        int64_t used = 0;
+        TCI2_CALL(t, tci_dsweep_halfsweep_f64(t->h, f, a.data(), (int64_t)a.size(), 1e-14, abstol, t->acc, t->arena_out.data(), cap, &used));
+        const int32_t* o = t->arena_out.data();
+        const int status = o[0], next = o[1];
+        t->ndevsweeps++;
+        for (int st = s; st < next; ++st) {
+            const int bb = fwd ? st : N - 2 - st;
+            const int32_t* rec = o + kArenaHdr + (size_t)kArenaStep * (st - s);
+            const int r = rec[0];
+            IdxTable& nI = t->I[bb + 1]; IdxTable& nJ = t->J[bb];
+            nI.n = r; nI.v.assign(o + rec[1], o + rec[1] + (size_t)r * nI.len);
+            nJ.n = r; nJ.v.assign(o + rec[2], o + rec[2] + (size_t)r * nJ.len);
+            std::vector<double> errs((size_t)r + 1);
+            std::memcpy(errs.data(), o + rec[3], sizeof(double) * ((size_t)r + 1));
+            updateerrors(t, bb, errs);
+            t->nevals += (int64_t)rec[4] * rec[5];
+            t->nbondupdates++; t->ndevbonds++;
+        }
+        t->t_lu += now_s() - t0;
+        if (status == 2) return fail(t, TCI_ERR_NAN_L, "lu.L contains NaNs");
+        if (status == 3) return fail(t, TCI_ERR_NAN_U, "lu.U contains NaNs");
+        s = next;
+        if (status == 1 && s < N - 1) {                     // this bond outgrew shared memory: per-bond path, then go on
+            const int bb = fwd ? s : N - 2 - s;
+            int rc = updatepivots(t, f, bb, fwd, 1e-14, abstol, maxbonddim, useextra ? &(*extraI)[bb + 1] : nullptr,
+                                  useextra ? &(*extraJ)[bb] : nullptr, false);
+            if (rc) return rc;
+            ++s;
+        }
+    }
+    return TCI_OK;
+}
+
 // sweep2site! (tensorci2.jl:1195-1258)
 int sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, int64_t maxbonddim, int strategy, bool strictlynested,
                bool dofill) {
@@ -560,6 +654,13 @@ int sweep2site(tci_tci2 t, tci_functor f, int niter, int iter1, double abstol, i
         t->histI = t->I; t->histJ = t->J; t->have_hist = true; t->nhist++;                   // push!(Iset_history, deepcopy(Iset))
         t->pivoterrors.clear();                                                              // flushpivoterror!
         const bool fwd = forwardsweep(strategy, it);
+        // only the last bond's tensors can survive the call, and only without the final fill: that case keeps the per-bond path
+        const bool lastkeeps = !dofill && it == iter1 + niter - 1;
+        if (t->engine == 1 && t->pivotsearch == 0 && !lastkeeps && tci_dsweep_supported(t->h, f)) {
+            int rc = device_halfsweep(t, f, fwd, abstol, maxbonddim, useextra ? &extraI : nullptr, useextra ? &extraJ : nullptr);
+            if (rc) return rc;
+            continue;
+        }
         for (int step = 0; step < N - 1; ++step) {                                           // :1226-1250
             const int b0 = fwd ? step : N - 2 - step;
             // only the tensors of the very last bond update can survive this call, and only without the final fill
@@ -746,6 +847,12 @@ int tci_tci2_destroy(tci_tci2 t) {
 const char* tci_tci2_last_error(tci_tci2 t) { return t ? t->err.c_str() : "NULL tci_tci2"; }
 
 int tci_tci2_seed(tci_tci2 t, uint64_t seed) { if (!t) return TCI_ERR_INVALID; t->rng = seed; return TCI_OK; }
+
+int tci_tci2_set_engine(tci_tci2 t, int engine) {
+    if (!t || (engine != 0 && engine != 1)) return TCI_ERR_INVALID;
+    t->engine = engine;
+    return TCI_OK;
+}
 
 int tci_tci2_set_pivotsearch(tci_tci2 t, int rook, uint64_t seed) {
     if (!t || (rook != 0 && rook != 1)) return TCI_ERR_INVALID;

@@ -61,6 +61,11 @@ class NativeTCI2:
     def seed(self, seed):
         self._check(self.L.tci_tci2_seed(self._t, C.c_uint64(int(seed) & ((1 << 64) - 1))))
 
+    def set_engine(self, engine):
+        """'percall' (one C-ABI call per bond phase) or 'device' (half-sweeps whose Pi fit shared memory as ONE launch each,
+        csrc/sweep.cu); identical index sets, ranks and errors."""
+        self._check(self.L.tci_tci2_set_engine(self._t, {"percall": 0, "device": 1}[engine]))
+
     def set_pivotsearch(self, pivotsearch, seed=0):
         """'full' or 'rook' (tensorci2.jl:845-914); `seed` starts the stream behind pushrandomsubset!."""
         if pivotsearch not in ("full", "rook"):

@@ -544,7 +544,7 @@ def reconstractglobalpivotsfromijset(localdims, Isets, Jsets):     # tensorci2.j
     return piv
 
 
-ENGINES = ("python", "native")
+ENGINES = ("python", "native", "device")
 
 
 def convergencecriterion(ranks, errors, nglobalpivots, tolerance, maxbonddim, ncheckhistory, checkconvglobalpivot=True):
@@ -730,7 +730,7 @@ def _native_eligible(f, kwargs):
             and not kwargs.get("checkbatchevaluatable", False))
 
 
-def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs):
+def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs, device=False):
     """crossinterpolate2 with the whole optimize! loop run by the compiled sweep driver (csrc/tci2_driver.cpp, native.py): one
     C call instead of an interpreted host loop over bonds.  Same kernels, same order of operations; the result is handed
     back as an ordinary TensorCI2 (index sets on the host, site tensors in torch-owned device memory)."""
@@ -755,6 +755,8 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs)
     if initialpivots is None:
         initialpivots = [[1] * n]
     nat = NativeTCI2(_lib.lib(), h.h, localdims)
+    if device:
+        nat.set_engine("device")
     if seed is not None:
         nat.seed(seed)
     nat.set_pivotsearch(pivotsearch, 0 if seed is None else seed)        # same default stream as TensorCI2.rng = Rng(0)
@@ -783,18 +785,20 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs)
 def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
     """crossinterpolate2(Float64, f, localdims, initialpivots; kwargs...) — tensorci2.jl:1313-1323.
     `engine` (not in the reference): "native" hands the optimize! loop to the compiled sweep driver (fewer microseconds of host
-    work per bond, identical kernels and results), "python" runs it in this module; the default "auto" takes the compiled
-    driver whenever it covers the call (device functor, one GPU, no Python-side finder / rng / verbosity)."""
+    work per bond, identical kernels and results), "device" is that driver with the bond loop of every half-sweep running
+    inside ONE kernel launch wherever the Pi matrices fit shared memory (csrc/sweep.cu), "python" runs the loop in this module;
+    the default "auto" takes the compiled driver whenever it covers the call (device functor, one GPU, no Python-side finder /
+    rng / verbosity)."""
     seed = kwargs.pop("seed", None)                         # not in the reference (it uses Julia's global RNG): starts the two
                                                             # splitmix64 streams (rook columns, global-pivot starts) for every engine;
                                                             # without it the Python engine's finder draws from an unseeded numpy RNG
     engine = kwargs.pop("engine", "auto")
     if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module
         engine = "native" if _native_eligible(f, kwargs) else "python"
-    if engine == "native":
-        return _crossinterpolate2_native(f, localdims, initialpivots, seed, kwargs.pop("handle", None), kwargs)
+    if engine in ("native", "device"):
+        return _crossinterpolate2_native(f, localdims, initialpivots, seed, kwargs.pop("handle", None), kwargs, device=engine == "device")
     if engine != "python":
-        raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown engine {engine}: choose 'python' or 'native'.")
+        raise TCIError(_lib.TCI_ERR_INVALID, f"Unknown engine {engine}: choose 'python', 'native' or 'device'.")
     tci = TensorCI2(localdims, f, initialpivots, handle=kwargs.pop("handle", None))
     if seed is not None:
         from .matrixlu import Rng

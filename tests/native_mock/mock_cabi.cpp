@@ -180,4 +180,69 @@ int tci_tt_sum_f64(tci_handle h, const double* const* h_core_ptrs, const int64_t
     return TCI_OK;
 }
 
+// ---- tci_dsweep_*: the arena protocol of the device-resident half-sweep (csrc/sweep.cu) restated on the host with the oracle's
+// arithmetic, so the driver's packing / unpacking / fall-back logic is checked without a GPU.  `mock_set_dsweep_limit(h, e)`
+// makes bonds with more than e Pi entries "not fit" (status 1), which exercises the driver's per-bond fall-back.
+static int64_t g_dsweep_limit = 1 << 30;
+void mock_set_dsweep_limit(tci_handle, int64_t elems) { g_dsweep_limit = elems; }
+int tci_dsweep_supported(tci_handle, tci_functor f) { return f != nullptr; }
+
+int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* in, int64_t, double reltol, double abstol, void* acc,
+                             int32_t* out, int64_t out_cap, int64_t* used_words) {
+    h->ncalls++;
+    const int N = in[0], fwd = in[1], s0 = in[2], s1 = in[3], maxbond = in[4], useextra = in[5];
+    const int32_t* ld = in + 8; const int32_t* desc = ld + N;
+    int64_t used = 8 + 6LL * (s1 - s0);
+    out[0] = 0; out[1] = s1; out[2] = (int)used;
+    typedef std::vector<std::vector<int32_t>> Rows;
+    auto rows_of = [&](int cnt, int off, int len) { Rows r((size_t)cnt); for (int i = 0; i < cnt; ++i) r[(size_t)i].assign(in + off + (size_t)i * len, in + off + (size_t)(i + 1) * len); return r; };
+    Rows mov; bool have_mov = false;
+    MockAcc* a = (MockAcc*)acc;
+    for (int s = s0; s < s1; ++s) {
+        const int b0 = fwd ? s : N - 2 - s;
+        const int32_t* dI = desc + 8 * b0; const int32_t* dJ = desc + 8 * (b0 + 1);
+        Rows I = rows_of(dI[0], dI[1], b0), J = rows_of(dJ[2], dJ[3], N - b0 - 2);
+        if (have_mov) { if (fwd) I = mov; else J = mov; }
+        Rows Ic, Jc;
+        for (int d = 1; d <= ld[b0]; ++d) for (auto r : I) { r.push_back(d); Ic.push_back(r); }
+        for (const auto& r : J) for (int d = 1; d <= ld[b0 + 1]; ++d) { std::vector<int32_t> x; x.push_back(d); x.insert(x.end(), r.begin(), r.end()); Jc.push_back(x); }
+        if (useextra) {
+            const int32_t* dXI = desc + 8 * (b0 + 1); const int32_t* dXJ = desc + 8 * b0;
+            for (const auto& r : rows_of(dXI[4], dXI[5], b0 + 1)) { bool dup = false; for (const auto& y : Ic) if (y == r) { dup = true; break; } if (!dup) Ic.push_back(r); }
+            for (const auto& r : rows_of(dXJ[6], dXJ[7], N - b0 - 1)) { bool dup = false; for (const auto& y : Jc) if (y == r) { dup = true; break; } if (!dup) Jc.push_back(r); }
+        }
+        const int64_t m = (int64_t)Ic.size(), n = (int64_t)Jc.size(), mn = m < n ? m : n;
+        const int64_t rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
+        const int lenA = b0 + 1, lenB = N - b0 - 1;
+        if (m * n > g_dsweep_limit || used + rcap * (lenA + lenB) + 2 * (rcap + 1) + 2 > out_cap) { out[0] = 1; out[1] = s; break; }
+        std::vector<int32_t> lt, rt;
+        for (const auto& r : Ic) lt.insert(lt.end(), r.begin(), r.end());
+        for (const auto& r : Jc) rt.insert(rt.end(), r.begin(), r.end());
+        std::vector<double> Pi((size_t)(m * n));
+        if (orc_batcheval((void*)f, ld, N, lt.data(), m, lenA, rt.data(), n, lenB, 0, Pi.data())) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        double mx = a->nan ? NAN : a->mx;
+        merge_maxabs(&mx, Pi.data(), Pi.size());
+        if (mx != mx) a->nan = 1; else a->mx = mx;
+        std::vector<int64_t> rp((size_t)m), cp((size_t)n);
+        std::vector<double> pe((size_t)rcap + 1);
+        int64_t npiv = 0; double err = 0.0;
+        const int st = orc_rrlu(Pi.data(), m, n, m, rcap, reltol, abstol, fwd, rp.data(), cp.data(), &npiv, &err, nullptr, m, nullptr, rcap, pe.data());
+        if (st == -1) { out[0] = 2; out[1] = s; break; }
+        if (st == -2) { out[0] = 3; out[1] = s; break; }
+        if (st) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        const int64_t offA = used, offB = offA + npiv * lenA; int64_t offE = offB + npiv * lenB; offE += offE & 1;
+        Rows newI, newJ;
+        for (int64_t k = 0; k < npiv; ++k) { newI.push_back(Ic[(size_t)(rp[(size_t)k] - 1)]); newJ.push_back(Jc[(size_t)(cp[(size_t)k] - 1)]); }
+        for (int64_t k = 0; k < npiv; ++k) { std::memcpy(out + offA + k * lenA, newI[(size_t)k].data(), sizeof(int32_t) * lenA); std::memcpy(out + offB + k * lenB, newJ[(size_t)k].data(), sizeof(int32_t) * lenB); }
+        std::memcpy(out + offE, pe.data(), sizeof(double) * (size_t)(npiv + 1));
+        int32_t* rec = out + 8 + 6 * (s - s0);
+        rec[0] = (int)npiv; rec[1] = (int)offA; rec[2] = (int)offB; rec[3] = (int)offE; rec[4] = (int)m; rec[5] = (int)n;
+        used = offE + 2 * (npiv + 1);
+        out[2] = (int)used;
+        mov = fwd ? newI : newJ; have_mov = true;
+    }
+    if (used_words) *used_words = used;
+    return TCI_OK;
+}
+
 } // extern "C"

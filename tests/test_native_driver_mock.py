@@ -95,6 +95,30 @@ def test_optimize_identical_to_oracle(mock, name, kind, params, localdims, kw):
     assert t.stats()["nevals"] > 0
 
 
+@pytest.mark.parametrize("limit", [1 << 30, 400, 0])
+@pytest.mark.parametrize("name,kind,params,localdims,kw", CASES, ids=[c[0] for c in CASES])
+def test_device_engine_bookkeeping_identical_to_oracle(mock, name, kind, params, localdims, kw, limit):
+    """engine = device: the driver packs the index sets (and the history extras) into one arena per half-sweep and unpacks the
+    new sets / pivot errors (tci_dsweep_halfsweep_f64; here the arena protocol restated on the host).  `limit` makes bonds
+    with more Pi entries "not fit", so the per-bond fall-back and the continuation behind it are exercised (0: every bond
+    falls back)."""
+    L, h = mock
+    f = O.Func(kind, params)
+    piv = [[1] * len(localdims)] if kind != O.F_QEXPSIN else [[2, 1] * (len(localdims) // 2)]
+    o, oranks, oerrors = O.crossinterpolate2(f, localdims, piv, **kw)
+    t = _native(mock, localdims, f, piv)
+    t.set_engine("device")
+    L.mock_set_dsweep_limit(h, C.c_int64(limit))
+    try:
+        ranks, errors = t.optimize(f.h, nsearchglobalpivot=0, **kw)
+    finally:
+        L.mock_set_dsweep_limit(h, C.c_int64(1 << 30))
+    np.testing.assert_array_equal(ranks, oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    _same_state(t, o)
+    assert t.stats()["nevals"] == o.stats()["nevals"]
+
+
 def test_stepwise_calls_identical_to_oracle(mock):
     """test/test_tensorci2.jl:247-273 driven call by call: updatepivots! per bond, addglobalpivots + makecanonical,
     sweep2site without the final fill, sweep1site in both directions, fillsitetensors."""
