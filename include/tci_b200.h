@@ -291,6 +291,19 @@ int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const in
  * leftorthogonal = forward.  max |f| of every evaluated element is merged into d_acc16 (see tci_batcheval_acc_f64).
  * Built-in functor kinds only (tci_dsweep_supported); results are bit-identical to the per-bond entry points. */
 int tci_dsweep_supported(tci_handle h, tci_functor f);
+/* fillsitetensors!(tci, f) (src/globalsearch.jl:202-208; per site setsitetensor! src/tensorci2.jl:599-629: T_b = Pi1 inv(P), the last
+ * tensor by evaluation) for ALL sites in one launch.  h_in: the arena above (steps / extras unused); h_d_cores[b] = device buffer
+ * of |Iset[b]| * d_b * |Jset[b]| doubles for site tensor b (dense column-major).  Every bond dimension must be <= 64.  Returns
+ * TCI_ERR_NOT_SQUARE where the reference throws "Pivot matrix at bond b is not square!" (:623). */
+int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, void* d_acc16, double* const* h_d_cores);
+/* sweep1site!(tci, f, :forward; reltol, abstol, maxbonddim, updatetensors=true) (src/tensorci2.jl:659-725) in one launch: per bond
+ * Pi = f((Iset[b] x s_b) x Jset[b]), MatrixLUCI, the new Iset[b+1] / Jset[b], T_b = left(luci) (src/matrixluci.jl:194-213, :256-262),
+ * the last tensor by evaluation.  h_in: the arena above with [4] = maxbonddim; h_d_cores[b] / h_core_capacity[b]: buffer and its
+ * size in doubles (|Jset[b-1]| * d_b * |Jset[b]| suffices).  h_out as above (one record per bond); status 4 = "Error: NaN in
+ * tensor T[b]" (:705-707) at bond [1]; status 1 with [1] = N-1 means only the last tensor is left to the caller. */
+int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
+                              void* d_acc16, double* const* h_d_cores, const int64_t* h_core_capacity, int32_t* h_out,
+                              int64_t out_cap_words, int64_t* h_used_words);
 int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
                              void* d_acc16, int32_t* h_out, int64_t out_cap_words, int64_t* h_used_words);
 

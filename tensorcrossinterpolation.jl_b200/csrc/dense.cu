@@ -9,6 +9,7 @@
 // Operands are addressed with explicit element strides (row stride, column stride), so transposes and
 // the reference's `permutedims`+`reshape` views (src/contraction.jl:211-212) cost nothing.
 #include "context.h"
+#include "solve_small.h"
 #include <cmath>
 #include <cstdlib>
 #include <vector>
@@ -417,8 +418,6 @@ namespace {
 // gather, two blocked triangular solves, scatter: a dozen launches) is pure launch latency.  Here every CTA factorises P in
 // shared memory by full-pivot LU (redundantly: chi <= 64, a few microseconds) and then each thread carries one row of B
 // through the two substitutions.  P[rp, cp] = L U  =>  X[:, rp] = (B[:, cp] U^-1) L^-1.
-constexpr int kSolveRows = 128;                            // rows of B per CTA = threads per CTA
-constexpr int kSolveMaxR = 64;
 
 __global__ void __launch_bounds__(kSolveRows)
 solve_small_kernel(const double* __restrict__ B, long long ldb, const double* __restrict__ P, long long ldp, int q, int r,
@@ -428,69 +427,17 @@ solve_small_kernel(const double* __restrict__ B, long long ldb, const double* __
     double* S = sm;                                        // S[j * lds + i] = P(i, j), becomes L \ U in swapped coordinates
     double* W = S + (size_t)lds * r;                       // W[k * kSolveRows + tid]: this thread's row, column k
     __shared__ int rp[kSolveMaxR], cp[kSolveMaxR];
-    __shared__ double s_a[kSolveRows / 32];
-    __shared__ int s_e[kSolveRows / 32];
-    __shared__ int s_best;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ SmallLuScratch<kSolveRows> scratch;
+    const int tid = threadIdx.x;
     for (int e = tid; e < r * r; e += kSolveRows) { const int i = e % r, j = e / r; S[j * lds + i] = P[(long long)j * ldp + i]; }
-    for (int t = tid; t < r; t += kSolveRows) { rp[t] = t; cp[t] = t; }
     __syncthreads();
-    bool singular = false;
-    for (int k = 0; k < r; ++k) {
-        // full pivot search over the trailing block; ties -> smallest column, then smallest row (deterministic, so every CTA
-        // takes the same decisions); NaN never wins
-        const int rem = r - k;
-        double ba = -1.0; int be = 0x7fffffff;
-        for (int e = tid; e < rem * rem; e += kSolveRows) {
-            const double a = fabs(S[(k + e / rem) * lds + k + e % rem]);
-            if (a > ba) { ba = a; be = e; }
-        }
-        for (int d = 16; d > 0; d >>= 1) {
-            const double oa = __shfl_down_sync(0xffffffffu, ba, d);
-            const int oe = __shfl_down_sync(0xffffffffu, be, d);
-            if (oa > ba || (oa == ba && oe < be)) { ba = oa; be = oe; }
-        }
-        if (lane == 0) { s_a[warp] = ba; s_e[warp] = be; }
-        __syncthreads();
-        if (tid == 0) {
-            for (int w = 1; w < kSolveRows / 32; ++w)
-                if (s_a[w] > ba || (s_a[w] == ba && s_e[w] < be)) { ba = s_a[w]; be = s_e[w]; }
-            s_best = (ba > 0.0) ? be : -1;                 // zero (or all-NaN) trailing block: P is singular
-        }
-        __syncthreads();
-        const int e = s_best;
-        if (e < 0) { singular = true; break; }
-        const int pi = k + e % rem, pj = k + e / rem;
-        if (pi != k) for (int j = tid; j < r; j += kSolveRows) { const double a = S[j * lds + k]; S[j * lds + k] = S[j * lds + pi]; S[j * lds + pi] = a; }
-        __syncthreads();
-        if (pj != k) for (int i = tid; i < r; i += kSolveRows) { const double a = S[k * lds + i]; S[k * lds + i] = S[pj * lds + i]; S[pj * lds + i] = a; }
-        if (tid == 0) { int t = rp[k]; rp[k] = rp[pi]; rp[pi] = t; t = cp[k]; cp[k] = cp[pj]; cp[pj] = t; }
-        __syncthreads();
-        const double piv = S[k * lds + k];
-        for (int i = k + 1 + tid; i < r; i += kSolveRows) S[k * lds + i] = S[k * lds + i] / piv;
-        __syncthreads();
-        const int rm = rem - 1;
-        for (int t = tid; t < rm * rm; t += kSolveRows) {
-            const int i = k + 1 + t % rm, j = k + 1 + t / rm;
-            S[j * lds + i] = S[j * lds + i] - S[k * lds + i] * S[j * lds + k];
-        }
-        __syncthreads();
-    }
+    const bool singular = small_lu_fullpivot<kSolveRows>(S, lds, r, rp, cp, scratch);
     if (tid == 0) *flag = singular ? 1 : 0;                // every CTA writes the same value
     if (singular) return;
     const long long row = (long long)blockIdx.x * kSolveRows + tid;
     const bool valid = row < q;
     for (int k = 0; k < r; ++k) W[k * kSolveRows + tid] = valid ? B[(long long)cp[k] * ldb + row] : 0.0;
-    for (int k = 0; k < r; ++k) {                          // Z U = B[:, cp]   (U(j, k) = S[k * lds + j], j <= k)
-        double s = W[k * kSolveRows + tid];
-        for (int j = 0; j < k; ++j) s = s - W[j * kSolveRows + tid] * S[k * lds + j];
-        W[k * kSolveRows + tid] = s / S[k * lds + k];
-    }
-    for (int k = r - 2; k >= 0; --k) {                     // Xr L = Z, L unit lower (L(j, k) = S[k * lds + j], j > k)
-        double s = W[k * kSolveRows + tid];
-        for (int j = k + 1; j < r; ++j) s = s - W[j * kSolveRows + tid] * S[k * lds + j];
-        W[k * kSolveRows + tid] = s;
-    }
+    small_solve_row<kSolveRows>(W, S, lds, r);
     if (valid) for (int k = 0; k < r; ++k) X[(long long)rp[k] * ldx + row] = W[k * kSolveRows + tid];
 }
 

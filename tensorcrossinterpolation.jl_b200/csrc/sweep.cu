@@ -37,6 +37,7 @@
 // into one int32 arena, gets one arena back.  tci_dsweep_* are declared in include/tci_b200.h.
 #include "context.h"
 #include "functors.h"
+#include "solve_small.h"
 #include <cooperative_groups.h>
 #include <cmath>
 #include <cstring>
@@ -169,6 +170,165 @@ struct SweepParams {
     int smem_bytes;                          // dynamic shared memory available per CTA
 };
 
+#define TCI_DS_CONSIDER(v, ii, jj)                                                                          \
+    {                                                                                                   \
+            const double q__ = __dmul_rn((v), (v));                                                         \
+            if (q__ == q__) {                                                                               \
+                const unsigned long long k__ = (unsigned long long)__double_as_longlong(q__) + 1ull;        \
+                if (k__ > best.key) { best.key = k__; best.x = (v); best.i = (ii); best.j = (jj); }         \
+                else if (k__ == best.key) {                                                                 \
+                    const unsigned p1__ = ((unsigned)c.colpos[(jj)] << 16) | (unsigned)c.rowpos[(ii)];      \
+                    const unsigned p0__ = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];  \
+                    if (p1__ < p0__) { best.x = (v); best.i = (ii); best.j = (jj); }                        \
+                }                                                                                           \
+            }                                                                                               \
+        }
+
+// The loop of _optimizerrlu! (matrixlu.jl:356-369) on the matrix in shared memory (columns j with j % CS == crank live in this
+// CTA, column-major, leading dimension c.lds).  `best` holds this thread's candidate of the FIRST search (fused into the
+// fill by the caller).  Nothing moves: c.rowat / c.colat (position -> physical index) and c.rowpos / c.colpos simulate the
+// reference's swaps; on return the first r entries of rowat / colat are the pivots in order, c.piv their values, and every
+// L / U entry sits where it was computed:  L(p, t) = A[rowat[p], colat[t]] (/ piv[t] below the diagonal when leftorthogonal),
+// U(t, q) = A[rowat[t], colat[q]] (/ piv[t] right of the diagonal otherwise).  `fwd` is leftorthogonal.
+template <int NT, int CS>
+__device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int n, const int rcap, const int fwd, const double reltol,
+                                         const double abstol, Win best, Win (*s_w)[32], Win (*s_cl)[kMaxCS], const SweepParams& P,
+                                         const int crank, double* error_out) {
+    constexpr int NW = NT / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double* A = c.A;
+    const int lds = c.lds;
+        int np = 0;
+        double maxerror = 0.0, error = nan("");
+        unsigned rmask = 0xffffffffu;                  // bit q: row lane + 32 q is still in the trailing block
+        for (;;) {
+            if (best.i >= 0) best.pos = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];
+            else { best.key = 0; best.pos = 0xffffffffu; }
+            warp_argmax(best);
+            Win* sw = s_w[np & 1];
+            if (lane == 0) sw[warp] = best;
+            __syncthreads();                                                        // barrier 1
+            Win g = (lane < NW) ? sw[lane] : Win{0ull, 0.0, 0xffffffffu, -1, -1, 0};
+            warp_argmax(g);                                                         // every warp: the CTA's winner
+            double piv_own = g.x;
+            if constexpr (CS > 1) {
+                // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
+                cg::cluster_group cl = cg::this_cluster();
+                const int par = np & 1;
+                if (tid < CS) { Win* dst = cl.map_shared_rank(&s_cl[par][crank], tid); *dst = g; }
+                if (g.key != 0) {
+                    double* slot = P.xs_g + ((size_t)par * CS + crank) * P.mcap;
+                    const double* col = A + (size_t)(g.j / CS) * lds;
+                    const bool lo = fwd != 0;
+                    for (int i = tid; i < m; i += NT) slot[i] = lo ? col[i] / piv_own : col[i];
+                }
+                cl.sync();                                                          // the one cluster barrier of the step
+                Win w = s_cl[par][0];
+                int owner = 0;
+                for (int cc = 1; cc < CS; ++cc) { const Win o = s_cl[par][cc]; if (win_before(o, w)) { w = o; owner = cc; } }
+                g = w; g.pad = owner;
+            }
+            int pi, pj; double piv;
+            if (g.key == 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }   // all-NaN block: the reference keeps (k, k)
+            else { pi = g.i; pj = g.j; piv = g.x; }
+            const double err = fabs(piv);                                           // :360
+            error = err;
+            if ((err < reltol * maxerror || err < abstol) && np > 0) break;     // :363
+            maxerror = jl_max(maxerror, err);                                       // :367
+            const int k = np;
+            // stage the pivot column: x[i] = A[i, pj] / pivot (leftorthogonal, :303-305) or A[i, pj]
+            if constexpr (CS > 1) {
+                if (g.key != 0) {
+                    const double* slot = P.xs_g + ((size_t)(np & 1) * CS + g.pad) * P.mcap;
+                    for (int i = tid; i < m; i += NT) c.xs[i] = __ldcg(slot + i);
+                } else if (pj % CS == crank) {
+                    // NaN pivot picked by position: only its owner has the column; everything it touches becomes NaN anyway
+                    const double* col = A + (size_t)(pj / CS) * lds;
+                    for (int i = tid; i < m; i += NT) c.xs[i] = nan("");
+                    (void)col;
+                } else { for (int i = tid; i < m; i += NT) c.xs[i] = nan(""); }
+            } else {
+                const double* col = A + (size_t)pj * lds;
+                if (fwd) { for (int i = tid; i < m; i += NT) c.xs[i] = col[i] / piv; }
+                else     { for (int i = tid; i < m; i += NT) c.xs[i] = col[i]; }
+            }
+            if (tid == 0) {                                                         // swaprow!/swapcol! on the position maps (:254-275)
+                const int rk = c.rowat[k], pp = c.rowpos[pi];
+                c.rowat[k] = pi; c.rowat[pp] = rk; c.rowpos[rk] = pp; c.rowpos[pi] = k;
+                const int ck = c.colat[k], qq = c.colpos[pj];
+                c.colat[k] = pj; c.colat[qq] = ck; c.colpos[ck] = qq; c.colpos[pj] = k;
+                c.piv[k] = piv;
+            }
+            if ((pi & 31) == lane) rmask &= ~(1u << (pi >> 5));
+            __syncthreads();                                                        // barrier 2
+            np = k + 1;
+            if (np >= rcap) break;                                                  // :356
+            best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1;
+            for (int j = crank + CS * warp; j < n; j += CS * NW) {                  // :316-320 + the next search
+                if (c.colpos[j] < np) continue;
+                double* col = A + (size_t)(j / CS) * lds;
+                double y = col[pi];
+                if (!fwd) y = y / piv;                                              // :307-309
+                unsigned rm = rmask;
+                for (int i = lane; i < m; i += 32, rm >>= 1) {
+                    if (!(rm & 1u)) continue;
+                    const double v = __dsub_rn(col[i], __dmul_rn(c.xs[i], y));
+                    col[i] = v;
+                    TCI_DS_CONSIDER(v, i, j)
+                }
+            }
+        }
+        const int r = np;
+        if (r >= (m < n ? m : n)) error = 0.0;                                       // :391-393
+        __syncthreads();
+        *error_out = error;
+        return r;
+
+}
+
+// "lu.L contains NaNs" / "lu.U contains NaNs" (matrixlu.jl:376-381): bit 0 / bit 1 of *s_flags (shared, zeroed by the caller).
+template <int NT, int CS>
+__device__ __forceinline__ void lu_nan_flags(const Carve& c, const int m, const int n, const int r, const int fwd, const int crank, int* s_flags) {
+    constexpr int NW = NT / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double* A = c.A;
+    const int lds = c.lds;
+        {
+            int flags = 0;
+            for (int t = warp; t < r; t += NW) {
+                const int ct = c.colat[t], rt = c.rowat[t];
+                const double pv = c.piv[t];
+                if (ct % CS == crank) {
+                    const double* col = A + (size_t)(ct / CS) * lds;
+                    for (int i = lane; i < m; i += 32) {
+                        const int p = c.rowpos[i];
+                        if (p < t) continue;
+                        const double v = (fwd && p > t) ? col[i] / pv : col[i];
+                        if (v != v) flags |= 1;
+                    }
+                }
+                for (int j = crank + CS * lane; j < n; j += CS * 32) {
+                    const int q = c.colpos[j];
+                    if (q < t) continue;
+                    const double a = A[(size_t)(j / CS) * lds + rt];
+                    const double v = (!fwd && q > t) ? a / pv : a;
+                    if (v != v) flags |= 2;
+                }
+            }
+            if (flags) atomicOr(s_flags, flags);
+            __syncthreads();
+            if constexpr (CS > 1) {
+                cg::cluster_group cl = cg::this_cluster();
+                if (tid == 0 && *s_flags && crank != 0) atomicOr(cl.map_shared_rank(s_flags, 0), *s_flags);
+                cl.sync();
+                const int fl = *cl.map_shared_rank(s_flags, 0);
+                cl.sync();
+                if (tid == 0) *s_flags = fl;
+                __syncthreads();
+            }
+        }
+}
+
 // One half-sweep.  All CTAs of the cluster run the same control flow on the same inputs (index bookkeeping is replicated,
 // it is a few hundred integer operations); only the columns of Pi are divided.
 template <class F, int NT, int CS>
@@ -299,19 +459,6 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         double* A = c.A;
         const int lds = c.lds;
         Win best; best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1; best.pad = 0;
-#define TCI_DS_CONSIDER(v, ii, jj)                                                                          \
-        {                                                                                                   \
-            const double q__ = __dmul_rn((v), (v));                                                         \
-            if (q__ == q__) {                                                                               \
-                const unsigned long long k__ = (unsigned long long)__double_as_longlong(q__) + 1ull;        \
-                if (k__ > best.key) { best.key = k__; best.x = (v); best.i = (ii); best.j = (jj); }         \
-                else if (k__ == best.key) {                                                                 \
-                    const unsigned p1__ = ((unsigned)c.colpos[(jj)] << 16) | (unsigned)c.rowpos[(ii)];      \
-                    const unsigned p0__ = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];  \
-                    if (p1__ < p0__) { best.x = (v); best.i = (ii); best.j = (jj); }                        \
-                }                                                                                           \
-            }                                                                                               \
-        }
         for (int j = crank + CS * warp; j < n; j += CS * NW) {
             const S rj = Rst[j];
             double* col = A + (size_t)(j / CS) * lds;
@@ -324,127 +471,9 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
             }
         }
 
-        // ---- the loop of _optimizerrlu! (matrixlu.jl:356-369)
-        int np = 0;
-        double maxerror = 0.0, error = nan("");
-        unsigned rmask = 0xffffffffu;                  // bit q: row lane + 32 q is still in the trailing block
-        for (;;) {
-            if (best.i >= 0) best.pos = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];
-            else { best.key = 0; best.pos = 0xffffffffu; }
-            warp_argmax(best);
-            Win* sw = s_w[np & 1];
-            if (lane == 0) sw[warp] = best;
-            __syncthreads();                                                        // barrier 1
-            Win g = (lane < NW) ? sw[lane] : Win{0ull, 0.0, 0xffffffffu, -1, -1, 0};
-            warp_argmax(g);                                                         // every warp: the CTA's winner
-            double piv_own = g.x;
-            if constexpr (CS > 1) {
-                // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
-                cg::cluster_group cl = cg::this_cluster();
-                const int par = np & 1;
-                if (tid < CS) { Win* dst = cl.map_shared_rank(&s_cl[par][crank], tid); *dst = g; }
-                if (g.key != 0) {
-                    double* slot = P.xs_g + ((size_t)par * CS + crank) * P.mcap;
-                    const double* col = A + (size_t)(g.j / CS) * lds;
-                    const bool lo = fwd != 0;
-                    for (int i = tid; i < m; i += NT) slot[i] = lo ? col[i] / piv_own : col[i];
-                }
-                cl.sync();                                                          // the one cluster barrier of the step
-                Win w = s_cl[par][0];
-                int owner = 0;
-                for (int cc = 1; cc < CS; ++cc) { const Win o = s_cl[par][cc]; if (win_before(o, w)) { w = o; owner = cc; } }
-                g = w; g.pad = owner;
-            }
-            int pi, pj; double piv;
-            if (g.key == 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }   // all-NaN block: the reference keeps (k, k)
-            else { pi = g.i; pj = g.j; piv = g.x; }
-            const double err = fabs(piv);                                           // :360
-            error = err;
-            if ((err < P.reltol * maxerror || err < P.abstol) && np > 0) break;     // :363
-            maxerror = jl_max(maxerror, err);                                       // :367
-            const int k = np;
-            // stage the pivot column: x[i] = A[i, pj] / pivot (leftorthogonal, :303-305) or A[i, pj]
-            if constexpr (CS > 1) {
-                if (g.key != 0) {
-                    const double* slot = P.xs_g + ((size_t)(np & 1) * CS + g.pad) * P.mcap;
-                    for (int i = tid; i < m; i += NT) c.xs[i] = __ldcg(slot + i);
-                } else if (pj % CS == crank) {
-                    // NaN pivot picked by position: only its owner has the column; everything it touches becomes NaN anyway
-                    const double* col = A + (size_t)(pj / CS) * lds;
-                    for (int i = tid; i < m; i += NT) c.xs[i] = nan("");
-                    (void)col;
-                } else { for (int i = tid; i < m; i += NT) c.xs[i] = nan(""); }
-            } else {
-                const double* col = A + (size_t)pj * lds;
-                if (fwd) { for (int i = tid; i < m; i += NT) c.xs[i] = col[i] / piv; }
-                else     { for (int i = tid; i < m; i += NT) c.xs[i] = col[i]; }
-            }
-            if (tid == 0) {                                                         // swaprow!/swapcol! on the position maps (:254-275)
-                const int rk = c.rowat[k], pp = c.rowpos[pi];
-                c.rowat[k] = pi; c.rowat[pp] = rk; c.rowpos[rk] = pp; c.rowpos[pi] = k;
-                const int ck = c.colat[k], qq = c.colpos[pj];
-                c.colat[k] = pj; c.colat[qq] = ck; c.colpos[ck] = qq; c.colpos[pj] = k;
-                c.piv[k] = piv;
-            }
-            if ((pi & 31) == lane) rmask &= ~(1u << (pi >> 5));
-            __syncthreads();                                                        // barrier 2
-            np = k + 1;
-            if (np >= rcap) break;                                                  // :356
-            best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1;
-            for (int j = crank + CS * warp; j < n; j += CS * NW) {                  // :316-320 + the next search
-                if (c.colpos[j] < np) continue;
-                double* col = A + (size_t)(j / CS) * lds;
-                double y = col[pi];
-                if (!fwd) y = y / piv;                                              // :307-309
-                unsigned rm = rmask;
-                for (int i = lane; i < m; i += 32, rm >>= 1) {
-                    if (!(rm & 1u)) continue;
-                    const double v = __dsub_rn(col[i], __dmul_rn(c.xs[i], y));
-                    col[i] = v;
-                    TCI_DS_CONSIDER(v, i, j)
-                }
-            }
-        }
-        const int r = np;
-        if (r >= mn) error = 0.0;                                                    // :391-393
-        __syncthreads();
-
-        // ---- lu.L / lu.U contain NaNs? (:376-381)  L(p, t) = A[rowat[p], colat[t]] (/ pivot_t below the diagonal when
-        //      leftorthogonal), p >= t;  U(t, q) = A[rowat[t], colat[q]] (/ pivot_t right of the diagonal otherwise), q >= t
-        {
-            int flags = 0;
-            for (int t = warp; t < r; t += NW) {
-                const int ct = c.colat[t], rt = c.rowat[t];
-                const double pv = c.piv[t];
-                if (ct % CS == crank) {
-                    const double* col = A + (size_t)(ct / CS) * lds;
-                    for (int i = lane; i < m; i += 32) {
-                        const int p = c.rowpos[i];
-                        if (p < t) continue;
-                        const double v = (fwd && p > t) ? col[i] / pv : col[i];
-                        if (v != v) flags |= 1;
-                    }
-                }
-                for (int j = crank + CS * lane; j < n; j += CS * 32) {
-                    const int q = c.colpos[j];
-                    if (q < t) continue;
-                    const double a = A[(size_t)(j / CS) * lds + rt];
-                    const double v = (!fwd && q > t) ? a / pv : a;
-                    if (v != v) flags |= 2;
-                }
-            }
-            if (flags) atomicOr(&s_flags, flags);
-            __syncthreads();
-            if constexpr (CS > 1) {
-                cg::cluster_group cl = cg::this_cluster();
-                if (tid == 0 && s_flags && crank != 0) atomicOr(cl.map_shared_rank(&s_flags, 0), s_flags);
-                cl.sync();
-                const int fl = *cl.map_shared_rank(&s_flags, 0);
-                cl.sync();
-                if (tid == 0) s_flags = fl;
-                __syncthreads();
-            }
-        }
+        double error;
+        const int r = smem_rrlu<NT, CS>(c, m, n, rcap, fwd, P.reltol, P.abstol, best, s_w, s_cl, P, crank, &error);
+        lu_nan_flags<NT, CS>(c, m, n, r, fwd, crank, &s_flags);
         if (s_flags) {
             if (writer && tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = s; }
             break;
@@ -486,12 +515,269 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         __threadfence();
         cluster_or_block_sync<CS>();                   // the new rows (global) and `carry` are visible to every thread / CTA
     }
-#undef TCI_DS_CONSIDER
 
     // ---- updatemaxsample! (tensorci2.jl:636-638): one atomic per warp
     unsigned long long b = (unsigned long long)__double_as_longlong(mx);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_down_sync(FULL, b, d); b = o > b ? o : b; }
+    const unsigned anyn = __ballot_sync(FULL, isn);
+    if (lane == 0) { if (b) atomicMax(P.acc, b); if (anyn) atomicOr(reinterpret_cast<int*>(P.acc + 1), 1); }
+}
+
+
+// ---- fillsitetensors! (src/globalsearch.jl:202-208 -> setsitetensor! src/tensorci2.jl:599-629) for ALL sites in one launch ------
+// CTA = (site b, block of 128 rows of Pi1).  Site b < N-1:  T_b = Pi1 * inv(P),  Pi1 = f((Iset[b] x s_b) x Jset[b]),
+// P = f(Iset[b+1] x Jset[b]) (:617-626): the CTA evaluates P into shared memory, factorises it by full-pivot LU
+// (solve_small.h, the arithmetic of tci_solve_right_f64), evaluates its rows of Pi1 on the fly and solves.  Last site:
+// plain evaluation (:612-615).  Every evaluated value is merged into the max |f| accumulator.
+struct FillParams {
+    const int* in;                           // input arena (same format as the half-sweep's; extras unused)
+    double* const* cores;                    // device array: cores[b] = (chil * d) x chir, dense column-major
+    const int* blockmap;                     // per CTA: site, first row
+    unsigned long long* acc;
+    int* flag;                               // set to 1 + site when a pivot matrix is singular
+};
+
+template <class F>
+__global__ void __launch_bounds__(kSolveRows)
+dsweep_fill_kernel(F f, FillParams P) {
+    typedef typename F::State S;
+    extern __shared__ __align__(16) unsigned char dynf[];
+    __shared__ int rp[kSolveMaxR], cp[kSolveMaxR];
+    __shared__ SmallLuScratch<kSolveRows> scratch;
+    __shared__ __align__(16) unsigned char s_R_raw[kSolveMaxR * sizeof(S)];
+    __shared__ __align__(16) unsigned char s_L_raw[kSolveMaxR * sizeof(S)];
+    S* Rst = reinterpret_cast<S*>(s_R_raw);
+    S* LPst = reinterpret_cast<S*>(s_L_raw);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int* in = P.in;
+    const int N = in[0];
+    const int* ld = in + kHdr; const int* desc = ld + N;
+    const int b0 = P.blockmap[2 * blockIdx.x], row0 = P.blockmap[2 * blockIdx.x + 1];
+    const int d = ld[b0];
+    const int nI = desc[kDesc * b0 + 0], nJ = desc[kDesc * b0 + 2];
+    const int* tabI = in + desc[kDesc * b0 + 1];
+    const int* tabJ = in + desc[kDesc * b0 + 3];
+    const int lenI = b0, lenJ = N - b0 - 1;
+    const int q = nI * d;
+    double* T = P.cores[b0];
+    double mx = 0.0; bool isn = false;
+    const int row = row0 + tid;
+    S st = f.zero();
+    if (row < q) {
+        const int* r_ = tabI + (size_t)(row % nI) * lenI;
+        for (int p = 0; p < lenI; ++p) f.push(st, p, r_[p]);
+        f.push(st, b0, row / nI + 1);
+    }
+    if (b0 == N - 1) {                                                              // :612-615
+        for (int j = 0; j < nJ; ++j) {
+            if (row < q) {
+                const double v = f.finish(f.merge(st, f.zero()));
+                T[(size_t)j * q + row] = v;
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+            }
+        }
+    } else {
+        const int r = nJ;                                                           // == |Iset[b0+1]| (checked by the host, :623)
+        const int lds = r | 1;
+        double* Sm = reinterpret_cast<double*>(dynf);
+        double* W = Sm + (size_t)lds * r;
+        const int* tabI1 = in + desc[kDesc * (b0 + 1) + 1];
+        for (int t = tid; t < 2 * r; t += kSolveRows) {
+            S s2 = f.zero();
+            if (t < r) { const int* r_ = tabJ + (size_t)t * lenJ; for (int p = 0; p < lenJ; ++p) f.push(s2, b0 + 1 + p, r_[p]); Rst[t] = s2; }
+            else { const int* r_ = tabI1 + (size_t)(t - r) * (b0 + 1); for (int p = 0; p <= b0; ++p) f.push(s2, p, r_[p]); LPst[t - r] = s2; }
+        }
+        __syncthreads();
+        for (int e = tid; e < r * r; e += kSolveRows) {
+            const int i = e % r, j = e / r;
+            const double v = f.finish(f.merge(LPst[i], Rst[j]));
+            Sm[j * lds + i] = v;
+            const double a = fabs(v);
+            if (a != a) isn = true; else mx = a > mx ? a : mx;
+        }
+        __syncthreads();
+        const bool singular = small_lu_fullpivot<kSolveRows>(Sm, lds, r, rp, cp, scratch);
+        if (singular) { if (tid == 0) atomicMax(P.flag, 1 + b0); }
+        else {
+            double* W2 = W;
+            for (int k = 0; k < r; ++k) {                                           // B[:, cp]: Pi1[row, cp[k]]
+                double v = 0.0;
+                if (row < q) {
+                    v = f.finish(f.merge(st, Rst[cp[k]]));
+                    const double a = fabs(v);
+                    if (a != a) isn = true; else mx = a > mx ? a : mx;
+                }
+                W2[k * kSolveRows + tid] = v;
+            }
+            small_solve_row<kSolveRows>(W2, Sm, lds, r);
+            if (row < q) for (int k = 0; k < r; ++k) T[(size_t)rp[k] * q + row] = W2[k * kSolveRows + tid];
+        }
+    }
+    unsigned long long b = (unsigned long long)__double_as_longlong(mx);
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) { const unsigned long long o = __shfl_down_sync(FULL, b, dd); b = o > b ? o : b; }
+    const unsigned anyn = __ballot_sync(FULL, isn);
+    if (lane == 0) { if (b) atomicMax(P.acc, b); if (anyn) atomicOr(reinterpret_cast<int*>(P.acc + 1), 1); }
+}
+
+// ---- sweep1site!(tci, f, :forward; reltol, abstol, maxbonddim, updatetensors=true) (src/tensorci2.jl:659-725) in ONE launch ----
+// Per bond b: Pi = f((Iset[b] x s_b) x Jset[b]) (:681-686), MatrixLUCI (:688-694), Iset[b+1] / Jset[b] from the pivots
+// (:696-698), T_b = left(luci) = P_row^T [I_r ; L2 inv(L1)] (src/matrixluci.jl:194-213), NaN check (:705-707); the last tensor
+// by evaluation (:719-723).  One CTA; the same swap-free rrLU as the half-sweep kernel.
+struct Sweep1Params {
+    SweepParams sp;
+    double* const* cores;
+    const long long* corecap;                // doubles available in cores[b]
+};
+
+template <class F, int NT>
+__global__ void __launch_bounds__(NT, 1)
+dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
+    typedef typename F::State S;
+    const SweepParams& P = Q.sp;
+    extern __shared__ __align__(16) unsigned char dyn[];
+    __shared__ Win s_w[2][32];
+    __shared__ Win s_cl[2][kMaxCS];
+    __shared__ __align__(16) unsigned char s_carry_raw[kRMax * sizeof(S)];
+    __shared__ int s_flags;
+    S* carry = reinterpret_cast<S*>(s_carry_raw);
+    constexpr int NW = NT / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int* in = P.in;
+    const int N = in[0], maxbond = in[4];
+    const int* ld = in + kHdr; const int* desc = ld + N;
+    int* out = P.out;
+    long long used = kHdr + (long long)kStepRec * (N - 1);
+    if (tid == 0) { out[0] = 0; out[1] = N - 1; out[2] = (int)used; }
+    const int* mov = in + desc[1]; int nmov = desc[0];       // Iset[0]
+    bool carried = false;
+    double mx = 0.0; bool isn = false;
+    bool stopped = false;
+    for (int b0 = 0; b0 < N - 1; ++b0) {
+        const int d = ld[b0];
+        const int* tabI = mov; const int nI = nmov; const int lenI = b0;
+        const int nJ = desc[kDesc * b0 + 2]; const int* tabJ = in + desc[kDesc * b0 + 3]; const int lenJ = N - b0 - 1;
+        const int m = nI * d, n = nJ, mn = m < n ? m : n;
+        const int rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
+        Carve c = carve<S>(dyn, m, n, n, rcap, 0, 0);
+        double* L1s = reinterpret_cast<double*>(dyn + c.bytes);                     // scaled unit-lower factor of the pivot block
+        const size_t bytes = c.bytes + sizeof(double) * (size_t)rcap * rcap;
+        const long long need_out = used + (long long)rcap * (lenI + 1 + lenJ) + 2 * (rcap + 1) + 2;
+        const bool fits = m >= 1 && n >= 1 && m <= 1024 && bytes <= (size_t)P.smem_bytes && rcap <= kRMax && need_out <= P.out_cap
+                          && (long long)m * rcap <= Q.corecap[b0];
+        if (!fits) { if (tid == 0) { out[0] = 1; out[1] = b0; } stopped = true; break; }
+        S* Lst = reinterpret_cast<S*>(c.Lst);
+        S* Rst = reinterpret_cast<S*>(c.Rst);
+        __syncthreads();
+        for (int t = tid; t < m + n; t += NT) {
+            if (t < m) {
+                const int ir = t % nI, dig = t / nI + 1;
+                S st;
+                if (carried) st = carry[ir];
+                else { st = f.zero(); const int* row = tabI + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, row[p]); }
+                f.push(st, b0, dig);
+                Lst[t] = st; c.rowpos[t] = t; c.rowat[t] = t;
+            } else {
+                const int j = t - m;
+                S st = f.zero();
+                const int* row = tabJ + (size_t)j * lenJ;
+                for (int p = 0; p < lenJ; ++p) f.push(st, b0 + 1 + p, row[p]);
+                Rst[j] = st; c.colpos[j] = j; c.colat[j] = j;
+            }
+        }
+        if (tid == 0) s_flags = 0;
+        __syncthreads();
+        double* A = c.A; const int lds = c.lds;
+        Win best; best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1; best.pad = 0;
+        for (int j = warp; j < n; j += NW) {
+            const S rj = Rst[j];
+            double* col = A + (size_t)j * lds;
+            for (int i = lane; i < m; i += 32) {
+                const double v = f.finish(f.merge(Lst[i], rj));
+                col[i] = v;
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+                TCI_DS_CONSIDER(v, i, j)
+            }
+        }
+        double error;
+        const int r = smem_rrlu<NT, 1>(c, m, n, rcap, 1, P.reltol, P.abstol, best, s_w, s_cl, P, 0, &error);
+        lu_nan_flags<NT, 1>(c, m, n, r, 1, 0, &s_flags);
+        if (s_flags) { if (tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = b0; } stopped = true; break; }
+        // ---- new index sets and pivot errors
+        const int lenA = b0 + 1, lenB = lenJ;
+        const long long offA = used, offB = offA + (long long)r * lenA;
+        long long offE = offB + (long long)r * lenB; offE += offE & 1;
+        const long long endw = offE + 2LL * (r + 1);
+        {
+            int* oa = out + offA; int* ob = out + offB;
+            for (int e = tid; e < r * lenA; e += NT) {
+                const int kk = e / lenA, p = e % lenA, i = c.rowat[kk];
+                oa[e] = (p < lenI) ? tabI[(size_t)(i % nI) * lenI + p] : i / nI + 1;
+            }
+            for (int e = tid; e < r * lenB; e += NT) { const int kk = e / lenB, p = e % lenB; ob[e] = tabJ[(size_t)c.colat[kk] * lenJ + p]; }
+            double* oe = reinterpret_cast<double*>(out + offE);
+            for (int t = tid; t <= r; t += NT) oe[t] = t < r ? fabs(c.piv[t]) : error;
+            if (tid == 0) {
+                int* rec = out + kHdr + kStepRec * b0;
+                rec[0] = r; rec[1] = (int)offA; rec[2] = (int)offB; rec[3] = (int)offE; rec[4] = m; rec[5] = n;
+                out[2] = (int)endw;
+            }
+        }
+        // ---- T_b = left(luci): rows at pivot positions are unit vectors, the others L2 inv(L1) by back substitution, in place
+        for (int e = tid; e < r * r; e += NT) {
+            const int j = e / r, t = e % r;                                         // L1(j, t), j > t
+            if (j > t) L1s[j * r + t] = A[(size_t)c.colat[t] * lds + c.rowat[j]] / c.piv[t];
+        }
+        __syncthreads();
+        double* T = Q.cores[b0];
+        bool tnan = false;
+        for (int i = tid; i < m; i += NT) {
+            const int p = c.rowpos[i];
+            if (p < r) { for (int k = 0; k < r; ++k) T[(size_t)k * m + i] = (k == p) ? 1.0 : 0.0; continue; }
+            for (int t = r - 1; t >= 0; --t) {
+                double x = A[(size_t)c.colat[t] * lds + i] / c.piv[t];              // L2(p, t)
+                for (int j = t + 1; j < r; ++j) x = x - A[(size_t)c.colat[j] * lds + i] * L1s[j * r + t];
+                A[(size_t)c.colat[t] * lds + i] = x;                                // X(p, t), final
+                if (x != x) tnan = true;
+                T[(size_t)t * m + i] = x;
+            }
+        }
+        if (tnan) atomicOr(&s_flags, 4);
+        for (int t = tid; t < r; t += NT) carry[t] = Lst[c.rowat[t]];
+        __syncthreads();
+        if (s_flags) { if (tid == 0) { out[0] = 4; out[1] = b0; } stopped = true; break; }        // "Error: NaN in tensor T[b]" :705-707
+        used = endw; mov = out + offA; nmov = r; carried = true;
+        __threadfence();
+        __syncthreads();
+    }
+    if (!stopped) {                                                                // last tensor by evaluation (:719-723)
+        const int b0 = N - 1, d = ld[b0];
+        const int nI = nmov, lenI = b0;
+        const int nJ = desc[kDesc * b0 + 2];
+        const long long q = (long long)nI * d;
+        if (q * nJ > Q.corecap[b0]) { if (tid == 0) { out[0] = 1; out[1] = N - 1; } }
+        else {
+            double* T = Q.cores[b0];
+            for (long long e = tid; e < q * nJ; e += NT) {
+                const int row = (int)(e % q);
+                const int ir = row % nI, dig = row / nI + 1;
+                S st;
+                if (carried) st = carry[ir];
+                else { st = f.zero(); const int* rw = mov + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, rw[p]); }
+                f.push(st, b0, dig);
+                const double v = f.finish(f.merge(st, f.zero()));
+                T[e] = v;
+                const double a = fabs(v);
+                if (a != a) isn = true; else mx = a > mx ? a : mx;
+            }
+        }
+    }
+    unsigned long long b = (unsigned long long)__double_as_longlong(mx);
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) { const unsigned long long o = __shfl_down_sync(FULL, b, dd); b = o > b ? o : b; }
     const unsigned anyn = __ballot_sync(FULL, isn);
     if (lane == 0) { if (b) atomicMax(P.acc, b); if (anyn) atomicOr(reinterpret_cast<int*>(P.acc + 1), 1); }
 }
@@ -554,6 +840,89 @@ int run_halfsweep(tci_handle h, const F& f, SweepParams P, const SweepShape& sh,
     return launch_halfsweep<F, 1024, kMaxCS>(h, f, P, kDynBytes);
 }
 
+
+// staging of one launch: arena words, then (8-byte aligned) extra blocks; ONE host-to-device copy
+struct Staging {
+    std::vector<unsigned char> bytes;
+    size_t add(const void* p, size_t n, size_t align = 8) {
+        size_t off = (bytes.size() + align - 1) / align * align;
+        bytes.resize(off + n);
+        if (n) memcpy(bytes.data() + off, p, n);
+        return off;
+    }
+};
+
+template <class F>
+int launch_fill(tci_handle h, const F& f, const FillParams& P, int nblocks, int rmax) {
+    auto kern = dsweep_fill_kernel<F>;
+    const size_t smem = sizeof(double) * ((size_t)(rmax | 1) * rmax + (size_t)rmax * kSolveRows);
+    static thread_local int optin_done = 0;
+    if (smem > 48 * 1024 && !optin_done) {
+        const size_t most = sizeof(double) * ((size_t)(kSolveMaxR | 1) * kSolveMaxR + (size_t)kSolveMaxR * kSolveRows);
+        TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)most));
+        optin_done = 1;
+    }
+    kern<<<nblocks, kSolveRows, smem, h->stream>>>(f, P);
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+template <class F>
+int launch_sweep1(tci_handle h, const F& f, Sweep1Params Q, long long maxelems) {
+    Q.sp.smem_bytes = kDynBytes;
+    if (maxelems <= 4096) {
+        auto kern = dsweep_sweep1site_kernel<F, 256>;
+        static thread_local int optin_a = 0;
+        if (!optin_a) { TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynBytes)); optin_a = 1; }
+        kern<<<1, 256, kDynBytes, h->stream>>>(f, Q);
+    } else {
+        auto kern = dsweep_sweep1site_kernel<F, 1024>;
+        static thread_local int optin_b = 0;
+        if (!optin_b) { TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynBytes)); optin_b = 1; }
+        kern<<<1, 1024, kDynBytes, h->stream>>>(f, Q);
+    }
+    TCI_LAUNCH_CHECK(h);
+    return TCI_OK;
+}
+
+int check_arena(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, const char* who) {
+    if (!f || !h_in || in_words < kHdr) return tci_fail(h, TCI_ERR_INVALID, "%s: bad arguments", who);
+    if (!tci_dsweep_supported(h, f)) return tci_fail(h, TCI_ERR_INVALID, "%s: needs a built-in device functor", who);
+    const int N = h_in[0];
+    if (N < 2 || N > 128 || in_words < kHdr + (int64_t)N * (1 + kDesc)) return tci_fail(h, TCI_ERR_INVALID, "%s: malformed input arena", who);
+    if (f->kind == TCI_F_DENSE && f->ndims != N) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, N);
+    return TCI_OK;
+}
+
+// read the append-only output arena back: a prefix first, the rest only when more was written
+int read_out(tci_handle h, const int* d_out, int32_t* h_out, int64_t out_cap_words, int64_t* h_used_words, const char* who) {
+    const int64_t first = std::min<int64_t>(out_cap_words, 16384);
+    int rc = tci_pinned_reserve(h, (size_t)first * 4); if (rc) return rc;
+    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, d_out, (size_t)first * 4, cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    memcpy(h_out, h->pinned, (size_t)first * 4);
+    const int64_t used = h_out[2];
+    if (used > out_cap_words) return tci_fail(h, TCI_ERR_INVALID, "%s: output arena overrun", who);
+    if (used > first) {
+        TCI_CUDA(h, cudaMemcpyAsync(h_out + first, d_out + first, (size_t)(used - first) * 4, cudaMemcpyDeviceToHost, h->stream));
+        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    if (h_used_words) *h_used_words = used;
+    return TCI_OK;
+}
+
+#define TCI_DS_DISPATCH(rc, f, CALL)                                                                                         \
+    switch ((f)->kind) {                                                                                                     \
+    case TCI_F_LORENTZ: { LorentzF F_{(f)->p[0]}; rc = CALL; } break;                                                        \
+    case TCI_F_SUM: { SumF F_{(f)->p[0]}; rc = CALL; } break;                                                                \
+    case TCI_F_QEXPSIN: { QuanticsF<TCI_F_QEXPSIN> F_{(f)->p[0], (f)->p[1], (f)->p[2]}; rc = CALL; } break;                  \
+    case TCI_F_QEXPPLUSSIN: { QuanticsF<TCI_F_QEXPPLUSSIN> F_{(f)->p[0], (f)->p[1], (f)->p[2]}; rc = CALL; } break;          \
+    case TCI_F_QEXP2: { QuanticsF<TCI_F_QEXP2> F_{(f)->p[0], (f)->p[1], (f)->p[2]}; rc = CALL; } break;                      \
+    case TCI_F_HASH: { HashF F_{(f)->p[0], (f)->p[1]}; rc = CALL; } break;                                                   \
+    case TCI_F_DENSE: { DenseF F_{(f)->d_table, (f)->d_strides}; rc = CALL; } break;                                         \
+    default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", (f)->kind);                                        \
+    }
+
 } // namespace
 
 extern "C" {
@@ -602,20 +971,84 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
     }
     if (rc) return rc;
-    // the output is append-only: read a prefix, then the rest only when more was written
-    const int64_t first = std::min<int64_t>(out_cap_words, 16384);
-    rc = tci_pinned_reserve(h, (size_t)first * 4); if (rc) return rc;
-    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, P.out, (size_t)first * 4, cudaMemcpyDeviceToHost, h->stream));
-    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
-    memcpy(h_out, h->pinned, (size_t)first * 4);
-    const int64_t used = h_out[2];
-    if (used > out_cap_words) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: output arena overrun");
-    if (used > first) {
-        TCI_CUDA(h, cudaMemcpyAsync(h_out + first, P.out + first, (size_t)(used - first) * 4, cudaMemcpyDeviceToHost, h->stream));
-        TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    return read_out(h, P.out, h_out, out_cap_words, h_used_words, "tci_dsweep_halfsweep_f64");
+}
+
+int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, void* d_acc16, double* const* h_d_cores) {
+    if (!h) return TCI_ERR_INVALID;
+    int rc = check_arena(h, f, h_in, in_words, "tci_dsweep_fill_f64"); if (rc) return rc;
+    if (!d_acc16 || !h_d_cores) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_fill_f64: NULL argument");
+    const int N = h_in[0];
+    const int32_t* ld = h_in + kHdr; const int32_t* desc = ld + N;
+    std::vector<int> blockmap;
+    int rmax = 1;
+    for (int b = 0; b < N; ++b) {
+        const int nI = desc[kDesc * b + 0], nJ = desc[kDesc * b + 2];
+        if (b < N - 1) {
+            if (desc[kDesc * (b + 1) + 0] != nJ) return tci_fail(h, TCI_ERR_NOT_SQUARE, "Pivot matrix at bond %d is not square!", b + 1);
+            if (nJ > kSolveMaxR) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_fill_f64: bond dimension %d > %d", nJ, kSolveMaxR);
+            rmax = std::max(rmax, nJ);
+        }
+        if (!h_d_cores[b]) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_fill_f64: NULL core buffer");
+        const long long q = (long long)nI * ld[b];
+        for (long long r0 = 0; r0 < q; r0 += kSolveRows) { blockmap.push_back(b); blockmap.push_back((int)r0); }
     }
-    if (h_used_words) *h_used_words = used;
+    if (blockmap.empty()) return TCI_OK;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    Staging st;
+    st.add(h_in, (size_t)in_words * 4);
+    const size_t off_c = st.add(h_d_cores, sizeof(double*) * (size_t)N);
+    const size_t off_b = st.add(blockmap.data(), sizeof(int) * blockmap.size());
+    const int zero = 0;
+    const size_t off_f = st.add(&zero, sizeof(int));
+    rc = tci_ws_reserve(h, h->ws_c, st.bytes.size() + 256); if (rc) return rc;
+    unsigned char* base = (unsigned char*)h->ws_c.ptr;
+    TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
+    FillParams P;
+    P.in = (const int*)base; P.cores = (double* const*)(base + off_c); P.blockmap = (const int*)(base + off_b);
+    P.acc = (unsigned long long*)d_acc16; P.flag = (int*)(base + off_f);
+    const int nblocks = (int)(blockmap.size() / 2);
+    TCI_DS_DISPATCH(rc, f, launch_fill(h, F_, P, nblocks, rmax))
+    if (rc) return rc;
+    rc = tci_pinned_reserve(h, 64); if (rc) return rc;
+    TCI_CUDA(h, cudaMemcpyAsync(h->pinned, P.flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    TCI_CUDA(h, cudaStreamSynchronize(h->stream));
+    const int flag = *(int*)h->pinned;
+    if (flag) return tci_fail(h, TCI_ERR_INVALID, "tci_solve_right_f64: pivot matrix is singular (site %d)", flag);
     return TCI_OK;
+}
+
+int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
+                              void* d_acc16, double* const* h_d_cores, const int64_t* h_core_capacity, int32_t* h_out,
+                              int64_t out_cap_words, int64_t* h_used_words) {
+    if (!h) return TCI_ERR_INVALID;
+    int rc = check_arena(h, f, h_in, in_words, "tci_dsweep_sweep1site_f64"); if (rc) return rc;
+    const int N = h_in[0];
+    if (!d_acc16 || !h_d_cores || !h_core_capacity || !h_out || out_cap_words < kHdr + (int64_t)kStepRec * (N - 1))
+        return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_sweep1site_f64: bad arguments");
+    const int32_t* ld = h_in + kHdr; const int32_t* desc = ld + N;
+    long long maxelems = 0;
+    for (int b = 0; b < N - 1; ++b) {
+        const long long nIb = b == 0 ? desc[0] : desc[kDesc * (b - 1) + 2];          // |Iset[b]| after the previous bond <= |Jset[b-1]|
+        maxelems = std::max(maxelems, nIb * ld[b] * (long long)desc[kDesc * b + 2]);
+    }
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    Staging st;
+    st.add(h_in, (size_t)in_words * 4);
+    const size_t off_c = st.add(h_d_cores, sizeof(double*) * (size_t)N);
+    std::vector<long long> cap(h_core_capacity, h_core_capacity + N);
+    const size_t off_k = st.add(cap.data(), sizeof(long long) * (size_t)N);
+    const size_t in_b = (st.bytes.size() + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
+    rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + 256); if (rc) return rc;
+    unsigned char* base = (unsigned char*)h->ws_c.ptr;
+    TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
+    Sweep1Params Q;
+    Q.sp.in = (const int*)base; Q.sp.out = (int*)(base + in_b); Q.sp.out_cap = out_cap_words; Q.sp.reltol = reltol; Q.sp.abstol = abstol;
+    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes;
+    Q.cores = (double* const*)(base + off_c); Q.corecap = (const long long*)(base + off_k);
+    TCI_DS_DISPATCH(rc, f, launch_sweep1(h, F_, Q, maxelems))
+    if (rc) return rc;
+    return read_out(h, Q.sp.out, h_out, out_cap_words, h_used_words, "tci_dsweep_sweep1site_f64");
 }
 
 } // extern "C"

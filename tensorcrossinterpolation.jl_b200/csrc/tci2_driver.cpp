@@ -491,17 +491,31 @@ int setsitetensor(tci_tci2 t, tci_functor f, int b0) {
     return TCI_OK;
 }
 
+int device_fillsitetensors(tci_tci2 t, tci_functor f, bool* done);
+
 int fillsitetensors(tci_tci2 t, tci_functor f) {                                             // globalsearch.jl:202-208
+    if (t->engine == 1 && tci_dsweep_supported(t->h, f)) {
+        bool done = false;
+        int rc = device_fillsitetensors(t, f, &done); if (rc) return rc;
+        if (done) return TCI_OK;
+    }
     for (int b0 = 0; b0 < t->N; ++b0) { int rc = setsitetensor(t, f, b0); if (rc) return rc; }
     return TCI_OK;
 }
 
 // sweep1site! (tensorci2.jl:659-725)
+int device_sweep1site(tci_tci2 t, tci_functor f, double reltol, double abstol, int64_t maxbonddim, int* next_step);
+
 int sweep1site(tci_tci2 t, tci_functor f, bool fwd, double reltol, double abstol, int64_t maxbonddim, bool updatetensors) {
     t->pivoterrors.clear();                                                                  // flushpivoterror!
     invalidate(t);
     const int N = t->N;
-    for (int step = 0; step < N - 1; ++step) {
+    int first = 0;
+    if (t->engine == 1 && fwd && updatetensors && tci_dsweep_supported(t->h, f)) {           // the whole pass as ONE launch (csrc/sweep.cu)
+        int rc = device_sweep1site(t, f, reltol, abstol, maxbonddim, &first); if (rc) return rc;
+        if (first > N - 1) return sync_maxsample(t);                                          // every bond and the last tensor done
+    }
+    for (int step = first; step < N - 1; ++step) {
         const int b0 = fwd ? step : N - 1 - step;
         const int d = t->localdims[b0];
         IdxTable Is = fwd ? kronecker_left(t->I[b0], d) : t->I[b0];                          // :679-680
@@ -569,6 +583,24 @@ void append_table(std::vector<int32_t>& a, const IdxTable* t, int32_t* cnt_off) 
     if (t && !t->v.empty()) a.insert(a.end(), t->v.begin(), t->v.end());
 }
 
+void pack_sets(tci_tci2 t, std::vector<int32_t>& a, bool fwd, int s0, int s1, int64_t maxbonddim, const std::vector<IdxTable>* extraI,
+               const std::vector<IdxTable>* extraJ) {
+    const int N = t->N;
+    const bool useextra = extraI != nullptr;
+    a.assign((size_t)kArenaHdr + (size_t)N * (1 + kArenaDesc), 0);
+    a[0] = N; a[1] = fwd ? 1 : 0; a[2] = s0; a[3] = s1;
+    a[4] = (maxbonddim <= 0 || maxbonddim > 0x7fffffff) ? 0 : (int32_t)maxbonddim; a[5] = useextra ? 1 : 0;
+    for (int b = 0; b < N; ++b) a[(size_t)kArenaHdr + b] = t->localdims[b];
+    for (int b = 0; b < N; ++b) {
+        int32_t d[8];
+        append_table(a, &t->I[b], d + 0);
+        append_table(a, &t->J[b], d + 2);
+        append_table(a, useextra ? &(*extraI)[b] : nullptr, d + 4);
+        append_table(a, useextra ? &(*extraJ)[b] : nullptr, d + 6);
+        std::memcpy(a.data() + kArenaHdr + N + (size_t)kArenaDesc * b, d, sizeof d);
+    }
+}
+
 int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t maxbonddim, const std::vector<IdxTable>* extraI,
                      const std::vector<IdxTable>* extraJ) {
     const int N = t->N;
@@ -590,20 +622,7 @@ int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t
         }
         const double t0 = now_s();
         std::vector<int32_t>& a = t->arena_in;
-        a.assign((size_t)kArenaHdr + (size_t)N * (1 + kArenaDesc), 0);
-        a[0] = N; a[1] = fwd ? 1 : 0; a[2] = s; a[3] = N - 1;
-        a[4] = (maxbonddim <= 0 || maxbonddim > 0x7fffffff) ? 0 : (int32_t)maxbonddim; a[5] = useextra ? 1 : 0;
-        for (int b = 0; b < N; ++b) a[(size_t)kArenaHdr + b] = t->localdims[b];
-        int64_t rowsum = 0;
-        for (int b = 0; b < N; ++b) {
-            int32_t d[8];
-            append_table(a, &t->I[b], d + 0);
-            append_table(a, &t->J[b], d + 2);
-            append_table(a, useextra ? &(*extraI)[b] : nullptr, d + 4);
-            append_table(a, useextra ? &(*extraJ)[b] : nullptr, d + 6);
-            std::memcpy(a.data() + kArenaHdr + N + (size_t)kArenaDesc * b, d, sizeof d);
-            rowsum = std::max<int64_t>(rowsum, std::max(t->I[b].n, t->J[b].n));
-        }
+        pack_sets(t, a, fwd, s, N - 1, maxbonddim, extraI, extraJ);
         // output capacity: every bond may return up to rcap rows of N ints twice; rcap is bounded by what fits the kernel (512)
         int64_t rcap = 512;
         if (maxbonddim > 0 && maxbonddim < rcap) rcap = maxbonddim;
@@ -638,6 +657,92 @@ int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t
             if (rc) return rc;
             ++s;
         }
+    }
+    return TCI_OK;
+}
+
+// fillsitetensors! (globalsearch.jl:202-208) as ONE launch over all sites (tci_dsweep_fill_f64) when every bond is <= 64
+int device_fillsitetensors(tci_tci2 t, tci_functor f, bool* done) {
+    const int N = t->N;
+    *done = false;
+    for (int b = 0; b + 1 < N; ++b) {
+        if (t->J[b].n > 64 || t->J[b].n < 1 || t->I[b].n < 1) return TCI_OK;
+        if (t->I[b + 1].n != t->J[b].n) return fail(t, TCI_ERR_NOT_SQUARE, "Pivot matrix at bond %d is not square!", b + 1);   // :623
+    }
+    if (t->I[N - 1].n < 1 || t->J[N - 1].n < 1) return TCI_OK;
+    const double t0 = now_s();
+    std::vector<double*> ptrs((size_t)N);
+    for (int b = 0; b < N; ++b) {
+        Core& c = t->T[b];
+        const int64_t q = t->I[b].n * t->localdims[b], r = t->J[b].n;
+        int rc = reserve(t, c.buf, (size_t)(q * r)); if (rc) return rc;
+        ptrs[(size_t)b] = c.buf.p;
+    }
+    pack_sets(t, t->arena_in, true, 0, 0, 0, nullptr, nullptr);
+    TCI2_CALL(t, tci_dsweep_fill_f64(t->h, f, t->arena_in.data(), (int64_t)t->arena_in.size(), t->acc, ptrs.data()));
+    for (int b = 0; b < N; ++b) {
+        Core& c = t->T[b];
+        c.chil = t->I[b].n; c.d = t->localdims[b]; c.chir = t->J[b].n; c.valid = true;
+        t->nevals += c.chil * c.d * c.chir + (b + 1 < N ? c.chir * c.chir : 0);
+    }
+    t->t_factors += now_s() - t0;
+    *done = true;
+    return TCI_OK;
+}
+
+// sweep1site!(tci, f, :forward; updatetensors=true) (tensorci2.jl:659-725) as ONE launch (tci_dsweep_sweep1site_f64).  *next_step =
+// the first step the kernel did NOT do (N: everything including the last tensor; the caller continues from there per bond).
+int device_sweep1site(tci_tci2 t, tci_functor f, double reltol, double abstol, int64_t maxbonddim, int* next_step) {
+    const int N = t->N;
+    *next_step = 0;
+    for (int b = 0; b < N; ++b) if (t->I[b].n < 1 || t->J[b].n < 1) return TCI_OK;
+    const double t0 = now_s();
+    std::vector<double*> ptrs((size_t)N);
+    std::vector<int64_t> caps((size_t)N);
+    for (int b = 0; b < N; ++b) {                          // |Iset[b]| after bond b-1 <= |Jset[b-1]|, the new |Jset[b]| <= the old one
+        const int64_t nIb = b == 0 ? t->I[0].n : t->J[b - 1].n;
+        caps[(size_t)b] = nIb * t->localdims[b] * std::max<int64_t>(t->J[b].n, 1);
+        int rc = reserve(t, t->T[b].buf, (size_t)caps[(size_t)b]); if (rc) return rc;
+        ptrs[(size_t)b] = t->T[b].buf.p;
+        caps[(size_t)b] = (int64_t)t->T[b].buf.cap;
+    }
+    pack_sets(t, t->arena_in, true, 0, N - 1, maxbonddim, nullptr, nullptr);
+    int64_t rcap = 512;
+    if (maxbonddim > 0 && maxbonddim < rcap) rcap = maxbonddim;
+    const int64_t cap = kArenaHdr + (int64_t)kArenaStep * (N - 1) + (int64_t)(N - 1) * (rcap * (N + 1) + 2 * (rcap + 2));
+    t->arena_out.resize((size_t)cap);
+    int64_t used = 0;
+    TCI2_CALL(t, tci_dsweep_sweep1site_f64(t->h, f, t->arena_in.data(), (int64_t)t->arena_in.size(), reltol, abstol, t->acc, ptrs.data(),
+                                           caps.data(), t->arena_out.data(), cap, &used));
+    const int32_t* o = t->arena_out.data();
+    const int status = o[0], next = o[1];
+    t->ndevsweeps++;
+    for (int b0 = 0; b0 < next && b0 < N - 1; ++b0) {
+        const int32_t* rec = o + kArenaHdr + (size_t)kArenaStep * b0;
+        const int r = rec[0];
+        const int64_t nIb = t->I[b0].n;                    // already the new Iset[b0] (set by the previous step)
+        IdxTable& nI = t->I[b0 + 1]; IdxTable& nJ = t->J[b0];
+        nI.n = r; nI.v.assign(o + rec[1], o + rec[1] + (size_t)r * nI.len);
+        nJ.n = r; nJ.v.assign(o + rec[2], o + rec[2] + (size_t)r * nJ.len);
+        std::vector<double> errs((size_t)r + 1);
+        std::memcpy(errs.data(), o + rec[3], sizeof(double) * ((size_t)r + 1));
+        updateerrors(t, b0, errs);
+        Core& c = t->T[b0];
+        c.chil = nIb; c.d = t->localdims[b0]; c.chir = r; c.valid = true;
+        t->nevals += (int64_t)rec[4] * rec[5];
+        t->nbondupdates++; t->ndevbonds++;
+    }
+    t->t_lu += now_s() - t0;
+    if (status == 2) return fail(t, TCI_ERR_NAN_L, "lu.L contains NaNs");
+    if (status == 3) return fail(t, TCI_ERR_NAN_U, "lu.U contains NaNs");
+    if (status == 4) return fail(t, TCI_ERR_NAN_TENSOR, "Error: NaN in tensor T[%d]", next + 1);
+    if (status == 0) {                                     // the last tensor was evaluated too
+        Core& c = t->T[N - 1];
+        c.chil = t->I[N - 1].n; c.d = t->localdims[N - 1]; c.chir = t->J[N - 1].n; c.valid = true;
+        t->nevals += c.chil * c.d * c.chir;
+        *next_step = N;
+    } else {
+        *next_step = next;                                 // status 1: bond `next` (or the last tensor, next == N - 1) does not fit
     }
     return TCI_OK;
 }

@@ -245,4 +245,107 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* in, int
     return TCI_OK;
 }
 
+int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* in, int64_t, void* acc, double* const* cores) {
+    h->ncalls++;
+    const int N = in[0];
+    const int32_t* ld = in + 8; const int32_t* desc = ld + N;
+    MockAcc* a = (MockAcc*)acc;
+    for (int b = 0; b < N; ++b) {
+        const int nI = desc[8 * b], nJ = desc[8 * b + 2], d = ld[b];
+        const int32_t* tI = in + desc[8 * b + 1]; const int32_t* tJ = in + desc[8 * b + 3];
+        const int64_t q = (int64_t)nI * d;
+        static const int32_t dummy = 0;
+        std::vector<double> pi1((size_t)(q * nJ));
+        if (orc_batcheval((void*)f, ld, N, b > 0 ? tI : &dummy, nI, b, N - b - 1 > 0 ? tJ : &dummy, nJ, N - b - 1, 1, pi1.data()))
+            return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        double mx = a->nan ? NAN : a->mx;
+        merge_maxabs(&mx, pi1.data(), pi1.size());
+        if (b == N - 1) { std::memcpy(cores[b], pi1.data(), sizeof(double) * pi1.size()); }
+        else {
+            const int nI1 = desc[8 * (b + 1)];
+            if (nI1 != nJ) return mfail(h, TCI_ERR_NOT_SQUARE, "Pivot matrix at bond is not square!");
+            std::vector<double> Pm((size_t)nJ * nJ), X((size_t)(q * nJ));
+            if (orc_batcheval((void*)f, ld, N, in + desc[8 * (b + 1) + 1], nI1, b + 1, N - b - 1 > 0 ? tJ : &dummy, nJ, N - b - 1, 0, Pm.data()))
+                return mfail(h, TCI_ERR_INVALID, orc_last_error());
+            merge_maxabs(&mx, Pm.data(), Pm.size());
+            if (orc_solve_right(Pm.data(), nJ, pi1.data(), q, X.data())) return mfail(h, TCI_ERR_INVALID, "tci_solve_right_f64: pivot matrix is singular");
+            std::memcpy(cores[b], X.data(), sizeof(double) * X.size());
+        }
+        if (mx != mx) a->nan = 1; else a->mx = mx;
+    }
+    return TCI_OK;
+}
+
+int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* in, int64_t, double reltol, double abstol, void* acc,
+                              double* const* cores, const int64_t* corecap, int32_t* out, int64_t out_cap, int64_t* used_words) {
+    h->ncalls++;
+    const int N = in[0], maxbond = in[4];
+    const int32_t* ld = in + 8; const int32_t* desc = ld + N;
+    int64_t used = 8 + 6LL * (N - 1);
+    out[0] = 0; out[1] = N - 1; out[2] = (int)used;
+    MockAcc* a = (MockAcc*)acc;
+    std::vector<int32_t> mov(in + desc[1], in + desc[1] + 0);       // Iset[0]: rows of length 0
+    int nmov = desc[0];
+    static const int32_t dummy = 0;
+    bool stopped = false;
+    for (int b0 = 0; b0 < N - 1; ++b0) {
+        const int d = ld[b0], nI = nmov, nJ = desc[8 * b0 + 2];
+        const int32_t* tJ = in + desc[8 * b0 + 3];
+        const int64_t m = (int64_t)nI * d, n = nJ, mn = m < n ? m : n;
+        const int64_t rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
+        if (m * n > g_dsweep_limit || m * rcap > corecap[b0] || used + rcap * (N + 1) + 2 * (rcap + 2) > out_cap) { out[0] = 1; out[1] = b0; stopped = true; break; }
+        std::vector<double> Pi((size_t)(m * n));
+        if (orc_batcheval((void*)f, ld, N, b0 > 0 ? mov.data() : &dummy, nI, b0, N - b0 - 1 > 0 ? tJ : &dummy, nJ, N - b0 - 1, 1, Pi.data()))
+            return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        double mx = a->nan ? NAN : a->mx;
+        merge_maxabs(&mx, Pi.data(), Pi.size());
+        if (mx != mx) a->nan = 1; else a->mx = mx;
+        std::vector<int64_t> rp((size_t)m), cp((size_t)n);
+        std::vector<double> pe((size_t)rcap + 1), Lm((size_t)(m * rcap)), Um((size_t)(rcap * n));
+        int64_t r = 0; double err = 0.0;
+        const int st = orc_rrlu(Pi.data(), m, n, m, rcap, reltol, abstol, 1, rp.data(), cp.data(), &r, &err, Lm.data(), m, Um.data(), rcap, pe.data());
+        if (st == -1) { out[0] = 2; out[1] = b0; stopped = true; break; }
+        if (st == -2) { out[0] = 3; out[1] = b0; stopped = true; break; }
+        if (st) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        std::vector<double> left((size_t)(m * r)), right((size_t)(r * n));
+        if (r > 0 && orc_luci_factors(m, n, r, 1, rp.data(), cp.data(), Lm.data(), m, Um.data(), rcap, left.data(), right.data()))
+            return mfail(h, TCI_ERR_INVALID, orc_last_error());
+        bool tnan = false;
+        for (double v : left) if (v != v) tnan = true;
+        std::memcpy(cores[b0], left.data(), sizeof(double) * left.size());
+        if (tnan) { out[0] = 4; out[1] = b0; stopped = true; break; }
+        const int lenA = b0 + 1, lenB = N - b0 - 1;
+        const int64_t offA = used, offB = offA + r * lenA; int64_t offE = offB + r * lenB; offE += offE & 1;
+        std::vector<int32_t> newI((size_t)(r * lenA));
+        for (int64_t k = 0; k < r; ++k) {
+            const int64_t i = rp[(size_t)k] - 1;
+            for (int p = 0; p < b0; ++p) newI[(size_t)(k * lenA + p)] = mov[(size_t)((i % nI) * b0 + p)];
+            newI[(size_t)(k * lenA + b0)] = (int32_t)(i / nI + 1);
+            std::memcpy(out + offB + k * lenB, tJ + (cp[(size_t)k] - 1) * lenB, sizeof(int32_t) * lenB);
+        }
+        std::memcpy(out + offA, newI.data(), sizeof(int32_t) * newI.size());
+        std::memcpy(out + offE, pe.data(), sizeof(double) * (size_t)(r + 1));
+        int32_t* rec = out + 8 + 6 * b0;
+        rec[0] = (int)r; rec[1] = (int)offA; rec[2] = (int)offB; rec[3] = (int)offE; rec[4] = (int)m; rec[5] = (int)n;
+        used = offE + 2 * (r + 1);
+        out[2] = (int)used;
+        mov = newI; nmov = (int)r;
+    }
+    if (!stopped) {
+        const int b0 = N - 1, d = ld[b0], nJ = desc[8 * b0 + 2];
+        const int64_t q = (int64_t)nmov * d;
+        if (q * nJ > corecap[b0]) { out[0] = 1; out[1] = N - 1; }
+        else {
+            std::vector<double> T((size_t)(q * nJ));
+            if (orc_batcheval((void*)f, ld, N, mov.data(), nmov, b0, &dummy, nJ, 0, 1, T.data())) return mfail(h, TCI_ERR_INVALID, orc_last_error());
+            double mx = a->nan ? NAN : a->mx;
+            merge_maxabs(&mx, T.data(), T.size());
+            if (mx != mx) a->nan = 1; else a->mx = mx;
+            std::memcpy(cores[b0], T.data(), sizeof(double) * T.size());
+        }
+    }
+    if (used_words) *used_words = used;
+    return TCI_OK;
+}
+
 } // extern "C"
