@@ -168,6 +168,7 @@ struct SweepParams {
     double* xs_g;                            // cluster variant: [2][CS][mcap] candidate columns
     int mcap;
     int smem_bytes;                          // dynamic shared memory available per CTA
+    long long* prof;                         // diagnostics (TCI_DSWEEP_PROF=1): clock64 cycles thread 0 of CTA 0 spent per phase, else NULL
 };
 
 #define TCI_DS_CONSIDER(v, ii, jj)                                                                          \
@@ -193,7 +194,7 @@ struct SweepParams {
 template <int NT, int CS>
 __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int n, const int rcap, const int fwd, const double reltol,
                                          const double abstol, Win best, Win (*s_w)[32], Win (*s_cl)[kMaxCS], const SweepParams& P,
-                                         const int crank, double* error_out) {
+                                         const int crank, double* error_out, long long* pc = nullptr) {
     constexpr int NW = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* A = c.A;
@@ -201,6 +202,8 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int 
         int np = 0;
         double maxerror = 0.0, error = nan("");
         unsigned rmask = 0xffffffffu;                  // bit q: row lane + 32 q is still in the trailing block
+        long long tc0 = clock64();
+#define TCI_DS_TICK(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tc0; tc0 = t1__; } }
         for (;;) {
             if (best.i >= 0) best.pos = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];
             else { best.key = 0; best.pos = 0xffffffffu; }
@@ -210,6 +213,7 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int 
             __syncthreads();                                                        // barrier 1
             Win g = (lane < NW) ? sw[lane] : Win{0ull, 0.0, 0xffffffffu, -1, -1, 0};
             warp_argmax(g);                                                         // every warp: the CTA's winner
+            TCI_DS_TICK(0)
             double piv_own = g.x;
             if constexpr (CS > 1) {
                 // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
@@ -228,6 +232,7 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int 
                 for (int cc = 1; cc < CS; ++cc) { const Win o = s_cl[par][cc]; if (win_before(o, w)) { w = o; owner = cc; } }
                 g = w; g.pad = owner;
             }
+            TCI_DS_TICK(1)
             int pi, pj; double piv;
             if (g.key == 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }   // all-NaN block: the reference keeps (k, k)
             else { pi = g.i; pj = g.j; piv = g.x; }
@@ -261,6 +266,7 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int 
             }
             if ((pi & 31) == lane) rmask &= ~(1u << (pi >> 5));
             __syncthreads();                                                        // barrier 2
+            TCI_DS_TICK(2)
             np = k + 1;
             if (np >= rcap) break;                                                  // :356
             best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1;
@@ -277,6 +283,7 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int 
                     TCI_DS_CONSIDER(v, i, j)
                 }
             }
+            TCI_DS_TICK(3)
         }
         const int r = np;
         if (r >= (m < n ? m : n)) error = 0.0;                                       // :391-393
@@ -359,6 +366,10 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
     int nmov = -1;                           // ... -1: take it from the input arena (first step of the launch)
     double mx = 0.0; bool isn = false;       // running max |f| of this thread
 
+    long long pcnt[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    long long* pc = (P.prof && writer && tid == 0) ? pcnt : nullptr;
+    long long tk0 = clock64();
+#define TCI_DS_PHASE(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tk0; tk0 = t1__; } }
     for (int s = s0; s < s1; ++s) {
         const int b0 = fwd ? s : N - 2 - s;
         const int dL = ld[b0], dR = ld[b0 + 1];
@@ -393,6 +404,7 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
             if (lane == 0) s_keepJ = k;
         }
         __syncthreads();
+        TCI_DS_PHASE(4)
         const int nKI = s_keepI, nKJ = s_keepJ;
         const int mk = nI * dL, nk = dR * nJ;          // kronecker parts
         const int m = mk + nKI, n = nk + nKJ;
@@ -454,6 +466,7 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         }
         if (tid == 0) s_flags = 0;
         __syncthreads();
+        TCI_DS_PHASE(5)
 
         // ---- Pi (own columns) + the first pivot search (positions are the identity)
         double* A = c.A;
@@ -471,9 +484,12 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
             }
         }
 
+        TCI_DS_PHASE(6)
         double error;
-        const int r = smem_rrlu<NT, CS>(c, m, n, rcap, fwd, P.reltol, P.abstol, best, s_w, s_cl, P, crank, &error);
+        const int r = smem_rrlu<NT, CS>(c, m, n, rcap, fwd, P.reltol, P.abstol, best, s_w, s_cl, P, crank, &error, pc);
+        if (pc) { tk0 = clock64(); pc[10] += r; pc[11] += 1; }
         lu_nan_flags<NT, CS>(c, m, n, r, fwd, crank, &s_flags);
+        TCI_DS_PHASE(7)
         if (s_flags) {
             if (writer && tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = s; }
             break;
@@ -514,7 +530,9 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         nmov = r;
         __threadfence();
         cluster_or_block_sync<CS>();                   // the new rows (global) and `carry` are visible to every thread / CTA
+        TCI_DS_PHASE(8)
     }
+    if (pc) for (int q = 0; q < 12; ++q) P.prof[q] = pcnt[q];
 
     // ---- updatemaxsample! (tensorci2.jl:636-638): one atomic per warp
     unsigned long long b = (unsigned long long)__double_as_longlong(mx);
@@ -952,11 +970,13 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     const int mcap = ((std::max(sh.maxm, 1) * 2 + 63) / 64) * 64;                  // room for the moving set to grow
     const size_t in_b = ((size_t)in_words * 4 + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
     const size_t xs_b = sizeof(double) * 2 * kMaxCS * (size_t)mcap;
-    int rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + xs_b + 256); if (rc) return rc;
+    int rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + xs_b + 512); if (rc) return rc;
     unsigned char* base = (unsigned char*)h->ws_c.ptr;
     SweepParams P;
     P.in = (const int*)base; P.out = (int*)(base + in_b); P.out_cap = out_cap_words; P.reltol = reltol; P.abstol = abstol;
     P.acc = (unsigned long long*)d_acc16; P.xs_g = (double*)(base + in_b + out_b); P.mcap = mcap; P.smem_bytes = 0;
+    const bool prof = getenv("TCI_DSWEEP_PROF") != nullptr;
+    P.prof = prof ? (long long*)(base + in_b + out_b + xs_b) : nullptr;
     TCI_CUDA(h, cudaMemcpyAsync(base, h_in, (size_t)in_words * 4, cudaMemcpyHostToDevice, h->stream));
     const char* fe = getenv("TCI_DSWEEP_CLUSTER");         // tests: 1 / 8 force the single-CTA / cluster variant
     const int force_cs = fe ? atoi(fe) : 0;
@@ -971,7 +991,16 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
     }
     if (rc) return rc;
-    return read_out(h, P.out, h_out, out_cap_words, h_used_words, "tci_dsweep_halfsweep_f64");
+    rc = read_out(h, P.out, h_out, out_cap_words, h_used_words, "tci_dsweep_halfsweep_f64");
+    if (rc == TCI_OK && prof) {
+        long long pcs[12];
+        TCI_CUDA(h, cudaMemcpy(pcs, P.prof, sizeof pcs, cudaMemcpyDeviceToHost));
+        static const char* names[12] = {"lu.reduce", "lu.exchange", "lu.stage", "lu.update", "extras", "states", "fill", "lu+nan", "output", "-", "pivots", "bonds"};
+        fprintf(stderr, "dsweep prof (cycles):");
+        for (int q = 0; q < 12; ++q) if (q != 9) fprintf(stderr, " %s=%lld", names[q], pcs[q]);
+        fprintf(stderr, "\n");
+    }
+    return rc;
 }
 
 int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, void* d_acc16, double* const* h_d_cores) {
@@ -1044,7 +1073,7 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, 
     TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
     Sweep1Params Q;
     Q.sp.in = (const int*)base; Q.sp.out = (int*)(base + in_b); Q.sp.out_cap = out_cap_words; Q.sp.reltol = reltol; Q.sp.abstol = abstol;
-    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes;
+    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.prof = nullptr;
     Q.cores = (double* const*)(base + off_c); Q.corecap = (const long long*)(base + off_k);
     TCI_DS_DISPATCH(rc, f, launch_sweep1(h, F_, Q, maxelems))
     if (rc) return rc;
