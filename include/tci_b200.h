@@ -278,10 +278,11 @@ int tci_tt_evaluate_f64(tci_handle h, const double* const* h_core_ptrs, const in
  * ~210 KB; a cluster of 8 CTAs with distributed shared memory: ~1.7 MB).  The host keeps the index sets between launches and
  * exchanges them as int32 arenas:
  *   h_in  (in_words):  [0] N  [1] forward (1/0)  [2] s0  [3] s1  — steps [s0, s1) of the sweep order, bond b0 = forward ? s : N-2-s
- *                      (0-based) —  [4] maxbonddim (<= 0: none)  [5] useextra  [6..7] 0;  localdims[N];  per site b (8 words):
- *                      nI, offI, nJ, offJ, nXI, offXI, nXJ, offXJ — counts and word offsets of Iset[b] (rows of length b),
- *                      Jset[b] (rows of length N-b-1) and of the history entries used as extraIset / extraJset; then the tables
- *                      (row-major, 1-based values).
+ *                      (0-based) —  [4] maxbonddim (<= 0: none)  [5] useextra  [6] total number of table rows  [7] 0;  localdims[N];
+ *                      per site b (12 words): nI, offI, nJ, offJ, nXI, offXI, nXJ, offXJ — counts and word offsets of Iset[b]
+ *                      (rows of length b), Jset[b] (rows of length N-b-1) and of the history entries used as extraIset /
+ *                      extraJset — then baseI, baseJ, baseXI, baseXJ: the running row count before each table in the order
+ *                      I_0, J_0, XI_0, XJ_0, I_1, ...; then the tables (row-major, 1-based values).  The sets hold unique rows.
  *   h_out (capacity out_cap_words, *h_used_words written): [0] status — 0 all steps done, 1 stopped before step [1] because
  *                      its Pi does not fit (run that bond through tci_tci2_updatepivots-style calls and continue), 2 / 3
  *                      "lu.L / lu.U contains NaNs" at step [1];  [2] words used;  per step s-s0 (6 words at 8 + 6 (s-s0)):

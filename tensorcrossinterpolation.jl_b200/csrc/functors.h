@@ -49,7 +49,10 @@ struct QuanticsF {
     double p0, p1, p2;
     typedef double State;
     __device__ State zero() const { return 0.0; }
-    __device__ void push(State& s, int site, int v) const { s += ldexp((double)(v - 1), -(site + 1)); }
+    // (v - 1) * 2^-(site+1): the power of two is built from its exponent field (exact, the same value ldexp returns; site < 1022)
+    __device__ void push(State& s, int site, int v) const {
+        s += (double)(v - 1) * __longlong_as_double((long long)(1022 - site) << 52);
+    }
     __device__ State merge(State a, State b) const { return a + b; }
     __device__ double finish(State x) const {
         if (KIND == TCI_F_QEXPSIN) return exp(-p0 * x) * sin(2.0 * 3.14159265358979323846 * p1 * pow(x, p2));   // test_tensorci2.jl:437

@@ -61,36 +61,33 @@ namespace {
 //                            N-b0-1), offE (pivoterrors(luci): r+1 doubles at an even word offset), m, n (size of Pi)
 //         data
 constexpr int kHdr = 8;
-constexpr int kDesc = 8;
+constexpr int kDesc = 12;
 constexpr int kStepRec = 6;
 constexpr int kRMax = 512;                   // carried functor states (rows of the set that moves with the sweep)
 constexpr int kMaxCS = 8;
 constexpr unsigned FULL = 0xffffffffu;
 
-struct alignas(16) Win {                     // argmax candidate: key = bits(|a|^2) + 1 (0: none), pos = colpos << 16 | rowpos
-    unsigned long long key;
-    double x;
+// Argmax candidates.  key = bits of |a|^2 read as a SIGNED 64-bit integer (non-negative doubles order like their bit patterns);
+// NaN, inactive elements and "nothing yet" carry a negative key (NaN never wins, matrixlu.jl:55), so validity is `key >= 0`.
+// pos = colpos << 16 | rowpos: the element's place in the reference's swapped layout, which decides ties (smallest column,
+// then smallest row) and identifies the element (rowat / colat).
+constexpr long long kNoKey = (long long)0x8000000000000000ULL;
+
+struct alignas(16) Win {
+    long long key;
+    double x;                                // value of the candidate (cluster exchange)
     unsigned pos;
-    int i, j, pad;
+    int owner, pad0, pad1;
 };
 
-__device__ __forceinline__ void warp_argmax(Win& w) {
-    const unsigned hi = (unsigned)(w.key >> 32), lo = (unsigned)w.key;
+// argmax over the warp of (key descending, pos ascending): three redux.sync, the result is uniform — no shuffles
+__device__ __forceinline__ void warp_argmax(long long& key, unsigned& pos) {
+    const unsigned hi = (unsigned)((unsigned long long)key >> 32) ^ 0x80000000u, lo = (unsigned)key;
     const unsigned mhi = __reduce_max_sync(FULL, hi);
     const unsigned mlo = __reduce_max_sync(FULL, hi == mhi ? lo : 0u);
     const bool eq = hi == mhi && lo == mlo;
-    const unsigned mpos = __reduce_min_sync(FULL, eq ? w.pos : 0xffffffffu);
-    const unsigned b = __ballot_sync(FULL, eq && w.pos == mpos);
-    const int src = __ffs(b) - 1;
-    w.key = ((unsigned long long)mhi << 32) | mlo;
-    w.pos = mpos;
-    w.x = __shfl_sync(FULL, w.x, src);
-    w.i = __shfl_sync(FULL, w.i, src);
-    w.j = __shfl_sync(FULL, w.j, src);
-}
-
-__device__ __forceinline__ bool win_before(const Win& a, const Win& b) {       // a precedes b in the reference's scan
-    return a.key > b.key || (a.key == b.key && a.pos < b.pos);
+    pos = __reduce_min_sync(FULL, eq ? pos : 0xffffffffu);
+    key = (long long)(((unsigned long long)(mhi ^ 0x80000000u) << 32) | mlo);
 }
 
 __device__ __forceinline__ double jl_max(double a, double b) {                  // Julia's max propagates NaN
@@ -102,9 +99,15 @@ template <int CS> __device__ __forceinline__ void cluster_or_block_sync() {
     if constexpr (CS > 1) cg::this_cluster().sync(); else __syncthreads();
 }
 
+__device__ __forceinline__ unsigned long long mixh(int site, int v) {           // per-(site, value) hash term of an index row
+    unsigned long long z = ((unsigned long long)(unsigned)site << 32) | (unsigned)v;
+    z += 0x9e3779b97f4a7c15ULL; z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+    return z ^ (z >> 31);
+}
+
 struct Carve {                               // dynamic shared memory of one bond
-    double* A; int lds;
-    double* xs;
+    double* A; int lds, mp;                  // mp = length of rowpos / xs incl. padding (a multiple of 128 unless the flat map is used)
+    double* xs; double* ys;
     double* piv;
     void* Lst; void* Rst;
     int* rowpos; int* rowat; int* colpos; int* colat;
@@ -112,18 +115,25 @@ struct Carve {                               // dynamic shared memory of one bon
     size_t bytes;
 };
 
+constexpr int kFlat = 8;                     // flat element -> thread map: at most this many elements per thread
+
+template <int NT> __host__ __device__ inline bool use_flat(int m, int nloc) { return (long long)m * nloc <= (long long)kFlat * NT; }
+
 template <class S>
-__host__ __device__ inline Carve carve(unsigned char* base, int m, int n, int nloc, int rcap, int nXI, int nXJ) {
+__host__ __device__ inline Carve carve(unsigned char* base, int m, int n, int nloc, int rcap, int nXI, int nXJ, bool flat) {
     Carve c;
     size_t o = 0;
     auto take = [&](size_t bytes) { void* p = base ? (void*)(base + o) : nullptr; o += (bytes + 15) & ~(size_t)15; return p; };
-    c.lds = m | 1;
+    c.mp = flat ? m : (m + 127) / 128 * 128;             // rowpos / xs: padded to whole groups of 128 rows (position -1: never active)
+    c.lds = (flat ? m : (m + 31) / 32 * 32) | 1;         // a group's loads past the end of a column read the next column: harmless
+    if (!flat && nloc > 0) nloc += 1;                    // ... and past the last column this spare one
     c.A = (double*)take(sizeof(double) * (size_t)c.lds * (size_t)(nloc > 0 ? nloc : 1));
-    c.xs = (double*)take(sizeof(double) * (size_t)m);
+    c.xs = (double*)take(sizeof(double) * (size_t)c.mp);
+    c.ys = (double*)take(sizeof(double) * (size_t)(nloc > 0 ? nloc : 1));
     c.piv = (double*)take(sizeof(double) * (size_t)(rcap + 1));
     c.Lst = take(sizeof(S) * (size_t)m);
     c.Rst = take(sizeof(S) * (size_t)n);
-    c.rowpos = (int*)take(sizeof(int) * (size_t)m);
+    c.rowpos = (int*)take(sizeof(int) * (size_t)c.mp);
     c.rowat = (int*)take(sizeof(int) * (size_t)m);
     c.colpos = (int*)take(sizeof(int) * (size_t)n);
     c.colat = (int*)take(sizeof(int) * (size_t)n);
@@ -131,32 +141,6 @@ __host__ __device__ inline Carve carve(unsigned char* base, int m, int n, int nl
     c.xkeepJ = (int*)take(sizeof(int) * (size_t)(nXJ > 0 ? nXJ : 1));
     c.bytes = o;
     return c;
-}
-
-// Does any row of `tab` (cnt rows of `len` ints) equal `row`?  One warp; returns the same value in every lane.
-__device__ __forceinline__ bool warp_contains(const int* __restrict__ tab, int cnt, int len, const int* __restrict__ row, int lane) {
-    bool found = false;
-    for (int r0 = 0; r0 < cnt && !found; r0 += 32) {
-        const int r = r0 + lane;
-        bool eq = r < cnt;
-        if (eq) { const int* t = tab + (size_t)r * len; for (int p = 0; p < len; ++p) if (t[p] != row[p]) { eq = false; break; } }
-        found = __any_sync(FULL, eq);
-    }
-    return found;
-}
-
-// Stable compaction of the extras that are not already in the kronecker part: keep[e] = original index of the e-th kept
-// extra.  Warp 0 only; returns the number kept (valid in warp 0's lanes).
-//   left side  (rows of length len = b0 + 1): extra is a duplicate iff its first b0 entries are a row of Iset[b0]
-//   right side (rows of length len = N - b0 - 1): duplicate iff its last len - 1 entries are a row of Jset[b0 + 1]
-__device__ int keep_extras(const int* __restrict__ xt, int nx, int len, const int* __restrict__ base, int nbase, bool left, int* keep, int lane) {
-    int kept = 0;
-    for (int e = 0; e < nx; ++e) {
-        const int* row = xt + (size_t)e * len;
-        const bool dup = nbase > 0 && ((len - 1 == 0) ? true : warp_contains(base, nbase, len - 1, left ? row : row + 1, lane));
-        if (!dup) { if (lane == 0) keep[kept] = e; ++kept; }
-    }
-    return kept;
 }
 
 struct SweepParams {
@@ -169,128 +153,235 @@ struct SweepParams {
     int mcap;
     int smem_bytes;                          // dynamic shared memory available per CTA
     long long* prof;                         // diagnostics (TCI_DSWEEP_PROF=1): clock64 cycles thread 0 of CTA 0 spent per phase, else NULL
+    void* st_g;                              // functor state of every input table row (prologue), Rtot entries
+    unsigned long long* hs_g;                // hash of every input table row
 };
 
-#define TCI_DS_CONSIDER(v, ii, jj)                                                                          \
-    {                                                                                                   \
-            const double q__ = __dmul_rn((v), (v));                                                         \
-            if (q__ == q__) {                                                                               \
-                const unsigned long long k__ = (unsigned long long)__double_as_longlong(q__) + 1ull;        \
-                if (k__ > best.key) { best.key = k__; best.x = (v); best.i = (ii); best.j = (jj); }         \
-                else if (k__ == best.key) {                                                                 \
-                    const unsigned p1__ = ((unsigned)c.colpos[(jj)] << 16) | (unsigned)c.rowpos[(ii)];      \
-                    const unsigned p0__ = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];  \
-                    if (p1__ < p0__) { best.x = (v); best.i = (ii); best.j = (jj); }                        \
-                }                                                                                           \
-            }                                                                                               \
-        }
+// ---- own elements of the matrix --------------------------------------------------------------------------------------------
+// Columns j with j % CS == crank live in this CTA (local index jl = j / CS).  Small blocks (at most kFlat elements per thread)
+// use a FLAT element -> thread map held in registers for the whole factorisation: perfectly balanced, no padding.  Larger
+// blocks deal (column, group of 128 rows) pairs round-robin to the warps: lane l of the warp handles rows g*128 + l + 32 u,
+// u < 4, of its pair — four independent elements in flight per thread, rows padded to a multiple of 128 (rowpos = -1 there).
+struct Own {
+    int m, nown, crank, flat, nslots, ngroups;   // nown = own columns; nslots = used flat slots; ngroups = mp / 128
+    int e[kFlat];                                // flat: i | jl << 16, or -1
+};
 
-// The loop of _optimizerrlu! (matrixlu.jl:356-369) on the matrix in shared memory (columns j with j % CS == crank live in this
-// CTA, column-major, leading dimension c.lds).  `best` holds this thread's candidate of the FIRST search (fused into the
-// fill by the caller).  Nothing moves: c.rowat / c.colat (position -> physical index) and c.rowpos / c.colpos simulate the
-// reference's swaps; on return the first r entries of rowat / colat are the pivots in order, c.piv their values, and every
-// L / U entry sits where it was computed:  L(p, t) = A[rowat[p], colat[t]] (/ piv[t] below the diagonal when leftorthogonal),
-// U(t, q) = A[rowat[t], colat[q]] (/ piv[t] right of the diagonal otherwise).  `fwd` is leftorthogonal.
 template <int NT, int CS>
-__device__ __forceinline__ int smem_rrlu(const Carve& c, const int m, const int n, const int rcap, const int fwd, const double reltol,
-                                         const double abstol, Win best, Win (*s_w)[32], Win (*s_cl)[kMaxCS], const SweepParams& P,
-                                         const int crank, double* error_out, long long* pc = nullptr) {
+__device__ __forceinline__ Own own_elements(const Carve& c, int m, int n, int nloc, int crank) {
+    Own o;
+    o.m = m; o.crank = crank;
+    o.nown = n > crank ? (n - crank + CS - 1) / CS : 0;
+    const long long tot = (long long)m * o.nown;
+    o.flat = use_flat<NT>(m, nloc);
+    o.nslots = o.flat ? (int)((tot + NT - 1) / NT) : 0;
+    o.ngroups = c.mp / 128;
+#pragma unroll
+    for (int q = 0; q < kFlat; ++q) {
+        const long long idx = (long long)threadIdx.x + (long long)NT * q;
+        o.e[q] = (o.flat && idx < tot) ? (int)(idx % m) | ((int)(idx / m) << 16) : -1;
+    }
+    return o;
+}
+
+// body(i, jl, j) for every own element (used by the fill, where the functor dominates)
+template <int NT, int CS, class Body>
+__device__ __forceinline__ void foreach_own(const Own& o, Body body) {
+    if (o.flat) {
+#pragma unroll
+        for (int q = 0; q < kFlat; ++q) {
+            if (q < o.nslots && o.e[q] >= 0) { const int i = o.e[q] & 0xffff, jl = o.e[q] >> 16; body(i, jl, o.crank + CS * jl); }
+        }
+    } else {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const int npairs = o.nown * o.ngroups;
+        for (int pr = warp; pr < npairs; pr += NT / 32) {
+            const int jl = pr / o.ngroups, g = pr - jl * o.ngroups, j = o.crank + CS * jl;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { const int i = g * 128 + lane + 32 * u; if (i < o.m) body(i, jl, j); }
+        }
+    }
+}
+
+__device__ __forceinline__ long long abs2_key(double v) {                        // bits(v * v); negative for NaN
+    return __double_as_longlong(fmax(__dmul_rn(v, v), -1.0));                    // fmax(NaN, x) = x
+}
+
+// keep (bk, bi, bj) = the first element in the reference's scan order among those seen: larger key, then smaller position
+#define TCI_DS_TAKE(k, i, j, bk, bi, bj)                                                                                 \
+    if ((k) > (bk)) { (bk) = (k); (bi) = (i); (bj) = (j); }                                                             \
+    else if ((k) == (bk) && (k) >= 0) {                                                                                  \
+        const unsigned p1__ = ((unsigned)c.colpos[(j)] << 16) | (unsigned)c.rowpos[(i)];                                 \
+        const unsigned p0__ = ((unsigned)c.colpos[(bj)] << 16) | (unsigned)c.rowpos[(bi)];                               \
+        if (p1__ < p0__) { (bi) = (i); (bj) = (j); }                                                                     \
+    }
+
+struct KP { long long key; unsigned pos; unsigned pad; };
+
+// The loop of _optimizerrlu! (matrixlu.jl:356-369) on the matrix in shared memory.  (bkey, bi, bj) holds this thread's candidate
+// of the FIRST search (fused into the fill by the caller).  Nothing moves: c.rowat / c.colat (position -> physical index) and
+// c.rowpos / c.colpos simulate the reference's swaps; on return the first r entries of rowat / colat are the pivots in order,
+// c.piv their values, and every L / U entry sits where it was computed:  L(p, t) = A[rowat[p], colat[t]] (/ piv[t] below the
+// diagonal when leftorthogonal), U(t, q) = A[rowat[t], colat[q]] (/ piv[t] right of the diagonal otherwise).  `fwd` is
+// leftorthogonal.  Per pivot: [update + search] -> warp argmax -> partials -> barrier 1 -> every warp reduces the partials
+// (-> cluster: records + speculative scaled columns, ONE cluster barrier) -> stop rule -> stage pivot column / row, one thread
+// swaps the position maps -> barrier 2.
+template <int NT, int CS>
+__device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const int m, const int n, const int rcap, const int fwd,
+                                         const double reltol, const double abstol, long long bkey, int bi, int bj, KP (*s_w)[32],
+                                         Win (*s_cl)[kMaxCS], const SweepParams& P, const int crank, double* error_out,
+                                         long long* pc = nullptr) {
     constexpr int NW = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double* A = c.A;
     const int lds = c.lds;
-        int np = 0;
-        double maxerror = 0.0, error = nan("");
-        unsigned rmask = 0xffffffffu;                  // bit q: row lane + 32 q is still in the trailing block
-        long long tc0 = clock64();
+    int np = 0;
+    double maxerror = 0.0, error = nan("");
+    long long tc0 = clock64();
 #define TCI_DS_TICK(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tc0; tc0 = t1__; } }
-        for (;;) {
-            if (best.i >= 0) best.pos = ((unsigned)c.colpos[best.j] << 16) | (unsigned)c.rowpos[best.i];
-            else { best.key = 0; best.pos = 0xffffffffu; }
-            warp_argmax(best);
-            Win* sw = s_w[np & 1];
-            if (lane == 0) sw[warp] = best;
-            __syncthreads();                                                        // barrier 1
-            Win g = (lane < NW) ? sw[lane] : Win{0ull, 0.0, 0xffffffffu, -1, -1, 0};
-            warp_argmax(g);                                                         // every warp: the CTA's winner
-            TCI_DS_TICK(0)
-            double piv_own = g.x;
-            if constexpr (CS > 1) {
-                // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
-                cg::cluster_group cl = cg::this_cluster();
-                const int par = np & 1;
-                if (tid < CS) { Win* dst = cl.map_shared_rank(&s_cl[par][crank], tid); *dst = g; }
-                if (g.key != 0) {
-                    double* slot = P.xs_g + ((size_t)par * CS + crank) * P.mcap;
-                    const double* col = A + (size_t)(g.j / CS) * lds;
-                    const bool lo = fwd != 0;
-                    for (int i = tid; i < m; i += NT) slot[i] = lo ? col[i] / piv_own : col[i];
-                }
-                cl.sync();                                                          // the one cluster barrier of the step
-                Win w = s_cl[par][0];
-                int owner = 0;
-                for (int cc = 1; cc < CS; ++cc) { const Win o = s_cl[par][cc]; if (win_before(o, w)) { w = o; owner = cc; } }
-                g = w; g.pad = owner;
+    for (;;) {
+        unsigned bpos = bkey >= 0 ? ((unsigned)c.colpos[bj] << 16) | (unsigned)c.rowpos[bi] : 0xffffffffu;
+        warp_argmax(bkey, bpos);
+        KP* sw = s_w[np & 1];
+        if (lane == 0) { sw[warp].key = bkey; sw[warp].pos = bpos; }
+        __syncthreads();                                                            // barrier 1
+        long long gkey = lane < NW ? sw[lane].key : kNoKey;
+        unsigned gpos = lane < NW ? sw[lane].pos : 0xffffffffu;
+        warp_argmax(gkey, gpos);                                                    // every warp: the CTA's winner
+        TCI_DS_TICK(0)
+        int pi = -1, pj = -1, owner = crank;
+        double piv = nan("");
+        if (gkey >= 0) { pi = c.rowat[gpos & 0xffffu]; pj = c.colat[gpos >> 16]; piv = A[(size_t)(pj / CS) * lds + pi]; }
+        if constexpr (CS > 1) {
+            // publish this CTA's candidate record to every peer and its candidate's scaled column to the scratch slot
+            cg::cluster_group cl = cg::this_cluster();
+            const int par = np & 1;
+            if (tid < CS) {
+                Win w; w.key = gkey; w.x = piv; w.pos = gpos; w.owner = crank; w.pad0 = 0; w.pad1 = 0;
+                *cl.map_shared_rank(&s_cl[par][crank], tid) = w;
             }
-            TCI_DS_TICK(1)
-            int pi, pj; double piv;
-            if (g.key == 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }   // all-NaN block: the reference keeps (k, k)
-            else { pi = g.i; pj = g.j; piv = g.x; }
-            const double err = fabs(piv);                                           // :360
-            error = err;
-            if ((err < reltol * maxerror || err < abstol) && np > 0) break;     // :363
-            maxerror = jl_max(maxerror, err);                                       // :367
-            const int k = np;
-            // stage the pivot column: x[i] = A[i, pj] / pivot (leftorthogonal, :303-305) or A[i, pj]
-            if constexpr (CS > 1) {
-                if (g.key != 0) {
-                    const double* slot = P.xs_g + ((size_t)(np & 1) * CS + g.pad) * P.mcap;
-                    for (int i = tid; i < m; i += NT) c.xs[i] = __ldcg(slot + i);
-                } else if (pj % CS == crank) {
-                    // NaN pivot picked by position: only its owner has the column; everything it touches becomes NaN anyway
-                    const double* col = A + (size_t)(pj / CS) * lds;
-                    for (int i = tid; i < m; i += NT) c.xs[i] = nan("");
-                    (void)col;
-                } else { for (int i = tid; i < m; i += NT) c.xs[i] = nan(""); }
-            } else {
-                const double* col = A + (size_t)pj * lds;
-                if (fwd) { for (int i = tid; i < m; i += NT) c.xs[i] = col[i] / piv; }
-                else     { for (int i = tid; i < m; i += NT) c.xs[i] = col[i]; }
+            if (gkey >= 0) {
+                double* slot = P.xs_g + ((size_t)par * CS + crank) * P.mcap;
+                const double* col = A + (size_t)(pj / CS) * lds;
+                if (fwd) { for (int i = tid; i < m; i += NT) slot[i] = col[i] / piv; }
+                else     { for (int i = tid; i < m; i += NT) slot[i] = col[i]; }
             }
-            if (tid == 0) {                                                         // swaprow!/swapcol! on the position maps (:254-275)
-                const int rk = c.rowat[k], pp = c.rowpos[pi];
-                c.rowat[k] = pi; c.rowat[pp] = rk; c.rowpos[rk] = pp; c.rowpos[pi] = k;
-                const int ck = c.colat[k], qq = c.colpos[pj];
-                c.colat[k] = pj; c.colat[qq] = ck; c.colpos[ck] = qq; c.colpos[pj] = k;
-                c.piv[k] = piv;
+            TCI_DS_TICK(12)
+            cl.sync();                                                              // the one cluster barrier of the step
+            TCI_DS_TICK(13)
+            gkey = s_cl[par][0].key; gpos = s_cl[par][0].pos; owner = 0;
+#pragma unroll
+            for (int cc = 1; cc < CS; ++cc) {
+                const long long ok = s_cl[par][cc].key; const unsigned op = s_cl[par][cc].pos;
+                if (ok > gkey || (ok == gkey && op < gpos)) { gkey = ok; gpos = op; owner = cc; }
             }
-            if ((pi & 31) == lane) rmask &= ~(1u << (pi >> 5));
-            __syncthreads();                                                        // barrier 2
-            TCI_DS_TICK(2)
-            np = k + 1;
-            if (np >= rcap) break;                                                  // :356
-            best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1;
-            for (int j = crank + CS * warp; j < n; j += CS * NW) {                  // :316-320 + the next search
-                if (c.colpos[j] < np) continue;
-                double* col = A + (size_t)(j / CS) * lds;
-                double y = col[pi];
-                if (!fwd) y = y / piv;                                              // :307-309
-                unsigned rm = rmask;
-                for (int i = lane; i < m; i += 32, rm >>= 1) {
-                    if (!(rm & 1u)) continue;
-                    const double v = __dsub_rn(col[i], __dmul_rn(c.xs[i], y));
-                    col[i] = v;
-                    TCI_DS_CONSIDER(v, i, j)
-                }
-            }
-            TCI_DS_TICK(3)
+            piv = s_cl[par][owner].x;
+            if (gkey >= 0) { pi = c.rowat[gpos & 0xffffu]; pj = c.colat[gpos >> 16]; }
         }
-        const int r = np;
-        if (r >= (m < n ? m : n)) error = 0.0;                                       // :391-393
-        __syncthreads();
-        *error_out = error;
-        return r;
-
+        TCI_DS_TICK(1)
+        if (gkey < 0) { pi = c.rowat[np]; pj = c.colat[np]; piv = nan(""); }        // all-NaN block: the reference keeps (k, k)
+        const double err = fabs(piv);                                               // :360
+        error = err;
+        if ((err < reltol * maxerror || err < abstol) && np > 0) break;             // :363
+        maxerror = jl_max(maxerror, err);                                           // :367
+        const int k = np;
+        // stage the pivot column x[i] = A[i, pj] (/ pivot when leftorthogonal, :303-305) and the pivot row y[jl] = A[pi, j]
+        // (/ pivot otherwise, :307-309) of the own columns
+        if constexpr (CS > 1) {
+            if (gkey >= 0) {
+                const double* slot = P.xs_g + ((size_t)(np & 1) * CS + owner) * P.mcap;
+                for (int i = tid; i < m; i += NT) c.xs[i] = __ldcg(slot + i);
+            } else { for (int i = tid; i < m; i += NT) c.xs[i] = nan(""); }
+        } else {
+            const double* col = A + (size_t)pj * lds;
+            if (fwd) { for (int i = tid; i < m; i += NT) c.xs[i] = col[i] / piv; }
+            else     { for (int i = tid; i < m; i += NT) c.xs[i] = col[i]; }
+        }
+        for (int jl = NT - 1 - tid; jl < own.nown; jl += NT) {                      // (from the last threads: the first ones do x)
+            const double y = A[(size_t)jl * lds + pi];
+            c.ys[jl] = fwd ? y : y / piv;
+        }
+        if (tid == NT - 32) {                                                       // swaprow!/swapcol! on the position maps (:254-275)
+            const int rk = c.rowat[k], pp = c.rowpos[pi];
+            c.rowat[k] = pi; c.rowat[pp] = rk; c.rowpos[rk] = pp; c.rowpos[pi] = k;
+            const int ck = c.colat[k], qq = c.colpos[pj];
+            c.colat[k] = pj; c.colat[qq] = ck; c.colpos[ck] = qq; c.colpos[pj] = k;
+            c.piv[k] = piv;
+        }
+        __syncthreads();                                                            // barrier 2
+        TCI_DS_TICK(2)
+        np = k + 1;
+        if (np >= rcap) break;                                                      // :356
+        bkey = kNoKey; bi = 0; bj = 0;
+        // :316-320 + the next search: loads first, then arithmetic, then the candidate selection
+        if (own.flat) {
+#pragma unroll
+            for (int q0 = 0; q0 < kFlat; q0 += 2) {
+                if (q0 < own.nslots) {
+                    int rp[2], cp[2], ei[2], ej[2]; double av[2], xv[2], yv[2]; double* ap[2]; bool ok[2];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const int e = own.e[q0 + u];
+                        ok[u] = e >= 0;
+                        const int ee = ok[u] ? e : 0, jl = ee >> 16;
+                        ei[u] = ee & 0xffff; ej[u] = crank + CS * jl;
+                        ap[u] = A + (size_t)jl * lds + ei[u];
+                        rp[u] = c.rowpos[ei[u]]; cp[u] = c.colpos[ej[u]]; av[u] = *ap[u]; xv[u] = c.xs[ei[u]]; yv[u] = c.ys[jl];
+                    }
+                    long long kq[2];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const bool act = ok[u] && rp[u] >= np && cp[u] >= np;
+                        const double v = __dsub_rn(av[u], __dmul_rn(xv[u], yv[u]));
+                        if (act) *ap[u] = v;
+                        const long long k0 = abs2_key(v);
+                        kq[u] = act ? k0 : kNoKey;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) TCI_DS_TAKE(kq[u], ei[u], ej[u], bkey, bi, bj)
+                }
+            }
+        } else {
+            // warp w keeps row group g = w % ngroups for the whole pass and walks the columns w / ngroups, + NW / ngroups, ...:
+            // the pivot column entries and positions of its 4 x 32 rows are loaded once, not once per element
+            const int ng = own.ngroups, wpg = NW / ng;                              // warps per row group (the last NW % ng warps idle)
+            const int g = warp % ng, jl0 = warp / ng;
+            if (jl0 < wpg) {
+                const int i0 = g * 128 + lane;
+                int rp[4]; double xv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) { rp[u] = c.rowpos[i0 + 32 * u]; xv[u] = c.xs[i0 + 32 * u]; }
+                if (__any_sync(FULL, rp[0] >= np || rp[1] >= np || rp[2] >= np || rp[3] >= np)) {
+                    for (int jl = jl0; jl < own.nown; jl += wpg) {
+                        const int j = crank + CS * jl;
+                        if (c.colpos[j] < np) continue;
+                        const double y = c.ys[jl];
+                        double* col = A + (size_t)jl * lds + i0;
+                        double av[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) av[u] = col[32 * u];
+                        long long kq[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const bool act = rp[u] >= np;                           // padding rows carry position -1
+                            const double v = __dsub_rn(av[u], __dmul_rn(xv[u], y));
+                            if (act) col[32 * u] = v;
+                            const long long k0 = abs2_key(v);
+                            kq[u] = act ? k0 : kNoKey;
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) TCI_DS_TAKE(kq[u], i0 + 32 * u, j, bkey, bi, bj)
+                    }
+                }
+            }
+        }
+        TCI_DS_TICK(3)
+    }
+    const int r = np;
+    if (r >= (m < n ? m : n)) error = 0.0;                                          // :391-393
+    __syncthreads();
+    *error_out = error;
+    return r;
 }
 
 // "lu.L contains NaNs" / "lu.U contains NaNs" (matrixlu.jl:376-381): bit 0 / bit 1 of *s_flags (shared, zeroed by the caller).
@@ -300,40 +391,66 @@ __device__ __forceinline__ void lu_nan_flags(const Carve& c, const int m, const 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const double* A = c.A;
     const int lds = c.lds;
-        {
-            int flags = 0;
-            for (int t = warp; t < r; t += NW) {
-                const int ct = c.colat[t], rt = c.rowat[t];
-                const double pv = c.piv[t];
-                if (ct % CS == crank) {
-                    const double* col = A + (size_t)(ct / CS) * lds;
-                    for (int i = lane; i < m; i += 32) {
-                        const int p = c.rowpos[i];
-                        if (p < t) continue;
-                        const double v = (fwd && p > t) ? col[i] / pv : col[i];
-                        if (v != v) flags |= 1;
-                    }
-                }
-                for (int j = crank + CS * lane; j < n; j += CS * 32) {
-                    const int q = c.colpos[j];
-                    if (q < t) continue;
-                    const double a = A[(size_t)(j / CS) * lds + rt];
-                    const double v = (!fwd && q > t) ? a / pv : a;
-                    if (v != v) flags |= 2;
-                }
-            }
-            if (flags) atomicOr(s_flags, flags);
-            __syncthreads();
-            if constexpr (CS > 1) {
-                cg::cluster_group cl = cg::this_cluster();
-                if (tid == 0 && *s_flags && crank != 0) atomicOr(cl.map_shared_rank(s_flags, 0), *s_flags);
-                cl.sync();
-                const int fl = *cl.map_shared_rank(s_flags, 0);
-                cl.sync();
-                if (tid == 0) *s_flags = fl;
-                __syncthreads();
+    int flags = 0;
+    for (int t = warp; t < r; t += NW) {
+        const int ct = c.colat[t], rt = c.rowat[t];
+        const double pv = c.piv[t];
+        if (ct % CS == crank) {
+            const double* col = A + (size_t)(ct / CS) * lds;
+            for (int i = lane; i < m; i += 32) {
+                const int p = c.rowpos[i];
+                if (p < t) continue;
+                const double v = (fwd && p > t) ? col[i] / pv : col[i];
+                if (v != v) flags |= 1;
             }
         }
+        for (int j = crank + CS * lane; j < n; j += CS * 32) {
+            const int q = c.colpos[j];
+            if (q < t) continue;
+            const double a = A[(size_t)(j / CS) * lds + rt];
+            const double v = (!fwd && q > t) ? a / pv : a;
+            if (v != v) flags |= 2;
+        }
+    }
+    if (flags) atomicOr(s_flags, flags);
+    __syncthreads();
+    if constexpr (CS > 1) {
+        cg::cluster_group cl = cg::this_cluster();
+        if (tid == 0 && *s_flags && crank != 0) atomicOr(cl.map_shared_rank(s_flags, 0), *s_flags);
+        cl.sync();
+        const int fl = *cl.map_shared_rank(s_flags, 0);
+        cl.sync();
+        if (tid == 0) *s_flags = fl;
+        __syncthreads();
+    }
+}
+
+// ---- prologue: functor state and hash of every input table row ---------------------------------------------------------------
+// Table (site b, w): w = 0 Iset[b] (sites 0 .. b-1), 1 Jset[b] (sites b+1 .. N-1), 2 / 3 the history entries of the same
+// shapes.  desc[kDesc b + 8 + w] is the index of the table's first row in the scratch arrays.
+template <class F, int NT, int CS>
+__device__ __forceinline__ void fold_all_rows(const F& f, const int* in, const SweepParams& P, int crank) {
+    typedef typename F::State S;
+    const int N = in[0], rtot = in[6];
+    const int* desc = in + kHdr + N;
+    S* st = reinterpret_cast<S*>(P.st_g);
+    for (int g = crank * NT + threadIdx.x; g < rtot; g += NT * CS) {
+        int lo = 0, hi = 4 * N - 1;                        // last table whose base <= g
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (desc[kDesc * (mid >> 2) + 8 + (mid & 3)] <= g) lo = mid; else hi = mid - 1;
+        }
+        const int b = lo >> 2, w = lo & 3;
+        const int r = g - desc[kDesc * b + 8 + w];
+        const bool left = (w & 1) == 0;
+        const int len = left ? b : N - b - 1, site0 = left ? 0 : b + 1;
+        const int* row = in + desc[kDesc * b + 2 * w + 1] + (size_t)r * len;
+        S s = f.zero();
+        unsigned long long hh = 0;
+        for (int p = 0; p < len; ++p) { const int v = row[p]; f.push(s, site0 + p, v); hh += mixh(site0 + p, v); }
+        st[g] = s;
+        P.hs_g[g] = hh;
+    }
 }
 
 // One half-sweep.  All CTAs of the cluster run the same control flow on the same inputs (index bookkeeping is replicated,
@@ -343,12 +460,12 @@ __global__ void __launch_bounds__(NT, 1)
 dsweep_halfsweep_kernel(F f, SweepParams P) {
     typedef typename F::State S;
     extern __shared__ __align__(16) unsigned char dyn[];
-    __shared__ Win s_w[2][32];
+    __shared__ KP s_w[2][32];
     __shared__ Win s_cl[2][kMaxCS];
     __shared__ __align__(16) unsigned char s_carry_raw[kRMax * sizeof(S)];
+    __shared__ unsigned long long s_carryh[kRMax];
     __shared__ int s_keepI, s_keepJ, s_flags;
     S* carry = reinterpret_cast<S*>(s_carry_raw);
-    constexpr int NW = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int crank = 0;
     if constexpr (CS > 1) crank = (int)cg::this_cluster().block_rank();
@@ -361,15 +478,23 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
     int* out = P.out;
     long long used = kHdr + (long long)kStepRec * (s1 - s0);
     if (writer && tid == 0) { out[0] = 0; out[1] = s1; out[2] = (int)used; }
+    __shared__ long long pcnt[16];                       // diagnostics: thread 0 of CTA 0 only
+    long long* pc = (P.prof && writer && tid == 0) ? pcnt : nullptr;
+    if (pc) for (int q = 0; q < 16; ++q) pcnt[q] = 0;
+    long long tk0 = clock64();
+#define TCI_DS_PHASE(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tk0; tk0 = t1__; } }
+
+    fold_all_rows<F, NT, CS>(f, in, P, crank);
+    __threadfence();
+    cluster_or_block_sync<CS>();
+    TCI_DS_PHASE(9)
+    const S* stg = reinterpret_cast<const S*>(P.st_g);
+    const unsigned long long* hsg = P.hs_g;
 
     const int* mov = nullptr;                // the set that moves with the sweep (Iset[b0] forward, Jset[b0+1] backward) ...
     int nmov = -1;                           // ... -1: take it from the input arena (first step of the launch)
     double mx = 0.0; bool isn = false;       // running max |f| of this thread
 
-    long long pcnt[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    long long* pc = (P.prof && writer && tid == 0) ? pcnt : nullptr;
-    long long tk0 = clock64();
-#define TCI_DS_PHASE(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tk0; tk0 = t1__; } }
     for (int s = s0; s < s1; ++s) {
         const int b0 = fwd ? s : N - 2 - s;
         const int dL = ld[b0], dR = ld[b0 + 1];
@@ -379,29 +504,69 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         const int* tabI = in + dI[1]; int nI = dI[0];
         const int* tabJ = in + dJ[3]; int nJ = dJ[2];
         const bool carried = nmov >= 0;
-        if (carried) { if (fwd) { tabI = mov; nI = nmov; } else { tabJ = mov; nJ = nmov; } }
+        const bool movI = carried && fwd, movJ = carried && !fwd;
+        if (movI) { tabI = mov; nI = nmov; }
+        if (movJ) { tabJ = mov; nJ = nmov; }
+        const S* stI = stg + dI[8]; const unsigned long long* hI = hsg + dI[8];
+        const S* stJ = stg + dJ[9]; const unsigned long long* hJ = hsg + dJ[9];
         // extras: extraIset = history Iset[b0 + 1] (rows of length b0 + 1), extraJset = history Jset[b0] (length N - b0 - 1)
         const int* dXI = desc + kDesc * (b0 + 1);
         const int* dXJ = desc + kDesc * b0;
         const int nXI = useextra ? dXI[4] : 0, nXJ = useextra ? dXJ[6] : 0;
         const int* tabXI = in + dXI[5];
         const int* tabXJ = in + dXJ[7];
+        const S* stXI = stg + dXI[10]; const unsigned long long* hXI = hsg + dXI[10];
+        const S* stXJ = stg + dXJ[11]; const unsigned long long* hXJ = hsg + dXJ[11];
         const int lenXI = b0 + 1, lenXJ = N - b0 - 1;
 
-        // ---- which extras survive the union (tensorci2.jl:842-843); needs a provisional place for the keep lists: the
-        //      start of the dynamic buffer (re-carved below, after the counts are known)
-        int* keepI0 = reinterpret_cast<int*>(dyn);
+        // ---- which extras survive the union (tensorci2.jl:842-843): an extra is a duplicate iff its first b0 entries are a row
+        //      of Iset[b0] (the kronecker part holds every digit) / its last entries a row of Jset[b0+1].  Hash match, then an
+        //      exact compare; the kept ones in order (first-seen union).  Provisional lists at the start of the dynamic buffer.
+        int* flg = reinterpret_cast<int*>(dyn);                                     // [nXI + nXJ] 1 = keep
+        int* keepI0 = flg + nXI + nXJ;
         int* keepJ0 = keepI0 + (nXI > 0 ? nXI : 1);
-        if ((size_t)(nXI + nXJ + 2) * sizeof(int) > (size_t)P.smem_bytes) {         // cannot even hold the lists
+        if ((size_t)(2 * (nXI + nXJ) + 4) * sizeof(int) > (size_t)P.smem_bytes) {
             if (writer && tid == 0) { out[0] = 1; out[1] = s; }
             break;
         }
-        if (warp == 0) {
-            const int k = keep_extras(tabXI, nXI, lenXI, tabI, nI, true, keepI0, lane);
-            if (lane == 0) s_keepI = k;
-        } else if (warp == 1) {
-            const int k = keep_extras(tabXJ, nXJ, lenXJ, tabJ, nJ, false, keepJ0, lane);
-            if (lane == 0) s_keepJ = k;
+        for (int t = tid; t < nXI + nXJ; t += NT) {
+            const bool left = t < nXI;
+            const int e = left ? t : t - nXI;
+            const int* row = left ? tabXI + (size_t)e * lenXI : tabXJ + (size_t)e * lenXJ;
+            const int nb = left ? nI : nJ, blen = left ? lenI : lenJ;
+            const int* btab = left ? tabI : tabJ;
+            const unsigned long long hp = left ? hXI[e] - mixh(b0, row[lenXI - 1]) : hXJ[e] - mixh(b0 + 1, row[0]);
+            const int* sub = left ? row : row + 1;
+            const bool bm = left ? movI : movJ;
+            const unsigned long long* hb = left ? hI : hJ;
+            int cand = -1;                                                          // first base row with the same hash
+            for (int r = nb - 1; r >= 0; --r) { const unsigned long long hr = bm ? s_carryh[r] : hb[r]; cand = hr == hp ? r : cand; }
+            bool dup = false;
+            while (cand >= 0) {                                                     // (a second candidate needs a 64-bit hash collision)
+                const int* br = btab + (size_t)cand * blen;
+                int diff = 0;
+                for (int p = 0; p < blen; ++p) diff |= br[p] ^ sub[p];              // no early exit: the loads are independent
+                if (diff == 0) { dup = true; break; }
+                int nxt = -1;
+                for (int r = nb - 1; r > cand; --r) { const unsigned long long hr = bm ? s_carryh[r] : hb[r]; nxt = hr == hp ? r : nxt; }
+                cand = nxt;
+            }
+            flg[t] = dup ? 0 : 1;
+        }
+        __syncthreads();
+        if (warp < 2) {                                                             // stable compaction: warp 0 left, warp 1 right
+            const int cnt = warp == 0 ? nXI : nXJ;
+            const int* fl = warp == 0 ? flg : flg + nXI;
+            int* keep = warp == 0 ? keepI0 : keepJ0;
+            int kept = 0;
+            for (int e0 = 0; e0 < cnt; e0 += 32) {
+                const int e = e0 + lane;
+                const bool kp = e < cnt && fl[e] != 0;
+                const unsigned bal = __ballot_sync(FULL, kp);
+                if (kp) keep[kept + __popc(bal & ((1u << lane) - 1u))] = e;
+                kept += __popc(bal);
+            }
+            if (lane == 0) { if (warp == 0) s_keepI = kept; else s_keepJ = kept; }
         }
         __syncthreads();
         TCI_DS_PHASE(4)
@@ -415,7 +580,7 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         int myKeepI = -1, myKeepJ = -1;
         if (tid < nKI) myKeepI = keepI0[tid];
         if (tid < nKJ) myKeepJ = keepJ0[tid];
-        const Carve c = carve<S>(dyn, m, n, nloc, rcap, nXI, nXJ);
+        const Carve c = carve<S>(dyn, m, n, nloc, rcap, nXI, nXJ, use_flat<NT>(m, nloc));
         const long long need_out = used + (long long)rcap * (lenXI + lenXJ) + 2 * (rcap + 1) + 2;
         const bool fits = m >= 1 && n >= 1 && m <= 1024 && n <= 65535 && c.bytes <= (size_t)P.smem_bytes && rcap <= kRMax
                           && nKI <= NT && nKJ <= NT && need_out <= P.out_cap && (CS == 1 || m <= P.mcap);
@@ -435,35 +600,20 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
             if (t < m) {
                 const int i = t;
                 S st;
-                if (i < mk) {
-                    const int ir = i % nI, dig = i / nI + 1;
-                    if (carried && fwd) st = carry[ir];
-                    else { st = f.zero(); const int* row = tabI + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, row[p]); }
-                    f.push(st, b0, dig);
-                } else {
-                    st = f.zero();
-                    const int* row = tabXI + (size_t)c.xkeepI[i - mk] * lenXI;
-                    for (int p = 0; p < lenXI; ++p) f.push(st, p, row[p]);
-                }
+                if (i < mk) { const int ir = i % nI; st = movI ? carry[ir] : stI[ir]; f.push(st, b0, i / nI + 1); }
+                else st = stXI[c.xkeepI[i - mk]];
                 Lst[i] = st;
                 c.rowpos[i] = i; c.rowat[i] = i;
             } else {
                 const int j = t - m;
                 S st;
-                if (j < nk) {
-                    const int dig = j % dR + 1, jr = j / dR;
-                    if (carried && !fwd) st = carry[jr];
-                    else { st = f.zero(); const int* row = tabJ + (size_t)jr * lenJ; for (int p = 0; p < lenJ; ++p) f.push(st, b0 + 2 + p, row[p]); }
-                    f.push(st, b0 + 1, dig);
-                } else {
-                    st = f.zero();
-                    const int* row = tabXJ + (size_t)c.xkeepJ[j - nk] * lenXJ;
-                    for (int p = 0; p < lenXJ; ++p) f.push(st, b0 + 1 + p, row[p]);
-                }
+                if (j < nk) { const int jr = j / dR; st = movJ ? carry[jr] : stJ[jr]; f.push(st, b0 + 1, j % dR + 1); }
+                else st = stXJ[c.xkeepJ[j - nk]];
                 Rst[j] = st;
                 c.colpos[j] = j; c.colat[j] = j;
             }
         }
+        for (int t = m + tid; t < c.mp; t += NT) { c.rowpos[t] = -1; c.xs[t] = 0.0; }           // padding rows: never active
         if (tid == 0) s_flags = 0;
         __syncthreads();
         TCI_DS_PHASE(5)
@@ -471,22 +621,19 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         // ---- Pi (own columns) + the first pivot search (positions are the identity)
         double* A = c.A;
         const int lds = c.lds;
-        Win best; best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1; best.pad = 0;
-        for (int j = crank + CS * warp; j < n; j += CS * NW) {
-            const S rj = Rst[j];
-            double* col = A + (size_t)(j / CS) * lds;
-            for (int i = lane; i < m; i += 32) {
-                const double v = f.finish(f.merge(Lst[i], rj));
-                col[i] = v;
-                const double a = fabs(v);
-                if (a != a) isn = true; else mx = a > mx ? a : mx;
-                TCI_DS_CONSIDER(v, i, j)
-            }
-        }
-
+        const Own own = own_elements<NT, CS>(c, m, n, nloc, crank);
+        long long bkey = kNoKey; int bi = 0, bj = 0;
+        foreach_own<NT, CS>(own, [&](int i, int jl, int j) {
+            const double v = f.finish(f.merge(Lst[i], Rst[j]));
+            A[(size_t)jl * lds + i] = v;
+            const double a = fabs(v);
+            if (a != a) isn = true; else mx = a > mx ? a : mx;
+            const long long kq = abs2_key(v);
+            TCI_DS_TAKE(kq, i, j, bkey, bi, bj)
+        });
         TCI_DS_PHASE(6)
         double error;
-        const int r = smem_rrlu<NT, CS>(c, m, n, rcap, fwd, P.reltol, P.abstol, best, s_w, s_cl, P, crank, &error, pc);
+        const int r = smem_rrlu<NT, CS>(c, own, m, n, rcap, fwd, P.reltol, P.abstol, bkey, bi, bj, s_w, s_cl, P, crank, &error, pc);
         if (pc) { tk0 = clock64(); pc[10] += r; pc[11] += 1; }
         lu_nan_flags<NT, CS>(c, m, n, r, fwd, crank, &s_flags);
         TCI_DS_PHASE(7)
@@ -523,16 +670,29 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
                 out[2] = (int)endw;
             }
         }
-        // carry the functor states of the chosen rows (forward) / columns (backward) to the next bond
+        // carry the functor states and hashes of the chosen rows (forward) / columns (backward) to the next bond
+        unsigned long long myh[ (kRMax + NT - 1) / NT ];
+#pragma unroll
+        for (int q = 0; q < (kRMax + NT - 1) / NT; ++q) {
+            const int t = tid + q * NT;
+            myh[q] = 0;
+            if (t < r) {
+                if (fwd) { const int i = c.rowat[t]; myh[q] = i < mk ? (movI ? s_carryh[i % nI] : hI[i % nI]) + mixh(b0, i / nI + 1) : hXI[c.xkeepI[i - mk]]; }
+                else { const int j = c.colat[t]; myh[q] = j < nk ? (movJ ? s_carryh[j / dR] : hJ[j / dR]) + mixh(b0 + 1, j % dR + 1) : hXJ[c.xkeepJ[j - nk]]; }
+            }
+        }
+        __syncthreads();                               // every read of the old carried hashes is done
+#pragma unroll
+        for (int q = 0; q < (kRMax + NT - 1) / NT; ++q) { const int t = tid + q * NT; if (t < r) s_carryh[t] = myh[q]; }
         for (int t = tid; t < r; t += NT) carry[t] = fwd ? Lst[c.rowat[t]] : Rst[c.colat[t]];
         used = endw;
         mov = fwd ? out + offA : out + offB;
         nmov = r;
         __threadfence();
-        cluster_or_block_sync<CS>();                   // the new rows (global) and `carry` are visible to every thread / CTA
+        cluster_or_block_sync<CS>();                   // the new rows (global) and the carried states are visible to every thread / CTA
         TCI_DS_PHASE(8)
     }
-    if (pc) for (int q = 0; q < 12; ++q) P.prof[q] = pcnt[q];
+    if (pc) for (int q = 0; q < 16; ++q) P.prof[q] = pcnt[q];
 
     // ---- updatemaxsample! (tensorci2.jl:636-638): one atomic per warp
     unsigned long long b = (unsigned long long)__double_as_longlong(mx);
@@ -541,7 +701,6 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
     const unsigned anyn = __ballot_sync(FULL, isn);
     if (lane == 0) { if (b) atomicMax(P.acc, b); if (anyn) atomicOr(reinterpret_cast<int*>(P.acc + 1), 1); }
 }
-
 
 // ---- fillsitetensors! (src/globalsearch.jl:202-208 -> setsitetensor! src/tensorci2.jl:599-629) for ALL sites in one launch ------
 // CTA = (site b, block of 128 rows of Pi1).  Site b < N-1:  T_b = Pi1 * inv(P),  Pi1 = f((Iset[b] x s_b) x Jset[b]),
@@ -656,19 +815,21 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
     typedef typename F::State S;
     const SweepParams& P = Q.sp;
     extern __shared__ __align__(16) unsigned char dyn[];
-    __shared__ Win s_w[2][32];
+    __shared__ KP s_w[2][32];
     __shared__ Win s_cl[2][kMaxCS];
     __shared__ __align__(16) unsigned char s_carry_raw[kRMax * sizeof(S)];
     __shared__ int s_flags;
     S* carry = reinterpret_cast<S*>(s_carry_raw);
-    constexpr int NW = NT / 32;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int* in = P.in;
     const int N = in[0], maxbond = in[4];
     const int* ld = in + kHdr; const int* desc = ld + N;
     int* out = P.out;
     long long used = kHdr + (long long)kStepRec * (N - 1);
     if (tid == 0) { out[0] = 0; out[1] = N - 1; out[2] = (int)used; }
+    fold_all_rows<F, NT, 1>(f, in, P, 0);
+    __syncthreads();
+    const S* stg = reinterpret_cast<const S*>(P.st_g);
     const int* mov = in + desc[1]; int nmov = desc[0];       // Iset[0]
     bool carried = false;
     double mx = 0.0; bool isn = false;
@@ -677,51 +838,47 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
         const int d = ld[b0];
         const int* tabI = mov; const int nI = nmov; const int lenI = b0;
         const int nJ = desc[kDesc * b0 + 2]; const int* tabJ = in + desc[kDesc * b0 + 3]; const int lenJ = N - b0 - 1;
+        const S* stI = stg + desc[kDesc * b0 + 8];           // only used while the input Iset[0] is current
+        const S* stJ = stg + desc[kDesc * b0 + 9];
         const int m = nI * d, n = nJ, mn = m < n ? m : n;
         const int rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
-        Carve c = carve<S>(dyn, m, n, n, rcap, 0, 0);
+        Carve c = carve<S>(dyn, m, n, n, rcap, 0, 0, use_flat<NT>(m, n));
         double* L1s = reinterpret_cast<double*>(dyn + c.bytes);                     // scaled unit-lower factor of the pivot block
         const size_t bytes = c.bytes + sizeof(double) * (size_t)rcap * rcap;
         const long long need_out = used + (long long)rcap * (lenI + 1 + lenJ) + 2 * (rcap + 1) + 2;
-        const bool fits = m >= 1 && n >= 1 && m <= 1024 && bytes <= (size_t)P.smem_bytes && rcap <= kRMax && need_out <= P.out_cap
-                          && (long long)m * rcap <= Q.corecap[b0];
+        const bool fits = m >= 1 && n >= 1 && m <= 1024 && n <= 65535 && bytes <= (size_t)P.smem_bytes && rcap <= kRMax
+                          && need_out <= P.out_cap && (long long)m * rcap <= Q.corecap[b0];
         if (!fits) { if (tid == 0) { out[0] = 1; out[1] = b0; } stopped = true; break; }
         S* Lst = reinterpret_cast<S*>(c.Lst);
         S* Rst = reinterpret_cast<S*>(c.Rst);
         __syncthreads();
         for (int t = tid; t < m + n; t += NT) {
             if (t < m) {
-                const int ir = t % nI, dig = t / nI + 1;
-                S st;
-                if (carried) st = carry[ir];
-                else { st = f.zero(); const int* row = tabI + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, row[p]); }
-                f.push(st, b0, dig);
+                const int ir = t % nI;
+                S st = carried ? carry[ir] : stI[ir];
+                f.push(st, b0, t / nI + 1);
                 Lst[t] = st; c.rowpos[t] = t; c.rowat[t] = t;
             } else {
                 const int j = t - m;
-                S st = f.zero();
-                const int* row = tabJ + (size_t)j * lenJ;
-                for (int p = 0; p < lenJ; ++p) f.push(st, b0 + 1 + p, row[p]);
-                Rst[j] = st; c.colpos[j] = j; c.colat[j] = j;
+                Rst[j] = stJ[j]; c.colpos[j] = j; c.colat[j] = j;
             }
         }
+        for (int t = m + tid; t < c.mp; t += NT) { c.rowpos[t] = -1; c.xs[t] = 0.0; }
         if (tid == 0) s_flags = 0;
         __syncthreads();
         double* A = c.A; const int lds = c.lds;
-        Win best; best.key = 0; best.x = 0.0; best.pos = 0xffffffffu; best.i = -1; best.j = -1; best.pad = 0;
-        for (int j = warp; j < n; j += NW) {
-            const S rj = Rst[j];
-            double* col = A + (size_t)j * lds;
-            for (int i = lane; i < m; i += 32) {
-                const double v = f.finish(f.merge(Lst[i], rj));
-                col[i] = v;
-                const double a = fabs(v);
-                if (a != a) isn = true; else mx = a > mx ? a : mx;
-                TCI_DS_CONSIDER(v, i, j)
-            }
-        }
+        const Own own = own_elements<NT, 1>(c, m, n, n, 0);
+        long long bkey = kNoKey; int bi = 0, bj = 0;
+        foreach_own<NT, 1>(own, [&](int i, int jl, int j) {
+            const double v = f.finish(f.merge(Lst[i], Rst[j]));
+            A[(size_t)jl * lds + i] = v;
+            const double a = fabs(v);
+            if (a != a) isn = true; else mx = a > mx ? a : mx;
+            const long long kq = abs2_key(v);
+            TCI_DS_TAKE(kq, i, j, bkey, bi, bj)
+        });
         double error;
-        const int r = smem_rrlu<NT, 1>(c, m, n, rcap, 1, P.reltol, P.abstol, best, s_w, s_cl, P, 0, &error);
+        const int r = smem_rrlu<NT, 1>(c, own, m, n, rcap, 1, P.reltol, P.abstol, bkey, bi, bj, s_w, s_cl, P, 0, &error);
         lu_nan_flags<NT, 1>(c, m, n, r, 1, 0, &s_flags);
         if (s_flags) { if (tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = b0; } stopped = true; break; }
         // ---- new index sets and pivot errors
@@ -773,19 +930,18 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
     }
     if (!stopped) {                                                                // last tensor by evaluation (:719-723)
         const int b0 = N - 1, d = ld[b0];
-        const int nI = nmov, lenI = b0;
+        const int nI = nmov;
         const int nJ = desc[kDesc * b0 + 2];
+        const S* stI = stg + desc[kDesc * b0 + 8];
         const long long q = (long long)nI * d;
         if (q * nJ > Q.corecap[b0]) { if (tid == 0) { out[0] = 1; out[1] = N - 1; } }
         else {
             double* T = Q.cores[b0];
             for (long long e = tid; e < q * nJ; e += NT) {
                 const int row = (int)(e % q);
-                const int ir = row % nI, dig = row / nI + 1;
-                S st;
-                if (carried) st = carry[ir];
-                else { st = f.zero(); const int* rw = mov + (size_t)ir * lenI; for (int p = 0; p < lenI; ++p) f.push(st, p, rw[p]); }
-                f.push(st, b0, dig);
+                const int ir = row % nI;
+                S st = carried ? carry[ir] : stI[ir];
+                f.push(st, b0, row / nI + 1);
                 const double v = f.finish(f.merge(st, f.zero()));
                 T[e] = v;
                 const double a = fabs(v);
@@ -843,16 +999,19 @@ int launch_halfsweep(tci_handle h, const F& f, const SweepParams& P, int dyn_byt
     return TCI_OK;
 }
 
-constexpr int kDynBytes = 214 * 1024;                    // + ~11 KB static (carried states, candidate records) <= 227 KB
+constexpr int kDynBytes = 208 * 1024;                    // + up to ~15 KB static (carried states and hashes, candidate records) <= 227 KB
 
 template <class F>
 int run_halfsweep(tci_handle h, const F& f, SweepParams P, const SweepShape& sh, int force_cs) {
     P.smem_bytes = kDynBytes;
-    const size_t one = sizeof(double) * (size_t)(sh.maxm | 1) * (size_t)sh.maxn + 40 * (size_t)(sh.maxm + sh.maxn) + 4096;
+    const size_t lds1 = (size_t)((sh.maxm + 31) / 32 * 32) | 1;                // padded column length, one spare column
+    const size_t one = sizeof(double) * lds1 * ((size_t)sh.maxn + 1) + 48 * (lds1 + 128 + (size_t)sh.maxn) + 4096;
     int cs = one <= (size_t)kDynBytes ? 1 : kMaxCS;
     if (force_cs == 1 || force_cs == kMaxCS) cs = force_cs;
     if (cs == 1) {
-        if (sh.maxelems <= 4096) return launch_halfsweep<F, 256, 1>(h, f, P, kDynBytes);
+        const char* ne = getenv("TCI_DSWEEP_NT");          // experiments: force the block size of the single-CTA variant
+        const int nt = ne ? atoi(ne) : (sh.maxelems <= 4096 ? 256 : 1024);
+        if (nt == 256) return launch_halfsweep<F, 256, 1>(h, f, P, kDynBytes);
         return launch_halfsweep<F, 1024, 1>(h, f, P, kDynBytes);
     }
     return launch_halfsweep<F, 1024, kMaxCS>(h, f, P, kDynBytes);
@@ -909,6 +1068,14 @@ int check_arena(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_wor
     const int N = h_in[0];
     if (N < 2 || N > 128 || in_words < kHdr + (int64_t)N * (1 + kDesc)) return tci_fail(h, TCI_ERR_INVALID, "%s: malformed input arena", who);
     if (f->kind == TCI_F_DENSE && f->ndims != N) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, N);
+    const int32_t* desc = h_in + kHdr + N;
+    int64_t rows = 0;
+    for (int b = 0; b < N; ++b)
+        for (int w = 0; w < 4; ++w) {
+            if (desc[kDesc * b + 8 + w] != rows) return tci_fail(h, TCI_ERR_INVALID, "%s: row bases of the input arena are inconsistent", who);
+            rows += desc[kDesc * b + 2 * w];
+        }
+    if (rows != h_in[6]) return tci_fail(h, TCI_ERR_INVALID, "%s: total row count of the input arena is inconsistent", who);
     return TCI_OK;
 }
 
@@ -957,26 +1124,25 @@ int tci_dsweep_supported(tci_handle h, tci_functor f) {
 int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, int64_t in_words, double reltol, double abstol,
                              void* d_acc16, int32_t* h_out, int64_t out_cap_words, int64_t* h_used_words) {
     if (!h) return TCI_ERR_INVALID;
-    if (!f || !h_in || !h_out || !d_acc16 || in_words < kHdr || out_cap_words < kHdr)
-        return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: bad arguments");
-    if (!tci_dsweep_supported(h, f)) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: needs a built-in device functor");
+    { int rc0 = check_arena(h, f, h_in, in_words, "tci_dsweep_halfsweep_f64"); if (rc0) return rc0; }
+    if (!h_out || !d_acc16 || out_cap_words < kHdr) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: bad arguments");
     const int N = h_in[0], s0 = h_in[2], s1 = h_in[3];
-    if (N < 2 || N > 128 || s0 < 0 || s1 > N - 1 || s0 > s1 || in_words < kHdr + (int64_t)N * (1 + kDesc))
-        return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: malformed input arena");
-    if (f->kind == TCI_F_DENSE && f->ndims != N) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, N);
+    if (s0 < 0 || s1 > N - 1 || s0 > s1) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: malformed input arena");
     if (out_cap_words < kHdr + (int64_t)kStepRec * (s1 - s0)) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: output arena too small");
     TCI_CUDA(h, cudaSetDevice(h->device));
     const SweepShape sh = predict(h_in);
     const int mcap = ((std::max(sh.maxm, 1) * 2 + 63) / 64) * 64;                  // room for the moving set to grow
     const size_t in_b = ((size_t)in_words * 4 + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
     const size_t xs_b = sizeof(double) * 2 * kMaxCS * (size_t)mcap;
-    int rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + xs_b + 512); if (rc) return rc;
+    const size_t rtot = (size_t)std::max(h_in[6], 0), st_b = (rtot * 16 + 255) & ~(size_t)255, hs_b = (rtot * 8 + 255) & ~(size_t)255;
+    int rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + xs_b + 512 + st_b + hs_b); if (rc) return rc;
     unsigned char* base = (unsigned char*)h->ws_c.ptr;
     SweepParams P;
     P.in = (const int*)base; P.out = (int*)(base + in_b); P.out_cap = out_cap_words; P.reltol = reltol; P.abstol = abstol;
     P.acc = (unsigned long long*)d_acc16; P.xs_g = (double*)(base + in_b + out_b); P.mcap = mcap; P.smem_bytes = 0;
     const bool prof = getenv("TCI_DSWEEP_PROF") != nullptr;
     P.prof = prof ? (long long*)(base + in_b + out_b + xs_b) : nullptr;
+    P.st_g = base + in_b + out_b + xs_b + 512; P.hs_g = (unsigned long long*)(base + in_b + out_b + xs_b + 512 + st_b);
     TCI_CUDA(h, cudaMemcpyAsync(base, h_in, (size_t)in_words * 4, cudaMemcpyHostToDevice, h->stream));
     const char* fe = getenv("TCI_DSWEEP_CLUSTER");         // tests: 1 / 8 force the single-CTA / cluster variant
     const int force_cs = fe ? atoi(fe) : 0;
@@ -993,11 +1159,12 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     if (rc) return rc;
     rc = read_out(h, P.out, h_out, out_cap_words, h_used_words, "tci_dsweep_halfsweep_f64");
     if (rc == TCI_OK && prof) {
-        long long pcs[12];
+        long long pcs[16];
         TCI_CUDA(h, cudaMemcpy(pcs, P.prof, sizeof pcs, cudaMemcpyDeviceToHost));
-        static const char* names[12] = {"lu.reduce", "lu.exchange", "lu.stage", "lu.update", "extras", "states", "fill", "lu+nan", "output", "-", "pivots", "bonds"};
+        static const char* names[16] = {"lu.reduce", "lu.exchange", "lu.stage", "lu.update", "extras", "states", "fill", "lu+nan", "output", "prologue",
+                                        "pivots", "bonds", "x.publish", "x.clustersync", "-", "-"};
         fprintf(stderr, "dsweep prof (cycles):");
-        for (int q = 0; q < 12; ++q) if (q != 9) fprintf(stderr, " %s=%lld", names[q], pcs[q]);
+        for (int q = 0; q < 14; ++q) fprintf(stderr, " %s=%lld", names[q], pcs[q]);
         fprintf(stderr, "\n");
     }
     return rc;
@@ -1068,12 +1235,14 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, 
     std::vector<long long> cap(h_core_capacity, h_core_capacity + N);
     const size_t off_k = st.add(cap.data(), sizeof(long long) * (size_t)N);
     const size_t in_b = (st.bytes.size() + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
-    rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + 256); if (rc) return rc;
+    const size_t rtot = (size_t)std::max(h_in[6], 0), st_b = (rtot * 16 + 255) & ~(size_t)255, hs_b = (rtot * 8 + 255) & ~(size_t)255;
+    rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + st_b + hs_b + 256); if (rc) return rc;
     unsigned char* base = (unsigned char*)h->ws_c.ptr;
     TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
     Sweep1Params Q;
     Q.sp.in = (const int*)base; Q.sp.out = (int*)(base + in_b); Q.sp.out_cap = out_cap_words; Q.sp.reltol = reltol; Q.sp.abstol = abstol;
     Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.prof = nullptr;
+    Q.sp.st_g = base + in_b + out_b; Q.sp.hs_g = (unsigned long long*)(base + in_b + out_b + st_b);
     Q.cores = (double* const*)(base + off_c); Q.corecap = (const long long*)(base + off_k);
     TCI_DS_DISPATCH(rc, f, launch_sweep1(h, F_, Q, maxelems))
     if (rc) return rc;

@@ -569,12 +569,12 @@ inline bool forwardsweep(int strategy, int iter) {      // sweepstrategies.jl:41
 // The bond loop of one half-sweep (tensorci2.jl:1226-1250) as ONE launch per stretch of bonds whose Pi fits shared memory:
 // the index sets (and the history entries used as extras) go down as one int32 arena, the new sets and pivot errors come
 // back as one arena.  A bond that does not fit is done by the per-bond path above and the sweep continues behind it.
-constexpr int kArenaHdr = 8, kArenaDesc = 8, kArenaStep = 6;
+constexpr int kArenaHdr = 8, kArenaDesc = 12, kArenaStep = 6;
 
-bool device_bond_fits(int64_t m, int64_t n) {             // mirror of the kernel's own check (8-CTA cluster, 214 KB each)
+bool device_bond_fits(int64_t m, int64_t n) {             // mirror of the kernel's own check (8-CTA cluster, 208 KB each)
     if (m < 1 || n < 1 || m > 1024 || n > 65535) return false;
-    const int64_t nloc = (n + 7) / 8;
-    return 8 * (m | 1) * nloc + 48 * (m + n) + 8192 <= 214 * 1024;
+    const int64_t nloc = (n + 7) / 8 + 1, lds = ((m + 31) / 32 * 32) | 1;        // padded column length, one spare column
+    return 8 * lds * nloc + 48 * (m + 128 + n) + 8192 <= 208 * 1024;
 }
 
 void append_table(std::vector<int32_t>& a, const IdxTable* t, int32_t* cnt_off) {
@@ -591,14 +591,18 @@ void pack_sets(tci_tci2 t, std::vector<int32_t>& a, bool fwd, int s0, int s1, in
     a[0] = N; a[1] = fwd ? 1 : 0; a[2] = s0; a[3] = s1;
     a[4] = (maxbonddim <= 0 || maxbonddim > 0x7fffffff) ? 0 : (int32_t)maxbonddim; a[5] = useextra ? 1 : 0;
     for (int b = 0; b < N; ++b) a[(size_t)kArenaHdr + b] = t->localdims[b];
+    int32_t rows = 0;
     for (int b = 0; b < N; ++b) {
-        int32_t d[8];
-        append_table(a, &t->I[b], d + 0);
-        append_table(a, &t->J[b], d + 2);
-        append_table(a, useextra ? &(*extraI)[b] : nullptr, d + 4);
-        append_table(a, useextra ? &(*extraJ)[b] : nullptr, d + 6);
+        int32_t d[12];
+        const IdxTable* tabs[4] = {&t->I[b], &t->J[b], useextra ? &(*extraI)[b] : nullptr, useextra ? &(*extraJ)[b] : nullptr};
+        for (int w = 0; w < 4; ++w) {
+            append_table(a, tabs[w], d + 2 * w);
+            d[8 + w] = rows;                              // index of the table's first row among all rows of the arena
+            rows += d[2 * w];
+        }
         std::memcpy(a.data() + kArenaHdr + N + (size_t)kArenaDesc * b, d, sizeof d);
     }
+    a[6] = rows;
 }
 
 int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t maxbonddim, const std::vector<IdxTable>* extraI,

@@ -793,8 +793,11 @@ def crossinterpolate2(f, localdims, initialpivots=None, **kwargs):
                                                             # splitmix64 streams (rook columns, global-pivot starts) for every engine;
                                                             # without it the Python engine's finder draws from an unseeded numpy RNG
     engine = kwargs.pop("engine", "auto")
-    if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module
-        engine = "native" if _native_eligible(f, kwargs) else "python"
+    if engine == "auto":                                    # the compiled driver whenever it covers the call, else this module;
+        engine = "python"                                   # with the bond loop on the device for the built-in functors
+        if _native_eligible(f, kwargs):
+            h = kwargs.get("handle") or f.handle
+            engine = "device" if (kwargs.get("pivotsearch", "full") == "full" and _lib.lib().tci_dsweep_supported(h.h, f._f)) else "native"
     if engine in ("native", "device"):
         return _crossinterpolate2_native(f, localdims, initialpivots, seed, kwargs.pop("handle", None), kwargs, device=engine == "device")
     if engine != "python":

@@ -200,14 +200,14 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* in, int
     MockAcc* a = (MockAcc*)acc;
     for (int s = s0; s < s1; ++s) {
         const int b0 = fwd ? s : N - 2 - s;
-        const int32_t* dI = desc + 8 * b0; const int32_t* dJ = desc + 8 * (b0 + 1);
+        const int32_t* dI = desc + 12 * b0; const int32_t* dJ = desc + 12 * (b0 + 1);
         Rows I = rows_of(dI[0], dI[1], b0), J = rows_of(dJ[2], dJ[3], N - b0 - 2);
         if (have_mov) { if (fwd) I = mov; else J = mov; }
         Rows Ic, Jc;
         for (int d = 1; d <= ld[b0]; ++d) for (auto r : I) { r.push_back(d); Ic.push_back(r); }
         for (const auto& r : J) for (int d = 1; d <= ld[b0 + 1]; ++d) { std::vector<int32_t> x; x.push_back(d); x.insert(x.end(), r.begin(), r.end()); Jc.push_back(x); }
         if (useextra) {
-            const int32_t* dXI = desc + 8 * (b0 + 1); const int32_t* dXJ = desc + 8 * b0;
+            const int32_t* dXI = desc + 12 * (b0 + 1); const int32_t* dXJ = desc + 12 * b0;
             for (const auto& r : rows_of(dXI[4], dXI[5], b0 + 1)) { bool dup = false; for (const auto& y : Ic) if (y == r) { dup = true; break; } if (!dup) Ic.push_back(r); }
             for (const auto& r : rows_of(dXJ[6], dXJ[7], N - b0 - 1)) { bool dup = false; for (const auto& y : Jc) if (y == r) { dup = true; break; } if (!dup) Jc.push_back(r); }
         }
@@ -251,8 +251,8 @@ int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* in, int64_t,
     const int32_t* ld = in + 8; const int32_t* desc = ld + N;
     MockAcc* a = (MockAcc*)acc;
     for (int b = 0; b < N; ++b) {
-        const int nI = desc[8 * b], nJ = desc[8 * b + 2], d = ld[b];
-        const int32_t* tI = in + desc[8 * b + 1]; const int32_t* tJ = in + desc[8 * b + 3];
+        const int nI = desc[12 * b], nJ = desc[12 * b + 2], d = ld[b];
+        const int32_t* tI = in + desc[12 * b + 1]; const int32_t* tJ = in + desc[12 * b + 3];
         const int64_t q = (int64_t)nI * d;
         static const int32_t dummy = 0;
         std::vector<double> pi1((size_t)(q * nJ));
@@ -262,10 +262,10 @@ int tci_dsweep_fill_f64(tci_handle h, tci_functor f, const int32_t* in, int64_t,
         merge_maxabs(&mx, pi1.data(), pi1.size());
         if (b == N - 1) { std::memcpy(cores[b], pi1.data(), sizeof(double) * pi1.size()); }
         else {
-            const int nI1 = desc[8 * (b + 1)];
+            const int nI1 = desc[12 * (b + 1)];
             if (nI1 != nJ) return mfail(h, TCI_ERR_NOT_SQUARE, "Pivot matrix at bond is not square!");
             std::vector<double> Pm((size_t)nJ * nJ), X((size_t)(q * nJ));
-            if (orc_batcheval((void*)f, ld, N, in + desc[8 * (b + 1) + 1], nI1, b + 1, N - b - 1 > 0 ? tJ : &dummy, nJ, N - b - 1, 0, Pm.data()))
+            if (orc_batcheval((void*)f, ld, N, in + desc[12 * (b + 1) + 1], nI1, b + 1, N - b - 1 > 0 ? tJ : &dummy, nJ, N - b - 1, 0, Pm.data()))
                 return mfail(h, TCI_ERR_INVALID, orc_last_error());
             merge_maxabs(&mx, Pm.data(), Pm.size());
             if (orc_solve_right(Pm.data(), nJ, pi1.data(), q, X.data())) return mfail(h, TCI_ERR_INVALID, "tci_solve_right_f64: pivot matrix is singular");
@@ -289,8 +289,8 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* in, in
     static const int32_t dummy = 0;
     bool stopped = false;
     for (int b0 = 0; b0 < N - 1; ++b0) {
-        const int d = ld[b0], nI = nmov, nJ = desc[8 * b0 + 2];
-        const int32_t* tJ = in + desc[8 * b0 + 3];
+        const int d = ld[b0], nI = nmov, nJ = desc[12 * b0 + 2];
+        const int32_t* tJ = in + desc[12 * b0 + 3];
         const int64_t m = (int64_t)nI * d, n = nJ, mn = m < n ? m : n;
         const int64_t rcap = (maxbond > 0 && maxbond < mn) ? maxbond : mn;
         if (m * n > g_dsweep_limit || m * rcap > corecap[b0] || used + rcap * (N + 1) + 2 * (rcap + 2) > out_cap) { out[0] = 1; out[1] = b0; stopped = true; break; }
@@ -332,7 +332,7 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* in, in
         mov = newI; nmov = (int)r;
     }
     if (!stopped) {
-        const int b0 = N - 1, d = ld[b0], nJ = desc[8 * b0 + 2];
+        const int b0 = N - 1, d = ld[b0], nJ = desc[12 * b0 + 2];
         const int64_t q = (int64_t)nmov * d;
         if (q * nJ > corecap[b0]) { out[0] = 1; out[1] = N - 1; }
         else {
