@@ -18,7 +18,7 @@ static int die(const char* what, const char* msg) {
     return 2;
 }
 
-int main(void) {
+int main(int argc, char** argv) {
     tci_handle h = NULL;
     if (tci_create(&h, 0) != TCI_OK) return die("tci_create", tci_last_error(NULL));
 
@@ -30,6 +30,8 @@ int main(void) {
 
     tci_tci2 t = NULL;
     if (tci_tci2_create(h, localdims, N, &t) != TCI_OK) return die("tci_tci2_create", tci_last_error(h));
+    /* argv[1] = "percall": one C-ABI call per bond phase; default: half-sweeps as single launches (csrc/sweep.cu) */
+    if (tci_tci2_set_engine(t, (argc > 1 && argv[1][0] == 'p') ? 0 : 1) != TCI_OK) return die("tci_tci2_set_engine", tci_tci2_last_error(t));
     if (tci_tci2_addglobalpivots(t, pivot, 1) != TCI_OK || tci_tci2_init_maxsample(t, f, pivot, 1) != TCI_OK)
         return die("initial pivot", tci_tci2_last_error(t));
 

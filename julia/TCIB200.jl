@@ -4,8 +4,9 @@
 # through the B200 library.  It overloads the reference's own extension points and nothing else:
 #   B1  (f::BatchEvaluator{Float64})(leftindexset, rightindexset, Val(M))   src/batcheval.jl:196-214, docs/src/index.md:181-237
 #   B2  rrlu / rrlu! / MatrixLUCI on a device-resident Pi matrix            src/matrixlu.jl:420-463, src/matrixluci.jl:55
-#   B3  left/right(::MatrixLUCI), the solve of setsitetensor!, sum, evaluate src/matrixluci.jl:256-283, src/tensorci2.jl:626,
-#                                                                           src/abstracttensortrain.jl:328-441
+#   B3  left/right(::MatrixLUCI), the solve of setsitetensor!, _contract,   src/matrixluci.jl:256-283, src/tensorci2.jl:599-629,
+#       sum, evaluate                                                        src/contraction.jl:193-215, src/abstracttensortrain.jl:328-441
+#   and, optionally, the bond loop itself: halfsweep! / fillsitetensors! as single launches (tci_dsweep_*, csrc/sweep.cu)
 # Sweep strategy, index-set bookkeeping and convergence control stay in the unmodified Julia package.
 #
 # NOT TESTED in this repository: the build image and the GPU box have no Julia (see DESIGN.md §1).  The same C ABI is
@@ -271,6 +272,154 @@ function TCI.optfirstpivot(f::B200Function, localdims::Union{Vector{Int},NTuple{
     check(f.h.ptr, ccall((:tci_optfirstpivot_f64, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Cint, Ptr{Int32}, Cint),
         f.h.ptr, f.f, f.localdims, length(f.localdims), pivot, maxsweep))
     return Int.(pivot)
+end
+
+# ---- B3: the solve of setsitetensor! and _contract ------------------------------------------------------------------------
+# setsitetensor!(tci, f, b) (src/tensorci2.jl:599-629): Pi1 and P are evaluated on the device and T = Pi1 * inv(P) (:626,
+# `transpose(transpose(P) \ transpose(Pi1))`) is tci_solve_right_f64; only the finished site tensor visits the host.
+function TCI.setsitetensor!(tci::TCI.TensorCI2{Float64}, f::B200Function, b::Int; leftorthogonal=true)
+    leftorthogonal || error("leftorthogonal==false is not supported!")
+    Is = leftorthogonal ? TCI.kronecker(tci.Iset[b], tci.localdims[b]) : tci.Iset[b]
+    Js = leftorthogonal ? tci.Jset[b] : TCI.kronecker(tci.localdims[b], tci.Jset[b])
+    mx = Ref(tci.maxsamplevalue)
+    Pi1 = DeviceMatrix(f.h, length(Is), length(Js))
+    evaluate_device!(f, Pi1, Is, Js, length(Is), Pi1.ld, mx)                          # :617-620 (+ updatemaxsample!)
+    if (leftorthogonal && b == length(tci)) || (!leftorthogonal && b == 1)            # :612-615
+        tci.maxsamplevalue = mx[]
+        TCI.setsitetensor!(tci, b, Array(Pi1))
+        return tci.sitetensors[b]
+    end
+    P = DeviceMatrix(f.h, length(tci.Iset[b+1]), length(tci.Jset[b]))
+    evaluate_device!(f, P, tci.Iset[b+1], tci.Jset[b], length(tci.Iset[b+1]), P.ld, mx)   # :622
+    tci.maxsamplevalue = mx[]
+    length(tci.Iset[b+1]) == length(tci.Jset[b]) || error("Pivot matrix at bond $(b) is not square!")   # :623
+    T = DeviceMatrix(f.h, length(Is), length(Js))
+    check(f.h.ptr, ccall((:tci_solve_right_f64, LIB), Cint,
+        (Ptr{Cvoid}, Ptr{Float64}, Int64, Int64, Ptr{Float64}, Int64, Int64, Ptr{Float64}, Int64),
+        f.h.ptr, Pi1.ptr, Pi1.m, Pi1.ld, P.ptr, P.m, P.ld, T.ptr, T.ld))             # :626
+    tci.sitetensors[b] = reshape(Array(T), length(tci.Iset[b]), tci.localdims[b], length(tci.Jset[b]))
+    return tci.sitetensors[b]
+end
+
+# _contract(a, b, idx_a, idx_b) (src/contraction.jl:193-215) on device tensors: the permutedims / reshape of :211-212 are
+# element strides of tci_gemm_f64 (one GEMM, no copies).  Handles the case the contraction code uses everywhere: the
+# contracted legs are a contiguous trailing block of `a` and a contiguous leading block of `b`, in the same order
+# (idx_a = (k+1, ..., na), idx_b = (1, ..., nb')); anything else goes through tci_strided_copy_f64 first.
+struct DeviceTensor{N}
+    M::DeviceMatrix                      # dense column-major storage, M.ld == M.m
+    dims::NTuple{N,Int}
+end
+function DeviceTensor(h::Handle, A::Array{Float64,N}) where {N}
+    M = DeviceMatrix(h, max(length(A), 1), 1)
+    check(h.ptr, ccall((:tci_memcpy_h2d, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Csize_t), h.ptr, M.ptr, A, 8 * length(A)))
+    return DeviceTensor{N}(M, size(A))
+end
+function Base.Array(T::DeviceTensor{N}) where {N}
+    out = Array{Float64,N}(undef, T.dims...)
+    check(T.M.h.ptr, ccall((:tci_memcpy_d2h, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Csize_t), T.M.h.ptr, out, T.M.ptr, 8 * length(out)))
+    return out
+end
+function TCI._contract(a::DeviceTensor{N1}, b::DeviceTensor{N2}, idx_a::NTuple{n1,Int}, idx_b::NTuple{n2,Int}) where {N1,N2,n1,n2}
+    length(idx_a) == length(idx_b) || error("length(idx_a) != length(idx_b)")                       # :200
+    length(unique(idx_a)) == length(idx_a) && length(unique(idx_b)) == length(idx_b) || error("idx_a or idx_b contains duplicate elements")
+    all(1 <= i <= N1 for i in idx_a) && all(1 <= i <= N2 for i in idx_b) || error("idx_a or idx_b contains elements out of range")
+    k = length(idx_a)
+    idx_a == ntuple(i -> N1 - k + i, k) && idx_b == ntuple(i -> i, k) || error("TCIB200._contract: permute the operands with tci_strided_copy_f64 first")
+    rest_a, rest_b = a.dims[1:N1-k], b.dims[k+1:N2]
+    Mr, Kc, Nc = prod(rest_a; init=1), prod(a.dims[N1-k+1:N1]; init=1), prod(rest_b; init=1)
+    Kc == prod(b.dims[1:k]; init=1) || error("contracted dimensions do not match")
+    h = a.M.h
+    C = DeviceMatrix(h, max(Mr * Nc, 1), 1)
+    check(h.ptr, ccall((:tci_gemm_f64, LIB), Cint,
+        (Ptr{Cvoid}, Int64, Int64, Int64, Float64, Ptr{Float64}, Int64, Int64, Ptr{Float64}, Int64, Int64, Float64, Ptr{Float64}, Int64, Int64,
+         Int64, Int64, Int64, Int64),
+        h.ptr, Mr, Nc, Kc, 1.0, a.M.ptr, 1, Mr, b.M.ptr, 1, Kc, 0.0, C.ptr, 1, Mr, 1, 0, 0, 0))                    # amat * bmat, :214
+    return DeviceTensor{N1 + N2 - 2k}(C, (rest_a..., rest_b...))
+end
+
+# ---- the bond loop on the device (csrc/sweep.cu): a whole half-sweep / fillsitetensors! / final sweep1site! per call ----------
+# pack Iset / Jset (and the history entries used as extras) into the int32 arena of tci_dsweep_* (include/tci_b200.h)
+function _arena(tci::TCI.TensorCI2{Float64}, forward::Bool, s0::Int, s1::Int, maxbonddim::Int,
+                extraI::Union{Nothing,Vector{Vector{MultiIndex}}}, extraJ::Union{Nothing,Vector{Vector{MultiIndex}}})
+    N = length(tci)
+    a = zeros(Int32, 8 + N * 13)
+    a[1] = N; a[2] = forward; a[3] = s0; a[4] = s1
+    a[5] = maxbonddim >= typemax(Int32) ? 0 : maxbonddim; a[6] = extraI !== nothing
+    a[9:8+N] .= tci.localdims
+    rows = 0
+    for b in 1:N
+        tabs = (tci.Iset[b], tci.Jset[b], extraI === nothing ? MultiIndex[] : extraI[b], extraJ === nothing ? MultiIndex[] : extraJ[b])
+        for (w, t) in enumerate(tabs)
+            d = 8 + N + 12 * (b - 1)
+            a[d+2w-1] = length(t); a[d+2w] = length(a)                      # count, word offset (0-based) of the table
+            a[d+8+w] = rows; rows += length(t)
+            for r in t; append!(a, Int32.(r)); end
+        end
+    end
+    a[7] = rows
+    return a
+end
+
+"""One half-sweep of sweep2site! (src/tensorci2.jl:1226-1250) as ONE launch wherever the Pi matrices fit shared memory; bonds that
+do not fit run through `TCI.updatepivots!` above.  `extraI/extraJ`: the history entries (tensorci2.jl:1212-1218) or nothing."""
+function halfsweep!(tci::TCI.TensorCI2{Float64}, f::B200Function, forward::Bool; abstol::Float64, maxbonddim::Int=typemax(Int),
+                    extraI=nothing, extraJ=nothing, acc::MaxAccumulator=MaxAccumulator(tci.maxsamplevalue; h=f.h))
+    N = length(tci)
+    TCI.invalidatesitetensors!(tci)
+    s = 0
+    while s < N - 1
+        a = _arena(tci, forward, s, N - 1, maxbonddim, extraI, extraJ)
+        out = Vector{Int32}(undef, 8 + 6 * (N - 1) + (N - 1) * (512 * (N + 1) + 1028))
+        used = Ref{Int64}(0)
+        check(f.h.ptr, ccall((:tci_dsweep_halfsweep_f64, LIB), Cint,
+            (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Int64, Float64, Float64, Ptr{Cvoid}, Ptr{Int32}, Int64, Ref{Int64}),
+            f.h.ptr, f.f, a, length(a), 1e-14, abstol, acc.ptr, out, length(out), used))
+        status, next = out[1], Int(out[2])
+        for st in s:next-1
+            b = forward ? st + 1 : N - 1 - st                                     # 1-based bond
+            rec = 8 + 6 * (st - s)
+            r, offA, offB, offE = Int(out[rec+1]), Int(out[rec+2]), Int(out[rec+3]), Int(out[rec+4])
+            tci.Iset[b+1] = [Int.(out[offA+1+(k-1)*b:offA+k*b]) for k in 1:r]
+            tci.Jset[b] = [Int.(out[offB+1+(k-1)*(N-b):offB+k*(N-b)]) for k in 1:r]
+            errs = collect(reinterpret(Float64, out[offE+1:offE+2*(r+1)]))
+            TCI.updateerrors!(tci, b, errs)
+        end
+        status == 2 && error("lu.L contains NaNs")
+        status == 3 && error("lu.U contains NaNs")
+        s = next
+        if status == 1 && s < N - 1                                               # this bond's Pi does not fit: per-bond path
+            b = forward ? s + 1 : N - 1 - s
+            TCI.updatepivots!(tci, b, f, forward; abstol=abstol, maxbonddim=maxbonddim,
+                              extraIset=extraI === nothing ? MultiIndex[] : extraI[b+1], extraJset=extraJ === nothing ? MultiIndex[] : extraJ[b])
+            s += 1
+        end
+    end
+    tci.maxsamplevalue = acc[]
+    nothing
+end
+
+"""fillsitetensors!(tci, f) (src/globalsearch.jl:202-208) for all sites in one launch (bond dimensions <= 64)."""
+function TCI.fillsitetensors!(tci::TCI.TensorCI2{Float64}, f::B200Function)
+    N = length(tci)
+    if maximum(length.(tci.Jset[1:N-1])) > 64
+        for b in 1:N; TCI.setsitetensor!(tci, f, b); end
+        return nothing
+    end
+    acc = MaxAccumulator(tci.maxsamplevalue; h=f.h)
+    cores = [DeviceMatrix(f.h, length(tci.Iset[b]) * tci.localdims[b], length(tci.Jset[b])) for b in 1:N]
+    a = _arena(tci, true, 0, 0, typemax(Int), nothing, nothing)
+    ptrs = [c.ptr for c in cores]
+    # (cores are allocated with ld == rows here: DeviceMatrix pads ld, so request dense buffers)
+    check(f.h.ptr, ccall((:tci_dsweep_fill_f64, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Int32}, Int64, Ptr{Cvoid}, Ptr{Ptr{Float64}}),
+                         f.h.ptr, f.f, a, length(a), acc.ptr, ptrs))
+    for b in 1:N
+        q, r = length(tci.Iset[b]) * tci.localdims[b], length(tci.Jset[b])
+        host = Vector{Float64}(undef, q * r)
+        check(f.h.ptr, ccall((:tci_memcpy_d2h, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}, Csize_t), f.h.ptr, host, cores[b].ptr, 8 * q * r))
+        tci.sitetensors[b] = reshape(host, length(tci.Iset[b]), tci.localdims[b], r)
+    end
+    tci.maxsamplevalue = acc[]
+    nothing
 end
 
 end # module

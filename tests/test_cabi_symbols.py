@@ -76,6 +76,6 @@ def test_header_is_plain_c_and_example_fails_loudly_without_a_device(tmp_path):
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(ROOT, "include"),
                            os.path.join(ROOT, "examples", "c1_lorentz.c"), "-L" + libdir, "-ltci_b200", "-Wl,-rpath," + libdir, "-o", exe])
     if torch.cuda.is_available():
-        pytest.skip("a GPU is present: the example would run the full interpolation")
+        pytest.skip("a GPU is present: tests/test_gpu_c_example.py runs the example")
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 2 and "no CPU fallback" in r.stderr
