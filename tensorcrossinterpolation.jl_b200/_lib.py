@@ -65,11 +65,24 @@ class Handle:
         if rc != TCI_OK:
             raise TCIError(rc, lib().tci_last_error(None).decode())
         self.device = int(device)
+        self._stream = None
         # torch owns the device buffers, so run on torch's current stream: its copies and our kernels stay ordered
         self.use_torch_stream()
 
     @property
     def h(self):
+        """The raw tci_handle for a library call.  Every call site reads this property right before the call, so it is also
+        where the handle follows torch's CURRENT stream: under `with torch.cuda.stream(s)` torch's copies go to `s`, and
+        library kernels left on the stream bound at construction would race with them (read-before-write on Pi and the
+        factors).  One pointer compare per call when nothing changed."""
+        try:
+            import torch
+            s = torch.cuda.current_stream(self.device).cuda_stream
+        except Exception:                                   # no CUDA device: calls fail loudly in the library itself
+            return self._h
+        if s != self._stream:
+            self._stream = s
+            lib().tci_set_stream(self._h, C.c_void_p(s))
         return self._h
 
     def check(self, rc):
@@ -80,6 +93,7 @@ class Handle:
         """Launch on torch's current stream so torch.cuda.Event timing brackets our kernels."""
         import torch
         s = torch.cuda.current_stream(self.device).cuda_stream
+        self._stream = s
         self.check(lib().tci_set_stream(self._h, C.c_void_p(s)))
 
     def synchronize(self):

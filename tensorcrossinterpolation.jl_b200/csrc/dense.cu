@@ -10,6 +10,8 @@
 // the reference's `permutedims`+`reshape` views (src/contraction.jl:211-212) cost nothing.
 #include "context.h"
 #include "solve_small.h"
+
+static inline unsigned ycap(long long cols) { return (unsigned)(cols < 1 ? 1 : (cols > 65535 ? 65535 : cols)); }   // gridDim.y limit; the kernels loop
 #include <cmath>
 #include <cstdlib>
 #include <vector>
@@ -281,8 +283,10 @@ int launch_pipe(tci_handle h, const GemmArgs& g, int batch) {
 
 __global__ void copy_strided_kernel(const double* __restrict__ src, long long ssr, long long ssc, double* __restrict__ dst,
                                         long long dsr, long long dsc, int rows, int cols) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i < rows && j < cols) dst[(long long)i * dsr + (long long)j * dsc] = src[(long long)i * ssr + (long long)j * ssc];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    for (int j = blockIdx.y; j < cols; j += gridDim.y)       // grid.y is capped at 65535: wide matrices loop
+        dst[(long long)i * dsr + (long long)j * dsc] = src[(long long)i * ssr + (long long)j * ssc];
 }
 
 int launch_gemm(tci_handle h, const GemmArgs& g, int batch) {
@@ -368,7 +372,7 @@ int trsm_right(tci_handle h, const double* T, long long sr, long long sc, int r,
         GemmArgs g1{q, nb, nb, 1.0, 0.0, Bm + (long long)o * sbc, sbr, sbc, 0, inv + (size_t)b * NB * NB, 1, NB, 0, tmp, 1, q, 0};
         rc = launch_gemm(h, g1, 1);
         if (rc) return rc;
-        copy_strided_kernel<<<dim3((q + 255) / 256, nb), 256, 0, h->stream>>>(tmp, 1, q, Bm + (long long)o * sbc, sbr, sbc, q, nb);
+        copy_strided_kernel<<<dim3((q + 255) / 256, ycap(nb)), 256, 0, h->stream>>>(tmp, 1, q, Bm + (long long)o * sbc, sbr, sbc, q, nb);
         TCI_LAUNCH_CHECK(h);
     }
     return TCI_OK;
@@ -381,24 +385,29 @@ namespace {
 // out[perm[i], :] = (i < nident) ? e_i : W[i - woff, :]   (rows scattered through a 0-based permutation)
 __global__ void scatter_rows_kernel(double* __restrict__ out, long long ldo, const double* __restrict__ W, long long ldw,
                                     const int* __restrict__ perm, int m, int r, int nident) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i >= m || j >= r) return;
-    const double v = (i < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)j * ldw + (i - nident)];
-    out[(long long)j * ldo + perm[i]] = v;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    for (int j = blockIdx.y; j < r; j += gridDim.y) {
+        const double v = (i < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)j * ldw + (i - nident)];
+        out[(long long)j * ldo + perm[i]] = v;
+    }
 }
 // out[:, perm[j]] = (j < nident) ? e_j : W[:, j - nident]
 __global__ void scatter_cols_kernel(double* __restrict__ out, long long ldo, const double* __restrict__ W, long long ldw,
                                     const int* __restrict__ perm, int r, int n, int nident) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i >= r || j >= n) return;
-    const double v = (j < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)(j - nident) * ldw + i];
-    out[(long long)perm[j] * ldo + i] = v;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= r) return;
+    for (int j = blockIdx.y; j < n; j += gridDim.y) {
+        const double v = (j < nident) ? (i == j ? 1.0 : 0.0) : W[(long long)(j - nident) * ldw + i];
+        out[(long long)perm[j] * ldo + i] = v;
+    }
 }
 // W[:, j] = src[:, perm[j]]
 __global__ void gather_cols_kernel(double* __restrict__ W, long long ldw, const double* __restrict__ src, long long lds,
                                    const int* __restrict__ perm, int q, int r) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i < q && j < r) W[(long long)j * ldw + i] = src[(long long)perm[j] * lds + i];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= q) return;
+    for (int j = blockIdx.y; j < r; j += gridDim.y) W[(long long)j * ldw + i] = src[(long long)perm[j] * lds + i];
 }
 
 int upload_perm(tci_handle h, const int64_t* h_perm, int len, int* d_dst, size_t) {
@@ -511,17 +520,17 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
         if (leftorthogonal) {                             // colstimespivotinv  matrixluci.jl:194-213
             const int q = M - R;
             if (q > 0) {
-                copy_strided_kernel<<<dim3((q + 255) / 256, R), 256, 0, h->stream>>>(d_L + R, 1, ldl, W, 1, q, q, R);
+                copy_strided_kernel<<<dim3((q + 255) / 256, ycap(R)), 256, 0, h->stream>>>(d_L + R, 1, ldl, W, 1, q, q, R);
                 TCI_LAUNCH_CHECK(h);
                 rc = trsm_right(h, d_L, 1, ldl, R, 1, 0, W, 1, q, q);   // diagonal read from L (1.0 where the LU is left-orthogonal)
                 if (rc) return rc;
             }
-            scatter_rows_kernel<<<dim3((M + 255) / 256, R), 256, 0, h->stream>>>(d_left, ldleft, W, q > 0 ? q : 1, d_rp, M, R, R);
+            scatter_rows_kernel<<<dim3((M + 255) / 256, ycap(R)), 256, 0, h->stream>>>(d_left, ldleft, W, q > 0 ? q : 1, d_rp, M, R, R);
             TCI_LAUNCH_CHECK(h);
         } else {                                          // colmatrix  matrixluci.jl:161-165
             GemmArgs g{M, R, R, 1.0, 0.0, d_L, 1, ldl, 0, d_U, 1, ldu, 0, W, 1, M, 0};
             rc = launch_gemm(h, g, 1); if (rc) return rc;
-            scatter_rows_kernel<<<dim3((M + 255) / 256, R), 256, 0, h->stream>>>(d_left, ldleft, W, M, d_rp, M, R, 0);
+            scatter_rows_kernel<<<dim3((M + 255) / 256, ycap(R)), 256, 0, h->stream>>>(d_left, ldleft, W, M, d_rp, M, R, 0);
             TCI_LAUNCH_CHECK(h);
         }
     }
@@ -529,18 +538,18 @@ int tci_luci_factors_f64(tci_handle h, int64_t m, int64_t n, int64_t r, int left
         if (leftorthogonal) {                             // rowmatrix  matrixluci.jl:175-177
             GemmArgs g{R, N, R, 1.0, 0.0, d_L, 1, ldl, 0, d_U, 1, ldu, 0, W, 1, R, 0};
             rc = launch_gemm(h, g, 1); if (rc) return rc;
-            scatter_cols_kernel<<<dim3((R + 255) / 256, N), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, 0);
+            scatter_cols_kernel<<<dim3((R + 255) / 256, ycap(N)), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, 0);
             TCI_LAUNCH_CHECK(h);
         } else {                                          // pivotinvtimesrows  matrixluci.jl:227-241
             const int q = N - R;
             if (q > 0) {
-                copy_strided_kernel<<<dim3((R + 255) / 256, q), 256, 0, h->stream>>>(d_U + (long long)R * ldu, 1, ldu, W, 1, R, R, q);
+                copy_strided_kernel<<<dim3((R + 255) / 256, ycap(q)), 256, 0, h->stream>>>(d_U + (long long)R * ldu, 1, ldu, W, 1, R, R, q);
                 TCI_LAUNCH_CHECK(h);
                 // U1 X = U2  <=>  X^T U1^T = U2^T : right solve with the lower-triangular view U1^T
                 rc = trsm_right(h, d_U, ldu, 1, R, 1, 0, W, R, 1, q);
                 if (rc) return rc;
             }
-            scatter_cols_kernel<<<dim3((R + 255) / 256, N), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, R);
+            scatter_cols_kernel<<<dim3((R + 255) / 256, ycap(N)), 256, 0, h->stream>>>(d_right, ldright, W, R, d_cp, R, N, R);
             TCI_LAUNCH_CHECK(h);
         }
     }
@@ -565,7 +574,7 @@ int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb,
     int* d_rp = (int*)h->ws_b.ptr; int* d_cp = d_rp + R;
     double* Pw = (double*)((char*)h->ws_b.ptr + permbytes);
     double* Lw = Pw + (size_t)ldw * R; double* Uw = Lw + (size_t)ldw * R; double* W = Uw + (size_t)ldw * R;
-    copy_strided_kernel<<<dim3((R + 255) / 256, R), 256, 0, h->stream>>>(d_P, 1, ldp, Pw, 1, ldw, R, R);
+    copy_strided_kernel<<<dim3((R + 255) / 256, ycap(R)), 256, 0, h->stream>>>(d_P, 1, ldp, Pw, 1, ldw, R, R);
     TCI_LAUNCH_CHECK(h);
     std::vector<int64_t> rp(R), cp(R);
     int64_t npiv = 0; double err = 0.0;
@@ -575,11 +584,11 @@ int tci_solve_right_f64(tci_handle h, const double* d_B, int64_t q, int64_t ldb,
     rc = tci_pinned_reserve(h, permbytes + 64); if (rc) return rc;
     rc = upload_perm(h, rp.data(), R, d_rp, 0); if (rc) return rc;
     rc = upload_perm(h, cp.data(), R, d_cp, sizeof(int) * (size_t)R); if (rc) return rc;
-    gather_cols_kernel<<<dim3((Q + 255) / 256, R), 256, 0, h->stream>>>(W, Q, d_B, ldb, d_cp, Q, R);
+    gather_cols_kernel<<<dim3((Q + 255) / 256, ycap(R)), 256, 0, h->stream>>>(W, Q, d_B, ldb, d_cp, Q, R);
     TCI_LAUNCH_CHECK(h);
     rc = trsm_right(h, Uw, 1, ldw, R, 0, 0, W, 1, Q, Q); if (rc) return rc;      // W <- W U^-1
     rc = trsm_right(h, Lw, 1, ldw, R, 1, 1, W, 1, Q, Q); if (rc) return rc;      // W <- W L^-1
-    scatter_cols_kernel<<<dim3((Q + 255) / 256, R), 256, 0, h->stream>>>(d_X, ldx, W, Q, d_rp, Q, R, 0);
+    scatter_cols_kernel<<<dim3((Q + 255) / 256, ycap(R)), 256, 0, h->stream>>>(d_X, ldx, W, Q, d_rp, Q, R, 0);
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;
 }

@@ -140,9 +140,10 @@ __global__ void __launch_bounds__(256) transpose_kernel(const double* __restrict
 }
 
 __global__ void diag_scale_kernel(double* __restrict__ M, long long ld, int rows, int cols, const double* __restrict__ s, int by_rows) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i >= rows || j >= cols) return;
-    M[(long long)j * ld + i] = M[(long long)j * ld + i] * (by_rows ? s[i] : s[j]);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    for (int j = blockIdx.y; j < cols; j += gridDim.y)          // grid.y is capped at 65535: wide matrices loop
+        M[(long long)j * ld + i] = M[(long long)j * ld + i] * (by_rows ? s[i] : s[j]);
 }
 
 } // namespace
@@ -260,14 +261,14 @@ int tci_diag_scale_f64(tci_handle h, double* d_M, int64_t rows, int64_t cols, in
     if (!h) return TCI_ERR_INVALID;
     if (rows < 0 || cols < 0 || rows > INT32_MAX || cols > INT32_MAX) return tci_fail(h, TCI_ERR_INVALID, "tci_diag_scale_f64: bad sizes");
     if (rows == 0 || cols == 0) return TCI_OK;
-    if (!d_M || !h_s || ld < rows || cols > 65535) return tci_fail(h, TCI_ERR_INVALID, "tci_diag_scale_f64: bad arguments");
+    if (!d_M || !h_s || ld < rows) return tci_fail(h, TCI_ERR_INVALID, "tci_diag_scale_f64: bad arguments");
     TCI_CUDA(h, cudaSetDevice(h->device));
     const size_t ns = (size_t)(by_rows ? rows : cols);
     int rc = tci_ws_reserve(h, h->ws_c, sizeof(double) * ns);
     if (rc) return rc;
     std::vector<double> stage(h_s, h_s + ns);             // pageable copy: returns after the data is staged
     TCI_CUDA(h, cudaMemcpyAsync(h->ws_c.ptr, stage.data(), sizeof(double) * ns, cudaMemcpyHostToDevice, h->stream));
-    diag_scale_kernel<<<dim3((unsigned)((rows + 255) / 256), (unsigned)cols), 256, 0, h->stream>>>(d_M, ld, (int)rows, (int)cols,
+    diag_scale_kernel<<<dim3((unsigned)((rows + 255) / 256), (unsigned)(cols > 65535 ? 65535 : cols)), 256, 0, h->stream>>>(d_M, ld, (int)rows, (int)cols,
                                                                                                  (const double*)h->ws_c.ptr, by_rows);
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;

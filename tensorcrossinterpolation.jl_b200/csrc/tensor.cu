@@ -105,10 +105,12 @@ __global__ void maxabs_kernel(const double* __restrict__ x, long long rows, long
 // out[perm[i], j] = in[i, j]  (rows) / out[i, perm[j]] = in[i, j]  (cols); perm 0-based on the device
 __global__ void unpermute_kernel(const double* __restrict__ in, long long ldi, double* __restrict__ out, long long ldo,
                                  const int* __restrict__ perm, int rows, int cols, int by_rows) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-    if (i >= rows || j >= cols) return;
-    const double v = in[(long long)j * ldi + i];
-    if (by_rows) out[(long long)j * ldo + perm[i]] = v; else out[(long long)perm[j] * ldo + i] = v;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    for (int j = blockIdx.y; j < cols; j += gridDim.y) {       // grid.y is capped at 65535: wide matrices loop
+        const double v = in[(long long)j * ldi + i];
+        if (by_rows) out[(long long)j * ldo + perm[i]] = v; else out[(long long)perm[j] * ldo + i] = v;
+    }
 }
 
 } // namespace
@@ -200,10 +202,9 @@ int tci_maxabs_f64(tci_handle h, const double* d_x, int64_t rows, int64_t cols, 
 int tci_unpermute_f64(tci_handle h, const double* d_in, int64_t ldi, double* d_out, int64_t ldo, const int64_t* h_perm,
                       int64_t rows, int64_t cols, int by_rows) {
     if (!h) return TCI_ERR_INVALID;
-    if (rows < 0 || cols < 0 || rows > INT32_MAX || cols > 65535LL * 65535LL) return tci_fail(h, TCI_ERR_INVALID, "tci_unpermute_f64: bad sizes");
+    if (rows < 0 || cols < 0 || rows > INT32_MAX || cols > INT32_MAX) return tci_fail(h, TCI_ERR_INVALID, "tci_unpermute_f64: bad sizes");
     if (rows == 0 || cols == 0) return TCI_OK;
     if (!d_in || !d_out || !h_perm) return tci_fail(h, TCI_ERR_INVALID, "tci_unpermute_f64: NULL buffer");
-    if (cols > 65535) return tci_fail(h, TCI_ERR_INVALID, "tci_unpermute_f64: more than 65535 columns");
     TCI_CUDA(h, cudaSetDevice(h->device));
     const int64_t len = by_rows ? rows : cols;
     int rc = tci_ws_reserve(h, h->ws_c, sizeof(int) * (size_t)len + 256); if (rc) return rc;
@@ -212,7 +213,7 @@ int tci_unpermute_f64(tci_handle h, const double* d_in, int64_t ldi, double* d_o
     for (int64_t i = 0; i < len; ++i) pin[i] = (int)(h_perm[i] - 1);
     TCI_CUDA(h, cudaMemcpyAsync(h->ws_c.ptr, pin, sizeof(int) * (size_t)len, cudaMemcpyHostToDevice, h->stream));
     TCI_CUDA(h, cudaStreamSynchronize(h->stream));
-    unpermute_kernel<<<dim3((unsigned)((rows + 255) / 256), (unsigned)cols), 256, 0, h->stream>>>(d_in, ldi, d_out, ldo, (const int*)h->ws_c.ptr, (int)rows, (int)cols, by_rows);
+    unpermute_kernel<<<dim3((unsigned)((rows + 255) / 256), (unsigned)(cols > 65535 ? 65535 : cols)), 256, 0, h->stream>>>(d_in, ldi, d_out, ldo, (const int*)h->ws_c.ptr, (int)rows, (int)cols, by_rows);
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;
 }
