@@ -40,10 +40,12 @@ struct EvalShape {
                                          // (peer-mapped through NVLink): the assembly IS the all-gather
 };
 
-// fold the left multi-indices (sites 0..nl-1) and the right ones (sites N-nr..N-1)
+// fold the left multi-indices (sites 0..nl-1) and the right ones (sites N-nr..N-1); with Cs != NULL also, per (c, j) pair
+// (c = centre multi-index, first site fastest), the state of "centre digits + right index" and the pair's output offset, so
+// that the assembly kernel does no index arithmetic at all
 template <class F>
 __global__ void fold_kernel(F f, const int* __restrict__ left, const int* __restrict__ right, EvalShape sh, int nsites,
-                            typename F::State* Ls, typename F::State* Rs) {
+                            typename F::State* Ls, typename F::State* Rs, typename F::State* Cs, long long* Off) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t < sh.nleft) {
         typename F::State s = f.zero();
@@ -54,6 +56,15 @@ __global__ void fold_kernel(F f, const int* __restrict__ left, const int* __rest
         typename F::State s = f.zero();
         for (int p = 0; p < sh.nr; ++p) f.push(s, nsites - sh.nr + p, right[j * sh.nr + p]);
         Rs[j] = s;
+    } else if (Cs && t < sh.nleft + sh.nright + sh.ncent * sh.nright) {
+        const long long cj = t - sh.nleft - sh.nright;
+        const long long j = cj / sh.ncent, c = cj - j * sh.ncent;
+        typename F::State s = f.zero();
+        for (int p = 0; p < sh.nr; ++p) f.push(s, nsites - sh.nr + p, right[j * sh.nr + p]);
+        long long rem = c;
+        for (int x = 0; x < sh.ncent_sites; ++x) { f.push(s, sh.nl + x, (int)(rem % sh.cdims[x]) + 1); rem /= sh.cdims[x]; }
+        Cs[cj] = s;
+        Off[cj] = c * sh.stride_c + j * sh.stride_j;
     }
 }
 
@@ -121,6 +132,46 @@ assemble_kernel(F f, EvalShape sh, int nsites, const typename F::State* __restri
     maxabs_commit(mx, isn, maxbits, nanflag);
 }
 
+// Vectorised assembly for the bulk case (one destination, even strides, 16-byte aligned output): a thread keeps the left
+// states of FOUR consecutive-pair rows (i, i+1) and (i + 2 T, i + 2 T + 1) ... in registers for the whole launch and walks the
+// (c, j) pairs of its block, so per element there is one merge, one finish and half a 128-bit store — no index arithmetic,
+// no re-load of the row state.  Grid: x over blocks of 4 * 256 rows, y over the pairs (strided).
+template <class F>
+__global__ void __launch_bounds__(256, 6)
+assemble4_kernel(F f, EvalShape sh, const typename F::State* __restrict__ Ls, const typename F::State* __restrict__ Cs,
+                 const long long* __restrict__ Off, unsigned long long* maxbits, int* nanflag) {
+    typedef typename F::State S;
+    const int nleft = (int)sh.nleft;
+    const int ncj = (int)(sh.ncent * sh.nright);
+    const int ia = blockIdx.x * 1024 + 2 * threadIdx.x, ib = ia + 512;   // rows ia, ia+1 and ib, ib+1 of this block's 1024 rows
+    const bool va0 = ia < nleft, va1 = ia + 1 < nleft, vb0 = ib < nleft, vb1 = ib + 1 < nleft;
+    S la0 = f.zero(), la1 = f.zero(), lb0 = f.zero(), lb1 = f.zero();
+    if (va0) la0 = Ls[ia]; if (va1) la1 = Ls[ia + 1]; if (vb0) lb0 = Ls[ib]; if (vb1) lb1 = Ls[ib + 1];
+    unsigned long long mb = 0;                                        // bits of the largest |value| seen; any NaN exceeds the bits of +Inf
+    double* __restrict__ out = sh.outs[0];
+    int cj = blockIdx.y;
+    S csn = cj < ncj ? Cs[cj] : f.zero();
+    long long offn = cj < ncj ? Off[cj] : 0;
+    for (; cj < ncj; cj += gridDim.y) {
+        const S cs = csn;
+        double* __restrict__ o = out + offn;
+        const int cn = cj + gridDim.y;                                  // the next pair's state and offset: loaded one iteration ahead
+        if (cn < ncj) { csn = Cs[cn]; offn = Off[cn]; }
+        const double a0 = f.finish(f.merge(la0, cs)), a1 = f.finish(f.merge(la1, cs));
+        const double b0 = f.finish(f.merge(lb0, cs)), b1 = f.finish(f.merge(lb1, cs));
+        if (va1) *reinterpret_cast<double2*>(o + ia) = make_double2(a0, a1); else if (va0) o[ia] = a0;
+        if (vb1) *reinterpret_cast<double2*>(o + ib) = make_double2(b0, b1); else if (vb0) o[ib] = b0;
+        const unsigned long long k0 = va0 ? (unsigned long long)__double_as_longlong(a0) & 0x7fffffffffffffffULL : 0ULL;
+        const unsigned long long k1 = va1 ? (unsigned long long)__double_as_longlong(a1) & 0x7fffffffffffffffULL : 0ULL;
+        const unsigned long long k2 = vb0 ? (unsigned long long)__double_as_longlong(b0) & 0x7fffffffffffffffULL : 0ULL;
+        const unsigned long long k3 = vb1 ? (unsigned long long)__double_as_longlong(b1) & 0x7fffffffffffffffULL : 0ULL;
+        const unsigned long long ka = k0 > k1 ? k0 : k1, kb = k2 > k3 ? k2 : k3, kc = ka > kb ? ka : kb;
+        mb = kc > mb ? kc : mb;
+    }
+    const bool isn = mb > 0x7ff0000000000000ULL;                      // a NaN was written (Julia's max propagates it, util.jl:34-43)
+    maxabs_commit(isn ? 0.0 : __longlong_as_double((long long)mb), isn, maxbits, nanflag);
+}
+
 // generic kernel source for NVRTC user functors; the user supplies
 //   __device__ double tci_user_f(const int* idx, int n, const double* params, int nparams);
 const char* kUserKernelSrc = R"SRC(
@@ -161,19 +212,24 @@ tci_user_assemble(const int* __restrict__ left, const int* __restrict__ right, i
 
 namespace {
 
-struct EvalBuffers { int* d_left; int* d_right; void* Ls; void* Rs; unsigned long long* maxbits; int* nanflag; };
+struct EvalBuffers { int* d_left; int* d_right; void* Ls; void* Rs; void* Cs; long long* Off; unsigned long long* maxbits; int* nanflag; };
 
 int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, const EvalShape& sh, EvalBuffers* b, bool zero_acc = true) {
     const size_t nli = (size_t)sh.nleft * sh.nl, nri = (size_t)sh.nright * sh.nr;
     const size_t ints = ((nli + nri) * sizeof(int) + 255) & ~(size_t)255;
     int rc = tci_ws_reserve(h, h->ws_a, ints + 256);
     if (rc) return rc;
-    rc = tci_ws_reserve(h, h->ws_b, 16 * (size_t)(sh.nleft + sh.nright) + 256);        // a State is at most 16 bytes
+    const size_t npair = (size_t)(sh.ncent * sh.nright);
+    const size_t st_bytes = 16 * (size_t)(sh.nleft + sh.nright);                      // a State is at most 16 bytes
+    const bool pairs = npair <= ((size_t)1 << 22);                                   // per-pair states for the vectorised assembly (<= 96 MB)
+    rc = tci_ws_reserve(h, h->ws_b, st_bytes + (pairs ? 24 * npair : 0) + 256);
     if (rc) return rc;
     b->d_left = (int*)h->ws_a.ptr; b->d_right = b->d_left + nli;
     b->maxbits = (unsigned long long*)((char*)h->ws_a.ptr + ints);
     b->nanflag = (int*)(b->maxbits + 1);
     b->Ls = h->ws_b.ptr; b->Rs = (char*)h->ws_b.ptr + 16 * (size_t)sh.nleft;
+    b->Cs = pairs ? (char*)h->ws_b.ptr + st_bytes : nullptr;
+    b->Off = pairs ? (long long*)((char*)h->ws_b.ptr + st_bytes + 16 * npair) : nullptr;
     if (zero_acc) TCI_CUDA(h, cudaMemsetAsync(b->maxbits, 0, 16, h->stream));
     // The index tables are pageable host memory: cudaMemcpyAsync stages them before it returns, so there is no host
     // synchronisation here and the caller may reuse its arrays immediately.
@@ -185,9 +241,27 @@ int stage_tables(tci_handle h, const int32_t* h_left, const int32_t* h_right, co
 template <class F>
 int run_builtin(tci_handle h, const F& f, const EvalShape& sh, int nsites, const EvalBuffers& b) {
     typedef typename F::State S;
-    const long long nfold = sh.nleft + sh.nright;
-    fold_kernel<F><<<(unsigned)((nfold + 255) / 256), 256, 0, h->stream>>>(f, b.d_left, b.d_right, sh, nsites, (S*)b.Ls, (S*)b.Rs);
+    // bulk case: the vectorised kernel (rows in registers, 128-bit streaming stores, per-pair states from the fold)
+    const long long ncj = sh.ncent * sh.nright;
+    const bool bulk = sh.nouts == 1 && sh.nleft >= 512 && sh.nleft < (1LL << 30) && ncj < (1LL << 30) && ncj >= 64 && (sh.stride_c % 2) == 0 &&
+                      (sh.stride_j % 2) == 0 && ((uintptr_t)sh.outs[0] % 16) == 0 && b.Cs != nullptr;
+    const long long nfold = sh.nleft + sh.nright + (bulk ? ncj : 0);
+    fold_kernel<F><<<(unsigned)((nfold + 255) / 256), 256, 0, h->stream>>>(f, b.d_left, b.d_right, sh, nsites, (S*)b.Ls, (S*)b.Rs,
+                                                                           bulk ? (S*)b.Cs : nullptr, bulk ? b.Off : nullptr);
     TCI_LAUNCH_CHECK(h);
+    if (bulk) {
+        const long long bx = (sh.nleft + 1023) / 1024;
+        // exactly one resident wave (a persistent grid): 1.3 waves of a write-bound kernel leave a third of the GPU idle at the end
+        static thread_local int occ = 0;
+        if (!occ) { if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, assemble4_kernel<F>, 256, 0) != cudaSuccess || occ < 1) occ = 4; }
+        long long by = ((long long)h->num_sms * occ) / bx;
+        if (by < 1) by = 1;
+        if (by > ncj) by = ncj;
+        if (by > 65535) by = 65535;
+        assemble4_kernel<F><<<dim3((unsigned)bx, (unsigned)by), 256, 0, h->stream>>>(f, sh, (const S*)b.Ls, (const S*)b.Cs, b.Off, b.maxbits, b.nanflag);
+        TCI_LAUNCH_CHECK(h);
+        return TCI_OK;
+    }
     long long gx = (sh.nleft + 256 * 8 - 1) / (256 * 8);        // ~8 rows per thread per (c, j) pair
     if (gx > 32) gx = 32;
     long long gy = sh.ncent * sh.nright;
@@ -331,7 +405,7 @@ static int batcheval_enqueue(tci_handle h, tci_functor f, const int32_t* h_local
     if (rc) return rc;
     if (d_acc) { b.maxbits = (unsigned long long*)d_acc; b.nanflag = (int*)(b.maxbits + 1); }
     switch (f->kind) {
-    case TCI_F_LORENTZ: rc = run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b); break;
+    case TCI_F_LORENTZ: rc = f->p[0] == 1.0 ? run_builtin(h, LorentzUnitF{}, sh, nsites, b) : run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b); break;
     case TCI_F_SUM: rc = run_builtin(h, SumF{f->p[0]}, sh, nsites, b); break;
     case TCI_F_QEXPSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b); break;
     case TCI_F_QEXPPLUSSIN: rc = run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b); break;

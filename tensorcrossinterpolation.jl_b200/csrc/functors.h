@@ -28,10 +28,23 @@ struct LorentzF {                        // p0 / (1 + sum v^2): README.md:21-29
     __device__ State merge(State a, State b) const { return a + b; }
     __device__ double finish(State s) const {
         const long long d = 1 + s;
-        // int32 -> double conversion when it fits (the 64-bit one runs on the slow XU path); 1/x through the correctly
-        // rounded reciprocal when coeff == 1 (same bits as the IEEE division 1.0 / x, fewer Newton steps)
-        const double x = (d < 0x7fffffffLL) ? (double)(int)d : (double)d;
-        return coeff == 1.0 ? __drcp_rn(x) : coeff / x;
+        // exact int64 -> double for 0 <= d < 2^52 with one add (the I2F.F64.S64 conversion runs on the slow XU path): the
+        // bits 0x433 << 52 | d are the double 2^52 + d
+        const double x = (d >= 0 && d < (1LL << 52)) ? __longlong_as_double(0x4330000000000000LL | d) - 4503599627370496.0 : (double)d;
+        // coeff == 1 (the README function): the correctly rounded reciprocal — the same bits as the IEEE division 1.0 / x
+        if (coeff == 1.0) return __drcp_rn(x);
+        return coeff / x;
+    }
+};
+struct LorentzUnitF {                    // coeff == 1: 1 / (1 + sum v^2) through the correctly rounded reciprocal (the same bits as
+    typedef long long State;             // the IEEE division 1.0 / x of LorentzF, without the multiply-and-correct tail of a division)
+    __device__ State zero() const { return 0; }
+    __device__ void push(State& s, int, int v) const { s += (long long)v * v; }
+    __device__ State merge(State a, State b) const { return a + b; }
+    __device__ double finish(State s) const {
+        const long long d = 1 + s;
+        const double x = (d >= 0 && d < (1LL << 52)) ? __longlong_as_double(0x4330000000000000LL | d) - 4503599627370496.0 : (double)d;
+        return __drcp_rn(x);
     }
 };
 struct SumF {                            // p0 * sum v: test/test_batcheval.jl:18
