@@ -43,6 +43,8 @@ def main():
     ap.add_argument("--chi", type=int, default=200)
     ap.add_argument("--d", type=int, default=4)
     ap.add_argument("--cpu-sites", type=int, default=3)
+    ap.add_argument("--tci", action="store_true", help="also time contract_TCI(maxbonddim=chi)")
+    ap.add_argument("--tci-maxiter", type=int, default=2)
     args = ap.parse_args()
     import torch
     import tci_b200 as T
@@ -63,9 +65,55 @@ def main():
 
     dt, tt, s, nl = gpu_run(A, B)
     fl = zipup_flops(args.sites, args.chi, args.d)
+    # ---- per-phase DEVICE time of one more run: the two GEMMs per site (_contract) and the factorisation (_factorize -> rrLU),
+    #      bracketed with CUDA events on the stream the library launches on (torch's current stream)
+    from tci_b200 import contraction as CM
+    ev = {"gemm": [], "factorize": []}
+    orig_c, orig_f = CM._contract, CM._factorize
+
+    def timed(kind, fn):
+        def w(*a, **k):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); r = fn(*a, **k); e1.record()
+            ev[kind].append((e0, e1))
+            return r
+        return w
+    CM._contract, CM._factorize = timed("gemm", orig_c), timed("factorize", orig_f)
+    try:
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        T.contract_zipup(A, B, tolerance=1e-12, method="LU", maxbonddim=args.chi)
+        torch.cuda.synchronize(); dt_inst = time.perf_counter() - t0
+    finally:
+        CM._contract, CM._factorize = orig_c, orig_f
+    t_gemm = sum(a.elapsed_time(b) for a, b in ev["gemm"]) * 1e-3
+    t_fact = sum(a.elapsed_time(b) for a, b in ev["factorize"]) * 1e-3
+    # algorithmic Schur-update bytes of the factorisations (16 B per updated element): site n factorises a
+    # (lc * d * d) x (chi * chi) matrix with maxrank chi
+    bonds = [1] + [args.chi] * (args.sites - 1) + [1]
+    lc, upd = 1, 0.0
+    for k in range(args.sites - 1):
+        m_, n_ = lc * args.d * args.d, bonds[k + 1] * bonds[k + 1]
+        r_ = min(args.chi, m_, n_)
+        upd += sum(16.0 * (m_ - q) * (n_ - q) for q in range(1, r_ + 1))
+        lc = r_
+    peak_hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+    torch.cuda.synchronize(); t0 = time.perf_counter(); ssum = tt.sum(); torch.cuda.synchronize(); t_sum = time.perf_counter() - t0
     line = {"config": f"C5: MPO x MPO zip-up (:LU), {args.sites} sites, legs {args.d}x{args.d}, bond {args.chi}, maxbonddim={args.chi}, FP64",
             "gpu": {"wall_s": dt, "gemm_flop": fl, "gemm_tflops_over_wall": fl / dt / 1e12, "sum": s, "linkdims_max": max(tt.linkdims()),
-                    "launches": nl}}
+                    "launches": nl,
+                    "phases": {"instrumented_wall_s": dt_inst, "gemm_device_s": t_gemm, "gemm_tflops": fl / t_gemm / 1e12,
+                               "gemm_frac_of_dgemm_peak_35.3": fl / t_gemm / 1e12 / 35.3,
+                               "factorize_device_s": t_fact, "rrlu_update_GB": upd / 1e9, "rrlu_update_GBps": upd / t_fact / 1e9,
+                               "rrlu_frac_of_hbm_peak": upd / t_fact / 1e9 / peak_hbm, "hbm_peak_GBps": peak_hbm,
+                               "note": "factorize = rrLU of the (lc d^2) x chi^2 matrix incl. its swap / extraction kernels and the "
+                                       "un-permutation of L and U; GB/s counts the Schur-update bytes only"},
+                    "sum_wall_s": t_sum}}
+    if args.tci:
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        tt2 = T.contract_TCI(A, B, tolerance=1e-10, maxbonddim=args.chi, maxiter=args.tci_maxiter, rng=np.random.default_rng(5), nsearchglobalpivot=0)
+        torch.cuda.synchronize(); dt2 = time.perf_counter() - t0
+        line["gpu"]["contract_TCI"] = {"wall_s": dt2, "maxbonddim": args.chi, "maxiter": args.tci_maxiter, "linkdims_max": max(tt2.linkdims()),
+                                       "sum": tt2.sum(), "zipup_sum": ssum}
     if args.cpu_sites > 0:
         from oracle import contraction_oracle as CO
         k = args.cpu_sites
