@@ -56,6 +56,7 @@ int tci_malloc(tci_handle h, void** d_ptr, size_t bytes);
 int tci_free(tci_handle h, void* d_ptr);
 int tci_memcpy_h2d(tci_handle h, void* d_dst, const void* h_src, size_t bytes);
 int tci_memcpy_d2h(tci_handle h, void* h_dst, const void* d_src, size_t bytes);
+int tci_memcpy_d2d(tci_handle h, void* d_dst, const void* d_src, size_t bytes);     /* enqueued on the handle's stream, not synchronised */
 
 /* ---- K2 + K3: full-pivot rank-revealing LU --------------------------------------------------
  * Replaces  rrlu!(A; maxrank, reltol, abstol, leftorthogonal)        src/matrixlu.jl:420-430
@@ -366,6 +367,12 @@ int tci_tci2_optimize(tci_tci2 t, tci_functor f, double tolerance, int64_t maxbo
  * call that changes the object.  Fails when the site tensors are invalidated (:206-220). */
 int tci_tci2_core(tci_tci2 t, int site, const double** d_core, int64_t* h_shape3);
 int tci_tci2_sitetensors_available(tci_tci2 t);
+/* The whole result in two calls: all site tensors copied device-to-device (enqueued, not synchronised) into ONE caller buffer,
+ * dense and back to back — h_shapes3[3b..] = (chi_l, d, chi_r), h_offsets[b] = first element of tensor b, *h_total = doubles
+ * needed (call with d_dst = NULL to size the buffer) — and all index sets packed as I_0, J_0, I_1, J_1, ... (row-major int32
+ * tables; h_counts2[2b] = |Iset[b]|, [2b+1] = |Jset[b]|; h_dst = NULL queries *h_total). */
+int tci_tci2_export_cores(tci_tci2 t, double* d_dst, int64_t capacity, int64_t* h_shapes3, int64_t* h_offsets, int64_t* h_total);
+int tci_tci2_export_indexsets(tci_tci2 t, int32_t* h_dst, int64_t capacity, int64_t* h_counts2, int64_t* h_total);
 /* evaluate(tci, indexset) src/abstracttensortrain.jl:328-342 at npoints multi-indices (h_points: npoints x nsites, 1-based; values
  * to h_out) and sum(tci) :428-441, on the object's own site tensors (tci_tt_evaluate_f64 / tci_tt_sum_f64 underneath). */
 int tci_tci2_evaluate(tci_tci2 t, const int32_t* h_points, int64_t npoints, double* h_out);

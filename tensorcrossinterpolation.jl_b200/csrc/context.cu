@@ -112,6 +112,11 @@ int tci_memcpy_h2d(tci_handle h, void* d_dst, const void* h_src, size_t bytes) {
     TCI_CUDA(h, cudaStreamSynchronize(h->stream));
     return TCI_OK;
 }
+int tci_memcpy_d2d(tci_handle h, void* d_dst, const void* d_src, size_t bytes) {          /* enqueued on the handle's stream, no sync */
+    if (!h) return TCI_ERR_INVALID;
+    TCI_CUDA(h, cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, h->stream));
+    return TCI_OK;
+}
 int tci_memcpy_d2h(tci_handle h, void* h_dst, const void* d_src, size_t bytes) {
     if (!h) return TCI_ERR_INVALID;
     TCI_CUDA(h, cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, h->stream));

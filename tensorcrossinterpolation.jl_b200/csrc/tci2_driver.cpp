@@ -1108,6 +1108,48 @@ int tci_tci2_sum(tci_tci2 t, double* h_out) {
     return TCI_OK;
 }
 
+/* Everything a host wants after optimize!, in two calls instead of 4 N: all site tensors copied (device to device, enqueued, no
+ * synchronisation) into ONE caller buffer, dense and back to back — h_shapes[3b..] = (chi_l, d, chi_r), h_offsets[b] = first
+ * element of tensor b in d_dst (query the total with d_dst = NULL first) — and all index sets packed into one int32 buffer. */
+int tci_tci2_export_cores(tci_tci2 t, double* d_dst, int64_t capacity, int64_t* h_shapes, int64_t* h_offsets, int64_t* h_total) {
+    if (!t || !h_shapes || !h_offsets || !h_total) return TCI_ERR_INVALID;
+    int64_t off = 0;
+    for (int b = 0; b < t->N; ++b) {
+        const Core& c = t->T[b];
+        if (!c.valid) return fail(t, TCI_ERR_INVALID, "site tensors are not available (call fillsitetensors! or a sweep first)");
+        h_shapes[3 * b] = c.chil; h_shapes[3 * b + 1] = c.d; h_shapes[3 * b + 2] = c.chir;
+        h_offsets[b] = off;
+        off += c.chil * c.d * c.chir;
+    }
+    *h_total = off;
+    if (!d_dst) return TCI_OK;
+    if (capacity < off) return fail(t, TCI_ERR_INVALID, "tci_tci2_export_cores: buffer too small");
+    for (int b = 0; b < t->N; ++b) {
+        const Core& c = t->T[b];
+        const int64_t sz = c.chil * c.d * c.chir;
+        if (sz > 0) TCI2_CALL(t, tci_memcpy_d2d(t->h, d_dst + h_offsets[b], c.buf.p, sizeof(double) * (size_t)sz));
+    }
+    return TCI_OK;
+}
+
+int tci_tci2_export_indexsets(tci_tci2 t, int32_t* h_dst, int64_t capacity, int64_t* h_counts2, int64_t* h_total) {
+    if (!t || !h_counts2 || !h_total) return TCI_ERR_INVALID;            /* h_counts2[2b] = |Iset[b]|, [2b+1] = |Jset[b]|; I_0, J_0, I_1, ... */
+    int64_t off = 0;
+    for (int b = 0; b < t->N; ++b) {
+        h_counts2[2 * b] = t->I[b].n; h_counts2[2 * b + 1] = t->J[b].n;
+        off += (int64_t)t->I[b].v.size() + (int64_t)t->J[b].v.size();
+    }
+    *h_total = off;
+    if (!h_dst) return TCI_OK;
+    if (capacity < off) return fail(t, TCI_ERR_INVALID, "tci_tci2_export_indexsets: buffer too small");
+    int32_t* w = h_dst;
+    for (int b = 0; b < t->N; ++b) {
+        if (!t->I[b].v.empty()) { std::memcpy(w, t->I[b].v.data(), sizeof(int32_t) * t->I[b].v.size()); w += t->I[b].v.size(); }
+        if (!t->J[b].v.empty()) { std::memcpy(w, t->J[b].v.data(), sizeof(int32_t) * t->J[b].v.size()); w += t->J[b].v.size(); }
+    }
+    return TCI_OK;
+}
+
 int tci_tci2_sitetensors_available(tci_tci2 t) {
     if (!t) return 0;
     for (const auto& c : t->T) if (!c.valid || c.chil * c.chir == 0) return 0;

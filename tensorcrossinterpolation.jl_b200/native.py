@@ -130,6 +130,30 @@ class NativeTCI2:
         self._check(self.L.tci_tci2_core(self._t, site, C.byref(ptr), p_i64(shape)))
         return ptr.value, tuple(int(v) for v in shape)
 
+    def export_indexsets(self):
+        """(Iset, Jset): lists of (count, length) int32 tables for every site, fetched with two C calls."""
+        n = len(self)
+        counts, tot = np.zeros(2 * n, dtype=np.int64), C.c_int64()
+        self._check(self.L.tci_tci2_export_indexsets(self._t, None, C.c_int64(0), p_i64(counts), C.byref(tot)))
+        buf = np.zeros(max(tot.value, 1), dtype=np.int32)
+        self._check(self.L.tci_tci2_export_indexsets(self._t, p_i32(buf), C.c_int64(buf.size), p_i64(counts), C.byref(tot)))
+        I, J, off = [], [], 0
+        for b in range(n):
+            li, lj = b, n - b - 1
+            ci, cj = int(counts[2 * b]), int(counts[2 * b + 1])
+            I.append(buf[off:off + ci * li].reshape(ci, li).copy()); off += ci * li
+            J.append(buf[off:off + cj * lj].reshape(cj, lj).copy()); off += cj * lj
+        return I, J
+
+    def export_cores(self, alloc):
+        """All site tensors in ONE device buffer: `alloc(ndoubles)` returns (device pointer, owner); -> (owner, shapes, offsets)."""
+        n = len(self)
+        shapes, offs, tot = np.zeros(3 * n, dtype=np.int64), np.zeros(n, dtype=np.int64), C.c_int64()
+        self._check(self.L.tci_tci2_export_cores(self._t, None, C.c_int64(0), p_i64(shapes), p_i64(offs), C.byref(tot)))
+        ptr, owner = alloc(max(tot.value, 1))
+        self._check(self.L.tci_tci2_export_cores(self._t, C.c_void_p(ptr), C.c_int64(max(tot.value, 1)), p_i64(shapes), p_i64(offs), C.byref(tot)))
+        return owner, shapes.reshape(n, 3), offs
+
     def evaluate(self, points):
         """evaluate(tci, indexset) at many multi-indices (npoints x nsites, 1-based): numpy vector."""
         tab, n = _table(points, len(self))

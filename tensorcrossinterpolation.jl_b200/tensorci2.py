@@ -766,15 +766,18 @@ def _crossinterpolate2_native(f, localdims, initialpivots, seed, handle, kwargs,
         kwargs["tolerance"] = 1e-8
     ranks, errors = nat.optimize(f._f, **kwargs)
     tci = TensorCI2(localdims, handle=h)
-    tci.Iset = [nat.Iset(b + 1) for b in range(n)]
-    tci.Jset = [nat.Jset(b + 1) for b in range(n)]
+    tci.Iset, tci.Jset = nat.export_indexsets()
     tci.bonderrors, tci.pivoterrors, tci.maxsamplevalue = nat.errors()
     dev = f"cuda:{h.device}"
+
+    def alloc(ndoubles):                                    # one torch-owned buffer for all site tensors (the driver's die with `nat`)
+        buf = torch.empty(int(ndoubles), dtype=torch.float64, device=dev)
+        return buf.data_ptr(), buf
+    flat, shapes, offs = nat.export_cores(alloc)
     for b in range(n):
-        ptr, (chil, d, chir) = nat.core(b + 1)
-        size = chil * d * chir
-        flat = torch.as_tensor(_RawCuda(ptr, size), device=dev).clone()        # own the memory: the driver's buffers die with `nat`
-        tci._T[b] = DeviceCore(Mat(flat.view(chir, chil * d), chil * d, chir), chil, (d,), chir)
+        chil, d, chir = (int(v) for v in shapes[b])
+        o = int(offs[b])
+        tci._T[b] = DeviceCore(Mat(flat[o:o + chil * d * chir].view(chir, chil * d), chil * d, chir), chil, (d,), chir)
     st = nat.stats()
     tci.stats.update({k: st[k] for k in ("nevals", "t_eval", "t_lu", "t_factors", "t_host")})
     tci.stats["nbondupdates"] = st["nbondupdates"]

@@ -406,3 +406,27 @@ def test_evaluate_and_sum_on_the_object(mock):             # abstracttensortrain
     o, _, _ = O.crossinterpolate2(f, localdims, [[1] * 4], tolerance=1e-12)
     np.testing.assert_array_equal(vals, O.tt_evaluate(o.sitetensors(), pts))
     assert t.sum() == O.tt_sum(o.sitetensors())
+
+
+def test_bulk_export_matches_per_site_accessors(mock):
+    """tci_tci2_export_indexsets / tci_tci2_export_cores (the whole result in two calls) against the per-site accessors."""
+    localdims = [3, 5, 2, 4, 3]
+    f = O.Func(O.F_HASH, [1.0, 0.5])
+    t = _native(mock, localdims, f, [[1] * 5])
+    t.optimize(f.h, tolerance=1e-9, nsearchglobalpivot=0, maxiter=4)
+    I, J = t.export_indexsets()
+    for b in range(1, 6):
+        np.testing.assert_array_equal(I[b - 1], t.Iset(b))
+        np.testing.assert_array_equal(J[b - 1], t.Jset(b))
+    keep = {}
+
+    def alloc(n):                                           # "device" memory of the mock is host memory
+        keep["buf"] = np.zeros(n)
+        return keep["buf"].ctypes.data, keep["buf"]
+    flat, shapes, offs = t.export_cores(alloc)
+    for b in range(1, 6):
+        ptr, shape = t.core(b)
+        assert tuple(int(v) for v in shapes[b - 1]) == shape
+        size = int(np.prod(shape))
+        got = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(size,))
+        np.testing.assert_array_equal(flat[int(offs[b - 1]):int(offs[b - 1]) + size], got)
