@@ -337,11 +337,11 @@ def run_ours(args):
         work.copy_(A0)                       # rrlu copies A (matrixlu.jl:462)
         return _rrlu_device(h, work, n, n, n, r, 1e-14, 0.0, True, extract=True)
 
+    sampler = ClockSampler(local)
+    sampler.start()
     for _ in range(args.warmup):
         lu = step_device()
     npivot = lu.npivot
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier()
     l0 = h.launch_count()
     e0.record()
@@ -446,11 +446,11 @@ def run_sharded(args, T, torch, dist, h, dev, A0, world, rank, local, peak, peak
         work.copy_(blk0)                            # rrlu copies A (matrixlu.jl:462)
         return rrlu_sharded(T.Mat(work, n, nloc), n, s, comm, maxrank=r, handle=h, check_every=0, fused=True, peers=peers)
 
+    sampler = ClockSampler(local)                   # started before the warm-up: nvidia-smi needs a moment on an 8-GPU box
+    sampler.start()
     for _ in range(args.warmup):
         out = step_device()
     npivot = int(out["npivot"])
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier()
     l0 = h.launch_count()
     e0.record()
