@@ -54,6 +54,11 @@ int64_t tci_launch_count(tci_handle h);
 /* Raw device memory for hosts that have no allocator of their own (the Julia shim). */
 int tci_malloc(tci_handle h, void** d_ptr, size_t bytes);
 int tci_free(tci_handle h, void* d_ptr);
+/* Stream-ordered variants (cudaMallocAsync on the handle's stream, default pool with an unbounded release threshold): no
+ * device-wide synchronisation, a regrow costs microseconds.  Used by the native driver for its growing scratch (the
+ * reference's Julia arrays come from the GC's pools the same way, tensorci2.jl:560-575 allocates Pi per bond). */
+int tci_malloc_pooled(tci_handle h, void** d_ptr, size_t bytes);
+int tci_free_pooled(tci_handle h, void* d_ptr);
 int tci_memcpy_h2d(tci_handle h, void* d_dst, const void* h_src, size_t bytes);
 int tci_memcpy_d2h(tci_handle h, void* h_dst, const void* d_src, size_t bytes);
 int tci_memcpy_d2d(tci_handle h, void* d_dst, const void* d_src, size_t bytes);     /* enqueued on the handle's stream, not synchronised */

@@ -106,6 +106,29 @@ int tci_free(tci_handle h, void* d_ptr) {
     TCI_CUDA(h, cudaFree(d_ptr));
     return TCI_OK;
 }
+/* Stream-ordered allocation from the device's default memory pool (cudaMallocAsync): the native driver's scratch grows over the
+ * first sweeps, and cudaMalloc / cudaFree each cost hundreds of microseconds plus a device-wide sync.  The pool keeps what is
+ * freed (release threshold = unbounded), so a regrow is a few microseconds and never synchronises. */
+int tci_malloc_pooled(tci_handle h, void** d_ptr, size_t bytes) {
+    if (!h || !d_ptr) return TCI_ERR_INVALID;
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    static bool configured[64] = {};
+    if (h->device >= 0 && h->device < 64 && !configured[h->device]) {
+        cudaMemPool_t pool;
+        TCI_CUDA(h, cudaDeviceGetDefaultMemPool(&pool, h->device));
+        unsigned long long keep = ~0ull;
+        TCI_CUDA(h, cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        configured[h->device] = true;
+    }
+    cudaError_t e = cudaMallocAsync(d_ptr, bytes ? bytes : 1, h->stream);
+    if (e != cudaSuccess) return tci_fail(h, TCI_ERR_NOMEM, "cudaMallocAsync(%zu): %s", bytes, cudaGetErrorString(e));
+    return TCI_OK;
+}
+int tci_free_pooled(tci_handle h, void* d_ptr) {          /* ordered after the work already enqueued on the handle's stream */
+    if (!h) return TCI_ERR_INVALID;
+    if (d_ptr) TCI_CUDA(h, cudaFreeAsync(d_ptr, h->stream));
+    return TCI_OK;
+}
 int tci_memcpy_h2d(tci_handle h, void* d_dst, const void* h_src, size_t bytes) {
     if (!h) return TCI_ERR_INVALID;
     TCI_CUDA(h, cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, h->stream));

@@ -247,11 +247,11 @@ int libfail(tci_tci2 t, int code) {                     // a C-ABI call failed: 
 
 int reserve(tci_tci2 t, DevBuf& b, size_t doubles) {
     if (b.cap >= doubles && b.p) return TCI_OK;
-    if (b.p) { TCI2_CALL(t, tci_free(t->h, b.p)); b.p = nullptr; b.cap = 0; }
-    // cudaMalloc/cudaFree cost hundreds of microseconds and the sets grow over the first sweeps: start at 128 KB and double
-    size_t want = std::max<size_t>(2 * doubles, 16384);
+    if (b.p) { TCI2_CALL(t, tci_free_pooled(t->h, b.p)); b.p = nullptr; b.cap = 0; }
+    // stream-ordered pool (cudaMallocAsync): a regrow neither synchronises nor costs a cudaMalloc; start small and double
+    size_t want = std::max<size_t>(2 * doubles, 2048);
     void* p = nullptr;
-    TCI2_CALL(t, tci_malloc(t->h, &p, want * sizeof(double)));
+    TCI2_CALL(t, tci_malloc_pooled(t->h, &p, want * sizeof(double)));
     b.p = (double*)p; b.cap = want;
     return TCI_OK;
 }
@@ -894,7 +894,7 @@ int tci_optfirstpivot_f64(tci_handle h, tci_functor f, const int32_t* h_localdim
         dmax = std::max(dmax, (int)h_localdims[b]);
     }
     void* d_vals = nullptr;
-    int rc = tci_malloc(h, &d_vals, sizeof(double) * (size_t)dmax);
+    int rc = tci_malloc_pooled(h, &d_vals, sizeof(double) * (size_t)dmax);
     if (rc) return rc;
     std::vector<double> vals((size_t)dmax);
     std::vector<int32_t> pts((size_t)dmax * nsites);
@@ -921,7 +921,7 @@ int tci_optfirstpivot_f64(tci_handle h, tci_functor f, const int32_t* h_localdim
         }
         if (prev == valf) break;
     }
-    tci_free(h, d_vals);
+    tci_free_pooled(h, d_vals);
     return rc;
 }
 
@@ -934,8 +934,8 @@ int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tc
     t->I.resize(nsites); t->J.resize(nsites); t->T.resize(nsites);
     for (int b = 0; b < nsites; ++b) { t->I[b].len = b; t->J[b].len = nsites - b - 1; }
     t->bonderrors.assign((size_t)nsites - 1, 0.0);
-    if (tci_malloc(h, &t->acc, 64) != TCI_OK || tci_maxacc_set(h, t->acc, 0.0) != TCI_OK) {
-        if (t->acc) tci_free(h, t->acc);
+    if (tci_malloc_pooled(h, &t->acc, 64) != TCI_OK || tci_maxacc_set(h, t->acc, 0.0) != TCI_OK) {
+        if (t->acc) tci_free_pooled(h, t->acc);
         delete t;
         return TCI_ERR_NOMEM;
     }
@@ -946,9 +946,9 @@ int tci_tci2_create(tci_handle h, const int32_t* h_localdims, int nsites, tci_tc
 int tci_tci2_destroy(tci_tci2 t) {
     if (!t) return TCI_OK;
     DevBuf* bufs[] = {&t->pi, &t->L, &t->U, &t->pi1, &t->pmat, &t->pts};
-    for (DevBuf* b : bufs) if (b->p) tci_free(t->h, b->p);
-    for (auto& c : t->T) if (c.buf.p) tci_free(t->h, c.buf.p);
-    if (t->acc) tci_free(t->h, t->acc);
+    for (DevBuf* b : bufs) if (b->p) tci_free_pooled(t->h, b->p);
+    for (auto& c : t->T) if (c.buf.p) tci_free_pooled(t->h, c.buf.p);
+    if (t->acc) tci_free_pooled(t->h, t->acc);
     delete t;
     return TCI_OK;
 }

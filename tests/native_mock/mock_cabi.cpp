@@ -39,6 +39,8 @@ int64_t mock_ncalls(tci_handle h) { return h->ncalls; }
 const char* tci_last_error(tci_handle h) { return h ? h->err.c_str() : ""; }
 int tci_malloc(tci_handle, void** p, size_t bytes) { *p = std::malloc(bytes ? bytes : 1); return *p ? TCI_OK : TCI_ERR_NOMEM; }
 int tci_free(tci_handle, void* p) { std::free(p); return TCI_OK; }
+int tci_malloc_pooled(tci_handle h, void** p, size_t bytes) { return tci_malloc(h, p, bytes); }
+int tci_free_pooled(tci_handle h, void* p) { return tci_free(h, p); }
 int tci_memcpy_d2h(tci_handle, void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); return TCI_OK; }
 int tci_memcpy_d2d(tci_handle, void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); return TCI_OK; }
 
