@@ -189,6 +189,23 @@ int tci_batcheval_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, i
 int tci_batcheval_acc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
                           const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
                           double* d_out, int64_t stride_c, int64_t stride_j, void* d_acc16);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, same kernels and
+ * bit-identical results as tci_batcheval_acc_f64, but the call allocates NOTHING (no cudaMalloc / cudaFree / allocating
+ * library routine): the uploaded index tables and the folded functor states live in one file-scope `static __device__` array
+ * of TCI_BATCHEVAL_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.
+ *   limit:  256-aligned(4 (nleft nl + nright nr)) + 256-aligned(16 (nleft + nright)) <= TCI_BATCHEVAL_NOALLOC_SCRATCH_BYTES, else
+ *           TCI_ERR_INVALID with a message naming both numbers (tci_last_error); the per-pair states of the vectorised
+ *           assembly (24 bytes per (centre, right) pair) are used only when they fit too, else the plain assembly kernel runs.
+ *   d_acc16 must not be NULL (the running maximum is the caller's, see above); nothing in the array has to start at zero.
+ *   EVERY call on a device shares the array, which keeps the previous call's contents: two calls that overlap on the GPU
+ *   (different streams / handles on the same device) RACE.  Keep them on one stream or order them with events.
+ *   The first call on each device resolves the array's address (cudaGetSymbolAddress, with that device current); make that
+ *   call outside stream capture. */
+#define TCI_BATCHEVAL_NOALLOC_SCRATCH_BYTES (4u << 20)
+int tci_batcheval_noalloc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                              const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                              double* d_out, int64_t stride_c, int64_t stride_j, void* d_acc16);
 int tci_maxacc_set(tci_handle h, void* d_acc16, double value);
 int tci_maxacc_get(tci_handle h, const void* d_acc16, double* h_value);
 

@@ -21,6 +21,7 @@
 #include <nvrtc.h>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "functors.h"
@@ -505,6 +506,97 @@ int tci_ipc_close(tci_handle h, void* d_ptr) {
     TCI_CUDA(h, cudaSetDevice(h->device));
     TCI_CUDA(h, cudaIpcCloseMemHandle(d_ptr));
     return TCI_OK;
+}
+
+} // extern "C"
+
+// ---- allocation-free variant of the batch evaluation --------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  tci_batcheval_acc_f64's scratch — the uploaded
+// index tables and the folded per-row / per-pair functor states, normally carved from the handle's growing cudaMalloc'ed
+// workspaces — lives here in ONE file-scope device array of kNoAllocScratchBytes that every GPU loading the library holds until
+// exit.  Host code must not pass the symbol itself to a kernel (it is a host-side stand-in, not a device address): the
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr size_t kNoAllocScratchBytes = TCI_BATCHEVAL_NOALLOC_SCRATCH_BYTES;   // 4 MiB (include/tci_b200.h)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+static int noalloc_scratch_address(tci_handle h, unsigned char** out) {      // h->device is current (the caller set it)
+    static unsigned char* addr[64] = {};
+    static std::mutex mu;
+    if (h->device < 0 || h->device >= 64) return tci_fail(h, TCI_ERR_INVALID, "tci_batcheval_noalloc_f64: device ordinal %d out of range", h->device);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[h->device]) {
+        unsigned char* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return tci_fail(h, TCI_ERR_CUDA, "tci_batcheval_noalloc_f64: cudaGetSymbolAddress(scratch) on device %d: %s", h->device, cudaGetErrorString(e));
+        addr[h->device] = ptr;
+    }
+    *out = addr[h->device];
+    return TCI_OK;
+}
+
+extern "C" {
+
+int tci_batcheval_noalloc_f64(tci_handle h, tci_functor f, const int32_t* h_localdims, int nsites,
+                              const int32_t* h_left, int64_t nleft, int nl, const int32_t* h_right, int64_t nright, int nr,
+                              double* d_out, int64_t stride_c, int64_t stride_j, void* d_acc16) {
+    const char* who = "tci_batcheval_noalloc_f64";
+    if (!h) return TCI_ERR_INVALID;
+    if (!f || !h_localdims) return tci_fail(h, TCI_ERR_INVALID, "%s: NULL functor or localdims", who);
+    if (!d_acc16) return tci_fail(h, TCI_ERR_INVALID, "%s: NULL accumulator", who);
+    if (nsites < 1 || nsites > kMaxSites) return tci_fail(h, TCI_ERR_INVALID, "%s: nsites must be in 1..%d", who, kMaxSites);
+    const int ncs = nsites - nl - nr;
+    if (nl < 0 || nr < 0 || ncs < 0) return tci_fail(h, TCI_ERR_INVALID, "Invalid number of central indices");    // tensorci2.jl:492
+    if (ncs > 8) return tci_fail(h, TCI_ERR_INVALID, "%s: at most 8 free centre sites", who);
+    if (nleft < 0 || nright < 0) return tci_fail(h, TCI_ERR_INVALID, "%s: negative set size", who);
+    if (nleft == 0 || nright == 0) return TCI_OK;                               // batcheval.jl:140-142: empty result
+    if (f->kind == TCI_F_DENSE && f->ndims != nsites) return tci_fail(h, TCI_ERR_INVALID, "dense functor has %d dims, localdims has %d", f->ndims, nsites);
+    if ((nl > 0 && !h_left) || (nr > 0 && !h_right) || !d_out) return tci_fail(h, TCI_ERR_INVALID, "%s: NULL buffer", who);
+    TCI_CUDA(h, cudaSetDevice(h->device));
+    EvalShape sh;
+    sh.nl = nl; sh.nr = nr; sh.ncent_sites = ncs; sh.nleft = nleft; sh.nright = nright; sh.ncent = 1;
+    for (int x = 0; x < 8; ++x) sh.cdims[x] = 1;
+    for (int x = 0; x < ncs; ++x) { sh.cdims[x] = h_localdims[nl + x]; sh.ncent *= h_localdims[nl + x]; }
+    sh.stride_c = stride_c > 0 ? stride_c : nleft;
+    sh.stride_j = stride_j > 0 ? stride_j : sh.stride_c * sh.ncent;
+    sh.nouts = 1;
+    for (int p = 0; p < 8; ++p) sh.outs[p] = nullptr;
+    sh.outs[0] = d_out;
+    // carve the static array: [index tables | left + right states | per-pair states + offsets (only if they fit)]
+    auto al = [](double x) { return (double)(((unsigned long long)x + 255ull) & ~255ull); };    // sizes are checked in double: no overflow
+    const double nli = (double)nleft * nl, nri = (double)nright * nr;
+    const double ints = al((nli + nri) * sizeof(int)), st_bytes = al(16.0 * ((double)nleft + (double)nright));
+    if ((double)nleft > 1e12 || (double)nright > 1e12 || ints + st_bytes > (double)kNoAllocScratchBytes)
+        return tci_fail(h, TCI_ERR_INVALID, "%s: %lld + %lld index rows need %.0f bytes of scratch, the static array holds %zu "
+                        "(use tci_batcheval_acc_f64, which allocates)", who, (long long)nleft, (long long)nright, ints + st_bytes, kNoAllocScratchBytes);
+    const double npair = (double)sh.ncent * (double)nright;
+    const bool pairs = ints + st_bytes + 24.0 * npair <= (double)kNoAllocScratchBytes;   // else the kernel that folds the centre digits itself
+    unsigned char* base = nullptr;
+    int rc = noalloc_scratch_address(h, &base);
+    if (rc) return rc;
+    EvalBuffers b;
+    b.d_left = (int*)base; b.d_right = b.d_left + (size_t)nli;
+    b.Ls = base + (size_t)ints; b.Rs = (char*)b.Ls + 16 * (size_t)nleft;
+    b.Cs = pairs ? base + (size_t)ints + (size_t)st_bytes : nullptr;
+    b.Off = pairs ? (long long*)((char*)b.Cs + 16 * (size_t)npair) : nullptr;
+    b.maxbits = (unsigned long long*)d_acc16; b.nanflag = (int*)(b.maxbits + 1);
+    // Nothing in the array has to start at zero: the tables are uploaded and every state / offset is written by the fold kernel
+    // before the assembly reads it; the running maximum lives in the CALLER's accumulator.  Pageable sources are staged by
+    // cudaMemcpyAsync before it returns.
+    if (nli > 0) TCI_CUDA(h, cudaMemcpyAsync(b.d_left, h_left, (size_t)nli * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    if (nri > 0) TCI_CUDA(h, cudaMemcpyAsync(b.d_right, h_right, (size_t)nri * sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    switch (f->kind) {
+    case TCI_F_LORENTZ: return f->p[0] == 1.0 ? run_builtin(h, LorentzUnitF{}, sh, nsites, b) : run_builtin(h, LorentzF{f->p[0]}, sh, nsites, b);
+    case TCI_F_SUM: return run_builtin(h, SumF{f->p[0]}, sh, nsites, b);
+    case TCI_F_QEXPSIN: return run_builtin(h, QuanticsF<TCI_F_QEXPSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b);
+    case TCI_F_QEXPPLUSSIN: return run_builtin(h, QuanticsF<TCI_F_QEXPPLUSSIN>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b);
+    case TCI_F_QEXP2: return run_builtin(h, QuanticsF<TCI_F_QEXP2>{f->p[0], f->p[1], f->p[2]}, sh, nsites, b);
+    case TCI_F_HASH: return run_builtin(h, HashF{f->p[0], f->p[1]}, sh, nsites, b);
+    case TCI_F_DENSE: return run_builtin(h, DenseF{f->d_table, f->d_strides}, sh, nsites, b);
+    case TCI_F_USER: return run_user(h, f, sh, b);
+    default: return tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
+    }
 }
 
 } // extern "C"
