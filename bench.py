@@ -282,10 +282,85 @@ def sweep_multi_gpu(T, torch, dist, h, comm, world, rank):
     flag = torch.tensor([1.0 if same else 0.0], dtype=torch.float64, device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     ev = int(ref.stats["nevals"])
-    return {"C3H": {"config": "full-rank hash functor, localdims=fill(20,10), maxbonddim=256, maxiter=2; sequential bond order, columns of "
+    extra = {}
+    try:
+        extra.update(_k1_sharded(T, torch, dist, h, comm, world, dev))
+        extra.update(_oddeven_sweep(T, torch, dist, f, ld, kw, comm, dev, timed, t1))
+    except Exception as ex:                                          # never lose the headline to an auxiliary measurement
+        extra["partitions_error"] = f"{type(ex).__name__}: {ex}"
+    return {**extra,
+            "C3H": {"config": "full-rank hash functor, localdims=fill(20,10), maxbonddim=256, maxiter=2; sequential bond order, columns of "
                               "every Pi >= 2^20 entries spread over the ranks",
                     "one_gpu_wall_ms": 1e3 * t1, "wall_ms": 1e3 * tn, "speedup": t1 / tn, "evals": ev, "evals_per_s": ev / tn,
                     "sharded_bonds": int(sh.stats.get("nsharded", 0)), "pivot_sets_identical_to_one_gpu": bool(flag.item() == 1.0)}}
+
+
+def _k1_sharded(T, torch, dist, h, comm, world, dev):
+    """north_star partition 1: ONE Pi fill of the C3 worst-case shape (5120 x 5120, 26.2 M evaluations, 210 MB) with
+    the evaluations split over the ranks and every rank's block stored straight into every peer's copy of Pi by the evaluation
+    kernel (fused compute + all-gather over peer memory); against the same fill done entirely on every rank.  Device-side wall
+    time, max over ranks; the assembled matrix must equal the local one bit for bit on every rank."""
+    ld = [20] * 10
+    rng = np.random.default_rng(0)
+    nI = nJ = 5120
+    left = rng.integers(1, 21, size=(nI, 5)).astype(np.int32)
+    right = rng.integers(1, 21, size=(nJ, 5)).astype(np.int32)
+    f = T.HashFunction(ld, 1.0, 1.0, handle=h)
+    buf = torch.empty(nI * nJ, dtype=torch.float64, device=dev)
+
+    def timed(fn, reps=5):
+        fn(); fn()
+        ts = []
+        for _ in range(reps):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        t = torch.tensor([min(ts)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    t_local = timed(lambda: f.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
+    ga = T.ShardedBatchEvaluator(f, comm)
+    t_gather = timed(lambda: ga.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
+    fu = T.ShardedBatchEvaluator(f, comm, fused=True)
+
+    def fused():
+        m = fu.alloc_matrix(nI, nJ, 16)
+        o = m.buf if m is not None else buf
+        fu.evaluate_batch(left, right, 0, out=o, stride_c=nI, stride_j=nI, maxabs=0.0)
+        return o
+    t_fused = timed(fused)
+    ref = f.evaluate_batch(left, right, 0, out=torch.empty_like(buf), stride_c=nI, stride_j=nI)[0]
+    o = fused()
+    torch.cuda.synchronize(); dist.barrier()
+    same = torch.tensor([1.0 if torch.equal(o.reshape(-1)[: nI * nJ], ref.reshape(-1)[: nI * nJ]) else 0.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    return {"K1_sharded": {"config": "Pi fill 5120 x 5120 (C3 worst-case bond), full-rank hash functor, columns of Pi over the ranks",
+                           "note": "the hash functor costs ~5 ns per 1000 evaluations per SM: evaluating everything on every rank is cheaper than "
+                                   "moving 8 B per value over NVLink; the split pays for arithmetic-heavy functors (benchmarks/multigpu_bench.py, "
+                                   "heavy_plugin) and, in the sweep, because the sharded rrLU wants column blocks anyway",
+                           "evals": nI * nJ, "local_ms": 1e3 * t_local, "sharded_nccl_allgather_ms": 1e3 * t_gather,
+                           "sharded_fused_peer_store_ms": 1e3 * t_fused, "evals_per_s": nI * nJ / t_fused,
+                           "nvlink_GBps_per_rank": 8 * nI * nJ * (world - 1) / world / t_fused / 1e9,
+                           "identical_to_local_on_every_rank": bool(same.item() == 1.0)}}
+
+
+def _oddeven_sweep(T, torch, dist, f, ld, kw, comm, dev, timed, t_seq):
+    """north_star partition 2: the parallel-bond sweep — bonds of one parity are independent, so they are dealt to
+    the ranks and the new pivot sets exchanged (NCCL) after each parity.  The schedule differs from the reference's sequential
+    one by construction (tests compare it with the oracle's odd/even schedule); here: index sets of the N-rank run must equal
+    the same schedule run on one GPU."""
+    t_oe1, one = timed(bondorder="oddeven")
+    t_oen, par = timed(bondorder="oddeven", comm=comm)
+    same = all(np.array_equal(a, b) for a, b in zip(one.Iset, par.Iset)) and all(np.array_equal(a, b) for a, b in zip(one.Jset, par.Jset))
+    flag = torch.tensor([1.0 if same else 0.0], dtype=torch.float64, device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ev = int(par.stats["nevals"])
+    return {"C3H_parallel_bonds": {"config": "the C3H sweep with bondorder='oddeven': bonds of one parity spread over the ranks, pivot sets exchanged per parity",
+                                   "sequential_one_gpu_wall_ms": 1e3 * t_seq, "oddeven_one_gpu_wall_ms": 1e3 * t_oe1, "wall_ms": 1e3 * t_oen,
+                                   "speedup_vs_sequential": t_seq / t_oen, "evals": ev, "evals_per_s": ev / t_oen,
+                                   "pivot_sets_identical_to_one_gpu_same_schedule": bool(flag.item() == 1.0)}}
 
 
 # ---- the rrLU headline -----------------------------------------------------------------------------------------------

@@ -207,6 +207,24 @@ __device__ __forceinline__ long long abs2_key(double v) {                       
     return __double_as_longlong(fmax(__dmul_rn(v, v), -1.0));                    // fmax(NaN, x) = x
 }
 
+// Candidate update for one element, branch-free (predicates and selects only; written in PTX because the compiler turns the
+// C++ form into three branches per element): the element counts iff apos >= np (apos = its smaller position) and q = v^2 is
+// not NaN; then (key = bits(q), pos) replaces (bkey, bpos) iff key > bkey, or key == bkey and pos < bpos — the reference's
+// scan order (matrixlu.jl:46-87: largest abs2, then smallest column, then smallest row, in swapped coordinates).
+__device__ __forceinline__ void take_elem(long long& bkey, unsigned& bpos, double q, int apos, int np, unsigned pos) {
+    asm("{\n\t.reg .pred ok, eq, b;\n\t.reg .b64 k;\n\t"
+        "setp.ge.s32 ok, %3, %4;\n\t"
+        "setp.eq.and.f64 ok, %2, %2, ok;\n\t"
+        "mov.b64 k, %2;\n\t"
+        "selp.b64 k, k, 0x8000000000000000, ok;\n\t"
+        "setp.eq.s64 eq, k, %0;\n\t"
+        "setp.lt.and.u32 b, %5, %1, eq;\n\t"
+        "setp.gt.or.s64 b, k, %0, b;\n\t"
+        "selp.b64 %0, k, %0, b;\n\t"
+        "selp.b32 %1, %5, %1, b;\n\t}"
+        : "+l"(bkey), "+r"(bpos) : "d"(q), "r"(apos), "r"(np), "r"(pos));
+}
+
 // keep (bk, bi, bj) = the first element in the reference's scan order among those seen: larger key, then smaller position
 #define TCI_DS_TAKE(k, i, j, bk, bi, bj)                                                                                 \
     if ((k) > (bk)) { (bk) = (k); (bi) = (i); (bj) = (j); }                                                             \
@@ -239,8 +257,11 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
     double maxerror = 0.0, error = nan("");
     long long tc0 = clock64();
 #define TCI_DS_TICK(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tc0; tc0 = t1__; } }
+    // this thread's candidate as (key, position): the searches below track the position directly — one branch-free
+    // lexicographic compare per element instead of a compare with a divergent tie branch that re-reads the position maps
+    unsigned bpos = bkey >= 0 ? ((unsigned)c.colpos[bj] << 16) | (unsigned)c.rowpos[bi] : 0xffffffffu;
     for (;;) {
-        unsigned bpos = bkey >= 0 ? ((unsigned)c.colpos[bj] << 16) | (unsigned)c.rowpos[bi] : 0xffffffffu;
+        if (bkey < 0) bpos = 0xffffffffu;
         warp_argmax(bkey, bpos);
         KP* sw = s_w[np & 1];
         if (lane == 0) { sw[warp].key = bkey; sw[warp].pos = bpos; }
@@ -312,33 +333,28 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
         TCI_DS_TICK(2)
         np = k + 1;
         if (np >= rcap) break;                                                      // :356
-        bkey = kNoKey; bi = 0; bj = 0;
-        // :316-320 + the next search: loads first, then arithmetic, then the candidate selection
+        bkey = kNoKey; bpos = 0xffffffffu;
+        // :316-320 + the next search (take_elem): loads first, then arithmetic, then the candidate selection
         if (own.flat) {
 #pragma unroll
             for (int q0 = 0; q0 < kFlat; q0 += 2) {
                 if (q0 < own.nslots) {
-                    int rp[2], cp[2], ei[2], ej[2]; double av[2], xv[2], yv[2]; double* ap[2]; bool ok[2];
+                    int rp[2], cp[2]; double av[2], xv[2], yv[2]; double* ap[2]; bool ok[2];
 #pragma unroll
                     for (int u = 0; u < 2; ++u) {
                         const int e = own.e[q0 + u];
                         ok[u] = e >= 0;
-                        const int ee = ok[u] ? e : 0, jl = ee >> 16;
-                        ei[u] = ee & 0xffff; ej[u] = crank + CS * jl;
-                        ap[u] = A + (size_t)jl * lds + ei[u];
-                        rp[u] = c.rowpos[ei[u]]; cp[u] = c.colpos[ej[u]]; av[u] = *ap[u]; xv[u] = c.xs[ei[u]]; yv[u] = c.ys[jl];
+                        const int ee = ok[u] ? e : 0, jl = ee >> 16, ei = ee & 0xffff;
+                        ap[u] = A + (size_t)jl * lds + ei;
+                        rp[u] = c.rowpos[ei]; cp[u] = c.colpos[crank + CS * jl]; av[u] = *ap[u]; xv[u] = c.xs[ei]; yv[u] = c.ys[jl];
                     }
-                    long long kq[2];
 #pragma unroll
                     for (int u = 0; u < 2; ++u) {
-                        const bool act = ok[u] && rp[u] >= np && cp[u] >= np;
+                        const int apos = ok[u] ? min(rp[u], cp[u]) : -1;
                         const double v = __dsub_rn(av[u], __dmul_rn(xv[u], yv[u]));
-                        if (act) *ap[u] = v;
-                        const long long k0 = abs2_key(v);
-                        kq[u] = act ? k0 : kNoKey;
+                        if (apos >= np) *ap[u] = v;
+                        take_elem(bkey, bpos, __dmul_rn(v, v), apos, np, ((unsigned)cp[u] << 16) | (unsigned)rp[u]);
                     }
-#pragma unroll
-                    for (int u = 0; u < 2; ++u) TCI_DS_TAKE(kq[u], ei[u], ej[u], bkey, bi, bj)
                 }
             }
         } else {
@@ -353,24 +369,20 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
                 for (int u = 0; u < 4; ++u) { rp[u] = c.rowpos[i0 + 32 * u]; xv[u] = c.xs[i0 + 32 * u]; }
                 if (__any_sync(FULL, rp[0] >= np || rp[1] >= np || rp[2] >= np || rp[3] >= np)) {
                     for (int jl = jl0; jl < own.nown; jl += wpg) {
-                        const int j = crank + CS * jl;
-                        if (c.colpos[j] < np) continue;
+                        const int cpj = c.colpos[crank + CS * jl];
+                        if (cpj < np) continue;
+                        const unsigned cp16 = (unsigned)cpj << 16;
                         const double y = c.ys[jl];
                         double* col = A + (size_t)jl * lds + i0;
                         double av[4];
 #pragma unroll
                         for (int u = 0; u < 4; ++u) av[u] = col[32 * u];
-                        long long kq[4];
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            const bool act = rp[u] >= np;                           // padding rows carry position -1
                             const double v = __dsub_rn(av[u], __dmul_rn(xv[u], y));
-                            if (act) col[32 * u] = v;
-                            const long long k0 = abs2_key(v);
-                            kq[u] = act ? k0 : kNoKey;
+                            if (rp[u] >= np) col[32 * u] = v;                       // padding rows carry position -1
+                            take_elem(bkey, bpos, __dmul_rn(v, v), rp[u], np, cp16 | (unsigned)rp[u]);
                         }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) TCI_DS_TAKE(kq[u], i0 + 32 * u, j, bkey, bi, bj)
                     }
                 }
             }
