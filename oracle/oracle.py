@@ -317,6 +317,11 @@ class TCI2:
         _check(lib().orc_tci_sweep1site(self.h, int(direction == "forward"), C.c_double(reltol), C.c_double(abstol),
                                         C.c_int64(int(maxbonddim)), int(updatetensors)))
 
+    def sweep0site(self, b, reltol=1e-14, abstol=0.0):                       # sweep0site! tensorci2.jl:559-587, b 1-based
+        _check(lib().orc_tci_sweep0site(self.h, int(b), C.c_double(reltol), C.c_double(abstol)))
+
+    rmbadpivots = sweep0site                                                 # tensorci2.jl:589
+
     def makecanonical(self, reltol=1e-14, abstol=0.0, maxbonddim=INT64_MAX):
         _check(lib().orc_tci_makecanonical(self.h, C.c_double(reltol), C.c_double(abstol), C.c_int64(int(maxbonddim))))
 

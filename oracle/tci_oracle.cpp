@@ -643,6 +643,7 @@ struct TCI2 {
     void fillsitetensors(const Func& f) { for (int b = 0; b < n(); ++b) setsitetensor_f(f, b); }   // globalsearch.jl:202-208
     int sweep1site(const Func& f, bool forward, double reltol, double abstol, int64_t maxbonddim, bool updatetensors);
     int makecanonical(const Func& f, double reltol, double abstol, int64_t maxbonddim);
+    int sweep0site(const Func& f, int b, double reltol, double abstol);
     int sweep2site(const Func& f, int niter, int iter1, double abstol, int64_t maxbonddim, int sweepstrategy,
                    bool strictlynested, bool fillsite);
     double evaluate(const MultiIndex& idx) const;
@@ -792,6 +793,26 @@ int TCI2::sweep1site(const Func& f, bool forward, double reltol, double abstol, 
         const int64_t cols = forward ? localdims[last] : (int64_t)Jset[0].size();
         setsitetensor(last, fillmatrix(f, Iset[last], Jset[last], 1, rows, cols));
     }
+    return 0;
+}
+
+int TCI2::sweep0site(const Func& f, int b, double reltol, double abstol) {       // sweep0site! / rmbadpivots! :559-589 (b 0-based)
+    invalidatesitetensors();
+    const int64_t r0 = (int64_t)Iset[b + 1].size(), c0 = (int64_t)Jset[b].size();
+    Mat P = fillmatrix(f, Iset[b + 1], Jset[b], 0, r0, c0);                     // :566-568
+    updatemaxsample(P.a);                                                       // :569
+    RRLU lu;
+    int st = rrlu_inplace(P, lu, std::numeric_limits<int64_t>::max(), reltol, abstol, true);   // MatrixLUCI(P; reltol, abstol, leftorthogonal=true) :572-577
+    if (st) return st;
+    int64_t ndiag = 0;                                                          // :580 (a count over the whole diagonal, not a prefix)
+    for (int64_t i = 0; i < lu.npivot; ++i) {
+        const double u = lu.U(i, i), u0 = lu.U(0, 0);
+        if (std::fabs(u) > abstol && std::fabs(u / u0) > reltol) ++ndiag;
+    }
+    IndexList newI, newJ;
+    for (int64_t k = 0; k < ndiag; ++k) newI.push_back(Iset[b + 1][lu.rowperm[k] - 1]);      // :583
+    for (int64_t k = 0; k < ndiag; ++k) newJ.push_back(Jset[b][lu.colperm[k] - 1]);          // :584
+    Iset[b + 1] = newI; Jset[b] = newJ;
     return 0;
 }
 
@@ -1179,6 +1200,12 @@ int orc_tci_sweep2site(void* h_, int niter, int iter1, double abstol, int64_t ma
 int orc_tci_sweep1site(void* h_, int forward, double reltol, double abstol, int64_t maxbonddim, int updatetensors) {
     ORC_TRY OrcTCI* h = (OrcTCI*)h_;
     return h->tci.sweep1site(*h->f, forward != 0, reltol, abstol, maxbonddim, updatetensors != 0);
+    ORC_CATCH(-10)
+}
+int orc_tci_sweep0site(void* h_, int b, double reltol, double abstol) {
+    ORC_TRY OrcTCI* h = (OrcTCI*)h_;
+    if (b < 1 || b >= h->tci.n()) return -11;
+    return h->tci.sweep0site(*h->f, b - 1, reltol, abstol);
     ORC_CATCH(-10)
 }
 int orc_tci_makecanonical(void* h_, double reltol, double abstol, int64_t maxbonddim) {

@@ -367,6 +367,7 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
                 int rp[4]; double xv[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) { rp[u] = c.rowpos[i0 + 32 * u]; xv[u] = c.xs[i0 + 32 * u]; }
+                TCI_DS_TICK(14)
                 if (__any_sync(FULL, rp[0] >= np || rp[1] >= np || rp[2] >= np || rp[3] >= np)) {
                     for (int jl = jl0; jl < own.nown; jl += wpg) {
                         const int cpj = c.colpos[crank + CS * jl];
@@ -1174,9 +1175,9 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
         long long pcs[16];
         TCI_CUDA(h, cudaMemcpy(pcs, P.prof, sizeof pcs, cudaMemcpyDeviceToHost));
         static const char* names[16] = {"lu.reduce", "lu.exchange", "lu.stage", "lu.update", "extras", "states", "fill", "lu+nan", "output", "prologue",
-                                        "pivots", "bonds", "x.publish", "x.clustersync", "-", "-"};
+                                        "pivots", "bonds", "x.publish", "x.clustersync", "upd.preamble", "-"};
         fprintf(stderr, "dsweep prof (cycles):");
-        for (int q = 0; q < 14; ++q) fprintf(stderr, " %s=%lld", names[q], pcs[q]);
+        for (int q = 0; q < 15; ++q) fprintf(stderr, " %s=%lld", names[q], pcs[q]);
         fprintf(stderr, "\n");
     }
     return rc;

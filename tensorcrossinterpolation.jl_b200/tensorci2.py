@@ -455,6 +455,24 @@ class TensorCI2(AbstractTensorTrain):
             cols = self.localdims[last] if fwd else self.Jset[0].shape[0]
             self._set_core(last, self._fill(f, self.Iset[last], self.Jset[last], 1, rows, cols))
 
+    def sweep0site(self, f, b, reltol=1e-14, abstol=0.0):
+        """sweep0site! (tensorci2.jl:559-587): remove bad pivots at bond b (1-based) — fill the pivot matrix
+        P = f(Iset[b+1], Jset[b]), factorise it (MatrixLUCI, leftorthogonal), keep as many leading pivots as there are diagonal
+        entries of U above both thresholds (:580 counts over the whole diagonal)."""
+        f = makebatchevaluatable(f, self.localdims, self.handle)
+        if not 1 <= b < len(self):
+            raise TCIError(_lib.TCI_ERR_INVALID, f"sweep0site!: bond {b} out of range 1:{len(self) - 1}")
+        self.invalidatesitetensors()
+        I, J = self.Iset[b], self.Jset[b - 1]
+        P = self._fill(f, I, J, 0, I.shape[0], J.shape[0], slot=0)
+        luci = MatrixLUCI(P, reltol=reltol, abstol=abstol, leftorthogonal=True, handle=self.handle)
+        diag = np.asarray(luci.pivoterrors(), dtype=np.float64)[:luci.npivots()]       # |U[i, i]| (leftorthogonal: U carries the pivots)
+        ndiag = int(np.count_nonzero((diag > abstol) & (diag / diag[0] > reltol))) if diag.size else 0
+        self.Iset[b] = I[luci.rowindices()[:ndiag] - 1]
+        self.Jset[b - 1] = J[luci.colindices()[:ndiag] - 1]
+
+    rmbadpivots = sweep0site                                                        # tensorci2.jl:589
+
     def makecanonical(self, f, reltol=1e-14, abstol=0.0, maxbonddim=INT_MAX):      # tensorci2.jl:738-749
         self.sweep1site(f, "forward", reltol=0.0, abstol=0.0, maxbonddim=INT_MAX, updatetensors=False)
         self.sweep1site(f, "backward", reltol=reltol, abstol=abstol, maxbonddim=maxbonddim, updatetensors=False)

@@ -164,3 +164,26 @@ def test_reconstruct_from_sets(tci):                    # test/test_tensorci2.jl
     t2 = tci.TensorCI2([10, 10], f, Iset=t.Iset, Jset=t.Jset)
     assert t2.maxsamplevalue == t.maxsamplevalue or t2.maxsamplevalue <= t.maxsamplevalue
     assert all(np.array_equal(a, b) for a, b in zip(t2.Iset, t.Iset))
+
+
+def test_sweep0site_matches_oracle(tci):                # sweep0site! / rmbadpivots! tensorci2.jl:559-589
+    """Same over-resolved state in the product and the oracle (index sets identical after crossinterpolate2), then bad-pivot
+    removal bond by bond: the kept index sets must stay identical."""
+    ld = [6] * 5
+    g = O.Func(O.F_LORENTZ, [1.0])
+    o, _, _ = O.crossinterpolate2(g, ld, tolerance=1e-12, maxiter=8)
+    f = tci.LorentzFunction(ld)
+    t, _, _ = tci.crossinterpolate2(f, ld, tolerance=1e-12, maxiter=8, nsearchglobalpivot=0, engine="python")
+    for b in range(1, 6):
+        np.testing.assert_array_equal(t.Iset[b - 1], o.Iset(b))
+        np.testing.assert_array_equal(t.Jset[b - 1], o.Jset(b))
+    before = list(t.linkdims())
+    for b in range(1, 5):
+        o.sweep0site(b, reltol=1e-6)
+        (t.sweep0site if b % 2 else t.rmbadpivots)(f, b, reltol=1e-6)
+        np.testing.assert_array_equal(t.Iset[b], o.Iset(b + 1))
+        np.testing.assert_array_equal(t.Jset[b - 1], o.Jset(b))
+    assert sum(t.linkdims()) < sum(before)
+    assert t.maxsamplevalue == o.maxsamplevalue
+    with pytest.raises(tci.TCIError):
+        t.sweep0site(f, 5)

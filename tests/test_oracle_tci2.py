@@ -232,3 +232,26 @@ def test_insert_global_pivots_oracle():                 # test/test_tensorci2.jl
     tci.addglobalpivots2sitesweep([r], tolerance=abstol, normalizeerror=False, maxbonddim=1000)
     assert tci.evaluate(r) == pytest.approx(1.0, rel=1e-12)
     assert tci.evaluate([1] * R) == pytest.approx(1.0, rel=1e-12)
+
+
+def test_sweep0site_removes_bad_pivots():               # sweep0site! / rmbadpivots! tensorci2.jl:559-589
+    """An over-resolved TCI (tolerance 1e-12) has pivot matrices with diagonal entries down to 1e-12 of the first; sweep0site!
+    with reltol 1e-6 keeps exactly the leading pivots of rrlu(P) whose |U_ii / U_11| exceeds it.  Checked against the same
+    steps written with the oracle's rrlu on a P evaluated point by point."""
+    ld = [6] * 5
+    g = O.Func(O.F_LORENTZ, [1.0])
+    o, _, _ = O.crossinterpolate2(g, ld, tolerance=1e-12, maxiter=8)
+    before = o.linkdims()
+    for b in range(1, 5):
+        I, J = o.Iset(b + 1), o.Jset(b)
+        P = np.array([[g(list(i) + list(j)) for j in J] for i in I])
+        lu = O.rrlu(P, reltol=1e-6)
+        d = np.abs(np.diag(lu.U)[:lu.npivot])
+        nd = int(np.sum((d > 0.0) & (d / d[0] > 1e-6)))
+        o.rmbadpivots(b, reltol=1e-6)
+        np.testing.assert_array_equal(o.Iset(b + 1), I[lu.rowindices()[:nd] - 1])
+        np.testing.assert_array_equal(o.Jset(b), J[lu.colindices()[:nd] - 1])
+    after = o.linkdims()
+    assert all(a <= b for a, b in zip(after, before)) and sum(after) < sum(before)
+    with pytest.raises(O.OracleError):
+        o.sweep0site(5)
