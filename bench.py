@@ -356,7 +356,9 @@ def _oddeven_sweep(T, torch, dist, f, ld, kw, comm, dev, timed, t_seq):
     same = all(np.array_equal(a, b) for a, b in zip(one.Iset, par.Iset)) and all(np.array_equal(a, b) for a, b in zip(one.Jset, par.Jset))
     flag = torch.tensor([1.0 if same else 0.0], dtype=torch.float64, device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    ev = int(par.stats["nevals"])
+    evt = torch.tensor([float(par.stats["nevals"])], dtype=torch.float64, device=dev)      # every rank evaluates only its own bonds
+    dist.all_reduce(evt, op=dist.ReduceOp.SUM)
+    ev = int(evt.item())
     return {"C3H_parallel_bonds": {"config": "the C3H sweep with bondorder='oddeven': bonds of one parity spread over the ranks, pivot sets exchanged per parity",
                                    "sequential_one_gpu_wall_ms": 1e3 * t_seq, "oddeven_one_gpu_wall_ms": 1e3 * t_oe1, "wall_ms": 1e3 * t_oen,
                                    "speedup_vs_sequential": t_seq / t_oen, "evals": ev, "evals_per_s": ev / t_oen,
