@@ -39,6 +39,7 @@
 #include "functors.h"
 #include "solve_small.h"
 #include <cooperative_groups.h>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <vector>
@@ -1143,6 +1144,9 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     if (s0 < 0 || s1 > N - 1 || s0 > s1) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: malformed input arena");
     if (out_cap_words < kHdr + (int64_t)kStepRec * (s1 - s0)) return tci_fail(h, TCI_ERR_INVALID, "tci_dsweep_halfsweep_f64: output arena too small");
     TCI_CUDA(h, cudaSetDevice(h->device));
+    static const bool hostprof = getenv("TCI_DSWEEP_HOSTPROF") != nullptr;          // diagnostics: host wall time per stage of this call
+    auto now = [] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double th0 = hostprof ? now() : 0.0;
     const SweepShape sh = predict(h_in);
     const int mcap = ((std::max(sh.maxm, 1) * 2 + 63) / 64) * 64;                  // room for the moving set to grow
     const size_t in_b = ((size_t)in_words * 4 + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
@@ -1156,7 +1160,9 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     const bool prof = getenv("TCI_DSWEEP_PROF") != nullptr;
     P.prof = prof ? (long long*)(base + in_b + out_b + xs_b) : nullptr;
     P.st_g = base + in_b + out_b + xs_b + 512; P.hs_g = (unsigned long long*)(base + in_b + out_b + xs_b + 512 + st_b);
+    const double th1 = hostprof ? now() : 0.0;
     TCI_CUDA(h, cudaMemcpyAsync(base, h_in, (size_t)in_words * 4, cudaMemcpyHostToDevice, h->stream));
+    const double th2 = hostprof ? now() : 0.0;
     const char* fe = getenv("TCI_DSWEEP_CLUSTER");         // tests: 1 / 8 force the single-CTA / cluster variant
     const int force_cs = fe ? atoi(fe) : 0;
     switch (f->kind) {
@@ -1170,7 +1176,13 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     default: rc = tci_fail(h, TCI_ERR_INVALID, "unknown functor kind %d", f->kind);
     }
     if (rc) return rc;
+    const double th3 = hostprof ? now() : 0.0;
+    if (hostprof) cudaStreamSynchronize(h->stream);
+    const double th4 = hostprof ? now() : 0.0;
     rc = read_out(h, P.out, h_out, out_cap_words, h_used_words, "tci_dsweep_halfsweep_f64");
+    if (hostprof)
+        fprintf(stderr, "dsweep host (us): check+reserve=%.1f h2d(%lld words)=%.1f launch=%.1f kernel_wait=%.1f read_out(%lld words)=%.1f\n", th1 - th0,
+                (long long)in_words, th2 - th1, th3 - th2, th4 - th3, h_used_words ? (long long)*h_used_words : -1LL, now() - th4);
     if (rc == TCI_OK && prof) {
         long long pcs[16];
         TCI_CUDA(h, cudaMemcpy(pcs, P.prof, sizeof pcs, cudaMemcpyDeviceToHost));

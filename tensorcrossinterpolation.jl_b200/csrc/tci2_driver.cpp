@@ -14,6 +14,7 @@
 // Matrices are column-major FP64 in device memory.  Bonds/sites in the C entry points are 1-based like the reference.
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -627,6 +628,8 @@ int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t
         const double t0 = now_s();
         std::vector<int32_t>& a = t->arena_in;
         pack_sets(t, a, fwd, s, N - 1, maxbonddim, extraI, extraJ);
+        static const bool hostprof = getenv("TCI_DSWEEP_HOSTPROF") != nullptr;
+        const double tp1 = now_s();
         // output capacity: every bond may return up to rcap rows of N ints twice; rcap is bounded by what fits the kernel (512)
         int64_t rcap = 512;
         if (maxbonddim > 0 && maxbonddim < rcap) rcap = maxbonddim;
@@ -634,6 +637,7 @@ int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t
         t->arena_out.resize((size_t)cap);
         int64_t used = 0;
         TCI2_CALL(t, tci_dsweep_halfsweep_f64(t->h, f, a.data(), (int64_t)a.size(), 1e-14, abstol, t->acc, t->arena_out.data(), cap, &used));
+        const double tp2 = now_s();
         const int32_t* o = t->arena_out.data();
         const int status = o[0], next = o[1];
         t->ndevsweeps++;
@@ -651,6 +655,7 @@ int device_halfsweep(tci_tci2 t, tci_functor f, bool fwd, double abstol, int64_t
             t->nbondupdates++; t->ndevbonds++;
         }
         t->t_lu += now_s() - t0;
+        if (hostprof) fprintf(stderr, "driver halfsweep (us): pack=%.1f call=%.1f unpack=%.1f\n", 1e6 * (tp1 - t0), 1e6 * (tp2 - tp1), 1e6 * (now_s() - tp2));
         if (status == 2) return fail(t, TCI_ERR_NAN_L, "lu.L contains NaNs");
         if (status == 3) return fail(t, TCI_ERR_NAN_U, "lu.U contains NaNs");
         s = next;
