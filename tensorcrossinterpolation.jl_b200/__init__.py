@@ -16,7 +16,7 @@ from .batcheval import (BatchEvaluator, BuiltinFunction, LorentzFunction, SumFun
 from .tensortrain import TensorTrain, AbstractTensorTrain, DeviceCore, tensortrain, compress, _factorize, add, subtract, norm2, norm, _addtttensor                       # noqa: F401
 from .tensorci2 import (TensorCI2, crossinterpolate2, optimize, convergencecriterion, kronecker_left,      # noqa: F401
                         kronecker_right, DefaultGlobalPivotFinder, GlobalPivotSearchInput, forwardsweep,
-                        HostFunctionAdapter, makebatchevaluatable, optfirstpivot, ENGINES)
+                        HostFunctionAdapter, ThreadedBatchEvaluator, makebatchevaluatable, optfirstpivot, ENGINES)
 from .tensor import DTensor, _contract                                                                  # noqa: F401
 from .contraction import (Contraction, ElementwiseMap, contract, contract_naive, contract_zipup, contract_TCI)   # noqa: F401
 from .parallel import Comm, ShardedBatchEvaluator, partition, bond_passes, MailboxPool, gather_sharded_U                               # noqa: F401

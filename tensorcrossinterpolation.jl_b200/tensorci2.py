@@ -93,6 +93,15 @@ class HostFunctionAdapter(BatchEvaluator):
         super().__init__(localdims, handle)
         self.f = f
 
+    def _host_values(self, lt, rt, cents, vals):
+        """The triple loop of _batchevaluate_dispatch (batcheval.jl:157-171): one call of the user's function per element."""
+        nleft, nright = lt.shape[0], rt.shape[0]
+        for j in range(nright):
+            for c, cidx in enumerate(cents):
+                mid = list(reversed(cidx))
+                for i in range(nleft):
+                    vals[j, c, i] = self.f(list(lt[i]) + mid + list(rt[j]))
+
     def evaluate_batch(self, left, right, M, out=None, stride_c=0, stride_j=0, maxabs=None):
         import itertools
         import torch
@@ -106,11 +115,7 @@ class HostFunctionAdapter(BatchEvaluator):
         ncent = int(np.prod(cd)) if cd else 1
         vals = np.empty((nright, ncent, nleft))
         cents = list(itertools.product(*[range(1, d + 1) for d in reversed(cd)]))
-        for j in range(nright):
-            for c, cidx in enumerate(cents):
-                mid = list(reversed(cidx))
-                for i in range(nleft):
-                    vals[j, c, i] = self.f(list(lt[i]) + mid + list(rt[j]))
+        self._host_values(lt, rt, cents, vals)
         sc = stride_c if stride_c > 0 else nleft
         sj = stride_j if stride_j > 0 else sc * ncent
         if out is None:
@@ -128,6 +133,37 @@ class HostFunctionAdapter(BatchEvaluator):
         if len(args) == 1:
             return float(self.f([int(v) for v in args[0]]))
         return super().__call__(*args)
+
+
+class ThreadedBatchEvaluator(HostFunctionAdapter):
+    """ThreadedBatchEvaluator (batcheval.jl:247-308): the same element-by-element evaluation of a host callable, with the
+    elements of a batch spread over a pool of host threads (the reference's `Threads.@threads` over `elements`, :300).  Like the
+    reference's it only threads INSIDE one batch call.  Python threads run concurrently only while the callable releases the
+    GIL (numpy / ctypes / I/O-bound functions), which is the case this class is for; an expensive pure function belongs in a
+    device functor (`UserFunction`, tci_functor_from_source)."""
+
+    def __init__(self, f, localdims, nthreads=None, handle=None):
+        super().__init__(f, localdims, handle)
+        import os
+        self.nthreads = int(nthreads) if nthreads else max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+
+    def _host_values(self, lt, rt, cents, vals):
+        from concurrent.futures import ThreadPoolExecutor
+        nleft, nright, ncent = lt.shape[0], rt.shape[0], len(cents)
+        mids = [list(reversed(c)) for c in cents]
+        lrows, rrows = [list(r) for r in lt], [list(r) for r in rt]
+        total = nright * ncent * nleft
+
+        def work(lo, hi):                                    # a contiguous stretch of the (j, c, i) element list
+            for e in range(lo, hi):
+                i, rem = e % nleft, e // nleft
+                c, j = rem % ncent, rem // ncent
+                vals[j, c, i] = self.f(lrows[i] + mids[c] + rrows[j])
+        nt = max(1, min(self.nthreads, total))
+        step = (total + nt - 1) // nt
+        with ThreadPoolExecutor(max_workers=nt) as pool:
+            for fut in [pool.submit(work, lo, min(total, lo + step)) for lo in range(0, total, step)]:
+                fut.result()                                 # re-raises the callable's exception, like @threads does
 
 
 def makebatchevaluatable(f, localdims, handle=None):       # batcheval.jl:57

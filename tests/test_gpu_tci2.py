@@ -187,3 +187,43 @@ def test_sweep0site_matches_oracle(tci):                # sweep0site! / rmbadpiv
     assert t.maxsamplevalue == o.maxsamplevalue
     with pytest.raises(tci.TCIError):
         t.sweep0site(f, 5)
+
+
+def test_threaded_batch_evaluator_equals_serial_adapter(tci):      # ThreadedBatchEvaluator batcheval.jl:247-308
+    """A host callable through the threaded adapter: every batch equals the serial adapter's and the oracle's bit for bit
+    (M = 0, 1, 2 centre sites, empty sets), exceptions propagate, and a whole crossinterpolate2 run reproduces the oracle."""
+    import math
+    import threading
+    ld = [3, 4, 2, 5, 3]
+    seen = set()
+
+    def fun(v):
+        seen.add(threading.get_ident())
+        return math.cos(0.3 * sum((k + 1) * x for k, x in enumerate(v))) + 0.01 * v[0] * v[-1]
+    ser = tci.HostFunctionAdapter(fun, ld)
+    thr = tci.ThreadedBatchEvaluator(fun, ld, nthreads=4)
+    g = O.Func(O.F_CALLBACK, callback=fun)
+    rng = np.random.default_rng(11)
+    for nl, M in [(2, 0), (2, 1), (1, 2), (3, 1)]:
+        nr = len(ld) - nl - M
+        left = np.stack([rng.integers(1, ld[p] + 1, size=7) for p in range(nl)], axis=1)
+        right = np.stack([rng.integers(1, ld[len(ld) - nr + p] + 1, size=5) for p in range(nr)], axis=1)
+        a = tci.to_numpy(thr.evaluate_batch(left, right, M)[0])
+        b = tci.to_numpy(ser.evaluate_batch(left, right, M)[0])
+        np.testing.assert_array_equal(a, b)
+        np.testing.assert_array_equal(a, O.batchevaluate(g, ld, left, right, M))
+    assert len(seen) > 1                                             # the pool really ran the callable on several threads
+    assert thr.evaluate_batch(np.zeros((0, 2), dtype=np.int64), np.ones((3, 3), dtype=np.int64), 0)[0].numel() == 0
+    assert thr([1, 2, 1, 3, 2]) == fun([1, 2, 1, 3, 2])
+
+    def bad(v):
+        raise ValueError("boom")
+    with pytest.raises(ValueError, match="boom"):
+        tci.ThreadedBatchEvaluator(bad, ld, nthreads=2).evaluate_batch(np.ones((2, 2), dtype=np.int64), np.ones((2, 3), dtype=np.int64), 0)
+    t, ranks, errors = tci.crossinterpolate2(thr, ld, tolerance=1e-10, nsearchglobalpivot=0)
+    o, oranks, oerrors = O.crossinterpolate2(g, ld, tolerance=1e-10)
+    assert list(ranks) == list(oranks)
+    np.testing.assert_array_equal(errors, oerrors)
+    for b in range(1, len(ld) + 1):
+        np.testing.assert_array_equal(t.Iset[b - 1], o.Iset(b))
+        np.testing.assert_array_equal(t.Jset[b - 1], o.Jset(b))
