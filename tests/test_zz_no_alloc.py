@@ -69,14 +69,16 @@ def test_noalloc_matches_allocating_entry_point_on_calls_in_a_row(tci):
     for acc in (acc_a, acc_b):
         f0 = work[0][0]
         f0.handle.check(L.tci_maxacc_set(f0.handle.h, C.c_void_p(acc.data_ptr()), C.c_double(1e-9)))
+    import gc
     for rounds in range(2):                                                     # the whole list twice: 12 calls share the array
+        gc.collect()                                                            # objects of earlier tests release their device memory now, not mid-loop
         torch.cuda.synchronize()
         free0 = torch.cuda.mem_get_info(h.device)[0]
         for k, (f, ld, left, right, a, b) in enumerate(work):
             f.handle.check(_call(L, "tci_batcheval_noalloc_f64", f.handle, f, ld, left, right, a, acc_a))
             torch.cuda.synchronize()
-            if rounds == 1:                                                     # round 0 loads the kernels' code lazily; round 1 must not move memory
-                assert torch.cuda.mem_get_info(h.device)[0] == free0, "device memory moved across an allocation-free call"
+            if rounds == 1:                                                     # round 0 loads the kernels' code lazily; round 1 must not take memory
+                assert torch.cuda.mem_get_info(h.device)[0] >= free0, "free device memory shrank across an allocation-free call"
         for k, (f, ld, left, right, a, b) in enumerate(work):
             f.handle.check(_call(L, "tci_batcheval_acc_f64", f.handle, f, ld, left, right, b, acc_b))
             torch.cuda.synchronize()
