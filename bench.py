@@ -244,7 +244,7 @@ def sweep_single_gpu(T, torch, h, engine):
                  "note": "libm (CPU leg) and libdevice differ in the last ulp; bit-exact index-set parity against the oracle fed the "
                          "device values is tests/test_gpu_baseline_configs.py::test_c4_full_size_device_fed_oracle"}
     ld = [20] * 10
-    g, gt = _timed_sweep(T, torch, h, lambda: T.HashFunction(ld, 1.0, 1.0, handle=h), ld, 1, tolerance=1e-10, maxbonddim=256, maxiter=2,
+    g, gt = _timed_sweep(T, torch, h, lambda: T.HashFunction(ld, 1.0, 1.0, handle=h), ld, 2, tolerance=1e-10, maxbonddim=256, maxiter=2,
                          engine=engine, handle=h)
     gs, gts = _timed_sweep(T, torch, h, lambda: T.HashFunction(ld, 1.0, 1.0, handle=h), ld, 1, tolerance=1e-10, maxbonddim=64, maxiter=1,
                            engine=engine, handle=h)

@@ -66,6 +66,7 @@ constexpr int kDesc = 12;
 constexpr int kStepRec = 6;
 constexpr int kRMax = 512;                   // carried functor states (rows of the set that moves with the sweep)
 constexpr int kMaxCS = 8;
+constexpr int kMovCap = 2048;                // resident mode: ints per buffer of the moving set's rows (two buffers)
 constexpr unsigned FULL = 0xffffffffu;
 
 // Argmax candidates.  key = bits of |a|^2 read as a SIGNED 64-bit integer (non-negative doubles order like their bit patterns);
@@ -156,7 +157,9 @@ struct SweepParams {
     long long* prof;                         // diagnostics (TCI_DSWEEP_PROF=1): clock64 cycles thread 0 of CTA 0 spent per phase, else NULL
     void* st_g;                              // functor state of every input table row (prologue), Rtot entries
     unsigned long long* hs_g;                // hash of every input table row
-};
+    int in_words;                            // length of the input arena
+    int resident;                            // single-CTA variant: keep the input arena, the row states and the row hashes in shared
+};                                           // memory for the whole launch (every table access is then ~30 cycles instead of an L2 round trip)
 
 // ---- own elements of the matrix --------------------------------------------------------------------------------------------
 // Columns j with j % CS == crank live in this CTA (local index jl = j / CS).  Small blocks (at most kFlat elements per thread)
@@ -443,11 +446,10 @@ __device__ __forceinline__ void lu_nan_flags(const Carve& c, const int m, const 
 // Table (site b, w): w = 0 Iset[b] (sites 0 .. b-1), 1 Jset[b] (sites b+1 .. N-1), 2 / 3 the history entries of the same
 // shapes.  desc[kDesc b + 8 + w] is the index of the table's first row in the scratch arrays.
 template <class F, int NT, int CS>
-__device__ __forceinline__ void fold_all_rows(const F& f, const int* in, const SweepParams& P, int crank) {
+__device__ __forceinline__ void fold_all_rows(const F& f, const int* in, typename F::State* st, unsigned long long* hs, int crank) {
     typedef typename F::State S;
     const int N = in[0], rtot = in[6];
     const int* desc = in + kHdr + N;
-    S* st = reinterpret_cast<S*>(P.st_g);
     for (int g = crank * NT + threadIdx.x; g < rtot; g += NT * CS) {
         int lo = 0, hi = 4 * N - 1;                        // last table whose base <= g
         while (lo < hi) {
@@ -463,7 +465,7 @@ __device__ __forceinline__ void fold_all_rows(const F& f, const int* in, const S
         unsigned long long hh = 0;
         for (int p = 0; p < len; ++p) { const int v = row[p]; f.push(s, site0 + p, v); hh += mixh(site0 + p, v); }
         st[g] = s;
-        P.hs_g[g] = hh;
+        hs[g] = hh;
     }
 }
 
@@ -486,6 +488,25 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
     const bool writer = crank == 0;
 
     const int* in = P.in;
+    S* stw = reinterpret_cast<S*>(P.st_g);
+    unsigned long long* hsw = P.hs_g;
+    unsigned char* dynb = dyn;               // where the per-bond carve starts
+    int smem_avail = P.smem_bytes;
+    int* s_mov[2] = {nullptr, nullptr};      // resident mode: the moving set's rows also stay in shared memory (double-buffered: a bond
+    int mpar = 0;                            // reads the previous bond's rows while it writes its own)
+    if (CS == 1 && P.resident) {             // tables, states and hashes live in shared memory for the whole launch
+        const int rtot = in[6];
+        int* s_in = reinterpret_cast<int*>(dyn);
+        for (int t = tid; t < P.in_words; t += NT) s_in[t] = in[t];
+        size_t o = ((size_t)P.in_words * 4 + 15) & ~(size_t)15;
+        stw = reinterpret_cast<S*>(dyn + o); o += ((size_t)rtot * sizeof(S) + 15) & ~(size_t)15;
+        hsw = reinterpret_cast<unsigned long long*>(dyn + o); o += ((size_t)rtot * 8 + 15) & ~(size_t)15;
+        s_mov[0] = reinterpret_cast<int*>(dyn + o); o += sizeof(int) * kMovCap;
+        s_mov[1] = reinterpret_cast<int*>(dyn + o); o += sizeof(int) * kMovCap;
+        dynb = dyn + o; smem_avail -= (int)o;
+        __syncthreads();
+        in = s_in;
+    }
     const int N = in[0], fwd = in[1], s0 = in[2], s1 = in[3], maxbond = in[4], useextra = in[5];
     const int* ld = in + kHdr;
     const int* desc = ld + N;
@@ -498,12 +519,12 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
     long long tk0 = clock64();
 #define TCI_DS_PHASE(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tk0; tk0 = t1__; } }
 
-    fold_all_rows<F, NT, CS>(f, in, P, crank);
+    fold_all_rows<F, NT, CS>(f, in, stw, hsw, crank);
     __threadfence();
     cluster_or_block_sync<CS>();
     TCI_DS_PHASE(9)
-    const S* stg = reinterpret_cast<const S*>(P.st_g);
-    const unsigned long long* hsg = P.hs_g;
+    const S* stg = stw;
+    const unsigned long long* hsg = hsw;
 
     const int* mov = nullptr;                // the set that moves with the sweep (Iset[b0] forward, Jset[b0+1] backward) ...
     int nmov = -1;                           // ... -1: take it from the input arena (first step of the launch)
@@ -536,10 +557,10 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         // ---- which extras survive the union (tensorci2.jl:842-843): an extra is a duplicate iff its first b0 entries are a row
         //      of Iset[b0] (the kronecker part holds every digit) / its last entries a row of Jset[b0+1].  Hash match, then an
         //      exact compare; the kept ones in order (first-seen union).  Provisional lists at the start of the dynamic buffer.
-        int* flg = reinterpret_cast<int*>(dyn);                                     // [nXI + nXJ] 1 = keep
+        int* flg = reinterpret_cast<int*>(dynb);                                    // [nXI + nXJ] 1 = keep
         int* keepI0 = flg + nXI + nXJ;
         int* keepJ0 = keepI0 + (nXI > 0 ? nXI : 1);
-        if ((size_t)(2 * (nXI + nXJ) + 4) * sizeof(int) > (size_t)P.smem_bytes) {
+        if ((size_t)(2 * (nXI + nXJ) + 4) * sizeof(int) > (size_t)smem_avail) {
             if (writer && tid == 0) { out[0] = 1; out[1] = s; }
             break;
         }
@@ -594,9 +615,9 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         int myKeepI = -1, myKeepJ = -1;
         if (tid < nKI) myKeepI = keepI0[tid];
         if (tid < nKJ) myKeepJ = keepJ0[tid];
-        const Carve c = carve<S>(dyn, m, n, nloc, rcap, nXI, nXJ, use_flat<NT>(m, nloc));
+        const Carve c = carve<S>(dynb, m, n, nloc, rcap, nXI, nXJ, use_flat<NT>(m, nloc));
         const long long need_out = used + (long long)rcap * (lenXI + lenXJ) + 2 * (rcap + 1) + 2;
-        const bool fits = m >= 1 && n >= 1 && m <= 1024 && n <= 65535 && c.bytes <= (size_t)P.smem_bytes && rcap <= kRMax
+        const bool fits = m >= 1 && n >= 1 && m <= 1024 && n <= 65535 && c.bytes <= (size_t)smem_avail && rcap <= kRMax
                           && nKI <= NT && nKJ <= NT && need_out <= P.out_cap && (CS == 1 || m <= P.mcap);
         if (!fits) {                                   // uniform over the cluster: same inputs everywhere
             if (writer && tid == 0) { out[0] = 1; out[1] = s; }
@@ -660,21 +681,27 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         const long long offA = used, offB = offA + (long long)r * lenXI;
         long long offE = offB + (long long)r * lenXJ; offE += offE & 1;
         const long long endw = offE + 2LL * (r + 1);
+        const bool movres = CS == 1 && s_mov[0] != nullptr && (long long)r * (fwd ? lenXI : lenXJ) <= kMovCap;
+        int* smov = movres ? s_mov[mpar] : nullptr;
         if (writer) {
             int* oa = out + offA; int* ob = out + offB;
-            for (int e = tid; e < r * lenXI; e += NT) {
-                const int kk = e / lenXI, p = e % lenXI, i = c.rowat[kk];
-                int v;
-                if (i < mk) v = (p < lenI) ? tabI[(size_t)(i % nI) * lenI + p] : i / nI + 1;
-                else v = tabXI[(size_t)c.xkeepI[i - mk] * lenXI + p];
-                oa[e] = v;
-            }
-            for (int e = tid; e < r * lenXJ; e += NT) {
-                const int kk = e / lenXJ, p = e % lenXJ, j = c.colat[kk];
-                int v;
-                if (j < nk) v = (p == 0) ? j % dR + 1 : tabJ[(size_t)(j / dR) * lenJ + p - 1];
-                else v = tabXJ[(size_t)c.xkeepJ[j - nk] * lenXJ + p];
-                ob[e] = v;
+            const int nA = r * lenXI, nB = r * lenXJ;                                  // one loop over both sets: their table reads overlap
+            for (int e0 = tid; e0 < nA + nB; e0 += NT) {
+                if (e0 < nA) {
+                    const int e = e0, kk = e / lenXI, p = e % lenXI, i = c.rowat[kk];
+                    int v;
+                    if (i < mk) v = (p < lenI) ? tabI[(size_t)(i % nI) * lenI + p] : i / nI + 1;
+                    else v = tabXI[(size_t)c.xkeepI[i - mk] * lenXI + p];
+                    oa[e] = v;
+                    if (smov && fwd) smov[e] = v;
+                } else {
+                    const int e = e0 - nA, kk = e / lenXJ, p = e % lenXJ, j = c.colat[kk];
+                    int v;
+                    if (j < nk) v = (p == 0) ? j % dR + 1 : tabJ[(size_t)(j / dR) * lenJ + p - 1];
+                    else v = tabXJ[(size_t)c.xkeepJ[j - nk] * lenXJ + p];
+                    ob[e] = v;
+                    if (smov && !fwd) smov[e] = v;
+                }
             }
             double* oe = reinterpret_cast<double*>(out + offE);
             for (int t = tid; t <= r; t += NT) oe[t] = t < r ? fabs(c.piv[t]) : error;
@@ -700,10 +727,10 @@ dsweep_halfsweep_kernel(F f, SweepParams P) {
         for (int q = 0; q < (kRMax + NT - 1) / NT; ++q) { const int t = tid + q * NT; if (t < r) s_carryh[t] = myh[q]; }
         for (int t = tid; t < r; t += NT) carry[t] = fwd ? Lst[c.rowat[t]] : Rst[c.colat[t]];
         used = endw;
-        mov = fwd ? out + offA : out + offB;
+        if (movres) { mov = smov; mpar ^= 1; }         // the next bond reads the rows from shared memory: no fence on the global copy
+        else { mov = fwd ? out + offA : out + offB; __threadfence(); }
         nmov = r;
-        __threadfence();
-        cluster_or_block_sync<CS>();                   // the new rows (global) and the carried states are visible to every thread / CTA
+        cluster_or_block_sync<CS>();                   // the new rows and the carried states are visible to every thread / CTA
         TCI_DS_PHASE(8)
     }
     if (pc) for (int q = 0; q < 16; ++q) P.prof[q] = pcnt[q];
@@ -841,7 +868,7 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
     int* out = P.out;
     long long used = kHdr + (long long)kStepRec * (N - 1);
     if (tid == 0) { out[0] = 0; out[1] = N - 1; out[2] = (int)used; }
-    fold_all_rows<F, NT, 1>(f, in, P, 0);
+    fold_all_rows<F, NT, 1>(f, in, reinterpret_cast<S*>(P.st_g), P.hs_g, 0);
     __syncthreads();
     const S* stg = reinterpret_cast<const S*>(P.st_g);
     const int* mov = in + desc[1]; int nmov = desc[0];       // Iset[0]
@@ -1022,6 +1049,13 @@ int run_halfsweep(tci_handle h, const F& f, SweepParams P, const SweepShape& sh,
     const size_t one = sizeof(double) * lds1 * ((size_t)sh.maxn + 1) + 48 * (lds1 + 128 + (size_t)sh.maxn) + 4096;
     int cs = one <= (size_t)kDynBytes ? 1 : kMaxCS;
     if (force_cs == 1 || force_cs == kMaxCS) cs = force_cs;
+    // resident tables (single CTA): arena + state + 8 B hash per row, if 1.5 x the predicted Pi carve still fits beside them (the
+    // moving set may grow; a bond that does not fit the reduced space is handed back to the host like any other that does not fit)
+    const size_t nrows = (size_t)P.resident;                                     // the row count on entry
+    const size_t res = (((size_t)P.in_words * 4 + 15) & ~(size_t)15) + ((nrows * sizeof(typename F::State) + 15) & ~(size_t)15)
+                       + ((nrows * 8 + 15) & ~(size_t)15) + 2 * sizeof(int) * kMovCap;
+    static const bool no_res = getenv("TCI_DSWEEP_NORESIDENT") != nullptr;
+    P.resident = (cs == 1 && !no_res && res + one + one / 2 <= (size_t)kDynBytes) ? 1 : 0;
     if (cs == 1) {
         const char* ne = getenv("TCI_DSWEEP_NT");          // experiments: force the block size of the single-CTA variant
         const int nt = ne ? atoi(ne) : (sh.maxelems <= 4096 ? 256 : 1024);
@@ -1160,6 +1194,7 @@ int tci_dsweep_halfsweep_f64(tci_handle h, tci_functor f, const int32_t* h_in, i
     const bool prof = getenv("TCI_DSWEEP_PROF") != nullptr;
     P.prof = prof ? (long long*)(base + in_b + out_b + xs_b) : nullptr;
     P.st_g = base + in_b + out_b + xs_b + 512; P.hs_g = (unsigned long long*)(base + in_b + out_b + xs_b + 512 + st_b);
+    P.in_words = (int)in_words; P.resident = (int)rtot;    // run_halfsweep turns the row count into the residency decision
     const double th1 = hostprof ? now() : 0.0;
     TCI_CUDA(h, cudaMemcpyAsync(base, h_in, (size_t)in_words * 4, cudaMemcpyHostToDevice, h->stream));
     const double th2 = hostprof ? now() : 0.0;
@@ -1266,7 +1301,7 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, 
     TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
     Sweep1Params Q;
     Q.sp.in = (const int*)base; Q.sp.out = (int*)(base + in_b); Q.sp.out_cap = out_cap_words; Q.sp.reltol = reltol; Q.sp.abstol = abstol;
-    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.prof = nullptr;
+    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.prof = nullptr; Q.sp.in_words = (int)in_words; Q.sp.resident = 0;
     Q.sp.st_g = base + in_b + out_b; Q.sp.hs_g = (unsigned long long*)(base + in_b + out_b + st_b);
     Q.cores = (double* const*)(base + off_c); Q.corecap = (const long long*)(base + off_k);
     TCI_DS_DISPATCH(rc, f, launch_sweep1(h, F_, Q, maxelems))
