@@ -211,22 +211,21 @@ __device__ __forceinline__ long long abs2_key(double v) {                       
     return __double_as_longlong(fmax(__dmul_rn(v, v), -1.0));                    // fmax(NaN, x) = x
 }
 
-// Candidate update for one element, branch-free (predicates and selects only; written in PTX because the compiler turns the
-// C++ form into three branches per element): the element counts iff apos >= np (apos = its smaller position) and q = v^2 is
-// not NaN; then (key = bits(q), pos) replaces (bkey, bpos) iff key > bkey, or key == bkey and pos < bpos — the reference's
-// scan order (matrixlu.jl:46-87: largest abs2, then smallest column, then smallest row, in swapped coordinates).
-__device__ __forceinline__ void take_elem(long long& bkey, unsigned& bpos, double q, int apos, int np, unsigned pos) {
-    asm("{\n\t.reg .pred ok, eq, b;\n\t.reg .b64 k;\n\t"
-        "setp.ge.s32 ok, %3, %4;\n\t"
-        "setp.eq.and.f64 ok, %2, %2, ok;\n\t"
-        "mov.b64 k, %2;\n\t"
-        "selp.b64 k, k, 0x8000000000000000, ok;\n\t"
-        "setp.eq.s64 eq, k, %0;\n\t"
-        "setp.lt.and.u32 b, %5, %1, eq;\n\t"
-        "setp.gt.or.s64 b, k, %0, b;\n\t"
-        "selp.b64 %0, k, %0, b;\n\t"
-        "selp.b32 %1, %5, %1, b;\n\t}"
-        : "+l"(bkey), "+r"(bpos) : "d"(q), "r"(apos), "r"(np), "r"(pos));
+// Candidate update for one element, branch-free (predicates and selects only; written in PTX because the compiler turns the C++ form
+// into three branches per element, and the reference's test functions are symmetric, so ties are common).  (q = v^2, pos) replaces
+// (bq, bpos) iff q > bq, or q == bq and pos < bpos — the reference's scan order (matrixlu.jl:46-87: largest abs2, then smallest
+// column, then smallest row, in swapped coordinates).
+// q = v^2 is a non-negative double or NaN, and non-negative doubles order like their bit patterns, so the FP64 compares decide
+// exactly what compares of the integer keys (warp_argmax) decide — in 3 predicate instructions.  A NaN q (a NaN entry, or an element the caller poisoned because it is not active) compares false everywhere: never taken.
+// bq = -1.0 means "no candidate yet".
+__device__ __forceinline__ void take_elem_f(double& bq, unsigned& bpos, double q, unsigned pos) {
+    asm("{\n\t.reg .pred eq, b;\n\t"
+        "setp.eq.f64 eq, %2, %0;\n\t"
+        "setp.lt.and.u32 b, %3, %1, eq;\n\t"
+        "setp.gt.or.f64 b, %2, %0, b;\n\t"
+        "selp.f64 %0, %2, %0, b;\n\t"
+        "selp.b32 %1, %3, %1, b;\n\t}"
+        : "+d"(bq), "+r"(bpos) : "d"(q), "r"(pos));
 }
 
 // keep (bk, bi, bj) = the first element in the reference's scan order among those seen: larger key, then smaller position
@@ -264,7 +263,10 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
     // this thread's candidate as (key, position): the searches below track the position directly — one branch-free
     // lexicographic compare per element instead of a compare with a divergent tie branch that re-reads the position maps
     unsigned bpos = bkey >= 0 ? ((unsigned)c.colpos[bj] << 16) | (unsigned)c.rowpos[bi] : 0xffffffffu;
+    double bq = bkey >= 0 ? __longlong_as_double(bkey) : -1.0;                      // the candidate's v^2 (take_elem_f)
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
     for (;;) {
+        bkey = __double_as_longlong(bq);                                            // -1.0 -> negative key: no candidate
         if (bkey < 0) bpos = 0xffffffffu;
         warp_argmax(bkey, bpos);
         KP* sw = s_w[np & 1];
@@ -337,8 +339,10 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
         TCI_DS_TICK(2)
         np = k + 1;
         if (np >= rcap) break;                                                      // :356
-        bkey = kNoKey; bpos = 0xffffffffu;
-        // :316-320 + the next search (take_elem): loads first, then arithmetic, then the candidate selection
+        bq = -1.0; bpos = 0xffffffffu;
+        double bq1 = -1.0; unsigned bpos1 = 0xffffffffu;                            // a second, independent candidate chain (odd elements): the
+        // rule is a total order, so the two are merged by one more take at the end — half the dependent chain per element
+        // :316-320 + the next search (take_elem_f): loads first, then arithmetic, then the candidate selection
         if (own.flat) {
 #pragma unroll
             for (int q0 = 0; q0 < kFlat; q0 += 2) {
@@ -354,10 +358,11 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
                     }
 #pragma unroll
                     for (int u = 0; u < 2; ++u) {
-                        const int apos = ok[u] ? min(rp[u], cp[u]) : -1;
+                        const bool act = ok[u] && min(rp[u], cp[u]) >= np;
                         const double v = __dsub_rn(av[u], __dmul_rn(xv[u], yv[u]));
-                        if (apos >= np) *ap[u] = v;
-                        take_elem(bkey, bpos, __dmul_rn(v, v), apos, np, ((unsigned)cp[u] << 16) | (unsigned)rp[u]);
+                        if (act) *ap[u] = v;
+                        if (u == 0) take_elem_f(bq, bpos, act ? __dmul_rn(v, v) : qnan, ((unsigned)cp[u] << 16) | (unsigned)rp[u]);
+                        else take_elem_f(bq1, bpos1, act ? __dmul_rn(v, v) : qnan, ((unsigned)cp[u] << 16) | (unsigned)rp[u]);
                     }
                 }
             }
@@ -370,7 +375,10 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
                 const int i0 = g * 128 + lane;
                 int rp[4]; double xv[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) { rp[u] = c.rowpos[i0 + 32 * u]; xv[u] = c.xs[i0 + 32 * u]; }
+                for (int u = 0; u < 4; ++u) {                                        // rows that are not active carry x = NaN: their v^2 is NaN,
+                    rp[u] = c.rowpos[i0 + 32 * u];                                  // which take_elem_f never takes (padding rows have position -1)
+                    xv[u] = rp[u] >= np ? c.xs[i0 + 32 * u] : qnan;
+                }
                 TCI_DS_TICK(14)
                 if (__any_sync(FULL, rp[0] >= np || rp[1] >= np || rp[2] >= np || rp[3] >= np)) {
                     for (int jl = jl0; jl < own.nown; jl += wpg) {
@@ -385,13 +393,15 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
                             const double v = __dsub_rn(av[u], __dmul_rn(xv[u], y));
-                            if (rp[u] >= np) col[32 * u] = v;                       // padding rows carry position -1
-                            take_elem(bkey, bpos, __dmul_rn(v, v), rp[u], np, cp16 | (unsigned)rp[u]);
+                            if (rp[u] >= np) col[32 * u] = v;
+                            if ((u & 1) == 0) take_elem_f(bq, bpos, __dmul_rn(v, v), cp16 | (unsigned)rp[u]);
+                            else take_elem_f(bq1, bpos1, __dmul_rn(v, v), cp16 | (unsigned)rp[u]);
                         }
                     }
                 }
             }
         }
+        take_elem_f(bq, bpos, bq1, bpos1);
         TCI_DS_TICK(3)
     }
     const int r = np;
