@@ -378,8 +378,12 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":      # NCCL prints its version banner to STDOUT: keep stdout to the JSON line
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL prints its version banner from C to file descriptor 1.  Keep stdout to the ONE JSON line: Python's sys.stdout moves
+        # to a duplicate of the original descriptor, descriptor 1 itself is pointed at stderr for everything native.
+        sys.stdout.flush()
+        keep = os.dup(1)
+        os.dup2(2, 1)
+        sys.stdout = os.fdopen(keep, "w", buffering=1)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     dev = torch.device(f"cuda:{local}")
     h = tci_b200.Handle(local)
