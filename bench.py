@@ -295,17 +295,27 @@ def sweep_multi_gpu(T, torch, dist, h, comm, world, rank):
                     "sharded_bonds": int(sh.stats.get("nsharded", 0)), "pivot_sets_identical_to_one_gpu": bool(flag.item() == 1.0)}}
 
 
+K1_HEAVY_SRC = """
+__device__ double tci_user_f(const int* idx, int n, const double* p, int np) {
+    double s = 0.0;
+    for (int i = 0; i < n; ++i) s += sin(p[0] * idx[i] * (i + 1)) * exp(-p[1] * idx[i]);
+    return s / (1.0 + s * s);
+}
+"""
+
+
 def _k1_sharded(T, torch, dist, h, comm, world, dev):
     """north_star partition 1: ONE Pi fill of the C3 worst-case shape (5120 x 5120, 26.2 M evaluations, 210 MB) with
     the evaluations split over the ranks and every rank's block stored straight into every peer's copy of Pi by the evaluation
-    kernel (fused compute + all-gather over peer memory); against the same fill done entirely on every rank.  Device-side wall
-    time, max over ranks; the assembled matrix must equal the local one bit for bit on every rank."""
+    kernel (fused compute + all-gather over peer memory); against the same fill done entirely on every rank.  Two functors: the
+    cheap built-in hash functor (HBM-write-bound: the split cannot pay, NVLink moves 8 B per value) and an arithmetic-heavy
+    NVRTC plugin functor (20 sin + 20 exp per value: the split pays).  Device-side wall time, max over ranks; the assembled
+    matrix must equal the local one bit for bit on every rank."""
     ld = [20] * 10
     rng = np.random.default_rng(0)
     nI = nJ = 5120
     left = rng.integers(1, 21, size=(nI, 5)).astype(np.int32)
     right = rng.integers(1, 21, size=(nJ, 5)).astype(np.int32)
-    f = T.HashFunction(ld, 1.0, 1.0, handle=h)
     buf = torch.empty(nI * nJ, dtype=torch.float64, device=dev)
 
     def timed(fn, reps=5):
@@ -320,30 +330,31 @@ def _k1_sharded(T, torch, dist, h, comm, world, dev):
         t = torch.tensor([min(ts)], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
-    t_local = timed(lambda: f.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
-    ga = T.ShardedBatchEvaluator(f, comm)
-    t_gather = timed(lambda: ga.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
-    fu = T.ShardedBatchEvaluator(f, comm, fused=True)
+    out = {"config": "Pi fill 5120 x 5120 (C3 worst-case bond), columns of Pi over the ranks; per functor: everything on every rank / split + NCCL "
+                     "all-gather / split + fused peer stores", "evals": nI * nJ}
+    for name, f in (("hash", T.HashFunction(ld, 1.0, 1.0, handle=h)), ("heavy_plugin", T.UserFunction(K1_HEAVY_SRC, ld, [0.37, 0.05], handle=h))):
+        t_local = timed(lambda: f.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
+        ga = T.ShardedBatchEvaluator(f, comm)
+        t_gather = timed(lambda: ga.evaluate_batch(left, right, 0, out=buf, stride_c=nI, stride_j=nI, maxabs=0.0))
+        fu = T.ShardedBatchEvaluator(f, comm, fused=True)
 
-    def fused():
-        m = fu.alloc_matrix(nI, nJ, 16)
-        o = m.buf if m is not None else buf
-        fu.evaluate_batch(left, right, 0, out=o, stride_c=nI, stride_j=nI, maxabs=0.0)
-        return o
-    t_fused = timed(fused)
-    ref = f.evaluate_batch(left, right, 0, out=torch.empty_like(buf), stride_c=nI, stride_j=nI)[0]
-    o = fused()
-    torch.cuda.synchronize(); dist.barrier()
-    same = torch.tensor([1.0 if torch.equal(o.reshape(-1)[: nI * nJ], ref.reshape(-1)[: nI * nJ]) else 0.0], dtype=torch.float64, device=dev)
-    dist.all_reduce(same, op=dist.ReduceOp.MIN)
-    return {"K1_sharded": {"config": "Pi fill 5120 x 5120 (C3 worst-case bond), full-rank hash functor, columns of Pi over the ranks",
-                           "note": "the hash functor costs ~5 ns per 1000 evaluations per SM: evaluating everything on every rank is cheaper than "
-                                   "moving 8 B per value over NVLink; the split pays for arithmetic-heavy functors (benchmarks/multigpu_bench.py, "
-                                   "heavy_plugin) and, in the sweep, because the sharded rrLU wants column blocks anyway",
-                           "evals": nI * nJ, "local_ms": 1e3 * t_local, "sharded_nccl_allgather_ms": 1e3 * t_gather,
-                           "sharded_fused_peer_store_ms": 1e3 * t_fused, "evals_per_s": nI * nJ / t_fused,
-                           "nvlink_GBps_per_rank": 8 * nI * nJ * (world - 1) / world / t_fused / 1e9,
-                           "identical_to_local_on_every_rank": bool(same.item() == 1.0)}}
+        def fused():
+            m = fu.alloc_matrix(nI, nJ, 16)
+            o = m.buf if m is not None else buf
+            fu.evaluate_batch(left, right, 0, out=o, stride_c=nI, stride_j=nI, maxabs=0.0)
+            return o
+        t_fused = timed(fused)
+        ref = f.evaluate_batch(left, right, 0, out=torch.empty_like(buf), stride_c=nI, stride_j=nI)[0]
+        o = fused()
+        torch.cuda.synchronize(); dist.barrier()
+        same = torch.tensor([1.0 if torch.equal(o.reshape(-1)[: nI * nJ], ref.reshape(-1)[: nI * nJ]) else 0.0], dtype=torch.float64, device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        out[name] = {"local_ms": 1e3 * t_local, "sharded_nccl_allgather_ms": 1e3 * t_gather, "sharded_fused_peer_store_ms": 1e3 * t_fused,
+                     "evals_per_s": nI * nJ / min(t_local, t_fused), "speedup_fused_vs_local": t_local / t_fused,
+                     "nvlink_GBps_per_rank": 8 * nI * nJ * (world - 1) / world / t_fused / 1e9,
+                     "identical_to_local_on_every_rank": bool(same.item() == 1.0)}
+        del fu, ga
+    return {"K1_sharded": out}
 
 
 def _oddeven_sweep(T, torch, dist, f, ld, kw, comm, dev, timed, t_seq):
