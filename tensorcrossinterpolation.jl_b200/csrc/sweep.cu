@@ -419,24 +419,30 @@ __device__ __forceinline__ void lu_nan_flags(const Carve& c, const int m, const 
     const double* A = c.A;
     const int lds = c.lds;
     int flags = 0;
+    // The scaled entries a / pivot are not formed here: an IEEE quotient is NaN exactly when a or the pivot is NaN, or both are
+    // zero, or both are infinite — three compares instead of a division per entry.
     for (int t = warp; t < r; t += NW) {
         const int ct = c.colat[t], rt = c.rowat[t];
         const double pv = c.piv[t];
+        const bool pvnan = pv != pv, pvzero = pv == 0.0, pvinf = isinf(pv);
         if (ct % CS == crank) {
             const double* col = A + (size_t)(ct / CS) * lds;
             for (int i = lane; i < m; i += 32) {
                 const int p = c.rowpos[i];
                 if (p < t) continue;
-                const double v = (fwd && p > t) ? col[i] / pv : col[i];
-                if (v != v) flags |= 1;
+                const double a = col[i];
+                bool bad = a != a;
+                if (fwd && p > t) bad = bad || pvnan || (pvzero && a == 0.0) || (pvinf && isinf(a));
+                if (bad) flags |= 1;
             }
         }
         for (int j = crank + CS * lane; j < n; j += CS * 32) {
             const int q = c.colpos[j];
             if (q < t) continue;
             const double a = A[(size_t)(j / CS) * lds + rt];
-            const double v = (!fwd && q > t) ? a / pv : a;
-            if (v != v) flags |= 2;
+            bool bad = a != a;
+            if (!fwd && q > t) bad = bad || pvnan || (pvzero && a == 0.0) || (pvinf && isinf(a));
+            if (bad) flags |= 2;
         }
     }
     if (flags) atomicOr(s_flags, flags);
@@ -878,8 +884,14 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
     int* out = P.out;
     long long used = kHdr + (long long)kStepRec * (N - 1);
     if (tid == 0) { out[0] = 0; out[1] = N - 1; out[2] = (int)used; }
+    __shared__ long long pcnt1[8];                       // diagnostics (TCI_DSWEEP_PROF=1): cycles of thread 0 per phase
+    long long* pc = (P.prof && tid == 0) ? pcnt1 : nullptr;
+    if (pc) for (int q = 0; q < 8; ++q) pcnt1[q] = 0;
+    long long tk0 = clock64();
+#define TCI_S1_PHASE(slot) { if (pc) { const long long t1__ = clock64(); pc[slot] += t1__ - tk0; tk0 = t1__; } }
     fold_all_rows<F, NT, 1>(f, in, reinterpret_cast<S*>(P.st_g), P.hs_g, 0);
     __syncthreads();
+    TCI_S1_PHASE(0)
     const S* stg = reinterpret_cast<const S*>(P.st_g);
     const int* mov = in + desc[1]; int nmov = desc[0];       // Iset[0]
     bool carried = false;
@@ -917,6 +929,7 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
         for (int t = m + tid; t < c.mp; t += NT) { c.rowpos[t] = -1; c.xs[t] = 0.0; }
         if (tid == 0) s_flags = 0;
         __syncthreads();
+        TCI_S1_PHASE(1)
         double* A = c.A; const int lds = c.lds;
         const Own own = own_elements<NT, 1>(c, m, n, n, 0);
         long long bkey = kNoKey; int bi = 0, bj = 0;
@@ -928,9 +941,12 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
             const long long kq = abs2_key(v);
             TCI_DS_TAKE(kq, i, j, bkey, bi, bj)
         });
+        TCI_S1_PHASE(2)
         double error;
         const int r = smem_rrlu<NT, 1>(c, own, m, n, rcap, 1, P.reltol, P.abstol, bkey, bi, bj, s_w, s_cl, P, 0, &error);
+        TCI_S1_PHASE(3)
         lu_nan_flags<NT, 1>(c, m, n, r, 1, 0, &s_flags);
+        TCI_S1_PHASE(4)
         if (s_flags) { if (tid == 0) { out[0] = (s_flags & 1) ? 2 : 3; out[1] = b0; } stopped = true; break; }
         // ---- new index sets and pivot errors
         const int lenA = b0 + 1, lenB = lenJ;
@@ -952,6 +968,7 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
                 out[2] = (int)endw;
             }
         }
+        TCI_S1_PHASE(5)
         // ---- T_b = left(luci): rows at pivot positions are unit vectors, the others L2 inv(L1) by back substitution, in place
         for (int e = tid; e < r * r; e += NT) {
             const int j = e / r, t = e % r;                                         // L1(j, t), j > t
@@ -978,7 +995,9 @@ dsweep_sweep1site_kernel(F f, Sweep1Params Q) {
         used = endw; mov = out + offA; nmov = r; carried = true;
         __threadfence();
         __syncthreads();
+        TCI_S1_PHASE(6)
     }
+    if (pc) for (int q = 0; q < 8; ++q) P.prof[q] = pcnt1[q];
     if (!stopped) {                                                                // last tensor by evaluation (:719-723)
         const int b0 = N - 1, d = ld[b0];
         const int nI = nmov;
@@ -1105,7 +1124,8 @@ int launch_fill(tci_handle h, const F& f, const FillParams& P, int nblocks, int 
 template <class F>
 int launch_sweep1(tci_handle h, const F& f, Sweep1Params Q, long long maxelems) {
     Q.sp.smem_bytes = kDynBytes;
-    if (maxelems <= 4096) {
+    static const int force_nt = getenv("TCI_DSWEEP_S1NT") ? atoi(getenv("TCI_DSWEEP_S1NT")) : 0;     // experiments
+    if (force_nt == 256 || (force_nt != 1024 && maxelems <= 8192)) {      // measured at C3 (360 x 18 per bond): 256 threads 1.06 ms, 1024 threads 1.28 ms
         auto kern = dsweep_sweep1site_kernel<F, 256>;
         static thread_local int optin_a = 0;
         if (!optin_a) { TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynBytes)); optin_a = 1; }
@@ -1306,17 +1326,26 @@ int tci_dsweep_sweep1site_f64(tci_handle h, tci_functor f, const int32_t* h_in, 
     const size_t off_k = st.add(cap.data(), sizeof(long long) * (size_t)N);
     const size_t in_b = (st.bytes.size() + 255) & ~(size_t)255, out_b = ((size_t)out_cap_words * 4 + 255) & ~(size_t)255;
     const size_t rtot = (size_t)std::max(h_in[6], 0), st_b = (rtot * 16 + 255) & ~(size_t)255, hs_b = (rtot * 8 + 255) & ~(size_t)255;
-    rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + st_b + hs_b + 256); if (rc) return rc;
+    rc = tci_ws_reserve(h, h->ws_c, in_b + out_b + st_b + hs_b + 512); if (rc) return rc;
     unsigned char* base = (unsigned char*)h->ws_c.ptr;
     TCI_CUDA(h, cudaMemcpyAsync(base, st.bytes.data(), st.bytes.size(), cudaMemcpyHostToDevice, h->stream));
+    const bool prof1 = getenv("TCI_DSWEEP_PROF") != nullptr;
     Sweep1Params Q;
     Q.sp.in = (const int*)base; Q.sp.out = (int*)(base + in_b); Q.sp.out_cap = out_cap_words; Q.sp.reltol = reltol; Q.sp.abstol = abstol;
-    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.prof = nullptr; Q.sp.in_words = (int)in_words; Q.sp.resident = 0;
+    Q.sp.acc = (unsigned long long*)d_acc16; Q.sp.xs_g = nullptr; Q.sp.mcap = 0; Q.sp.smem_bytes = kDynBytes; Q.sp.in_words = (int)in_words; Q.sp.resident = 0;
+    Q.sp.prof = prof1 ? (long long*)(base + in_b + out_b + st_b + hs_b + 256) : nullptr;
     Q.sp.st_g = base + in_b + out_b; Q.sp.hs_g = (unsigned long long*)(base + in_b + out_b + st_b);
     Q.cores = (double* const*)(base + off_c); Q.corecap = (const long long*)(base + off_k);
     TCI_DS_DISPATCH(rc, f, launch_sweep1(h, F_, Q, maxelems))
     if (rc) return rc;
-    return read_out(h, Q.sp.out, h_out, out_cap_words, h_used_words, "tci_dsweep_sweep1site_f64");
+    rc = read_out(h, Q.sp.out, h_out, out_cap_words, h_used_words, "tci_dsweep_sweep1site_f64");
+    if (rc == TCI_OK && prof1) {
+        long long pcs[8];
+        TCI_CUDA(h, cudaMemcpy(pcs, Q.sp.prof, sizeof pcs, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "dsweep1 prof (cycles): prologue=%lld states=%lld fill=%lld lu=%lld nan=%lld output=%lld left+carry=%lld\n", pcs[0], pcs[1],
+                pcs[2], pcs[3], pcs[4], pcs[5], pcs[6]);
+    }
+    return rc;
 }
 
 } // extern "C"
