@@ -32,8 +32,8 @@ KERNELS = [
      r"18rrlu_update_kernelILb1ELb1ELi8E", r"LDG\.E\.128|DMUL|DADD|STG\.E\.128"),
     ("gemm_dmma_pipe_kernel<0,1> — K4 FP64 tensor-core GEMM (csrc/dense.cu)", "dense.o",
      r"gemm_dmma_pipe_kernelILb0ELb1E", r"DMMA|LDGSTS"),
-    ("dsweep_halfsweep_kernel<LorentzF, 1024, 8> — device-resident half-sweep, cluster variant (csrc/sweep.cu)", "sweep.o",
-     r"dsweep_halfsweep_kernelIN12tci_functors8LorentzFELi1024ELi8E", r"CREDUX|UCGABAR|DMUL|DADD"),
+    ("dsweep_halfsweep_kernel<LorentzF, 512, 8> — device-resident half-sweep, cluster variant (csrc/sweep.cu)", "sweep.o",
+     r"dsweep_halfsweep_kernelIN12tci_functors8LorentzFELi512ELi8E", r"CREDUX|UCGABAR|DMUL|DADD"),
     ("assemble4_kernel<LorentzUnitF> — K1 Pi assembly (csrc/batcheval.cu)", "batcheval.o",
      r"assemble4_kernelIN12tci_functors12LorentzUnitF", r"STG\.E\.128|MUFU\.RCP64H"),
 ]

@@ -42,6 +42,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <type_traits>
 #include <vector>
 
 namespace cg = cooperative_groups;
@@ -1085,13 +1086,16 @@ int run_halfsweep(tci_handle h, const F& f, SweepParams P, const SweepShape& sh,
                        + ((nrows * 8 + 15) & ~(size_t)15) + 2 * sizeof(int) * kMovCap;
     static const bool no_res = getenv("TCI_DSWEEP_NORESIDENT") != nullptr;
     P.resident = (cs == 1 && !no_res && res + one + one / 2 <= (size_t)kDynBytes) ? 1 : 0;
+    // Block size of the larger variants: 512 threads, not 1024.  At 1024 the 64-register ceiling spills in the update loop (120 B of
+    // local memory per thread in the single-CTA kernel, 336 B in the cluster kernel); at 512 nothing spills and the update, which is
+    // issue-bound, loses nothing: C1 2.83 -> 2.52 ms, C3 13.25 -> 11.7 ms (A/B in one run).
     if (cs == 1) {
-        const char* ne = getenv("TCI_DSWEEP_NT");          // experiments: force the block size of the single-CTA variant
-        const int nt = ne ? atoi(ne) : (sh.maxelems <= 4096 ? 256 : 1024);
+        const char* ne = getenv("TCI_DSWEEP_NT");          // experiments: force the block size of the single-CTA variant (256 | 512)
+        const int nt = ne ? atoi(ne) : (sh.maxelems <= 4096 ? 256 : 512);
         if (nt == 256) return launch_halfsweep<F, 256, 1>(h, f, P, kDynBytes);
-        return launch_halfsweep<F, 1024, 1>(h, f, P, kDynBytes);
+        return launch_halfsweep<F, 512, 1>(h, f, P, kDynBytes);
     }
-    return launch_halfsweep<F, 1024, kMaxCS>(h, f, P, kDynBytes);
+    return launch_halfsweep<F, 512, kMaxCS>(h, f, P, kDynBytes);
 }
 
 
@@ -1125,16 +1129,16 @@ template <class F>
 int launch_sweep1(tci_handle h, const F& f, Sweep1Params Q, long long maxelems) {
     Q.sp.smem_bytes = kDynBytes;
     static const int force_nt = getenv("TCI_DSWEEP_S1NT") ? atoi(getenv("TCI_DSWEEP_S1NT")) : 0;     // experiments
-    if (force_nt == 256 || (force_nt != 1024 && maxelems <= 8192)) {      // measured at C3 (360 x 18 per bond): 256 threads 1.06 ms, 1024 threads 1.28 ms
+    if (force_nt == 256 || (force_nt != 512 && maxelems <= 8192)) {       // measured at C3 (360 x 18 per bond): 256 threads 1.06 ms, 1024 threads 1.28 ms
         auto kern = dsweep_sweep1site_kernel<F, 256>;
         static thread_local int optin_a = 0;
         if (!optin_a) { TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynBytes)); optin_a = 1; }
         kern<<<1, 256, kDynBytes, h->stream>>>(f, Q);
     } else {
-        auto kern = dsweep_sweep1site_kernel<F, 1024>;
+        auto kern = dsweep_sweep1site_kernel<F, 512>;
         static thread_local int optin_b = 0;
         if (!optin_b) { TCI_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kDynBytes)); optin_b = 1; }
-        kern<<<1, 1024, kDynBytes, h->stream>>>(f, Q);
+        kern<<<1, 512, kDynBytes, h->stream>>>(f, Q);
     }
     TCI_LAUNCH_CHECK(h);
     return TCI_OK;
