@@ -120,7 +120,9 @@ struct Carve {                               // dynamic shared memory of one bon
 
 constexpr int kFlat = 8;                     // flat element -> thread map: at most this many elements per thread
 
-template <int NT> __host__ __device__ inline bool use_flat(int m, int nloc) { return (long long)m * nloc <= (long long)kFlat * NT; }
+// (only the 256-thread kernels use it: the larger variants are dispatched for blocks that are too big for it anyway, and without the
+// flat path their register budget of 128 holds the update loop without spills)
+template <int NT> __host__ __device__ inline bool use_flat(int m, int nloc) { return NT <= 256 && (long long)m * nloc <= (long long)kFlat * NT; }
 
 template <class S>
 __host__ __device__ inline Carve carve(unsigned char* base, int m, int n, int nloc, int rcap, int nXI, int nXJ, bool flat) {
