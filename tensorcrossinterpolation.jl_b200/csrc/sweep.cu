@@ -299,11 +299,12 @@ __device__ __forceinline__ int smem_rrlu(const Carve& c, const Own& own, const i
             TCI_DS_TICK(12)
             cl.sync();                                                              // the one cluster barrier of the step
             TCI_DS_TICK(13)
-            gkey = s_cl[par][0].key; gpos = s_cl[par][0].pos; owner = 0;
-#pragma unroll
-            for (int cc = 1; cc < CS; ++cc) {
-                const long long ok = s_cl[par][cc].key; const unsigned op = s_cl[par][cc].pos;
-                if (ok > gkey || (ok == gkey && op < gpos)) { gkey = ok; gpos = op; owner = cc; }
+            {   // the winner among the CS records: one record per lane, the warp-wide argmax (uniform), then the first lane that holds it
+                const long long myk = lane < CS ? s_cl[par][lane].key : kNoKey;
+                const unsigned myp = lane < CS ? s_cl[par][lane].pos : 0xffffffffu;
+                gkey = myk; gpos = myp;
+                warp_argmax(gkey, gpos);
+                owner = __ffs(__ballot_sync(FULL, lane < CS && myk == gkey && myp == gpos)) - 1;
             }
             piv = s_cl[par][owner].x;
             if (gkey >= 0) { pi = c.rowat[gpos & 0xffffu]; pj = c.colat[gpos >> 16]; }
