@@ -56,6 +56,17 @@ def p_i32(a):
     return a.ctypes.data_as(C.POINTER(C.c_int32))
 
 
+def _raw_stream(device):
+    """torch's current stream on `device` as an integer.  torch._C._cuda_getCurrentRawStream is the sub-microsecond accessor
+    (torch.cuda.current_stream builds a Stream object: ~10 us, and Handle.h is read before EVERY library call — 1.5 M times in
+    one contract_TCI run at BASELINE C5 size)."""
+    import torch
+    get = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+    if get is not None:
+        return int(get(int(device)))
+    return int(torch.cuda.current_stream(device).cuda_stream)
+
+
 class Handle:
     """One tci_handle = one CUDA device + stream + workspaces (not thread-safe)."""
 
@@ -76,8 +87,7 @@ class Handle:
         library kernels left on the stream bound at construction would race with them (read-before-write on Pi and the
         factors).  One pointer compare per call when nothing changed."""
         try:
-            import torch
-            s = torch.cuda.current_stream(self.device).cuda_stream
+            s = _raw_stream(self.device)
         except Exception:                                   # no CUDA device: calls fail loudly in the library itself
             return self._h
         if s != self._stream:
