@@ -157,7 +157,12 @@ class Contraction(BatchEvaluator):
             return
         cache = self.leftcache if left else self.rightcache
         L, N, h = len(rows[0]), len(self), self.handle
-        for lev in range(1, L + 1):
+        first = 1                                                       # the deepest level that is already complete (in a sweep: L - 1)
+        for lev in range(L, 0, -1):
+            if all((r[:lev] if left else r[L - lev:]) in cache for r in rows):
+                first = lev + 1
+                break
+        for lev in range(first, L + 1):
             missing = [k for k in {(r[:lev] if left else r[L - lev:]) for r in rows} if k not in cache]
             if not missing:
                 continue
